@@ -1,0 +1,167 @@
+/*
+ * margin_b200.h — C ABI of the B200-native pair-HMM hot path of MarginPolish.
+ *
+ * This is the drop-in boundary.  Everything is plain C: POD
+ * structs, pointers and sizes.  No torch / sonLib / margin types appear here.
+ * The reference-side binding (how `pairwiseAligner.h`'s stList/SymbolString
+ * entry points are routed onto these calls) is shown in INTEGRATION.md and
+ * implemented in compat/pairwiseAligner_b200.c.
+ *
+ * Reference interfaces replaced (all paths relative to the margin tree):
+ *   margin_b200_posteriors_batch  <- getAlignedPairsWithIndelsUsingAnchors  inc/pairwiseAligner.h:81-84
+ *                                    getAlignedPairsUsingAnchors            inc/pairwiseAligner.h:77-79
+ *                                    (the per-read loop of poa_realign,     impl/poa.c:682-713)
+ *   margin_b200_forward_batch     <- computeForwardProbability              inc/pairwiseAligner.h:54-57
+ *                                    (the allele x read loop,               impl/bubbleGraph.c:1045-1073)
+ *   margin_b200_model             <- StateMachine3 + (Rle)NucleotideEmissions + RepeatSubMatrix
+ *                                    impl/stateMachine.c:507-519, :716-720; inc/stateMachine.h:77-82
+ *   margin_b200_params            <- PairwiseAlignmentParameters            inc/pairwiseAligner.h:28-39
+ *   margin_b200_bands             <- band_constructDynamic / band_construct impl/pairwiseAligner.c:120-226
+ */
+#ifndef MARGIN_B200_H_
+#define MARGIN_B200_H_
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MARGIN_B200_MAX_RL 51          /* MAXIMUM_REPEAT_LENGTH, inc/margin.h:133 */
+#define MARGIN_B200_PROB_1 10000000    /* PAIR_ALIGNMENT_PROB_1, inc/pairwiseAligner.h:26 */
+
+/* Transition slots; value = natural log of the transition probability.
+ * Names follow StateMachine3 (impl/stateMachine.c:507-519). */
+enum {
+    MB_T_MATCH_CONTINUE = 0,   /* M -> M */
+    MB_T_MATCH_FROM_GAP_X = 1, /* X -> M */
+    MB_T_MATCH_FROM_GAP_Y = 2, /* Y -> M */
+    MB_T_GAP_OPEN_X = 3,       /* M -> X */
+    MB_T_GAP_EXTEND_X = 4,     /* X -> X */
+    MB_T_GAP_SWITCH_TO_X = 5,  /* Y -> X */
+    MB_T_GAP_OPEN_Y = 6,       /* M -> Y */
+    MB_T_GAP_EXTEND_Y = 7,     /* Y -> Y */
+    MB_T_GAP_SWITCH_TO_Y = 8   /* X -> Y */
+};
+
+/* One flattened state machine (one strand).  `rle` selects the emission
+ * function: 0 = NucleotideEmissions (impl/stateMachine.c:363-383), symbols are
+ * compared whole (anything >= 4 is ambiguous); 1 = RleNucleotideEmissions
+ * (impl/stateMachine.c:722-738): base = symbol & 255, run length = symbol >> 8,
+ * match emission = match[xb*4+yb] + 2.3025 * rsm[tbl(xb)][rlX][rlY] where
+ * tbl(b) = b for b<4 else 0 and `rsm` is ALREADY resolved for the strand, i.e.
+ * rsm[b] holds logProbabilities[(strand ? b : 3-b)] of impl/repeatSubMatrix.c:28-31,
+ * laid out [base][underlying = ref run length][observed = read run length]. */
+typedef struct margin_b200_model {
+    double t[9];
+    double match[16];
+    double gap_x[4];
+    double gap_y[4];
+    int32_t rle;
+    int32_t max_rl; /* row stride of rsm (51); run lengths must be < max_rl */
+    double rsm[4 * MARGIN_B200_MAX_RL * MARGIN_B200_MAX_RL];
+} margin_b200_model;
+
+/* PairwiseAlignmentParameters (inc/pairwiseAligner.h:28-39), hot-path fields only. */
+typedef struct margin_b200_params {
+    double threshold;
+    int64_t min_diags_between_traceback;
+    int64_t traceback_diagonals;
+    int64_t diagonal_expansion;
+    int64_t split_matrix_bigger_than_this;
+    int32_t dynamic_anchor_expansion;
+    int32_t reserved;
+} margin_b200_params;
+
+/* A batch of independent alignments (one per read of a chunk, or per allele x
+ * read substring).  Sequences are concatenated Symbol (uint16) arrays;
+ * alignment i uses sym_x[off_x[i] .. off_x[i+1]) (the reference, "X") and
+ * sym_y[off_y[i] .. off_y[i+1]) (the read, "Y").  Anchors are (x, y, expansion)
+ * int32 triples, 0-based sequence coordinates, strictly increasing in x and y,
+ * expansion even (impl/pairwiseAligner.c:143-159); alignment i owns triples
+ * off_a[i] .. off_a[i+1).  model_slot[i] picks the state machine (0 = forward-
+ * strand read, 1 = reverse-strand read; impl/poa.c:646-649). */
+typedef struct margin_b200_batch {
+    int64_t n;
+    const uint16_t *sym_x;
+    const int64_t *off_x;
+    const uint16_t *sym_y;
+    const int64_t *off_y;
+    const int32_t *anchors;
+    const int64_t *off_a;
+    const uint8_t *model_slot;
+    const uint8_t *ragged_left;
+    const uint8_t *ragged_right;
+} margin_b200_batch;
+
+/* One posterior tuple, same meaning as the reference's stIntTuple (weight, x, y)
+ * (impl/pairwiseAligner.c:598-608): weight = floor(p * 1e7), x/y 0-based, gap
+ * lists may hold -1. */
+typedef struct margin_b200_pair {
+    int32_t w, x, y;
+} margin_b200_pair;
+
+/* Result of a posterior batch.  Memory is pinned host memory owned by the
+ * context and valid until the next call on the same context.  List l of
+ * alignment i is pairs[l][off[l][i] .. off[l][i+1]), in exactly the order the
+ * reference's stList would have (impl/pairwiseAligner.c:1104-1123).
+ * l: 0 = match, 1 = gapX (delete), 2 = gapY (insert); lists 1,2 are empty when
+ * want_indels == 0. */
+typedef struct margin_b200_result {
+    int64_t n;
+    const margin_b200_pair *pairs[3];
+    const int64_t *off[3];
+    int64_t band_cells;      /* lattice cells inside the bands of this batch */
+    int64_t diagonals;       /* anti-diagonals swept */
+    int64_t jobs;            /* device jobs (alignments after large-gap splitting) */
+    int64_t segments;        /* traceback segments */
+    float gpu_ms;            /* device time of this call (CUDA events) */
+    int32_t kernel_launches; /* kernels launched by this call */
+} margin_b200_result;
+
+typedef struct margin_b200_ctx margin_b200_ctx;
+
+/* All functions return 0 on success, non-zero on error; the message is
+ * available from margin_b200_last_error().  There is no CPU fallback: a call
+ * without a usable CUDA device fails. */
+int margin_b200_create(margin_b200_ctx **ctx, int device);
+void margin_b200_destroy(margin_b200_ctx *ctx);
+const char *margin_b200_last_error(void);
+int margin_b200_version(void);
+
+int margin_b200_set_model(margin_b200_ctx *ctx, int slot, const margin_b200_model *model);
+int margin_b200_set_params(margin_b200_ctx *ctx, const margin_b200_params *params);
+
+/* Banded forward/backward/posterior for every alignment of the batch. */
+int margin_b200_posteriors_batch(margin_b200_ctx *ctx, const margin_b200_batch *batch, int want_indels,
+                                 margin_b200_result *out);
+
+/* The same call in three steps, so that the kernels can be timed with inputs
+ * already resident in HBM: upload copies the batch host->device;
+ * posteriors_resident runs every kernel on the uploaded batch and leaves the
+ * result lists in HBM (out->pairs / out->off are NULL, the counters are set);
+ * download copies the lists device->host and fills out->pairs / out->off.
+ * margin_b200_posteriors_batch == upload + resident + download. */
+int margin_b200_upload_batch(margin_b200_ctx *ctx, const margin_b200_batch *batch);
+int margin_b200_posteriors_resident(margin_b200_ctx *ctx, int want_indels, margin_b200_result *out);
+int margin_b200_download_result(margin_b200_ctx *ctx, margin_b200_result *out);
+
+/* Forward-only log-likelihood per alignment (computeForwardProbability):
+ * out_log_prob[i] is the natural-log total probability (double, the reference
+ * truncates to float at the call site, impl/bubbleGraph.c:1067). */
+int margin_b200_forward_batch(margin_b200_ctx *ctx, const margin_b200_batch *batch, double *out_log_prob,
+                              margin_b200_result *stats);
+/* Kernel-only step of the above on a batch staged by margin_b200_upload_batch. */
+int margin_b200_forward_resident(margin_b200_ctx *ctx, margin_b200_result *stats);
+
+/* Band geometry only (band_constructDynamic / band_construct): for alignment i
+ * and anti-diagonal d in [0, lX+lY], xmy_l / xmy_r at off_d[i] + d, where
+ * off_d is the exclusive prefix sum of (lX+lY+1).  Buffers are caller-owned
+ * host memory. */
+int margin_b200_bands(margin_b200_ctx *ctx, const margin_b200_batch *batch, int32_t *xmy_l, int32_t *xmy_r);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,182 @@
+"""ctypes mirror of include/margin_b200.h and the loader of the CUDA library.
+
+There is no CPU fallback in this package: :func:`load_library` raises if
+``libmargin_b200.so`` has not been built (``python -c 'import __graft_entry__ as g; g.build()'``)
+and the library itself fails every compute call when no CUDA device is usable.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+MAX_RL = 51  # MAXIMUM_REPEAT_LENGTH, inc/margin.h:133
+PROB_1 = 10000000  # PAIR_ALIGNMENT_PROB_1, inc/pairwiseAligner.h:26
+
+T_MATCH_CONTINUE, T_MATCH_FROM_GAP_X, T_MATCH_FROM_GAP_Y = 0, 1, 2
+T_GAP_OPEN_X, T_GAP_EXTEND_X, T_GAP_SWITCH_TO_X = 3, 4, 5
+T_GAP_OPEN_Y, T_GAP_EXTEND_Y, T_GAP_SWITCH_TO_Y = 6, 7, 8
+
+
+class Model(C.Structure):
+    """margin_b200_model: one flattened StateMachine3 + emissions (one strand)."""
+
+    _fields_ = [
+        ("t", C.c_double * 9),
+        ("match", C.c_double * 16),
+        ("gap_x", C.c_double * 4),
+        ("gap_y", C.c_double * 4),
+        ("rle", C.c_int32),
+        ("max_rl", C.c_int32),
+        ("rsm", C.c_double * (4 * MAX_RL * MAX_RL)),
+    ]
+
+    def same_as(self, other):
+        return bytes(self) == bytes(other)
+
+
+class Params(C.Structure):
+    """margin_b200_params: PairwiseAlignmentParameters (inc/pairwiseAligner.h:28-39)."""
+
+    _fields_ = [
+        ("threshold", C.c_double),
+        ("min_diags_between_traceback", C.c_int64),
+        ("traceback_diagonals", C.c_int64),
+        ("diagonal_expansion", C.c_int64),
+        ("split_matrix_bigger_than_this", C.c_int64),
+        ("dynamic_anchor_expansion", C.c_int32),
+        ("reserved", C.c_int32),
+    ]
+
+    @classmethod
+    def defaults(cls):
+        """pairwiseAlignmentBandingParameters_construct (impl/pairwiseAligner.c:1048-1060)."""
+        return cls(0.01, 1000, 40, 20, 3000 * 3000, 0, 0)
+
+    def copy(self, **kw):
+        p = Params.from_buffer_copy(bytes(self))
+        for k, v in kw.items():
+            setattr(p, k, v)
+        return p
+
+
+class BatchStruct(C.Structure):
+    _fields_ = [
+        ("n", C.c_int64),
+        ("sym_x", C.c_void_p),
+        ("off_x", C.c_void_p),
+        ("sym_y", C.c_void_p),
+        ("off_y", C.c_void_p),
+        ("anchors", C.c_void_p),
+        ("off_a", C.c_void_p),
+        ("model_slot", C.c_void_p),
+        ("ragged_left", C.c_void_p),
+        ("ragged_right", C.c_void_p),
+    ]
+
+
+PAIR_DTYPE = np.dtype([("w", "<i4"), ("x", "<i4"), ("y", "<i4")])
+
+
+class ResultStruct(C.Structure):
+    _fields_ = [
+        ("n", C.c_int64),
+        ("pairs", C.c_void_p * 3),
+        ("off", C.c_void_p * 3),
+        ("band_cells", C.c_int64),
+        ("diagonals", C.c_int64),
+        ("jobs", C.c_int64),
+        ("segments", C.c_int64),
+        ("gpu_ms", C.c_float),
+        ("kernel_launches", C.c_int32),
+    ]
+
+
+class Batch:
+    """Host-side packing of a list of alignments into the flat margin_b200_batch layout.
+
+    Each item: (sym_x uint16[], sym_y uint16[], anchors int32[k,3], model_slot, ragged_left, ragged_right).
+    """
+
+    def __init__(self, items):
+        n = len(items)
+        self.n = n
+        lx = np.array([len(it[0]) for it in items], dtype=np.int64)
+        ly = np.array([len(it[1]) for it in items], dtype=np.int64)
+        la = np.array([len(it[2]) for it in items], dtype=np.int64)
+        self.off_x = np.concatenate([[0], np.cumsum(lx)]).astype(np.int64)
+        self.off_y = np.concatenate([[0], np.cumsum(ly)]).astype(np.int64)
+        self.off_a = np.concatenate([[0], np.cumsum(la)]).astype(np.int64)
+        cat = lambda arrs, dt, shape: (np.ascontiguousarray(np.concatenate(arrs).astype(dt)) if n and sum(
+            len(a) for a in arrs) else np.zeros(shape, dtype=dt))
+        self.sym_x = cat([np.asarray(it[0], dtype=np.uint16) for it in items], np.uint16, (1,))
+        self.sym_y = cat([np.asarray(it[1], dtype=np.uint16) for it in items], np.uint16, (1,))
+        self.anchors = cat([np.asarray(it[2], dtype=np.int32).reshape(-1, 3) for it in items], np.int32, (1, 3))
+        self.model_slot = np.array([it[3] for it in items], dtype=np.uint8) if n else np.zeros(1, np.uint8)
+        self.ragged_left = np.array([it[4] for it in items], dtype=np.uint8) if n else np.zeros(1, np.uint8)
+        self.ragged_right = np.array([it[5] for it in items], dtype=np.uint8) if n else np.zeros(1, np.uint8)
+        self.struct = BatchStruct(
+            n, self.sym_x.ctypes.data, self.off_x.ctypes.data, self.sym_y.ctypes.data, self.off_y.ctypes.data,
+            self.anchors.ctypes.data, self.off_a.ctypes.data, self.model_slot.ctypes.data,
+            self.ragged_left.ctypes.data, self.ragged_right.ctypes.data)
+
+    def item(self, i):
+        return (self.sym_x[self.off_x[i]:self.off_x[i + 1]], self.sym_y[self.off_y[i]:self.off_y[i + 1]],
+                self.anchors[self.off_a[i]:self.off_a[i + 1]], int(self.model_slot[i]), int(self.ragged_left[i]),
+                int(self.ragged_right[i]))
+
+    @property
+    def h2d_bytes(self):
+        return int(self.sym_x.nbytes + self.sym_y.nbytes + self.anchors.nbytes + 3 * self.off_x.nbytes + 3 * self.n)
+
+
+_LIB = None
+LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc", "libmargin_b200.so")
+
+
+def load_library():
+    """dlopen the CUDA library.  Raises (never falls back) when it is missing."""
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            "margin_b200: %s is not built; run __graft_entry__.build() (needs nvcc). "
+            "There is no CPU fallback." % LIB_PATH)
+    lib = C.CDLL(LIB_PATH)
+    vp, i32, i64 = C.c_void_p, C.c_int, C.c_int64
+    lib.margin_b200_create.argtypes = [C.POINTER(vp), i32]
+    lib.margin_b200_create.restype = i32
+    lib.margin_b200_destroy.argtypes = [vp]
+    lib.margin_b200_destroy.restype = None
+    lib.margin_b200_last_error.argtypes = []
+    lib.margin_b200_last_error.restype = C.c_char_p
+    lib.margin_b200_version.argtypes = []
+    lib.margin_b200_version.restype = i32
+    lib.margin_b200_set_model.argtypes = [vp, i32, C.POINTER(Model)]
+    lib.margin_b200_set_model.restype = i32
+    lib.margin_b200_set_params.argtypes = [vp, C.POINTER(Params)]
+    lib.margin_b200_set_params.restype = i32
+    lib.margin_b200_posteriors_batch.argtypes = [vp, C.POINTER(BatchStruct), i32, C.POINTER(ResultStruct)]
+    lib.margin_b200_posteriors_batch.restype = i32
+    lib.margin_b200_upload_batch.argtypes = [vp, C.POINTER(BatchStruct)]
+    lib.margin_b200_upload_batch.restype = i32
+    lib.margin_b200_posteriors_resident.argtypes = [vp, i32, C.POINTER(ResultStruct)]
+    lib.margin_b200_posteriors_resident.restype = i32
+    lib.margin_b200_download_result.argtypes = [vp, C.POINTER(ResultStruct)]
+    lib.margin_b200_download_result.restype = i32
+    lib.margin_b200_forward_batch.argtypes = [vp, C.POINTER(BatchStruct), vp, C.POINTER(ResultStruct)]
+    lib.margin_b200_forward_batch.restype = i32
+    lib.margin_b200_forward_resident.argtypes = [vp, C.POINTER(ResultStruct)]
+    lib.margin_b200_forward_resident.restype = i32
+    lib.margin_b200_bands.argtypes = [vp, C.POINTER(BatchStruct), vp, vp]
+    lib.margin_b200_bands.restype = i32
+    _LIB = lib
+    return lib
+
+
+EXPORTED_SYMBOLS = [
+    "margin_b200_create", "margin_b200_destroy", "margin_b200_last_error", "margin_b200_version",
+    "margin_b200_set_model", "margin_b200_set_params", "margin_b200_posteriors_batch",
+    "margin_b200_upload_batch", "margin_b200_posteriors_resident", "margin_b200_download_result",
+    "margin_b200_forward_batch", "margin_b200_forward_resident", "margin_b200_bands",
+]
