@@ -1,0 +1,754 @@
+// margin_b200.cu — host side of the C ABI in include/margin_b200.h.
+//
+// One context = one CUDA device + one stream + grow-only device / pinned buffers, meant to be owned by one host
+// thread (the reference runs one chunk per OpenMP thread, polish.c:476; thread t uses device t % nGPU).
+// There is no CPU fallback anywhere in this file: without a usable device every entry point fails.
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include <cub/device/device_scan.cuh>
+
+#include "../../include/margin_b200.h"
+#include "pairhmm_kernels.cuh"
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(const char *fmt, ...) {
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return 1;
+}
+
+#define CU(call)                                                                                        \
+    do {                                                                                                \
+        cudaError_t e_ = (call);                                                                        \
+        if (e_ != cudaSuccess) return fail("%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+
+// Grow-only device buffer.
+struct DevBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+    int ensure(size_t bytes) {
+        if (bytes <= cap) return 0;
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+        size_t want = bytes + bytes / 8 + 256;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e != cudaSuccess) return fail("cudaMalloc(%zu bytes) failed: %s", want, cudaGetErrorString(e));
+        cap = want;
+        return 0;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+    template <typename T> T *as() { return reinterpret_cast<T *>(p); }
+};
+
+// Grow-only pinned host buffer.
+struct PinBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+    int ensure(size_t bytes) {
+        if (bytes <= cap) return 0;
+        if (p) cudaFreeHost(p);
+        p = nullptr;
+        cap = 0;
+        size_t want = bytes + bytes / 8 + 256;
+        cudaError_t e = cudaMallocHost(&p, want);
+        if (e != cudaSuccess) return fail("cudaMallocHost(%zu bytes) failed: %s", want, cudaGetErrorString(e));
+        cap = want;
+        return 0;
+    }
+    void release() {
+        if (p) cudaFreeHost(p);
+        p = nullptr;
+        cap = 0;
+    }
+    template <typename T> T *as() { return reinterpret_cast<T *>(p); }
+};
+
+}  // namespace
+
+struct margin_b200_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    bool have_model[2] = {false, false};
+    bool have_params = false;
+    margin_b200_params params{};
+    mb::DevModel host_models[2];
+    DevBuf d_models, d_rsm[2];
+
+    // the uploaded batch
+    int64_t n_aln = 0;
+    std::vector<mb::Job> jobs;
+    std::vector<int32_t> aln_first_slot;
+    std::vector<int32_t> aln_first_job;
+    int64_t total_diag = 0;  // entries in kl / cell_off
+    int total_slots = 0;
+    DevBuf d_symx, d_symy, d_anchors, d_jobs, d_kl, d_kr, d_cell_off, d_job_cells, d_job_maxw, d_job_nseg, d_err;
+    DevBuf d_segs, d_seg_counts, d_seg_off, d_scan_tmp, d_slot_ring_off, d_ring, d_ids, d_aln_first_slot;
+    DevBuf d_F, d_stage, d_out, d_off_out, d_fwd_out;
+    PinBuf h_stage_in, h_small, h_out, h_off;
+    // after band_kernel
+    std::vector<int64_t> job_cells;
+    std::vector<int32_t> job_maxw;
+    int64_t total_cells = 0;
+    int64_t total_tuples = 0;
+    int64_t list_tuples[3] = {0, 0, 0};
+    int launches = 0;
+};
+
+namespace {
+
+int check_device(int device) {
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        return fail("margin_b200: no usable CUDA device (%s); there is no CPU fallback",
+                    e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+    if (device < 0 || device >= count) return fail("margin_b200: device %d out of range (0..%d)", device, count - 1);
+    return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char *margin_b200_last_error(void) { return g_err.c_str(); }
+
+int margin_b200_version(void) { return 100; }
+
+int margin_b200_create(margin_b200_ctx **out, int device) {
+    if (!out) return fail("margin_b200_create: null output pointer");
+    *out = nullptr;
+    if (check_device(device)) return 1;
+    CU(cudaSetDevice(device));
+    margin_b200_ctx *c = new margin_b200_ctx();
+    c->device = device;
+    CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    CU(cudaEventCreate(&c->ev0));
+    CU(cudaEventCreate(&c->ev1));
+    *out = c;
+    return 0;
+}
+
+void margin_b200_destroy(margin_b200_ctx *c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    DevBuf *bufs[] = {&c->d_models, &c->d_rsm[0], &c->d_rsm[1], &c->d_symx, &c->d_symy, &c->d_anchors, &c->d_jobs,
+                      &c->d_kl, &c->d_kr, &c->d_cell_off, &c->d_job_cells, &c->d_job_maxw, &c->d_job_nseg, &c->d_err,
+                      &c->d_segs, &c->d_seg_counts, &c->d_seg_off, &c->d_scan_tmp, &c->d_slot_ring_off, &c->d_ring,
+                      &c->d_ids, &c->d_aln_first_slot, &c->d_F, &c->d_stage, &c->d_out, &c->d_off_out, &c->d_fwd_out};
+    for (DevBuf *b : bufs) b->release();
+    c->h_stage_in.release();
+    c->h_small.release();
+    c->h_out.release();
+    c->h_off.release();
+    cudaEventDestroy(c->ev0);
+    cudaEventDestroy(c->ev1);
+    cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+int margin_b200_set_model(margin_b200_ctx *c, int slot, const margin_b200_model *m) {
+    if (!c || !m) return fail("margin_b200_set_model: null argument");
+    if (slot < 0 || slot > 1) return fail("margin_b200_set_model: slot must be 0 or 1");
+    if (m->rle && m->max_rl != MARGIN_B200_MAX_RL) return fail("margin_b200_set_model: max_rl must be %d", MARGIN_B200_MAX_RL);
+    CU(cudaSetDevice(c->device));
+    mb::DevModel &d = c->host_models[slot];
+    memset(&d, 0, sizeof(d));
+    memcpy(d.t, m->t, sizeof(d.t));
+    memcpy(d.match, m->match, sizeof(d.match));
+    for (int b = 0; b < 4; b++) {
+        d.gap_x[b] = m->gap_x[b];
+        d.gap_y[b] = m->gap_y[b];
+    }
+    d.gap_x[4] = -1.386294361;  // ambiguous symbol, impl/stateMachine.c:363-368
+    d.gap_y[4] = -1.386294361;
+    const int tx[3] = {MB_T_GAP_OPEN_X, MB_T_GAP_EXTEND_X, MB_T_GAP_SWITCH_TO_X};
+    const int ty[3] = {MB_T_GAP_OPEN_Y, MB_T_GAP_EXTEND_Y, MB_T_GAP_SWITCH_TO_Y};
+    for (int b = 0; b < 5; b++) {
+        for (int k = 0; k < 3; k++) {
+            d.ex_t[b][k] = d.gap_x[b] + m->t[tx[k]];  // the reference's (eP + tP), pairwiseAligner.c:313
+            d.ey_t[b][k] = d.gap_y[b] + m->t[ty[k]];
+        }
+    }
+    d.end_p[0][0] = m->t[MB_T_MATCH_CONTINUE];  // impl/stateMachine.c:532-545
+    d.end_p[0][1] = m->t[MB_T_MATCH_FROM_GAP_X];
+    d.end_p[0][2] = m->t[MB_T_MATCH_FROM_GAP_Y];
+    d.end_p[1][0] = (m->t[MB_T_GAP_OPEN_X] + m->t[MB_T_GAP_OPEN_Y]) / 2.0;  // :547-560
+    d.end_p[1][1] = m->t[MB_T_GAP_EXTEND_X];
+    d.end_p[1][2] = m->t[MB_T_GAP_EXTEND_Y];
+    d.rle = m->rle;
+    d.max_rl = MARGIN_B200_MAX_RL;
+    const size_t nr = (size_t) 4 * MARGIN_B200_MAX_RL * MARGIN_B200_MAX_RL;
+    std::vector<double> scaled(nr);
+    for (size_t i = 0; i < nr; i++) scaled[i] = 2.3025 * m->rsm[i];  // impl/stateMachine.c:735-736
+    if (c->d_rsm[slot].ensure(nr * sizeof(double))) return 1;
+    CU(cudaMemcpyAsync(c->d_rsm[slot].p, scaled.data(), nr * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+    d.rsm_scaled = c->d_rsm[slot].as<double>();
+    if (c->d_models.ensure(2 * sizeof(mb::DevModel))) return 1;
+    CU(cudaMemcpyAsync(c->d_models.p, c->host_models, 2 * sizeof(mb::DevModel), cudaMemcpyHostToDevice, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    c->have_model[slot] = true;
+    return 0;
+}
+
+int margin_b200_set_params(margin_b200_ctx *c, const margin_b200_params *p) {
+    if (!c || !p) return fail("margin_b200_set_params: null argument");
+    // the prerequisites asserted at impl/pairwiseAligner.c:714-718
+    if (p->traceback_diagonals < 1) return fail("traceBackDiagonals must be >= 1");
+    if (p->diagonal_expansion < 0 || p->diagonal_expansion % 2 != 0) return fail("diagonalExpansion must be even and >= 0");
+    if (p->min_diags_between_traceback < 2) return fail("minDiagsBetweenTraceBack must be >= 2");
+    if (p->traceback_diagonals + 1 >= p->min_diags_between_traceback)
+        return fail("traceBackDiagonals + 1 must be < minDiagsBetweenTraceBack");
+    if (!(p->threshold >= 0.0 && p->threshold <= 1.0)) return fail("threshold must be in [0,1]");
+    c->params = *p;
+    c->have_params = true;
+    return 0;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------------------------------
+// Batch upload: large-gap splitting (host, pure integer) + job table + H2D copies
+// ------------------------------------------------------------------------------------------------------------------
+namespace {
+
+struct Block {
+    int64_t x1, y1, x2, y2;
+};
+
+// getSplitPointsP / getSplitPoints (impl/pairwiseAligner.c:913-965)
+bool split_p(int64_t &x1, int64_t &y1, int64_t x2, int64_t y2, int64_t x3, int64_t y3, std::vector<Block> &out,
+             int64_t limit, bool skip_block) {
+    const int64_t l_x2 = x3 - x2, l_y2 = y3 - y2;
+    if (l_x2 * l_y2 > limit) {
+        const int64_t max_len = (int64_t) std::sqrt((double) limit);
+        const int64_t hx = l_x2 / 2 > max_len ? max_len : l_x2 / 2;
+        const int64_t hy = l_y2 / 2 > max_len ? max_len : l_y2 / 2;
+        if (!skip_block) out.push_back(Block{x1, y1, x2 + hx, y2 + hy});
+        x1 = x3 - hx;
+        y1 = y3 - hy;
+        return true;
+    }
+    return false;
+}
+
+void split_points(const int32_t *anc, int64_t na, int64_t lx, int64_t ly, int64_t limit, bool ragged_l, bool ragged_r,
+                  std::vector<Block> &out) {
+    out.clear();
+    int64_t x1 = 0, y1 = 0, x2 = 0, y2 = 0;
+    for (int64_t i = 0; i < na; i++) {
+        const int64_t x3 = anc[3 * i], y3 = anc[3 * i + 1];
+        split_p(x1, y1, x2, y2, x3, y3, out, limit, ragged_l && i == 0);
+        x2 = x3 + 1;
+        y2 = y3 + 1;
+    }
+    if (!split_p(x1, y1, x2, y2, lx, ly, out, limit, ragged_l && na == 0) || !ragged_r) out.push_back(Block{x1, y1, lx, ly});
+}
+
+int validate_anchors(const int32_t *anc, int64_t na, int64_t lx, int64_t ly, int64_t aln) {
+    // the asserts of band_constructDynamic (impl/pairwiseAligner.c:150-158), which are compiled out in the reference
+    int64_t px = -1, py = -1;
+    for (int64_t i = 0; i < na; i++) {
+        const int64_t x = anc[3 * i], y = anc[3 * i + 1], e = anc[3 * i + 2];
+        if (x <= px || y <= py || x < 0 || y < 0 || x >= lx || y >= ly || e < 0 || (e & 1))
+            return fail("alignment %lld: anchor %lld (%lld,%lld,%lld) is not strictly increasing / in range / even",
+                        (long long) aln, (long long) i, (long long) x, (long long) y, (long long) e);
+        px = x;
+        py = y;
+    }
+    return 0;
+}
+
+}  // namespace
+
+extern "C" int margin_b200_upload_batch(margin_b200_ctx *c, const margin_b200_batch *b) {
+    if (!c || !b) return fail("margin_b200_upload_batch: null argument");
+    if (!c->have_params) return fail("margin_b200_upload_batch: margin_b200_set_params has not been called");
+    if (b->n < 0) return fail("margin_b200_upload_batch: negative batch size");
+    if (check_device(c->device)) return 1;
+    CU(cudaSetDevice(c->device));
+    const margin_b200_params &p = c->params;
+    const int64_t n = b->n;
+    c->n_aln = n;
+    c->jobs.clear();
+    c->aln_first_slot.assign(n + 1, 0);
+    c->aln_first_job.assign(n + 1, 0);
+    std::vector<int32_t> extra_anchors;
+    const int64_t total_anchor_triples = n ? b->off_a[n] : 0;
+    std::vector<Block> blocks;
+    int64_t diag_off = 0;
+    int64_t slot_base = 0;
+    const int64_t seg_step = p.min_diags_between_traceback - p.traceback_diagonals - 1;
+    for (int64_t i = 0; i < n; i++) {
+        const int64_t lx = b->off_x[i + 1] - b->off_x[i], ly = b->off_y[i + 1] - b->off_y[i];
+        const int64_t na = b->off_a[i + 1] - b->off_a[i];
+        if (lx < 0 || ly < 0 || na < 0) return fail("alignment %lld: negative length", (long long) i);
+        if (lx + ly > (int64_t) 1 << 30) return fail("alignment %lld: sequences too long", (long long) i);
+        const int32_t *anc = b->anchors + 3 * b->off_a[i];
+        if (validate_anchors(anc, na, lx, ly, i)) return 1;
+        const bool rl = b->ragged_left && b->ragged_left[i], rr = b->ragged_right && b->ragged_right[i];
+        const uint8_t slot = b->model_slot ? b->model_slot[i] : 0;
+        if (slot > 1 || !c->have_model[slot]) return fail("alignment %lld: model slot %d has not been set", (long long) i, slot);
+        split_points(anc, na, lx, ly, p.split_matrix_bigger_than_this, rl, rr, blocks);
+        c->aln_first_slot[i] = (int32_t) slot_base;
+        c->aln_first_job[i] = (int32_t) c->jobs.size();
+        int64_t j = 0;
+        for (size_t k = 0; k < blocks.size(); k++) {
+            const Block &bl = blocks[k];
+            const int64_t j0 = j;
+            while (j < na && (int64_t) anc[3 * j] + anc[3 * j + 1] < bl.x2 + bl.y2) j++;
+            mb::Job job;
+            memset(&job, 0, sizeof(job));
+            job.symx_off = b->off_x[i] + bl.x1;
+            job.symy_off = b->off_y[i] + bl.y1;
+            job.lx = (int32_t) (bl.x2 - bl.x1);
+            job.ly = (int32_t) (bl.y2 - bl.y1);
+            job.n_anc = (int32_t) (j - j0);
+            if (bl.x1 == 0 && bl.y1 == 0) {
+                job.anc_off = b->off_a[i] + j0;
+            } else {  // re-based copy (impl/pairwiseAligner.c:1010-1023)
+                job.anc_off = total_anchor_triples + (int64_t) extra_anchors.size() / 3;
+                for (int64_t q = j0; q < j; q++) {
+                    extra_anchors.push_back(anc[3 * q] - (int32_t) bl.x1);
+                    extra_anchors.push_back(anc[3 * q + 1] - (int32_t) bl.y1);
+                    extra_anchors.push_back(anc[3 * q + 2]);
+                }
+            }
+            job.x1 = (int32_t) bl.x1;
+            job.y1 = (int32_t) bl.y1;
+            job.aln = (int32_t) i;
+            job.slot = slot;
+            job.ragged_l = rl || k > 0;
+            job.ragged_r = rr || k + 1 < blocks.size();
+            job.diag_off = diag_off;
+            const int64_t N = (int64_t) job.lx + job.ly;
+            diag_off += N + 2;
+            job.max_seg = (int32_t) (N / seg_step + 2);
+            job.seg_base = (int32_t) slot_base;
+            slot_base += job.max_seg;
+            if (slot_base > (int64_t) 1 << 30) return fail("batch too large: too many traceback segments");
+            c->jobs.push_back(job);
+        }
+    }
+    c->aln_first_slot[n] = (int32_t) slot_base;
+    c->aln_first_job[n] = (int32_t) c->jobs.size();
+    c->total_diag = diag_off;
+    c->total_slots = (int) slot_base;
+    c->total_cells = 0;
+
+    const int64_t nx = n ? b->off_x[n] : 0, ny = n ? b->off_y[n] : 0;
+    const size_t anchor_ints = (size_t) 3 * total_anchor_triples + extra_anchors.size();
+    if (c->d_symx.ensure((nx + 1) * sizeof(uint16_t)) || c->d_symy.ensure((ny + 1) * sizeof(uint16_t)) ||
+        c->d_anchors.ensure((anchor_ints + 3) * sizeof(int32_t)) ||
+        c->d_jobs.ensure((c->jobs.size() + 1) * sizeof(mb::Job)) ||
+        c->d_aln_first_slot.ensure((n + 1) * sizeof(int32_t)))
+        return 1;
+    if (nx) CU(cudaMemcpyAsync(c->d_symx.p, b->sym_x, nx * sizeof(uint16_t), cudaMemcpyHostToDevice, c->stream));
+    if (ny) CU(cudaMemcpyAsync(c->d_symy.p, b->sym_y, ny * sizeof(uint16_t), cudaMemcpyHostToDevice, c->stream));
+    if (total_anchor_triples)
+        CU(cudaMemcpyAsync(c->d_anchors.p, b->anchors, (size_t) 3 * total_anchor_triples * sizeof(int32_t),
+                           cudaMemcpyHostToDevice, c->stream));
+    if (!extra_anchors.empty())
+        CU(cudaMemcpyAsync(c->d_anchors.as<int32_t>() + 3 * total_anchor_triples, extra_anchors.data(),
+                           extra_anchors.size() * sizeof(int32_t), cudaMemcpyHostToDevice, c->stream));
+    if (!c->jobs.empty())
+        CU(cudaMemcpyAsync(c->d_jobs.p, c->jobs.data(), c->jobs.size() * sizeof(mb::Job), cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(c->d_aln_first_slot.p, c->aln_first_slot.data(), (n + 1) * sizeof(int32_t), cudaMemcpyHostToDevice,
+                       c->stream));
+    CU(cudaStreamSynchronize(c->stream));  // extra_anchors / jobs are pageable host memory about to go out of scope
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// Kernel pipeline
+// ------------------------------------------------------------------------------------------------------------------
+namespace {
+
+mb::Params dev_params(const margin_b200_params &p) {
+    mb::Params q;
+    q.threshold = p.threshold;
+    q.min_diags = (int32_t) p.min_diags_between_traceback;
+    q.tb_diags = (int32_t) p.traceback_diagonals;
+    q.expansion = (int32_t) p.diagonal_expansion;
+    q.dynamic = p.dynamic_anchor_expansion;
+    return q;
+}
+
+constexpr int kFwdThreads = 128;
+constexpr int kBwdThreads = 128;
+
+inline int group_of(int maxw) { return maxw <= 8 ? 8 : (maxw <= 16 ? 16 : 32); }
+
+// band_kernel (+ schedule_kernel) and the one host round trip of the pipeline: per-job cell counts, widths and
+// segment counts come back so that F / staging can be sized and jobs binned by band width.
+int run_band(margin_b200_ctx *c, bool dynamic, bool with_schedule, bool want_kr) {
+    const int nj = (int) c->jobs.size();
+    mb::Params q = dev_params(c->params);
+    q.dynamic = dynamic ? 1 : 0;
+    if (c->d_kl.ensure((c->total_diag + 1) * sizeof(int32_t)) || c->d_cell_off.ensure((c->total_diag + 1) * sizeof(uint32_t)) ||
+        c->d_job_cells.ensure((nj + 1) * sizeof(int64_t)) || c->d_job_maxw.ensure((nj + 1) * sizeof(int32_t)) ||
+        c->d_job_nseg.ensure((nj + 1) * sizeof(int32_t)) || c->d_err.ensure(sizeof(int)) ||
+        c->d_segs.ensure(((size_t) c->total_slots + 1) * sizeof(mb::Seg)))
+        return 1;
+    if (want_kr && c->d_kr.ensure((c->total_diag + 1) * sizeof(int32_t))) return 1;
+    CU(cudaMemsetAsync(c->d_err.p, 0, sizeof(int), c->stream));
+    c->job_cells.assign(nj, 0);
+    c->job_maxw.assign(nj, 0);
+    std::vector<int32_t> nseg(nj, 0);
+    if (nj > 0) {
+        mb::band_kernel<256><<<nj, 256, 0, c->stream>>>(c->d_jobs.as<mb::Job>(), nj, c->d_anchors.as<int32_t>(), q,
+                                                        c->d_kl.as<int32_t>(), c->d_cell_off.as<uint32_t>(),
+                                                        c->d_job_cells.as<int64_t>(), c->d_job_maxw.as<int32_t>(),
+                                                        want_kr ? c->d_kr.as<int32_t>() : nullptr, c->d_err.as<int>());
+        c->launches++;
+        if (with_schedule) {
+            CU(cudaMemsetAsync(c->d_segs.p, 0xff, ((size_t) c->total_slots + 1) * sizeof(mb::Seg), c->stream));
+            const int threads = 128, per_block = threads / 32;
+            mb::schedule_kernel<<<(nj + per_block - 1) / per_block, threads, 0, c->stream>>>(
+                c->d_jobs.as<mb::Job>(), nj, c->d_cell_off.as<uint32_t>(), q, c->d_segs.as<mb::Seg>(),
+                c->d_job_nseg.as<int32_t>());
+            c->launches++;
+            CU(cudaMemcpyAsync(nseg.data(), c->d_job_nseg.p, nj * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+        }
+        CU(cudaMemcpyAsync(c->job_cells.data(), c->d_job_cells.p, nj * sizeof(int64_t), cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaMemcpyAsync(c->job_maxw.data(), c->d_job_maxw.p, nj * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+    }
+    int err = 0;
+    CU(cudaMemcpyAsync(&err, c->d_err.p, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    CU(cudaGetLastError());
+    if (err)
+        return fail("PAIRWISE_ALIGNMENT_EXCEPTION: Attempt to create diagonal with invalid coordinates "
+                    "(anchors inconsistent with the sequence lengths)");
+    int64_t cells = 0;
+    for (int j = 0; j < nj; j++) {
+        c->jobs[j].cell_base = cells;
+        c->jobs[j].ring_w = c->job_maxw[j];
+        cells += c->job_cells[j];
+        if (with_schedule) {
+            if (nseg[j] > c->jobs[j].max_seg) return fail("internal error: segment bound exceeded");
+        }
+    }
+    c->total_cells = cells;
+    // stash nseg in the pad-free way: reuse a vector on the ctx via job_maxw's sibling
+    c->h_small.ensure((nj + 1) * sizeof(int32_t));
+    memcpy(c->h_small.p, nseg.data(), nj * sizeof(int32_t));
+    return 0;
+}
+
+// Builds the per-group-width id lists (jobs for the forward sweep, used slots for the backward sweep), sorted by
+// length so that the groups sharing a warp finish together.  Layout of d_ids: [fwd8 | fwd16 | fwd32 | bwd8 | bwd16 | bwd32].
+struct Bins {
+    int fwd_off[4];
+    int bwd_off[4];
+};
+
+int build_bins(margin_b200_ctx *c, bool with_slots, Bins &bins, int force_group) {
+    const int nj = (int) c->jobs.size();
+    const int32_t *nseg = c->h_small.as<int32_t>();
+    std::vector<int32_t> order(nj);
+    for (int j = 0; j < nj; j++) order[j] = j;
+    std::sort(order.begin(), order.end(), [&](int a, int b) {
+        const int na = c->jobs[a].lx + c->jobs[a].ly, nb = c->jobs[b].lx + c->jobs[b].ly;
+        return na != nb ? na > nb : a < b;
+    });
+    std::vector<int32_t> ids;
+    const int gs[3] = {8, 16, 32};
+    for (int k = 0; k < 3; k++) {
+        bins.fwd_off[k] = (int) ids.size();
+        for (int j : order) {
+            const int g = force_group ? force_group : group_of(c->job_maxw[j]);
+            if (g == gs[k]) ids.push_back(j);
+        }
+    }
+    bins.fwd_off[3] = (int) ids.size();
+    std::vector<int64_t> slot_ring_off;
+    int64_t ring_cells = 0;
+    if (with_slots) {
+        slot_ring_off.assign((size_t) c->total_slots + 1, 0);
+        for (int k = 0; k < 3; k++) {
+            bins.bwd_off[k] = (int) ids.size();
+            for (int j : order) {
+                const int g = force_group ? force_group : group_of(c->job_maxw[j]);
+                if (g != gs[k]) continue;
+                const mb::Job &job = c->jobs[j];
+                for (int s = 0; s < nseg[j]; s++) {
+                    const int slot = job.seg_base + (job.max_seg - 1 - s);
+                    ids.push_back(slot);
+                    slot_ring_off[slot] = ring_cells;
+                    ring_cells += 3 * (int64_t) job.ring_w;
+                }
+            }
+        }
+        bins.bwd_off[3] = (int) ids.size();
+    }
+    if (c->d_ids.ensure((ids.size() + 1) * sizeof(int32_t))) return 1;
+    if (!ids.empty())
+        CU(cudaMemcpyAsync(c->d_ids.p, ids.data(), ids.size() * sizeof(int32_t), cudaMemcpyHostToDevice, c->stream));
+    if (with_slots) {
+        if (c->d_slot_ring_off.ensure(slot_ring_off.size() * sizeof(int64_t)) ||
+            c->d_ring.ensure((size_t) (ring_cells + 1) * 3 * sizeof(double)))
+            return 1;
+        CU(cudaMemcpyAsync(c->d_slot_ring_off.p, slot_ring_off.data(), slot_ring_off.size() * sizeof(int64_t),
+                           cudaMemcpyHostToDevice, c->stream));
+    }
+    if (nj) CU(cudaMemcpyAsync(c->d_jobs.p, c->jobs.data(), nj * sizeof(mb::Job), cudaMemcpyHostToDevice, c->stream));
+    CU(cudaStreamSynchronize(c->stream));  // ids / slot_ring_off are local pageable vectors
+    return 0;
+}
+
+template <int G>
+void launch_forward(margin_b200_ctx *c, int off, int count) {
+    if (count <= 0) return;
+    const int per_block = kFwdThreads / G;
+    mb::forward_kernel<G, kFwdThreads><<<(count + per_block - 1) / per_block, kFwdThreads, 0, c->stream>>>(
+        c->d_jobs.as<mb::Job>(), c->d_ids.as<int32_t>() + off, count, c->d_models.as<mb::DevModel>(),
+        c->d_symx.as<uint16_t>(), c->d_symy.as<uint16_t>(), c->d_kl.as<int32_t>(), c->d_cell_off.as<uint32_t>(),
+        c->d_F.as<double>());
+    c->launches++;
+}
+
+template <int G, bool INDELS>
+void launch_backward(margin_b200_ctx *c, int off, int count, int64_t stage_stride) {
+    if (count <= 0) return;
+    const int per_block = kBwdThreads / G;
+    mb::backward_kernel<G, kBwdThreads, INDELS><<<(count + per_block - 1) / per_block, kBwdThreads, 0, c->stream>>>(
+        c->d_jobs.as<mb::Job>(), c->d_segs.as<mb::Seg>(), c->d_ids.as<int32_t>() + off, count,
+        c->d_models.as<mb::DevModel>(), c->d_symx.as<uint16_t>(), c->d_symy.as<uint16_t>(), c->d_kl.as<int32_t>(),
+        c->d_cell_off.as<uint32_t>(), c->d_F.as<double>(), dev_params(c->params), c->d_ring.as<double>(),
+        c->d_slot_ring_off.as<int64_t>(), c->d_stage.as<mb::Pair>(), stage_stride, c->d_seg_counts.as<int64_t>(),
+        c->total_slots);
+    c->launches++;
+}
+
+int force_group_env() {
+    const char *e = getenv("MARGIN_B200_FORCE_GROUP");  // test hook: 8, 16 or 32 exercises the wide-diagonal fallback
+    if (!e) return 0;
+    int g = atoi(e);
+    return (g == 8 || g == 16 || g == 32) ? g : 0;
+}
+
+void fill_stats(margin_b200_ctx *c, margin_b200_result *out, int64_t segments, float ms) {
+    out->n = c->n_aln;
+    out->band_cells = c->total_cells;
+    out->diagonals = c->total_diag - (int64_t) c->jobs.size();  // N+1 per job
+    out->jobs = (int64_t) c->jobs.size();
+    out->segments = segments;
+    out->gpu_ms = ms;
+    out->kernel_launches = c->launches;
+}
+
+}  // namespace
+
+extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_indels, margin_b200_result *out) {
+    if (!c || !out) return fail("margin_b200_posteriors_resident: null argument");
+    if (check_device(c->device)) return 1;
+    CU(cudaSetDevice(c->device));
+    memset(out, 0, sizeof(*out));
+    c->launches = 0;
+    c->total_tuples = 0;
+    c->list_tuples[0] = c->list_tuples[1] = c->list_tuples[2] = 0;
+    const int nj = (int) c->jobs.size();
+    const int n_lists = want_indels ? 3 : 1;
+    CU(cudaEventRecord(c->ev0, c->stream));
+    if (run_band(c, c->params.dynamic_anchor_expansion != 0, true, false)) return 1;
+    Bins bins;
+    if (build_bins(c, true, bins, force_group_env())) return 1;
+    const int64_t cells = c->total_cells;
+    const int S = c->total_slots;
+    if (c->d_F.ensure((size_t) (cells + 1) * 3 * sizeof(double)) ||
+        c->d_stage.ensure((size_t) (cells + 1) * n_lists * sizeof(mb::Pair)) ||
+        c->d_seg_counts.ensure(((size_t) 3 * S + 1) * sizeof(int64_t)) ||
+        c->d_seg_off.ensure(((size_t) 3 * S + 1) * sizeof(int64_t)) ||
+        c->d_off_out.ensure((size_t) 3 * (c->n_aln + 1) * sizeof(int64_t)))
+        return 1;
+    CU(cudaMemsetAsync(c->d_seg_counts.p, 0, ((size_t) 3 * S + 1) * sizeof(int64_t), c->stream));
+    launch_forward<8>(c, bins.fwd_off[0], bins.fwd_off[1] - bins.fwd_off[0]);
+    launch_forward<16>(c, bins.fwd_off[1], bins.fwd_off[2] - bins.fwd_off[1]);
+    launch_forward<32>(c, bins.fwd_off[2], bins.fwd_off[3] - bins.fwd_off[2]);
+    const int64_t stride = cells + 1;
+    if (want_indels) {
+        launch_backward<8, true>(c, bins.bwd_off[0], bins.bwd_off[1] - bins.bwd_off[0], stride);
+        launch_backward<16, true>(c, bins.bwd_off[1], bins.bwd_off[2] - bins.bwd_off[1], stride);
+        launch_backward<32, true>(c, bins.bwd_off[2], bins.bwd_off[3] - bins.bwd_off[2], stride);
+    } else {
+        launch_backward<8, false>(c, bins.bwd_off[0], bins.bwd_off[1] - bins.bwd_off[0], stride);
+        launch_backward<16, false>(c, bins.bwd_off[1], bins.bwd_off[2] - bins.bwd_off[1], stride);
+        launch_backward<32, false>(c, bins.bwd_off[2], bins.bwd_off[3] - bins.bwd_off[2], stride);
+    }
+    // exclusive scan of the tuple counts over [list][slot] (+ one trailing zero so that the total comes out too)
+    size_t tmp_bytes = 0;
+    const int n_scan = 3 * S + 1;
+    CU(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, c->d_seg_counts.as<int64_t>(), c->d_seg_off.as<int64_t>(), n_scan,
+                                     c->stream));
+    if (c->d_scan_tmp.ensure(tmp_bytes + 16)) return 1;
+    CU(cub::DeviceScan::ExclusiveSum(c->d_scan_tmp.p, tmp_bytes, c->d_seg_counts.as<int64_t>(), c->d_seg_off.as<int64_t>(),
+                                     n_scan, c->stream));
+    c->launches++;
+    int64_t bounds[4] = {0, 0, 0, 0};
+    for (int l = 0; l < 4; l++)
+        CU(cudaMemcpyAsync(&bounds[l], c->d_seg_off.as<int64_t>() + (size_t) l * S, sizeof(int64_t), cudaMemcpyDeviceToHost,
+                           c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    CU(cudaGetLastError());
+    c->total_tuples = bounds[3];
+    for (int l = 0; l < 3; l++) c->list_tuples[l] = bounds[l + 1] - bounds[l];
+    if (c->d_out.ensure((size_t) (c->total_tuples + 1) * sizeof(mb::Pair))) return 1;
+    if (S > 0 && nj > 0) {
+        mb::gather_kernel<<<S, 128, 0, c->stream>>>(c->d_jobs.as<mb::Job>(), c->d_segs.as<mb::Seg>(), S,
+                                                    c->d_cell_off.as<uint32_t>(), c->d_seg_counts.as<int64_t>(),
+                                                    c->d_seg_off.as<int64_t>(), c->d_stage.as<mb::Pair>(), stride,
+                                                    c->d_out.as<mb::Pair>(), n_lists);
+        c->launches++;
+    }
+    {
+        const int threads = 128;
+        const int blocks = (int) ((c->n_aln + 1 + threads - 1) / threads);
+        mb::list_offsets_kernel<<<blocks, threads, 0, c->stream>>>(c->d_aln_first_slot.as<int32_t>(), (int) c->n_aln, S,
+                                                                   c->d_seg_off.as<int64_t>(), c->d_off_out.as<int64_t>());
+        c->launches++;
+    }
+    CU(cudaEventRecord(c->ev1, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    CU(cudaGetLastError());
+    float ms = 0;
+    CU(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+    int64_t segments = 0;
+    const int32_t *nseg = c->h_small.as<int32_t>();
+    for (int j = 0; j < nj; j++) segments += nseg[j];
+    fill_stats(c, out, segments, ms);
+    return 0;
+}
+
+extern "C" int margin_b200_download_result(margin_b200_ctx *c, margin_b200_result *out) {
+    if (!c || !out) return fail("margin_b200_download_result: null argument");
+    CU(cudaSetDevice(c->device));
+    const int64_t n = c->n_aln;
+    if (c->h_out.ensure((size_t) (c->total_tuples + 1) * sizeof(mb::Pair)) ||
+        c->h_off.ensure((size_t) 3 * (n + 1) * sizeof(int64_t)))
+        return 1;
+    if (c->total_tuples)
+        CU(cudaMemcpyAsync(c->h_out.p, c->d_out.p, (size_t) c->total_tuples * sizeof(mb::Pair), cudaMemcpyDeviceToHost,
+                           c->stream));
+    CU(cudaMemcpyAsync(c->h_off.p, c->d_off_out.p, (size_t) 3 * (n + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    const margin_b200_pair *base = c->h_out.as<margin_b200_pair>();
+    int64_t acc = 0;
+    for (int l = 0; l < 3; l++) {
+        out->pairs[l] = base + acc;
+        out->off[l] = c->h_off.as<int64_t>() + (size_t) l * (n + 1);
+        acc += c->list_tuples[l];
+    }
+    return 0;
+}
+
+extern "C" int margin_b200_posteriors_batch(margin_b200_ctx *c, const margin_b200_batch *b, int want_indels,
+                                            margin_b200_result *out) {
+    if (margin_b200_upload_batch(c, b)) return 1;
+    if (margin_b200_posteriors_resident(c, want_indels, out)) return 1;
+    return margin_b200_download_result(c, out);
+}
+
+static_assert(sizeof(mb::Pair) == sizeof(margin_b200_pair), "tuple layouts must agree");
+
+// computeForwardProbability for every alignment of the uploaded batch (impl/pairwiseAligner.c:849-903): static band
+// with diagonalExpansion (callers pass no anchors => the full matrix), forward sweep, end-state dot product.
+// Large-gap splitting does not apply to this entry point, so upload must have produced one job per alignment.
+extern "C" int margin_b200_forward_resident(margin_b200_ctx *c, margin_b200_result *stats) {
+    if (!c) return fail("margin_b200_forward_resident: null argument");
+    if (check_device(c->device)) return 1;
+    CU(cudaSetDevice(c->device));
+    c->launches = 0;
+    const int nj = (int) c->jobs.size();
+    if ((int64_t) nj != c->n_aln)
+        return fail("margin_b200_forward: an alignment was split by splitMatrixBiggerThanThis; the forward-only "
+                    "path takes whole matrices");
+    CU(cudaEventRecord(c->ev0, c->stream));
+    if (run_band(c, false, false, false)) return 1;
+    Bins bins;
+    if (build_bins(c, false, bins, force_group_env())) return 1;
+    if (c->d_F.ensure((size_t) (c->total_cells + 1) * 3 * sizeof(double)) ||
+        c->d_fwd_out.ensure((size_t) (c->n_aln + 1) * sizeof(double)))
+        return 1;
+    launch_forward<8>(c, bins.fwd_off[0], bins.fwd_off[1] - bins.fwd_off[0]);
+    launch_forward<16>(c, bins.fwd_off[1], bins.fwd_off[2] - bins.fwd_off[1]);
+    launch_forward<32>(c, bins.fwd_off[2], bins.fwd_off[3] - bins.fwd_off[2]);
+    if (nj > 0) {
+        mb::final_dot_kernel<<<(nj + 127) / 128, 128, 0, c->stream>>>(c->d_jobs.as<mb::Job>(), nj,
+                                                                      c->d_models.as<mb::DevModel>(),
+                                                                      c->d_cell_off.as<uint32_t>(), c->d_F.as<double>(),
+                                                                      c->d_fwd_out.as<double>());
+        c->launches++;
+    }
+    CU(cudaEventRecord(c->ev1, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    CU(cudaGetLastError());
+    float ms = 0;
+    CU(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+    if (stats) {
+        memset(stats, 0, sizeof(*stats));
+        fill_stats(c, stats, 0, ms);
+    }
+    return 0;
+}
+
+extern "C" int margin_b200_forward_batch(margin_b200_ctx *c, const margin_b200_batch *b, double *out_log_prob,
+                                         margin_b200_result *stats) {
+    if (!c || !b || !out_log_prob) return fail("margin_b200_forward_batch: null argument");
+    // the forward-only path never splits: lift the limit for the upload, then restore it
+    const int64_t saved = c->params.split_matrix_bigger_than_this;
+    c->params.split_matrix_bigger_than_this = INT64_MAX;
+    const int rc = margin_b200_upload_batch(c, b);
+    c->params.split_matrix_bigger_than_this = saved;
+    if (rc) return 1;
+    if (margin_b200_forward_resident(c, stats)) return 1;
+    if (b->n)
+        CU(cudaMemcpyAsync(out_log_prob, c->d_fwd_out.p, (size_t) b->n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+// Band geometry only; the test hook for band_constructDynamic / band_construct (tests/pairwiseAlignerTest.c:64-127).
+extern "C" int margin_b200_bands(margin_b200_ctx *c, const margin_b200_batch *b, int32_t *xmy_l, int32_t *xmy_r) {
+    if (!c || !b || !xmy_l || !xmy_r) return fail("margin_b200_bands: null argument");
+    const int64_t saved = c->params.split_matrix_bigger_than_this;
+    c->params.split_matrix_bigger_than_this = INT64_MAX;
+    const int rc = margin_b200_upload_batch(c, b);
+    c->params.split_matrix_bigger_than_this = saved;
+    if (rc) return 1;
+    c->launches = 0;
+    if (run_band(c, c->params.dynamic_anchor_expansion != 0, false, true)) return 1;
+    // device layout has N+2 entries per job; the caller's has N+1
+    std::vector<int32_t> kl(c->total_diag + 1), kr(c->total_diag + 1);
+    CU(cudaMemcpyAsync(kl.data(), c->d_kl.p, c->total_diag * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemcpyAsync(kr.data(), c->d_kr.p, c->total_diag * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    int64_t o = 0;
+    for (const mb::Job &job : c->jobs) {
+        const int64_t N = (int64_t) job.lx + job.ly;
+        memcpy(xmy_l + o, kl.data() + job.diag_off, (N + 1) * sizeof(int32_t));
+        memcpy(xmy_r + o, kr.data() + job.diag_off, (N + 1) * sizeof(int32_t));
+        o += N + 1;
+    }
+    return 0;
+}

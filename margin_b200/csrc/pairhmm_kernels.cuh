@@ -1,0 +1,675 @@
+// pairhmm_kernels.cuh — CUDA kernels of the banded pair-HMM path (sm_100a).
+//
+// Pipeline for a batch (one launch each, all on the context's stream):
+//   band_kernel      band geometry per anti-diagonal + cell offsets   (band_constructDynamic, pairwiseAligner.c:120-226)
+//   schedule_kernel  traceback segments per job                       (the trigger at pairwiseAligner.c:746-749, :768)
+//   forward_kernel   forward sweep, F stored in HBM                   (diagonalCalculationForward, :566-570)
+//   backward_kernel  per segment: backward, total probability, posterior tuples staged per segment (:572-681, :753-818)
+//   (cub scan)       exclusive scan of per-segment tuple counts in final list order
+//   gather_kernel    staged tuples -> final lists in the reference's stList order (:1104-1123)
+// and for computeForwardProbability (:849-903): band_kernel + forward_kernel + final_dot_kernel,
+// or tiny_forward_kernel when the whole matrix is small (the bubble-graph case).
+//
+// Work decomposition: a "job" is one alignment block (an alignment, or one piece of it after
+// large-gap splitting); a job is swept by a group of G lanes (G = 8, 16 or 32), lane = x mod G,
+// so that the three neighbours of a cell are on the same lane (x, y-1) or on lane-1 (x-1, y) and
+// (x-1, y-1): two rotate-shuffles per state and no shared memory.  Diagonals wider than G fall back
+// to reading the neighbours from the F array in HBM / the B ring in scratch.
+#pragma once
+#include "pairhmm_device.cuh"
+
+namespace mb {
+
+struct Job {
+    int64_t symx_off, symy_off;  // element offsets into the device symbol pools (block start included)
+    int64_t anc_off;             // triple offset into the device anchor pool (already re-based to the block)
+    int64_t diag_off;            // offset into kl[] / cell_off[] (lx+ly+2 entries per job)
+    int64_t cell_base;           // offset of the job's first cell in F / staging (set after band_kernel)
+    int64_t ring_off;            // offset (in cells) of the job's backward ring scratch, per segment slot
+    int32_t lx, ly;
+    int32_t n_anc;
+    int32_t x1, y1;              // block origin, added back to the emitted coordinates
+    int32_t aln;                 // alignment index in the batch
+    int32_t seg_base, max_seg;   // slot range in the segment table
+    int32_t ring_w;              // ring capacity in cells per diagonal (max band width of the job)
+    uint8_t slot, ragged_l, ragged_r, pad;
+};
+
+struct Seg {
+    int32_t job;  // -1 = unused slot
+    int32_t D, tb_to, tb_from;
+    int32_t at_end;
+};
+
+struct Params {
+    double threshold;
+    int32_t min_diags, tb_diags, expansion, dynamic;
+};
+
+// ------------------------------------------------------------------------------------------ band
+
+__device__ __forceinline__ int bound_coord(int z, int l) { return z < 0 ? 0 : (z > l ? l : z); }
+
+// band_setCurrentDiagonal (pairwiseAligner.c:96-114); C division semantics kept (operands are non-negative here
+// after bounding, except the pre-bound values which are bounded before use).
+__device__ __forceinline__ void clip_diagonal(int xay, int xL, int yL, int xU, int yU, int &kl, int &kr) {
+    int l = xL - yL, r = xU - yU;
+    if ((xay + l) & 1) l += 1;
+    if ((xay + r) & 1) r += 1;
+    int i = (xay + l) / 2;
+    if (i < xL) l += 2 * (xL - i);
+    i = (xay - l) / 2;
+    if (yL < i) l += 2 * (i - yL);
+    i = (xay + r) / 2;
+    if (xU < i) r -= 2 * (i - xU);
+    i = (xay - r) / 2;
+    if (i < yU) r -= 2 * (yU - i);
+    kl = l;
+    kr = r;
+}
+
+// One CTA per job.  For every anti-diagonal d the governing (previous, next) anchor pair is found by binary
+// search on the anchors' own anti-diagonals, which makes the walk of band_constructDynamic data-parallel.
+// Writes kl[d] and the exclusive prefix sum of the widths (cell_off[d], d = 0..N+1).
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS)
+band_kernel(const Job *__restrict__ jobs, int n_jobs, const int32_t *__restrict__ anchors, Params p,
+            int32_t *__restrict__ kl_out, uint32_t *__restrict__ cell_off, int64_t *__restrict__ job_cells,
+            int32_t *__restrict__ job_maxw, int32_t *__restrict__ kr_out /* may be null */, int *__restrict__ err) {
+    const int j = blockIdx.x;
+    if (j >= n_jobs) return;
+    const Job job = jobs[j];
+    const int lx = job.lx, ly = job.ly, N = lx + ly, na = job.n_anc;
+    const int32_t *anc = anchors + 3 * job.anc_off;
+    __shared__ uint32_t warp_sums[THREADS / 32];
+    __shared__ uint32_t carry_s;
+    __shared__ int maxw_s;
+    if (threadIdx.x == 0) {
+        carry_s = 0;
+        maxw_s = 0;
+    }
+    __syncthreads();
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    for (int base = 0; base <= N; base += THREADS) {
+        const int d = base + threadIdx.x;
+        int w = 0, kl = 0, kr = 0;
+        if (d <= N) {
+            if (d > 0) {
+                // smallest anchor index i with (ax+1)+(ay+1) >= d
+                int lo = 0, hi = na;
+                while (lo < hi) {
+                    int mid = (lo + hi) >> 1;
+                    int s = anc[3 * mid] + anc[3 * mid + 1] + 2;
+                    if (s >= d) hi = mid; else lo = mid + 1;
+                }
+                int nx = lx, ny = ly, px = 0, py = 0, e;
+                if (lo < na) {
+                    nx = anc[3 * lo] + 1;
+                    ny = anc[3 * lo + 1] + 1;
+                    e = p.dynamic ? anc[3 * lo + 2] : p.expansion;
+                } else {
+                    e = p.dynamic ? (na > 0 ? anc[3 * (na - 1) + 2] : 0) : p.expansion;
+                }
+                if (lo > 0) {
+                    px = anc[3 * (lo - 1)] + 1;
+                    py = anc[3 * (lo - 1) + 1] + 1;
+                }
+                const int pxay = px + py, pxmy = px - py, nxay = nx + ny, nxmy = nx - ny;
+                const int xL = bound_coord((pxay + pxmy - e) / 2, lx);
+                const int yL = bound_coord((nxay - (nxmy - e)) / 2, ly);
+                const int xU = bound_coord((nxay + nxmy + e) / 2, lx);
+                const int yU = bound_coord((pxay - (pxmy + e)) / 2, ly);
+                clip_diagonal(d, xL, yL, xU, yU, kl, kr);
+            }
+            w = (kr - kl) / 2 + 1;
+            if (kr < kl) {  // diagonal_construct would throw (pairwiseAligner.c:22-27)
+                atomicExch(err, 1);
+                w = 1;
+            }
+        }
+        // block-wide exclusive scan of w
+        uint32_t v = (uint32_t) w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            uint32_t n = __shfl_up_sync(0xffffffffu, v, o);
+            if (lane >= o) v += n;
+        }
+        if (lane == 31) warp_sums[wid] = v;
+        int mw = w;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) mw = max(mw, __shfl_xor_sync(0xffffffffu, mw, o));
+        if (lane == 0) atomicMax(&maxw_s, mw);
+        __syncthreads();
+        uint32_t pre = carry_s;
+        for (int k = 0; k < wid; k++) pre += warp_sums[k];
+        uint32_t excl = pre + v - (uint32_t) w;
+        if (d <= N) {
+            kl_out[job.diag_off + d] = kl;
+            if (kr_out) kr_out[job.diag_off + d] = kr;
+            cell_off[job.diag_off + d] = excl;
+        }
+        __syncthreads();
+        if (threadIdx.x == THREADS - 1) carry_s = pre + v;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        cell_off[job.diag_off + N + 1] = carry_s;
+        job_cells[j] = carry_s;
+        job_maxw[j] = maxw_s;
+    }
+}
+
+// -------------------------------------------------------------------------------------- schedule
+
+// One warp per job: replays the traceback trigger of getPosteriorProbsWithBanding (pairwiseAligner.c:746-768),
+// which depends only on band widths.  Segment s of a job is stored at slot seg_base + (max_seg-1-s) so that the
+// slots of an alignment are already in the reference's final list order (later tracebacks first, :1104-1123).
+__global__ void schedule_kernel(const Job *__restrict__ jobs, int n_jobs, const uint32_t *__restrict__ cell_off, Params p,
+                                Seg *__restrict__ segs, int32_t *__restrict__ job_nseg) {
+    const int j = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (j >= n_jobs) return;
+    const Job job = jobs[j];
+    const int N = job.lx + job.ly;
+    const uint32_t *co = cell_off + job.diag_off;
+    int tb_to = 0, s = 0;
+    const int wmax = 2 * p.expansion + 1;
+    while (N > 0) {
+        int D = N, at_end = 1;
+        for (int base = tb_to + p.min_diags; base < N; base += 32) {
+            const int d = base + lane;
+            bool hit = d < N && (int) (co[d + 1] - co[d]) <= wmax;
+            unsigned b = __ballot_sync(0xffffffffu, hit);
+            if (b) {
+                D = base + __ffs(b) - 1;
+                at_end = 0;
+                break;
+            }
+        }
+        const int tb_from = at_end ? D : D - (p.tb_diags + 1);
+        if (lane == 0) {
+            Seg sg;
+            sg.job = j;
+            sg.D = D;
+            sg.tb_to = tb_to;
+            sg.tb_from = tb_from;
+            sg.at_end = at_end;
+            if (s < job.max_seg) segs[job.seg_base + (job.max_seg - 1 - s)] = sg;
+        }
+        s++;
+        tb_to = tb_from;
+        if (at_end) break;
+    }
+    if (lane == 0) job_nseg[j] = s;
+}
+
+
+// --------------------------------------------------------------------------------------- forward
+
+template <int G>
+__device__ __forceinline__ unsigned group_mask() {
+    if constexpr (G == 32) {
+        return 0xffffffffu;
+    } else {
+        return ((1u << G) - 1u) << ((threadIdx.x & 31) / G * G);
+    }
+}
+
+template <int G>
+__device__ __forceinline__ Cell shfl_cell(unsigned mask, const Cell &c, int src) {
+    Cell r;
+    r.m = __shfl_sync(mask, c.m, src, G);
+    r.x = __shfl_sync(mask, c.x, src, G);
+    r.y = __shfl_sync(mask, c.y, src, G);
+    return r;
+}
+
+__device__ __forceinline__ Cell load_cell_cg(const double *base, int64_t cell) {
+    Cell c;
+    const double *q = base + 3 * cell;
+    c.m = __ldcg(q);
+    c.x = __ldcg(q + 1);
+    c.y = __ldcg(q + 2);
+    return c;
+}
+
+__device__ __forceinline__ void store_cell(double *base, int64_t cell, const Cell &c) {
+    double *q = base + 3 * cell;
+    q[0] = c.m;
+    q[1] = c.x;
+    q[2] = c.y;
+}
+
+__device__ __forceinline__ unsigned sym_at(const uint16_t *s, int i) {  // getXCharacter / getYCharacter (:535-545)
+    return i > 0 ? (unsigned) __ldg(s + i - 1) : 4u;
+}
+
+// One forward cell: stateMachine3_cellCalculate + doTransitionForward (stateMachine.c:562-586, pairwiseAligner.c:311-314).
+// Each target state folds its three sources left to right starting from -inf; logAdd(-inf, v) == v.
+__device__ __forceinline__ Cell forward_cell(const DevModel &m, bool has_lower, const Cell &lower, bool has_middle,
+                                             const Cell &middle, bool has_upper, const Cell &upper, unsigned cx,
+                                             unsigned cy) {
+    Cell c = cell_neg_inf();
+    if (has_lower) {
+        const double *e = m.ex_t[gap_index(m, cx)];
+        double a = dadd(lower.m, e[0]);
+        a = logadd(a, dadd(lower.x, e[1]));
+        a = logadd(a, dadd(lower.y, e[2]));
+        c.x = a;
+    }
+    if (has_middle) {
+        const double e = emit_match(m, cx, cy);
+        double a = dadd(middle.m, dadd(e, m.t[T_MM]));
+        a = logadd(a, dadd(middle.x, dadd(e, m.t[T_XM])));
+        a = logadd(a, dadd(middle.y, dadd(e, m.t[T_YM])));
+        c.m = a;
+    }
+    if (has_upper) {
+        const double *e = m.ey_t[gap_index(m, cy)];
+        double a = dadd(upper.m, e[0]);
+        a = logadd(a, dadd(upper.y, e[1]));
+        a = logadd(a, dadd(upper.x, e[2]));
+        c.y = a;
+    }
+    return c;
+}
+
+__device__ __forceinline__ int mod_g(int v, int G) { return v & (G - 1); }
+
+// Forward sweep.  One group of G lanes per job; lane = x mod G.  F (3 doubles per band cell) goes to HBM for the
+// backward kernel.  Neighbour diagonals no wider than G stay in registers and move by one rotate-shuffle.
+template <int G, int THREADS>
+__global__ void __launch_bounds__(THREADS)
+forward_kernel(const Job *__restrict__ jobs, const int32_t *__restrict__ job_ids, int n_ids,
+               const DevModel *__restrict__ models, const uint16_t *__restrict__ symx,
+               const uint16_t *__restrict__ symy, const int32_t *__restrict__ kl_arr,
+               const uint32_t *__restrict__ cell_off, double *__restrict__ F) {
+    __shared__ DevModel sm[2];
+    for (int i = threadIdx.x; i < (int) (2 * sizeof(DevModel) / 8); i += THREADS)
+        reinterpret_cast<double *>(sm)[i] = reinterpret_cast<const double *>(models)[i];
+    __syncthreads();
+    const int g = (blockIdx.x * THREADS + threadIdx.x) / G;
+    if (g >= n_ids) return;
+    const unsigned gm = group_mask<G>();
+    const int lane = threadIdx.x & (G - 1);
+    const Job job = jobs[job_ids[g]];
+    const DevModel &m = sm[job.slot];
+    const int N = job.lx + job.ly;
+    const uint16_t *sx = symx + job.symx_off, *sy = symy + job.symy_off;
+    const int32_t *kls = kl_arr + job.diag_off;
+    const uint32_t *co = cell_off + job.diag_off;
+    double *Fj = F + 3 * job.cell_base;
+
+    // diagonal 0: the single cell (0,0) holds the start state (stateMachine.c:521-530)
+    Cell f1 = cell_neg_inf(), f2 = cell_neg_inf();
+    if (lane == 0) {
+        f1.m = job.ragged_l ? MB_NEG_INF : 0.0;
+        f1.x = job.ragged_l ? 0.0 : MB_NEG_INF;
+        f1.y = f1.x;
+        store_cell(Fj, 0, f1);
+    }
+    int xlo1 = 0, w1 = 1, xlo2 = 0, w2 = 0;
+    uint32_t co1 = 0, co2 = 0;
+    const int prev_lane = mod_g(lane - 1, G);
+    for (int d = 1; d <= N; d++) {
+        const int kl = kls[d];
+        const uint32_t cod = co[d];
+        const int w = (int) (co[d + 1] - cod);
+        const int xlo = (d + kl) >> 1;
+        const int xhi = xlo + w - 1;
+        const int nch = (w + G - 1) / G;
+        if (w1 > G || w2 > G) __syncwarp(gm);  // make the earlier diagonals' stores visible to the group
+        Cell cur = cell_neg_inf();
+        for (int jc = 0; jc < nch; jc++) {
+            const int x = xlo + mod_g(lane - xlo, G) + jc * G;
+            const int y = d - x;
+            const bool active = x <= xhi;
+            const bool has_lower = active && (x - 1 >= xlo1) && (x - 1 < xlo1 + w1);
+            const bool has_upper = active && (x >= xlo1) && (x < xlo1 + w1);
+            const bool has_middle = active && (w2 > 0) && (x - 1 >= xlo2) && (x - 1 < xlo2 + w2);
+            Cell lower, upper, middle;
+            if (w1 <= G) {
+                lower = shfl_cell<G>(gm, f1, prev_lane);
+                upper = f1;
+            } else {
+                if (has_lower) lower = load_cell_cg(Fj, (int64_t) co1 + (x - 1 - xlo1));
+                if (has_upper) upper = load_cell_cg(Fj, (int64_t) co1 + (x - xlo1));
+            }
+            if (w2 <= G) {
+                middle = shfl_cell<G>(gm, f2, prev_lane);
+            } else {
+                if (has_middle) middle = load_cell_cg(Fj, (int64_t) co2 + (x - 1 - xlo2));
+            }
+            if (active) {
+                Cell c = forward_cell(m, has_lower, lower, has_middle, middle, has_upper, upper, sym_at(sx, x),
+                                      sym_at(sy, y));
+                store_cell(Fj, (int64_t) cod + (x - xlo), c);
+                cur = c;
+            }
+        }
+        f2 = f1;
+        xlo2 = xlo1;
+        w2 = w1;
+        co2 = co1;
+        f1 = cur;
+        xlo1 = xlo;
+        w1 = w;
+        co1 = cod;
+    }
+}
+
+
+// -------------------------------------------------------------------------------------- backward
+
+struct Pair {
+    int32_t w, x, y;
+};
+
+// Gather form of diagonalCalculationBackward (pairwiseAligner.c:572-576 with doTransitionBackward :322-325).
+// The reference scatters from a cell into its three neighbours; a cell (x,y) of diagonal d therefore receives,
+// in this order: its match term from (x+1,y+1) while d+2 is processed, then while d+1 is processed (cells in
+// ascending x-y) the gap-Y term from (x,y+1) and the gap-X term from (x+1,y).  Folding in that order from -inf
+// reproduces the scatter bit for bit.
+__device__ __forceinline__ Cell backward_cell(const DevModel &m, bool has_mm, double b2m, bool has_y, double b1y_y,
+                                              bool has_x, double b1x_x, unsigned cx1, unsigned cy1) {
+    // cx1 = sX[x] (the symbol consumed when moving to x+1), cy1 = sY[y]
+    Cell c = cell_neg_inf();
+    if (has_mm) {
+        const double e = emit_match(m, cx1, cy1);
+        c.m = dadd(b2m, dadd(e, m.t[T_MM]));
+        c.x = dadd(b2m, dadd(e, m.t[T_XM]));
+        c.y = dadd(b2m, dadd(e, m.t[T_YM]));
+    }
+    if (has_y) {
+        const double *e = m.ey_t[gap_index(m, cy1)];  // [0]=M->Y, [1]=Y->Y, [2]=X->Y
+        c.m = logadd(c.m, dadd(b1y_y, e[0]));
+        c.x = logadd(c.x, dadd(b1y_y, e[2]));
+        c.y = logadd(c.y, dadd(b1y_y, e[1]));
+    }
+    if (has_x) {
+        const double *e = m.ex_t[gap_index(m, cx1)];  // [0]=M->X, [1]=X->X, [2]=Y->X
+        c.m = logadd(c.m, dadd(b1x_x, e[0]));
+        c.x = logadd(c.x, dadd(b1x_x, e[1]));
+        c.y = logadd(c.y, dadd(b1x_x, e[2]));
+    }
+    return c;
+}
+
+// Sequential (non-associative!) logAdd fold of one value per band cell, cells in ascending x, as
+// dpDiagonal_dotProduct does (pairwiseAligner.c:450-461).  `val` is this lane's value for chunk jc.
+template <int G>
+__device__ __forceinline__ double fold_chunk(unsigned gm, double acc, double val, int xlo, int jc, int w) {
+    const int n = min(G, w - jc * G);
+    for (int i = 0; i < n; i++) {
+        const double v = __shfl_sync(gm, val, mod_g(xlo + i, G), G);
+        acc = logadd(acc, v);
+    }
+    return acc;
+}
+
+__device__ __forceinline__ bool posterior_weight(double f, double b, double total, double threshold, int32_t &w) {
+    // exp((F + B) - total), threshold, clamp, floor(p * 1e7): pairwiseAligner.c:598-608, :629-631
+    double pr = exp(dadd(dadd(f, b), -total));
+    if (!(pr >= threshold)) return false;
+    if (pr > 1.0) pr = 1.0;
+    w = (int32_t) floor(dmul(pr, 10000000.0));
+    return true;
+}
+
+template <int G>
+__device__ __forceinline__ void emit_list(unsigned gm, bool ok, int32_t wt, int x, int y, int rank, int xlo, Pair *dst,
+                                          int &cnt) {
+    unsigned bits = __ballot_sync(gm, ok);
+    const int r = mod_g(xlo, G);
+    unsigned rot;
+    if constexpr (G == 32) {
+        rot = __funnelshift_r(bits, bits, r);
+    } else {
+        bits = (bits >> ((threadIdx.x & 31) / G * G)) & ((1u << G) - 1u);
+        rot = ((bits >> r) | (bits << (G - r))) & ((1u << G) - 1u);
+    }
+    if (ok) {
+        const int pos = cnt + __popc(rot & ((1u << rank) - 1u));
+        Pair pr;
+        pr.w = wt;
+        pr.x = x;
+        pr.y = y;
+        dst[pos] = pr;
+    }
+    cnt += __popc(bits);
+}
+
+// One group of G lanes per traceback segment (the walk-back loop of getPosteriorProbsWithBanding,
+// pairwiseAligner.c:753-818).  Segments are independent once F is in HBM, so all tracebacks of all reads run
+// concurrently.  Tuples are staged per segment in emission order; gather_kernel puts them in list order.
+template <int G, int THREADS, bool INDELS>
+__global__ void __launch_bounds__(THREADS)
+backward_kernel(const Job *__restrict__ jobs, const Seg *__restrict__ segs, const int32_t *__restrict__ slot_ids,
+                int n_ids, const DevModel *__restrict__ models, const uint16_t *__restrict__ symx,
+                const uint16_t *__restrict__ symy, const int32_t *__restrict__ kl_arr,
+                const uint32_t *__restrict__ cell_off, const double *__restrict__ F, Params p,
+                double *__restrict__ ring, const int64_t *__restrict__ slot_ring_off, Pair *__restrict__ stage,
+                int64_t stage_stride, int64_t *__restrict__ seg_counts, int total_slots) {
+    __shared__ DevModel sm[2];
+    for (int i = threadIdx.x; i < (int) (2 * sizeof(DevModel) / 8); i += THREADS)
+        reinterpret_cast<double *>(sm)[i] = reinterpret_cast<const double *>(models)[i];
+    __syncthreads();
+    const int g = (blockIdx.x * THREADS + threadIdx.x) / G;
+    if (g >= n_ids) return;
+    const int slot = slot_ids[g];
+    const Seg seg = segs[slot];
+    if (seg.job < 0) return;
+    const unsigned gm = group_mask<G>();
+    const int lane = threadIdx.x & (G - 1);
+    const Job job = jobs[seg.job];
+    const DevModel &m = sm[job.slot];
+    const uint16_t *sx = symx + job.symx_off, *sy = symy + job.symy_off;
+    const int32_t *kls = kl_arr + job.diag_off;
+    const uint32_t *co = cell_off + job.diag_off;
+    const double *Fj = F + 3 * job.cell_base;
+    const int ring_w = job.ring_w;
+    double *rg = ring + 3 * slot_ring_off[slot];
+    const int D = seg.D, tb_to = seg.tb_to, tb_from = seg.tb_from;
+    const double *endp = m.end_p[(seg.at_end && job.ragged_r) ? 1 : 0];
+    const int64_t region = job.cell_base + co[tb_to + 1];
+    Pair *stM = stage + region, *stX = stage + stage_stride + region, *stY = stage + 2 * stage_stride + region;
+    int cntM = 0, cntX = 0, cntY = 0;
+
+    Cell b1 = cell_neg_inf(), b2 = cell_neg_inf();
+    int xlo1 = 0, w1 = 0, xlo2 = 0, w2 = 0;
+    const int next_lane = mod_g(lane + 1, G);
+    double total = MB_NEG_INF;
+    int done = 0;
+    for (int d = D; d > tb_to; d--) {
+        const int kl = kls[d];
+        const uint32_t cod = co[d];
+        const int w = (int) (co[d + 1] - cod);
+        const int xlo = (d + kl) >> 1;
+        const int xhi = xlo + w - 1;
+        const int nch = (w + G - 1) / G;
+        const bool post = d <= tb_from;
+        const bool do_total = post && (done % 10 == 0);
+        if (w > G || w1 > G || w2 > G) __syncwarp(gm);
+        double *rg_d = rg + 3 * (int64_t) ((d % 3) * ring_w);
+        const double *rg_d1 = rg + 3 * (int64_t) (((d + 1) % 3) * ring_w);
+        const double *rg_d2 = rg + 3 * (int64_t) (((d + 2) % 3) * ring_w);
+        Cell cur = cell_neg_inf();
+        double first = MB_NEG_INF;
+        // ---- pass 1: backward values of diagonal d (+ first term of the total probability)
+        for (int jc = 0; jc < nch; jc++) {
+            const int x = xlo + mod_g(lane - xlo, G) + jc * G;
+            const int y = d - x;
+            const bool active = x <= xhi;
+            Cell b;
+            if (d == D) {
+                b.m = endp[0];
+                b.x = endp[1];
+                b.y = endp[2];
+            } else {
+                const bool has_mm = active && w2 > 0 && (x + 1 >= xlo2) && (x + 1 < xlo2 + w2);
+                const bool has_y = active && (x >= xlo1) && (x < xlo1 + w1);
+                const bool has_x = active && (x + 1 >= xlo1) && (x + 1 < xlo1 + w1);
+                double b2m = 0, b1yy = 0, b1xx = 0;
+                if (w2 > 0) {
+                    if (w2 <= G) b2m = __shfl_sync(gm, b2.m, next_lane, G);
+                    else if (has_mm) b2m = __ldcg(rg_d2 + 3 * (x + 1 - xlo2));
+                }
+                if (w1 <= G) {
+                    b1yy = b1.y;
+                    b1xx = __shfl_sync(gm, b1.x, next_lane, G);
+                } else {
+                    if (has_y) b1yy = __ldcg(rg_d1 + 3 * (x - xlo1) + 2);
+                    if (has_x) b1xx = __ldcg(rg_d1 + 3 * (x + 1 - xlo1) + 1);
+                }
+                b = cell_neg_inf();
+                if (active) b = backward_cell(m, has_mm, b2m, has_y, b1yy, has_x, b1xx, sym_at(sx, x + 1), sym_at(sy, y + 1));
+            }
+            if (active) {
+                cur = b;
+                if (w > G) {
+                    double *q = rg_d + 3 * (x - xlo);
+                    q[0] = b.m;
+                    q[1] = b.x;
+                    q[2] = b.y;
+                }
+            }
+            if (do_total) {
+                double dot = MB_NEG_INF;
+                if (active) {
+                    Cell f = load_cell_cg(Fj, (int64_t) cod + (x - xlo));
+                    dot = cell_dot(f, b);
+                }
+                first = fold_chunk<G>(gm, first, dot, xlo, jc, w);
+            }
+        }
+        if (post) {
+            if (do_total) {
+                // second term (pairwiseAligner.c:586-594): paths that jump over d with a match, i.e. the match block
+                // of the forward recursion from F(d-1) into the cells of d+1, dotted with B(d+1).
+                total = first;
+                if (d < D) {
+                    double second = MB_NEG_INF;
+                    const int klm = kls[d - 1];
+                    const uint32_t com = co[d - 1];
+                    const int wm = (int) (co[d] - com);
+                    const int xlom = (d - 1 + klm) >> 1;
+                    const int nch1 = (w1 + G - 1) / G;
+                    for (int jc = 0; jc < nch1; jc++) {
+                        const int x = xlo1 + mod_g(lane - xlo1, G) + jc * G;
+                        const int y = d + 1 - x;
+                        const bool active = x < xlo1 + w1;
+                        double val = MB_NEG_INF;
+                        if (active) {
+                            double gm_ = MB_NEG_INF;
+                            if (x - 1 >= xlom && x - 1 < xlom + wm) {
+                                Cell f = load_cell_cg(Fj, (int64_t) com + (x - 1 - xlom));
+                                const double e = emit_match(m, sym_at(sx, x), sym_at(sy, y));
+                                gm_ = dadd(f.m, dadd(e, m.t[T_MM]));
+                                gm_ = logadd(gm_, dadd(f.x, dadd(e, m.t[T_XM])));
+                                gm_ = logadd(gm_, dadd(f.y, dadd(e, m.t[T_YM])));
+                            }
+                            double b1m = (w1 <= G) ? b1.m : __ldcg(rg_d1 + 3 * (x - xlo1));
+                            val = dadd(gm_, b1m);
+                        }
+                        second = fold_chunk<G>(gm, second, val, xlo1, jc, w1);
+                    }
+                    total = logadd(total, second);
+                }
+            }
+            // ---- pass 2: posteriors of diagonal d (diagonalCalculationPosteriorProbs, :637-681)
+            for (int jc = 0; jc < nch; jc++) {
+                const int rank = mod_g(lane - xlo, G);
+                const int x = xlo + rank + jc * G;
+                const int y = d - x;
+                const bool active = x <= xhi;
+                Cell b = cur, f = cell_neg_inf();
+                if (active) {
+                    if (w > G) b = load_cell_cg(rg_d, x - xlo);
+                    f = load_cell_cg(Fj, (int64_t) cod + (x - xlo));
+                }
+                int32_t wt = 0;
+                bool ok = active && x > 0 && y > 0 && posterior_weight(f.m, b.m, total, p.threshold, wt);
+                emit_list<G>(gm, ok, wt, x - 1 + job.x1, y - 1 + job.y1, rank, xlo, stM, cntM);
+                if (INDELS) {
+                    ok = active && x > 0 && posterior_weight(f.x, b.x, total, p.threshold, wt);
+                    emit_list<G>(gm, ok, wt, x - 1 + job.x1, y - 1 + job.y1, rank, xlo, stX, cntX);
+                    ok = active && y > 0 && posterior_weight(f.y, b.y, total, p.threshold, wt);
+                    emit_list<G>(gm, ok, wt, x - 1 + job.x1, y - 1 + job.y1, rank, xlo, stY, cntY);
+                }
+            }
+            done++;
+        }
+        b2 = b1;
+        xlo2 = xlo1;
+        w2 = w1;
+        b1 = cur;
+        xlo1 = xlo;
+        w1 = w;
+    }
+    if (lane == 0) {
+        seg_counts[slot] = cntM;
+        seg_counts[total_slots + slot] = cntX;
+        seg_counts[2 * total_slots + slot] = cntY;
+    }
+}
+
+
+// ---------------------------------------------------------------------------------------- gather
+
+// Moves the staged tuples of every segment into the final lists.  seg_off is the exclusive scan of seg_counts over
+// [list][slot]; slots are already in final order (schedule_kernel), and inside a segment the reference's pop loop
+// (pairwiseAligner.c:1104-1123) reverses the emission order.
+__global__ void gather_kernel(const Job *__restrict__ jobs, const Seg *__restrict__ segs, int total_slots,
+                              const uint32_t *__restrict__ cell_off, const int64_t *__restrict__ seg_counts,
+                              const int64_t *__restrict__ seg_off, const Pair *__restrict__ stage, int64_t stage_stride,
+                              Pair *__restrict__ out, int n_lists) {
+    const int slot = blockIdx.x;
+    const Seg seg = segs[slot];
+    if (seg.job < 0) return;
+    const Job job = jobs[seg.job];
+    const int64_t region = job.cell_base + cell_off[job.diag_off + seg.tb_to + 1];
+    for (int l = 0; l < n_lists; l++) {
+        const int64_t c = seg_counts[(int64_t) l * total_slots + slot];
+        const int64_t o = seg_off[(int64_t) l * total_slots + slot];
+        const Pair *src = stage + (int64_t) l * stage_stride + region;
+        for (int64_t i = threadIdx.x; i < c; i += blockDim.x) out[o + i] = src[c - 1 - i];
+    }
+}
+
+// Per-alignment list offsets (relative to the start of each list) from the scanned slot offsets.
+__global__ void list_offsets_kernel(const int32_t *__restrict__ aln_first_slot, int n_aln, int total_slots,
+                                    const int64_t *__restrict__ seg_off, int64_t *__restrict__ off_out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i > n_aln) return;
+    for (int l = 0; l < 3; l++) {
+        const int64_t base = seg_off[(int64_t) l * total_slots];
+        const int64_t v = i < n_aln ? seg_off[(int64_t) l * total_slots + aln_first_slot[i]]
+                                    : seg_off[(int64_t) (l + 1) * total_slots];
+        off_out[(int64_t) l * (n_aln + 1) + i] = v - base;
+    }
+}
+
+// computeForwardProbability's last step (pairwiseAligner.c:881-891): the only cell of the last diagonal is
+// (lX, lY); total = cell_dotProduct(F, end state probs).  An empty problem returns LOG_ONE (:860-862).
+__global__ void final_dot_kernel(const Job *__restrict__ jobs, int n_jobs, const DevModel *__restrict__ models,
+                                 const uint32_t *__restrict__ cell_off, const double *__restrict__ F,
+                                 double *__restrict__ out) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n_jobs) return;
+    const Job job = jobs[j];
+    const int N = job.lx + job.ly;
+    if (N == 0) {
+        out[job.aln] = 0.0;
+        return;
+    }
+    const DevModel &m = models[job.slot];
+    Cell f = load_cell_cg(F + 3 * job.cell_base, cell_off[job.diag_off + N]);
+    Cell e;
+    e.m = m.end_p[job.ragged_r ? 1 : 0][0];
+    e.x = m.end_p[job.ragged_r ? 1 : 0][1];
+    e.y = m.end_p[job.ragged_r ? 1 : 0][2];
+    // dpDiagonal_dotProduct folds from -inf: logAdd(-inf, v) == v
+    out[job.aln] = cell_dot(f, e);
+}
+
+}  // namespace mb

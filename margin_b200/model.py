@@ -193,3 +193,25 @@ def default_nucleotide_model():
     m.rle = 0
     m.max_rl = abi.MAX_RL
     return m
+
+
+def load_flat_model(path):
+    """Reads a flattened model file (2 x margin_b200_model, margin_b200_params, 3 int32 flags).
+
+    This is the form in which a host program hands its already-parsed PolishParams to the library when the
+    params JSON is not around (e.g. tests/golden/model_*.bin, produced by the reference's own parser).
+    """
+    import ctypes as C
+
+    with open(path, "rb") as fh:
+        raw = fh.read()
+    ms, ps = C.sizeof(abi.Model), C.sizeof(abi.Params)
+    if len(raw) != 2 * ms + ps + 12:
+        raise ValueError("%s: unexpected size %d" % (path, len(raw)))
+    pm = PolishModel()
+    pm.models = (abi.Model.from_buffer_copy(raw[0:ms]), abi.Model.from_buffer_copy(raw[ms:2 * ms]))
+    pm.p = abi.Params.from_buffer_copy(raw[2 * ms:2 * ms + ps])
+    flags = [int.from_bytes(raw[2 * ms + ps + 4 * i:2 * ms + ps + 4 * i + 4], "little", signed=True) for i in range(3)]
+    pm.use_rle, pm.use_repeat_counts = bool(flags[0]), bool(flags[1])
+    pm.rsm = [] if pm.use_repeat_counts else None
+    return pm

@@ -1,0 +1,47 @@
+"""Seeded random alignment problems shared by the parity tests (own xorshift-free numpy RNG)."""
+import numpy as np
+
+
+def random_symbols(rng, n, rle=True, n_frac=0.02, max_rl=51):
+    b = rng.integers(0, 4, n).astype(np.uint16)
+    if n_frac > 0:
+        b[rng.random(n) < n_frac] = 4
+    if rle:
+        rl = np.minimum(rng.geometric(0.55, n), max_rl - 1).astype(np.uint16)
+        if n > 3:
+            rl[rng.integers(0, n)] = max_rl - 1  # exercise the clipped maximum
+        b = (rl << 8) | b
+    return b
+
+
+def mutate(rng, sx, sub=0.05, ins=0.04, dele=0.04, rle=True):
+    """Returns (sy, anchors) where anchors are the true match columns (x, y)."""
+    sy, anchors = [], []
+    for x, s in enumerate(sx):
+        r = rng.random()
+        if r < dele:
+            continue
+        if r < dele + ins:
+            sy.append(int(random_symbols(rng, 1, rle, 0.0)[0]))
+        if rng.random() < sub:
+            s2 = int(random_symbols(rng, 1, rle, 0.0)[0])
+        else:
+            s2 = int(s)
+            if rle and rng.random() < 0.15:
+                rlv = max(1, min(50, (s2 >> 8) + int(rng.integers(-1, 2))))
+                s2 = (rlv << 8) | (s2 & 255)
+        anchors.append((x, len(sy)))
+        sy.append(s2)
+    return np.array(sy, dtype=np.uint16), anchors
+
+
+def random_case(rng, lx, rle=True, anchor_keep=0.7, expansions=(0, 2, 4, 10), ragged=True, n_frac=0.02):
+    sx = random_symbols(rng, lx, rle, n_frac)
+    sy, true = mutate(rng, sx, rle=rle)
+    anchors = [(x, y, int(rng.choice(expansions))) for (x, y) in true if rng.random() < anchor_keep]
+    if rng.random() < 0.15:
+        anchors = []
+    rl = int(ragged and rng.random() < 0.3)
+    rr = int(ragged and rng.random() < 0.3)
+    slot = int(rng.random() < 0.5)
+    return sx, sy, np.array(anchors, dtype=np.int32).reshape(-1, 3), slot, rl, rr

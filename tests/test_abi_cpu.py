@@ -1,0 +1,45 @@
+"""CPU checks of the boundary: the C-ABI library loads and exports every symbol include/margin_b200.h declares
+(no compute calls here), and refuses to compute without a device."""
+import ctypes as C
+import os
+import re
+
+import pytest
+
+from margin_b200 import abi
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared():
+    src = open(os.path.join(ROOT, "include", "margin_b200.h")).read()
+    return sorted(set(re.findall(r"\b(margin_b200_[a-z_]+)\s*\(", src)))
+
+
+def test_library_exports_every_declared_symbol():
+    if not os.path.exists(abi.LIB_PATH):
+        import __graft_entry__ as g
+        g.build()
+    lib = C.CDLL(abi.LIB_PATH)
+    names = _declared()
+    assert len(names) >= 13
+    for n in names:
+        assert hasattr(lib, n), n
+    assert sorted(abi.EXPORTED_SYMBOLS) == names
+
+
+def test_struct_layouts_match_header():
+    assert C.sizeof(abi.Model) == 8 * (9 + 16 + 4 + 4) + 8 + 8 * 4 * 51 * 51
+    assert C.sizeof(abi.Params) == 48
+    assert C.sizeof(abi.BatchStruct) == 80
+    assert abi.PAIR_DTYPE.itemsize == 12
+
+
+def test_no_cpu_fallback_without_device():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a device is present")
+    lib = abi.load_library()
+    h = C.c_void_p()
+    assert lib.margin_b200_create(C.byref(h), 0) != 0
+    assert b"no usable CUDA device" in lib.margin_b200_last_error()

@@ -1,0 +1,154 @@
+"""GPU parity tests proper: everything goes through the C ABI (libmargin_b200.so) on cuda:0 and is compared with
+the oracle, the committed golden vectors of the reference, and (where oracle/_ref travelled) the reference itself."""
+import os
+
+import numpy as np
+import pytest
+
+import gen
+from common import compare_lists, load_golden_cases
+from margin_b200 import abi, model, symbols
+from margin_b200.aligner import AlignerError, PairHmmAligner
+
+pytestmark = pytest.mark.gpu
+
+
+def _mk_batch(rng, n, max_len, rle=True, **kw):
+    return [gen.random_case(rng, int(rng.integers(0, max_len)), rle=rle, **kw) for _ in range(n)]
+
+
+@pytest.mark.parametrize("name", ["r94g360", "r94g344", "hifi", "no_rle"])
+def test_golden_vectors_of_the_reference(golden_model, name):
+    pm = golden_model(name)
+    al = PairHmmAligner(pm.models, pm.p, 0)
+    ndiff = ntot = 0
+    for c in load_golden_cases(name):
+        al.set_params(pm.p.copy(min_diags_between_traceback=c["min_diags"], dynamic_anchor_expansion=c["dynamic"]))
+        item = (c["sx"], c["sy"], c["a"], c["slot"], c["rl"], c["rr"])
+        got = al.posteriors_batch([item], True)[0]
+        ndiff += compare_lists(got, c["lists"], tol_w=1)
+        ntot += sum(len(x) for x in got)
+        fwd = al.forward_batch([(c["sx"][:60], c["sy"][:60], np.zeros((0, 3), np.int32), c["slot"], c["rl"], c["rr"])])
+        assert fwd[0] == c["fwd"]  # FP64 forward sweep is bit-exact
+        kl, kr = al.bands([item])[0]
+        assert np.array_equal(kl, c["kl"]) and np.array_equal(kr, c["kr"])
+    # weights may differ by one unit only where device exp() and glibc exp() round differently
+    assert ndiff <= max(2, ntot // 100000)
+    al.close()
+
+
+@pytest.mark.parametrize("force_group", ["", "8", "32"])
+def test_random_batch_vs_oracle(oracle, golden_model, force_group, monkeypatch):
+    """Mixed batch: empty and 1-symbol sequences, no anchors (full matrix => wide diagonals), ragged ends, N symbols,
+    clipped run lengths, both strands, several tracebacks.  MARGIN_B200_FORCE_GROUP exercises the wide-diagonal
+    fallback (diagonals wider than the lane group) and the 32-lane path on every job."""
+    if force_group:
+        monkeypatch.setenv("MARGIN_B200_FORCE_GROUP", force_group)
+    pm = golden_model("r94g360")
+    rng = np.random.default_rng(17)
+    items = _mk_batch(rng, 96, 420)
+    items[0] = (np.zeros(0, np.uint16), np.zeros(0, np.uint16), np.zeros((0, 3), np.int32), 0, 0, 0)
+    items[1] = (items[1][0][:1], np.zeros(0, np.uint16), np.zeros((0, 3), np.int32), 1, 0, 0)
+    items[2] = (np.zeros(0, np.uint16), items[2][1][:3], np.zeros((0, 3), np.int32), 0, 1, 1)
+    for md, dyn, wi in ((5000, 1, 1), (90, 1, 1), (64, 0, 1), (130, 1, 0)):
+        p = pm.p.copy(min_diags_between_traceback=md, dynamic_anchor_expansion=dyn)
+        al = PairHmmAligner(pm.models, p, 0)
+        res = al.posteriors_batch(items, bool(wi))
+        ndiff = 0
+        for i, it in enumerate(items):
+            want = oracle.posteriors(pm.models[it[3]], p, it[0], it[1], it[2], it[4], it[5], wi)
+            ndiff += compare_lists(res[i], want, tol_w=1)
+        assert ndiff <= 2
+        assert res.stats["kernel_launches"] > 0 and res.stats["band_cells"] > 0
+        al.close()
+
+
+def test_long_alignment_many_tracebacks(oracle, golden_model):
+    pm = golden_model("r94g360")
+    rng = np.random.default_rng(23)
+    items = [gen.random_case(rng, 9000, anchor_keep=0.9, expansions=(4,), ragged=False) for _ in range(3)]
+    al = PairHmmAligner(pm.models, pm.p, 0)  # shipped parameters: traceback every >= 5000 diagonals
+    res = al.posteriors_batch(items, True)
+    assert res.stats["segments"] >= 3 * 3
+    for i, it in enumerate(items):
+        want = oracle.posteriors(pm.models[it[3]], pm.p, it[0], it[1], it[2], it[4], it[5], 1)
+        compare_lists(res[i], want, tol_w=1)
+    al.close()
+
+
+def test_forward_only_batch(oracle, golden_model):
+    """computeForwardProbability on bubble-graph-sized problems (median 11x11) and a few larger ones: bit-exact."""
+    pm = golden_model("r94g360")
+    rng = np.random.default_rng(29)
+    items = []
+    for i in range(400):
+        sx = gen.random_symbols(rng, int(rng.integers(0, 44)), True, 0.02)
+        sy = gen.random_symbols(rng, int(rng.integers(0, 44)), True, 0.02)
+        items.append((sx, sy, np.zeros((0, 3), np.int32), int(rng.integers(0, 2)), int(rng.random() < 0.2),
+                      int(rng.random() < 0.2)))
+    al = PairHmmAligner(pm.models, pm.p, 0)
+    got = al.forward_batch(items)
+    for i, it in enumerate(items):
+        want = oracle.forward(pm.models[it[3]], pm.p, it[0], it[1], (), it[4], it[5])
+        assert got[i] == want, (i, got[i], want)
+    al.close()
+
+
+def test_known_answers_on_gpu():
+    """test_diagonalDPCalculations (tests/pairwiseAlignerTest.c:257-342) and test_bands (:64-127) through the GPU."""
+    m = model.default_nucleotide_model()
+    p = abi.Params.defaults().copy(threshold=0.2)
+    al = PairHmmAligner((m, m), p, 0)
+    sx, sy = symbols.bases_to_symbols("AGCG"), symbols.bases_to_symbols("AGTTCG")
+    pairs = al.get_aligned_pairs(0, sx, sy)
+    assert sorted((int(t["x"]), int(t["y"])) for t in pairs) == [(0, 0), (1, 1), (2, 4), (3, 5)]
+    al.set_params(abi.Params.defaults().copy(diagonal_expansion=2, dynamic_anchor_expansion=0))
+    kl, kr = al.bands([(np.zeros(6, np.uint16), np.zeros(5, np.uint16), [(1, 0, 2), (2, 1, 2), (3, 3, 2)], 0, 0, 0)])[0]
+    assert list(zip(kl.tolist(), kr.tolist())) == [(0, 0), (-1, 1), (-2, 2), (-1, 3), (-2, 4), (-1, 3), (-2, 4), (-3, 3),
+                                                    (-2, 2), (-1, 3), (0, 2), (1, 1)]
+    al.close()
+
+
+def test_large_gap_split_vs_oracle(oracle, golden_model):
+    """Multi-block alignments (the unpatched reference is broken here; the oracle implements the
+    intended semantics, validated in the survey against the one-line-patched reference)."""
+    pm = golden_model("r94g360")
+    rng = np.random.default_rng(31)
+    items = [gen.random_case(rng, int(rng.integers(150, 500)), anchor_keep=0.04) for _ in range(40)]
+    p = pm.p.copy(split_matrix_bigger_than_this=60 * 60, min_diags_between_traceback=100)
+    al = PairHmmAligner(pm.models, p, 0)
+    res = al.posteriors_batch(items, True)
+    assert res.stats["jobs"] > len(items)
+    for i, it in enumerate(items):
+        want = oracle.posteriors(pm.models[it[3]], p, it[0], it[1], it[2], it[4], it[5], 1)
+        compare_lists(res[i], want, tol_w=1)
+    al.close()
+
+
+def test_reference_itself_on_this_box(reference, golden_model):
+    """Where oracle/_ref travelled with the snapshot: GPU vs the unmodified reference, same process."""
+    pm = golden_model("r94g360")
+    sms = [reference.sm_from_model(pm.models[s]) for s in (0, 1)]
+    rng = np.random.default_rng(37)
+    items = _mk_batch(rng, 32, 600)
+    p = pm.p.copy(min_diags_between_traceback=200)
+    al = PairHmmAligner(pm.models, p, 0)
+    res = al.posteriors_batch(items, True)
+    for i, it in enumerate(items):
+        want = reference.posteriors(sms[it[3]], p, it[0], it[1], it[2], it[4], it[5], 1)
+        compare_lists(res[i], want, tol_w=1)
+    al.close()
+
+
+def test_errors_are_loud(golden_model):
+    pm = golden_model("r94g360")
+    al = PairHmmAligner(pm.models, pm.p, 0)
+    sx = gen.random_symbols(np.random.default_rng(1), 20)
+    with pytest.raises(AlignerError):  # anchors must increase strictly (asserts at pairwiseAligner.c:150-158)
+        al.posteriors_batch([(sx, sx, [(5, 5, 4), (4, 6, 4)], 0, 0, 0)])
+    with pytest.raises(AlignerError):  # odd expansion
+        al.posteriors_batch([(sx, sx, [(5, 5, 3)], 0, 0, 0)])
+    with pytest.raises(AlignerError):  # traceBackDiagonals + 1 < minDiagsBetweenTraceBack (:718)
+        al.set_params(pm.p.copy(min_diags_between_traceback=30))
+    assert len(al.posteriors_batch([])) == 0
+    al.close()
