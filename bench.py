@@ -1,0 +1,380 @@
+#!/usr/bin/env python
+"""bench.py — pair-HMM GCUPS of the B200 path on BASELINE.json's configs[1], with the reference CPU aligner beside it.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload NAME]
+
+One "step" = one ``poa_realign`` sweep of the aligner over one synthetic chunk (100 kb contig,
+60x, 20 kb ONT-like reads at ~10 % error, r94-g360 RLE model): banded forward + backward + posterior tuples of all
+three lists for every read.  Metric: GCUPS = 1e-9 x credited cell-passes / s, where an alignment with C band
+cells is credited 2*C cell-passes (forward + backward) however many the kernels execute.
+
+* ``value``  inputs already resident in HBM, timed with CUDA events on the library's stream, L2 flushed between steps.
+* ``e2e``    the same sweep through the C-ABI call a host program makes (``margin_b200_posteriors_batch``) with HOST
+             buffers: H2D of symbols/anchors and D2H of the tuple lists inside the timed region.
+* N > 1      one process per GPU (torchrun), every rank sweeps its own chunk (chunks share no state, so there is no
+             data-path collective; weak scaling), time = max over ranks, value = sum of the ranks' cell-passes / time.
+* ``--impl reference``  the UNMODIFIED reference aligner (oracle/_ref, built from /root/reference by oracle/Makefile)
+             on the host cores, OpenMP over reads, on a bounded sample of the same chunk.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "pair-HMM GCUPS (banded forward+backward+posterior, poa_realign sweep)"
+UNIT = "GCUPS"
+DEFAULT_WORKLOAD = "c2_ont_100kb_60x_20kb"
+MODEL_FILE = os.path.join(ROOT, "tests", "golden", "model_r94g360.bin")
+FLOP_PER_CELL_PASS = 108.0
+FLOP_PER_POSTERIOR_CELL = 30.0 + 14.0
+
+
+def env_int(name, default):
+    try:
+        return int(os.environ.get(name, default))
+    except ValueError:
+        return default
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as fh:
+            d = json.load(fh)
+        return dict(hbm_gbs=float(d.get("hbm_gbs", 6650.0)), sm_max_mhz=float(d.get("sm_max_mhz", 1965.0)),
+                    source="measured")
+    return dict(hbm_gbs=6650.0, sm_max_mhz=1965.0, source="fallback")
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons through NVML while the timed region runs."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index = index
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop_evt = threading.Event()
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if self.nv is None:
+            return
+        nv = self.nv
+        names = {
+            getattr(nv, "nvmlClocksThrottleReasonHwSlowdown", 0x8): "hw_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonSwPowerCap", 0x4): "sw_power_cap",
+        }
+        while not self._stop_evt.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, nm in names.items():
+                    if r & bit:
+                        self.reasons.add(nm)
+            except Exception:
+                pass
+            self._stop_evt.wait(0.02)
+
+    def finish(self):
+        self._stop_evt.set()
+        self.join(timeout=2)
+        med = float(np.median(self.samples)) if self.samples else None
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(self.samples)}
+
+
+def build_items(workload, seed, scale=1.0):
+    from margin_b200 import model, synth
+    pm = model.load_flat_model(MODEL_FILE)
+    items = synth.workload(workload, pm, seed=seed, scale=scale)
+    return pm, items
+
+
+def dist_setup(n_gpus):
+    """torch.distributed only as plumbing for the barrier and the max-over-ranks (no data-path collective)."""
+    world = env_int("WORLD_SIZE", 1)
+    rank = env_int("RANK", 0)
+    local = env_int("LOCAL_RANK", 0)
+    dist = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist_mod
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29511")
+        backend = "nccl" if torch.cuda.is_available() else "gloo"
+        if backend == "nccl":
+            torch.cuda.set_device(local)
+        dist_mod.init_process_group(backend=backend, rank=rank, world_size=world)
+        dist = dist_mod
+    return rank, local, world, dist
+
+
+def reduce_scalar(dist, value, op, device):
+    if dist is None:
+        return value
+    import torch
+    t = torch.tensor([float(value)], dtype=torch.float64, device=device)
+    dist.all_reduce(t, op=getattr(dist.ReduceOp, op))
+    return float(t.item())
+
+
+# ----------------------------------------------------------------------------------------------- reference arm
+
+def time_reference(pm, items, steps, warmup, threads, sample_reads=None):
+    """The reference's own CPU aligner (getAlignedPairsWithIndelsUsingAnchors per read, OpenMP over reads like the
+    chunk loop of polish.c:476) from oracle/_ref; falls back to the C restatement (kind 'port') when the reference
+    build did not travel.  Returns dict(value GCUPS, seconds per step, cells per step, kind, sample)."""
+    from margin_b200 import abi
+    from oracle import oracle_py
+    n = len(items)
+    k = min(n, sample_reads or max(32, 16 * threads))
+    sample = items[:k]
+    batch = abi.Batch(sample)
+    orc = oracle_py.Oracle()
+    # band cells of the sample: counted by the restatement's band builder (pure integer, same as the reference's)
+    cells = 0
+    for it in sample:
+        kl, kr = orc.band(it[2], len(it[0]), len(it[1]), pm.p.dynamic_anchor_expansion, pm.p.diagonal_expansion)
+        cells += int(((kr - kl) // 2 + 1).sum())
+    if oracle_py.Reference.available():
+        ref = oracle_py.Reference()
+        sms = [ref.sm_from_model(pm.models[s]) for s in (0, 1)]
+        run = lambda: ref.posteriors_batch(sms, pm.p, batch, 1, threads)
+        kind = "reference"
+    else:
+        run = lambda: orc.posteriors_batch(pm.models, pm.p, batch, 1, threads, keep=False)
+        kind = "port"
+    for _ in range(warmup):
+        run()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        run()
+    dt = (time.perf_counter() - t0) / max(steps, 1)
+    return dict(value=2.0 * cells / dt * 1e-9, sec_per_step=dt, cells=cells, kind=kind, cores=threads,
+                sample="%d of %d reads of the chunk (%d band cells), %d OpenMP threads" % (k, n, cells, threads))
+
+
+def main_reference(args):
+    rank, local, world, dist = dist_setup(args.gpus)
+    if rank != 0:
+        if dist is not None:
+            dist.barrier()
+            dist.destroy_process_group()
+        return 0
+    pm, items = build_items(args.workload, args.seed)
+    threads = host_cores()
+    r = time_reference(pm, items, args.steps, args.warmup, threads)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["sec_per_step"] * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": args.workload, "seed": args.seed, "params": "ont/r9.4 r94-g360 (RLE, repeat counts)",
+                   "l2": "n/a (host)"},
+        "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": r["kind"],
+                         "sample": r["sample"]},
+        "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+# ---------------------------------------------------------------------------------------------------- our arm
+
+def pin_batch(batch):
+    """Page-locks the batch's host arrays (cudaHostRegister) so that the e2e leg copies from pinned memory."""
+    import torch
+    rt = torch.cuda.cudart()
+    for a in (batch.sym_x, batch.sym_y, batch.anchors, batch.off_x, batch.off_y, batch.off_a):
+        if a.nbytes:
+            rt.cudaHostRegister(a.ctypes.data, a.nbytes, 0)
+
+
+def main_ours(args):
+    import torch
+    from margin_b200 import abi
+    from margin_b200.aligner import PairHmmAligner
+
+    rank, local, world, dist = dist_setup(args.gpus)
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    peaks = load_peaks()
+
+    pm, items = build_items(args.workload, args.seed + rank)  # every rank polishes its own chunk
+    batch = abi.Batch(items)
+    pin_batch(batch)
+    al = PairHmmAligner(pm.models, pm.p, device=local)
+    flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+
+    def l2_flush():
+        flush.zero_()
+        torch.cuda.synchronize(dev)
+
+    # ---- kernel-only leg: inputs resident in HBM
+    al.upload(batch)
+    for _ in range(args.warmup):
+        l2_flush()
+        st = al.posteriors_resident(True)
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize(dev)
+    sampler = ClockSampler(local)
+    sampler.start()
+    dev_ms, launches = 0.0, 0
+    ktimes = {}
+    t_wall0 = time.perf_counter()
+    for _ in range(args.steps):
+        l2_flush()
+        st = al.posteriors_resident(True)
+        dev_ms += st["gpu_ms"]
+        launches += st["kernel_launches"]
+        for k, (ms, ln) in al.kernel_times().items():
+            a = ktimes.setdefault(k, [0.0, 0])
+            a[0] += ms
+            a[1] += ln
+    torch.cuda.synchronize(dev)
+    t_wall = time.perf_counter() - t_wall0
+    clocks = sampler.finish()
+    if dist is not None:
+        dist.barrier()
+    cells = st["band_cells"]
+    ms_step = reduce_scalar(dist, dev_ms / args.steps, "MAX", dev)
+    cell_passes = reduce_scalar(dist, 2.0 * cells, "SUM", dev)
+    value = cell_passes / (ms_step * 1e-3) * 1e-9
+
+    # ---- end-to-end leg: host buffers in, host tuple lists out, through the public C-ABI call
+    for _ in range(max(1, min(args.warmup, 2))):
+        res = al.posteriors_host(batch, True)
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize(dev)
+    t0 = time.perf_counter()
+    e2e_steps = max(1, min(args.steps, 5))
+    for _ in range(e2e_steps):
+        l2_flush()
+        res = al.posteriors_host(batch, True)
+    e2e_s = (time.perf_counter() - t0) / e2e_steps
+    # the flush is not part of the path: time it and take it out
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        l2_flush()
+    e2e_s -= (time.perf_counter() - t0) / e2e_steps
+    e2e_s = reduce_scalar(dist, e2e_s, "MAX", dev)
+    e2e_value = cell_passes / e2e_s * 1e-9
+    d2h = int(res["tuples"]) * 12 + 3 * (batch.n + 1) * 8
+
+    # ---- roofline of the dominant kernel (CUDA events around each launch, same timed region)
+    dom = max(ktimes.items(), key=lambda kv: kv[1][0])[0] if ktimes else "none"
+    dom_ms = ktimes[dom][0] / max(ktimes[dom][1], 1) if ktimes else 0.0
+    roof = roofline(dom, dom_ms, ktimes, cells, st, peaks, al)
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": al.arithmetic(), "data": "synthetic",
+        "config": {"workload": args.workload, "seed": args.seed, "reads_per_chunk": batch.n, "chunks_per_gpu": 1,
+                   "band_cells_per_chunk": int(cells), "diagonals": int(st["diagonals"]),
+                   "segments": int(st["segments"]), "params": "ont/r9.4 r94-g360 (RLE, repeat counts)",
+                   "l2": "flushed between steps (512 MiB write)", "wall_ms_per_step_incl_flush": t_wall / args.steps * 1e3},
+        "clocks": clocks,
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": batch.h2d_bytes, "d2h_bytes_per_step": d2h,
+                "ms_per_step": e2e_s * 1e3},
+        "gpu_launches": launches,
+        "kernel_ms_per_step": {k: v[0] / args.steps for k, v in ktimes.items() if v[1]},
+        "roofline": roof,
+    }
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        r = time_reference(pm, items, 1, 1, host_cores())
+        line["cpu_baseline"] = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": r["kind"],
+                                "sample": r["sample"]}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    al.close()
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def roofline(dom, dom_ms, ktimes, cells, st, peaks, al):
+    """Roofline of the dominant kernel.  The path is a log-space recurrence, so the pipe that bounds it is the
+    non-tensor FP pipe of the arithmetic type the kernels compute in; the HBM view of the
+    same launch is reported beside it."""
+    import torch
+    prop = torch.cuda.get_device_properties(torch.cuda.current_device())
+    sms = prop.multi_processor_count
+    dtype = al.arithmetic()
+    lanes = 64 if dtype == "f64" else 128  # FP64 units per SM are half the FP32 lanes on sm_100
+    peak_tflops = sms * lanes * 2 * peaks["sm_max_mhz"] * 1e6 * 1e-12
+    n_launch = max(ktimes[dom][1], 1) if ktimes else 1
+    steps = max(1, n_launch // max(1, al.launches_per_step(dom)))
+    # algorithmic work of one step attributed to the dominant kernel class
+    if dom == "forward":
+        flop = cells * FLOP_PER_CELL_PASS
+        bytes_alg = cells * (0.9 + 2.7 + al.f_bytes_per_cell())
+    elif dom in ("backward", "fused"):
+        flop = cells * ((2.0 if dom == "fused" else 1.0) * FLOP_PER_CELL_PASS + FLOP_PER_POSTERIOR_CELL)
+        bytes_alg = cells * (0.9 + 2.7 + 2.6 + (al.f_bytes_per_cell() if dom == "backward" else 0.0))
+    else:
+        flop = 0.0
+        bytes_alg = cells * 2.6
+    class_ms_step = ktimes[dom][0] / steps if ktimes else 0.0
+    ach_tflops = flop / (class_ms_step * 1e-3) * 1e-12 if class_ms_step > 0 else 0.0
+    ach_gbs = bytes_alg / (class_ms_step * 1e-3) * 1e-9 if class_ms_step > 0 else 0.0
+    return {
+        "kernel": dom, "bound": "fp64-pipe" if dtype == "f64" else "fp32-pipe", "achieved": ach_tflops,
+        "peak": peak_tflops, "unit": "TFLOP/s", "frac": ach_tflops / peak_tflops if peak_tflops else None,
+        "traffic": None, "peak_source": "%d SMs x %d lanes x 2 x %.0f MHz (%s sm_max_mhz)" % (
+            sms, lanes, peaks["sm_max_mhz"], peaks["source"]),
+        "avg_launch_ms": dom_ms, "class_ms_per_step": class_ms_step,
+        "hbm": {"achieved": ach_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                "frac": ach_gbs / peaks["hbm_gbs"], "algorithmic_bytes": bytes_alg, "peak_source": peaks["source"]},
+    }
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD)
+    ap.add_argument("--seed", type=int, default=42)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return main_reference(args)
+    return main_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

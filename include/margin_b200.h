@@ -155,6 +155,12 @@ int margin_b200_forward_batch(margin_b200_ctx *ctx, const margin_b200_batch *bat
 /* Kernel-only step of the above on a batch staged by margin_b200_upload_batch. */
 int margin_b200_forward_resident(margin_b200_ctx *ctx, margin_b200_result *stats);
 
+/* Device time of the last *_resident / *_batch call split by kernel class (CUDA events recorded on the
+ * context's stream around every launch): ms[k] = summed duration, launches[k] = number of launches.
+ * Classes, in order: band, schedule, forward, backward, scan, gather, offsets, final. */
+#define MARGIN_B200_KERNEL_CLASSES 8
+int margin_b200_last_kernel_ms(margin_b200_ctx *ctx, float *ms, int32_t *launches, int n_class);
+
 /* Band geometry only (band_constructDynamic / band_construct): for alignment i
  * and anti-diagonal d in [0, lX+lY], xmy_l / xmy_r at off_d[i] + d, where
  * off_d is the exclusive prefix sum of (lX+lY+1).  Buffers are caller-owned

@@ -170,6 +170,8 @@ def load_library():
     lib.margin_b200_forward_resident.restype = i32
     lib.margin_b200_bands.argtypes = [vp, C.POINTER(BatchStruct), vp, vp]
     lib.margin_b200_bands.restype = i32
+    lib.margin_b200_last_kernel_ms.argtypes = [vp, vp, vp, i32]
+    lib.margin_b200_last_kernel_ms.restype = i32
     _LIB = lib
     return lib
 
@@ -179,4 +181,7 @@ EXPORTED_SYMBOLS = [
     "margin_b200_set_model", "margin_b200_set_params", "margin_b200_posteriors_batch",
     "margin_b200_upload_batch", "margin_b200_posteriors_resident", "margin_b200_download_result",
     "margin_b200_forward_batch", "margin_b200_forward_resident", "margin_b200_bands",
+    "margin_b200_last_kernel_ms",
 ]
+
+KERNEL_CLASSES = ["band", "schedule", "forward", "backward", "scan", "gather", "offsets", "final"]

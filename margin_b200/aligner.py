@@ -101,6 +101,29 @@ class PairHmmAligner:
         self._check(self.lib.margin_b200_posteriors_batch(self._h, C.byref(batch.struct), int(want_indels), C.byref(res)))
         return self._collect(res, batch.n)
 
+    def posteriors_host(self, batch, want_indels=True):
+        """margin_b200_posteriors_batch with host buffers in and the tuple lists left in the context's pinned host
+        memory (no Python-side copies): what a C caller does.  Returns the counters and the number of tuples."""
+        res = abi.ResultStruct()
+        self._check(self.lib.margin_b200_posteriors_batch(self._h, C.byref(batch.struct), int(want_indels), C.byref(res)))
+        out = _stats(res)
+        n = batch.n
+        out["tuples"] = sum(int(C.cast(res.off[l], C.POINTER(C.c_int64))[n]) for l in range(3)) if n else 0
+        return out
+
+    def arithmetic(self):
+        """Arithmetic type of the DP kernels."""
+        return "f64"
+
+    def f_bytes_per_cell(self):
+        """Bytes of forward state per band cell that cross HBM in each direction (3 doubles)."""
+        return 24.0
+
+    def launches_per_step(self, kernel_class):
+        """Launches of a kernel class per call: one per lane-group width (8/16/32) that has jobs."""
+        t = self.kernel_times()
+        return max(1, t.get(kernel_class, (0.0, 1))[1])
+
     def upload(self, batch):
         self._check(self.lib.margin_b200_upload_batch(self._h, C.byref(batch.struct)))
 
@@ -113,6 +136,14 @@ class PairHmmAligner:
         res = abi.ResultStruct()
         self._check(self.lib.margin_b200_download_result(self._h, C.byref(res)))
         return res
+
+    def kernel_times(self):
+        """{class: (ms, launches)} of the last call (CUDA events around every launch)."""
+        n = len(abi.KERNEL_CLASSES)
+        ms = np.zeros(n, np.float32)
+        ln = np.zeros(n, np.int32)
+        self._check(self.lib.margin_b200_last_kernel_ms(self._h, ms.ctypes.data, ln.ctypes.data, n))
+        return {k: (float(ms[i]), int(ln[i])) for i, k in enumerate(abi.KERNEL_CLASSES)}
 
     def forward_batch(self, batch):
         if not isinstance(batch, abi.Batch):

@@ -112,9 +112,35 @@ struct margin_b200_ctx {
     int64_t total_tuples = 0;
     int64_t list_tuples[3] = {0, 0, 0};
     int launches = 0;
+    // per-kernel-class device times of the last call (CUDA events on the stream around each launch)
+    std::vector<cudaEvent_t> ev_pool;
+    std::vector<int> ev_class;  // class of the i-th (start, stop) pair
+    int ev_used = 0;
 };
 
 namespace {
+
+enum { K_BAND = 0, K_SCHEDULE, K_FORWARD, K_BACKWARD, K_SCAN, K_GATHER, K_OFFSETS, K_FINAL, K_NCLASS };
+
+// Records an event pair around one launch; the pairs are resolved by margin_b200_last_kernel_ms.
+struct KTimer {
+    margin_b200_ctx *c;
+    int idx;
+    KTimer(margin_b200_ctx *ctx, int cls) : c(ctx) {
+        if ((size_t) (2 * c->ev_used + 2) > c->ev_pool.size()) {
+            cudaEvent_t a, b;
+            cudaEventCreate(&a);
+            cudaEventCreate(&b);
+            c->ev_pool.push_back(a);
+            c->ev_pool.push_back(b);
+            c->ev_class.push_back(cls);
+        }
+        idx = c->ev_used++;
+        c->ev_class[idx] = cls;
+        cudaEventRecord(c->ev_pool[2 * idx], c->stream);
+    }
+    ~KTimer() { cudaEventRecord(c->ev_pool[2 * idx + 1], c->stream); }
+};
 
 int check_device(int device) {
     int count = 0;
@@ -161,6 +187,7 @@ void margin_b200_destroy(margin_b200_ctx *c) {
     c->h_small.release();
     c->h_out.release();
     c->h_off.release();
+    for (cudaEvent_t e : c->ev_pool) cudaEventDestroy(e);
     cudaEventDestroy(c->ev0);
     cudaEventDestroy(c->ev1);
     cudaStreamDestroy(c->stream);
@@ -416,17 +443,17 @@ int run_band(margin_b200_ctx *c, bool dynamic, bool with_schedule, bool want_kr)
     c->job_maxw.assign(nj, 0);
     std::vector<int32_t> nseg(nj, 0);
     if (nj > 0) {
-        mb::band_kernel<256><<<nj, 256, 0, c->stream>>>(c->d_jobs.as<mb::Job>(), nj, c->d_anchors.as<int32_t>(), q,
+        { KTimer kt_(c, K_BAND); mb::band_kernel<256><<<nj, 256, 0, c->stream>>>(c->d_jobs.as<mb::Job>(), nj, c->d_anchors.as<int32_t>(), q,
                                                         c->d_kl.as<int32_t>(), c->d_cell_off.as<uint32_t>(),
                                                         c->d_job_cells.as<int64_t>(), c->d_job_maxw.as<int32_t>(),
-                                                        want_kr ? c->d_kr.as<int32_t>() : nullptr, c->d_err.as<int>());
+                                                        want_kr ? c->d_kr.as<int32_t>() : nullptr, c->d_err.as<int>()); }
         c->launches++;
         if (with_schedule) {
             CU(cudaMemsetAsync(c->d_segs.p, 0xff, ((size_t) c->total_slots + 1) * sizeof(mb::Seg), c->stream));
             const int threads = 128, per_block = threads / 32;
-            mb::schedule_kernel<<<(nj + per_block - 1) / per_block, threads, 0, c->stream>>>(
+            { KTimer kt_(c, K_SCHEDULE); mb::schedule_kernel<<<(nj + per_block - 1) / per_block, threads, 0, c->stream>>>(
                 c->d_jobs.as<mb::Job>(), nj, c->d_cell_off.as<uint32_t>(), q, c->d_segs.as<mb::Seg>(),
-                c->d_job_nseg.as<int32_t>());
+                c->d_job_nseg.as<int32_t>()); }
             c->launches++;
             CU(cudaMemcpyAsync(nseg.data(), c->d_job_nseg.p, nj * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
         }
@@ -521,10 +548,10 @@ template <int G>
 void launch_forward(margin_b200_ctx *c, int off, int count) {
     if (count <= 0) return;
     const int per_block = kFwdThreads / G;
-    mb::forward_kernel<G, kFwdThreads><<<(count + per_block - 1) / per_block, kFwdThreads, 0, c->stream>>>(
+    { KTimer kt_(c, K_FORWARD); mb::forward_kernel<G, kFwdThreads><<<(count + per_block - 1) / per_block, kFwdThreads, 0, c->stream>>>(
         c->d_jobs.as<mb::Job>(), c->d_ids.as<int32_t>() + off, count, c->d_models.as<mb::DevModel>(),
         c->d_symx.as<uint16_t>(), c->d_symy.as<uint16_t>(), c->d_kl.as<int32_t>(), c->d_cell_off.as<uint32_t>(),
-        c->d_F.as<double>());
+        c->d_F.as<double>()); }
     c->launches++;
 }
 
@@ -532,12 +559,12 @@ template <int G, bool INDELS>
 void launch_backward(margin_b200_ctx *c, int off, int count, int64_t stage_stride) {
     if (count <= 0) return;
     const int per_block = kBwdThreads / G;
-    mb::backward_kernel<G, kBwdThreads, INDELS><<<(count + per_block - 1) / per_block, kBwdThreads, 0, c->stream>>>(
+    { KTimer kt_(c, K_BACKWARD); mb::backward_kernel<G, kBwdThreads, INDELS><<<(count + per_block - 1) / per_block, kBwdThreads, 0, c->stream>>>(
         c->d_jobs.as<mb::Job>(), c->d_segs.as<mb::Seg>(), c->d_ids.as<int32_t>() + off, count,
         c->d_models.as<mb::DevModel>(), c->d_symx.as<uint16_t>(), c->d_symy.as<uint16_t>(), c->d_kl.as<int32_t>(),
         c->d_cell_off.as<uint32_t>(), c->d_F.as<double>(), dev_params(c->params), c->d_ring.as<double>(),
         c->d_slot_ring_off.as<int64_t>(), c->d_stage.as<mb::Pair>(), stage_stride, c->d_seg_counts.as<int64_t>(),
-        c->total_slots);
+        c->total_slots); }
     c->launches++;
 }
 
@@ -566,6 +593,7 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
     CU(cudaSetDevice(c->device));
     memset(out, 0, sizeof(*out));
     c->launches = 0;
+    c->ev_used = 0;
     c->total_tuples = 0;
     c->list_tuples[0] = c->list_tuples[1] = c->list_tuples[2] = 0;
     const int nj = (int) c->jobs.size();
@@ -602,8 +630,8 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
     CU(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, c->d_seg_counts.as<int64_t>(), c->d_seg_off.as<int64_t>(), n_scan,
                                      c->stream));
     if (c->d_scan_tmp.ensure(tmp_bytes + 16)) return 1;
-    CU(cub::DeviceScan::ExclusiveSum(c->d_scan_tmp.p, tmp_bytes, c->d_seg_counts.as<int64_t>(), c->d_seg_off.as<int64_t>(),
-                                     n_scan, c->stream));
+    { KTimer kt_(c, K_SCAN); CU(cub::DeviceScan::ExclusiveSum(c->d_scan_tmp.p, tmp_bytes, c->d_seg_counts.as<int64_t>(), c->d_seg_off.as<int64_t>(),
+                                     n_scan, c->stream)); }
     c->launches++;
     int64_t bounds[4] = {0, 0, 0, 0};
     for (int l = 0; l < 4; l++)
@@ -615,17 +643,17 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
     for (int l = 0; l < 3; l++) c->list_tuples[l] = bounds[l + 1] - bounds[l];
     if (c->d_out.ensure((size_t) (c->total_tuples + 1) * sizeof(mb::Pair))) return 1;
     if (S > 0 && nj > 0) {
-        mb::gather_kernel<<<S, 128, 0, c->stream>>>(c->d_jobs.as<mb::Job>(), c->d_segs.as<mb::Seg>(), S,
+        { KTimer kt_(c, K_GATHER); mb::gather_kernel<<<S, 128, 0, c->stream>>>(c->d_jobs.as<mb::Job>(), c->d_segs.as<mb::Seg>(), S,
                                                     c->d_cell_off.as<uint32_t>(), c->d_seg_counts.as<int64_t>(),
                                                     c->d_seg_off.as<int64_t>(), c->d_stage.as<mb::Pair>(), stride,
-                                                    c->d_out.as<mb::Pair>(), n_lists);
+                                                    c->d_out.as<mb::Pair>(), n_lists); }
         c->launches++;
     }
     {
         const int threads = 128;
         const int blocks = (int) ((c->n_aln + 1 + threads - 1) / threads);
-        mb::list_offsets_kernel<<<blocks, threads, 0, c->stream>>>(c->d_aln_first_slot.as<int32_t>(), (int) c->n_aln, S,
-                                                                   c->d_seg_off.as<int64_t>(), c->d_off_out.as<int64_t>());
+        { KTimer kt_(c, K_OFFSETS); mb::list_offsets_kernel<<<blocks, threads, 0, c->stream>>>(c->d_aln_first_slot.as<int32_t>(), (int) c->n_aln, S,
+                                                                   c->d_seg_off.as<int64_t>(), c->d_off_out.as<int64_t>()); }
         c->launches++;
     }
     CU(cudaEventRecord(c->ev1, c->stream));
@@ -671,6 +699,26 @@ extern "C" int margin_b200_posteriors_batch(margin_b200_ctx *c, const margin_b20
 
 static_assert(sizeof(mb::Pair) == sizeof(margin_b200_pair), "tuple layouts must agree");
 
+extern "C" int margin_b200_last_kernel_ms(margin_b200_ctx *c, float *ms, int32_t *launches, int n_class) {
+    if (!c || !ms || !launches) return fail("margin_b200_last_kernel_ms: null argument");
+    CU(cudaSetDevice(c->device));
+    CU(cudaStreamSynchronize(c->stream));
+    for (int k = 0; k < n_class; k++) {
+        ms[k] = 0.f;
+        launches[k] = 0;
+    }
+    for (int i = 0; i < c->ev_used; i++) {
+        float t = 0.f;
+        CU(cudaEventElapsedTime(&t, c->ev_pool[2 * i], c->ev_pool[2 * i + 1]));
+        const int k = c->ev_class[i];
+        if (k < n_class) {
+            ms[k] += t;
+            launches[k]++;
+        }
+    }
+    return 0;
+}
+
 // computeForwardProbability for every alignment of the uploaded batch (impl/pairwiseAligner.c:849-903): static band
 // with diagonalExpansion (callers pass no anchors => the full matrix), forward sweep, end-state dot product.
 // Large-gap splitting does not apply to this entry point, so upload must have produced one job per alignment.
@@ -679,6 +727,7 @@ extern "C" int margin_b200_forward_resident(margin_b200_ctx *c, margin_b200_resu
     if (check_device(c->device)) return 1;
     CU(cudaSetDevice(c->device));
     c->launches = 0;
+    c->ev_used = 0;
     const int nj = (int) c->jobs.size();
     if ((int64_t) nj != c->n_aln)
         return fail("margin_b200_forward: an alignment was split by splitMatrixBiggerThanThis; the forward-only "
@@ -694,10 +743,10 @@ extern "C" int margin_b200_forward_resident(margin_b200_ctx *c, margin_b200_resu
     launch_forward<16>(c, bins.fwd_off[1], bins.fwd_off[2] - bins.fwd_off[1]);
     launch_forward<32>(c, bins.fwd_off[2], bins.fwd_off[3] - bins.fwd_off[2]);
     if (nj > 0) {
-        mb::final_dot_kernel<<<(nj + 127) / 128, 128, 0, c->stream>>>(c->d_jobs.as<mb::Job>(), nj,
+        { KTimer kt_(c, K_FINAL); mb::final_dot_kernel<<<(nj + 127) / 128, 128, 0, c->stream>>>(c->d_jobs.as<mb::Job>(), nj,
                                                                       c->d_models.as<mb::DevModel>(),
                                                                       c->d_cell_off.as<uint32_t>(), c->d_F.as<double>(),
-                                                                      c->d_fwd_out.as<double>());
+                                                                      c->d_fwd_out.as<double>()); }
         c->launches++;
     }
     CU(cudaEventRecord(c->ev1, c->stream));
@@ -737,6 +786,7 @@ extern "C" int margin_b200_bands(margin_b200_ctx *c, const margin_b200_batch *b,
     c->params.split_matrix_bigger_than_this = saved;
     if (rc) return 1;
     c->launches = 0;
+    c->ev_used = 0;
     if (run_band(c, c->params.dynamic_anchor_expansion != 0, false, true)) return 1;
     // device layout has N+2 entries per job; the caller's has N+1
     std::vector<int32_t> kl(c->total_diag + 1), kr(c->total_diag + 1);
