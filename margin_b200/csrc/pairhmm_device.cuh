@@ -25,6 +25,10 @@ struct DevModel {
     int32_t rle;
     int32_t max_rl;
     const double *rsm_scaled;  // 2.3025 * rsm[b][under][obs], device pointer (4*51*51)
+    // Folded match emission for the tile kernels: emit5[((xb*5+yb)*51 + rlX)*51 + rlY] with xb, yb in 0..4
+    // (4 = ambiguous) = match[xb][yb] + 2.3025*rsm[...] rounded once, exactly the sum the reference forms per cell
+    // (impl/stateMachine.c:733-738).  Non-RLE models fill only the [rl=0][rl=0] entries.
+    const double *emit5;
 };
 
 enum { T_MM = 0, T_XM = 1, T_YM = 2, T_MX = 3, T_XX = 4, T_YX = 5, T_MY = 6, T_YY = 7, T_XY = 8 };
@@ -60,6 +64,32 @@ __device__ __forceinline__ double logadd(double x, double y) {
     const double d = dadd(hi, -lo);
     if (d >= 7.5) return hi;
     return dadd(la_lookup(d), lo);
+}
+
+// The four cubic pieces of lookup() as a [piece][c3,c2,c1,c0] table (copied to shared memory by the tile kernels).
+__device__ const double LA_COEF[16] = {
+    (double) -0.009350833524763f, (double) 0.130659527668286f, (double) 0.498799810682272f, (double) 0.693203116424741f,
+    (double) -0.014532321752540f, (double) 0.139942324101744f, (double) 0.495635523139337f, (double) 0.692140569840976f,
+    (double) -0.004605031767994f, (double) 0.063427417320019f, (double) 0.695956496475118f, (double) 0.514272634594009f,
+    (double) -0.000458661602210f, (double) 0.009695946122598f, (double) 0.930734667215156f, (double) 0.168037164329057f};
+
+// Branch-free logAdd for the tile kernels; operation-for-operation the same arithmetic as logadd() above.
+//   lo == -inf            -> hi - lo = +inf (or NaN when both are -inf) -> "d < 7.5" is false -> hi
+//   d >= 7.5              -> hi
+//   otherwise             -> lookup(d) + lo with the piece chosen by d <= 1, <= 2.5, <= 4.5
+__device__ __forceinline__ double logadd_tab(double x, double y, const double *lac) {
+    const bool lt = x < y;
+    const double hi = lt ? y : x;
+    const double lo = lt ? x : y;
+    const double d = dadd(hi, -lo);
+    const int idx = (int) (d > 1.0) + (int) (d > 2.5) + (int) (d > 4.5);
+    const double2 c32 = *reinterpret_cast<const double2 *>(lac + 4 * idx);
+    const double2 c10 = *reinterpret_cast<const double2 *>(lac + 4 * idx + 2);
+    double v = dadd(dmul(c32.x, d), c32.y);
+    v = dadd(dmul(v, d), c10.x);
+    v = dadd(dmul(v, d), c10.y);
+    v = dadd(v, lo);
+    return (d < 7.5) ? v : hi;
 }
 
 // Symbol decoding (impl/stateMachine.c:116-122): base = low 8 bits, run length = high 8 bits.
