@@ -118,6 +118,7 @@ typedef struct margin_b200_result {
     int64_t segments;        /* traceback segments */
     float gpu_ms;            /* device time of this call (CUDA events) */
     int32_t kernel_launches; /* kernels launched by this call */
+    int64_t tiles;           /* independent forward/backward work units the segments were cut into */
 } margin_b200_result;
 
 typedef struct margin_b200_ctx margin_b200_ctx;

@@ -88,6 +88,7 @@ class ResultStruct(C.Structure):
         ("segments", C.c_int64),
         ("gpu_ms", C.c_float),
         ("kernel_launches", C.c_int32),
+        ("tiles", C.c_int64),
     ]
 
 

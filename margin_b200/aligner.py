@@ -37,7 +37,7 @@ class BatchResult:
 
 def _stats(res):
     return dict(band_cells=res.band_cells, diagonals=res.diagonals, jobs=res.jobs, segments=res.segments,
-                gpu_ms=res.gpu_ms, kernel_launches=res.kernel_launches)
+                gpu_ms=res.gpu_ms, kernel_launches=res.kernel_launches, tiles=res.tiles)
 
 
 class PairHmmAligner:

@@ -14,7 +14,7 @@
 #include <cub/device/device_scan.cuh>
 
 #include "../../include/margin_b200.h"
-#include "pairhmm_kernels.cuh"
+#include "pairhmm_tiles.cuh"
 
 namespace {
 
@@ -100,7 +100,15 @@ struct margin_b200_ctx {
     std::vector<int32_t> aln_first_slot;
     std::vector<int32_t> aln_first_job;
     int64_t total_diag = 0;  // entries in kl / cell_off
-    int total_slots = 0;
+    int seg_slots = 0;       // capacity of the segment table (upper bound from the sequence lengths)
+    int total_slots = 0;     // tiles of the current batch
+    // tiling (pairhmm_tiles.cuh): tile length in diagonals (multiple of 10), warm-up diagonals on either side
+    bool mode_sequential = false;
+    int tile_len = 1000, warmup = 128, force_group = 0;  // tile_len % 10 == 0: tiles start on total-probability samples
+    std::vector<mb::Seg> segs;
+    std::vector<mb::Tile> tiles;
+    std::vector<int32_t> job_nseg, job_first_tile;
+    DevBuf d_geo, d_tiles, d_bnd, d_slot_bnd_off, d_emit5[2];
     DevBuf d_symx, d_symy, d_anchors, d_jobs, d_kl, d_kr, d_cell_off, d_job_cells, d_job_maxw, d_job_nseg, d_err;
     DevBuf d_segs, d_seg_counts, d_seg_off, d_scan_tmp, d_slot_ring_off, d_ring, d_ids, d_aln_first_slot;
     DevBuf d_F, d_stage, d_out, d_off_out, d_fwd_out;
@@ -170,6 +178,9 @@ int margin_b200_create(margin_b200_ctx **out, int device) {
     CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     CU(cudaEventCreate(&c->ev0));
     CU(cudaEventCreate(&c->ev1));
+    if (const char *e = getenv("MARGIN_B200_MODE")) c->mode_sequential = strcmp(e, "sequential") == 0;
+    if (const char *e = getenv("MARGIN_B200_TILE_LEN")) c->tile_len = std::max(10, atoi(e) / 10 * 10);
+    if (const char *e = getenv("MARGIN_B200_WARMUP")) c->warmup = std::max(1, atoi(e));
     *out = c;
     return 0;
 }
@@ -181,7 +192,8 @@ void margin_b200_destroy(margin_b200_ctx *c) {
     DevBuf *bufs[] = {&c->d_models, &c->d_rsm[0], &c->d_rsm[1], &c->d_symx, &c->d_symy, &c->d_anchors, &c->d_jobs,
                       &c->d_kl, &c->d_kr, &c->d_cell_off, &c->d_job_cells, &c->d_job_maxw, &c->d_job_nseg, &c->d_err,
                       &c->d_segs, &c->d_seg_counts, &c->d_seg_off, &c->d_scan_tmp, &c->d_slot_ring_off, &c->d_ring,
-                      &c->d_ids, &c->d_aln_first_slot, &c->d_F, &c->d_stage, &c->d_out, &c->d_off_out, &c->d_fwd_out};
+                      &c->d_ids, &c->d_aln_first_slot, &c->d_F, &c->d_stage, &c->d_out, &c->d_off_out, &c->d_fwd_out,
+                      &c->d_geo, &c->d_tiles, &c->d_bnd, &c->d_slot_bnd_off, &c->d_emit5[0], &c->d_emit5[1]};
     for (DevBuf *b : bufs) b->release();
     c->h_stage_in.release();
     c->h_small.release();
@@ -231,6 +243,29 @@ int margin_b200_set_model(margin_b200_ctx *c, int slot, const margin_b200_model 
     if (c->d_rsm[slot].ensure(nr * sizeof(double))) return 1;
     CU(cudaMemcpyAsync(c->d_rsm[slot].p, scaled.data(), nr * sizeof(double), cudaMemcpyHostToDevice, c->stream));
     d.rsm_scaled = c->d_rsm[slot].as<double>();
+    // folded match emission of the tile kernels: sub + 2.3025*rsm, one rounding, as impl/stateMachine.c:733-738 forms it
+    {
+        const int R = MARGIN_B200_MAX_RL;
+        std::vector<double> e5((size_t) 25 * R * R, 0.0);
+        for (int xb = 0; xb < 5; xb++)
+            for (int yb = 0; yb < 5; yb++) {
+                const double sub = (xb >= 4 || yb >= 4) ? -2.772588722 : m->match[xb * 4 + yb];
+                const int tb = xb >= 4 ? 0 : xb;
+                double *row = e5.data() + (size_t) (xb * 5 + yb) * R * R;
+                if (!m->rle) {
+                    row[0] = sub;
+                    continue;
+                }
+                for (int i = 0; i < R * R; i++) {
+                    const double r = scaled[(size_t) tb * R * R + i];
+                    row[i] = sub + r;
+                }
+            }
+        if (c->d_emit5[slot].ensure(e5.size() * sizeof(double))) return 1;
+        CU(cudaMemcpyAsync(c->d_emit5[slot].p, e5.data(), e5.size() * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+        CU(cudaStreamSynchronize(c->stream));
+        d.emit5 = c->d_emit5[slot].as<double>();
+    }
     if (c->d_models.ensure(2 * sizeof(mb::DevModel))) return 1;
     CU(cudaMemcpyAsync(c->d_models.p, c->host_models, 2 * sizeof(mb::DevModel), cudaMemcpyHostToDevice, c->stream));
     CU(cudaStreamSynchronize(c->stream));
@@ -380,10 +415,19 @@ extern "C" int margin_b200_upload_batch(margin_b200_ctx *c, const margin_b200_ba
     c->aln_first_slot[n] = (int32_t) slot_base;
     c->aln_first_job[n] = (int32_t) c->jobs.size();
     c->total_diag = diag_off;
-    c->total_slots = (int) slot_base;
+    c->seg_slots = (int) slot_base;
+    c->total_slots = 0;
     c->total_cells = 0;
 
     const int64_t nx = n ? b->off_x[n] : 0, ny = n ? b->off_y[n] : 0;
+    if (c->host_models[0].rle || c->host_models[1].rle) {
+        // run lengths index the 51 x 51 repeat-count table (symbol_addRepeatCount clips them, impl/stateMachine.c:124-131)
+        unsigned worst = 0;
+        for (int64_t i = 0; i < nx; i++) worst = std::max(worst, (unsigned) (b->sym_x[i] >> 8));
+        for (int64_t i = 0; i < ny; i++) worst = std::max(worst, (unsigned) (b->sym_y[i] >> 8));
+        if (worst >= (unsigned) MARGIN_B200_MAX_RL)
+            return fail("a symbol carries run length %u; the repeat-count model holds 0..%d", worst, MARGIN_B200_MAX_RL - 1);
+    }
     const size_t anchor_ints = (size_t) 3 * total_anchor_triples + extra_anchors.size();
     if (c->d_symx.ensure((nx + 1) * sizeof(uint16_t)) || c->d_symy.ensure((ny + 1) * sizeof(uint16_t)) ||
         c->d_anchors.ensure((anchor_ints + 3) * sizeof(int32_t)) ||
@@ -400,8 +444,6 @@ extern "C" int margin_b200_upload_batch(margin_b200_ctx *c, const margin_b200_ba
                            extra_anchors.size() * sizeof(int32_t), cudaMemcpyHostToDevice, c->stream));
     if (!c->jobs.empty())
         CU(cudaMemcpyAsync(c->d_jobs.p, c->jobs.data(), c->jobs.size() * sizeof(mb::Job), cudaMemcpyHostToDevice, c->stream));
-    CU(cudaMemcpyAsync(c->d_aln_first_slot.p, c->aln_first_slot.data(), (n + 1) * sizeof(int32_t), cudaMemcpyHostToDevice,
-                       c->stream));
     CU(cudaStreamSynchronize(c->stream));  // extra_anchors / jobs are pageable host memory about to go out of scope
     return 0;
 }
@@ -423,39 +465,50 @@ mb::Params dev_params(const margin_b200_params &p) {
 
 constexpr int kFwdThreads = 128;
 constexpr int kBwdThreads = 128;
+constexpr int kTileThreads = 128;
 
 inline int group_of(int maxw) { return maxw <= 8 ? 8 : (maxw <= 16 ? 16 : 32); }
 
-// band_kernel (+ schedule_kernel) and the one host round trip of the pipeline: per-job cell counts, widths and
-// segment counts come back so that F / staging can be sized and jobs binned by band width.
+// band_kernel (+ schedule_kernel) and the one host round trip of the pipeline: per-job cell counts, widths, segment
+// counts and the segments themselves come back so that F / staging can be sized and the work cut into tiles.
 int run_band(margin_b200_ctx *c, bool dynamic, bool with_schedule, bool want_kr) {
     const int nj = (int) c->jobs.size();
     mb::Params q = dev_params(c->params);
     q.dynamic = dynamic ? 1 : 0;
     if (c->d_kl.ensure((c->total_diag + 1) * sizeof(int32_t)) || c->d_cell_off.ensure((c->total_diag + 1) * sizeof(uint32_t)) ||
+        c->d_geo.ensure((c->total_diag + 1) * sizeof(int2)) ||
         c->d_job_cells.ensure((nj + 1) * sizeof(int64_t)) || c->d_job_maxw.ensure((nj + 1) * sizeof(int32_t)) ||
         c->d_job_nseg.ensure((nj + 1) * sizeof(int32_t)) || c->d_err.ensure(sizeof(int)) ||
-        c->d_segs.ensure(((size_t) c->total_slots + 1) * sizeof(mb::Seg)))
+        c->d_segs.ensure(((size_t) c->seg_slots + 1) * sizeof(mb::Seg)))
         return 1;
     if (want_kr && c->d_kr.ensure((c->total_diag + 1) * sizeof(int32_t))) return 1;
     CU(cudaMemsetAsync(c->d_err.p, 0, sizeof(int), c->stream));
     c->job_cells.assign(nj, 0);
     c->job_maxw.assign(nj, 0);
-    std::vector<int32_t> nseg(nj, 0);
+    c->job_nseg.assign(nj, 0);
+    c->segs.assign((size_t) c->seg_slots, mb::Seg{-1, 0, 0, 0, 0});
     if (nj > 0) {
-        { KTimer kt_(c, K_BAND); mb::band_kernel<256><<<nj, 256, 0, c->stream>>>(c->d_jobs.as<mb::Job>(), nj, c->d_anchors.as<int32_t>(), q,
-                                                        c->d_kl.as<int32_t>(), c->d_cell_off.as<uint32_t>(),
-                                                        c->d_job_cells.as<int64_t>(), c->d_job_maxw.as<int32_t>(),
-                                                        want_kr ? c->d_kr.as<int32_t>() : nullptr, c->d_err.as<int>()); }
+        {
+            KTimer kt_(c, K_BAND);
+            mb::band_kernel<256><<<nj, 256, 0, c->stream>>>(c->d_jobs.as<mb::Job>(), nj, c->d_anchors.as<int32_t>(), q,
+                                                            c->d_kl.as<int32_t>(), c->d_cell_off.as<uint32_t>(),
+                                                            c->d_job_cells.as<int64_t>(), c->d_job_maxw.as<int32_t>(),
+                                                            want_kr ? c->d_kr.as<int32_t>() : nullptr,
+                                                            c->d_geo.as<int2>(), c->d_err.as<int>());
+        }
         c->launches++;
         if (with_schedule) {
-            CU(cudaMemsetAsync(c->d_segs.p, 0xff, ((size_t) c->total_slots + 1) * sizeof(mb::Seg), c->stream));
             const int threads = 128, per_block = threads / 32;
-            { KTimer kt_(c, K_SCHEDULE); mb::schedule_kernel<<<(nj + per_block - 1) / per_block, threads, 0, c->stream>>>(
-                c->d_jobs.as<mb::Job>(), nj, c->d_cell_off.as<uint32_t>(), q, c->d_segs.as<mb::Seg>(),
-                c->d_job_nseg.as<int32_t>()); }
+            {
+                KTimer kt_(c, K_SCHEDULE);
+                mb::schedule_kernel<<<(nj + per_block - 1) / per_block, threads, 0, c->stream>>>(
+                    c->d_jobs.as<mb::Job>(), nj, c->d_cell_off.as<uint32_t>(), q, c->d_segs.as<mb::Seg>(),
+                    c->d_job_nseg.as<int32_t>());
+            }
             c->launches++;
-            CU(cudaMemcpyAsync(nseg.data(), c->d_job_nseg.p, nj * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+            CU(cudaMemcpyAsync(c->job_nseg.data(), c->d_job_nseg.p, nj * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+            CU(cudaMemcpyAsync(c->segs.data(), c->d_segs.p, (size_t) c->seg_slots * sizeof(mb::Seg), cudaMemcpyDeviceToHost,
+                               c->stream));
         }
         CU(cudaMemcpyAsync(c->job_cells.data(), c->d_job_cells.p, nj * sizeof(int64_t), cudaMemcpyDeviceToHost, c->stream));
         CU(cudaMemcpyAsync(c->job_maxw.data(), c->d_job_maxw.p, nj * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
@@ -472,75 +525,154 @@ int run_band(margin_b200_ctx *c, bool dynamic, bool with_schedule, bool want_kr)
         c->jobs[j].cell_base = cells;
         c->jobs[j].ring_w = c->job_maxw[j];
         cells += c->job_cells[j];
-        if (with_schedule) {
-            if (nseg[j] > c->jobs[j].max_seg) return fail("internal error: segment bound exceeded");
-        }
+        if (with_schedule && c->job_nseg[j] > c->jobs[j].max_seg) return fail("internal error: segment bound exceeded");
     }
     c->total_cells = cells;
-    // stash nseg in the pad-free way: reuse a vector on the ctx via job_maxw's sibling
-    c->h_small.ensure((nj + 1) * sizeof(int32_t));
-    memcpy(c->h_small.p, nseg.data(), nj * sizeof(int32_t));
     return 0;
 }
 
-// Builds the per-group-width id lists (jobs for the forward sweep, used slots for the backward sweep), sorted by
-// length so that the groups sharing a warp finish together.  Layout of d_ids: [fwd8 | fwd16 | fwd32 | bwd8 | bwd16 | bwd32].
+// A job runs on the tiled kernels when its widest diagonal fits a lane group and both sequences are non-empty;
+// anything else (very wide bands, e.g. alignments without anchors; degenerate one-row matrices) takes the
+// sequential per-alignment sweep.
+bool job_is_tiled(const margin_b200_ctx *c, int j) {
+    if (c->mode_sequential) return false;
+    const mb::Job &job = c->jobs[j];
+    return c->job_maxw[j] <= (c->force_group ? c->force_group : 32) && job.lx >= 1 && job.ly >= 1;
+}
+
+// Cuts every traceback segment into tiles (see pairhmm_tiles.cuh) and lays the tiles out in the order of the
+// reference's final lists: alignments in batch order, blocks of an alignment in order, later tracebacks first, and
+// inside a traceback the lowest diagonals first (each tile's tuples are reversed by the gather).
+void build_tiles(margin_b200_ctx *c) {
+    const int nj = (int) c->jobs.size();
+    const int L = c->tile_len, W = c->warmup;
+    c->tiles.clear();
+    c->job_first_tile.assign(nj + 1, 0);
+    int64_t a = 0;
+    for (int64_t i = 0; i < c->n_aln; i++) {
+        c->aln_first_slot[i] = (int32_t) c->tiles.size();
+        for (int j = c->aln_first_job[i]; j < c->aln_first_job[i + 1]; j++) {
+            const mb::Job &job = c->jobs[j];
+            const bool tiled = job_is_tiled(c, j);
+            c->job_first_tile[j] = (int32_t) c->tiles.size();
+            for (int s = c->job_nseg[j] - 1; s >= 0; s--) {
+                const mb::Seg &sg = c->segs[job.seg_base + s];
+                const int span = sg.tb_from - sg.tb_to;
+                int nt = 1;
+                if (tiled && span > L) {
+                    nt = span / L;
+                    if (span - nt * L >= L / 4) nt++;  // a short remainder is merged into the lowest tile
+                }
+                for (int k = nt - 1; k >= 0; k--) {  // lowest diagonals first
+                    mb::Tile t;
+                    t.job = j;
+                    t.tb_from = sg.tb_from - k * L;
+                    t.tb_to = (k == nt - 1) ? sg.tb_to : t.tb_from - L;
+                    t.D = (k == 0) ? sg.D : std::min(sg.D, t.tb_from + W);
+                    t.f0 = tiled ? std::max(0, t.tb_to - W) : 0;
+                    t.flags = ((t.D == sg.D && sg.at_end) ? mb::TILE_AT_END : 0) | (tiled ? mb::TILE_BND : 0);
+                    c->tiles.push_back(t);
+                }
+            }
+        }
+        a++;
+    }
+    (void) a;
+    c->aln_first_slot[c->n_aln] = (int32_t) c->tiles.size();
+    c->job_first_tile[nj] = (int32_t) c->tiles.size();
+    c->total_slots = (int) c->tiles.size();
+}
+
+// Id lists for the launches, each sorted by work (longest first) so that the groups sharing a warp finish together.
+// Layout of d_ids: [seq fwd 8|16|32][tile fwd 8|16|32][generic bwd 8|16|32][tile bwd 8|16|32].
 struct Bins {
-    int fwd_off[4];
-    int bwd_off[4];
+    int seq_fwd[4];
+    int tile_fwd[4];
+    int gen_bwd[4];
+    int tile_bwd[4];
 };
 
 int build_bins(margin_b200_ctx *c, bool with_slots, Bins &bins, int force_group) {
     const int nj = (int) c->jobs.size();
-    const int32_t *nseg = c->h_small.as<int32_t>();
-    std::vector<int32_t> order(nj);
-    for (int j = 0; j < nj; j++) order[j] = j;
+    const int gs[3] = {8, 16, 32};
+    auto grp = [&](int j) { return force_group ? force_group : group_of(c->job_maxw[j]); };
+    std::vector<int32_t> ids;
+    // sequential forward sweeps (whole jobs)
+    std::vector<int32_t> order;
+    for (int j = 0; j < nj; j++)
+        if (!with_slots || !job_is_tiled(c, j)) order.push_back(j);
     std::sort(order.begin(), order.end(), [&](int a, int b) {
         const int na = c->jobs[a].lx + c->jobs[a].ly, nb = c->jobs[b].lx + c->jobs[b].ly;
         return na != nb ? na > nb : a < b;
     });
-    std::vector<int32_t> ids;
-    const int gs[3] = {8, 16, 32};
     for (int k = 0; k < 3; k++) {
-        bins.fwd_off[k] = (int) ids.size();
-        for (int j : order) {
-            const int g = force_group ? force_group : group_of(c->job_maxw[j]);
-            if (g == gs[k]) ids.push_back(j);
-        }
+        bins.seq_fwd[k] = (int) ids.size();
+        for (int j : order)
+            if (grp(j) == gs[k]) ids.push_back(j);
     }
-    bins.fwd_off[3] = (int) ids.size();
-    std::vector<int64_t> slot_ring_off;
-    int64_t ring_cells = 0;
+    bins.seq_fwd[3] = (int) ids.size();
+    std::vector<int64_t> ring_off, bnd_off;
+    int64_t ring_cells = 0, bnd_cells = 0;
     if (with_slots) {
-        slot_ring_off.assign((size_t) c->total_slots + 1, 0);
+        const int S = c->total_slots;
+        ring_off.assign((size_t) S + 1, 0);
+        bnd_off.assign((size_t) S + 1, 0);
+        std::vector<int32_t> tl, gn;
+        for (int s = 0; s < S; s++) (job_is_tiled(c, c->tiles[s].job) ? tl : gn).push_back(s);
+        auto by = [&](std::vector<int32_t> &v, bool fwd) {
+            std::sort(v.begin(), v.end(), [&](int a, int b) {
+                const mb::Tile &ta = c->tiles[a], &tb = c->tiles[b];
+                const int wa = fwd ? ta.tb_from - ta.f0 : ta.D - ta.tb_to, wb = fwd ? tb.tb_from - tb.f0 : tb.D - tb.tb_to;
+                return wa != wb ? wa > wb : a < b;
+            });
+        };
+        by(tl, true);
         for (int k = 0; k < 3; k++) {
-            bins.bwd_off[k] = (int) ids.size();
-            for (int j : order) {
-                const int g = force_group ? force_group : group_of(c->job_maxw[j]);
-                if (g != gs[k]) continue;
-                const mb::Job &job = c->jobs[j];
-                for (int s = 0; s < nseg[j]; s++) {
-                    const int slot = job.seg_base + (job.max_seg - 1 - s);
-                    ids.push_back(slot);
-                    slot_ring_off[slot] = ring_cells;
-                    ring_cells += 3 * (int64_t) job.ring_w;
-                }
-            }
+            bins.tile_fwd[k] = (int) ids.size();
+            for (int s : tl)
+                if (grp(c->tiles[s].job) == gs[k]) ids.push_back(s);
         }
-        bins.bwd_off[3] = (int) ids.size();
+        bins.tile_fwd[3] = (int) ids.size();
+        by(gn, false);
+        for (int k = 0; k < 3; k++) {
+            bins.gen_bwd[k] = (int) ids.size();
+            for (int s : gn)
+                if (grp(c->tiles[s].job) == gs[k]) ids.push_back(s);
+        }
+        bins.gen_bwd[3] = (int) ids.size();
+        by(tl, false);
+        for (int k = 0; k < 3; k++) {
+            bins.tile_bwd[k] = (int) ids.size();
+            for (int s : tl)
+                if (grp(c->tiles[s].job) == gs[k]) ids.push_back(s);
+        }
+        bins.tile_bwd[3] = (int) ids.size();
+        for (int s : gn) {
+            ring_off[s] = ring_cells;
+            ring_cells += 3 * (int64_t) c->jobs[c->tiles[s].job].ring_w;
+        }
+        for (int s : tl) {
+            bnd_off[s] = bnd_cells;
+            bnd_cells += c->jobs[c->tiles[s].job].ring_w;
+        }
     }
     if (c->d_ids.ensure((ids.size() + 1) * sizeof(int32_t))) return 1;
     if (!ids.empty())
         CU(cudaMemcpyAsync(c->d_ids.p, ids.data(), ids.size() * sizeof(int32_t), cudaMemcpyHostToDevice, c->stream));
     if (with_slots) {
-        if (c->d_slot_ring_off.ensure(slot_ring_off.size() * sizeof(int64_t)) ||
-            c->d_ring.ensure((size_t) (ring_cells + 1) * 3 * sizeof(double)))
+        const size_t S = (size_t) c->total_slots;
+        if (c->d_slot_ring_off.ensure((S + 1) * sizeof(int64_t)) || c->d_slot_bnd_off.ensure((S + 1) * sizeof(int64_t)) ||
+            c->d_ring.ensure((size_t) (ring_cells + 1) * 3 * sizeof(double)) ||
+            c->d_bnd.ensure((size_t) (bnd_cells + 1) * 3 * sizeof(double)) || c->d_tiles.ensure((S + 1) * sizeof(mb::Tile)))
             return 1;
-        CU(cudaMemcpyAsync(c->d_slot_ring_off.p, slot_ring_off.data(), slot_ring_off.size() * sizeof(int64_t),
+        CU(cudaMemcpyAsync(c->d_slot_ring_off.p, ring_off.data(), (S + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, c->stream));
+        CU(cudaMemcpyAsync(c->d_slot_bnd_off.p, bnd_off.data(), (S + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, c->stream));
+        if (S) CU(cudaMemcpyAsync(c->d_tiles.p, c->tiles.data(), S * sizeof(mb::Tile), cudaMemcpyHostToDevice, c->stream));
+        CU(cudaMemcpyAsync(c->d_aln_first_slot.p, c->aln_first_slot.data(), (c->n_aln + 1) * sizeof(int32_t),
                            cudaMemcpyHostToDevice, c->stream));
     }
     if (nj) CU(cudaMemcpyAsync(c->d_jobs.p, c->jobs.data(), nj * sizeof(mb::Job), cudaMemcpyHostToDevice, c->stream));
-    CU(cudaStreamSynchronize(c->stream));  // ids / slot_ring_off are local pageable vectors
+    CU(cudaStreamSynchronize(c->stream));  // ids / offsets are local pageable vectors
     return 0;
 }
 
@@ -548,10 +680,23 @@ template <int G>
 void launch_forward(margin_b200_ctx *c, int off, int count) {
     if (count <= 0) return;
     const int per_block = kFwdThreads / G;
-    { KTimer kt_(c, K_FORWARD); mb::forward_kernel<G, kFwdThreads><<<(count + per_block - 1) / per_block, kFwdThreads, 0, c->stream>>>(
+    KTimer kt_(c, K_FORWARD);
+    mb::forward_kernel<G, kFwdThreads><<<(count + per_block - 1) / per_block, kFwdThreads, 0, c->stream>>>(
         c->d_jobs.as<mb::Job>(), c->d_ids.as<int32_t>() + off, count, c->d_models.as<mb::DevModel>(),
         c->d_symx.as<uint16_t>(), c->d_symy.as<uint16_t>(), c->d_kl.as<int32_t>(), c->d_cell_off.as<uint32_t>(),
-        c->d_F.as<double>()); }
+        c->d_F.as<double>());
+    c->launches++;
+}
+
+template <int G>
+void launch_forward_tiles(margin_b200_ctx *c, int off, int count) {
+    if (count <= 0) return;
+    const int per_block = kTileThreads / G;
+    KTimer kt_(c, K_FORWARD);
+    mb::forward_tile_kernel<G, kTileThreads><<<(count + per_block - 1) / per_block, kTileThreads, 0, c->stream>>>(
+        c->d_jobs.as<mb::Job>(), c->d_tiles.as<mb::Tile>(), c->d_ids.as<int32_t>() + off, count,
+        c->d_models.as<mb::DevModel>(), c->d_symx.as<uint16_t>(), c->d_symy.as<uint16_t>(), c->d_geo.as<int2>(),
+        c->d_F.as<double>(), c->d_bnd.as<double>(), c->d_slot_bnd_off.as<int64_t>());
     c->launches++;
 }
 
@@ -559,12 +704,26 @@ template <int G, bool INDELS>
 void launch_backward(margin_b200_ctx *c, int off, int count, int64_t stage_stride) {
     if (count <= 0) return;
     const int per_block = kBwdThreads / G;
-    { KTimer kt_(c, K_BACKWARD); mb::backward_kernel<G, kBwdThreads, INDELS><<<(count + per_block - 1) / per_block, kBwdThreads, 0, c->stream>>>(
-        c->d_jobs.as<mb::Job>(), c->d_segs.as<mb::Seg>(), c->d_ids.as<int32_t>() + off, count,
+    KTimer kt_(c, K_BACKWARD);
+    mb::backward_kernel<G, kBwdThreads, INDELS><<<(count + per_block - 1) / per_block, kBwdThreads, 0, c->stream>>>(
+        c->d_jobs.as<mb::Job>(), c->d_tiles.as<mb::Tile>(), c->d_ids.as<int32_t>() + off, count,
         c->d_models.as<mb::DevModel>(), c->d_symx.as<uint16_t>(), c->d_symy.as<uint16_t>(), c->d_kl.as<int32_t>(),
         c->d_cell_off.as<uint32_t>(), c->d_F.as<double>(), dev_params(c->params), c->d_ring.as<double>(),
         c->d_slot_ring_off.as<int64_t>(), c->d_stage.as<mb::Pair>(), stage_stride, c->d_seg_counts.as<int64_t>(),
-        c->total_slots); }
+        c->total_slots);
+    c->launches++;
+}
+
+template <int G, bool INDELS>
+void launch_backward_tiles(margin_b200_ctx *c, int off, int count, int64_t stage_stride) {
+    if (count <= 0) return;
+    const int per_block = kTileThreads / G;
+    KTimer kt_(c, K_BACKWARD);
+    mb::backward_tile_kernel<G, kTileThreads, INDELS><<<(count + per_block - 1) / per_block, kTileThreads, 0, c->stream>>>(
+        c->d_jobs.as<mb::Job>(), c->d_tiles.as<mb::Tile>(), c->d_ids.as<int32_t>() + off, count,
+        c->d_models.as<mb::DevModel>(), c->d_symx.as<uint16_t>(), c->d_symy.as<uint16_t>(), c->d_geo.as<int2>(),
+        c->d_F.as<double>(), c->d_bnd.as<double>(), c->d_slot_bnd_off.as<int64_t>(), dev_params(c->params),
+        c->d_stage.as<mb::Pair>(), stage_stride, c->d_seg_counts.as<int64_t>(), c->total_slots);
     c->launches++;
 }
 
@@ -596,12 +755,14 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
     c->ev_used = 0;
     c->total_tuples = 0;
     c->list_tuples[0] = c->list_tuples[1] = c->list_tuples[2] = 0;
+    c->force_group = force_group_env();
     const int nj = (int) c->jobs.size();
     const int n_lists = want_indels ? 3 : 1;
     CU(cudaEventRecord(c->ev0, c->stream));
     if (run_band(c, c->params.dynamic_anchor_expansion != 0, true, false)) return 1;
+    build_tiles(c);
     Bins bins;
-    if (build_bins(c, true, bins, force_group_env())) return 1;
+    if (build_bins(c, true, bins, c->force_group)) return 1;
     const int64_t cells = c->total_cells;
     const int S = c->total_slots;
     if (c->d_F.ensure((size_t) (cells + 1) * 3 * sizeof(double)) ||
@@ -611,18 +772,27 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
         c->d_off_out.ensure((size_t) 3 * (c->n_aln + 1) * sizeof(int64_t)))
         return 1;
     CU(cudaMemsetAsync(c->d_seg_counts.p, 0, ((size_t) 3 * S + 1) * sizeof(int64_t), c->stream));
-    launch_forward<8>(c, bins.fwd_off[0], bins.fwd_off[1] - bins.fwd_off[0]);
-    launch_forward<16>(c, bins.fwd_off[1], bins.fwd_off[2] - bins.fwd_off[1]);
-    launch_forward<32>(c, bins.fwd_off[2], bins.fwd_off[3] - bins.fwd_off[2]);
+    launch_forward<8>(c, bins.seq_fwd[0], bins.seq_fwd[1] - bins.seq_fwd[0]);
+    launch_forward<16>(c, bins.seq_fwd[1], bins.seq_fwd[2] - bins.seq_fwd[1]);
+    launch_forward<32>(c, bins.seq_fwd[2], bins.seq_fwd[3] - bins.seq_fwd[2]);
+    launch_forward_tiles<8>(c, bins.tile_fwd[0], bins.tile_fwd[1] - bins.tile_fwd[0]);
+    launch_forward_tiles<16>(c, bins.tile_fwd[1], bins.tile_fwd[2] - bins.tile_fwd[1]);
+    launch_forward_tiles<32>(c, bins.tile_fwd[2], bins.tile_fwd[3] - bins.tile_fwd[2]);
     const int64_t stride = cells + 1;
     if (want_indels) {
-        launch_backward<8, true>(c, bins.bwd_off[0], bins.bwd_off[1] - bins.bwd_off[0], stride);
-        launch_backward<16, true>(c, bins.bwd_off[1], bins.bwd_off[2] - bins.bwd_off[1], stride);
-        launch_backward<32, true>(c, bins.bwd_off[2], bins.bwd_off[3] - bins.bwd_off[2], stride);
+        launch_backward<8, true>(c, bins.gen_bwd[0], bins.gen_bwd[1] - bins.gen_bwd[0], stride);
+        launch_backward<16, true>(c, bins.gen_bwd[1], bins.gen_bwd[2] - bins.gen_bwd[1], stride);
+        launch_backward<32, true>(c, bins.gen_bwd[2], bins.gen_bwd[3] - bins.gen_bwd[2], stride);
+        launch_backward_tiles<8, true>(c, bins.tile_bwd[0], bins.tile_bwd[1] - bins.tile_bwd[0], stride);
+        launch_backward_tiles<16, true>(c, bins.tile_bwd[1], bins.tile_bwd[2] - bins.tile_bwd[1], stride);
+        launch_backward_tiles<32, true>(c, bins.tile_bwd[2], bins.tile_bwd[3] - bins.tile_bwd[2], stride);
     } else {
-        launch_backward<8, false>(c, bins.bwd_off[0], bins.bwd_off[1] - bins.bwd_off[0], stride);
-        launch_backward<16, false>(c, bins.bwd_off[1], bins.bwd_off[2] - bins.bwd_off[1], stride);
-        launch_backward<32, false>(c, bins.bwd_off[2], bins.bwd_off[3] - bins.bwd_off[2], stride);
+        launch_backward<8, false>(c, bins.gen_bwd[0], bins.gen_bwd[1] - bins.gen_bwd[0], stride);
+        launch_backward<16, false>(c, bins.gen_bwd[1], bins.gen_bwd[2] - bins.gen_bwd[1], stride);
+        launch_backward<32, false>(c, bins.gen_bwd[2], bins.gen_bwd[3] - bins.gen_bwd[2], stride);
+        launch_backward_tiles<8, false>(c, bins.tile_bwd[0], bins.tile_bwd[1] - bins.tile_bwd[0], stride);
+        launch_backward_tiles<16, false>(c, bins.tile_bwd[1], bins.tile_bwd[2] - bins.tile_bwd[1], stride);
+        launch_backward_tiles<32, false>(c, bins.tile_bwd[2], bins.tile_bwd[3] - bins.tile_bwd[2], stride);
     }
     // exclusive scan of the tuple counts over [list][slot] (+ one trailing zero so that the total comes out too)
     size_t tmp_bytes = 0;
@@ -630,8 +800,11 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
     CU(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, c->d_seg_counts.as<int64_t>(), c->d_seg_off.as<int64_t>(), n_scan,
                                      c->stream));
     if (c->d_scan_tmp.ensure(tmp_bytes + 16)) return 1;
-    { KTimer kt_(c, K_SCAN); CU(cub::DeviceScan::ExclusiveSum(c->d_scan_tmp.p, tmp_bytes, c->d_seg_counts.as<int64_t>(), c->d_seg_off.as<int64_t>(),
-                                     n_scan, c->stream)); }
+    {
+        KTimer kt_(c, K_SCAN);
+        CU(cub::DeviceScan::ExclusiveSum(c->d_scan_tmp.p, tmp_bytes, c->d_seg_counts.as<int64_t>(),
+                                         c->d_seg_off.as<int64_t>(), n_scan, c->stream));
+    }
     c->launches++;
     int64_t bounds[4] = {0, 0, 0, 0};
     for (int l = 0; l < 4; l++)
@@ -643,17 +816,19 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
     for (int l = 0; l < 3; l++) c->list_tuples[l] = bounds[l + 1] - bounds[l];
     if (c->d_out.ensure((size_t) (c->total_tuples + 1) * sizeof(mb::Pair))) return 1;
     if (S > 0 && nj > 0) {
-        { KTimer kt_(c, K_GATHER); mb::gather_kernel<<<S, 128, 0, c->stream>>>(c->d_jobs.as<mb::Job>(), c->d_segs.as<mb::Seg>(), S,
+        KTimer kt_(c, K_GATHER);
+        mb::gather_kernel<<<S, 128, 0, c->stream>>>(c->d_jobs.as<mb::Job>(), c->d_tiles.as<mb::Tile>(), S,
                                                     c->d_cell_off.as<uint32_t>(), c->d_seg_counts.as<int64_t>(),
                                                     c->d_seg_off.as<int64_t>(), c->d_stage.as<mb::Pair>(), stride,
-                                                    c->d_out.as<mb::Pair>(), n_lists); }
+                                                    c->d_out.as<mb::Pair>(), n_lists);
         c->launches++;
     }
     {
         const int threads = 128;
         const int blocks = (int) ((c->n_aln + 1 + threads - 1) / threads);
-        { KTimer kt_(c, K_OFFSETS); mb::list_offsets_kernel<<<blocks, threads, 0, c->stream>>>(c->d_aln_first_slot.as<int32_t>(), (int) c->n_aln, S,
-                                                                   c->d_seg_off.as<int64_t>(), c->d_off_out.as<int64_t>()); }
+        KTimer kt_(c, K_OFFSETS);
+        mb::list_offsets_kernel<<<blocks, threads, 0, c->stream>>>(c->d_aln_first_slot.as<int32_t>(), (int) c->n_aln, S,
+                                                                   c->d_seg_off.as<int64_t>(), c->d_off_out.as<int64_t>());
         c->launches++;
     }
     CU(cudaEventRecord(c->ev1, c->stream));
@@ -662,9 +837,9 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
     float ms = 0;
     CU(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
     int64_t segments = 0;
-    const int32_t *nseg = c->h_small.as<int32_t>();
-    for (int j = 0; j < nj; j++) segments += nseg[j];
+    for (int j = 0; j < nj; j++) segments += c->job_nseg[j];
     fill_stats(c, out, segments, ms);
+    out->tiles = S;
     return 0;
 }
 
@@ -735,13 +910,14 @@ extern "C" int margin_b200_forward_resident(margin_b200_ctx *c, margin_b200_resu
     CU(cudaEventRecord(c->ev0, c->stream));
     if (run_band(c, false, false, false)) return 1;
     Bins bins;
-    if (build_bins(c, false, bins, force_group_env())) return 1;
+    c->force_group = force_group_env();
+    if (build_bins(c, false, bins, c->force_group)) return 1;
     if (c->d_F.ensure((size_t) (c->total_cells + 1) * 3 * sizeof(double)) ||
         c->d_fwd_out.ensure((size_t) (c->n_aln + 1) * sizeof(double)))
         return 1;
-    launch_forward<8>(c, bins.fwd_off[0], bins.fwd_off[1] - bins.fwd_off[0]);
-    launch_forward<16>(c, bins.fwd_off[1], bins.fwd_off[2] - bins.fwd_off[1]);
-    launch_forward<32>(c, bins.fwd_off[2], bins.fwd_off[3] - bins.fwd_off[2]);
+    launch_forward<8>(c, bins.seq_fwd[0], bins.seq_fwd[1] - bins.seq_fwd[0]);
+    launch_forward<16>(c, bins.seq_fwd[1], bins.seq_fwd[2] - bins.seq_fwd[1]);
+    launch_forward<32>(c, bins.seq_fwd[2], bins.seq_fwd[3] - bins.seq_fwd[2]);
     if (nj > 0) {
         { KTimer kt_(c, K_FINAL); mb::final_dot_kernel<<<(nj + 127) / 128, 128, 0, c->stream>>>(c->d_jobs.as<mb::Job>(), nj,
                                                                       c->d_models.as<mb::DevModel>(),

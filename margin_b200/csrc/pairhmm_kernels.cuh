@@ -41,6 +41,17 @@ struct Seg {
     int32_t at_end;
 };
 
+// A unit of backward (and, in tiled mode, forward) work: a traceback segment or a piece of one (pairhmm_tiles.cuh).
+struct Tile {
+    int32_t job;
+    int32_t D;        // diagonal where the backward sweep starts
+    int32_t tb_to;    // posteriors are emitted for diagonals tb_to+1 .. tb_from
+    int32_t tb_from;
+    int32_t f0;       // diagonal where the tile's forward sweep starts (0 = the true start state)
+    int32_t flags;    // TILE_* bits
+};
+enum { TILE_AT_END = 1, TILE_BND = 2 };  // D is the job's last diagonal; F(tb_to) lives in the boundary buffer
+
 struct Params {
     double threshold;
     int32_t min_diags, tb_diags, expansion, dynamic;
@@ -75,7 +86,8 @@ template <int THREADS>
 __global__ void __launch_bounds__(THREADS)
 band_kernel(const Job *__restrict__ jobs, int n_jobs, const int32_t *__restrict__ anchors, Params p,
             int32_t *__restrict__ kl_out, uint32_t *__restrict__ cell_off, int64_t *__restrict__ job_cells,
-            int32_t *__restrict__ job_maxw, int32_t *__restrict__ kr_out /* may be null */, int *__restrict__ err) {
+            int32_t *__restrict__ job_maxw, int32_t *__restrict__ kr_out /* may be null */, int2 *__restrict__ geo_out,
+            int *__restrict__ err) {
     const int j = blockIdx.x;
     if (j >= n_jobs) return;
     const Job job = jobs[j];
@@ -147,6 +159,7 @@ band_kernel(const Job *__restrict__ jobs, int n_jobs, const int32_t *__restrict_
             kl_out[job.diag_off + d] = kl;
             if (kr_out) kr_out[job.diag_off + d] = kr;
             cell_off[job.diag_off + d] = excl;
+            geo_out[job.diag_off + d] = make_int2((d + kl) >> 1, (int) excl);  // {lowest x, cell offset}
         }
         __syncthreads();
         if (threadIdx.x == THREADS - 1) carry_s = pre + v;
@@ -154,6 +167,7 @@ band_kernel(const Job *__restrict__ jobs, int n_jobs, const int32_t *__restrict_
     }
     if (threadIdx.x == 0) {
         cell_off[job.diag_off + N + 1] = carry_s;
+        geo_out[job.diag_off + N + 1] = make_int2(0, (int) carry_s);
         job_cells[j] = carry_s;
         job_maxw[j] = maxw_s;
     }
@@ -162,8 +176,8 @@ band_kernel(const Job *__restrict__ jobs, int n_jobs, const int32_t *__restrict_
 // -------------------------------------------------------------------------------------- schedule
 
 // One warp per job: replays the traceback trigger of getPosteriorProbsWithBanding (pairwiseAligner.c:746-768),
-// which depends only on band widths.  Segment s of a job is stored at slot seg_base + (max_seg-1-s) so that the
-// slots of an alignment are already in the reference's final list order (later tracebacks first, :1104-1123).
+// which depends only on band widths.  Segment s of a job is stored at seg_base + s; the host cuts the segments into
+// tiles and orders them the way the reference's final lists are ordered (later tracebacks first, :1104-1123).
 __global__ void schedule_kernel(const Job *__restrict__ jobs, int n_jobs, const uint32_t *__restrict__ cell_off, Params p,
                                 Seg *__restrict__ segs, int32_t *__restrict__ job_nseg) {
     const int j = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -194,7 +208,7 @@ __global__ void schedule_kernel(const Job *__restrict__ jobs, int n_jobs, const 
             sg.tb_to = tb_to;
             sg.tb_from = tb_from;
             sg.at_end = at_end;
-            if (s < job.max_seg) segs[job.seg_base + (job.max_seg - 1 - s)] = sg;
+            if (s < job.max_seg) segs[job.seg_base + s] = sg;
         }
         s++;
         tb_to = tb_from;
@@ -444,7 +458,7 @@ __device__ __forceinline__ void emit_list(unsigned gm, bool ok, int32_t wt, int 
 // concurrently.  Tuples are staged per segment in emission order; gather_kernel puts them in list order.
 template <int G, int THREADS, bool INDELS>
 __global__ void __launch_bounds__(THREADS)
-backward_kernel(const Job *__restrict__ jobs, const Seg *__restrict__ segs, const int32_t *__restrict__ slot_ids,
+backward_kernel(const Job *__restrict__ jobs, const Tile *__restrict__ segs, const int32_t *__restrict__ slot_ids,
                 int n_ids, const DevModel *__restrict__ models, const uint16_t *__restrict__ symx,
                 const uint16_t *__restrict__ symy, const int32_t *__restrict__ kl_arr,
                 const uint32_t *__restrict__ cell_off, const double *__restrict__ F, Params p,
@@ -457,8 +471,7 @@ backward_kernel(const Job *__restrict__ jobs, const Seg *__restrict__ segs, cons
     const int g = (blockIdx.x * THREADS + threadIdx.x) / G;
     if (g >= n_ids) return;
     const int slot = slot_ids[g];
-    const Seg seg = segs[slot];
-    if (seg.job < 0) return;
+    const Tile seg = segs[slot];
     const unsigned gm = group_mask<G>();
     const int lane = threadIdx.x & (G - 1);
     const Job job = jobs[seg.job];
@@ -470,7 +483,7 @@ backward_kernel(const Job *__restrict__ jobs, const Seg *__restrict__ segs, cons
     const int ring_w = job.ring_w;
     double *rg = ring + 3 * slot_ring_off[slot];
     const int D = seg.D, tb_to = seg.tb_to, tb_from = seg.tb_from;
-    const double *endp = m.end_p[(seg.at_end && job.ragged_r) ? 1 : 0];
+    const double *endp = m.end_p[((seg.flags & TILE_AT_END) && job.ragged_r) ? 1 : 0];
     const int64_t region = job.cell_base + co[tb_to + 1];
     Pair *stM = stage + region, *stX = stage + stage_stride + region, *stY = stage + 2 * stage_stride + region;
     int cntM = 0, cntX = 0, cntY = 0;
@@ -619,13 +632,12 @@ backward_kernel(const Job *__restrict__ jobs, const Seg *__restrict__ segs, cons
 // Moves the staged tuples of every segment into the final lists.  seg_off is the exclusive scan of seg_counts over
 // [list][slot]; slots are already in final order (schedule_kernel), and inside a segment the reference's pop loop
 // (pairwiseAligner.c:1104-1123) reverses the emission order.
-__global__ void gather_kernel(const Job *__restrict__ jobs, const Seg *__restrict__ segs, int total_slots,
+__global__ void gather_kernel(const Job *__restrict__ jobs, const Tile *__restrict__ segs, int total_slots,
                               const uint32_t *__restrict__ cell_off, const int64_t *__restrict__ seg_counts,
                               const int64_t *__restrict__ seg_off, const Pair *__restrict__ stage, int64_t stage_stride,
                               Pair *__restrict__ out, int n_lists) {
     const int slot = blockIdx.x;
-    const Seg seg = segs[slot];
-    if (seg.job < 0) return;
+    const Tile seg = segs[slot];
     const Job job = jobs[seg.job];
     const int64_t region = job.cell_base + cell_off[job.diag_off + seg.tb_to + 1];
     for (int l = 0; l < n_lists; l++) {

@@ -12,13 +12,38 @@ from margin_b200.aligner import AlignerError, PairHmmAligner
 
 pytestmark = pytest.mark.gpu
 
+# Execution modes of the library (margin_b200/csrc/pairhmm_tiles.cuh): the default tiled mode, the tiled mode with
+# tiles much shorter than the test sequences (many tile boundaries), and the sequential per-alignment sweep.
+# Sequential mode is operation-for-operation the reference: weights are bit-exact except where device exp() and glibc
+# exp() round differently.  Tiled mode shifts F and B by a constant per tile, which changes last-ulp rounding: a
+# weight floor(p * 1e7) may then differ by ONE unit (1e-7 in probability), typically at cells with p == 1 up to
+# rounding; the (x, y) sets and their order stay identical.
+MODES = {
+    "tiles": dict(MARGIN_B200_MODE="tiles"),
+    "tiles_short": dict(MARGIN_B200_MODE="tiles", MARGIN_B200_TILE_LEN="60", MARGIN_B200_WARMUP="128"),
+    "sequential": dict(MARGIN_B200_MODE="sequential"),
+}
+
+
+@pytest.fixture(params=list(MODES))
+def mode(request, monkeypatch):
+    for k in ("MARGIN_B200_MODE", "MARGIN_B200_TILE_LEN", "MARGIN_B200_WARMUP"):
+        monkeypatch.delenv(k, raising=False)
+    for k, v in MODES[request.param].items():
+        monkeypatch.setenv(k, v)
+    return request.param
+
+
+def _allowed_diffs(mode, ntot):
+    return max(2, ntot // 100000) if mode == "sequential" else max(2, ntot // 20)
+
 
 def _mk_batch(rng, n, max_len, rle=True, **kw):
     return [gen.random_case(rng, int(rng.integers(0, max_len)), rle=rle, **kw) for _ in range(n)]
 
 
 @pytest.mark.parametrize("name", ["r94g360", "r94g344", "hifi", "no_rle"])
-def test_golden_vectors_of_the_reference(golden_model, name):
+def test_golden_vectors_of_the_reference(golden_model, name, mode):
     pm = golden_model(name)
     al = PairHmmAligner(pm.models, pm.p, 0)
     ndiff = ntot = 0
@@ -32,13 +57,12 @@ def test_golden_vectors_of_the_reference(golden_model, name):
         assert fwd[0] == c["fwd"]  # FP64 forward sweep is bit-exact
         kl, kr = al.bands([item])[0]
         assert np.array_equal(kl, c["kl"]) and np.array_equal(kr, c["kr"])
-    # weights may differ by one unit only where device exp() and glibc exp() round differently
-    assert ndiff <= max(2, ntot // 100000)
+    assert ndiff <= _allowed_diffs(mode, ntot)
     al.close()
 
 
 @pytest.mark.parametrize("force_group", ["", "8", "32"])
-def test_random_batch_vs_oracle(oracle, golden_model, force_group, monkeypatch):
+def test_random_batch_vs_oracle(oracle, golden_model, force_group, monkeypatch, mode):
     """Mixed batch: empty and 1-symbol sequences, no anchors (full matrix => wide diagonals), ragged ends, N symbols,
     clipped run lengths, both strands, several tracebacks.  MARGIN_B200_FORCE_GROUP exercises the wide-diagonal
     fallback (diagonals wider than the lane group) and the 32-lane path on every job."""
@@ -54,16 +78,17 @@ def test_random_batch_vs_oracle(oracle, golden_model, force_group, monkeypatch):
         p = pm.p.copy(min_diags_between_traceback=md, dynamic_anchor_expansion=dyn)
         al = PairHmmAligner(pm.models, p, 0)
         res = al.posteriors_batch(items, bool(wi))
-        ndiff = 0
+        ndiff = ntot = 0
         for i, it in enumerate(items):
             want = oracle.posteriors(pm.models[it[3]], p, it[0], it[1], it[2], it[4], it[5], wi)
             ndiff += compare_lists(res[i], want, tol_w=1)
-        assert ndiff <= 2
+            ntot += sum(len(x) for x in want)
+        assert ndiff <= _allowed_diffs(mode, ntot)
         assert res.stats["kernel_launches"] > 0 and res.stats["band_cells"] > 0
         al.close()
 
 
-def test_long_alignment_many_tracebacks(oracle, golden_model):
+def test_long_alignment_many_tracebacks(oracle, golden_model, mode):
     pm = golden_model("r94g360")
     rng = np.random.default_rng(23)
     items = [gen.random_case(rng, 9000, anchor_keep=0.9, expansions=(4,), ragged=False) for _ in range(3)]
@@ -109,7 +134,7 @@ def test_known_answers_on_gpu():
     al.close()
 
 
-def test_large_gap_split_vs_oracle(oracle, golden_model):
+def test_large_gap_split_vs_oracle(oracle, golden_model, mode):
     """Multi-block alignments (the unpatched reference is broken here; the oracle implements the
     intended semantics, validated in the survey against the one-line-patched reference)."""
     pm = golden_model("r94g360")
@@ -125,7 +150,7 @@ def test_large_gap_split_vs_oracle(oracle, golden_model):
     al.close()
 
 
-def test_reference_itself_on_this_box(reference, golden_model):
+def test_reference_itself_on_this_box(reference, golden_model, mode):
     """Where oracle/_ref travelled with the snapshot: GPU vs the unmodified reference, same process."""
     pm = golden_model("r94g360")
     sms = [reference.sm_from_model(pm.models[s]) for s in (0, 1)]
