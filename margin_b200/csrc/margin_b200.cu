@@ -108,7 +108,9 @@ struct margin_b200_ctx {
     std::vector<mb::Seg> segs;
     std::vector<mb::Tile> tiles;
     std::vector<int32_t> job_nseg, job_first_tile;
-    DevBuf d_geo, d_tiles, d_bnd, d_slot_bnd_off, d_emit5[2];
+    DevBuf d_geo, d_tiles, d_bnd, d_slot_bnd_off, d_emit5[2], d_px, d_py, d_stage2;
+    double v_thr = 0.0;
+    bool have_switch = false;
     DevBuf d_symx, d_symy, d_anchors, d_jobs, d_kl, d_kr, d_cell_off, d_job_cells, d_job_maxw, d_job_nseg, d_err;
     DevBuf d_segs, d_seg_counts, d_seg_off, d_scan_tmp, d_slot_ring_off, d_ring, d_ids, d_aln_first_slot;
     DevBuf d_F, d_stage, d_out, d_off_out, d_fwd_out;
@@ -193,7 +195,8 @@ void margin_b200_destroy(margin_b200_ctx *c) {
                       &c->d_kl, &c->d_kr, &c->d_cell_off, &c->d_job_cells, &c->d_job_maxw, &c->d_job_nseg, &c->d_err,
                       &c->d_segs, &c->d_seg_counts, &c->d_seg_off, &c->d_scan_tmp, &c->d_slot_ring_off, &c->d_ring,
                       &c->d_ids, &c->d_aln_first_slot, &c->d_F, &c->d_stage, &c->d_out, &c->d_off_out, &c->d_fwd_out,
-                      &c->d_geo, &c->d_tiles, &c->d_bnd, &c->d_slot_bnd_off, &c->d_emit5[0], &c->d_emit5[1]};
+                      &c->d_geo, &c->d_tiles, &c->d_bnd, &c->d_slot_bnd_off, &c->d_emit5[0], &c->d_emit5[1],
+                      &c->d_px, &c->d_py, &c->d_stage2};
     for (DevBuf *b : bufs) b->release();
     c->h_stage_in.release();
     c->h_small.release();
@@ -243,28 +246,29 @@ int margin_b200_set_model(margin_b200_ctx *c, int slot, const margin_b200_model 
     if (c->d_rsm[slot].ensure(nr * sizeof(double))) return 1;
     CU(cudaMemcpyAsync(c->d_rsm[slot].p, scaled.data(), nr * sizeof(double), cudaMemcpyHostToDevice, c->stream));
     d.rsm_scaled = c->d_rsm[slot].as<double>();
-    // folded match emission of the tile kernels: sub + 2.3025*rsm, one rounding, as impl/stateMachine.c:733-738 forms it
+    // folded match emission of the tile kernels, indexed by packed symbols (pairhmm_tiles.cuh): sub + 2.3025*rsm,
+    // one rounding, as impl/stateMachine.c:733-738 forms it
     {
-        const int R = MARGIN_B200_MAX_RL;
-        std::vector<double> e5((size_t) 25 * R * R, 0.0);
+        const int R = MARGIN_B200_MAX_RL, P = 5 * R;
+        std::vector<double> ep((size_t) P * P, 0.0);
         for (int xb = 0; xb < 5; xb++)
             for (int yb = 0; yb < 5; yb++) {
                 const double sub = (xb >= 4 || yb >= 4) ? -2.772588722 : m->match[xb * 4 + yb];
                 const int tb = xb >= 4 ? 0 : xb;
-                double *row = e5.data() + (size_t) (xb * 5 + yb) * R * R;
-                if (!m->rle) {
-                    row[0] = sub;
-                    continue;
-                }
-                for (int i = 0; i < R * R; i++) {
-                    const double r = scaled[(size_t) tb * R * R + i];
-                    row[i] = sub + r;
-                }
+                for (int rx = 0; rx < R; rx++)
+                    for (int ry = 0; ry < R; ry++) {
+                        double v = sub;
+                        if (m->rle) {
+                            const double r = scaled[((size_t) tb * R + rx) * R + ry];
+                            v = sub + r;
+                        }
+                        ep[(size_t) (xb * R + rx) * P + (yb * R + ry)] = v;
+                    }
             }
-        if (c->d_emit5[slot].ensure(e5.size() * sizeof(double))) return 1;
-        CU(cudaMemcpyAsync(c->d_emit5[slot].p, e5.data(), e5.size() * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+        if (c->d_emit5[slot].ensure(ep.size() * sizeof(double))) return 1;
+        CU(cudaMemcpyAsync(c->d_emit5[slot].p, ep.data(), ep.size() * sizeof(double), cudaMemcpyHostToDevice, c->stream));
         CU(cudaStreamSynchronize(c->stream));
-        d.emit5 = c->d_emit5[slot].as<double>();
+        d.emit_packed = c->d_emit5[slot].as<double>();
     }
     if (c->d_models.ensure(2 * sizeof(mb::DevModel))) return 1;
     CU(cudaMemcpyAsync(c->d_models.p, c->host_models, 2 * sizeof(mb::DevModel), cudaMemcpyHostToDevice, c->stream));
@@ -284,6 +288,20 @@ int margin_b200_set_params(margin_b200_ctx *c, const margin_b200_params *p) {
     if (!(p->threshold >= 0.0 && p->threshold <= 1.0)) return fail("threshold must be in [0,1]");
     c->params = *p;
     c->have_params = true;
+    // log-domain threshold of the tile kernels: smallest v with exp(v) >= threshold on this device
+    if (p->threshold <= 0.0) {
+        c->v_thr = -INFINITY;
+    } else if (p->threshold >= 1.0) {
+        c->v_thr = std::log(p->threshold);
+    } else {
+        if (check_device(c->device)) return 1;
+        CU(cudaSetDevice(c->device));
+        if (c->d_err.ensure(sizeof(double))) return 1;
+        mb::find_log_threshold_kernel<<<1, 1, 0, c->stream>>>(p->threshold, std::log(p->threshold), c->d_err.as<double>());
+        CU(cudaMemcpyAsync(&c->v_thr, c->d_err.p, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaStreamSynchronize(c->stream));
+        CU(cudaGetLastError());
+    }
     return 0;
 }
 
@@ -420,14 +438,6 @@ extern "C" int margin_b200_upload_batch(margin_b200_ctx *c, const margin_b200_ba
     c->total_cells = 0;
 
     const int64_t nx = n ? b->off_x[n] : 0, ny = n ? b->off_y[n] : 0;
-    if (c->host_models[0].rle || c->host_models[1].rle) {
-        // run lengths index the 51 x 51 repeat-count table (symbol_addRepeatCount clips them, impl/stateMachine.c:124-131)
-        unsigned worst = 0;
-        for (int64_t i = 0; i < nx; i++) worst = std::max(worst, (unsigned) (b->sym_x[i] >> 8));
-        for (int64_t i = 0; i < ny; i++) worst = std::max(worst, (unsigned) (b->sym_y[i] >> 8));
-        if (worst >= (unsigned) MARGIN_B200_MAX_RL)
-            return fail("a symbol carries run length %u; the repeat-count model holds 0..%d", worst, MARGIN_B200_MAX_RL - 1);
-    }
     const size_t anchor_ints = (size_t) 3 * total_anchor_triples + extra_anchors.size();
     if (c->d_symx.ensure((nx + 1) * sizeof(uint16_t)) || c->d_symy.ensure((ny + 1) * sizeof(uint16_t)) ||
         c->d_anchors.ensure((anchor_ints + 3) * sizeof(int32_t)) ||
@@ -444,6 +454,33 @@ extern "C" int margin_b200_upload_batch(margin_b200_ctx *c, const margin_b200_ba
                            extra_anchors.size() * sizeof(int32_t), cudaMemcpyHostToDevice, c->stream));
     if (!c->jobs.empty())
         CU(cudaMemcpyAsync(c->d_jobs.p, c->jobs.data(), c->jobs.size() * sizeof(mb::Job), cudaMemcpyHostToDevice, c->stream));
+    // packed one-byte symbols for the tile kernels (slack on both sides, see pairhmm_tiles.cuh)
+    {
+        bool used[2] = {false, false};
+        for (const mb::Job &job : c->jobs) used[job.slot] = true;
+        if (used[0] && used[1] && c->host_models[0].rle != c->host_models[1].rle)
+            return fail("the two state machines of a batch must both use (or both not use) repeat counts");
+        const int rle = c->host_models[used[0] ? 0 : 1].rle;
+        c->have_switch = false;
+        for (int k = 0; k < 2; k++)
+            if (used[k] && (c->host_models[k].t[mb::T_YX] != -INFINITY || c->host_models[k].t[mb::T_XY] != -INFINITY))
+                c->have_switch = true;
+        if (c->d_px.ensure((size_t) nx + 2 * mb::PACK_SLACK) || c->d_py.ensure((size_t) ny + 2 * mb::PACK_SLACK) ||
+            c->d_err.ensure(sizeof(double)))
+            return 1;
+        CU(cudaMemsetAsync(c->d_px.p, 0, (size_t) nx + 2 * mb::PACK_SLACK, c->stream));
+        CU(cudaMemsetAsync(c->d_py.p, 0, (size_t) ny + 2 * mb::PACK_SLACK, c->stream));
+        CU(cudaMemsetAsync(c->d_err.p, 0, sizeof(double), c->stream));
+        if (nx) mb::pack_symbols_kernel<<<(unsigned) ((nx + 255) / 256), 256, 0, c->stream>>>(
+                c->d_symx.as<uint16_t>(), c->d_px.as<uint8_t>() + mb::PACK_SLACK, nx, rle, c->d_err.as<int>());
+        if (ny) mb::pack_symbols_kernel<<<(unsigned) ((ny + 255) / 256), 256, 0, c->stream>>>(
+                c->d_symy.as<uint16_t>(), c->d_py.as<uint8_t>() + mb::PACK_SLACK, ny, rle, c->d_err.as<int>());
+        int perr = 0;
+        CU(cudaMemcpyAsync(&perr, c->d_err.p, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaStreamSynchronize(c->stream));
+        if (perr) return fail("a symbol carries a run length >= %d; the repeat-count model holds 0..%d", MARGIN_B200_MAX_RL,
+                              MARGIN_B200_MAX_RL - 1);
+    }
     CU(cudaStreamSynchronize(c->stream));  // extra_anchors / jobs are pageable host memory about to go out of scope
     return 0;
 }
@@ -688,16 +725,22 @@ void launch_forward(margin_b200_ctx *c, int off, int count) {
     c->launches++;
 }
 
+template <int G, bool SW>
+void launch_forward_tiles2(margin_b200_ctx *c, int off, int count) {
+    const int per_block = kTileThreads / G;
+    KTimer kt_(c, K_FORWARD);
+    mb::forward_tile_kernel<G, kTileThreads, SW><<<(count + per_block - 1) / per_block, kTileThreads, 0, c->stream>>>(
+        c->d_jobs.as<mb::Job>(), c->d_tiles.as<mb::Tile>(), c->d_ids.as<int32_t>() + off, count,
+        c->d_models.as<mb::DevModel>(), c->d_px.as<uint8_t>() + mb::PACK_SLACK, c->d_py.as<uint8_t>() + mb::PACK_SLACK,
+        c->d_geo.as<int2>(), c->d_F.as<double>(), c->d_bnd.as<double>(), c->d_slot_bnd_off.as<int64_t>());
+    c->launches++;
+}
+
 template <int G>
 void launch_forward_tiles(margin_b200_ctx *c, int off, int count) {
     if (count <= 0) return;
-    const int per_block = kTileThreads / G;
-    KTimer kt_(c, K_FORWARD);
-    mb::forward_tile_kernel<G, kTileThreads><<<(count + per_block - 1) / per_block, kTileThreads, 0, c->stream>>>(
-        c->d_jobs.as<mb::Job>(), c->d_tiles.as<mb::Tile>(), c->d_ids.as<int32_t>() + off, count,
-        c->d_models.as<mb::DevModel>(), c->d_symx.as<uint16_t>(), c->d_symy.as<uint16_t>(), c->d_geo.as<int2>(),
-        c->d_F.as<double>(), c->d_bnd.as<double>(), c->d_slot_bnd_off.as<int64_t>());
-    c->launches++;
+    if (c->have_switch) launch_forward_tiles2<G, true>(c, off, count);
+    else launch_forward_tiles2<G, false>(c, off, count);
 }
 
 template <int G, bool INDELS>
@@ -714,17 +757,23 @@ void launch_backward(margin_b200_ctx *c, int off, int count, int64_t stage_strid
     c->launches++;
 }
 
+template <int G, bool INDELS, bool SW>
+void launch_backward_tiles2(margin_b200_ctx *c, int off, int count, int64_t stage_stride) {
+    const int per_block = kTileThreads / G;
+    KTimer kt_(c, K_BACKWARD);
+    mb::backward_tile_kernel<G, kTileThreads, INDELS, SW><<<(count + per_block - 1) / per_block, kTileThreads, 0, c->stream>>>(
+        c->d_jobs.as<mb::Job>(), c->d_tiles.as<mb::Tile>(), c->d_ids.as<int32_t>() + off, count,
+        c->d_models.as<mb::DevModel>(), c->d_px.as<uint8_t>() + mb::PACK_SLACK, c->d_py.as<uint8_t>() + mb::PACK_SLACK,
+        c->d_geo.as<int2>(), c->d_F.as<double>(), c->d_bnd.as<double>(), c->d_slot_bnd_off.as<int64_t>(), c->v_thr,
+        c->d_stage2.as<mb::StagedPair>(), stage_stride, c->d_seg_counts.as<int64_t>(), c->total_slots);
+    c->launches++;
+}
+
 template <int G, bool INDELS>
 void launch_backward_tiles(margin_b200_ctx *c, int off, int count, int64_t stage_stride) {
     if (count <= 0) return;
-    const int per_block = kTileThreads / G;
-    KTimer kt_(c, K_BACKWARD);
-    mb::backward_tile_kernel<G, kTileThreads, INDELS><<<(count + per_block - 1) / per_block, kTileThreads, 0, c->stream>>>(
-        c->d_jobs.as<mb::Job>(), c->d_tiles.as<mb::Tile>(), c->d_ids.as<int32_t>() + off, count,
-        c->d_models.as<mb::DevModel>(), c->d_symx.as<uint16_t>(), c->d_symy.as<uint16_t>(), c->d_geo.as<int2>(),
-        c->d_F.as<double>(), c->d_bnd.as<double>(), c->d_slot_bnd_off.as<int64_t>(), dev_params(c->params),
-        c->d_stage.as<mb::Pair>(), stage_stride, c->d_seg_counts.as<int64_t>(), c->total_slots);
-    c->launches++;
+    if (c->have_switch) launch_backward_tiles2<G, INDELS, true>(c, off, count, stage_stride);
+    else launch_backward_tiles2<G, INDELS, false>(c, off, count, stage_stride);
 }
 
 int force_group_env() {
@@ -765,8 +814,10 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
     if (build_bins(c, true, bins, c->force_group)) return 1;
     const int64_t cells = c->total_cells;
     const int S = c->total_slots;
+    const bool any_generic = bins.gen_bwd[3] > bins.gen_bwd[0], any_tiled = bins.tile_bwd[3] > bins.tile_bwd[0];
     if (c->d_F.ensure((size_t) (cells + 1) * 3 * sizeof(double)) ||
-        c->d_stage.ensure((size_t) (cells + 1) * n_lists * sizeof(mb::Pair)) ||
+        (any_generic && c->d_stage.ensure((size_t) (cells + 1) * n_lists * sizeof(mb::Pair))) ||
+        (any_tiled && c->d_stage2.ensure((size_t) (cells + 1) * n_lists * sizeof(mb::StagedPair))) ||
         c->d_seg_counts.ensure(((size_t) 3 * S + 1) * sizeof(int64_t)) ||
         c->d_seg_off.ensure(((size_t) 3 * S + 1) * sizeof(int64_t)) ||
         c->d_off_out.ensure((size_t) 3 * (c->n_aln + 1) * sizeof(int64_t)))
@@ -815,12 +866,20 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
     c->total_tuples = bounds[3];
     for (int l = 0; l < 3; l++) c->list_tuples[l] = bounds[l + 1] - bounds[l];
     if (c->d_out.ensure((size_t) (c->total_tuples + 1) * sizeof(mb::Pair))) return 1;
-    if (S > 0 && nj > 0) {
+    if (S > 0 && nj > 0 && any_generic) {
         KTimer kt_(c, K_GATHER);
         mb::gather_kernel<<<S, 128, 0, c->stream>>>(c->d_jobs.as<mb::Job>(), c->d_tiles.as<mb::Tile>(), S,
                                                     c->d_cell_off.as<uint32_t>(), c->d_seg_counts.as<int64_t>(),
                                                     c->d_seg_off.as<int64_t>(), c->d_stage.as<mb::Pair>(), stride,
                                                     c->d_out.as<mb::Pair>(), n_lists);
+        c->launches++;
+    }
+    if (S > 0 && nj > 0 && any_tiled) {
+        KTimer kt_(c, K_GATHER);
+        mb::gather_staged_kernel<<<S, 128, 0, c->stream>>>(c->d_jobs.as<mb::Job>(), c->d_tiles.as<mb::Tile>(), S,
+                                                           c->d_geo.as<int2>(), c->d_seg_counts.as<int64_t>(),
+                                                           c->d_seg_off.as<int64_t>(), c->d_stage2.as<mb::StagedPair>(),
+                                                           stride, c->d_out.as<mb::Pair>(), n_lists);
         c->launches++;
     }
     {

@@ -25,10 +25,10 @@ struct DevModel {
     int32_t rle;
     int32_t max_rl;
     const double *rsm_scaled;  // 2.3025 * rsm[b][under][obs], device pointer (4*51*51)
-    // Folded match emission for the tile kernels: emit5[((xb*5+yb)*51 + rlX)*51 + rlY] with xb, yb in 0..4
-    // (4 = ambiguous) = match[xb][yb] + 2.3025*rsm[...] rounded once, exactly the sum the reference forms per cell
-    // (impl/stateMachine.c:733-738).  Non-RLE models fill only the [rl=0][rl=0] entries.
-    const double *emit5;
+    // Folded match emission for the tile kernels, indexed by packed symbols p = min(base,4)*51 + runLength:
+    // emit_packed[pX*255 + pY] = match[xb][yb] + 2.3025*rsm[...] rounded once, exactly the sum the reference forms
+    // per cell (impl/stateMachine.c:733-738).  Non-RLE models only use the runLength = 0 entries.
+    const double *emit_packed;
 };
 
 enum { T_MM = 0, T_XM = 1, T_YM = 2, T_MX = 3, T_XX = 4, T_YX = 5, T_MY = 6, T_YY = 7, T_XY = 8 };

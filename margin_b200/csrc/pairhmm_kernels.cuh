@@ -638,6 +638,7 @@ __global__ void gather_kernel(const Job *__restrict__ jobs, const Tile *__restri
                               Pair *__restrict__ out, int n_lists) {
     const int slot = blockIdx.x;
     const Tile seg = segs[slot];
+    if (seg.flags & TILE_BND) return;  // tiled jobs are gathered by gather_staged_kernel
     const Job job = jobs[seg.job];
     const int64_t region = job.cell_base + cell_off[job.diag_off + seg.tb_to + 1];
     for (int l = 0; l < n_lists; l++) {
