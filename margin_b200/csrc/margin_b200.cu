@@ -4,6 +4,7 @@
 // thread (the reference runs one chunk per OpenMP thread, polish.c:476; thread t uses device t % nGPU).
 // There is no CPU fallback anywhere in this file: without a usable device every entry point fails.
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -109,6 +110,16 @@ struct margin_b200_ctx {
     std::vector<mb::Tile> tiles;
     std::vector<int32_t> job_nseg, job_first_tile;
     DevBuf d_geo, d_tiles, d_bnd, d_slot_bnd_off, d_emit5[2], d_px, d_py, d_stage2;
+    DevBuf d_chunks, d_job_first_chunk, d_chunk_sum, d_chunk_maxw, d_totals;
+    DevBuf d_arena, d_offs, d_status;
+    PinBuf h_arena;
+    mb::Tile *p_tiles = nullptr;
+    int64_t *p_ring_off = nullptr, *p_bnd_off = nullptr;
+    int32_t *p_aln_first_slot = nullptr, *p_ids = nullptr;
+    std::vector<uint64_t> keys[4], key_tmp;
+    std::vector<uint32_t> key_cnt;
+    std::vector<mb::BandChunk> chunks;
+    std::vector<int32_t> job_first_chunk;
     double v_thr = 0.0;
     bool have_switch = false;
     DevBuf d_symx, d_symy, d_anchors, d_jobs, d_kl, d_kr, d_cell_off, d_job_cells, d_job_maxw, d_job_nseg, d_err;
@@ -150,6 +161,25 @@ struct KTimer {
         cudaEventRecord(c->ev_pool[2 * idx], c->stream);
     }
     ~KTimer() { cudaEventRecord(c->ev_pool[2 * idx + 1], c->stream); }
+};
+
+// Host-side phase trace (MARGIN_B200_TRACE=1): wall-clock microseconds between marks, printed to stderr.
+struct Trace {
+    bool on;
+    std::chrono::steady_clock::time_point t0;
+    std::string line;
+    Trace() : on(getenv("MARGIN_B200_TRACE") != nullptr), t0(std::chrono::steady_clock::now()) {}
+    void mark(const char *what) {
+        if (!on) return;
+        auto t1 = std::chrono::steady_clock::now();
+        char buf[64];
+        snprintf(buf, sizeof(buf), " %s=%.0fus", what, std::chrono::duration<double, std::micro>(t1 - t0).count());
+        line += buf;
+        t0 = t1;
+    }
+    ~Trace() {
+        if (on) fprintf(stderr, "[margin_b200 trace]%s\n", line.c_str());
+    }
 };
 
 int check_device(int device) {
@@ -196,10 +226,12 @@ void margin_b200_destroy(margin_b200_ctx *c) {
                       &c->d_segs, &c->d_seg_counts, &c->d_seg_off, &c->d_scan_tmp, &c->d_slot_ring_off, &c->d_ring,
                       &c->d_ids, &c->d_aln_first_slot, &c->d_F, &c->d_stage, &c->d_out, &c->d_off_out, &c->d_fwd_out,
                       &c->d_geo, &c->d_tiles, &c->d_bnd, &c->d_slot_bnd_off, &c->d_emit5[0], &c->d_emit5[1],
-                      &c->d_px, &c->d_py, &c->d_stage2};
+                      &c->d_px, &c->d_py, &c->d_stage2, &c->d_chunks, &c->d_job_first_chunk, &c->d_chunk_sum, &c->d_chunk_maxw,
+                      &c->d_totals, &c->d_arena, &c->d_offs, &c->d_status};
     for (DevBuf *b : bufs) b->release();
     c->h_stage_in.release();
     c->h_small.release();
+    c->h_arena.release();
     c->h_out.release();
     c->h_off.release();
     for (cudaEvent_t e : c->ev_pool) cudaEventDestroy(e);
@@ -367,14 +399,78 @@ extern "C" int margin_b200_upload_batch(margin_b200_ctx *c, const margin_b200_ba
     if (b->n < 0) return fail("margin_b200_upload_batch: negative batch size");
     if (check_device(c->device)) return 1;
     CU(cudaSetDevice(c->device));
+    Trace tr;
     const margin_b200_params &p = c->params;
     const int64_t n = b->n;
     c->n_aln = n;
     c->jobs.clear();
     c->aln_first_slot.assign(n + 1, 0);
     c->aln_first_job.assign(n + 1, 0);
-    std::vector<int32_t> extra_anchors;
     const int64_t total_anchor_triples = n ? b->off_a[n] : 0;
+    const int64_t nx = n ? b->off_x[n] : 0, ny = n ? b->off_y[n] : 0;
+    // ---- cheap per-alignment checks, then everything that is O(symbols) or O(anchors) happens on the device
+    bool used[2] = {false, false};
+    for (int64_t i = 0; i < n; i++) {
+        const int64_t lx = b->off_x[i + 1] - b->off_x[i], ly = b->off_y[i + 1] - b->off_y[i];
+        const int64_t na = b->off_a[i + 1] - b->off_a[i];
+        if (lx < 0 || ly < 0 || na < 0) return fail("alignment %lld: negative length", (long long) i);
+        if (lx + ly > (int64_t) 1 << 30) return fail("alignment %lld: sequences too long", (long long) i);
+        const uint8_t slot = b->model_slot ? b->model_slot[i] : 0;
+        if (slot > 1 || !c->have_model[slot]) return fail("alignment %lld: model slot %d has not been set", (long long) i, slot);
+        used[slot] = true;
+    }
+    if (used[0] && used[1] && c->host_models[0].rle != c->host_models[1].rle)
+        return fail("the two state machines of a batch must both use (or both not use) repeat counts");
+    const int rle = c->host_models[used[0] ? 0 : 1].rle;
+    c->have_switch = false;
+    for (int k = 0; k < 2; k++)
+        if (used[k] && (c->host_models[k].t[mb::T_YX] != -INFINITY || c->host_models[k].t[mb::T_XY] != -INFINITY))
+            c->have_switch = true;
+    if (c->d_symx.ensure((nx + 1) * sizeof(uint16_t)) || c->d_symy.ensure((ny + 1) * sizeof(uint16_t)) ||
+        c->d_anchors.ensure(((size_t) 3 * total_anchor_triples + 3) * sizeof(int32_t)) ||
+        c->d_offs.ensure((size_t) 3 * (n + 1) * sizeof(int64_t)) || c->d_status.ensure(((size_t) 2 * n + 2) * sizeof(int32_t)) ||
+        c->d_px.ensure((size_t) nx + 2 * mb::PACK_SLACK) || c->d_py.ensure((size_t) ny + 2 * mb::PACK_SLACK) ||
+        c->d_err.ensure(sizeof(double)) || c->h_small.ensure(((size_t) 2 * n + 4) * sizeof(int32_t)))
+        return 1;
+    if (nx) CU(cudaMemcpyAsync(c->d_symx.p, b->sym_x, nx * sizeof(uint16_t), cudaMemcpyHostToDevice, c->stream));
+    if (ny) CU(cudaMemcpyAsync(c->d_symy.p, b->sym_y, ny * sizeof(uint16_t), cudaMemcpyHostToDevice, c->stream));
+    if (total_anchor_triples)
+        CU(cudaMemcpyAsync(c->d_anchors.p, b->anchors, (size_t) 3 * total_anchor_triples * sizeof(int32_t),
+                           cudaMemcpyHostToDevice, c->stream));
+    int32_t *h_status = c->h_small.as<int32_t>();
+    if (n) {
+        int64_t *d_offs = c->d_offs.as<int64_t>();
+        CU(cudaMemcpyAsync(d_offs, b->off_a, (n + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, c->stream));
+        CU(cudaMemcpyAsync(d_offs + (n + 1), b->off_x, (n + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, c->stream));
+        CU(cudaMemcpyAsync(d_offs + 2 * (n + 1), b->off_y, (n + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, c->stream));
+        for (int64_t i = 0; i < n; i++) {
+            h_status[2 * i] = 0x7fffffff;
+            h_status[2 * i + 1] = 0;
+        }
+        CU(cudaMemcpyAsync(c->d_status.p, h_status, (size_t) 2 * n * sizeof(int32_t), cudaMemcpyHostToDevice, c->stream));
+        mb::check_anchors_kernel<<<(unsigned) n, 256, 0, c->stream>>>(c->d_anchors.as<int32_t>(), d_offs, d_offs + (n + 1),
+                                                                     d_offs + 2 * (n + 1), p.split_matrix_bigger_than_this,
+                                                                     c->d_status.as<int32_t>());
+    }
+    // packed one-byte symbols for the tile kernels (slack on both sides, see pairhmm_tiles.cuh)
+    CU(cudaMemsetAsync(c->d_px.p, 0, (size_t) nx + 2 * mb::PACK_SLACK, c->stream));
+    CU(cudaMemsetAsync(c->d_py.p, 0, (size_t) ny + 2 * mb::PACK_SLACK, c->stream));
+    CU(cudaMemsetAsync(c->d_err.p, 0, sizeof(double), c->stream));
+    if (nx) mb::pack_symbols_kernel<<<(unsigned) ((nx + 255) / 256), 256, 0, c->stream>>>(
+            c->d_symx.as<uint16_t>(), c->d_px.as<uint8_t>() + mb::PACK_SLACK, nx, rle, c->d_err.as<int>());
+    if (ny) mb::pack_symbols_kernel<<<(unsigned) ((ny + 255) / 256), 256, 0, c->stream>>>(
+            c->d_symy.as<uint16_t>(), c->d_py.as<uint8_t>() + mb::PACK_SLACK, ny, rle, c->d_err.as<int>());
+    if (n) CU(cudaMemcpyAsync(h_status, c->d_status.p, (size_t) 2 * n * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemcpyAsync(h_status + 2 * n, c->d_err.p, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    tr.mark("enqueue");
+    CU(cudaStreamSynchronize(c->stream));
+    CU(cudaGetLastError());
+    tr.mark("h2d+check sync");
+    if (h_status[2 * n])
+        return fail("a symbol carries a run length >= %d; the repeat-count model holds 0..%d", MARGIN_B200_MAX_RL,
+                    MARGIN_B200_MAX_RL - 1);
+    // ---- job table: one job per alignment, or one per block where getSplitPoints cuts (rare: host path)
+    std::vector<int32_t> extra_anchors;
     std::vector<Block> blocks;
     int64_t diag_off = 0;
     int64_t slot_base = 0;
@@ -382,21 +478,24 @@ extern "C" int margin_b200_upload_batch(margin_b200_ctx *c, const margin_b200_ba
     for (int64_t i = 0; i < n; i++) {
         const int64_t lx = b->off_x[i + 1] - b->off_x[i], ly = b->off_y[i + 1] - b->off_y[i];
         const int64_t na = b->off_a[i + 1] - b->off_a[i];
-        if (lx < 0 || ly < 0 || na < 0) return fail("alignment %lld: negative length", (long long) i);
-        if (lx + ly > (int64_t) 1 << 30) return fail("alignment %lld: sequences too long", (long long) i);
         const int32_t *anc = b->anchors + 3 * b->off_a[i];
-        if (validate_anchors(anc, na, lx, ly, i)) return 1;
+        if (h_status[2 * i] != 0x7fffffff) return validate_anchors(anc, na, lx, ly, i) ? 1 : fail("alignment %lld: bad anchors", (long long) i);
         const bool rl = b->ragged_left && b->ragged_left[i], rr = b->ragged_right && b->ragged_right[i];
         const uint8_t slot = b->model_slot ? b->model_slot[i] : 0;
-        if (slot > 1 || !c->have_model[slot]) return fail("alignment %lld: model slot %d has not been set", (long long) i, slot);
-        split_points(anc, na, lx, ly, p.split_matrix_bigger_than_this, rl, rr, blocks);
+        if (h_status[2 * i + 1]) {
+            split_points(anc, na, lx, ly, p.split_matrix_bigger_than_this, rl, rr, blocks);
+        } else {
+            blocks.assign(1, Block{0, 0, lx, ly});
+        }
         c->aln_first_slot[i] = (int32_t) slot_base;
         c->aln_first_job[i] = (int32_t) c->jobs.size();
         int64_t j = 0;
         for (size_t k = 0; k < blocks.size(); k++) {
             const Block &bl = blocks[k];
             const int64_t j0 = j;
-            while (j < na && (int64_t) anc[3 * j] + anc[3 * j + 1] < bl.x2 + bl.y2) j++;
+            if (blocks.size() == 1) j = na;
+            else
+                while (j < na && (int64_t) anc[3 * j] + anc[3 * j + 1] < bl.x2 + bl.y2) j++;
             mb::Job job;
             memset(&job, 0, sizeof(job));
             job.symx_off = b->off_x[i] + bl.x1;
@@ -432,55 +531,47 @@ extern "C" int margin_b200_upload_batch(margin_b200_ctx *c, const margin_b200_ba
     }
     c->aln_first_slot[n] = (int32_t) slot_base;
     c->aln_first_job[n] = (int32_t) c->jobs.size();
+    // chunks of the band construction (pairhmm_kernels.cuh): BAND_CHUNK diagonals of one job each
+    c->chunks.clear();
+    c->job_first_chunk.assign(c->jobs.size() + 1, 0);
+    for (size_t j = 0; j < c->jobs.size(); j++) {
+        c->job_first_chunk[j] = (int32_t) c->chunks.size();
+        const int entries = c->jobs[j].lx + c->jobs[j].ly + 2;
+        for (int d0 = 0; d0 < entries; d0 += mb::BAND_CHUNK) c->chunks.push_back(mb::BandChunk{(int32_t) j, d0});
+    }
+    c->job_first_chunk[c->jobs.size()] = (int32_t) c->chunks.size();
     c->total_diag = diag_off;
     c->seg_slots = (int) slot_base;
     c->total_slots = 0;
     c->total_cells = 0;
 
-    const int64_t nx = n ? b->off_x[n] : 0, ny = n ? b->off_y[n] : 0;
-    const size_t anchor_ints = (size_t) 3 * total_anchor_triples + extra_anchors.size();
-    if (c->d_symx.ensure((nx + 1) * sizeof(uint16_t)) || c->d_symy.ensure((ny + 1) * sizeof(uint16_t)) ||
-        c->d_anchors.ensure((anchor_ints + 3) * sizeof(int32_t)) ||
-        c->d_jobs.ensure((c->jobs.size() + 1) * sizeof(mb::Job)) ||
-        c->d_aln_first_slot.ensure((n + 1) * sizeof(int32_t)))
-        return 1;
-    if (nx) CU(cudaMemcpyAsync(c->d_symx.p, b->sym_x, nx * sizeof(uint16_t), cudaMemcpyHostToDevice, c->stream));
-    if (ny) CU(cudaMemcpyAsync(c->d_symy.p, b->sym_y, ny * sizeof(uint16_t), cudaMemcpyHostToDevice, c->stream));
-    if (total_anchor_triples)
-        CU(cudaMemcpyAsync(c->d_anchors.p, b->anchors, (size_t) 3 * total_anchor_triples * sizeof(int32_t),
-                           cudaMemcpyHostToDevice, c->stream));
-    if (!extra_anchors.empty())
+    if (!extra_anchors.empty()) {  // the re-based copies live behind the batch's own anchors
+        // grow without losing the anchors already on the device
+        const size_t need = ((size_t) 3 * total_anchor_triples + extra_anchors.size() + 3) * sizeof(int32_t);
+        if (need > c->d_anchors.cap) {
+            DevBuf bigger;
+            if (bigger.ensure(need)) return 1;
+            CU(cudaMemcpyAsync(bigger.p, c->d_anchors.p, (size_t) 3 * total_anchor_triples * sizeof(int32_t),
+                               cudaMemcpyDeviceToDevice, c->stream));
+            CU(cudaStreamSynchronize(c->stream));
+            c->d_anchors.release();
+            c->d_anchors = bigger;
+        }
         CU(cudaMemcpyAsync(c->d_anchors.as<int32_t>() + 3 * total_anchor_triples, extra_anchors.data(),
                            extra_anchors.size() * sizeof(int32_t), cudaMemcpyHostToDevice, c->stream));
+    }
+    if (c->d_jobs.ensure((c->jobs.size() + 1) * sizeof(mb::Job))) return 1;
     if (!c->jobs.empty())
         CU(cudaMemcpyAsync(c->d_jobs.p, c->jobs.data(), c->jobs.size() * sizeof(mb::Job), cudaMemcpyHostToDevice, c->stream));
-    // packed one-byte symbols for the tile kernels (slack on both sides, see pairhmm_tiles.cuh)
-    {
-        bool used[2] = {false, false};
-        for (const mb::Job &job : c->jobs) used[job.slot] = true;
-        if (used[0] && used[1] && c->host_models[0].rle != c->host_models[1].rle)
-            return fail("the two state machines of a batch must both use (or both not use) repeat counts");
-        const int rle = c->host_models[used[0] ? 0 : 1].rle;
-        c->have_switch = false;
-        for (int k = 0; k < 2; k++)
-            if (used[k] && (c->host_models[k].t[mb::T_YX] != -INFINITY || c->host_models[k].t[mb::T_XY] != -INFINITY))
-                c->have_switch = true;
-        if (c->d_px.ensure((size_t) nx + 2 * mb::PACK_SLACK) || c->d_py.ensure((size_t) ny + 2 * mb::PACK_SLACK) ||
-            c->d_err.ensure(sizeof(double)))
-            return 1;
-        CU(cudaMemsetAsync(c->d_px.p, 0, (size_t) nx + 2 * mb::PACK_SLACK, c->stream));
-        CU(cudaMemsetAsync(c->d_py.p, 0, (size_t) ny + 2 * mb::PACK_SLACK, c->stream));
-        CU(cudaMemsetAsync(c->d_err.p, 0, sizeof(double), c->stream));
-        if (nx) mb::pack_symbols_kernel<<<(unsigned) ((nx + 255) / 256), 256, 0, c->stream>>>(
-                c->d_symx.as<uint16_t>(), c->d_px.as<uint8_t>() + mb::PACK_SLACK, nx, rle, c->d_err.as<int>());
-        if (ny) mb::pack_symbols_kernel<<<(unsigned) ((ny + 255) / 256), 256, 0, c->stream>>>(
-                c->d_symy.as<uint16_t>(), c->d_py.as<uint8_t>() + mb::PACK_SLACK, ny, rle, c->d_err.as<int>());
-        int perr = 0;
-        CU(cudaMemcpyAsync(&perr, c->d_err.p, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
-        CU(cudaStreamSynchronize(c->stream));
-        if (perr) return fail("a symbol carries a run length >= %d; the repeat-count model holds 0..%d", MARGIN_B200_MAX_RL,
-                              MARGIN_B200_MAX_RL - 1);
-    }
+    if (c->d_chunks.ensure((c->chunks.size() + 1) * sizeof(mb::BandChunk)) ||
+        c->d_job_first_chunk.ensure((c->jobs.size() + 1) * sizeof(int32_t)))
+        return 1;
+    if (!c->chunks.empty())
+        CU(cudaMemcpyAsync(c->d_chunks.p, c->chunks.data(), c->chunks.size() * sizeof(mb::BandChunk), cudaMemcpyHostToDevice,
+                           c->stream));
+    CU(cudaMemcpyAsync(c->d_job_first_chunk.p, c->job_first_chunk.data(), (c->jobs.size() + 1) * sizeof(int32_t),
+                       cudaMemcpyHostToDevice, c->stream));
+    tr.mark("jobs");
     CU(cudaStreamSynchronize(c->stream));  // extra_anchors / jobs are pageable host memory about to go out of scope
     return 0;
 }
@@ -506,34 +597,49 @@ constexpr int kTileThreads = 128;
 
 inline int group_of(int maxw) { return maxw <= 8 ? 8 : (maxw <= 16 ? 16 : 32); }
 
-// band_kernel (+ schedule_kernel) and the one host round trip of the pipeline: per-job cell counts, widths, segment
-// counts and the segments themselves come back so that F / staging can be sized and the work cut into tiles.
+// Band geometry (chunk-parallel, 4 launches) + schedule_kernel, then the first host round trip of the pipeline:
+// per-job cell counts, widths, segment counts and the segments themselves come back (one pinned buffer, one sync) so
+// that F / staging can be sized and the work cut into tiles.  Job::cell_base / ring_w are filled in on the device.
 int run_band(margin_b200_ctx *c, bool dynamic, bool with_schedule, bool want_kr) {
     const int nj = (int) c->jobs.size();
+    const int nc = (int) c->chunks.size();
     mb::Params q = dev_params(c->params);
     q.dynamic = dynamic ? 1 : 0;
+    const size_t S = (size_t) c->seg_slots;
     if (c->d_kl.ensure((c->total_diag + 1) * sizeof(int32_t)) || c->d_cell_off.ensure((c->total_diag + 1) * sizeof(uint32_t)) ||
-        c->d_geo.ensure((c->total_diag + 1) * sizeof(int2)) ||
-        c->d_job_cells.ensure((nj + 1) * sizeof(int64_t)) || c->d_job_maxw.ensure((nj + 1) * sizeof(int32_t)) ||
-        c->d_job_nseg.ensure((nj + 1) * sizeof(int32_t)) || c->d_err.ensure(sizeof(int)) ||
-        c->d_segs.ensure(((size_t) c->seg_slots + 1) * sizeof(mb::Seg)))
+        c->d_geo.ensure((c->total_diag + 1) * sizeof(int2)) || c->d_job_cells.ensure((nj + 1) * sizeof(int64_t)) ||
+        c->d_job_maxw.ensure((nj + 1) * sizeof(int32_t)) || c->d_job_nseg.ensure((nj + 1) * sizeof(int32_t)) ||
+        c->d_err.ensure(sizeof(double)) || c->d_segs.ensure((S + 1) * sizeof(mb::Seg)) ||
+        c->d_chunk_sum.ensure((nc + 1) * sizeof(uint32_t)) || c->d_chunk_maxw.ensure((nc + 1) * sizeof(int32_t)) ||
+        c->d_totals.ensure(4 * sizeof(int64_t)))
         return 1;
     if (want_kr && c->d_kr.ensure((c->total_diag + 1) * sizeof(int32_t))) return 1;
+    // pinned landing zone: [totals 2 x int64][job_cells][job_maxw][job_nseg][segs][err]
+    const size_t o_cells = 16, o_maxw = o_cells + (size_t) nj * 8, o_nseg = o_maxw + (size_t) nj * 4,
+                 o_segs = o_nseg + (size_t) nj * 4, o_err = o_segs + S * sizeof(mb::Seg), o_end = o_err + 8;
+    if (c->h_small.ensure(o_end)) return 1;
+    char *h = c->h_small.as<char>();
+    memset(h, 0, 16);
+    *reinterpret_cast<int *>(h + o_err) = 0;
     CU(cudaMemsetAsync(c->d_err.p, 0, sizeof(int), c->stream));
-    c->job_cells.assign(nj, 0);
-    c->job_maxw.assign(nj, 0);
-    c->job_nseg.assign(nj, 0);
-    c->segs.assign((size_t) c->seg_slots, mb::Seg{-1, 0, 0, 0, 0});
     if (nj > 0) {
         {
             KTimer kt_(c, K_BAND);
-            mb::band_kernel<256><<<nj, 256, 0, c->stream>>>(c->d_jobs.as<mb::Job>(), nj, c->d_anchors.as<int32_t>(), q,
-                                                            c->d_kl.as<int32_t>(), c->d_cell_off.as<uint32_t>(),
-                                                            c->d_job_cells.as<int64_t>(), c->d_job_maxw.as<int32_t>(),
-                                                            want_kr ? c->d_kr.as<int32_t>() : nullptr,
-                                                            c->d_geo.as<int2>(), c->d_err.as<int>());
+            mb::band_chunk_kernel<256><<<nc, 256, 0, c->stream>>>(
+                c->d_jobs.as<mb::Job>(), c->d_chunks.as<mb::BandChunk>(), nc, c->d_anchors.as<int32_t>(), q,
+                c->d_geo.as<int2>(), want_kr ? c->d_kr.as<int32_t>() : nullptr, c->d_chunk_sum.as<uint32_t>(),
+                c->d_chunk_maxw.as<int32_t>(), c->d_err.as<int>());
+            mb::band_jobs_kernel<<<(nj + 3) / 4, 128, 0, c->stream>>>(nj, c->d_job_first_chunk.as<int32_t>(),
+                                                                     c->d_chunk_sum.as<uint32_t>(),
+                                                                     c->d_chunk_maxw.as<int32_t>(),
+                                                                     c->d_job_cells.as<int64_t>(), c->d_job_maxw.as<int32_t>());
+            mb::band_bases_kernel<512><<<1, 512, 0, c->stream>>>(c->d_jobs.as<mb::Job>(), nj, c->d_job_cells.as<int64_t>(),
+                                                               c->d_job_maxw.as<int32_t>(), c->d_totals.as<int64_t>());
+            mb::band_apply_kernel<256><<<nc, 256, 0, c->stream>>>(c->d_jobs.as<mb::Job>(), c->d_chunks.as<mb::BandChunk>(), nc,
+                                                                 c->d_chunk_sum.as<uint32_t>(), c->d_geo.as<int2>(),
+                                                                 c->d_kl.as<int32_t>(), c->d_cell_off.as<uint32_t>());
         }
-        c->launches++;
+        c->launches += 4;
         if (with_schedule) {
             const int threads = 128, per_block = threads / 32;
             {
@@ -543,20 +649,27 @@ int run_band(margin_b200_ctx *c, bool dynamic, bool with_schedule, bool want_kr)
                     c->d_job_nseg.as<int32_t>());
             }
             c->launches++;
-            CU(cudaMemcpyAsync(c->job_nseg.data(), c->d_job_nseg.p, nj * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
-            CU(cudaMemcpyAsync(c->segs.data(), c->d_segs.p, (size_t) c->seg_slots * sizeof(mb::Seg), cudaMemcpyDeviceToHost,
-                               c->stream));
+            CU(cudaMemcpyAsync(h + o_nseg, c->d_job_nseg.p, (size_t) nj * 4, cudaMemcpyDeviceToHost, c->stream));
+            if (S) CU(cudaMemcpyAsync(h + o_segs, c->d_segs.p, S * sizeof(mb::Seg), cudaMemcpyDeviceToHost, c->stream));
         }
-        CU(cudaMemcpyAsync(c->job_cells.data(), c->d_job_cells.p, nj * sizeof(int64_t), cudaMemcpyDeviceToHost, c->stream));
-        CU(cudaMemcpyAsync(c->job_maxw.data(), c->d_job_maxw.p, nj * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaMemcpyAsync(h, c->d_totals.p, 8, cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaMemcpyAsync(h + o_cells, c->d_job_cells.p, (size_t) nj * 8, cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaMemcpyAsync(h + o_maxw, c->d_job_maxw.p, (size_t) nj * 4, cudaMemcpyDeviceToHost, c->stream));
     }
-    int err = 0;
-    CU(cudaMemcpyAsync(&err, c->d_err.p, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemcpyAsync(h + o_err, c->d_err.p, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
     CU(cudaGetLastError());
-    if (err)
+    if (*reinterpret_cast<int *>(h + o_err))
         return fail("PAIRWISE_ALIGNMENT_EXCEPTION: Attempt to create diagonal with invalid coordinates "
                     "(anchors inconsistent with the sequence lengths)");
+    c->job_cells.assign(reinterpret_cast<int64_t *>(h + o_cells), reinterpret_cast<int64_t *>(h + o_cells) + nj);
+    c->job_maxw.assign(reinterpret_cast<int32_t *>(h + o_maxw), reinterpret_cast<int32_t *>(h + o_maxw) + nj);
+    c->job_nseg.assign(nj, 0);
+    if (with_schedule && nj) {
+        memcpy(c->job_nseg.data(), h + o_nseg, (size_t) nj * 4);
+        c->segs.resize(S);
+        if (S) memcpy(c->segs.data(), h + o_segs, S * sizeof(mb::Seg));
+    }
     int64_t cells = 0;
     for (int j = 0; j < nj; j++) {
         c->jobs[j].cell_base = cells;
@@ -564,6 +677,7 @@ int run_band(margin_b200_ctx *c, bool dynamic, bool with_schedule, bool want_kr)
         cells += c->job_cells[j];
         if (with_schedule && c->job_nseg[j] > c->jobs[j].max_seg) return fail("internal error: segment bound exceeded");
     }
+    if (nj && cells != *reinterpret_cast<int64_t *>(h)) return fail("internal error: cell totals disagree");
     c->total_cells = cells;
     return 0;
 }
@@ -629,87 +743,97 @@ struct Bins {
     int tile_bwd[4];
 };
 
+// Ascending sort of keys whose low 32 bits (the ids) are already ascending: two stable 16-bit counting passes over
+// the high half.  O(n); a comparison sort of ~10^4 tiles was the largest host cost of a call.
+void sort_keys(std::vector<uint64_t> &k, std::vector<uint64_t> &tmp, std::vector<uint32_t> &cnt) {
+    const size_t n = k.size();
+    if (n < 2) return;
+    tmp.resize(n);
+    for (int pass = 0; pass < 2; pass++) {
+        const int shift = 32 + 16 * pass;
+        cnt.assign(65537, 0);
+        for (size_t i = 0; i < n; i++) cnt[((k[i] >> shift) & 0xffff) + 1]++;
+        for (int b = 0; b < 65536; b++) cnt[b + 1] += cnt[b];
+        for (size_t i = 0; i < n; i++) tmp[cnt[(k[i] >> shift) & 0xffff]++] = k[i];
+        k.swap(tmp);
+    }
+}
+
 int build_bins(margin_b200_ctx *c, bool with_slots, Bins &bins, int force_group) {
     const int nj = (int) c->jobs.size();
-    const int gs[3] = {8, 16, 32};
-    auto grp = [&](int j) { return force_group ? force_group : group_of(c->job_maxw[j]); };
-    std::vector<int32_t> ids;
-    // sequential forward sweeps (whole jobs)
-    std::vector<int32_t> order;
+    const int S = with_slots ? c->total_slots : 0;
+    auto gbin = [&](int j) {
+        const int g = force_group ? force_group : group_of(c->job_maxw[j]);
+        return g == 8 ? 0 : (g == 16 ? 1 : 2);
+    };
+    // sort keys: (lane-group bin ascending, work descending, id ascending) packed into one integer
+    auto key = [](int bin, int work, int id) {
+        return ((uint64_t) bin << 60) | ((uint64_t) (0x0fffffff - std::min(work, 0x0fffffff)) << 32) | (uint32_t) id;
+    };
+    std::vector<uint64_t> &k0 = c->keys[0], &k1 = c->keys[1], &k2 = c->keys[2], &k3 = c->keys[3];
+    k0.clear();
+    k1.clear();
+    k2.clear();
+    k3.clear();
     for (int j = 0; j < nj; j++)
-        if (!with_slots || !job_is_tiled(c, j)) order.push_back(j);
-    std::sort(order.begin(), order.end(), [&](int a, int b) {
-        const int na = c->jobs[a].lx + c->jobs[a].ly, nb = c->jobs[b].lx + c->jobs[b].ly;
-        return na != nb ? na > nb : a < b;
-    });
-    for (int k = 0; k < 3; k++) {
-        bins.seq_fwd[k] = (int) ids.size();
-        for (int j : order)
-            if (grp(j) == gs[k]) ids.push_back(j);
-    }
-    bins.seq_fwd[3] = (int) ids.size();
-    std::vector<int64_t> ring_off, bnd_off;
+        if (!with_slots || !job_is_tiled(c, j)) k0.push_back(key(gbin(j), c->jobs[j].lx + c->jobs[j].ly, j));
     int64_t ring_cells = 0, bnd_cells = 0;
+    // arena layout (16-byte aligned sections): tiles | ring_off | bnd_off | aln_first_slot | ids
+    const size_t o_tiles = 0, o_ring = o_tiles + (((size_t) S + 1) * sizeof(mb::Tile) + 15) / 16 * 16,
+                 o_bnd = o_ring + ((size_t) S + 1) * 8, o_first = o_bnd + ((size_t) S + 1) * 8,
+                 o_ids = o_first + (((size_t) c->n_aln + 1) * 4 + 15) / 16 * 16,
+                 o_end = o_ids + ((size_t) nj + 2 * (size_t) S + 4) * 4;
+    if (c->h_arena.ensure(o_end) || c->d_arena.ensure(o_end)) return 1;
+    char *h = c->h_arena.as<char>();
+    int64_t *ring_off = reinterpret_cast<int64_t *>(h + o_ring), *bnd_off = reinterpret_cast<int64_t *>(h + o_bnd);
     if (with_slots) {
-        const int S = c->total_slots;
-        ring_off.assign((size_t) S + 1, 0);
-        bnd_off.assign((size_t) S + 1, 0);
-        std::vector<int32_t> tl, gn;
-        for (int s = 0; s < S; s++) (job_is_tiled(c, c->tiles[s].job) ? tl : gn).push_back(s);
-        auto by = [&](std::vector<int32_t> &v, bool fwd) {
-            std::sort(v.begin(), v.end(), [&](int a, int b) {
-                const mb::Tile &ta = c->tiles[a], &tb = c->tiles[b];
-                const int wa = fwd ? ta.tb_from - ta.f0 : ta.D - ta.tb_to, wb = fwd ? tb.tb_from - tb.f0 : tb.D - tb.tb_to;
-                return wa != wb ? wa > wb : a < b;
-            });
-        };
-        by(tl, true);
-        for (int k = 0; k < 3; k++) {
-            bins.tile_fwd[k] = (int) ids.size();
-            for (int s : tl)
-                if (grp(c->tiles[s].job) == gs[k]) ids.push_back(s);
+        for (int s = 0; s < S; s++) {
+            const mb::Tile &t = c->tiles[s];
+            const int b = gbin(t.job);
+            if (t.flags & mb::TILE_BND) {
+                k1.push_back(key(b, t.tb_from - t.f0, s));
+                k3.push_back(key(b, t.D - t.tb_to, s));
+                bnd_off[s] = bnd_cells;
+                ring_off[s] = 0;
+                bnd_cells += c->jobs[t.job].ring_w;
+            } else {
+                k2.push_back(key(b, t.D - t.tb_to, s));
+                ring_off[s] = ring_cells;
+                bnd_off[s] = 0;
+                ring_cells += 3 * (int64_t) c->jobs[t.job].ring_w;
+            }
         }
-        bins.tile_fwd[3] = (int) ids.size();
-        by(gn, false);
-        for (int k = 0; k < 3; k++) {
-            bins.gen_bwd[k] = (int) ids.size();
-            for (int s : gn)
-                if (grp(c->tiles[s].job) == gs[k]) ids.push_back(s);
-        }
-        bins.gen_bwd[3] = (int) ids.size();
-        by(tl, false);
-        for (int k = 0; k < 3; k++) {
-            bins.tile_bwd[k] = (int) ids.size();
-            for (int s : tl)
-                if (grp(c->tiles[s].job) == gs[k]) ids.push_back(s);
-        }
-        bins.tile_bwd[3] = (int) ids.size();
-        for (int s : gn) {
-            ring_off[s] = ring_cells;
-            ring_cells += 3 * (int64_t) c->jobs[c->tiles[s].job].ring_w;
-        }
-        for (int s : tl) {
-            bnd_off[s] = bnd_cells;
-            bnd_cells += c->jobs[c->tiles[s].job].ring_w;
-        }
+        ring_off[S] = bnd_off[S] = 0;
+        if (S) memcpy(h + o_tiles, c->tiles.data(), (size_t) S * sizeof(mb::Tile));
+        memcpy(h + o_first, c->aln_first_slot.data(), ((size_t) c->n_aln + 1) * 4);
     }
-    if (c->d_ids.ensure((ids.size() + 1) * sizeof(int32_t))) return 1;
-    if (!ids.empty())
-        CU(cudaMemcpyAsync(c->d_ids.p, ids.data(), ids.size() * sizeof(int32_t), cudaMemcpyHostToDevice, c->stream));
+    int32_t *ids = reinterpret_cast<int32_t *>(h + o_ids);
+    int n_ids = 0;
+    auto emit = [&](std::vector<uint64_t> &k, int *off4) {
+        sort_keys(k, c->key_tmp, c->key_cnt);
+        size_t q = 0;
+        for (int b = 0; b < 3; b++) {
+            off4[b] = n_ids;
+            while (q < k.size() && (int) (k[q] >> 60) == b) ids[n_ids++] = (int32_t) (uint32_t) k[q++];
+        }
+        off4[3] = n_ids;
+    };
+    emit(k0, bins.seq_fwd);
+    emit(k1, bins.tile_fwd);
+    emit(k2, bins.gen_bwd);
+    emit(k3, bins.tile_bwd);
+    CU(cudaMemcpyAsync(c->d_arena.p, h, o_ids + (size_t) n_ids * 4, cudaMemcpyHostToDevice, c->stream));
+    char *dv = c->d_arena.as<char>();
+    c->p_tiles = reinterpret_cast<mb::Tile *>(dv + o_tiles);
+    c->p_ring_off = reinterpret_cast<int64_t *>(dv + o_ring);
+    c->p_bnd_off = reinterpret_cast<int64_t *>(dv + o_bnd);
+    c->p_aln_first_slot = reinterpret_cast<int32_t *>(dv + o_first);
+    c->p_ids = reinterpret_cast<int32_t *>(dv + o_ids);
     if (with_slots) {
-        const size_t S = (size_t) c->total_slots;
-        if (c->d_slot_ring_off.ensure((S + 1) * sizeof(int64_t)) || c->d_slot_bnd_off.ensure((S + 1) * sizeof(int64_t)) ||
-            c->d_ring.ensure((size_t) (ring_cells + 1) * 3 * sizeof(double)) ||
-            c->d_bnd.ensure((size_t) (bnd_cells + 1) * 3 * sizeof(double)) || c->d_tiles.ensure((S + 1) * sizeof(mb::Tile)))
+        if (c->d_ring.ensure((size_t) (ring_cells + 1) * 3 * sizeof(double)) ||
+            c->d_bnd.ensure((size_t) (bnd_cells + 1) * 3 * sizeof(double)))
             return 1;
-        CU(cudaMemcpyAsync(c->d_slot_ring_off.p, ring_off.data(), (S + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, c->stream));
-        CU(cudaMemcpyAsync(c->d_slot_bnd_off.p, bnd_off.data(), (S + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, c->stream));
-        if (S) CU(cudaMemcpyAsync(c->d_tiles.p, c->tiles.data(), S * sizeof(mb::Tile), cudaMemcpyHostToDevice, c->stream));
-        CU(cudaMemcpyAsync(c->d_aln_first_slot.p, c->aln_first_slot.data(), (c->n_aln + 1) * sizeof(int32_t),
-                           cudaMemcpyHostToDevice, c->stream));
     }
-    if (nj) CU(cudaMemcpyAsync(c->d_jobs.p, c->jobs.data(), nj * sizeof(mb::Job), cudaMemcpyHostToDevice, c->stream));
-    CU(cudaStreamSynchronize(c->stream));  // ids / offsets are local pageable vectors
     return 0;
 }
 
@@ -719,7 +843,7 @@ void launch_forward(margin_b200_ctx *c, int off, int count) {
     const int per_block = kFwdThreads / G;
     KTimer kt_(c, K_FORWARD);
     mb::forward_kernel<G, kFwdThreads><<<(count + per_block - 1) / per_block, kFwdThreads, 0, c->stream>>>(
-        c->d_jobs.as<mb::Job>(), c->d_ids.as<int32_t>() + off, count, c->d_models.as<mb::DevModel>(),
+        c->d_jobs.as<mb::Job>(), c->p_ids + off, count, c->d_models.as<mb::DevModel>(),
         c->d_symx.as<uint16_t>(), c->d_symy.as<uint16_t>(), c->d_kl.as<int32_t>(), c->d_cell_off.as<uint32_t>(),
         c->d_F.as<double>());
     c->launches++;
@@ -730,9 +854,9 @@ void launch_forward_tiles2(margin_b200_ctx *c, int off, int count) {
     const int per_block = kTileThreads / G;
     KTimer kt_(c, K_FORWARD);
     mb::forward_tile_kernel<G, kTileThreads, SW><<<(count + per_block - 1) / per_block, kTileThreads, 0, c->stream>>>(
-        c->d_jobs.as<mb::Job>(), c->d_tiles.as<mb::Tile>(), c->d_ids.as<int32_t>() + off, count,
+        c->d_jobs.as<mb::Job>(), c->p_tiles, c->p_ids + off, count,
         c->d_models.as<mb::DevModel>(), c->d_px.as<uint8_t>() + mb::PACK_SLACK, c->d_py.as<uint8_t>() + mb::PACK_SLACK,
-        c->d_geo.as<int2>(), c->d_F.as<double>(), c->d_bnd.as<double>(), c->d_slot_bnd_off.as<int64_t>());
+        c->d_geo.as<int2>(), c->d_F.as<double>(), c->d_bnd.as<double>(), c->p_bnd_off);
     c->launches++;
 }
 
@@ -749,10 +873,10 @@ void launch_backward(margin_b200_ctx *c, int off, int count, int64_t stage_strid
     const int per_block = kBwdThreads / G;
     KTimer kt_(c, K_BACKWARD);
     mb::backward_kernel<G, kBwdThreads, INDELS><<<(count + per_block - 1) / per_block, kBwdThreads, 0, c->stream>>>(
-        c->d_jobs.as<mb::Job>(), c->d_tiles.as<mb::Tile>(), c->d_ids.as<int32_t>() + off, count,
+        c->d_jobs.as<mb::Job>(), c->p_tiles, c->p_ids + off, count,
         c->d_models.as<mb::DevModel>(), c->d_symx.as<uint16_t>(), c->d_symy.as<uint16_t>(), c->d_kl.as<int32_t>(),
         c->d_cell_off.as<uint32_t>(), c->d_F.as<double>(), dev_params(c->params), c->d_ring.as<double>(),
-        c->d_slot_ring_off.as<int64_t>(), c->d_stage.as<mb::Pair>(), stage_stride, c->d_seg_counts.as<int64_t>(),
+        c->p_ring_off, c->d_stage.as<mb::Pair>(), stage_stride, c->d_seg_counts.as<int64_t>(),
         c->total_slots);
     c->launches++;
 }
@@ -762,9 +886,9 @@ void launch_backward_tiles2(margin_b200_ctx *c, int off, int count, int64_t stag
     const int per_block = kTileThreads / G;
     KTimer kt_(c, K_BACKWARD);
     mb::backward_tile_kernel<G, kTileThreads, INDELS, SW><<<(count + per_block - 1) / per_block, kTileThreads, 0, c->stream>>>(
-        c->d_jobs.as<mb::Job>(), c->d_tiles.as<mb::Tile>(), c->d_ids.as<int32_t>() + off, count,
+        c->d_jobs.as<mb::Job>(), c->p_tiles, c->p_ids + off, count,
         c->d_models.as<mb::DevModel>(), c->d_px.as<uint8_t>() + mb::PACK_SLACK, c->d_py.as<uint8_t>() + mb::PACK_SLACK,
-        c->d_geo.as<int2>(), c->d_F.as<double>(), c->d_bnd.as<double>(), c->d_slot_bnd_off.as<int64_t>(), c->v_thr,
+        c->d_geo.as<int2>(), c->d_F.as<double>(), c->d_bnd.as<double>(), c->p_bnd_off, c->v_thr,
         c->d_stage2.as<mb::StagedPair>(), stage_stride, c->d_seg_counts.as<int64_t>(), c->total_slots);
     c->launches++;
 }
@@ -807,11 +931,15 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
     c->force_group = force_group_env();
     const int nj = (int) c->jobs.size();
     const int n_lists = want_indels ? 3 : 1;
+    Trace tr;
     CU(cudaEventRecord(c->ev0, c->stream));
     if (run_band(c, c->params.dynamic_anchor_expansion != 0, true, false)) return 1;
+    tr.mark("band+sync");
     build_tiles(c);
+    tr.mark("tiles");
     Bins bins;
     if (build_bins(c, true, bins, c->force_group)) return 1;
+    tr.mark("bins+h2d+sync");
     const int64_t cells = c->total_cells;
     const int S = c->total_slots;
     const bool any_generic = bins.gen_bwd[3] > bins.gen_bwd[0], any_tiled = bins.tile_bwd[3] > bins.tile_bwd[0];
@@ -857,42 +985,57 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
                                          c->d_seg_off.as<int64_t>(), n_scan, c->stream));
     }
     c->launches++;
-    int64_t bounds[4] = {0, 0, 0, 0};
+    // The list totals are only known on the device at this point.  The output buffer is sized from an estimate
+    // (0.22 tuples per band cell were measured on real data) and the gather refuses to write past it; the totals come
+    // back with the final synchronisation, and an overflow re-runs the gather into an exactly sized buffer.
+    int64_t *bounds = reinterpret_cast<int64_t *>(c->h_small.as<char>());  // pinned; run_band's landing zone is consumed
     for (int l = 0; l < 4; l++)
         CU(cudaMemcpyAsync(&bounds[l], c->d_seg_off.as<int64_t>() + (size_t) l * S, sizeof(int64_t), cudaMemcpyDeviceToHost,
                            c->stream));
-    CU(cudaStreamSynchronize(c->stream));
-    CU(cudaGetLastError());
-    c->total_tuples = bounds[3];
-    for (int l = 0; l < 3; l++) c->list_tuples[l] = bounds[l + 1] - bounds[l];
-    if (c->d_out.ensure((size_t) (c->total_tuples + 1) * sizeof(mb::Pair))) return 1;
-    if (S > 0 && nj > 0 && any_generic) {
-        KTimer kt_(c, K_GATHER);
-        mb::gather_kernel<<<S, 128, 0, c->stream>>>(c->d_jobs.as<mb::Job>(), c->d_tiles.as<mb::Tile>(), S,
-                                                    c->d_cell_off.as<uint32_t>(), c->d_seg_counts.as<int64_t>(),
-                                                    c->d_seg_off.as<int64_t>(), c->d_stage.as<mb::Pair>(), stride,
-                                                    c->d_out.as<mb::Pair>(), n_lists);
-        c->launches++;
-    }
-    if (S > 0 && nj > 0 && any_tiled) {
-        KTimer kt_(c, K_GATHER);
-        mb::gather_staged_kernel<<<S, 128, 0, c->stream>>>(c->d_jobs.as<mb::Job>(), c->d_tiles.as<mb::Tile>(), S,
-                                                           c->d_geo.as<int2>(), c->d_seg_counts.as<int64_t>(),
-                                                           c->d_seg_off.as<int64_t>(), c->d_stage2.as<mb::StagedPair>(),
-                                                           stride, c->d_out.as<mb::Pair>(), n_lists);
-        c->launches++;
-    }
+    const size_t want_cap = (size_t) cells / (want_indels ? 3 : 6) + 4096;
+    if (c->d_out.cap / sizeof(mb::Pair) < want_cap && c->d_out.ensure(want_cap * sizeof(mb::Pair))) return 1;
+    auto run_gather = [&]() {
+        const int64_t cap = (int64_t) (c->d_out.cap / sizeof(mb::Pair));
+        if (S > 0 && nj > 0 && any_generic) {
+            KTimer kt_(c, K_GATHER);
+            mb::gather_kernel<<<S, 128, 0, c->stream>>>(c->d_jobs.as<mb::Job>(), c->p_tiles, S, c->d_cell_off.as<uint32_t>(),
+                                                        c->d_seg_counts.as<int64_t>(), c->d_seg_off.as<int64_t>(),
+                                                        c->d_stage.as<mb::Pair>(), stride, c->d_out.as<mb::Pair>(), n_lists,
+                                                        cap);
+            c->launches++;
+        }
+        if (S > 0 && nj > 0 && any_tiled) {
+            KTimer kt_(c, K_GATHER);
+            mb::gather_staged_kernel<<<S, 128, 0, c->stream>>>(c->d_jobs.as<mb::Job>(), c->p_tiles, S, c->d_geo.as<int2>(),
+                                                               c->d_seg_counts.as<int64_t>(), c->d_seg_off.as<int64_t>(),
+                                                               c->d_stage2.as<mb::StagedPair>(), stride,
+                                                               c->d_out.as<mb::Pair>(), n_lists, cap);
+            c->launches++;
+        }
+    };
+    run_gather();
     {
         const int threads = 128;
         const int blocks = (int) ((c->n_aln + 1 + threads - 1) / threads);
         KTimer kt_(c, K_OFFSETS);
-        mb::list_offsets_kernel<<<blocks, threads, 0, c->stream>>>(c->d_aln_first_slot.as<int32_t>(), (int) c->n_aln, S,
+        mb::list_offsets_kernel<<<blocks, threads, 0, c->stream>>>(c->p_aln_first_slot, (int) c->n_aln, S,
                                                                    c->d_seg_off.as<int64_t>(), c->d_off_out.as<int64_t>());
         c->launches++;
     }
     CU(cudaEventRecord(c->ev1, c->stream));
+    tr.mark("launches");
     CU(cudaStreamSynchronize(c->stream));
     CU(cudaGetLastError());
+    tr.mark("final sync");
+    c->total_tuples = bounds[3];
+    for (int l = 0; l < 3; l++) c->list_tuples[l] = bounds[l + 1] - bounds[l];
+    if ((size_t) c->total_tuples > c->d_out.cap / sizeof(mb::Pair)) {  // estimate too small: exact size, gather again
+        if (c->d_out.ensure((size_t) (c->total_tuples + 1) * sizeof(mb::Pair))) return 1;
+        run_gather();
+        CU(cudaEventRecord(c->ev1, c->stream));
+        CU(cudaStreamSynchronize(c->stream));
+        CU(cudaGetLastError());
+    }
     float ms = 0;
     CU(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
     int64_t segments = 0;

@@ -173,6 +173,256 @@ band_kernel(const Job *__restrict__ jobs, int n_jobs, const int32_t *__restrict_
     }
 }
 
+// ------------------------------------------------------------------------------------- anchor check
+
+// One CTA per alignment: the preconditions band_constructDynamic asserts on the anchors (pairwiseAligner.c:150-158:
+// strictly increasing in x and y, inside the sequences, even expansion) and whether getSplitPoints (:913-965) would
+// cut the alignment (some anchor-free sub-matrix larger than `limit` cells).  status[2*i] = index of the first bad
+// anchor or INT_MAX, status[2*i+1] = 1 when the alignment needs the host's split path.
+__global__ void check_anchors_kernel(const int32_t *__restrict__ anchors, const int64_t *__restrict__ off_a,
+                                     const int64_t *__restrict__ off_x, const int64_t *__restrict__ off_y, int64_t limit,
+                                     int32_t *__restrict__ status) {
+    const int64_t i = blockIdx.x;
+    const int64_t a0 = off_a[i], na = off_a[i + 1] - a0;
+    const int64_t lx = off_x[i + 1] - off_x[i], ly = off_y[i + 1] - off_y[i];
+    const int32_t *anc = anchors + 3 * a0;
+    int bad = 0x7fffffff, split = 0;
+    for (int64_t k = threadIdx.x; k <= na; k += blockDim.x) {
+        const int64_t px = k > 0 ? anc[3 * (k - 1)] : -1, py = k > 0 ? anc[3 * (k - 1) + 1] : -1;
+        int64_t x = lx, y = ly;
+        if (k < na) {
+            x = anc[3 * k];
+            y = anc[3 * k + 1];
+            const int e = anc[3 * k + 2];
+            if (x <= px || y <= py || x < 0 || y < 0 || x >= lx || y >= ly || e < 0 || (e & 1)) bad = min(bad, (int) k);
+        }
+        if ((x - (px + 1)) * (y - (py + 1)) > limit) split = 1;
+    }
+    if (bad != 0x7fffffff) atomicMin(&status[2 * i], bad);
+    if (split) atomicOr(&status[2 * i + 1], 1);
+}
+
+// ------------------------------------------------------------------------------- band, chunk-parallel version
+
+// The same geometry as band_kernel, parallel over chunks of BAND_CHUNK consecutive diagonals of a job (a 20 kb read has
+// ~28 000 diagonals, so one CTA per job leaves most of the GPU idle).  Four launches:
+//   band_chunk_kernel   per chunk: {lowest x, width} of every diagonal, chunk-local exclusive scan of the widths
+//   band_jobs_kernel    per job (one warp): exclusive scan of the chunk sums -> chunk bases, job cells, widest diagonal
+//   band_bases_kernel   one CTA: exclusive scan of the job cells -> Job::cell_base, Job::ring_w, total cells
+//   band_apply_kernel   per chunk: adds the chunk base; writes geo {xlo, cell offset}, kl and cell_off
+constexpr int BAND_CHUNK = 1024;
+
+struct BandChunk {
+    int32_t job;
+    int32_t d0;  // first diagonal of the chunk; the chunk covers d0 .. min(d0 + BAND_CHUNK, N + 2) - 1
+};
+
+// smallest anchor index i in [lo, hi) with (ax+1)+(ay+1) >= d, else hi
+__device__ __forceinline__ int anchor_lower_bound(const int32_t *__restrict__ anc, int lo, int hi, int d) {
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        const int s = __ldg(anc + 3 * mid) + __ldg(anc + 3 * mid + 1) + 2;
+        if (s >= d) hi = mid; else lo = mid + 1;
+    }
+    return lo;
+}
+
+// `lo` = anchor_lower_bound over all anchors of the job for diagonal d
+__device__ __forceinline__ void band_diagonal(const int32_t *__restrict__ anc, int na, int lx, int ly, int d, int lo,
+                                              const Params &p, int &kl, int &kr) {
+    kl = 0;
+    kr = 0;
+    if (d == 0) return;
+    int nx = lx, ny = ly, px = 0, py = 0, e;
+    if (lo < na) {
+        nx = __ldg(anc + 3 * lo) + 1;
+        ny = __ldg(anc + 3 * lo + 1) + 1;
+        e = p.dynamic ? __ldg(anc + 3 * lo + 2) : p.expansion;
+    } else {
+        e = p.dynamic ? (na > 0 ? __ldg(anc + 3 * (na - 1) + 2) : 0) : p.expansion;
+    }
+    if (lo > 0) {
+        px = __ldg(anc + 3 * (lo - 1)) + 1;
+        py = __ldg(anc + 3 * (lo - 1) + 1) + 1;
+    }
+    const int pxay = px + py, pxmy = px - py, nxay = nx + ny, nxmy = nx - ny;
+    const int xL = bound_coord((pxay + pxmy - e) / 2, lx);
+    const int yL = bound_coord((nxay - (nxmy - e)) / 2, ly);
+    const int xU = bound_coord((nxay + nxmy + e) / 2, lx);
+    const int yU = bound_coord((pxay - (pxmy + e)) / 2, ly);
+    clip_diagonal(d, xL, yL, xU, yU, kl, kr);
+}
+
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS)
+band_chunk_kernel(const Job *__restrict__ jobs, const BandChunk *__restrict__ chunks, int n_chunks,
+                  const int32_t *__restrict__ anchors, Params p, int2 *__restrict__ geo, int32_t *__restrict__ kr_out,
+                  uint32_t *__restrict__ chunk_sum, int32_t *__restrict__ chunk_maxw, int *__restrict__ err) {
+    const int ci = blockIdx.x;
+    if (ci >= n_chunks) return;
+    const BandChunk ch = chunks[ci];
+    const Job job = jobs[ch.job];
+    const int lx = job.lx, ly = job.ly, N = lx + ly, na = job.n_anc;
+    const int32_t *anc = anchors + 3 * job.anc_off;
+    const int d_end = min(ch.d0 + BAND_CHUNK, N + 2);
+    __shared__ uint32_t warp_sums[THREADS / 32];
+    __shared__ uint32_t carry_s;
+    __shared__ int maxw_s;
+    // The anchors that can govern this chunk are a contiguous range [a_lo, a_hi]; their anti-diagonals are staged in
+    // shared memory so that the per-diagonal search runs at shared-memory latency.
+    constexpr int CAP = 2048;
+    __shared__ int s_diag[CAP];
+    __shared__ int a_range[2];
+    if (threadIdx.x == 0) {
+        carry_s = 0;
+        maxw_s = 0;
+        a_range[0] = anchor_lower_bound(anc, 0, na, ch.d0);
+    }
+    if (threadIdx.x == 32) a_range[1] = anchor_lower_bound(anc, 0, na, d_end);
+    __syncthreads();
+    const int a_lo = a_range[0], a_cnt = a_range[1] - a_range[0];
+    const bool staged = a_cnt <= CAP;
+    if (staged)
+        for (int k = threadIdx.x; k < a_cnt; k += THREADS)
+            s_diag[k] = __ldg(anc + 3 * (a_lo + k)) + __ldg(anc + 3 * (a_lo + k) + 1) + 2;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    for (int base = ch.d0; base < d_end; base += THREADS) {
+        const int d = base + threadIdx.x;
+        int w = 0, kl = 0, kr = 0;
+        if (d <= N) {
+            int lo_a;
+            if (staged) {
+                int lo = 0, hi = a_cnt;
+                while (lo < hi) {
+                    const int mid = (lo + hi) >> 1;
+                    if (s_diag[mid] >= d) hi = mid; else lo = mid + 1;
+                }
+                lo_a = a_lo + lo;
+            } else {
+                lo_a = anchor_lower_bound(anc, 0, na, d);
+            }
+            band_diagonal(anc, na, lx, ly, d, lo_a, p, kl, kr);
+            w = (kr - kl) / 2 + 1;
+            if (kr < kl) {  // diagonal_construct would throw (pairwiseAligner.c:22-27)
+                atomicExch(err, 1);
+                w = 1;
+            }
+        }
+        uint32_t v = (uint32_t) w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t n = __shfl_up_sync(0xffffffffu, v, o);
+            if (lane >= o) v += n;
+        }
+        if (lane == 31) warp_sums[wid] = v;
+        int mw = w;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) mw = max(mw, __shfl_xor_sync(0xffffffffu, mw, o));
+        if (lane == 0) atomicMax(&maxw_s, mw);
+        __syncthreads();
+        uint32_t pre = carry_s;
+        for (int k = 0; k < wid; k++) pre += warp_sums[k];
+        if (d < d_end) {
+            geo[job.diag_off + d] = make_int2((d + kl) >> 1, (int) (pre + v - (uint32_t) w));
+            if (kr_out) kr_out[job.diag_off + d] = kr;
+        }
+        __syncthreads();
+        if (threadIdx.x == THREADS - 1) carry_s = pre + v;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        chunk_sum[ci] = carry_s;
+        chunk_maxw[ci] = maxw_s;
+    }
+}
+
+// One warp per job; job_first_chunk[j] .. job_first_chunk[j+1] are the job's chunks.
+__global__ void band_jobs_kernel(int n_jobs, const int32_t *__restrict__ job_first_chunk, uint32_t *__restrict__ chunk_sum,
+                                 const int32_t *__restrict__ chunk_maxw, int64_t *__restrict__ job_cells,
+                                 int32_t *__restrict__ job_maxw) {
+    const int j = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (j >= n_jobs) return;
+    const int c0 = job_first_chunk[j], c1 = job_first_chunk[j + 1];
+    uint32_t carry = 0;
+    int mw = 0;
+    for (int base = c0; base < c1; base += 32) {
+        const int c = base + lane;
+        const uint32_t s = c < c1 ? chunk_sum[c] : 0u;
+        if (c < c1) mw = max(mw, chunk_maxw[c]);
+        uint32_t v = s;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t n = __shfl_up_sync(0xffffffffu, v, o);
+            if (lane >= o) v += n;
+        }
+        if (c < c1) chunk_sum[c] = carry + v - s;  // exclusive base of the chunk inside the job
+        carry += __shfl_sync(0xffffffffu, v, 31);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mw = max(mw, __shfl_xor_sync(0xffffffffu, mw, o));
+    if (lane == 0) {
+        job_cells[j] = carry;
+        job_maxw[j] = mw;
+    }
+}
+
+// One CTA: exclusive scan of the job cells; fills the device job table and totals[0] = cells of the batch.
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS)
+band_bases_kernel(Job *__restrict__ jobs, int n_jobs, const int64_t *__restrict__ job_cells,
+                  const int32_t *__restrict__ job_maxw, int64_t *__restrict__ totals) {
+    __shared__ int64_t warp_sums[THREADS / 32];
+    __shared__ int64_t carry_s;
+    if (threadIdx.x == 0) carry_s = 0;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    for (int base = 0; base < n_jobs; base += THREADS) {
+        const int j = base + threadIdx.x;
+        const int64_t s = j < n_jobs ? job_cells[j] : 0;
+        int64_t v = s;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int64_t n = __shfl_up_sync(0xffffffffu, v, o);
+            if (lane >= o) v += n;
+        }
+        if (lane == 31) warp_sums[wid] = v;
+        __syncthreads();
+        int64_t pre = carry_s;
+        for (int k = 0; k < wid; k++) pre += warp_sums[k];
+        if (j < n_jobs) {
+            jobs[j].cell_base = pre + v - s;
+            jobs[j].ring_w = job_maxw[j];
+        }
+        __syncthreads();
+        if (threadIdx.x == THREADS - 1) carry_s = pre + v;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) totals[0] = carry_s;
+}
+
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS)
+band_apply_kernel(const Job *__restrict__ jobs, const BandChunk *__restrict__ chunks, int n_chunks,
+                  const uint32_t *__restrict__ chunk_base, int2 *__restrict__ geo, int32_t *__restrict__ kl_out,
+                  uint32_t *__restrict__ cell_off) {
+    const int ci = blockIdx.x;
+    if (ci >= n_chunks) return;
+    const BandChunk ch = chunks[ci];
+    const Job job = jobs[ch.job];
+    const int N = job.lx + job.ly;
+    const int d_end = min(ch.d0 + BAND_CHUNK, N + 2);
+    const uint32_t base = chunk_base[ci];
+    for (int d = ch.d0 + threadIdx.x; d < d_end; d += THREADS) {
+        int2 g = geo[job.diag_off + d];
+        g.y = (int) ((uint32_t) g.y + base);
+        geo[job.diag_off + d] = g;
+        kl_out[job.diag_off + d] = 2 * g.x - d;
+        cell_off[job.diag_off + d] = (uint32_t) g.y;
+    }
+}
+
 // -------------------------------------------------------------------------------------- schedule
 
 // One warp per job: replays the traceback trigger of getPosteriorProbsWithBanding (pairwiseAligner.c:746-768),
@@ -635,8 +885,9 @@ backward_kernel(const Job *__restrict__ jobs, const Tile *__restrict__ segs, con
 __global__ void gather_kernel(const Job *__restrict__ jobs, const Tile *__restrict__ segs, int total_slots,
                               const uint32_t *__restrict__ cell_off, const int64_t *__restrict__ seg_counts,
                               const int64_t *__restrict__ seg_off, const Pair *__restrict__ stage, int64_t stage_stride,
-                              Pair *__restrict__ out, int n_lists) {
+                              Pair *__restrict__ out, int n_lists, int64_t out_capacity) {
     const int slot = blockIdx.x;
+    if (seg_off[(int64_t) 3 * total_slots] > out_capacity) return;  // the host re-runs with a larger buffer
     const Tile seg = segs[slot];
     if (seg.flags & TILE_BND) return;  // tiled jobs are gathered by gather_staged_kernel
     const Job job = jobs[seg.job];

@@ -420,8 +420,9 @@ backward_tile_kernel(const Job *__restrict__ jobs, const Tile *__restrict__ tile
 __global__ void gather_staged_kernel(const Job *__restrict__ jobs, const Tile *__restrict__ tiles, int total_slots,
                                      const int2 *__restrict__ geo, const int64_t *__restrict__ seg_counts,
                                      const int64_t *__restrict__ seg_off, const StagedPair *__restrict__ stage,
-                                     int64_t stage_stride, Pair *__restrict__ out, int n_lists) {
+                                     int64_t stage_stride, Pair *__restrict__ out, int n_lists, int64_t out_capacity) {
     const int slot = blockIdx.x;
+    if (seg_off[(int64_t) 3 * total_slots] > out_capacity) return;  // the host re-runs with a larger buffer
     const Tile t = tiles[slot];
     if (!(t.flags & TILE_BND)) return;  // sequential-mode jobs are gathered by gather_kernel
     const Job job = jobs[t.job];
