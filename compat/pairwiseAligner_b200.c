@@ -1,0 +1,346 @@
+/*
+ * pairwiseAligner_b200.c — the reference-side binding of libmargin_b200.so.
+ *
+ * This file is compiled AGAINST margin's own headers (inc/margin.h, sonLib) and linked INTO margin in place of the
+ * bodies of five functions; everything else of impl/pairwiseAligner.c and impl/poa.c stays the reference's code:
+ *
+ *   getAlignedPairsWithIndelsUsingAnchors   inc/pairwiseAligner.h:81-84   (impl/pairwiseAligner.c:1144-1171)
+ *   getAlignedPairsUsingAnchors             inc/pairwiseAligner.h:77-79   (impl/pairwiseAligner.c:1125-1142)
+ *   getAlignedPairsWithIndels               inc/pairwiseAligner.h:68-72   (impl/pairwiseAligner.c:1183-1191)
+ *   getAlignedPairs                         inc/pairwiseAligner.h:62-66   (impl/pairwiseAligner.c:1173-1181)
+ *   poa_realign                             inc/margin.h:684              (impl/poa.c:668-716), one batched call per chunk
+ *
+ * Same signatures, same ownership (callee-allocated stLists of individually allocated stIntTuples with
+ * stIntTuple_destruct as destructor), same list order, same error behaviour (invalid band ->
+ * PAIRWISE_ALIGNMENT_EXCEPTION_ID exception; anything else st_errAbort).  Thread model as in the reference: called
+ * concurrently from OpenMP threads (polish.c:476); every thread owns one library context on device
+ * (thread number % device count).  All computation happens in libmargin_b200.so on the GPU; there is no CPU fallback.
+ *
+ * See INTEGRATION.md for how it is linked (oracle/Makefile builds oracle/_ref/margin_b200cli this way for the
+ * end-to-end parity test).
+ */
+#include <omp.h>
+
+#include "margin.h"
+#include "margin_b200.h"
+
+/* Private layouts of impl/stateMachine.c (:507-519, :716-720), re-declared to flatten a StateMachine
+ * (the reference offers no accessor). */
+typedef struct {
+    StateMachine model;
+    double TRANSITION_MATCH_CONTINUE;
+    double TRANSITION_MATCH_FROM_GAP_X;
+    double TRANSITION_MATCH_FROM_GAP_Y;
+    double TRANSITION_GAP_OPEN_X;
+    double TRANSITION_GAP_OPEN_Y;
+    double TRANSITION_GAP_EXTEND_X;
+    double TRANSITION_GAP_EXTEND_Y;
+    double TRANSITION_GAP_SWITCH_TO_X;
+    double TRANSITION_GAP_SWITCH_TO_Y;
+} B200StateMachine3;
+
+typedef struct {
+    NucleotideEmissions ne;
+    RepeatSubMatrix *repeatSubMatrix;
+    bool strand;
+} B200RleNucleotideEmissions;
+
+typedef struct {
+    margin_b200_ctx *ctx;
+    StateMachine *sm[2];                 /* machines currently loaded in slots 0 / 1 */
+    PairwiseAlignmentParameters params;  /* parameters currently loaded */
+    int haveParams;
+    margin_b200_model scratch;
+} B200Thread;
+
+static __thread B200Thread tls;
+
+static void b200_fail(void) {
+    const char *msg = margin_b200_last_error();
+    if (strstr(msg, "PAIRWISE_ALIGNMENT_EXCEPTION") != NULL) {
+        stThrowNew(PAIRWISE_ALIGNMENT_EXCEPTION_ID, "%s", msg);
+    }
+    st_errAbort("margin_b200: %s\n", msg);
+}
+
+static margin_b200_ctx *b200_ctx(void) {
+    if (tls.ctx == NULL) {
+        int n = margin_b200_device_count();
+        if (n <= 0) st_errAbort("margin_b200: no CUDA device; this build of margin has no CPU aligner\n");
+        if (margin_b200_create(&tls.ctx, omp_get_thread_num() % n) != 0) b200_fail();
+    }
+    return tls.ctx;
+}
+
+/* RLE emissions are recognised by probing: only getRleNucleotideMatchProb looks at the run-length byte. */
+static int b200_is_rle(StateMachine *sM) {
+    Emissions *e = sM->emissions;
+    return e->emission(e, (Symbol) ((1 << 8) | 0), (Symbol) ((1 << 8) | 0)) !=
+           e->emission(e, (Symbol) ((2 << 8) | 0), (Symbol) ((1 << 8) | 0));
+}
+
+static void b200_load_machine(int slot, StateMachine *sM) {
+    if (tls.sm[slot] == sM) return;
+    if (sM->type != threeState && sM->type != threeStateAsymmetric) st_errAbort("margin_b200: unsupported state machine\n");
+    B200StateMachine3 *s = (B200StateMachine3 *) sM;
+    margin_b200_model *m = &tls.scratch;
+    memset(m, 0, sizeof(*m));
+    m->t[MB_T_MATCH_CONTINUE] = s->TRANSITION_MATCH_CONTINUE;
+    m->t[MB_T_MATCH_FROM_GAP_X] = s->TRANSITION_MATCH_FROM_GAP_X;
+    m->t[MB_T_MATCH_FROM_GAP_Y] = s->TRANSITION_MATCH_FROM_GAP_Y;
+    m->t[MB_T_GAP_OPEN_X] = s->TRANSITION_GAP_OPEN_X;
+    m->t[MB_T_GAP_EXTEND_X] = s->TRANSITION_GAP_EXTEND_X;
+    m->t[MB_T_GAP_SWITCH_TO_X] = s->TRANSITION_GAP_SWITCH_TO_X;
+    m->t[MB_T_GAP_OPEN_Y] = s->TRANSITION_GAP_OPEN_Y;
+    m->t[MB_T_GAP_EXTEND_Y] = s->TRANSITION_GAP_EXTEND_Y;
+    m->t[MB_T_GAP_SWITCH_TO_Y] = s->TRANSITION_GAP_SWITCH_TO_Y;
+    NucleotideEmissions *ne = (NucleotideEmissions *) sM->emissions;
+    memcpy(m->match, ne->EMISSION_MATCH_PROBS, sizeof(m->match));
+    memcpy(m->gap_x, ne->EMISSION_GAP_X_PROBS, sizeof(m->gap_x));
+    memcpy(m->gap_y, ne->EMISSION_GAP_Y_PROBS, sizeof(m->gap_y));
+    m->rle = b200_is_rle(sM);
+    m->max_rl = MARGIN_B200_MAX_RL;
+    if (m->rle) {
+        B200RleNucleotideEmissions *re = (B200RleNucleotideEmissions *) sM->emissions;
+        RepeatSubMatrix *r = re->repeatSubMatrix;
+        if (r->maximumRepeatLength != MARGIN_B200_MAX_RL) st_errAbort("margin_b200: repeat matrix must be 51 x 51\n");
+        int64_t sq = r->maximumRepeatLength * r->maximumRepeatLength;
+        for (int64_t b = 0; b < 4; b++) { /* repeatSubMatrix_setLogProb index, impl/repeatSubMatrix.c:28-31 */
+            memcpy(m->rsm + b * sq, r->logProbabilities + (re->strand ? b : 3 - b) * sq, sizeof(double) * sq);
+        }
+    }
+    if (margin_b200_set_model(b200_ctx(), slot, m) != 0) b200_fail();
+    tls.sm[slot] = sM;
+}
+
+static void b200_load_params(PairwiseAlignmentParameters *p) {
+    if (tls.haveParams && tls.params.threshold == p->threshold &&
+        tls.params.minDiagsBetweenTraceBack == p->minDiagsBetweenTraceBack &&
+        tls.params.traceBackDiagonals == p->traceBackDiagonals && tls.params.diagonalExpansion == p->diagonalExpansion &&
+        tls.params.splitMatrixBiggerThanThis == p->splitMatrixBiggerThanThis &&
+        tls.params.dynamicAnchorExpansion == p->dynamicAnchorExpansion)
+        return;
+    margin_b200_params q;
+    memset(&q, 0, sizeof(q));
+    q.threshold = p->threshold;
+    q.min_diags_between_traceback = p->minDiagsBetweenTraceBack;
+    q.traceback_diagonals = p->traceBackDiagonals;
+    q.diagonal_expansion = p->diagonalExpansion;
+    q.split_matrix_bigger_than_this = p->splitMatrixBiggerThanThis;
+    q.dynamic_anchor_expansion = p->dynamicAnchorExpansion;
+    if (margin_b200_set_params(b200_ctx(), &q) != 0) b200_fail();
+    tls.params = *p;
+    tls.haveParams = 1;
+}
+
+/* ------------------------------------------------------------------------------------------------ batches */
+
+typedef struct {
+    int64_t n, capX, capY, capA;
+    uint16_t *symX, *symY;
+    int32_t *anchors;
+    int64_t *offX, *offY, *offA;
+    uint8_t *slot, *raggedL, *raggedR;
+} B200Batch;
+
+static B200Batch *b200_batch_construct(int64_t n) {
+    B200Batch *b = st_calloc(1, sizeof(B200Batch));
+    b->offX = st_calloc(n + 1, sizeof(int64_t));
+    b->offY = st_calloc(n + 1, sizeof(int64_t));
+    b->offA = st_calloc(n + 1, sizeof(int64_t));
+    b->slot = st_calloc(n + 1, 1);
+    b->raggedL = st_calloc(n + 1, 1);
+    b->raggedR = st_calloc(n + 1, 1);
+    return b;
+}
+
+static void b200_batch_destruct(B200Batch *b) {
+    free(b->symX);
+    free(b->symY);
+    free(b->anchors);
+    free(b->offX);
+    free(b->offY);
+    free(b->offA);
+    free(b->slot);
+    free(b->raggedL);
+    free(b->raggedR);
+    free(b);
+}
+
+/* Appends one alignment; anchor x coordinates are shifted by -shiftX (the crop of impl/poa.c:637-639). */
+static void b200_batch_add(B200Batch *b, SymbolString sX, SymbolString sY, stList *anchorPairs, int64_t shiftX, int slot,
+                           bool raggedL, bool raggedR) {
+    int64_t i = b->n++;
+    int64_t nA = anchorPairs == NULL ? 0 : stList_length(anchorPairs);
+    int64_t oX = b->offX[i], oY = b->offY[i], oA = b->offA[i];
+    if (oX + sX.length > b->capX) {
+        b->capX = (oX + sX.length) * 2 + 1024;
+        b->symX = st_realloc(b->symX, b->capX * sizeof(uint16_t));
+    }
+    if (oY + sY.length > b->capY) {
+        b->capY = (oY + sY.length) * 2 + 1024;
+        b->symY = st_realloc(b->symY, b->capY * sizeof(uint16_t));
+    }
+    if (oA + nA > b->capA) {
+        b->capA = (oA + nA) * 2 + 1024;
+        b->anchors = st_realloc(b->anchors, b->capA * 3 * sizeof(int32_t));
+    }
+    memcpy(b->symX + oX, sX.sequence, sX.length * sizeof(uint16_t)); /* Symbol is uint16_t, inc/stateMachine.h:15 */
+    memcpy(b->symY + oY, sY.sequence, sY.length * sizeof(uint16_t));
+    for (int64_t k = 0; k < nA; k++) {
+        stIntTuple *a = stList_get(anchorPairs, k);
+        b->anchors[3 * (oA + k)] = (int32_t) (stIntTuple_get(a, 0) - shiftX);
+        b->anchors[3 * (oA + k) + 1] = (int32_t) stIntTuple_get(a, 1);
+        /* anchors may come as pairs (x, y): band_construct then uses p->diagonalExpansion and never reads a third field */
+        b->anchors[3 * (oA + k) + 2] =
+                (tls.params.dynamicAnchorExpansion && stIntTuple_length(a) > 2) ? (int32_t) stIntTuple_get(a, 2) : 0;
+    }
+    b->offX[i + 1] = oX + sX.length;
+    b->offY[i + 1] = oY + sY.length;
+    b->offA[i + 1] = oA + nA;
+    b->slot[i] = (uint8_t) slot;
+    b->raggedL[i] = raggedL;
+    b->raggedR[i] = raggedR;
+}
+
+static void b200_batch_run(B200Batch *b, int wantIndels, margin_b200_result *res) {
+    margin_b200_batch mb;
+    uint16_t dummyS = 0;
+    int32_t dummyA[3] = {0, 0, 0};
+    mb.n = b->n;
+    mb.sym_x = b->symX ? b->symX : &dummyS;
+    mb.off_x = b->offX;
+    mb.sym_y = b->symY ? b->symY : &dummyS;
+    mb.off_y = b->offY;
+    mb.anchors = b->anchors ? b->anchors : dummyA;
+    mb.off_a = b->offA;
+    mb.model_slot = b->slot;
+    mb.ragged_left = b->raggedL;
+    mb.ragged_right = b->raggedR;
+    if (margin_b200_posteriors_batch(b200_ctx(), &mb, wantIndels, res) != 0) b200_fail();
+}
+
+/* List l of alignment i as an stList of stIntTuple(weight, x + shiftX, y), the reference's own representation. */
+static stList *b200_list(const margin_b200_result *res, int l, int64_t i, int64_t shiftX) {
+    stList *out = stList_construct3(0, (void (*)(void *)) stIntTuple_destruct);
+    const margin_b200_pair *p = res->pairs[l];
+    for (int64_t k = res->off[l][i]; k < res->off[l][i + 1]; k++) {
+        stList_append(out, stIntTuple_construct3(p[k].w, (int64_t) p[k].x + shiftX, p[k].y));
+    }
+    return out;
+}
+
+/* ------------------------------------------------------------------- inc/pairwiseAligner.h entry points */
+
+void getAlignedPairsWithIndelsUsingAnchors(StateMachine *sM, SymbolString sX, SymbolString sY, stList *anchorPairs,
+                                           PairwiseAlignmentParameters *p, stList **alignedPairs, stList **gapXPairs,
+                                           stList **gapYPairs, bool alignmentHasRaggedLeftEnd,
+                                           bool alignmentHasRaggedRightEnd) {
+    b200_load_machine(0, sM);
+    b200_load_params(p);
+    B200Batch *b = b200_batch_construct(1);
+    b200_batch_add(b, sX, sY, anchorPairs, 0, 0, alignmentHasRaggedLeftEnd, alignmentHasRaggedRightEnd);
+    margin_b200_result res;
+    b200_batch_run(b, 1, &res);
+    *alignedPairs = b200_list(&res, 0, 0, 0);
+    *gapXPairs = b200_list(&res, 1, 0, 0);
+    *gapYPairs = b200_list(&res, 2, 0, 0);
+    b200_batch_destruct(b);
+}
+
+stList *getAlignedPairsUsingAnchors(StateMachine *sM, SymbolString sX, SymbolString sY, stList *anchorPairs,
+                                    PairwiseAlignmentParameters *p, bool alignmentHasRaggedLeftEnd,
+                                    bool alignmentHasRaggedRightEnd) {
+    b200_load_machine(0, sM);
+    b200_load_params(p);
+    B200Batch *b = b200_batch_construct(1);
+    b200_batch_add(b, sX, sY, anchorPairs, 0, 0, alignmentHasRaggedLeftEnd, alignmentHasRaggedRightEnd);
+    margin_b200_result res;
+    b200_batch_run(b, 0, &res);
+    stList *alignedPairs = b200_list(&res, 0, 0, 0);
+    b200_batch_destruct(b);
+    return alignedPairs;
+}
+
+stList *getAlignedPairs(StateMachine *sM, SymbolString sX, SymbolString sY, PairwiseAlignmentParameters *p,
+                        bool alignmentHasRaggedLeftEnd, bool alignmentHasRaggedRightEnd) {
+    return getAlignedPairsUsingAnchors(sM, sX, sY, NULL, p, alignmentHasRaggedLeftEnd, alignmentHasRaggedRightEnd);
+}
+
+void getAlignedPairsWithIndels(StateMachine *sM, SymbolString sX, SymbolString sY, PairwiseAlignmentParameters *p,
+                               stList **alignedPairs, stList **gapXPairs, stList **gapYPairs,
+                               bool alignmentHasRaggedLeftEnd, bool alignmentHasRaggedRightEnd) {
+    getAlignedPairsWithIndelsUsingAnchors(sM, sX, sY, NULL, p, alignedPairs, gapXPairs, gapYPairs,
+                                          alignmentHasRaggedLeftEnd, alignmentHasRaggedRightEnd);
+}
+
+/* ----------------------------------------------------------------------------- impl/poa.c:668-716, batched */
+
+/*
+ * poa_realign with ONE aligner call per chunk instead of one per read: pass 1 prepares every read exactly as
+ * getAlignedPairsWithIndelsCroppingReference does (impl/poa.c:612-666: crop the reference to the anchored span,
+ * shift the anchors, build both SymbolStrings, pick the strand's state machine), the batch runs on the GPU, pass 2
+ * hands each read's three lists to poa_augment in read order (matches, inserts <- gapY, deletes <- gapX, x shifted
+ * back by the crop).
+ */
+Poa *poa_realign(stList *bamChunkReads, stList *anchorAlignments, RleString *reference, PolishParams *polishParams) {
+    uint64_t maximumRepeatLength = 2; /* MRL is exclusive */
+    if (polishParams->useRunLengthEncoding) {
+        maximumRepeatLength = polishParams->repeatSubMatrix != NULL ? polishParams->repeatSubMatrix->maximumRepeatLength
+                                                                    : MAXIMUM_REPEAT_LENGTH;
+    }
+    Poa *poa = poa_getReferenceGraph(reference, polishParams->alphabet, maximumRepeatLength);
+    int64_t n = stList_length(bamChunkReads);
+    if (n == 0) return poa;
+
+    b200_load_machine(0, polishParams->stateMachineForForwardStrandRead);
+    b200_load_machine(1, polishParams->stateMachineForReverseStrandRead);
+    b200_load_params(polishParams->p);
+
+    B200Batch *b = b200_batch_construct(n);
+    int64_t *firstRefPositions = st_calloc(n, sizeof(int64_t));
+    for (int64_t i = 0; i < n; i++) {
+        BamChunkRead *chunkRead = stList_get(bamChunkReads, i);
+        RleString *read = chunkRead->rleRead;
+        stList *anchorPairs = anchorAlignments == NULL ? NULL : stList_get(anchorAlignments, i);
+        int64_t firstRefPosition = 0, endRefPosition = reference->length;
+        uint64_t maxRL = poa->maxRepeatCount - 1; /* the anchor-less branch, impl/poa.c:688-691 */
+        if (anchorAlignments != NULL) {
+            if (stList_length(anchorPairs) > 0) { /* impl/poa.c:621-633 */
+                stIntTuple *fPair = stList_get(anchorPairs, 0);
+                firstRefPosition = stIntTuple_get(fPair, 0) - stIntTuple_get(fPair, 1);
+                firstRefPosition = firstRefPosition < 0 ? 0 : firstRefPosition;
+                stIntTuple *lPair = stList_peek(anchorPairs);
+                endRefPosition = 1 + stIntTuple_get(lPair, 0) + (read->length - stIntTuple_get(lPair, 1));
+                endRefPosition = endRefPosition > reference->length ? reference->length : endRefPosition;
+            }
+            maxRL = polishParams->useRunLengthEncoding ? (uint64_t) polishParams->repeatSubMatrix->maximumRepeatLength : 2;
+        }
+        SymbolString sX = rleString_constructSymbolString(reference, firstRefPosition, endRefPosition - firstRefPosition,
+                                                          polishParams->alphabet,
+                                                          polishParams->useRepeatCountsInAlignment, maxRL);
+        SymbolString sY = rleString_constructSymbolString(read, 0, read->length, polishParams->alphabet,
+                                                          polishParams->useRepeatCountsInAlignment, maxRL);
+        b200_batch_add(b, sX, sY, anchorPairs, firstRefPosition, chunkRead->forwardStrand ? 0 : 1, 0, 0);
+        symbolString_destruct(sX);
+        symbolString_destruct(sY);
+        firstRefPositions[i] = firstRefPosition;
+    }
+
+    margin_b200_result res;
+    b200_batch_run(b, 1, &res);
+
+    for (int64_t i = 0; i < n; i++) {
+        BamChunkRead *chunkRead = stList_get(bamChunkReads, i);
+        stList *matches = b200_list(&res, 0, i, firstRefPositions[i]);
+        stList *deletes = b200_list(&res, 1, i, firstRefPositions[i]); /* gapX: reference base without read base */
+        stList *inserts = b200_list(&res, 2, i, firstRefPositions[i]); /* gapY */
+        poa_augment(poa, chunkRead->rleRead, chunkRead->forwardStrand, i, matches, inserts, deletes, polishParams);
+        stList_destruct(matches);
+        stList_destruct(inserts);
+        stList_destruct(deletes);
+    }
+    free(firstRefPositions);
+    b200_batch_destruct(b);
+    return poa;
+}

@@ -126,6 +126,7 @@ typedef struct margin_b200_ctx margin_b200_ctx;
 /* All functions return 0 on success, non-zero on error; the message is
  * available from margin_b200_last_error().  There is no CPU fallback: a call
  * without a usable CUDA device fails. */
+int margin_b200_device_count(void); /* usable CUDA devices (0 when there is none) */
 int margin_b200_create(margin_b200_ctx **ctx, int device);
 void margin_b200_destroy(margin_b200_ctx *ctx);
 const char *margin_b200_last_error(void);

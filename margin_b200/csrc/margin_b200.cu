@@ -200,6 +200,12 @@ const char *margin_b200_last_error(void) { return g_err.c_str(); }
 
 int margin_b200_version(void) { return 100; }
 
+int margin_b200_device_count(void) {
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess) return 0;
+    return count;
+}
+
 int margin_b200_create(margin_b200_ctx **out, int device) {
     if (!out) return fail("margin_b200_create: null output pointer");
     *out = nullptr;

@@ -1,0 +1,51 @@
+"""End-to-end drop-in check (SURVEY.md §8 C-4 iv): the reference's own `margin polish` CLI, with the five functions of
+compat/pairwiseAligner_b200.c linked in place of the reference's (oracle/Makefile target `polish`), must write a
+polished FASTA that is byte-identical to the unmodified reference's on the bundled ONT region
+(tests/data/realData/HG002.r94g360.chr20_59M_100k.bam, r94-g360 params).  The expected digest was produced here by
+oracle/_ref/margin_ref (the unmodified reference, 44 s on 8 cores) and equals the one recorded in SURVEY.md §6."""
+import hashlib
+import os
+import subprocess
+import time
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF = os.path.join(ROOT, "oracle", "_ref")
+EXPECTED_FASTA_MD5 = "7feefc269d7d43b18c387a21b23e1ef5"
+
+
+def _polish(binary, out_prefix, threads, env=None):
+    data = os.path.join(REF, "data")
+    cmd = [os.path.join(REF, binary), "polish", os.path.join(data, "HG002.r94g360.chr20_59M_100k.bam"),
+           os.path.join(data, "hg38.chr20_59M_100k.fa"),
+           os.path.join(data, "params", "polish", "ont", "r9.4", "allParams.np.human.r94-g360.json"),
+           "-t", str(threads), "-o", out_prefix, "-a", "info"]
+    t0 = time.time()
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=env, timeout=1500)
+    dt = time.time() - t0
+    assert r.returncode == 0, r.stdout[-3000:]
+    with open(out_prefix + ".fa", "rb") as fh:
+        return hashlib.md5(fh.read()).hexdigest(), dt, r.stdout
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode", ["tiles", "sequential"])
+def test_margin_polish_with_b200_aligner_is_byte_identical(tmp_path, mode):
+    if not os.path.exists(os.path.join(REF, "margin_b200cli")):
+        pytest.skip("oracle/_ref/margin_b200cli not built (needs /root/reference at build time)")
+    env = dict(os.environ, MARGIN_B200_MODE=mode)
+    md5, dt, log = _polish("margin_b200cli", str(tmp_path / "b200"), 2, env)
+    stages = [l.strip() for l in log.splitlines() if "Took" in l]
+    print("margin_b200cli (%s): %.1f s wall\n%s" % (mode, dt, "\n".join(stages[:12])))
+    assert md5 == EXPECTED_FASTA_MD5
+
+
+def test_reference_cli_reproduces_expected_digest(tmp_path):
+    """CPU: the unmodified reference built by oracle/Makefile writes the expected FASTA (pins the digest itself)."""
+    if not os.path.exists(os.path.join(REF, "margin_ref")):
+        pytest.skip("oracle/_ref/margin_ref not built")
+    if os.environ.get("MARGIN_B200_SLOW_TESTS") != "1":
+        pytest.skip("44 s of CPU; set MARGIN_B200_SLOW_TESTS=1")
+    md5, dt, _ = _polish("margin_ref", str(tmp_path / "ref"), 8)
+    assert md5 == EXPECTED_FASTA_MD5
