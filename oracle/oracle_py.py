@@ -24,6 +24,8 @@ def build(ref=True):
     subprocess.check_call(["make", "-s", "-C", HERE, "oracle"])
     if ref and os.path.isdir("/root/reference"):
         subprocess.check_call(["make", "-s", "-j8", "-C", HERE, "ref"])
+        # the reference CLI, with and without compat/pairwiseAligner_b200.c, + the bundled region (end-to-end test)
+        subprocess.check_call(["make", "-s", "-j8", "-C", HERE, "polish"])
 
 
 class Lists(C.Structure):
