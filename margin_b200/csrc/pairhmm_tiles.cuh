@@ -25,10 +25,21 @@
 #pragma once
 #include "pairhmm_kernels.cuh"
 
+#ifndef MB_TOTAL_ON
+#define MB_TOTAL_ON true
+#endif
 namespace mb {
 
 constexpr int PACK_STRIDE = 5 * MARGIN_B200_MAX_RL;  // 255 packed symbol values
 constexpr int PACK_SLACK = 64;                       // zeroed bytes in front of and behind the packed arrays
+constexpr int FAR_X = 0x40000000;                    // an x no band window contains
+
+// threadIdx.x read once (ptxas otherwise re-reads the special register inside the loops)
+__device__ __forceinline__ int tid_x_once() {
+    int v;
+    asm volatile("mov.u32 %0, %%tid.x;" : "=r"(v));
+    return v;
+}
 
 // uint16 Symbol -> packed byte.  rle: base = low 8 bits, run length = high 8 bits (impl/stateMachine.c:116-131);
 // otherwise the whole symbol is the base (anything >= 4 is ambiguous) and the run length slot is 0.
@@ -57,8 +68,10 @@ template <int G>
 __device__ __forceinline__ double shfl_g(double v, int src) { return __shfl_sync(0xffffffffu, v, src, G); }
 
 struct TileShared {
+    double lac[16];       // lookup() pieces, one 32-byte row {c3, c2, c1, c0} per piece (pairwiseAligner.c:282-293)
+    double gx[2][5][4];   // [model][base] {M->X, X->X, Y->X, 0}: the reference's (eP + tP) of the gap-X transitions
+    double gy[2][5][4];   // [model][base] {M->Y, Y->Y, X->Y, 0}
     DevModel model[2];
-    double lac[16];
 };
 
 template <int THREADS>
@@ -66,7 +79,55 @@ __device__ __forceinline__ void tile_shared_init(TileShared &s, const DevModel *
     for (int i = threadIdx.x; i < (int) (2 * sizeof(DevModel) / 8); i += THREADS)
         reinterpret_cast<double *>(s.model)[i] = reinterpret_cast<const double *>(models)[i];
     if (threadIdx.x < 16) s.lac[threadIdx.x] = LA_COEF[threadIdx.x];
+    if (threadIdx.x < 40) {
+        const int k = threadIdx.x & 3, b = (threadIdx.x >> 2) % 5, md = threadIdx.x / 20;
+        s.gx[md][b][k] = k < 3 ? models[md].ex_t[b][k] : 0.0;
+        s.gy[md][b][k] = k < 3 ? models[md].ey_t[b][k] : 0.0;
+    }
     __syncthreads();
+}
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t) __cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ double2 lds_f64x2(uint32_t a) {
+    double2 v;
+    asm("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "r"(a));
+    return v;
+}
+
+__device__ __forceinline__ double lds_f64(uint32_t a) {
+    double v;
+    asm("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(a));
+    return v;
+}
+
+// logAdd (pairwiseAligner.c:279-299) for the tile kernels, operation-for-operation the arithmetic of logadd():
+//   |x - y| is the reference's (max - min) bit for bit, so the difference is formed first and the hi/lo selects run
+//   beside the polynomial instead of in front of it; the piece is chosen by a three-deep select of the row offset
+//   (d > 1, d > 2.5, d > 4.5); lo == -inf gives d = +inf (or NaN when both are -inf), "d < 7.5" fails and hi comes out.
+// lac_s = shared-space address of TileShared::lac.
+__device__ __forceinline__ double logadd_t(double x, double y, uint32_t lac_s) {
+    const double ds = dadd(x, -y);
+    const bool lt = __double2hiint(ds) < 0;
+    const double hi = lt ? y : x;
+    const double lo = lt ? x : y;
+    const double d = fabs(ds);
+    uint32_t row;
+    asm("{\n\t.reg .pred p1, p2, p3;\n\t"
+        "setp.gt.f64 p1, %1, 0d3FF0000000000000;\n\t"
+        "setp.gt.f64 p2, %1, 0d4004000000000000;\n\t"
+        "setp.gt.f64 p3, %1, 0d4012000000000000;\n\t"
+        "selp.u32 %0, 32, 0, p1;\n\t"
+        "selp.u32 %0, 64, %0, p2;\n\t"
+        "selp.u32 %0, 96, %0, p3;\n\t}"
+        : "=r"(row) : "d"(d));
+    const double2 c32 = lds_f64x2(lac_s + row);
+    const double2 c10 = lds_f64x2(lac_s + row + 16);
+    double v = dadd(dmul(c32.x, d), c32.y);
+    v = dadd(dmul(v, d), c10.x);
+    v = dadd(dmul(v, d), c10.y);
+    v = dadd(v, lo);
+    return (d < 7.5) ? v : hi;
 }
 
 // A staged posterior: the log posterior v = F + B - total of a cell state that passes the threshold; the gather
@@ -77,113 +138,140 @@ struct StagedPair {
 };
 
 // ------------------------------------------------------------------------------------------------ forward tile
+//
+// Register software pipeline, period 4 (the loop body is four diagonals, so no value is ever moved between
+// registers): ring g[] holds the geometry of d .. d+3, the symbols of d+2 are fetched while d is computed, the
+// match emission and the gap-table rows of d+1 are fetched from the symbols loaded one step earlier.
+// A lane that is outside its diagonal keeps -inf, so a neighbour is valid exactly when its x lies in the G-wide
+// window of the lane mapping of its diagonal, and the select is applied once per target state (all sources of a
+// state come from the same neighbour cell).
 template <int G, int THREADS, bool SWITCH>
-__global__ void __launch_bounds__(THREADS)
+__global__ void __launch_bounds__(THREADS, 5)
 forward_tile_kernel(const Job *__restrict__ jobs, const Tile *__restrict__ tiles, const int32_t *__restrict__ ids,
                     int n_ids, const DevModel *__restrict__ models, const uint8_t *__restrict__ px,
                     const uint8_t *__restrict__ py, const int2 *__restrict__ geo, double *__restrict__ F,
                     double *__restrict__ Fbnd, const int64_t *__restrict__ slot_bnd_off) {
     __shared__ __align__(16) TileShared sh;
     tile_shared_init<THREADS>(sh, models);
-    const int g = (blockIdx.x * THREADS + threadIdx.x) / G;
+    const int tid = tid_x_once();
+    const int g = (blockIdx.x * THREADS + tid) / G;
     const bool real = g < n_ids;  // groups past the end shadow the last tile and store nothing
-    const int lane = threadIdx.x & (G - 1);
+    const int lane = tid & (G - 1);
     const int prev_lane = mod_g(lane - 1, G);
     const int slot = ids[min(g, n_ids - 1)];
     const Tile t = tiles[slot];
     const Job job = jobs[t.job];
     const DevModel &m = sh.model[job.slot];
-    const double *lac = sh.lac;
+    const uint32_t lac_s = smem_u32(sh.lac);
+    const uint32_t gx_s = smem_u32(&sh.gx[job.slot][0][0]), gy_s = smem_u32(&sh.gy[job.slot][0][0]);
     const int N = job.lx + job.ly;
-    const uint8_t *sx = px + job.symx_off, *sy = py + job.symy_off;
+    const uint8_t *sx = px + job.symx_off - 1, *sy = py + job.symy_off - 1;  // sx[x] = symbol of column x (1-based)
     const int2 *gj = geo + job.diag_off;
     double *Fj = F + 3 * job.cell_base;
     double *bnd = Fbnd + 3 * slot_bnd_off[slot];
     const double *emP = m.emit_packed;
     const double tMM = m.t[T_MM], tXM = m.t[T_XM], tYM = m.t[T_YM];
+    const int d0 = t.f0 + 1;  // first diagonal of the loop
+    const int tb_to = t.tb_to;
 
     // ---- diagonal f0: the true start state (stateMachine.c:521-530) or a flat state for the warm-up
-    int d = t.f0;
-    const int2 g0 = __ldg(gj + d), g1 = __ldg(gj + d + 1);
-    int xlo1 = g0.x, w1 = g1.y - g0.y, xlo2 = 0, w2 = 0;
-    Cell f1 = cell_neg_inf(), mid = cell_neg_inf();
+    int xlo1, xlo2 = -2 * G;  // nothing on "diagonal f0 - 1" is ever valid
+    Cell f1 = cell_neg_inf();
+    double midm = MB_NEG_INF, midx = MB_NEG_INF, midy = MB_NEG_INF;
     {
-        const int x = xlo1 + mod_g(lane - xlo1, G);
-        if (x < xlo1 + w1) {
-            if (d == 0) {
+        const int2 ga = __ldg(gj + t.f0), gb = __ldg(gj + t.f0 + 1);
+        xlo1 = ga.x;
+        const int r = mod_g(lane - xlo1, G);
+        if (r < gb.y - ga.y) {
+            if (t.f0 == 0) {
                 f1.m = job.ragged_l ? MB_NEG_INF : 0.0;
                 f1.x = job.ragged_l ? 0.0 : MB_NEG_INF;
                 f1.y = f1.x;
             } else {
                 f1.m = f1.x = f1.y = 0.0;
             }
-            if (real && d == t.tb_to) store_cell(bnd, x - xlo1, f1);
+            if (real && t.f0 == tb_to) store_cell(bnd, r, f1);
         }
     }
-    // ---- software pipeline prologue: geometry of d+1..d+3, symbols of d+1, d+2, emission of d+1
     auto geo_at = [&](int dd) { return __ldg(gj + min(dd, N + 1)); };
-    auto sym_x_at = [&](int2 gg) { return (unsigned) __ldg(sx + (gg.x + mod_g(lane - gg.x, G) - 1)); };
-    auto sym_y_at = [&](int2 gg, int dd) { return (unsigned) __ldg(sy + (dd - (gg.x + mod_g(lane - gg.x, G)) - 1)); };
-    int2 gA = g1, gB = geo_at(d + 2), gC = geo_at(d + 3);  // geometry of d+1, d+2, d+3
-    unsigned cx0 = sym_x_at(gA), cy0 = sym_y_at(gA, d + 1);
-    unsigned cx1 = sym_x_at(gB), cy1 = sym_y_at(gB, min(d + 2, N));
-    double eM0 = __ldg(emP + cx0 * PACK_STRIDE + cy0);
-
+    auto lane_x = [&](int xlo) { return xlo + mod_g(lane - xlo, G); };
+    // ---- pipeline prologue
+    int2 gr[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) gr[k] = geo_at(d0 + k);
+    unsigned csx[2], csy[2];
+    double eM[2];
+    uint32_t exa[2], eya[2];
+    {
+        const int xa = lane_x(gr[0].x);
+        const unsigned cx = __ldg(sx + xa), cy = __ldg(sy + (min(d0, N) - xa));
+        eM[0] = __ldg(emP + cx * PACK_STRIDE + cy);
+        exa[0] = gx_s + 32u * (unsigned) packed_base(cx);
+        eya[0] = gy_s + 32u * (unsigned) packed_base(cy);
+        const int xb = lane_x(gr[1].x);
+        csx[1] = __ldg(sx + xb);
+        csy[1] = __ldg(sy + (min(d0 + 1, N) - xb));
+    }
     const int n_it = t.tb_from - t.f0;
     const int n_max = __reduce_max_sync(0xffffffffu, n_it);
-#pragma unroll 2
-    for (int it = 0; it < n_max; it++) {
-        const bool live = real && it < n_it;
-        d = t.f0 + 1 + min(it, n_it - 1);
-        // stage loads for the diagonals ahead (independent of the recurrence)
-        const int2 gD = geo_at(d + 3);
-        const unsigned cx2 = sym_x_at(gC), cy2 = sym_y_at(gC, min(d + 2, N));
-        const double eM1 = __ldg(emP + cx1 * PACK_STRIDE + cy1);
-        // ---- diagonal d
-        const int xlo = gA.x, w = gB.y - gA.y;
-        const uint32_t co = (uint32_t) gA.y;
-        const int x = xlo + mod_g(lane - xlo, G);
-        const bool active = x < xlo + w;
-        Cell lower_raw;
-        lower_raw.m = shfl_g<G>(f1.m, prev_lane);
-        lower_raw.x = shfl_g<G>(f1.x, prev_lane);
-        lower_raw.y = shfl_g<G>(f1.y, prev_lane);
-        const Cell lower = cell_sel((unsigned) (x - 1 - xlo1) < (unsigned) w1, lower_raw);
-        const Cell upper = cell_sel((unsigned) (x - xlo1) < (unsigned) w1, f1);
-        const Cell middle = cell_sel((unsigned) (x - 1 - xlo2) < (unsigned) w2, mid);
-        const double *ex = m.ex_t[packed_base(cx0)];
-        const double *ey = m.ey_t[packed_base(cy0)];
-        Cell c;
-        // stateMachine3_cellCalculate (stateMachine.c:562-586): X from lower, M from middle, Y from upper
-        c.x = dadd(lower.m, ex[0]);
-        c.x = logadd_tab(c.x, dadd(lower.x, ex[1]), lac);
-        if (SWITCH) c.x = logadd_tab(c.x, dadd(lower.y, ex[2]), lac);
-        c.m = dadd(middle.m, dadd(eM0, tMM));
-        c.m = logadd_tab(c.m, dadd(middle.x, dadd(eM0, tXM)), lac);
-        c.m = logadd_tab(c.m, dadd(middle.y, dadd(eM0, tYM)), lac);
-        c.y = dadd(upper.m, ey[0]);
-        c.y = logadd_tab(c.y, dadd(upper.y, ey[1]), lac);
-        if (SWITCH) c.y = logadd_tab(c.y, dadd(upper.x, ey[2]), lac);
-        c = cell_sel(active, c);
-        if (live && active) {
-            if (d > t.tb_to) store_cell(Fj, (int64_t) co + (x - xlo), c);
-            else if (d == t.tb_to) store_cell(bnd, x - xlo, c);
+    for (int it0 = 0; it0 < n_max; it0 += 4) {
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const int it = it0 + k;
+            const int d = d0 + it;
+            const bool live = real && it < n_it;
+            // ---- loads for the diagonals ahead (independent of the recurrence)
+            {
+                const int x2 = lane_x(gr[(k + 2) & 3].x);
+                csx[k & 1] = __ldg(sx + x2);
+                csy[k & 1] = __ldg(sy + (min(d + 2, N) - x2));
+                const unsigned cx = csx[(k + 1) & 1], cy = csy[(k + 1) & 1];
+                eM[(k + 1) & 1] = __ldg(emP + cx * PACK_STRIDE + cy);
+                exa[(k + 1) & 1] = gx_s + 32u * (unsigned) packed_base(cx);
+                eya[(k + 1) & 1] = gy_s + 32u * (unsigned) packed_base(cy);
+            }
+            // ---- diagonal d
+            const int xlo = gr[k].x;
+            const uint32_t co = (uint32_t) gr[k].y;
+            const int w = gr[(k + 1) & 3].y - gr[k].y;
+            const int r = mod_g(lane - xlo, G);
+            const int x = xlo + r;
+            const bool active = r < w;
+            const double lm = shfl_g<G>(f1.m, prev_lane);
+            const double lx_ = shfl_g<G>(f1.x, prev_lane);
+            const double ly_ = shfl_g<G>(f1.y, prev_lane);
+            const int xe = active ? x : FAR_X;  // a lane outside its diagonal fails every window test
+            const bool ok_lower = (unsigned) (xe - 1 - xlo1) < (unsigned) G;
+            const bool ok_upper = (unsigned) (xe - xlo1) < (unsigned) G;
+            const bool ok_middle = (unsigned) (xe - 1 - xlo2) < (unsigned) G;
+            const double2 ex = lds_f64x2(exa[k & 1]), ey = lds_f64x2(eya[k & 1]);
+            const double e = eM[k & 1];
+            Cell c;
+            // stateMachine3_cellCalculate (stateMachine.c:562-586): X from lower, M from middle, Y from upper
+            c.x = logadd_t(dadd(lm, ex.x), dadd(lx_, ex.y), lac_s);
+            if (SWITCH) c.x = logadd_t(c.x, dadd(ly_, lds_f64(exa[k & 1] + 16)), lac_s);
+            c.m = logadd_t(dadd(midm, dadd(e, tMM)), dadd(midx, dadd(e, tXM)), lac_s);
+            c.m = logadd_t(c.m, dadd(midy, dadd(e, tYM)), lac_s);
+            c.y = logadd_t(dadd(f1.m, ey.x), dadd(f1.y, ey.y), lac_s);
+            if (SWITCH) c.y = logadd_t(c.y, dadd(f1.x, lds_f64(eya[k & 1] + 16)), lac_s);
+            c.x = ok_lower ? c.x : MB_NEG_INF;
+            c.m = ok_middle ? c.m : MB_NEG_INF;
+            c.y = ok_upper ? c.y : MB_NEG_INF;
+            if (live && active && d >= tb_to) {
+                double *q = (d == tb_to) ? bnd + 3 * r : Fj + 3 * ((int64_t) co + r);
+                q[0] = c.m;
+                q[1] = c.x;
+                q[2] = c.y;
+            }
+            // ---- carry
+            midm = lm;
+            midx = lx_;
+            midy = ly_;
+            f1 = c;
+            xlo2 = xlo1;
+            xlo1 = xlo;
+            gr[k] = geo_at(d + 4);
         }
-        // rotate
-        mid = lower_raw;
-        xlo2 = xlo1;
-        w2 = w1;
-        f1 = c;
-        xlo1 = xlo;
-        w1 = w;
-        gA = gB;
-        gB = gC;
-        gC = gD;
-        cx0 = cx1;
-        cy0 = cy1;
-        cx1 = cx2;
-        cy1 = cy2;
-        eM0 = eM1;
     }
 }
 
@@ -193,49 +281,58 @@ forward_tile_kernel(const Job *__restrict__ jobs, const Tile *__restrict__ tiles
 // `val` is this lane's value, the diagonal has w <= G cells starting at x = xlo.  Uniform trip count across the warp
 // (w_max = widest diagonal among the warp's groups); groups with fewer cells fold -inf, which leaves acc unchanged.
 template <int G>
-__device__ __forceinline__ double fold_diag(double val, int xlo, int w, int w_max, const double *lac) {
+__device__ __forceinline__ double fold_diag(double val, int xlo, int w, int w_max, uint32_t lac_s) {
     double acc = MB_NEG_INF;
     for (int i = 0; i < w_max; i++) {
         const double v = shfl_g<G>(val, mod_g(xlo + i, G));
-        acc = logadd_tab(acc, i < w ? v : MB_NEG_INF, lac);
+        acc = logadd_t(acc, i < w ? v : MB_NEG_INF, lac_s);
     }
     return acc;
 }
 
-__device__ __forceinline__ double cell_dot_tab(const Cell &a, const Cell &b, const double *lac) {
+__device__ __forceinline__ double cell_dot_t(const Cell &a, const Cell &b, uint32_t lac_s) {
     double tp = dadd(a.m, b.m);
-    tp = logadd_tab(tp, dadd(a.x, b.x), lac);
-    tp = logadd_tab(tp, dadd(a.y, b.y), lac);
+    tp = logadd_t(tp, dadd(a.x, b.x), lac_s);
+    tp = logadd_t(tp, dadd(a.y, b.y), lac_s);
     return tp;
 }
 
-// Appends the passing cells of one diagonal to a staged list in ascending x (the order the reference emits them).
+// Per-diagonal lane bookkeeping shared by the three staged lists: `bits` of a ballot are cut down to the group,
+// rotated so that bit i is the cell x = xlo + i, and a passing cell is appended behind the passing cells below it.
 template <int G>
-__device__ __forceinline__ void stage_list(bool ok, double v, int x, int y, int rank, int xlo, StagedPair *dst, int &cnt) {
-    unsigned bits = __ballot_sync(0xffffffffu, ok);
-    const int r = mod_g(xlo, G);
-    unsigned rot;
-    if constexpr (G == 32) {
-        rot = __funnelshift_r(bits, bits, r);
-    } else {
-        bits = (bits >> ((threadIdx.x & 31) / G * G)) & ((1u << G) - 1u);
-        rot = ((bits >> r) | (bits << (G - r))) & ((1u << G) - 1u);
+struct StageLane {
+    int shift, rot_r;
+    unsigned below;  // mask of the cells with smaller x
+    __device__ __forceinline__ StageLane(int xlo, int rank, int gshift)
+        : shift(gshift), rot_r(mod_g(xlo, G)), below((1u << rank) - 1u) {}
+    __device__ __forceinline__ void put(bool ok, double v, int x, int y, StagedPair *dst, int &cnt) const {
+        unsigned bits = __ballot_sync(0xffffffffu, ok);
+        unsigned rot;
+        if constexpr (G == 32) {
+            rot = __funnelshift_r(bits, bits, rot_r);
+        } else {
+            bits = (bits >> shift) & ((1u << G) - 1u);
+            rot = (bits >> rot_r) | (bits << (G - rot_r));  // bits above G are masked by `below`
+        }
+        if (ok) {
+            StagedPair sp;
+            sp.v = v;
+            sp.x = x;
+            sp.y = y;
+            dst[cnt + __popc(rot & below)] = sp;
+        }
+        cnt += __popc(bits);
     }
-    if (ok) {
-        StagedPair sp;
-        sp.v = v;
-        sp.x = x;
-        sp.y = y;
-        dst[cnt + __popc(rot & ((1u << rank) - 1u))] = sp;
-    }
-    cnt += __popc(bits);
-}
+};
 
 // One group of G lanes per tile: the walk-back loop of getPosteriorProbsWithBanding (pairwiseAligner.c:753-818) from
 // t.D down to t.tb_to+1, posteriors for diagonals <= t.tb_from.  The total probability is re-sampled every 10th
 // posterior diagonal counted from tb_from; tiles are cut so that their tb_from is one of the reference's samples.
 // A cell state is staged when its log posterior v >= v_thr, where v_thr is the smallest double whose exp() reaches
 // the posterior threshold (found once per context), i.e. exactly when exp(v) >= threshold.
+// Same period-4 register pipeline as the forward kernel, walking down: ring gr[] holds the geometry of d+1 .. d-2.
+// Lanes outside their diagonal keep -inf, so the three sources of a cell are valid exactly when their x lies in the
+// G-wide window of the lane mapping of their diagonal.
 template <int G, int THREADS, bool INDELS, bool SWITCH>
 __global__ void __launch_bounds__(THREADS)
 backward_tile_kernel(const Job *__restrict__ jobs, const Tile *__restrict__ tiles, const int32_t *__restrict__ ids,
@@ -246,15 +343,17 @@ backward_tile_kernel(const Job *__restrict__ jobs, const Tile *__restrict__ tile
                      int total_slots) {
     __shared__ __align__(16) TileShared sh;
     tile_shared_init<THREADS>(sh, models);
-    const int g = (blockIdx.x * THREADS + threadIdx.x) / G;
+    const int tid = tid_x_once();
+    const int g = (blockIdx.x * THREADS + tid) / G;
     const bool real = g < n_ids;
-    const int lane = threadIdx.x & (G - 1);
+    const int lane = tid & (G - 1);
     const int next_lane = mod_g(lane + 1, G);
     const int slot = ids[min(g, n_ids - 1)];
     const Tile t = tiles[slot];
     const Job job = jobs[t.job];
     const DevModel &m = sh.model[job.slot];
-    const double *lac = sh.lac;
+    const uint32_t lac_s = smem_u32(sh.lac);
+    const uint32_t gx_s = smem_u32(&sh.gx[job.slot][0][0]), gy_s = smem_u32(&sh.gy[job.slot][0][0]);
     const uint8_t *sx = px + job.symx_off, *sy = py + job.symy_off;
     const int2 *gj = geo + job.diag_off;
     const double *Fj = F + 3 * job.cell_base;
@@ -266,144 +365,150 @@ backward_tile_kernel(const Job *__restrict__ jobs, const Tile *__restrict__ tile
     const int64_t region = job.cell_base + (uint32_t) __ldg(gj + tb_to + 1).y;
     StagedPair *stM = stage + region, *stX = stage + stage_stride + region, *stY = stage + 2 * stage_stride + region;
     int cntM = 0, cntX = 0, cntY = 0;
+    const int xoff = job.x1 - 1, yoff = job.y1 - 1;
 
-    // symbols of cell (x, y) for the step INTO (x+1, y+1): sX[x], sY[y] (0-based)
     auto geo_at = [&](int dd) { return __ldg(gj + max(dd, 0)); };
-    auto sym_x_at = [&](int2 gg) { return (unsigned) __ldg(sx + (gg.x + mod_g(lane - gg.x, G))); };
-    auto sym_y_at = [&](int2 gg, int dd) { return (unsigned) __ldg(sy + (dd - (gg.x + mod_g(lane - gg.x, G)))); };
-    auto f_at = [&](int2 gg) {
-        const int x = gg.x + mod_g(lane - gg.x, G);
-        return load_cell_cg(Fj, (int64_t) (uint32_t) gg.y + (x - gg.x));
-    };
+    auto lane_x = [&](int xlo) { return xlo + mod_g(lane - xlo, G); };
 
     Cell b1 = cell_neg_inf();
     double b2m = MB_NEG_INF;  // b(d+2).m of lane+1, i.e. the m shuffled one diagonal earlier
-    int xlo1 = 0, w1 = 0, xlo2 = 0, w2 = 0;
+    int xlo2 = -2 * G, w1 = 0;
     double total = MB_NEG_INF;
-    int done = 0;
-    // pipeline prologue: geometry of D+1 (for the width), D, D-1, D-2; symbols of D, D-1; emission of D; F of D
-    int2 gUp = __ldg(gj + D + 1), gA = geo_at(D), gB = geo_at(D - 1), gC = geo_at(D - 2);
-    unsigned cx0 = sym_x_at(gA), cy0 = sym_y_at(gA, D), cx1 = sym_x_at(gB), cy1 = sym_y_at(gB, max(D - 1, 0));
-    double eM0 = __ldg(emP + cx0 * PACK_STRIDE + cy0);
-    Cell fc0 = cell_neg_inf();
+    int until_total = 0;  // posterior diagonals until the next total-probability sample
+    // ---- pipeline prologue: ring slot j holds the geometry of D+1-j; symbols, emission and F of D, symbols of D-1
+    int2 gr[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) gr[j] = geo_at(D + 1 - j);
+    unsigned csx[2], csy[2];
+    double eM[2];
+    uint32_t exa[2], eya[2];
+    Cell fc[2];
     {
-        const int x = gA.x + mod_g(lane - gA.x, G);
-        if (D <= tb_from && x < gA.x + (gUp.y - gA.y)) fc0 = f_at(gA);
+        const int xa = lane_x(gr[1].x);
+        const unsigned cx = __ldg(sx + xa), cy = __ldg(sy + (D - xa));
+        eM[0] = __ldg(emP + cx * PACK_STRIDE + cy);
+        exa[0] = gx_s + 32u * (unsigned) packed_base(cx);
+        eya[0] = gy_s + 32u * (unsigned) packed_base(cy);
+        const int xb = lane_x(gr[2].x);
+        csx[1] = __ldg(sx + xb);
+        csy[1] = __ldg(sy + (max(D - 1, 0) - xb));
+        fc[0] = cell_neg_inf();
+        if (D <= tb_from && xa - gr[1].x < gr[0].y - gr[1].y) fc[0] = load_cell_cg(Fj, (int64_t) (uint32_t) gr[1].y + (xa - gr[1].x));
     }
     const int n_it = D - tb_to;
     const int n_max = __reduce_max_sync(0xffffffffu, n_it);
-    for (int it = 0; it < n_max; it++) {
-        const bool live = real && it < n_it;
-        const int d = D - min(it, n_it - 1);
-        const int2 gD = geo_at(d - 3);
-        const unsigned cx2 = sym_x_at(gC), cy2 = sym_y_at(gC, max(d - 2, 0));
-        const double eM1 = __ldg(emP + cx1 * PACK_STRIDE + cy1);
-        const int xlo = gA.x, w = gUp.y - gA.y;
-        const int x = xlo + mod_g(lane - xlo, G);
-        const int y = d - x;
-        const bool active = x < xlo + w;
-        // F of the next diagonal down (used one iteration later)
-        Cell fc1 = cell_neg_inf();
-        {
-            const int wn = gA.y - gB.y;
-            const int xn = gB.x + mod_g(lane - gB.x, G);
-            if (d - 1 <= tb_from && d - 1 > tb_to && xn < gB.x + wn) fc1 = f_at(gB);
-        }
-        const bool post = live && d <= tb_from;
-        const bool do_total = post && (done % 10 == 0);
-        Cell b;
-        {
-            // gather form of diagonalCalculationBackward: match term from (x+1,y+1) first, then the gap-Y term from
-            // (x,y+1), then the gap-X term from (x+1,y) (see backward_cell in pairhmm_kernels.cuh)
-            const double nx = shfl_g<G>(b1.x, next_lane);
-            const double nm = shfl_g<G>(b1.m, next_lane);
-            const bool has_mm = (unsigned) (x + 1 - xlo2) < (unsigned) w2;
-            const bool has_y = (unsigned) (x - xlo1) < (unsigned) w1;
-            const bool has_x = (unsigned) (x + 1 - xlo1) < (unsigned) w1;
-            const double vm = has_mm ? b2m : MB_NEG_INF;
-            const double vy = has_y ? b1.y : MB_NEG_INF;
-            const double vx = has_x ? nx : MB_NEG_INF;
-            const double *ex = m.ex_t[packed_base(cx0)];  // [0]=M->X, [1]=X->X, [2]=Y->X
-            const double *ey = m.ey_t[packed_base(cy0)];  // [0]=M->Y, [1]=Y->Y, [2]=X->Y
-            b.m = dadd(vm, dadd(eM0, tMM));
-            b.x = dadd(vm, dadd(eM0, tXM));
-            b.y = dadd(vm, dadd(eM0, tYM));
-            b.m = logadd_tab(b.m, dadd(vy, ey[0]), lac);
-            if (SWITCH) b.x = logadd_tab(b.x, dadd(vy, ey[2]), lac);
-            b.y = logadd_tab(b.y, dadd(vy, ey[1]), lac);
-            b.m = logadd_tab(b.m, dadd(vx, ex[0]), lac);
-            b.x = logadd_tab(b.x, dadd(vx, ex[1]), lac);
-            if (SWITCH) b.y = logadd_tab(b.y, dadd(vx, ex[2]), lac);
-            b2m = nm;
-            if (it == 0) {  // d == D: the backward sweep starts from the end state on every cell (:754-762)
-                b.m = endp[0];
-                b.x = endp[1];
-                b.y = endp[2];
+    for (int it0 = 0; it0 < n_max; it0 += 4) {
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const int it = it0 + k;
+            const bool live = real && it < n_it;
+            const int d = D - min(it, n_it - 1);
+            const int2 gUp = gr[k], gA = gr[(k + 1) & 3], gB = gr[(k + 2) & 3], gC = gr[(k + 3) & 3];
+            // ---- loads for the diagonals below (independent of the recurrence)
+            {
+                const int x2 = lane_x(gC.x);
+                csx[k & 1] = __ldg(sx + x2);
+                csy[k & 1] = __ldg(sy + (max(d - 2, 0) - x2));
+                const unsigned cx = csx[(k + 1) & 1], cy = csy[(k + 1) & 1];
+                eM[(k + 1) & 1] = __ldg(emP + cx * PACK_STRIDE + cy);
+                exa[(k + 1) & 1] = gx_s + 32u * (unsigned) packed_base(cx);
+                eya[(k + 1) & 1] = gy_s + 32u * (unsigned) packed_base(cy);
+                // F of the next diagonal down (used one iteration later)
+                const int rn = mod_g(lane - gB.x, G);
+                Cell fn = cell_neg_inf();
+                if (d - 1 <= tb_from && d - 1 > tb_to && rn < gA.y - gB.y) fn = load_cell_cg(Fj, (int64_t) (uint32_t) gB.y + rn);
+                fc[(k + 1) & 1] = fn;
             }
-        }
-        b = cell_sel(active, b);
-        if (__any_sync(0xffffffffu, do_total)) {
-            // diagonalCalculationTotalProbability (pairwiseAligner.c:578-596); groups that do not sample on this
-            // iteration run along (uniform control flow) and discard the result
-            const int w_max = __reduce_max_sync(0xffffffffu, max(w, w1));
-            const double dot = active ? cell_dot_tab(fc0, b, lac) : MB_NEG_INF;
-            double tot = fold_diag<G>(dot, xlo, w, w_max, lac);
-            // paths that jump over d with a match: match block of the forward step from F(d-1) into the cells
-            // of d+1, dotted with B(d+1) (this lane's b1 is its cell of d+1)
-            const int xlom = gB.x, wm = gA.y - gB.y;
-            const int x1 = xlo1 + mod_g(lane - xlo1, G);
-            const int y1 = d + 1 - x1;
-            double val = MB_NEG_INF;
-            if (do_total && it > 0 && x1 < xlo1 + w1) {
-                double gm_ = MB_NEG_INF;
-                if ((unsigned) (x1 - 1 - xlom) < (unsigned) wm) {
-                    const Cell f = (d - 1 == tb_to && (t.flags & TILE_BND))
-                                       ? load_cell_cg(bnd, x1 - 1 - xlom)
-                                       : load_cell_cg(Fj, (int64_t) (uint32_t) gB.y + (x1 - 1 - xlom));
-                    const double e = __ldg(emP + (unsigned) __ldg(sx + x1 - 1) * PACK_STRIDE + (unsigned) __ldg(sy + y1 - 1));
-                    gm_ = dadd(f.m, dadd(e, tMM));
-                    gm_ = logadd_tab(gm_, dadd(f.x, dadd(e, tXM)), lac);
-                    gm_ = logadd_tab(gm_, dadd(f.y, dadd(e, tYM)), lac);
-                }
-                val = dadd(gm_, b1.m);
-            }
-            const double second = fold_diag<G>(val, xlo1, w1, w_max, lac);
-            if (it > 0) tot = logadd_tab(tot, second, lac);
-            if (do_total) total = tot;
-        }
-        {
-            // posteriors of diagonal d (diagonalCalculationPosteriorProbs, :637-681) in the log domain; the ballots
-            // inside stage_list are full-warp, so this block is executed by every group on every iteration
+            const int xlo = gA.x, w = gUp.y - gA.y, xlo1 = gUp.x;
             const int rank = mod_g(lane - xlo, G);
-            const double vM = dadd(dadd(fc0.m, b.m), -total);
-            const bool okM = post && active && x > 0 && y > 0 && vM >= v_thr;
-            stage_list<G>(okM, vM, x - 1 + job.x1, y - 1 + job.y1, rank, xlo, stM, cntM);
-            if (INDELS) {
-                const double vX = dadd(dadd(fc0.x, b.x), -total);
-                const bool okX = post && active && x > 0 && vX >= v_thr;
-                stage_list<G>(okX, vX, x - 1 + job.x1, y - 1 + job.y1, rank, xlo, stX, cntX);
-                const double vY = dadd(dadd(fc0.y, b.y), -total);
-                const bool okY = post && active && y > 0 && vY >= v_thr;
-                stage_list<G>(okY, vY, x - 1 + job.x1, y - 1 + job.y1, rank, xlo, stY, cntY);
+            const int x = xlo + rank;
+            const int y = d - x;
+            const bool active = rank < w;
+            const bool post = live && d <= tb_from;
+            const bool do_total = post && until_total == 0;
+            const Cell f0c = fc[k & 1];
+            Cell b;
+            {
+                // gather form of diagonalCalculationBackward: match term from (x+1,y+1) first, then the gap-Y term from
+                // (x,y+1), then the gap-X term from (x+1,y) (see backward_cell in pairhmm_kernels.cuh)
+                const double nx = shfl_g<G>(b1.x, next_lane);
+                const double nm = shfl_g<G>(b1.m, next_lane);
+                const int xe = active ? x : FAR_X;  // a lane outside its diagonal fails every window test
+                const bool has_mm = (unsigned) (xe + 1 - xlo2) < (unsigned) G;
+                const bool has_y = (unsigned) (xe - xlo1) < (unsigned) G;
+                const bool has_x = (unsigned) (xe + 1 - xlo1) < (unsigned) G;
+                const double vm = has_mm ? b2m : MB_NEG_INF;
+                const double vy = has_y ? b1.y : MB_NEG_INF;
+                const double vx = has_x ? nx : MB_NEG_INF;
+                const double2 ex = lds_f64x2(exa[k & 1]);  // {M->X, X->X}, +16: Y->X
+                const double2 ey = lds_f64x2(eya[k & 1]);  // {M->Y, Y->Y}, +16: X->Y
+                const double e = eM[k & 1];
+                b.m = dadd(vm, dadd(e, tMM));
+                b.x = dadd(vm, dadd(e, tXM));
+                b.y = dadd(vm, dadd(e, tYM));
+                b.m = logadd_t(b.m, dadd(vy, ey.x), lac_s);
+                if (SWITCH) b.x = logadd_t(b.x, dadd(vy, lds_f64(eya[k & 1] + 16)), lac_s);
+                b.y = logadd_t(b.y, dadd(vy, ey.y), lac_s);
+                b.m = logadd_t(b.m, dadd(vx, ex.x), lac_s);
+                b.x = logadd_t(b.x, dadd(vx, ex.y), lac_s);
+                if (SWITCH) b.y = logadd_t(b.y, dadd(vx, lds_f64(exa[k & 1] + 16)), lac_s);
+                b2m = nm;
+                if (k == 0 && it0 == 0) {  // d == D: the backward sweep starts from the end state on every cell (:754-762)
+                    b.m = active ? endp[0] : MB_NEG_INF;
+                    b.x = active ? endp[1] : MB_NEG_INF;
+                    b.y = active ? endp[2] : MB_NEG_INF;
+                }
             }
-            if (post) done++;
+            if (MB_TOTAL_ON && __any_sync(0xffffffffu, do_total)) {
+                // diagonalCalculationTotalProbability (pairwiseAligner.c:578-596); groups that do not sample on this
+                // iteration run along (uniform control flow) and discard the result
+                const int w_max = __reduce_max_sync(0xffffffffu, max(w, w1));
+                const double dot = active ? cell_dot_t(f0c, b, lac_s) : MB_NEG_INF;
+                double tot = fold_diag<G>(dot, xlo, w, w_max, lac_s);
+                // paths that jump over d with a match: match block of the forward step from F(d-1) into the cells
+                // of d+1, dotted with B(d+1) (this lane's b1 is its cell of d+1)
+                const int xlom = gB.x, wm = gA.y - gB.y;
+                const int x1 = lane_x(xlo1);
+                const int y1 = d + 1 - x1;
+                double val = MB_NEG_INF;
+                if (do_total && it > 0 && x1 < xlo1 + w1) {
+                    double gm_ = MB_NEG_INF;
+                    if ((unsigned) (x1 - 1 - xlom) < (unsigned) wm) {
+                        const Cell f = (d - 1 == tb_to && (t.flags & TILE_BND))
+                                           ? load_cell_cg(bnd, x1 - 1 - xlom)
+                                           : load_cell_cg(Fj, (int64_t) (uint32_t) gB.y + (x1 - 1 - xlom));
+                        const double e = __ldg(emP + (unsigned) __ldg(sx + x1 - 1) * PACK_STRIDE + (unsigned) __ldg(sy + y1 - 1));
+                        gm_ = dadd(f.m, dadd(e, tMM));
+                        gm_ = logadd_t(gm_, dadd(f.x, dadd(e, tXM)), lac_s);
+                        gm_ = logadd_t(gm_, dadd(f.y, dadd(e, tYM)), lac_s);
+                    }
+                    val = dadd(gm_, b1.m);
+                }
+                const double second = fold_diag<G>(val, xlo1, w1, w_max, lac_s);
+                if (it > 0) tot = logadd_t(tot, second, lac_s);
+                if (do_total) total = tot;
+            }
+            {
+                // posteriors of diagonal d (diagonalCalculationPosteriorProbs, :637-681) in the log domain; the ballots
+                // are full-warp, so this block is executed by every group on every iteration
+                const StageLane<G> sl(xlo, rank, (tid & 31) & ~(G - 1));
+                const bool pa = post && active;
+                const double vM = dadd(dadd(f0c.m, b.m), -total);
+                sl.put(pa && x > 0 && y > 0 && vM >= v_thr, vM, x + xoff, y + yoff, stM, cntM);
+                if (INDELS) {
+                    const double vX = dadd(dadd(f0c.x, b.x), -total);
+                    sl.put(pa && x > 0 && vX >= v_thr, vX, x + xoff, y + yoff, stX, cntX);
+                    const double vY = dadd(dadd(f0c.y, b.y), -total);
+                    sl.put(pa && y > 0 && vY >= v_thr, vY, x + xoff, y + yoff, stY, cntY);
+                }
+                if (post) until_total = until_total == 0 ? 9 : until_total - 1;
+            }
+            // ---- carry
+            b1 = b;
+            xlo2 = xlo1;
+            w1 = w;
+            gr[k] = geo_at(d - 3);
         }
-        // rotate
-        xlo2 = xlo1;
-        w2 = w1;
-        b1 = b;
-        xlo1 = xlo;
-        w1 = w;
-        gUp = gA;
-        gA = gB;
-        gB = gC;
-        gC = gD;
-        cx0 = cx1;
-        cy0 = cy1;
-        cx1 = cx2;
-        cy1 = cy2;
-        eM0 = eM1;
-        fc0 = fc1;
     }
     if (real && lane == 0) {
         seg_counts[slot] = cntM;
