@@ -38,6 +38,10 @@ int fail(const char *fmt, ...) {
     } while (0)
 
 // Grow-only device buffer.
+constexpr int kFwdThreads = 128;
+constexpr int kBwdThreads = 128;
+constexpr int kTileThreads = 128;
+
 struct DevBuf {
     void *p = nullptr;
     size_t cap = 0;
@@ -105,12 +109,13 @@ struct margin_b200_ctx {
     int total_slots = 0;     // tiles of the current batch
     // tiling (pairhmm_tiles.cuh): tile length in diagonals (multiple of 10), warm-up diagonals on either side
     bool mode_sequential = false;
-    int tile_len = 1000, warmup = 128, force_group = 0;  // tile_len % 10 == 0: tiles start on total-probability samples
+    int tile_len = 1000, warmup = 128, force_group = 0, tile_len_used = 0, bwd_slots = 0;
+    bool tile_len_fixed = false;  // tile_len % 10 == 0: tiles start on total-probability samples
     std::vector<mb::Seg> segs;
     std::vector<mb::Tile> tiles;
     std::vector<int32_t> job_nseg, job_first_tile;
     DevBuf d_geo, d_tiles, d_bnd, d_slot_bnd_off, d_emit5[2], d_px, d_py, d_stage2;
-    DevBuf d_chunks, d_job_first_chunk, d_chunk_sum, d_chunk_maxw, d_totals;
+    DevBuf d_chunks, d_job_first_chunk, d_chunk_sum, d_chunk_maxw, d_totals, d_band_out;
     DevBuf d_arena, d_offs, d_status;
     PinBuf h_arena;
     mb::Tile *p_tiles = nullptr;
@@ -217,7 +222,19 @@ int margin_b200_create(margin_b200_ctx **out, int device) {
     CU(cudaEventCreate(&c->ev0));
     CU(cudaEventCreate(&c->ev1));
     if (const char *e = getenv("MARGIN_B200_MODE")) c->mode_sequential = strcmp(e, "sequential") == 0;
-    if (const char *e = getenv("MARGIN_B200_TILE_LEN")) c->tile_len = std::max(10, atoi(e) / 10 * 10);
+    if (const char *e = getenv("MARGIN_B200_TILE_LEN")) {
+        c->tile_len = std::max(10, atoi(e) / 10 * 10);
+        c->tile_len_fixed = true;
+    }
+    if (const char *e = getenv("MARGIN_B200_TILE_MAX")) c->tile_len = std::max(200, atoi(e) / 10 * 10);
+    {
+        // lane groups of 8 the backward tile kernel keeps resident: occupancy x SMs x groups per CTA
+        int sms = 0, per_sm = 0;
+        CU(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, mb::backward_tile_kernel<8, kTileThreads, true, false>,
+                                                         kTileThreads, 0));
+        c->bwd_slots = sms * per_sm * (kTileThreads / 8);
+    }
     if (const char *e = getenv("MARGIN_B200_WARMUP")) c->warmup = std::max(1, atoi(e));
     *out = c;
     return 0;
@@ -233,7 +250,7 @@ void margin_b200_destroy(margin_b200_ctx *c) {
                       &c->d_ids, &c->d_aln_first_slot, &c->d_F, &c->d_stage, &c->d_out, &c->d_off_out, &c->d_fwd_out,
                       &c->d_geo, &c->d_tiles, &c->d_bnd, &c->d_slot_bnd_off, &c->d_emit5[0], &c->d_emit5[1],
                       &c->d_px, &c->d_py, &c->d_stage2, &c->d_chunks, &c->d_job_first_chunk, &c->d_chunk_sum, &c->d_chunk_maxw,
-                      &c->d_totals, &c->d_arena, &c->d_offs, &c->d_status};
+                      &c->d_totals, &c->d_band_out, &c->d_arena, &c->d_offs, &c->d_status};
     for (DevBuf *b : bufs) b->release();
     c->h_stage_in.release();
     c->h_small.release();
@@ -597,9 +614,6 @@ mb::Params dev_params(const margin_b200_params &p) {
     return q;
 }
 
-constexpr int kFwdThreads = 128;
-constexpr int kBwdThreads = 128;
-constexpr int kTileThreads = 128;
 
 inline int group_of(int maxw) { return maxw <= 8 ? 8 : (maxw <= 16 ? 16 : 32); }
 
@@ -612,35 +626,34 @@ int run_band(margin_b200_ctx *c, bool dynamic, bool with_schedule, bool want_kr)
     mb::Params q = dev_params(c->params);
     q.dynamic = dynamic ? 1 : 0;
     const size_t S = (size_t) c->seg_slots;
-    if (c->d_kl.ensure((c->total_diag + 1) * sizeof(int32_t)) || c->d_cell_off.ensure((c->total_diag + 1) * sizeof(uint32_t)) ||
-        c->d_geo.ensure((c->total_diag + 1) * sizeof(int2)) || c->d_job_cells.ensure((nj + 1) * sizeof(int64_t)) ||
-        c->d_job_maxw.ensure((nj + 1) * sizeof(int32_t)) || c->d_job_nseg.ensure((nj + 1) * sizeof(int32_t)) ||
-        c->d_err.ensure(sizeof(double)) || c->d_segs.ensure((S + 1) * sizeof(mb::Seg)) ||
-        c->d_chunk_sum.ensure((nc + 1) * sizeof(uint32_t)) || c->d_chunk_maxw.ensure((nc + 1) * sizeof(int32_t)) ||
-        c->d_totals.ensure(4 * sizeof(int64_t)))
-        return 1;
-    if (want_kr && c->d_kr.ensure((c->total_diag + 1) * sizeof(int32_t))) return 1;
-    // pinned landing zone: [totals 2 x int64][job_cells][job_maxw][job_nseg][segs][err]
+    // one device block mirrored by one pinned landing zone, so that everything the host needs comes back in one copy:
+    // [totals 2 x int64][job_cells][job_maxw][job_nseg][segs][err]
     const size_t o_cells = 16, o_maxw = o_cells + (size_t) nj * 8, o_nseg = o_maxw + (size_t) nj * 4,
                  o_segs = o_nseg + (size_t) nj * 4, o_err = o_segs + S * sizeof(mb::Seg), o_end = o_err + 8;
+    if (c->d_kl.ensure((c->total_diag + 1) * sizeof(int32_t)) || c->d_cell_off.ensure((c->total_diag + 1) * sizeof(uint32_t)) ||
+        c->d_geo.ensure((c->total_diag + 1) * sizeof(int2)) || c->d_band_out.ensure(o_end) ||
+        c->d_chunk_sum.ensure((nc + 1) * sizeof(uint32_t)) || c->d_chunk_maxw.ensure((nc + 1) * sizeof(int32_t)))
+        return 1;
+    if (want_kr && c->d_kr.ensure((c->total_diag + 1) * sizeof(int32_t))) return 1;
     if (c->h_small.ensure(o_end)) return 1;
     char *h = c->h_small.as<char>();
-    memset(h, 0, 16);
-    *reinterpret_cast<int *>(h + o_err) = 0;
-    CU(cudaMemsetAsync(c->d_err.p, 0, sizeof(int), c->stream));
+    char *dv = c->d_band_out.as<char>();
+    int64_t *d_totals = reinterpret_cast<int64_t *>(dv), *d_job_cells = reinterpret_cast<int64_t *>(dv + o_cells);
+    int32_t *d_job_maxw = reinterpret_cast<int32_t *>(dv + o_maxw), *d_job_nseg = reinterpret_cast<int32_t *>(dv + o_nseg);
+    mb::Seg *d_segs = reinterpret_cast<mb::Seg *>(dv + o_segs);
+    int *d_err = reinterpret_cast<int *>(dv + o_err);
+    CU(cudaMemsetAsync(dv, 0, o_end, c->stream));
     if (nj > 0) {
         {
             KTimer kt_(c, K_BAND);
             mb::band_chunk_kernel<256><<<nc, 256, 0, c->stream>>>(
                 c->d_jobs.as<mb::Job>(), c->d_chunks.as<mb::BandChunk>(), nc, c->d_anchors.as<int32_t>(), q,
                 c->d_geo.as<int2>(), want_kr ? c->d_kr.as<int32_t>() : nullptr, c->d_chunk_sum.as<uint32_t>(),
-                c->d_chunk_maxw.as<int32_t>(), c->d_err.as<int>());
+                c->d_chunk_maxw.as<int32_t>(), d_err);
             mb::band_jobs_kernel<<<(nj + 3) / 4, 128, 0, c->stream>>>(nj, c->d_job_first_chunk.as<int32_t>(),
                                                                      c->d_chunk_sum.as<uint32_t>(),
-                                                                     c->d_chunk_maxw.as<int32_t>(),
-                                                                     c->d_job_cells.as<int64_t>(), c->d_job_maxw.as<int32_t>());
-            mb::band_bases_kernel<512><<<1, 512, 0, c->stream>>>(c->d_jobs.as<mb::Job>(), nj, c->d_job_cells.as<int64_t>(),
-                                                               c->d_job_maxw.as<int32_t>(), c->d_totals.as<int64_t>());
+                                                                     c->d_chunk_maxw.as<int32_t>(), d_job_cells, d_job_maxw);
+            mb::band_bases_kernel<512><<<1, 512, 0, c->stream>>>(c->d_jobs.as<mb::Job>(), nj, d_job_cells, d_job_maxw, d_totals);
             mb::band_apply_kernel<256><<<nc, 256, 0, c->stream>>>(c->d_jobs.as<mb::Job>(), c->d_chunks.as<mb::BandChunk>(), nc,
                                                                  c->d_chunk_sum.as<uint32_t>(), c->d_geo.as<int2>(),
                                                                  c->d_kl.as<int32_t>(), c->d_cell_off.as<uint32_t>());
@@ -651,18 +664,12 @@ int run_band(margin_b200_ctx *c, bool dynamic, bool with_schedule, bool want_kr)
             {
                 KTimer kt_(c, K_SCHEDULE);
                 mb::schedule_kernel<<<(nj + per_block - 1) / per_block, threads, 0, c->stream>>>(
-                    c->d_jobs.as<mb::Job>(), nj, c->d_cell_off.as<uint32_t>(), q, c->d_segs.as<mb::Seg>(),
-                    c->d_job_nseg.as<int32_t>());
+                    c->d_jobs.as<mb::Job>(), nj, c->d_cell_off.as<uint32_t>(), q, d_segs, d_job_nseg);
             }
             c->launches++;
-            CU(cudaMemcpyAsync(h + o_nseg, c->d_job_nseg.p, (size_t) nj * 4, cudaMemcpyDeviceToHost, c->stream));
-            if (S) CU(cudaMemcpyAsync(h + o_segs, c->d_segs.p, S * sizeof(mb::Seg), cudaMemcpyDeviceToHost, c->stream));
         }
-        CU(cudaMemcpyAsync(h, c->d_totals.p, 8, cudaMemcpyDeviceToHost, c->stream));
-        CU(cudaMemcpyAsync(h + o_cells, c->d_job_cells.p, (size_t) nj * 8, cudaMemcpyDeviceToHost, c->stream));
-        CU(cudaMemcpyAsync(h + o_maxw, c->d_job_maxw.p, (size_t) nj * 4, cudaMemcpyDeviceToHost, c->stream));
     }
-    CU(cudaMemcpyAsync(h + o_err, c->d_err.p, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemcpyAsync(h, dv, o_end, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
     CU(cudaGetLastError());
     if (*reinterpret_cast<int *>(h + o_err))
@@ -700,9 +707,65 @@ bool job_is_tiled(const margin_b200_ctx *c, int j) {
 // Cuts every traceback segment into tiles (see pairhmm_tiles.cuh) and lays the tiles out in the order of the
 // reference's final lists: alignments in batch order, blocks of an alignment in order, later tracebacks first, and
 // inside a traceback the lowest diagonals first (each tile's tuples are reversed by the gather).
+// Number of tiles a traceback segment of `span` diagonals is cut into at tile length L (a remainder shorter than
+// L/4 is merged into the lowest tile).
+inline int tiles_of_span(int span, int L) {
+    if (span <= L) return 1;
+    const int nt = span / L;
+    return nt + ((span - nt * L >= L / 4) ? 1 : 0);
+}
+
+// Tile length for this batch.  The backward kernel is the longest launch and runs bwd_slots lane groups of 8 at a time
+// (occupancy x SMs); a launch takes about waves x (L + W) steps, so L is chosen among a few candidates (the lengths
+// that fill 1, 2, 3 ... waves, capped at the configured length) to minimise ceil(tiles / slots) x (L + W).
+// MARGIN_B200_TILE_LEN pins L instead.
+int pick_tile_len(const margin_b200_ctx *c) {
+    if (c->tile_len_fixed || c->bwd_slots <= 0) return c->tile_len;
+    const int nj = (int) c->jobs.size();
+    int64_t T = 0;
+    for (int j = 0; j < nj; j++) {
+        if (!job_is_tiled(c, j)) continue;
+        for (int s = 0; s < c->job_nseg[j]; s++) {
+            const mb::Seg &sg = c->segs[c->jobs[j].seg_base + s];
+            T += sg.tb_from - sg.tb_to;
+        }
+    }
+    if (T <= 0) return c->tile_len;
+    const int Lmax = c->tile_len, Lmin = 200, W = c->warmup;
+    int best_L = Lmax;
+    double best_cost = 1e300;
+    for (int n = 1; n <= 64; n++) {
+        // the length at which ~n waves are full; two neighbours absorb the per-segment remainders
+        const int64_t L0 = (T / ((int64_t) n * c->bwd_slots) + 9) / 10 * 10;
+        bool below = false;
+        for (int dl = 0; dl <= 40; dl += 20) {
+            const int L = (int) std::min<int64_t>(Lmax, std::max<int64_t>(Lmin, L0 + dl));
+            int64_t cnt = 0;
+            for (int j = 0; j < nj; j++) {
+                if (!job_is_tiled(c, j)) continue;
+                for (int s = 0; s < c->job_nseg[j]; s++) {
+                    const mb::Seg &sg = c->segs[c->jobs[j].seg_base + s];
+                    cnt += tiles_of_span(sg.tb_from - sg.tb_to, L);
+                }
+            }
+            const int64_t waves = (cnt + c->bwd_slots - 1) / c->bwd_slots;
+            const double cost = (double) waves * (L + W);
+            if (cost < best_cost) {
+                best_cost = cost;
+                best_L = L;
+            }
+            if (L == Lmin) below = true;
+        }
+        if (below || L0 < Lmin) break;
+        if (L0 + 40 < Lmax && n >= 4) break;  // more waves only add warm-up overhead
+    }
+    return best_L;
+}
+
 void build_tiles(margin_b200_ctx *c) {
     const int nj = (int) c->jobs.size();
-    const int L = c->tile_len, W = c->warmup;
+    const int L = pick_tile_len(c), W = c->warmup;
+    c->tile_len_used = L;
     c->tiles.clear();
     c->job_first_tile.assign(nj + 1, 0);
     int64_t a = 0;
@@ -715,11 +778,7 @@ void build_tiles(margin_b200_ctx *c) {
             for (int s = c->job_nseg[j] - 1; s >= 0; s--) {
                 const mb::Seg &sg = c->segs[job.seg_base + s];
                 const int span = sg.tb_from - sg.tb_to;
-                int nt = 1;
-                if (tiled && span > L) {
-                    nt = span / L;
-                    if (span - nt * L >= L / 4) nt++;  // a short remainder is merged into the lowest tile
-                }
+                const int nt = tiled ? tiles_of_span(span, L) : 1;
                 for (int k = nt - 1; k >= 0; k--) {  // lowest diagonals first
                     mb::Tile t;
                     t.job = j;
@@ -749,18 +808,28 @@ struct Bins {
     int tile_bwd[4];
 };
 
-// Ascending sort of keys whose low 32 bits (the ids) are already ascending: two stable 16-bit counting passes over
-// the high half.  O(n); a comparison sort of ~10^4 tiles was the largest host cost of a call.
+// Ascending sort of keys whose low 32 bits (the ids) are already ascending: stable LSD counting passes of 11 bits
+// over the high half, skipping every digit on which all keys agree (tile lengths span ~11 bits and most batches use
+// one lane-group width, so this is one or two passes over 2048 buckets).  O(n); a comparison sort of ~10^4 tiles was
+// the largest host cost of a call, and 16-bit digits spent more time on their 65536 buckets than on the keys.
 void sort_keys(std::vector<uint64_t> &k, std::vector<uint64_t> &tmp, std::vector<uint32_t> &cnt) {
     const size_t n = k.size();
     if (n < 2) return;
+    uint64_t all_or = 0, all_and = ~0ull;
+    for (size_t i = 0; i < n; i++) {
+        all_or |= k[i];
+        all_and &= k[i];
+    }
+    const uint64_t differ = (all_or ^ all_and) >> 32;
     tmp.resize(n);
-    for (int pass = 0; pass < 2; pass++) {
-        const int shift = 32 + 16 * pass;
-        cnt.assign(65537, 0);
-        for (size_t i = 0; i < n; i++) cnt[((k[i] >> shift) & 0xffff) + 1]++;
-        for (int b = 0; b < 65536; b++) cnt[b + 1] += cnt[b];
-        for (size_t i = 0; i < n; i++) tmp[cnt[(k[i] >> shift) & 0xffff]++] = k[i];
+    constexpr int BITS = 11;
+    for (int shift = 32; shift < 64; shift += BITS) {
+        const uint64_t mask = (1ull << std::min(BITS, 64 - shift)) - 1;
+        if (((differ >> (shift - 32)) & mask) == 0) continue;
+        cnt.assign(mask + 2, 0);
+        for (size_t i = 0; i < n; i++) cnt[((k[i] >> shift) & mask) + 1]++;
+        for (uint64_t b = 0; b < mask; b++) cnt[b + 1] += cnt[b];
+        for (size_t i = 0; i < n; i++) tmp[cnt[(k[i] >> shift) & mask]++] = k[i];
         k.swap(tmp);
     }
 }

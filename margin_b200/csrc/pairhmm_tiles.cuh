@@ -277,17 +277,22 @@ forward_tile_kernel(const Job *__restrict__ jobs, const Tile *__restrict__ tiles
 
 // ----------------------------------------------------------------------------------------------- backward tile
 
-// Sequential logAdd fold over the cells of one diagonal in ascending x (dpDiagonal_dotProduct, pairwiseAligner.c:450-461);
-// `val` is this lane's value, the diagonal has w <= G cells starting at x = xlo.  Uniform trip count across the warp
-// (w_max = widest diagonal among the warp's groups); groups with fewer cells fold -inf, which leaves acc unchanged.
+// Sequential logAdd folds over the cells of two diagonals in ascending x (dpDiagonal_dotProduct,
+// pairwiseAligner.c:450-461), interleaved: `va` / `vb` are this lane's values, diagonal a has wa <= G cells starting
+// at x = xa, diagonal b has wb cells starting at xb.  Uniform trip count across the warp (w_max = widest diagonal
+// among the warp's groups); a fold past its diagonal's width folds -inf, which leaves the sum unchanged.
 template <int G>
-__device__ __forceinline__ double fold_diag(double val, int xlo, int w, int w_max, uint32_t lac_s) {
-    double acc = MB_NEG_INF;
+__device__ __forceinline__ void fold_diag2(double va, int xa, int wa, double vb, int xb, int wb, int w_max,
+                                           uint32_t lac_s, double &acc_a, double &acc_b) {
+    acc_a = MB_NEG_INF;
+    acc_b = MB_NEG_INF;
+#pragma unroll 1
     for (int i = 0; i < w_max; i++) {
-        const double v = shfl_g<G>(val, mod_g(xlo + i, G));
-        acc = logadd_t(acc, i < w ? v : MB_NEG_INF, lac_s);
+        const double a = shfl_g<G>(va, mod_g(xa + i, G));
+        const double b = shfl_g<G>(vb, mod_g(xb + i, G));
+        acc_a = logadd_t(acc_a, i < wa ? a : MB_NEG_INF, lac_s);
+        acc_b = logadd_t(acc_b, i < wb ? b : MB_NEG_INF, lac_s);
     }
-    return acc;
 }
 
 __device__ __forceinline__ double cell_dot_t(const Cell &a, const Cell &b, uint32_t lac_s) {
@@ -330,7 +335,7 @@ struct StageLane {
 // posterior diagonal counted from tb_from; tiles are cut so that their tb_from is one of the reference's samples.
 // A cell state is staged when its log posterior v >= v_thr, where v_thr is the smallest double whose exp() reaches
 // the posterior threshold (found once per context), i.e. exactly when exp(v) >= threshold.
-// Same period-4 register pipeline as the forward kernel, walking down: ring gr[] holds the geometry of d+1 .. d-2.
+// Same register pipeline as the forward kernel, walking down, with the geometry of d+1 .. d-2 in a move chain.
 // Lanes outside their diagonal keep -inf, so the three sources of a cell are valid exactly when their x lies in the
 // G-wide window of the lane mapping of their diagonal.
 template <int G, int THREADS, bool INDELS, bool SWITCH>
@@ -375,35 +380,37 @@ backward_tile_kernel(const Job *__restrict__ jobs, const Tile *__restrict__ tile
     int xlo2 = -2 * G, w1 = 0;
     double total = MB_NEG_INF;
     int until_total = 0;  // posterior diagonals until the next total-probability sample
-    // ---- pipeline prologue: ring slot j holds the geometry of D+1-j; symbols, emission and F of D, symbols of D-1
-    int2 gr[4];
-#pragma unroll
-    for (int j = 0; j < 4; j++) gr[j] = geo_at(D + 1 - j);
+    // ---- pipeline prologue: geometry of D+1 .. D-2 (+ D-3 in flight); symbols, emission and F of D, symbols of D-1
+    int2 gUp = geo_at(D + 1), gA = geo_at(D), gB = geo_at(D - 1), gC = geo_at(D - 2);
+    int2 gn[2];  // landing registers: a geometry word is loaded one step and moved into the chain the next
+    gn[1] = geo_at(D - 3);
     unsigned csx[2], csy[2];
     double eM[2];
     uint32_t exa[2], eya[2];
     Cell fc[2];
     {
-        const int xa = lane_x(gr[1].x);
+        const int xa = lane_x(gA.x);
         const unsigned cx = __ldg(sx + xa), cy = __ldg(sy + (D - xa));
         eM[0] = __ldg(emP + cx * PACK_STRIDE + cy);
         exa[0] = gx_s + 32u * (unsigned) packed_base(cx);
         eya[0] = gy_s + 32u * (unsigned) packed_base(cy);
-        const int xb = lane_x(gr[2].x);
+        const int xb = lane_x(gB.x);
         csx[1] = __ldg(sx + xb);
         csy[1] = __ldg(sy + (max(D - 1, 0) - xb));
         fc[0] = cell_neg_inf();
-        if (D <= tb_from && xa - gr[1].x < gr[0].y - gr[1].y) fc[0] = load_cell_cg(Fj, (int64_t) (uint32_t) gr[1].y + (xa - gr[1].x));
+        if (D <= tb_from && xa - gA.x < gUp.y - gA.y) fc[0] = load_cell_cg(Fj, (int64_t) (uint32_t) gA.y + (xa - gA.x));
     }
     const int n_it = D - tb_to;
     const int n_max = __reduce_max_sync(0xffffffffu, n_it);
-    for (int it0 = 0; it0 < n_max; it0 += 4) {
+    // The loop body is two diagonals (the period of the symbol / emission / F rings); four would leave the geometry
+    // chain move-free too but, with the total-probability block in every copy, overflows the instruction cache.
+    for (int it0 = 0; it0 < n_max; it0 += 2) {
 #pragma unroll
-        for (int k = 0; k < 4; k++) {
+        for (int k = 0; k < 2; k++) {
             const int it = it0 + k;
             const bool live = real && it < n_it;
             const int d = D - min(it, n_it - 1);
-            const int2 gUp = gr[k], gA = gr[(k + 1) & 3], gB = gr[(k + 2) & 3], gC = gr[(k + 3) & 3];
+            gn[k & 1] = geo_at(d - 4);
             // ---- loads for the diagonals below (independent of the recurrence)
             {
                 const int x2 = lane_x(gC.x);
@@ -464,7 +471,6 @@ backward_tile_kernel(const Job *__restrict__ jobs, const Tile *__restrict__ tile
                 // iteration run along (uniform control flow) and discard the result
                 const int w_max = __reduce_max_sync(0xffffffffu, max(w, w1));
                 const double dot = active ? cell_dot_t(f0c, b, lac_s) : MB_NEG_INF;
-                double tot = fold_diag<G>(dot, xlo, w, w_max, lac_s);
                 // paths that jump over d with a match: match block of the forward step from F(d-1) into the cells
                 // of d+1, dotted with B(d+1) (this lane's b1 is its cell of d+1)
                 const int xlom = gB.x, wm = gA.y - gB.y;
@@ -484,7 +490,8 @@ backward_tile_kernel(const Job *__restrict__ jobs, const Tile *__restrict__ tile
                     }
                     val = dadd(gm_, b1.m);
                 }
-                const double second = fold_diag<G>(val, xlo1, w1, w_max, lac_s);
+                double tot, second;
+                fold_diag2<G>(dot, xlo, w, val, xlo1, w1, w_max, lac_s, tot, second);
                 if (it > 0) tot = logadd_t(tot, second, lac_s);
                 if (do_total) total = tot;
             }
@@ -507,7 +514,10 @@ backward_tile_kernel(const Job *__restrict__ jobs, const Tile *__restrict__ tile
             b1 = b;
             xlo2 = xlo1;
             w1 = w;
-            gr[k] = geo_at(d - 3);
+            gUp = gA;
+            gA = gB;
+            gB = gC;
+            gC = gn[(k + 1) & 1];
         }
     }
     if (real && lane == 0) {
