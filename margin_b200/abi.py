@@ -131,7 +131,8 @@ class Batch:
 
 
 _LIB = None
-LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc", "libmargin_b200.so")
+LIB_PATH = os.environ.get("MARGIN_B200_LIB") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc",
+                                                           "libmargin_b200.so")  # env: A/B builds of the kernels
 
 
 def load_library():
