@@ -4,12 +4,18 @@
 // thread (the reference runs one chunk per OpenMP thread, polish.c:476; thread t uses device t % nGPU).
 // There is no CPU fallback anywhere in this file: without a usable device every entry point fails.
 #include <algorithm>
+#include <array>
 #include <chrono>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <condition_variable>
+#include <functional>
+#include <memory>
+#include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include <cub/device/device_scan.cuh>
@@ -37,11 +43,11 @@ int fail(const char *fmt, ...) {
         if (e_ != cudaSuccess) return fail("%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
     } while (0)
 
-// Grow-only device buffer.
 constexpr int kFwdThreads = 128;
 constexpr int kBwdThreads = 128;
 constexpr int kTileThreads = 128;
 
+// Grow-only device buffer.
 struct DevBuf {
     void *p = nullptr;
     size_t cap = 0;
@@ -122,6 +128,20 @@ struct margin_b200_ctx {
     int64_t *p_ring_off = nullptr, *p_bnd_off = nullptr;
     int32_t *p_aln_first_slot = nullptr, *p_ids = nullptr;
     std::vector<uint64_t> keys[4], key_tmp;
+    std::vector<int32_t> span_tmp;
+    // ---- pipelined batches (posteriors_pipelined): sub-contexts with their own stream and arenas
+    std::vector<margin_b200_ctx *> subs;
+    std::unique_ptr<margin_b200_model> user_models[2];  // as given to set_model, replayed into new sub-contexts
+    int pipeline_k = 3;                                 // MARGIN_B200_PIPELINE (1 = off)
+    int pipe_fill = 2;                                  // MARGIN_B200_PIPE_FILL: SM share a run's tiles are cut for, in 1/K
+    int64_t pipeline_min_bytes = 8 << 20;               // MARGIN_B200_PIPELINE_MIN_BYTES of host input
+    bool is_sub = false, last_pipelined = false;
+    int last_k = 0;
+    PinBuf h_pipe_out[3], h_pipe_off;
+    std::function<void()> after_h2d_enqueue;            // fired once the batch's host->device copies are queued
+    int32_t *bins_ids_h = nullptr;
+    size_t bins_ids_off = 0;
+    int bins_n_ids = 0;
     std::vector<uint32_t> key_cnt;
     std::vector<mb::BandChunk> chunks;
     std::vector<int32_t> job_first_chunk;
@@ -173,7 +193,20 @@ struct Trace {
     bool on;
     std::chrono::steady_clock::time_point t0;
     std::string line;
-    Trace() : on(getenv("MARGIN_B200_TRACE") != nullptr), t0(std::chrono::steady_clock::now()) {}
+    const void *tag;
+    static std::chrono::steady_clock::time_point epoch() {
+        static const std::chrono::steady_clock::time_point e = std::chrono::steady_clock::now();
+        return e;
+    }
+    explicit Trace(const void *who = nullptr)
+        : on(getenv("MARGIN_B200_TRACE") != nullptr), t0(std::chrono::steady_clock::now()), tag(who) {
+        if (on) {
+            char buf[64];
+            snprintf(buf, sizeof(buf), " ctx=%04x t=%.0fus:", (unsigned) ((uintptr_t) who >> 4) & 0xffff,
+                     std::chrono::duration<double, std::micro>(t0 - epoch()).count());
+            line = buf;
+        }
+    }
     void mark(const char *what) {
         if (!on) return;
         auto t1 = std::chrono::steady_clock::now();
@@ -226,6 +259,9 @@ int margin_b200_create(margin_b200_ctx **out, int device) {
         c->tile_len = std::max(10, atoi(e) / 10 * 10);
         c->tile_len_fixed = true;
     }
+    if (const char *e = getenv("MARGIN_B200_PIPELINE")) c->pipeline_k = std::max(1, std::min(16, atoi(e)));
+    if (const char *e = getenv("MARGIN_B200_PIPE_FILL")) c->pipe_fill = std::max(1, std::min(16, atoi(e)));
+    if (const char *e = getenv("MARGIN_B200_PIPELINE_MIN_BYTES")) c->pipeline_min_bytes = std::max(0ll, atoll(e));
     if (const char *e = getenv("MARGIN_B200_TILE_MAX")) c->tile_len = std::max(200, atoi(e) / 10 * 10);
     {
         // lane groups of 8 the backward tile kernel keeps resident: occupancy x SMs x groups per CTA
@@ -242,6 +278,8 @@ int margin_b200_create(margin_b200_ctx **out, int device) {
 
 void margin_b200_destroy(margin_b200_ctx *c) {
     if (!c) return;
+    for (margin_b200_ctx *sub : c->subs) margin_b200_destroy(sub);
+    c->subs.clear();
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     DevBuf *bufs[] = {&c->d_models, &c->d_rsm[0], &c->d_rsm[1], &c->d_symx, &c->d_symy, &c->d_anchors, &c->d_jobs,
@@ -257,6 +295,8 @@ void margin_b200_destroy(margin_b200_ctx *c) {
     c->h_arena.release();
     c->h_out.release();
     c->h_off.release();
+    for (PinBuf &b : c->h_pipe_out) b.release();
+    c->h_pipe_off.release();
     for (cudaEvent_t e : c->ev_pool) cudaEventDestroy(e);
     cudaEventDestroy(c->ev0);
     cudaEventDestroy(c->ev1);
@@ -269,6 +309,11 @@ int margin_b200_set_model(margin_b200_ctx *c, int slot, const margin_b200_model 
     if (slot < 0 || slot > 1) return fail("margin_b200_set_model: slot must be 0 or 1");
     if (m->rle && m->max_rl != MARGIN_B200_MAX_RL) return fail("margin_b200_set_model: max_rl must be %d", MARGIN_B200_MAX_RL);
     CU(cudaSetDevice(c->device));
+    if (!c->is_sub) {
+        if (c->user_models[slot].get() != m) c->user_models[slot].reset(new margin_b200_model(*m));
+        for (margin_b200_ctx *sub : c->subs)
+            if (margin_b200_set_model(sub, slot, m)) return 1;
+    }
     mb::DevModel &d = c->host_models[slot];
     memset(&d, 0, sizeof(d));
     memcpy(d.t, m->t, sizeof(d.t));
@@ -343,6 +388,8 @@ int margin_b200_set_params(margin_b200_ctx *c, const margin_b200_params *p) {
     if (!(p->threshold >= 0.0 && p->threshold <= 1.0)) return fail("threshold must be in [0,1]");
     c->params = *p;
     c->have_params = true;
+    for (margin_b200_ctx *sub : c->subs)
+        if (margin_b200_set_params(sub, p)) return 1;
     // log-domain threshold of the tile kernels: smallest v with exp(v) >= threshold on this device
     if (p->threshold <= 0.0) {
         c->v_thr = -INFINITY;
@@ -422,7 +469,7 @@ extern "C" int margin_b200_upload_batch(margin_b200_ctx *c, const margin_b200_ba
     if (b->n < 0) return fail("margin_b200_upload_batch: negative batch size");
     if (check_device(c->device)) return 1;
     CU(cudaSetDevice(c->device));
-    Trace tr;
+    Trace tr(c);
     const margin_b200_params &p = c->params;
     const int64_t n = b->n;
     c->n_aln = n;
@@ -486,6 +533,7 @@ extern "C" int margin_b200_upload_batch(margin_b200_ctx *c, const margin_b200_ba
     if (n) CU(cudaMemcpyAsync(h_status, c->d_status.p, (size_t) 2 * n * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
     CU(cudaMemcpyAsync(h_status + 2 * n, c->d_err.p, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
     tr.mark("enqueue");
+    if (c->after_h2d_enqueue) c->after_h2d_enqueue();
     CU(cudaStreamSynchronize(c->stream));
     CU(cudaGetLastError());
     tr.mark("h2d+check sync");
@@ -719,45 +767,39 @@ inline int tiles_of_span(int span, int L) {
 // (occupancy x SMs); a launch takes about waves x (L + W) steps, so L is chosen among a few candidates (the lengths
 // that fill 1, 2, 3 ... waves, capped at the configured length) to minimise ceil(tiles / slots) x (L + W).
 // MARGIN_B200_TILE_LEN pins L instead.
-int pick_tile_len(const margin_b200_ctx *c) {
+int pick_tile_len(margin_b200_ctx *c) {
     if (c->tile_len_fixed || c->bwd_slots <= 0) return c->tile_len;
     const int nj = (int) c->jobs.size();
+    std::vector<int32_t> &spans = c->span_tmp;
+    spans.clear();
     int64_t T = 0;
     for (int j = 0; j < nj; j++) {
         if (!job_is_tiled(c, j)) continue;
         for (int s = 0; s < c->job_nseg[j]; s++) {
             const mb::Seg &sg = c->segs[c->jobs[j].seg_base + s];
+            spans.push_back(sg.tb_from - sg.tb_to);
             T += sg.tb_from - sg.tb_to;
         }
     }
     if (T <= 0) return c->tile_len;
     const int Lmax = c->tile_len, Lmin = 200, W = c->warmup;
+    const int64_t slots = c->bwd_slots;
+    const int64_t n_min = std::max<int64_t>(1, (T + slots * Lmax - 1) / (slots * Lmax));
     int best_L = Lmax;
     double best_cost = 1e300;
-    for (int n = 1; n <= 64; n++) {
-        // the length at which ~n waves are full; two neighbours absorb the per-segment remainders
-        const int64_t L0 = (T / ((int64_t) n * c->bwd_slots) + 9) / 10 * 10;
-        bool below = false;
+    for (int64_t n = n_min; n <= n_min + 1; n++) {
+        // the length at which ~n waves are full; its neighbours absorb the per-segment remainders
+        const int64_t L0 = (T / (n * slots) + 9) / 10 * 10;
         for (int dl = 0; dl <= 40; dl += 20) {
             const int L = (int) std::min<int64_t>(Lmax, std::max<int64_t>(Lmin, L0 + dl));
             int64_t cnt = 0;
-            for (int j = 0; j < nj; j++) {
-                if (!job_is_tiled(c, j)) continue;
-                for (int s = 0; s < c->job_nseg[j]; s++) {
-                    const mb::Seg &sg = c->segs[c->jobs[j].seg_base + s];
-                    cnt += tiles_of_span(sg.tb_from - sg.tb_to, L);
-                }
-            }
-            const int64_t waves = (cnt + c->bwd_slots - 1) / c->bwd_slots;
-            const double cost = (double) waves * (L + W);
+            for (int32_t sp : spans) cnt += tiles_of_span(sp, L);
+            const double cost = (double) ((cnt + slots - 1) / slots) * (L + W);
             if (cost < best_cost) {
                 best_cost = cost;
                 best_L = L;
             }
-            if (L == Lmin) below = true;
         }
-        if (below || L0 < Lmin) break;
-        if (L0 + 40 < Lmax && n >= 4) break;  // more waves only add warm-up overhead
     }
     return best_L;
 }
@@ -805,7 +847,7 @@ struct Bins {
     int seq_fwd[4];
     int tile_fwd[4];
     int gen_bwd[4];
-    int tile_bwd[4];
+    int tile_bwd[4] = {0, 0, 0, 0};  // filled by finish_bins()
 };
 
 // Ascending sort of keys whose low 32 bits (the ids) are already ascending: stable LSD counting passes of 11 bits
@@ -896,7 +938,11 @@ int build_bins(margin_b200_ctx *c, bool with_slots, Bins &bins, int force_group)
     emit(k0, bins.seq_fwd);
     emit(k1, bins.tile_fwd);
     emit(k2, bins.gen_bwd);
-    emit(k3, bins.tile_bwd);
+    // The id list of the tiled backward launches is sorted and sent by finish_bins(), after the forward kernels have
+    // been launched, so that this piece of host work runs beside them instead of in front of them.
+    c->bins_ids_h = ids;
+    c->bins_ids_off = o_ids;
+    c->bins_n_ids = n_ids;
     CU(cudaMemcpyAsync(c->d_arena.p, h, o_ids + (size_t) n_ids * 4, cudaMemcpyHostToDevice, c->stream));
     char *dv = c->d_arena.as<char>();
     c->p_tiles = reinterpret_cast<mb::Tile *>(dv + o_tiles);
@@ -909,6 +955,25 @@ int build_bins(margin_b200_ctx *c, bool with_slots, Bins &bins, int force_group)
             c->d_bnd.ensure((size_t) (bnd_cells + 1) * 3 * sizeof(double)))
             return 1;
     }
+    return 0;
+}
+
+int finish_bins(margin_b200_ctx *c, Bins &bins) {
+    std::vector<uint64_t> &k3 = c->keys[3];
+    sort_keys(k3, c->key_tmp, c->key_cnt);
+    int32_t *ids = c->bins_ids_h;
+    const int first = c->bins_n_ids;
+    int n_ids = first;
+    size_t q = 0;
+    for (int b = 0; b < 3; b++) {
+        bins.tile_bwd[b] = n_ids;
+        while (q < k3.size() && (int) (k3[q] >> 60) == b) ids[n_ids++] = (int32_t) (uint32_t) k3[q++];
+    }
+    bins.tile_bwd[3] = n_ids;
+    if (n_ids > first)
+        CU(cudaMemcpyAsync(c->d_arena.as<char>() + c->bins_ids_off + (size_t) first * 4, ids + first,
+                           (size_t) (n_ids - first) * 4, cudaMemcpyHostToDevice, c->stream));
+    c->bins_n_ids = n_ids;
     return 0;
 }
 
@@ -999,6 +1064,7 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
     if (check_device(c->device)) return 1;
     CU(cudaSetDevice(c->device));
     memset(out, 0, sizeof(*out));
+    c->last_pipelined = false;
     c->launches = 0;
     c->ev_used = 0;
     c->total_tuples = 0;
@@ -1006,7 +1072,7 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
     c->force_group = force_group_env();
     const int nj = (int) c->jobs.size();
     const int n_lists = want_indels ? 3 : 1;
-    Trace tr;
+    Trace tr(c);
     CU(cudaEventRecord(c->ev0, c->stream));
     if (run_band(c, c->params.dynamic_anchor_expansion != 0, true, false)) return 1;
     tr.mark("band+sync");
@@ -1017,7 +1083,7 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
     tr.mark("bins+h2d+sync");
     const int64_t cells = c->total_cells;
     const int S = c->total_slots;
-    const bool any_generic = bins.gen_bwd[3] > bins.gen_bwd[0], any_tiled = bins.tile_bwd[3] > bins.tile_bwd[0];
+    const bool any_generic = bins.gen_bwd[3] > bins.gen_bwd[0], any_tiled = bins.tile_fwd[3] > bins.tile_fwd[0];
     if (c->d_F.ensure((size_t) (cells + 1) * 3 * sizeof(double)) ||
         (any_generic && c->d_stage.ensure((size_t) (cells + 1) * n_lists * sizeof(mb::Pair))) ||
         (any_tiled && c->d_stage2.ensure((size_t) (cells + 1) * n_lists * sizeof(mb::StagedPair))) ||
@@ -1032,6 +1098,7 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
     launch_forward_tiles<8>(c, bins.tile_fwd[0], bins.tile_fwd[1] - bins.tile_fwd[0]);
     launch_forward_tiles<16>(c, bins.tile_fwd[1], bins.tile_fwd[2] - bins.tile_fwd[1]);
     launch_forward_tiles<32>(c, bins.tile_fwd[2], bins.tile_fwd[3] - bins.tile_fwd[2]);
+    if (finish_bins(c, bins)) return 1;
     const int64_t stride = cells + 1;
     if (want_indels) {
         launch_backward<8, true>(c, bins.gen_bwd[0], bins.gen_bwd[1] - bins.gen_bwd[0], stride);
@@ -1142,8 +1209,226 @@ extern "C" int margin_b200_download_result(margin_b200_ctx *c, margin_b200_resul
     return 0;
 }
 
+// ---------------------------------------------------------------------------------------------- pipelined batch
+//
+// A host-memory batch spends as long on PCIe as in the kernels (C2: 70 MB in, 105 MB out, ~1.4 + ~2.0 ms against
+// ~2.5 ms of device work).  posteriors_pipelined() cuts the batch into K runs of consecutive alignments and gives
+// each to a sub-context (own stream, own arenas) driven by its own host thread: the copies of one run overlap the
+// kernels of its neighbours, and the kernels of neighbouring runs share the SMs.  Host->device copies are queued in
+// run order (a ticket), so the first run has the link to itself and starts computing early; the tuple lists land
+// directly at their final place in three pinned arrays (one per list), run k behind run k-1 as soon as the sizes
+// of run k-1 are known, so the result is the same contiguous layout as the unpipelined call without a host copy.
+namespace {
+
+struct PipeShared {
+    std::mutex mu;
+    std::condition_variable cv;
+    int h2d_ticket = 0;   // run whose host->device copies may be queued next
+    int sized_upto = 0;   // runs whose list sizes are known
+    bool overflow = false;
+    std::vector<std::array<int64_t, 3>> base;  // [run][list] first tuple of the run in the final list
+};
+
+struct PipeRun {
+    int64_t first = 0, n = 0;
+    std::vector<int64_t> off_x, off_y, off_a;
+    margin_b200_batch view{};
+    margin_b200_result res{};
+    int rc = 0;
+    std::string err;
+};
+
+int ensure_subs(margin_b200_ctx *c, int K) {
+    while ((int) c->subs.size() < K) {
+        margin_b200_ctx *sub = nullptr;
+        if (margin_b200_create(&sub, c->device)) return 1;
+        sub->is_sub = true;
+        {
+            // earlier runs outrank later ones, so that a run's kernels are not held up by the runs queued behind it
+            // and its lists can start for the host while the others still compute
+            int least = 0, greatest = 0;
+            CU(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+            const int prio = std::min(least, greatest + (int) c->subs.size());
+            cudaStreamDestroy(sub->stream);
+            CU(cudaStreamCreateWithPriority(&sub->stream, cudaStreamNonBlocking, prio));
+        }
+        c->subs.push_back(sub);
+        for (int slot = 0; slot < 2; slot++)
+            if (c->have_model[slot] && margin_b200_set_model(sub, slot, c->user_models[slot].get())) return 1;
+        if (margin_b200_set_params(sub, &c->params)) return 1;
+    }
+    for (int k = 0; k < K; k++) {
+        margin_b200_ctx *sub = c->subs[k];
+        sub->mode_sequential = c->mode_sequential;
+        sub->tile_len = c->tile_len;
+        sub->tile_len_fixed = c->tile_len_fixed;
+        sub->warmup = c->warmup;
+        // Tile length of a run: with bwd_slots / K every run is cut as if it owned 1/K of the SMs (same tiles as the
+        // unpipelined call); a larger share means shorter tiles, i.e. a run finishes sooner (its lists reach the host
+        // while later runs still compute) at the price of more warm-up diagonals.
+        sub->bwd_slots = std::max(kTileThreads / 8, (int) ((int64_t) c->bwd_slots * c->pipe_fill / K));
+    }
+    return 0;
+}
+
+// device -> pinned copies of one run's lists to their final place; the run's per-alignment offsets to its own h_off
+int pipe_download(margin_b200_ctx *c, margin_b200_ctx *sub, const std::array<int64_t, 3> &base) {
+    const int64_t n = sub->n_aln;
+    Trace tr(sub);
+    if (sub->h_off.ensure((size_t) 3 * (n + 1) * sizeof(int64_t))) return 1;
+    int64_t acc = 0;
+    for (int l = 0; l < 3; l++) {
+        if (sub->list_tuples[l])
+            CU(cudaMemcpyAsync(c->h_pipe_out[l].as<mb::Pair>() + base[l], sub->d_out.as<mb::Pair>() + acc,
+                               (size_t) sub->list_tuples[l] * sizeof(mb::Pair), cudaMemcpyDeviceToHost, sub->stream));
+        acc += sub->list_tuples[l];
+    }
+    CU(cudaMemcpyAsync(sub->h_off.p, sub->d_off_out.p, (size_t) 3 * (n + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost,
+                       sub->stream));
+    CU(cudaStreamSynchronize(sub->stream));
+    tr.mark("pipe d2h");
+    return 0;
+}
+
+int posteriors_pipelined(margin_b200_ctx *c, const margin_b200_batch *b, int want_indels, margin_b200_result *out, int K) {
+    const int64_t n = b->n;
+    if (ensure_subs(c, K)) return 1;
+    // ---- runs of consecutive alignments with about equal host bytes
+    std::vector<PipeRun> runs(K);
+    {
+        auto bytes_upto = [&](int64_t i) { return 12 * b->off_a[i] + 2 * (b->off_x[i] + b->off_y[i]); };
+        const int64_t total = bytes_upto(n);
+        int64_t i = 0;
+        for (int k = 0; k < K; k++) {
+            runs[k].first = i;
+            if (k == K - 1) {
+                i = n;
+            } else {
+                const int64_t want = total * (k + 1) / K;
+                while (i < n - (K - 1 - k) && (i <= runs[k].first || bytes_upto(i) < want)) i++;
+            }
+            runs[k].n = i - runs[k].first;
+        }
+    }
+    for (PipeRun &r : runs) {
+        r.off_x.resize(r.n + 1);
+        r.off_y.resize(r.n + 1);
+        r.off_a.resize(r.n + 1);
+        for (int64_t i = 0; i <= r.n; i++) {
+            r.off_x[i] = b->off_x[r.first + i] - b->off_x[r.first];
+            r.off_y[i] = b->off_y[r.first + i] - b->off_y[r.first];
+            r.off_a[i] = b->off_a[r.first + i] - b->off_a[r.first];
+        }
+        r.view.n = r.n;
+        r.view.sym_x = b->sym_x + b->off_x[r.first];
+        r.view.sym_y = b->sym_y + b->off_y[r.first];
+        r.view.anchors = b->anchors + 3 * b->off_a[r.first];
+        r.view.off_x = r.off_x.data();
+        r.view.off_y = r.off_y.data();
+        r.view.off_a = r.off_a.data();
+        r.view.model_slot = b->model_slot ? b->model_slot + r.first : nullptr;
+        r.view.ragged_left = b->ragged_left ? b->ragged_left + r.first : nullptr;
+        r.view.ragged_right = b->ragged_right ? b->ragged_right + r.first : nullptr;
+    }
+    PipeShared sh;
+    sh.base.assign(K + 1, {0, 0, 0});
+    CU(cudaSetDevice(c->device));
+    CU(cudaEventRecord(c->ev0, c->stream));
+    auto work = [&](int k) {
+        PipeRun &r = runs[k];
+        margin_b200_ctx *sub = c->subs[k];
+        cudaSetDevice(c->device);
+        bool released = false;
+        auto release = [&]() {
+            if (released) return;
+            released = true;
+            std::lock_guard<std::mutex> lk(sh.mu);
+            sh.h2d_ticket = k + 1;
+            sh.cv.notify_all();
+        };
+        {
+            std::unique_lock<std::mutex> lk(sh.mu);
+            sh.cv.wait(lk, [&] { return sh.h2d_ticket == k; });
+        }
+        sub->after_h2d_enqueue = release;
+        r.rc = margin_b200_upload_batch(sub, &r.view);
+        sub->after_h2d_enqueue = nullptr;
+        release();
+        if (!r.rc) r.rc = margin_b200_posteriors_resident(sub, want_indels, &r.res);
+        std::array<int64_t, 3> base;
+        bool fits = true;
+        {
+            std::unique_lock<std::mutex> lk(sh.mu);
+            sh.cv.wait(lk, [&] { return sh.sized_upto == k; });
+            base = sh.base[k];
+            for (int l = 0; l < 3; l++) {
+                sh.base[k + 1][l] = base[l] + (r.rc ? 0 : sub->list_tuples[l]);
+                if ((size_t) sh.base[k + 1][l] * sizeof(mb::Pair) > c->h_pipe_out[l].cap) fits = false;
+            }
+            if (!fits) sh.overflow = true;
+            fits = fits && !sh.overflow;
+            sh.sized_upto = k + 1;
+            sh.cv.notify_all();
+        }
+        if (!r.rc && fits) r.rc = pipe_download(c, sub, base);
+        if (r.rc) r.err = g_err;
+    };
+    {
+        std::vector<std::thread> th;
+        for (int k = 1; k < K; k++) th.emplace_back(work, k);
+        work(0);
+        for (std::thread &t : th) t.join();
+    }
+    for (PipeRun &r : runs)
+        if (r.rc) return fail("%s", r.err.c_str());
+    if (sh.overflow) {  // first call (or a larger batch than any before): size the pinned lists, fetch again
+        for (int l = 0; l < 3; l++)
+            if (c->h_pipe_out[l].ensure((size_t) (sh.base[K][l] + sh.base[K][l] / 4 + 1024) * sizeof(mb::Pair))) return 1;
+        for (int k = 0; k < K; k++)
+            if (pipe_download(c, c->subs[k], sh.base[k])) return 1;
+    }
+    // ---- offsets of the whole batch, counters
+    if (c->h_pipe_off.ensure((size_t) 3 * (n + 1) * sizeof(int64_t))) return 1;
+    int64_t *off = c->h_pipe_off.as<int64_t>();
+    memset(out, 0, sizeof(*out));
+    for (int l = 0; l < 3; l++) {
+        for (int k = 0; k < K; k++) {
+            const int64_t *so = c->subs[k]->h_off.as<int64_t>() + (size_t) l * (runs[k].n + 1);
+            for (int64_t i = 0; i < runs[k].n; i++) off[(size_t) l * (n + 1) + runs[k].first + i] = sh.base[k][l] + so[i];
+        }
+        off[(size_t) l * (n + 1) + n] = sh.base[K][l];
+        out->pairs[l] = c->h_pipe_out[l].as<margin_b200_pair>();
+        out->off[l] = off + (size_t) l * (n + 1);
+    }
+    out->n = n;
+    for (const PipeRun &r : runs) {
+        out->band_cells += r.res.band_cells;
+        out->diagonals += r.res.diagonals;
+        out->jobs += r.res.jobs;
+        out->segments += r.res.segments;
+        out->tiles += r.res.tiles;
+        out->kernel_launches += r.res.kernel_launches;
+    }
+    CU(cudaEventRecord(c->ev1, c->stream));
+    CU(cudaEventSynchronize(c->ev1));
+    CU(cudaEventElapsedTime(&out->gpu_ms, c->ev0, c->ev1));  // the whole call, copies included
+    c->n_aln = n;
+    c->last_pipelined = true;
+    c->last_k = K;
+    return 0;
+}
+
+}  // namespace
+
 extern "C" int margin_b200_posteriors_batch(margin_b200_ctx *c, const margin_b200_batch *b, int want_indels,
                                             margin_b200_result *out) {
+    if (!c || !b || !out) return fail("margin_b200_posteriors_batch: null argument");
+    c->last_pipelined = false;
+    if (!c->is_sub && c->pipeline_k > 1 && b->n >= 2 && c->have_params) {
+        const int64_t bytes = 12 * b->off_a[b->n] + 2 * (b->off_x[b->n] + b->off_y[b->n]);
+        const int K = (int) std::min<int64_t>(c->pipeline_k, b->n / 2);
+        if (K > 1 && bytes >= c->pipeline_min_bytes) return posteriors_pipelined(c, b, want_indels, out, K);
+    }
     if (margin_b200_upload_batch(c, b)) return 1;
     if (margin_b200_posteriors_resident(c, want_indels, out)) return 1;
     return margin_b200_download_result(c, out);
@@ -1158,6 +1443,18 @@ extern "C" int margin_b200_last_kernel_ms(margin_b200_ctx *c, float *ms, int32_t
     for (int k = 0; k < n_class; k++) {
         ms[k] = 0.f;
         launches[k] = 0;
+    }
+    if (c->last_pipelined) {  // sums over the runs (their kernels overlap, so the sum exceeds the call's device time)
+        std::vector<float> m(n_class);
+        std::vector<int32_t> ln(n_class);
+        for (int r = 0; r < c->last_k; r++) {
+            if (margin_b200_last_kernel_ms(c->subs[r], m.data(), ln.data(), n_class)) return 1;
+            for (int k = 0; k < n_class; k++) {
+                ms[k] += m[k];
+                launches[k] += ln[k];
+            }
+        }
+        return 0;
     }
     for (int i = 0; i < c->ev_used; i++) {
         float t = 0.f;

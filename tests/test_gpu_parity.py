@@ -177,3 +177,34 @@ def test_errors_are_loud(golden_model):
         al.set_params(pm.p.copy(min_diags_between_traceback=30))
     assert len(al.posteriors_batch([])) == 0
     al.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("k", [2, 3, 5])
+def test_pipelined_batch_matches_the_plain_call(oracle, golden_model, monkeypatch, k):
+    """margin_b200_posteriors_batch cut into k overlapping runs (sub-contexts, own streams) returns the same lists in
+    the same contiguous layout as the unpipelined call, and both match the oracle."""
+    from margin_b200.aligner import PairHmmAligner
+    pm = golden_model("r94g360")
+    p = pm.p.copy(min_diags_between_traceback=300)
+    rng = np.random.default_rng(77)
+    items = [gen.random_case(rng, int(rng.integers(1, 1500))) for _ in range(23)]
+    items.insert(4, (np.zeros(0, np.uint16), items[0][1], np.zeros((0, 3), np.int32), 0, 0, 0))  # an empty sequence
+    monkeypatch.setenv("MARGIN_B200_PIPELINE", "1")
+    plain = PairHmmAligner(pm.models, p, device=0)
+    want = plain.posteriors_batch(items, True)
+    plain.close()
+    monkeypatch.setenv("MARGIN_B200_PIPELINE", str(k))
+    monkeypatch.setenv("MARGIN_B200_PIPELINE_MIN_BYTES", "0")
+    al = PairHmmAligner(pm.models, p, device=0)
+    for _ in range(2):  # the second call reuses the pinned lists sized by the first
+        got = al.posteriors_batch(items, True)
+        assert len(got) == len(items)
+        for i in range(len(items)):
+            compare_lists(got[i], want[i], tol_w=1)  # tile cuts differ between the two calls
+        assert got.stats["band_cells"] == want.stats["band_cells"]
+    for i in (0, 4, 11, 23):
+        it = items[i]
+        ref = oracle.posteriors(pm.models[it[3]], p, it[0], it[1], it[2], it[4], it[5], 1)
+        compare_lists(got[i], ref, tol_w=1)
+    al.close()
