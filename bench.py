@@ -128,7 +128,8 @@ def dist_setup(n_gpus):
         backend = "nccl" if torch.cuda.is_available() else "gloo"
         if backend == "nccl":
             torch.cuda.set_device(local)
-        dist_mod.init_process_group(backend=backend, rank=rank, world_size=world)
+        kw = {"device_id": torch.device("cuda", local)} if backend == "nccl" else {}
+        dist_mod.init_process_group(backend=backend, rank=rank, world_size=world, **kw)
         dist = dist_mod
     return rank, local, world, dist
 
@@ -212,9 +213,101 @@ def pin_batch(batch):
     """Page-locks the batch's host arrays (cudaHostRegister) so that the e2e leg copies from pinned memory."""
     import torch
     rt = torch.cuda.cudart()
-    for a in (batch.sym_x, batch.sym_y, batch.anchors, batch.off_x, batch.off_y, batch.off_a):
+    arrays = [batch.sym_x, batch.sym_y, batch.anchors, batch.off_x, batch.off_y, batch.off_a]
+    if batch.compact:
+        arrays.append(batch.anchors_delta)
+    for a in arrays:
         if a.nbytes:
             rt.cudaHostRegister(a.ctypes.data, a.nbytes, 0)
+
+
+def time_polish(threads):
+    """End-to-end `margin polish` on the bundled ONT region (BASELINE configs[0]; 0.1 Mb of contig): the reference's
+    CLI linked against this library (oracle/_ref/margin_b200cli) and the unmodified reference (oracle/_ref/margin_ref)
+    with -t threads each.  Both binaries and the data are built/copied by oracle/Makefile where /root/reference
+    exists and travel to the GPU box; returns None when they did not."""
+    import hashlib
+    import subprocess
+    import tempfile
+    ref = os.path.join(ROOT, "oracle", "_ref")
+    data = os.path.join(ref, "data")
+    bam = os.path.join(data, "HG002.r94g360.chr20_59M_100k.bam")
+    if not (os.path.exists(os.path.join(ref, "margin_b200cli")) and os.path.exists(bam)):
+        return None
+    out = {"region": "HG002 chr20:59M 100 kb, ont r9.4 g360 params", "contig_mb": 0.1, "threads": threads}
+    with tempfile.TemporaryDirectory() as tmp:
+        for key, binary in (("reference", "margin_ref"), ("b200", "margin_b200cli")):
+            if not os.path.exists(os.path.join(ref, binary)):
+                continue
+            prefix = os.path.join(tmp, key)
+            cmd = [os.path.join(ref, binary), "polish", bam, os.path.join(data, "hg38.chr20_59M_100k.fa"),
+                   os.path.join(data, "params", "polish", "ont", "r9.4", "allParams.np.human.r94-g360.json"),
+                   "-t", str(threads), "-o", prefix]
+            t0 = time.perf_counter()
+            r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=1500)
+            dt = time.perf_counter() - t0
+            if r.returncode != 0:
+                out[key] = {"error": r.stdout[-300:]}
+                continue
+            with open(prefix + ".fa", "rb") as fh:
+                md5 = hashlib.md5(fh.read()).hexdigest()
+            out[key] = {"wall_s": dt, "mb_per_hour": 0.1 / dt * 3600.0, "fasta_md5": md5}
+    if "reference" in out and "b200" in out and "fasta_md5" in out["reference"] and "fasta_md5" in out["b200"]:
+        out["byte_identical"] = out["reference"]["fasta_md5"] == out["b200"]["fasta_md5"]
+    return out
+
+
+def abi_mod():
+    from margin_b200 import abi
+    return abi
+
+
+def time_sustained(pm, batch, device, cell_passes_rank, contexts=3, rounds=4):
+    """`contexts` aligner contexts on one GPU, one host thread each, every thread pushes `rounds` chunks (the bench
+    chunk, host buffers in, host lists out) through margin_b200_posteriors_batch back to back."""
+    from margin_b200.aligner import PairHmmAligner
+    als = [PairHmmAligner(pm.models, pm.p, device=device) for _ in range(contexts)]
+    for al in als:
+        if batch.compact:
+            al.set_pair_format(abi_mod().PAIRS_PACKED64)
+    warm = threading.Barrier(contexts)
+
+    def warm_up(al):  # sizes the arenas of both call paths (alone on the device / beside another context)
+        al.posteriors_host(batch, True)
+        warm.wait()
+        al.posteriors_host(batch, True)
+
+    ws = [threading.Thread(target=warm_up, args=(al,)) for al in als]
+    for t in ws:
+        t.start()
+    for t in ws:
+        t.join()
+    start = threading.Barrier(contexts + 1)
+    errs = []
+
+    def worker(al):
+        try:
+            start.wait()
+            for _ in range(rounds):
+                al.posteriors_host(batch, True)
+        except Exception as e:  # noqa: BLE001
+            errs.append(e)
+
+    ths = [threading.Thread(target=worker, args=(al,)) for al in als]
+    for t in ths:
+        t.start()
+    start.wait()
+    t0 = time.perf_counter()
+    for t in ths:
+        t.join()
+    dt = time.perf_counter() - t0
+    for al in als:
+        al.close()
+    if errs:
+        raise errs[0]
+    n = contexts * rounds
+    return {"value": n * cell_passes_rank / dt * 1e-9, "unit": UNIT, "contexts": contexts, "chunks": n,
+            "ms_per_chunk": dt / n * 1e3}
 
 
 def main_ours(args):
@@ -230,9 +323,12 @@ def main_ours(args):
     peaks = load_peaks()
 
     pm, items = build_items(args.workload, args.seed + rank)  # every rank polishes its own chunk
-    batch = abi.Batch(items)
+    # the boundary formats a host program uses (include/margin_b200.h): 4-byte anchor steps in, 8-byte tuples out
+    batch = abi.Batch(items, compact=not args.plain_formats)
     pin_batch(batch)
     al = PairHmmAligner(pm.models, pm.p, device=local)
+    if not args.plain_formats:
+        al.set_pair_format(abi.PAIRS_PACKED64)
     flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
 
     def l2_flush():
@@ -290,7 +386,15 @@ def main_ours(args):
     e2e_s -= (time.perf_counter() - t0) / e2e_steps
     e2e_s = reduce_scalar(dist, e2e_s, "MAX", dev)
     e2e_value = cell_passes / e2e_s * 1e-9
-    d2h = int(res["tuples"]) * 12 + 3 * (batch.n + 1) * 8
+    d2h = int(res["tuples"]) * int(res["tuple_bytes"]) + 3 * (batch.n + 1) * 8
+
+    # ---- sustained end-to-end: two contexts on this GPU, each sweeping chunk after chunk from host buffers, so that one
+    # chunk's copies overlap the other's kernels (what the chunk scheduler does with contexts_per_gpu = 2)
+    sustained = None
+    if not args.no_sustained:
+        sustained = time_sustained(pm, batch, local, cell_passes_rank=2.0 * cells, contexts=3, rounds=4)
+        if dist is not None:
+            sustained["value"] = reduce_scalar(dist, sustained["value"], "SUM", dev)
 
     # ---- roofline of the dominant kernel (CUDA events around each launch, same timed region)
     dom = max(ktimes.items(), key=lambda kv: kv[1][0])[0] if ktimes else "none"
@@ -304,10 +408,11 @@ def main_ours(args):
         "config": {"workload": args.workload, "seed": args.seed, "reads_per_chunk": batch.n, "chunks_per_gpu": 1,
                    "band_cells_per_chunk": int(cells), "diagonals": int(st["diagonals"]),
                    "segments": int(st["segments"]), "params": "ont/r9.4 r94-g360 (RLE, repeat counts)",
-                   "l2": "flushed between steps (512 MiB write)", "wall_ms_per_step_incl_flush": t_wall / args.steps * 1e3},
+                   "l2": "flushed between steps (512 MiB write)",
+                   "boundary_formats": "plain" if args.plain_formats else "anchor steps 4 B, tuples 8 B", "wall_ms_per_step_incl_flush": t_wall / args.steps * 1e3},
         "clocks": clocks,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": batch.h2d_bytes, "d2h_bytes_per_step": d2h,
-                "ms_per_step": e2e_s * 1e3},
+                "ms_per_step": e2e_s * 1e3, "sustained_three_contexts": sustained},
         "gpu_launches": launches,
         "kernel_ms_per_step": {k: v[0] / args.steps for k, v in ktimes.items() if v[1]},
         "roofline": roof,
@@ -316,6 +421,8 @@ def main_ours(args):
         r = time_reference(pm, items, 1, 1, host_cores())
         line["cpu_baseline"] = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": r["kind"],
                                 "sample": r["sample"]}
+    if rank == 0 and world == 1 and args.polish:
+        line["polish"] = time_polish(min(host_cores(), 8))
     if rank == 0:
         print(json.dumps(line), flush=True)
     al.close()
@@ -370,6 +477,12 @@ def main():
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD)
     ap.add_argument("--seed", type=int, default=42)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--plain-formats", action="store_true",
+                    help="12-byte anchor triples in, 12-byte tuple records out instead of the compact boundary formats")
+    ap.add_argument("--no-sustained", action="store_true", help="skip the two-context sustained end-to-end leg")
+    ap.add_argument("--polish", action="store_true",
+                    help="also time `margin polish` on the bundled region: reference CLI vs the CLI linked against "
+                         "this library (oracle/_ref, built where /root/reference exists)")
     args = ap.parse_args()
     if args.impl == "reference":
         return main_reference(args)

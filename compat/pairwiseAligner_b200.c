@@ -68,6 +68,8 @@ static margin_b200_ctx *b200_ctx(void) {
         int n = margin_b200_device_count();
         if (n <= 0) st_errAbort("margin_b200: no CUDA device; this build of margin has no CPU aligner\n");
         if (margin_b200_create(&tls.ctx, omp_get_thread_num() % n) != 0) b200_fail();
+        /* 8-byte tuples over PCIe; b200_list() unpacks them while it builds the stIntTuples */
+        if (margin_b200_set_pair_format(tls.ctx, MARGIN_B200_PAIRS_PACKED64) != 0) b200_fail();
     }
     return tls.ctx;
 }
@@ -139,12 +141,15 @@ typedef struct {
     int64_t n, capX, capY, capA;
     uint16_t *symX, *symY;
     int32_t *anchors;
+    uint32_t *anchorsDelta; /* the compact words of margin_b200_batch.anchors_delta, kept beside the triples */
+    int compactOk;          /* every anchor so far fits a compact word */
     int64_t *offX, *offY, *offA;
     uint8_t *slot, *raggedL, *raggedR;
 } B200Batch;
 
 static B200Batch *b200_batch_construct(int64_t n) {
     B200Batch *b = st_calloc(1, sizeof(B200Batch));
+    b->compactOk = 1;
     b->offX = st_calloc(n + 1, sizeof(int64_t));
     b->offY = st_calloc(n + 1, sizeof(int64_t));
     b->offA = st_calloc(n + 1, sizeof(int64_t));
@@ -158,6 +163,7 @@ static void b200_batch_destruct(B200Batch *b) {
     free(b->symX);
     free(b->symY);
     free(b->anchors);
+    free(b->anchorsDelta);
     free(b->offX);
     free(b->offY);
     free(b->offA);
@@ -184,6 +190,7 @@ static void b200_batch_add(B200Batch *b, SymbolString sX, SymbolString sY, stLis
     if (oA + nA > b->capA) {
         b->capA = (oA + nA) * 2 + 1024;
         b->anchors = st_realloc(b->anchors, b->capA * 3 * sizeof(int32_t));
+        b->anchorsDelta = st_realloc(b->anchorsDelta, b->capA * sizeof(uint32_t));
     }
     memcpy(b->symX + oX, sX.sequence, sX.length * sizeof(uint16_t)); /* Symbol is uint16_t, inc/stateMachine.h:15 */
     memcpy(b->symY + oY, sY.sequence, sY.length * sizeof(uint16_t));
@@ -194,6 +201,12 @@ static void b200_batch_add(B200Batch *b, SymbolString sX, SymbolString sY, stLis
         /* anchors may come as pairs (x, y): band_construct then uses p->diagonalExpansion and never reads a third field */
         b->anchors[3 * (oA + k) + 2] =
                 (tls.params.dynamicAnchorExpansion && stIntTuple_length(a) > 2) ? (int32_t) stIntTuple_get(a, 2) : 0;
+        /* the same anchor as a 4-byte step from its predecessor: a third of the bytes over PCIe */
+        int64_t px = k > 0 ? b->anchors[3 * (oA + k - 1)] : -1, py = k > 0 ? b->anchors[3 * (oA + k - 1) + 1] : -1;
+        uint32_t w = margin_b200_pack_anchor(b->anchors[3 * (oA + k)] - px, b->anchors[3 * (oA + k) + 1] - py,
+                                             b->anchors[3 * (oA + k) + 2]);
+        if (w == 0) b->compactOk = 0;
+        b->anchorsDelta[oA + k] = w;
     }
     b->offX[i + 1] = oX + sX.length;
     b->offY[i + 1] = oY + sY.length;
@@ -207,12 +220,14 @@ static void b200_batch_run(B200Batch *b, int wantIndels, margin_b200_result *res
     margin_b200_batch mb;
     uint16_t dummyS = 0;
     int32_t dummyA[3] = {0, 0, 0};
+    memset(&mb, 0, sizeof(mb));
     mb.n = b->n;
     mb.sym_x = b->symX ? b->symX : &dummyS;
     mb.off_x = b->offX;
     mb.sym_y = b->symY ? b->symY : &dummyS;
     mb.off_y = b->offY;
     mb.anchors = b->anchors ? b->anchors : dummyA;
+    if (b->compactOk && b->anchorsDelta) mb.anchors_delta = b->anchorsDelta; /* takes precedence over the triples */
     mb.off_a = b->offA;
     mb.model_slot = b->slot;
     mb.ragged_left = b->raggedL;
@@ -223,6 +238,14 @@ static void b200_batch_run(B200Batch *b, int wantIndels, margin_b200_result *res
 /* List l of alignment i as an stList of stIntTuple(weight, x + shiftX, y), the reference's own representation. */
 static stList *b200_list(const margin_b200_result *res, int l, int64_t i, int64_t shiftX) {
     stList *out = stList_construct3(0, (void (*)(void *)) stIntTuple_destruct);
+    if (res->pair_format == MARGIN_B200_PAIRS_PACKED64) {
+        const uint64_t *v = (const uint64_t *) res->pairs[l];
+        for (int64_t k = res->off[l][i]; k < res->off[l][i + 1]; k++) {
+            margin_b200_pair q = margin_b200_unpack_pair(v[k]);
+            stList_append(out, stIntTuple_construct3(q.w, (int64_t) q.x + shiftX, q.y));
+        }
+        return out;
+    }
     const margin_b200_pair *p = res->pairs[l];
     for (int64_t k = res->off[l][i]; k < res->off[l][i + 1]; k++) {
         stList_append(out, stIntTuple_construct3(p[k].w, (int64_t) p[k].x + shiftX, p[k].y));

@@ -93,7 +93,22 @@ typedef struct margin_b200_batch {
     const uint8_t *model_slot;
     const uint8_t *ragged_left;
     const uint8_t *ragged_right;
+    /* Optional compact form of the anchors (NULL = use `anchors`): one 32-bit word per anchor,
+     *   bits 0-11  x - x_prev   (x_prev = -1 before an alignment's first anchor, so the field is >= 1)
+     *   bits 12-23 y - y_prev   (likewise)
+     *   bits 24-31 expansion / 2
+     * with the same off_a.  A host program that walks the reference's stList of stIntTuple anchors anyway
+     * (compat/pairwiseAligner_b200.c) emits this instead of triples and moves a third of the bytes over PCIe; the
+     * device expands it back to triples.  A batch with a step >= 4096 or an expansion >= 512 must use `anchors`
+     * (the margin_b200_pack_anchor helper below returns 0 for such an anchor). */
+    const uint32_t *anchors_delta;
 } margin_b200_batch;
+
+/* The compact anchor word, or 0 when the anchor does not fit (dx, dy in 1..4095, expansion even in 0..510). */
+static inline uint32_t margin_b200_pack_anchor(int64_t dx, int64_t dy, int64_t expansion) {
+    if (dx < 1 || dx > 4095 || dy < 1 || dy > 4095 || expansion < 0 || expansion > 510 || (expansion & 1)) return 0;
+    return (uint32_t) dx | ((uint32_t) dy << 12) | ((uint32_t) (expansion / 2) << 24);
+}
 
 /* One posterior tuple, same meaning as the reference's stIntTuple (weight, x, y)
  * (impl/pairwiseAligner.c:598-608): weight = floor(p * 1e7), x/y 0-based, gap
@@ -101,6 +116,20 @@ typedef struct margin_b200_batch {
 typedef struct margin_b200_pair {
     int32_t w, x, y;
 } margin_b200_pair;
+
+/* Tuple formats of a result (margin_b200_set_pair_format).  PACKED64 carries the same tuple in one 64-bit word,
+ *   bits 0-23 weight, bits 24-43 x + 1, bits 44-63 y + 1,
+ * which moves 8 instead of 12 bytes per tuple to the host; it needs every sequence of the batch to be shorter than
+ * 2^20 - 1 symbols, otherwise the call falls back to TRIPLES and says so in margin_b200_result.pair_format. */
+enum { MARGIN_B200_PAIRS_TRIPLES = 0, MARGIN_B200_PAIRS_PACKED64 = 1 };
+
+static inline margin_b200_pair margin_b200_unpack_pair(uint64_t v) {
+    margin_b200_pair p;
+    p.w = (int32_t) (v & 0xffffffu);
+    p.x = (int32_t) ((v >> 24) & 0xfffffu) - 1;
+    p.y = (int32_t) (v >> 44) - 1;
+    return p;
+}
 
 /* Result of a posterior batch.  Memory is pinned host memory owned by the
  * context and valid until the next call on the same context.  List l of
@@ -119,6 +148,8 @@ typedef struct margin_b200_result {
     float gpu_ms;            /* device time of this call (CUDA events) */
     int32_t kernel_launches; /* kernels launched by this call */
     int64_t tiles;           /* independent forward/backward work units the segments were cut into */
+    int32_t pair_format;     /* MARGIN_B200_PAIRS_*: with PACKED64, pairs[l] points at uint64_t words */
+    int32_t reserved;
 } margin_b200_result;
 
 typedef struct margin_b200_ctx margin_b200_ctx;
@@ -134,6 +165,8 @@ int margin_b200_version(void);
 
 int margin_b200_set_model(margin_b200_ctx *ctx, int slot, const margin_b200_model *model);
 int margin_b200_set_params(margin_b200_ctx *ctx, const margin_b200_params *params);
+/* Tuple format of the results of this context (default MARGIN_B200_PAIRS_TRIPLES). */
+int margin_b200_set_pair_format(margin_b200_ctx *ctx, int format);
 
 /* Banded forward/backward/posterior for every alignment of the batch. */
 int margin_b200_posteriors_batch(margin_b200_ctx *ctx, const margin_b200_batch *batch, int want_indels,

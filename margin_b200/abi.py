@@ -71,10 +71,40 @@ class BatchStruct(C.Structure):
         ("model_slot", C.c_void_p),
         ("ragged_left", C.c_void_p),
         ("ragged_right", C.c_void_p),
+        ("anchors_delta", C.c_void_p),
     ]
 
 
 PAIR_DTYPE = np.dtype([("w", "<i4"), ("x", "<i4"), ("y", "<i4")])
+PAIRS_TRIPLES, PAIRS_PACKED64 = 0, 1  # MARGIN_B200_PAIRS_*
+
+
+def unpack_pairs(words):
+    """MARGIN_B200_PAIRS_PACKED64 words -> (w, x, y) records (margin_b200_unpack_pair)."""
+    words = np.asarray(words, dtype=np.uint64)
+    out = np.empty(len(words), dtype=PAIR_DTYPE)
+    out["w"] = (words & np.uint64(0xffffff)).astype(np.int32)
+    out["x"] = ((words >> np.uint64(24)) & np.uint64(0xfffff)).astype(np.int32) - 1
+    out["y"] = (words >> np.uint64(44)).astype(np.int32) - 1
+    return out
+
+
+def pack_anchors_delta(anchors, off_a):
+    """(x, y, expansion) triples -> the compact words of margin_b200_batch.anchors_delta (margin_b200_pack_anchor),
+    or None when some anchor does not fit (step >= 4096, expansion >= 512 or odd)."""
+    a = np.asarray(anchors, dtype=np.int64).reshape(-1, 3)
+    if len(a) == 0:
+        return np.zeros(1, np.uint32)
+    prev = np.empty((len(a), 2), np.int64)
+    prev[1:] = a[:-1, :2]
+    first = np.asarray(off_a[:-1], dtype=np.int64)
+    first = first[first < len(a)]
+    prev[first] = -1
+    d = a[:, :2] - prev
+    e = a[:, 2]
+    if (d < 1).any() or (d > 4095).any() or (e < 0).any() or (e > 510).any() or (e & 1).any():
+        return None
+    return (d[:, 0] | (d[:, 1] << 12) | ((e // 2) << 24)).astype(np.uint32)
 
 
 class ResultStruct(C.Structure):
@@ -89,6 +119,8 @@ class ResultStruct(C.Structure):
         ("gpu_ms", C.c_float),
         ("kernel_launches", C.c_int32),
         ("tiles", C.c_int64),
+        ("pair_format", C.c_int32),
+        ("reserved", C.c_int32),
     ]
 
 
@@ -98,9 +130,10 @@ class Batch:
     Each item: (sym_x uint16[], sym_y uint16[], anchors int32[k,3], model_slot, ragged_left, ragged_right).
     """
 
-    def __init__(self, items):
+    def __init__(self, items, compact=False):
         n = len(items)
         self.n = n
+        self.compact = False
         lx = np.array([len(it[0]) for it in items], dtype=np.int64)
         ly = np.array([len(it[1]) for it in items], dtype=np.int64)
         la = np.array([len(it[2]) for it in items], dtype=np.int64)
@@ -118,7 +151,20 @@ class Batch:
         self.struct = BatchStruct(
             n, self.sym_x.ctypes.data, self.off_x.ctypes.data, self.sym_y.ctypes.data, self.off_y.ctypes.data,
             self.anchors.ctypes.data, self.off_a.ctypes.data, self.model_slot.ctypes.data,
-            self.ragged_left.ctypes.data, self.ragged_right.ctypes.data)
+            self.ragged_left.ctypes.data, self.ragged_right.ctypes.data, None)
+        if compact:
+            self.use_compact_anchors()
+
+    def use_compact_anchors(self):
+        """Switches the batch to the 4-byte anchor words (what a C host emits while walking its anchor lists); keeps
+        the triples when some anchor does not fit.  Returns whether the compact form is in use."""
+        d = pack_anchors_delta(self.anchors, self.off_a) if self.n else None
+        if d is None:
+            return False
+        self.anchors_delta = np.ascontiguousarray(d)
+        self.struct.anchors_delta = self.anchors_delta.ctypes.data  # takes precedence; the triples stay for the oracle
+        self.compact = True
+        return True
 
     def item(self, i):
         return (self.sym_x[self.off_x[i]:self.off_x[i + 1]], self.sym_y[self.off_y[i]:self.off_y[i + 1]],
@@ -127,7 +173,8 @@ class Batch:
 
     @property
     def h2d_bytes(self):
-        return int(self.sym_x.nbytes + self.sym_y.nbytes + self.anchors.nbytes + 3 * self.off_x.nbytes + 3 * self.n)
+        anchors = self.anchors_delta.nbytes if self.compact else self.anchors.nbytes
+        return int(self.sym_x.nbytes + self.sym_y.nbytes + anchors + 3 * self.off_x.nbytes + 3 * self.n)
 
 
 _LIB = None
@@ -160,6 +207,8 @@ def load_library():
     lib.margin_b200_set_model.restype = i32
     lib.margin_b200_set_params.argtypes = [vp, C.POINTER(Params)]
     lib.margin_b200_set_params.restype = i32
+    lib.margin_b200_set_pair_format.argtypes = [vp, i32]
+    lib.margin_b200_set_pair_format.restype = i32
     lib.margin_b200_posteriors_batch.argtypes = [vp, C.POINTER(BatchStruct), i32, C.POINTER(ResultStruct)]
     lib.margin_b200_posteriors_batch.restype = i32
     lib.margin_b200_upload_batch.argtypes = [vp, C.POINTER(BatchStruct)]
@@ -182,7 +231,7 @@ def load_library():
 
 EXPORTED_SYMBOLS = [
     "margin_b200_create", "margin_b200_destroy", "margin_b200_last_error", "margin_b200_version",
-    "margin_b200_set_model", "margin_b200_set_params", "margin_b200_posteriors_batch",
+    "margin_b200_set_model", "margin_b200_set_params", "margin_b200_set_pair_format", "margin_b200_posteriors_batch",
     "margin_b200_upload_batch", "margin_b200_posteriors_resident", "margin_b200_download_result",
     "margin_b200_forward_batch", "margin_b200_forward_resident", "margin_b200_bands",
     "margin_b200_last_kernel_ms", "margin_b200_device_count",

@@ -76,6 +76,10 @@ class PairHmmAligner:
         self.params = params.copy()
         self._check(self.lib.margin_b200_set_params(self._h, C.byref(self.params)))
 
+    def set_pair_format(self, fmt):
+        """abi.PAIRS_TRIPLES (12-byte records) or abi.PAIRS_PACKED64 (8-byte words, include/margin_b200.h)."""
+        self._check(self.lib.margin_b200_set_pair_format(self._h, int(fmt)))
+
     # ------------------------------------------------------------- batched calls
     def _collect(self, res, n, want_lists=True):
         lists = []
@@ -84,7 +88,10 @@ class PairHmmAligner:
             for l in range(3):
                 off = np.ctypeslib.as_array(C.cast(res.off[l], C.POINTER(C.c_int64)), shape=(n + 1,)).copy()
                 tot = int(off[n])
-                if tot:
+                if tot and res.pair_format == abi.PAIRS_PACKED64:
+                    buf = (C.c_char * (tot * 8)).from_address(res.pairs[l])
+                    arrs.append(abi.unpack_pairs(np.frombuffer(buf, dtype=np.uint64)))
+                elif tot:
                     buf = (C.c_char * (tot * 12)).from_address(res.pairs[l])
                     arrs.append(np.frombuffer(buf, dtype=abi.PAIR_DTYPE).copy())
                 else:
@@ -109,6 +116,7 @@ class PairHmmAligner:
         out = _stats(res)
         n = batch.n
         out["tuples"] = sum(int(C.cast(res.off[l], C.POINTER(C.c_int64))[n]) for l in range(3)) if n else 0
+        out["tuple_bytes"] = 8 if res.pair_format == abi.PAIRS_PACKED64 else 12
         return out
 
     def arithmetic(self):

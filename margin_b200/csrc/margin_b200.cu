@@ -5,6 +5,7 @@
 // There is no CPU fallback anywhere in this file: without a usable device every entry point fails.
 #include <algorithm>
 #include <array>
+#include <atomic>
 #include <chrono>
 #include <cmath>
 #include <cstdarg>
@@ -36,6 +37,9 @@ int fail(const char *fmt, ...) {
     g_err = buf;
     return 1;
 }
+
+constexpr int kMaxDevices = 64;
+std::atomic<int> g_live_contexts[kMaxDevices];  // top-level contexts per device (sub-contexts of a pipeline excluded)
 
 #define CU(call)                                                                                        \
     do {                                                                                                \
@@ -133,9 +137,13 @@ struct margin_b200_ctx {
     std::vector<margin_b200_ctx *> subs;
     std::unique_ptr<margin_b200_model> user_models[2];  // as given to set_model, replayed into new sub-contexts
     int pipeline_k = 3;                                 // MARGIN_B200_PIPELINE (1 = off)
+    bool pipeline_force = false;                        // MARGIN_B200_PIPELINE_FORCE: pipeline even beside other contexts
     int pipe_fill = 2;                                  // MARGIN_B200_PIPE_FILL: SM share a run's tiles are cut for, in 1/K
     int64_t pipeline_min_bytes = 8 << 20;               // MARGIN_B200_PIPELINE_MIN_BYTES of host input
-    bool is_sub = false, last_pipelined = false;
+    bool is_sub = false, last_pipelined = false, counted = false;
+    int pair_format = MARGIN_B200_PAIRS_TRIPLES;        // what the caller asked for
+    bool packed_now = false;                            // ... and what this batch gets (sequence lengths permitting)
+    DevBuf d_anchors_delta;
     int last_k = 0;
     PinBuf h_pipe_out[3], h_pipe_off;
     std::function<void()> after_h2d_enqueue;            // fired once the batch's host->device copies are queued
@@ -220,6 +228,49 @@ struct Trace {
     }
 };
 
+// ---- control transfers
+// Small host<->device transfers (job tables, band counters, tile lists, offsets) do NOT go through cudaMemcpyAsync: a
+// copy engine serves its queue in order, so a 30 KB read-back queued behind another context's (or another pipelined
+// run's) 100 MB list transfer waits for all of it and stalls the kernels that depend on it (measured: band phase
+// 0.26 -> 1.85 ms with a second context downloading).  A copy kernel moves them over the same PCIe link directly
+// between device memory and pinned host memory (cudaMallocHost memory is device-accessible under UVA).
+__global__ void ctl_copy_kernel(uint32_t *__restrict__ dst, const uint32_t *__restrict__ src, size_t n_words) {
+    const size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t n4 = n_words / 4;
+    if (i < n4) {
+        if (((uintptr_t) dst | (uintptr_t) src) % 16 == 0) {
+            reinterpret_cast<uint4 *>(dst)[i] = reinterpret_cast<const uint4 *>(src)[i];
+        } else {
+            for (int k = 0; k < 4; k++) dst[4 * i + k] = src[4 * i + k];
+        }
+    }
+    if (i < n_words - 4 * n4) dst[4 * n4 + i] = src[4 * n4 + i];
+}
+
+// bytes must be a multiple of 4; one of dst / src is pinned host memory, the other device memory
+int ctl_copy(cudaStream_t stream, void *dst, const void *src, size_t bytes) {
+    if (bytes == 0) return 0;
+    if (bytes % 4) return fail("internal error: control copy of %zu bytes", bytes);
+    const size_t words = bytes / 4, threads = std::max<size_t>(1, (words + 3) / 4);
+    ctl_copy_kernel<<<(unsigned) ((threads + 255) / 256), 256, 0, stream>>>(reinterpret_cast<uint32_t *>(dst),
+                                                                         reinterpret_cast<const uint32_t *>(src), words);
+    CU(cudaGetLastError());
+    return 0;
+}
+
+__global__ void ctl_fill_status_kernel(int32_t *status, int64_t n) {
+    const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) {
+        status[2 * i] = 0x7fffffff;
+        status[2 * i + 1] = 0;
+    }
+}
+
+// bounds[l] = seg_off[l * S] for l = 0..3, written straight to pinned host memory
+__global__ void ctl_bounds_kernel(const int64_t *__restrict__ seg_off, int S, int64_t *__restrict__ bounds) {
+    if (threadIdx.x < 4) bounds[threadIdx.x] = seg_off[(size_t) threadIdx.x * S];
+}
+
 int check_device(int device) {
     int count = 0;
     cudaError_t e = cudaGetDeviceCount(&count);
@@ -260,6 +311,7 @@ int margin_b200_create(margin_b200_ctx **out, int device) {
         c->tile_len_fixed = true;
     }
     if (const char *e = getenv("MARGIN_B200_PIPELINE")) c->pipeline_k = std::max(1, std::min(16, atoi(e)));
+    if (const char *e = getenv("MARGIN_B200_PIPELINE_FORCE")) c->pipeline_force = atoi(e) != 0;
     if (const char *e = getenv("MARGIN_B200_PIPE_FILL")) c->pipe_fill = std::max(1, std::min(16, atoi(e)));
     if (const char *e = getenv("MARGIN_B200_PIPELINE_MIN_BYTES")) c->pipeline_min_bytes = std::max(0ll, atoll(e));
     if (const char *e = getenv("MARGIN_B200_TILE_MAX")) c->tile_len = std::max(200, atoi(e) / 10 * 10);
@@ -272,6 +324,8 @@ int margin_b200_create(margin_b200_ctx **out, int device) {
         c->bwd_slots = sms * per_sm * (kTileThreads / 8);
     }
     if (const char *e = getenv("MARGIN_B200_WARMUP")) c->warmup = std::max(1, atoi(e));
+    c->counted = true;
+    g_live_contexts[device & (kMaxDevices - 1)].fetch_add(1);
     *out = c;
     return 0;
 }
@@ -280,6 +334,7 @@ void margin_b200_destroy(margin_b200_ctx *c) {
     if (!c) return;
     for (margin_b200_ctx *sub : c->subs) margin_b200_destroy(sub);
     c->subs.clear();
+    if (c->counted) g_live_contexts[c->device & (kMaxDevices - 1)].fetch_sub(1);
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     DevBuf *bufs[] = {&c->d_models, &c->d_rsm[0], &c->d_rsm[1], &c->d_symx, &c->d_symy, &c->d_anchors, &c->d_jobs,
@@ -288,7 +343,7 @@ void margin_b200_destroy(margin_b200_ctx *c) {
                       &c->d_ids, &c->d_aln_first_slot, &c->d_F, &c->d_stage, &c->d_out, &c->d_off_out, &c->d_fwd_out,
                       &c->d_geo, &c->d_tiles, &c->d_bnd, &c->d_slot_bnd_off, &c->d_emit5[0], &c->d_emit5[1],
                       &c->d_px, &c->d_py, &c->d_stage2, &c->d_chunks, &c->d_job_first_chunk, &c->d_chunk_sum, &c->d_chunk_maxw,
-                      &c->d_totals, &c->d_band_out, &c->d_arena, &c->d_offs, &c->d_status};
+                      &c->d_totals, &c->d_band_out, &c->d_anchors_delta, &c->d_arena, &c->d_offs, &c->d_status};
     for (DevBuf *b : bufs) b->release();
     c->h_stage_in.release();
     c->h_small.release();
@@ -407,6 +462,15 @@ int margin_b200_set_params(margin_b200_ctx *c, const margin_b200_params *p) {
     return 0;
 }
 
+int margin_b200_set_pair_format(margin_b200_ctx *c, int format) {
+    if (!c) return fail("margin_b200_set_pair_format: null context");
+    if (format != MARGIN_B200_PAIRS_TRIPLES && format != MARGIN_B200_PAIRS_PACKED64)
+        return fail("margin_b200_set_pair_format: unknown format %d", format);
+    c->pair_format = format;
+    for (margin_b200_ctx *sub : c->subs) sub->pair_format = format;
+    return 0;
+}
+
 }  // extern "C"
 
 // ------------------------------------------------------------------------------------------------------------------
@@ -480,11 +544,13 @@ extern "C" int margin_b200_upload_batch(margin_b200_ctx *c, const margin_b200_ba
     const int64_t nx = n ? b->off_x[n] : 0, ny = n ? b->off_y[n] : 0;
     // ---- cheap per-alignment checks, then everything that is O(symbols) or O(anchors) happens on the device
     bool used[2] = {false, false};
+    bool fits_packed = true;
     for (int64_t i = 0; i < n; i++) {
         const int64_t lx = b->off_x[i + 1] - b->off_x[i], ly = b->off_y[i + 1] - b->off_y[i];
         const int64_t na = b->off_a[i + 1] - b->off_a[i];
         if (lx < 0 || ly < 0 || na < 0) return fail("alignment %lld: negative length", (long long) i);
         if (lx + ly > (int64_t) 1 << 30) return fail("alignment %lld: sequences too long", (long long) i);
+        if (lx >= (1 << 20) - 1 || ly >= (1 << 20) - 1) fits_packed = false;
         const uint8_t slot = b->model_slot ? b->model_slot[i] : 0;
         if (slot > 1 || !c->have_model[slot]) return fail("alignment %lld: model slot %d has not been set", (long long) i, slot);
         used[slot] = true;
@@ -492,6 +558,7 @@ extern "C" int margin_b200_upload_batch(margin_b200_ctx *c, const margin_b200_ba
     if (used[0] && used[1] && c->host_models[0].rle != c->host_models[1].rle)
         return fail("the two state machines of a batch must both use (or both not use) repeat counts");
     const int rle = c->host_models[used[0] ? 0 : 1].rle;
+    c->packed_now = c->pair_format == MARGIN_B200_PAIRS_PACKED64 && fits_packed;
     c->have_switch = false;
     for (int k = 0; k < 2; k++)
         if (used[k] && (c->host_models[k].t[mb::T_YX] != -INFINITY || c->host_models[k].t[mb::T_XY] != -INFINITY))
@@ -500,24 +567,35 @@ extern "C" int margin_b200_upload_batch(margin_b200_ctx *c, const margin_b200_ba
         c->d_anchors.ensure(((size_t) 3 * total_anchor_triples + 3) * sizeof(int32_t)) ||
         c->d_offs.ensure((size_t) 3 * (n + 1) * sizeof(int64_t)) || c->d_status.ensure(((size_t) 2 * n + 2) * sizeof(int32_t)) ||
         c->d_px.ensure((size_t) nx + 2 * mb::PACK_SLACK) || c->d_py.ensure((size_t) ny + 2 * mb::PACK_SLACK) ||
-        c->d_err.ensure(sizeof(double)) || c->h_small.ensure(((size_t) 2 * n + 4) * sizeof(int32_t)))
+        c->d_err.ensure(sizeof(double)) ||
+        c->h_small.ensure(((size_t) 2 * n + 4) * sizeof(int32_t) + (size_t) 3 * (n + 1) * sizeof(int64_t)))
         return 1;
     if (nx) CU(cudaMemcpyAsync(c->d_symx.p, b->sym_x, nx * sizeof(uint16_t), cudaMemcpyHostToDevice, c->stream));
     if (ny) CU(cudaMemcpyAsync(c->d_symy.p, b->sym_y, ny * sizeof(uint16_t), cudaMemcpyHostToDevice, c->stream));
-    if (total_anchor_triples)
-        CU(cudaMemcpyAsync(c->d_anchors.p, b->anchors, (size_t) 3 * total_anchor_triples * sizeof(int32_t),
-                           cudaMemcpyHostToDevice, c->stream));
+    if (total_anchor_triples) {
+        if (b->anchors_delta) {
+            if (c->d_anchors_delta.ensure((size_t) total_anchor_triples * sizeof(uint32_t))) return 1;
+            CU(cudaMemcpyAsync(c->d_anchors_delta.p, b->anchors_delta, (size_t) total_anchor_triples * sizeof(uint32_t),
+                               cudaMemcpyHostToDevice, c->stream));
+        } else {
+            if (!b->anchors) return fail("margin_b200_upload_batch: the batch has anchor offsets but no anchors");
+            CU(cudaMemcpyAsync(c->d_anchors.p, b->anchors, (size_t) 3 * total_anchor_triples * sizeof(int32_t),
+                               cudaMemcpyHostToDevice, c->stream));
+        }
+    }
+    // pinned staging: [status 2n+2 int32 (read-back)][off_a | off_x | off_y, n+1 int64 each]
     int32_t *h_status = c->h_small.as<int32_t>();
     if (n) {
         int64_t *d_offs = c->d_offs.as<int64_t>();
-        CU(cudaMemcpyAsync(d_offs, b->off_a, (n + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, c->stream));
-        CU(cudaMemcpyAsync(d_offs + (n + 1), b->off_x, (n + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, c->stream));
-        CU(cudaMemcpyAsync(d_offs + 2 * (n + 1), b->off_y, (n + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, c->stream));
-        for (int64_t i = 0; i < n; i++) {
-            h_status[2 * i] = 0x7fffffff;
-            h_status[2 * i + 1] = 0;
-        }
-        CU(cudaMemcpyAsync(c->d_status.p, h_status, (size_t) 2 * n * sizeof(int32_t), cudaMemcpyHostToDevice, c->stream));
+        int64_t *h_offs = reinterpret_cast<int64_t *>(c->h_small.as<char>() + ((size_t) 2 * n + 4) * sizeof(int32_t));
+        memcpy(h_offs, b->off_a, (n + 1) * sizeof(int64_t));
+        memcpy(h_offs + (n + 1), b->off_x, (n + 1) * sizeof(int64_t));
+        memcpy(h_offs + 2 * (n + 1), b->off_y, (n + 1) * sizeof(int64_t));
+        if (ctl_copy(c->stream, d_offs, h_offs, (size_t) 3 * (n + 1) * sizeof(int64_t))) return 1;
+        ctl_fill_status_kernel<<<(unsigned) ((n + 255) / 256), 256, 0, c->stream>>>(c->d_status.as<int32_t>(), n);
+        if (total_anchor_triples && b->anchors_delta)
+            mb::expand_anchors_kernel<256><<<(unsigned) n, 256, 0, c->stream>>>(c->d_anchors_delta.as<uint32_t>(), d_offs,
+                                                                                c->d_anchors.as<int32_t>());
         mb::check_anchors_kernel<<<(unsigned) n, 256, 0, c->stream>>>(c->d_anchors.as<int32_t>(), d_offs, d_offs + (n + 1),
                                                                      d_offs + 2 * (n + 1), p.split_matrix_bigger_than_this,
                                                                      c->d_status.as<int32_t>());
@@ -530,8 +608,8 @@ extern "C" int margin_b200_upload_batch(margin_b200_ctx *c, const margin_b200_ba
             c->d_symx.as<uint16_t>(), c->d_px.as<uint8_t>() + mb::PACK_SLACK, nx, rle, c->d_err.as<int>());
     if (ny) mb::pack_symbols_kernel<<<(unsigned) ((ny + 255) / 256), 256, 0, c->stream>>>(
             c->d_symy.as<uint16_t>(), c->d_py.as<uint8_t>() + mb::PACK_SLACK, ny, rle, c->d_err.as<int>());
-    if (n) CU(cudaMemcpyAsync(h_status, c->d_status.p, (size_t) 2 * n * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
-    CU(cudaMemcpyAsync(h_status + 2 * n, c->d_err.p, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    if (n && ctl_copy(c->stream, h_status, c->d_status.p, (size_t) 2 * n * sizeof(int32_t))) return 1;
+    if (ctl_copy(c->stream, h_status + 2 * n, c->d_err.p, sizeof(int))) return 1;
     tr.mark("enqueue");
     if (c->after_h2d_enqueue) c->after_h2d_enqueue();
     CU(cudaStreamSynchronize(c->stream));
@@ -631,19 +709,27 @@ extern "C" int margin_b200_upload_batch(margin_b200_ctx *c, const margin_b200_ba
         CU(cudaMemcpyAsync(c->d_anchors.as<int32_t>() + 3 * total_anchor_triples, extra_anchors.data(),
                            extra_anchors.size() * sizeof(int32_t), cudaMemcpyHostToDevice, c->stream));
     }
-    if (c->d_jobs.ensure((c->jobs.size() + 1) * sizeof(mb::Job))) return 1;
-    if (!c->jobs.empty())
-        CU(cudaMemcpyAsync(c->d_jobs.p, c->jobs.data(), c->jobs.size() * sizeof(mb::Job), cudaMemcpyHostToDevice, c->stream));
-    if (c->d_chunks.ensure((c->chunks.size() + 1) * sizeof(mb::BandChunk)) ||
+    if (c->d_jobs.ensure((c->jobs.size() + 1) * sizeof(mb::Job)) ||
+        c->d_chunks.ensure((c->chunks.size() + 1) * sizeof(mb::BandChunk)) ||
         c->d_job_first_chunk.ensure((c->jobs.size() + 1) * sizeof(int32_t)))
         return 1;
-    if (!c->chunks.empty())
-        CU(cudaMemcpyAsync(c->d_chunks.p, c->chunks.data(), c->chunks.size() * sizeof(mb::BandChunk), cudaMemcpyHostToDevice,
-                           c->stream));
-    CU(cudaMemcpyAsync(c->d_job_first_chunk.p, c->job_first_chunk.data(), (c->jobs.size() + 1) * sizeof(int32_t),
-                       cudaMemcpyHostToDevice, c->stream));
+    {
+        // job table, band chunks and chunk index: staged in pinned memory, moved by the control-copy kernel
+        static_assert(sizeof(mb::Job) % 8 == 0 && sizeof(mb::BandChunk) % 4 == 0, "control copies move 4-byte words");
+        const size_t b_jobs = c->jobs.size() * sizeof(mb::Job), b_chunks = c->chunks.size() * sizeof(mb::BandChunk),
+                     b_first = (c->jobs.size() + 1) * sizeof(int32_t);
+        const size_t o_chunks = (b_jobs + 15) / 16 * 16, o_first = o_chunks + (b_chunks + 15) / 16 * 16;
+        if (c->h_stage_in.ensure(o_first + b_first)) return 1;
+        char *h = c->h_stage_in.as<char>();
+        if (b_jobs) memcpy(h, c->jobs.data(), b_jobs);
+        if (b_chunks) memcpy(h + o_chunks, c->chunks.data(), b_chunks);
+        memcpy(h + o_first, c->job_first_chunk.data(), b_first);
+        if (ctl_copy(c->stream, c->d_jobs.p, h, b_jobs) || ctl_copy(c->stream, c->d_chunks.p, h + o_chunks, b_chunks) ||
+            ctl_copy(c->stream, c->d_job_first_chunk.p, h + o_first, b_first))
+            return 1;
+    }
     tr.mark("jobs");
-    CU(cudaStreamSynchronize(c->stream));  // extra_anchors / jobs are pageable host memory about to go out of scope
+    if (!extra_anchors.empty()) CU(cudaStreamSynchronize(c->stream));  // pageable host memory about to go out of scope
     return 0;
 }
 
@@ -717,7 +803,7 @@ int run_band(margin_b200_ctx *c, bool dynamic, bool with_schedule, bool want_kr)
             c->launches++;
         }
     }
-    CU(cudaMemcpyAsync(h, dv, o_end, cudaMemcpyDeviceToHost, c->stream));
+    if (ctl_copy(c->stream, h, dv, (o_end + 3) / 4 * 4)) return 1;
     CU(cudaStreamSynchronize(c->stream));
     CU(cudaGetLastError());
     if (*reinterpret_cast<int *>(h + o_err))
@@ -943,7 +1029,7 @@ int build_bins(margin_b200_ctx *c, bool with_slots, Bins &bins, int force_group)
     c->bins_ids_h = ids;
     c->bins_ids_off = o_ids;
     c->bins_n_ids = n_ids;
-    CU(cudaMemcpyAsync(c->d_arena.p, h, o_ids + (size_t) n_ids * 4, cudaMemcpyHostToDevice, c->stream));
+    if (ctl_copy(c->stream, c->d_arena.p, h, o_ids + (size_t) n_ids * 4)) return 1;
     char *dv = c->d_arena.as<char>();
     c->p_tiles = reinterpret_cast<mb::Tile *>(dv + o_tiles);
     c->p_ring_off = reinterpret_cast<int64_t *>(dv + o_ring);
@@ -971,8 +1057,9 @@ int finish_bins(margin_b200_ctx *c, Bins &bins) {
     }
     bins.tile_bwd[3] = n_ids;
     if (n_ids > first)
-        CU(cudaMemcpyAsync(c->d_arena.as<char>() + c->bins_ids_off + (size_t) first * 4, ids + first,
-                           (size_t) (n_ids - first) * 4, cudaMemcpyHostToDevice, c->stream));
+        if (ctl_copy(c->stream, c->d_arena.as<char>() + c->bins_ids_off + (size_t) first * 4, ids + first,
+                     (size_t) (n_ids - first) * 4))
+            return 1;
     c->bins_n_ids = n_ids;
     return 0;
 }
@@ -1131,9 +1218,7 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
     // (0.22 tuples per band cell were measured on real data) and the gather refuses to write past it; the totals come
     // back with the final synchronisation, and an overflow re-runs the gather into an exactly sized buffer.
     int64_t *bounds = reinterpret_cast<int64_t *>(c->h_small.as<char>());  // pinned; run_band's landing zone is consumed
-    for (int l = 0; l < 4; l++)
-        CU(cudaMemcpyAsync(&bounds[l], c->d_seg_off.as<int64_t>() + (size_t) l * S, sizeof(int64_t), cudaMemcpyDeviceToHost,
-                           c->stream));
+    ctl_bounds_kernel<<<1, 32, 0, c->stream>>>(c->d_seg_off.as<int64_t>(), S, bounds);
     const size_t want_cap = (size_t) cells / (want_indels ? 3 : 6) + 4096;
     if (c->d_out.cap / sizeof(mb::Pair) < want_cap && c->d_out.ensure(want_cap * sizeof(mb::Pair))) return 1;
     auto run_gather = [&]() {
@@ -1142,16 +1227,16 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
             KTimer kt_(c, K_GATHER);
             mb::gather_kernel<<<S, 128, 0, c->stream>>>(c->d_jobs.as<mb::Job>(), c->p_tiles, S, c->d_cell_off.as<uint32_t>(),
                                                         c->d_seg_counts.as<int64_t>(), c->d_seg_off.as<int64_t>(),
-                                                        c->d_stage.as<mb::Pair>(), stride, c->d_out.as<mb::Pair>(), n_lists,
-                                                        cap);
+                                                        c->d_stage.as<mb::Pair>(), stride, c->d_out.p, c->packed_now ? 1 : 0,
+                                                        n_lists, cap);
             c->launches++;
         }
         if (S > 0 && nj > 0 && any_tiled) {
             KTimer kt_(c, K_GATHER);
             mb::gather_staged_kernel<<<S, 128, 0, c->stream>>>(c->d_jobs.as<mb::Job>(), c->p_tiles, S, c->d_geo.as<int2>(),
                                                                c->d_seg_counts.as<int64_t>(), c->d_seg_off.as<int64_t>(),
-                                                               c->d_stage2.as<mb::StagedPair>(), stride,
-                                                               c->d_out.as<mb::Pair>(), n_lists, cap);
+                                                               c->d_stage2.as<mb::StagedPair>(), stride, c->d_out.p,
+                                                               c->packed_now ? 1 : 0, n_lists, cap);
             c->launches++;
         }
     };
@@ -1194,18 +1279,19 @@ extern "C" int margin_b200_download_result(margin_b200_ctx *c, margin_b200_resul
     if (c->h_out.ensure((size_t) (c->total_tuples + 1) * sizeof(mb::Pair)) ||
         c->h_off.ensure((size_t) 3 * (n + 1) * sizeof(int64_t)))
         return 1;
+    const size_t tuple_bytes = c->packed_now ? sizeof(uint64_t) : sizeof(mb::Pair);
     if (c->total_tuples)
-        CU(cudaMemcpyAsync(c->h_out.p, c->d_out.p, (size_t) c->total_tuples * sizeof(mb::Pair), cudaMemcpyDeviceToHost,
-                           c->stream));
-    CU(cudaMemcpyAsync(c->h_off.p, c->d_off_out.p, (size_t) 3 * (n + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaMemcpyAsync(c->h_out.p, c->d_out.p, (size_t) c->total_tuples * tuple_bytes, cudaMemcpyDeviceToHost, c->stream));
+    if (ctl_copy(c->stream, c->h_off.p, c->d_off_out.p, (size_t) 3 * (n + 1) * sizeof(int64_t))) return 1;
     CU(cudaStreamSynchronize(c->stream));
-    const margin_b200_pair *base = c->h_out.as<margin_b200_pair>();
+    const char *base = c->h_out.as<char>();
     int64_t acc = 0;
     for (int l = 0; l < 3; l++) {
-        out->pairs[l] = base + acc;
+        out->pairs[l] = reinterpret_cast<const margin_b200_pair *>(base + (size_t) acc * tuple_bytes);
         out->off[l] = c->h_off.as<int64_t>() + (size_t) l * (n + 1);
         acc += c->list_tuples[l];
     }
+    out->pair_format = c->packed_now ? MARGIN_B200_PAIRS_PACKED64 : MARGIN_B200_PAIRS_TRIPLES;
     return 0;
 }
 
@@ -1243,6 +1329,8 @@ int ensure_subs(margin_b200_ctx *c, int K) {
         margin_b200_ctx *sub = nullptr;
         if (margin_b200_create(&sub, c->device)) return 1;
         sub->is_sub = true;
+        sub->counted = false;
+        g_live_contexts[c->device & (kMaxDevices - 1)].fetch_sub(1);
         {
             // earlier runs outrank later ones, so that a run's kernels are not held up by the runs queued behind it
             // and its lists can start for the host while the others still compute
@@ -1277,14 +1365,14 @@ int pipe_download(margin_b200_ctx *c, margin_b200_ctx *sub, const std::array<int
     Trace tr(sub);
     if (sub->h_off.ensure((size_t) 3 * (n + 1) * sizeof(int64_t))) return 1;
     int64_t acc = 0;
+    const size_t tb = sub->packed_now ? sizeof(uint64_t) : sizeof(mb::Pair);
     for (int l = 0; l < 3; l++) {
         if (sub->list_tuples[l])
-            CU(cudaMemcpyAsync(c->h_pipe_out[l].as<mb::Pair>() + base[l], sub->d_out.as<mb::Pair>() + acc,
-                               (size_t) sub->list_tuples[l] * sizeof(mb::Pair), cudaMemcpyDeviceToHost, sub->stream));
+            CU(cudaMemcpyAsync(c->h_pipe_out[l].as<char>() + (size_t) base[l] * tb, sub->d_out.as<char>() + (size_t) acc * tb,
+                               (size_t) sub->list_tuples[l] * tb, cudaMemcpyDeviceToHost, sub->stream));
         acc += sub->list_tuples[l];
     }
-    CU(cudaMemcpyAsync(sub->h_off.p, sub->d_off_out.p, (size_t) 3 * (n + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost,
-                       sub->stream));
+    if (ctl_copy(sub->stream, sub->h_off.p, sub->d_off_out.p, (size_t) 3 * (n + 1) * sizeof(int64_t))) return 1;
     CU(cudaStreamSynchronize(sub->stream));
     tr.mark("pipe d2h");
     return 0;
@@ -1296,7 +1384,8 @@ int posteriors_pipelined(margin_b200_ctx *c, const margin_b200_batch *b, int wan
     // ---- runs of consecutive alignments with about equal host bytes
     std::vector<PipeRun> runs(K);
     {
-        auto bytes_upto = [&](int64_t i) { return 12 * b->off_a[i] + 2 * (b->off_x[i] + b->off_y[i]); };
+        const int64_t anchor_bytes = b->anchors_delta ? 4 : 12;
+        auto bytes_upto = [&](int64_t i) { return anchor_bytes * b->off_a[i] + 2 * (b->off_x[i] + b->off_y[i]); };
         const int64_t total = bytes_upto(n);
         int64_t i = 0;
         for (int k = 0; k < K; k++) {
@@ -1322,7 +1411,8 @@ int posteriors_pipelined(margin_b200_ctx *c, const margin_b200_batch *b, int wan
         r.view.n = r.n;
         r.view.sym_x = b->sym_x + b->off_x[r.first];
         r.view.sym_y = b->sym_y + b->off_y[r.first];
-        r.view.anchors = b->anchors + 3 * b->off_a[r.first];
+        r.view.anchors = b->anchors ? b->anchors + 3 * b->off_a[r.first] : nullptr;
+        r.view.anchors_delta = b->anchors_delta ? b->anchors_delta + b->off_a[r.first] : nullptr;
         r.view.off_x = r.off_x.data();
         r.view.off_y = r.off_y.data();
         r.view.off_a = r.off_a.data();
@@ -1330,6 +1420,13 @@ int posteriors_pipelined(margin_b200_ctx *c, const margin_b200_batch *b, int wan
         r.view.ragged_left = b->ragged_left ? b->ragged_left + r.first : nullptr;
         r.view.ragged_right = b->ragged_right ? b->ragged_right + r.first : nullptr;
     }
+    // one tuple format for the whole batch (a run must not fall back on its own)
+    bool fits_packed = true;
+    for (int64_t i = 0; i < n; i++)
+        if (b->off_x[i + 1] - b->off_x[i] >= (1 << 20) - 1 || b->off_y[i + 1] - b->off_y[i] >= (1 << 20) - 1) fits_packed = false;
+    const int fmt = (c->pair_format == MARGIN_B200_PAIRS_PACKED64 && fits_packed) ? MARGIN_B200_PAIRS_PACKED64
+                                                                                  : MARGIN_B200_PAIRS_TRIPLES;
+    for (int k = 0; k < K; k++) c->subs[k]->pair_format = fmt;
     PipeShared sh;
     sh.base.assign(K + 1, {0, 0, 0});
     CU(cudaSetDevice(c->device));
@@ -1401,6 +1498,7 @@ int posteriors_pipelined(margin_b200_ctx *c, const margin_b200_batch *b, int wan
         out->off[l] = off + (size_t) l * (n + 1);
     }
     out->n = n;
+    out->pair_format = fmt;
     for (const PipeRun &r : runs) {
         out->band_cells += r.res.band_cells;
         out->diagonals += r.res.diagonals;
@@ -1420,17 +1518,35 @@ int posteriors_pipelined(margin_b200_ctx *c, const margin_b200_batch *b, int wan
 
 }  // namespace
 
+// Several contexts on one device (the chunk scheduler's contexts_per_gpu): left alone, threads that start together stay
+// in lock-step (all copy, then all compute, then all copy back) and nothing overlaps.  A per-device compute token makes
+// them take turns on the SMs, so one context's copies run beside another's kernels.  A context that is the only one on
+// its device pipelines inside the call instead (posteriors_pipelined).  The choice depends on the number of live
+// contexts, not on timing, so a context always takes the same path (and its arenas are sized once).
+namespace {
+std::mutex g_compute_token[kMaxDevices];
+}  // namespace
+
 extern "C" int margin_b200_posteriors_batch(margin_b200_ctx *c, const margin_b200_batch *b, int want_indels,
                                             margin_b200_result *out) {
     if (!c || !b || !out) return fail("margin_b200_posteriors_batch: null argument");
     c->last_pipelined = false;
-    if (!c->is_sub && c->pipeline_k > 1 && b->n >= 2 && c->have_params) {
+    if (c->is_sub) {
+        if (margin_b200_upload_batch(c, b)) return 1;
+        if (margin_b200_posteriors_resident(c, want_indels, out)) return 1;
+        return margin_b200_download_result(c, out);
+    }
+    const int dev_slot = c->device & (kMaxDevices - 1);
+    if ((g_live_contexts[dev_slot].load() == 1 || c->pipeline_force) && c->pipeline_k > 1 && b->n >= 2 && c->have_params) {
         const int64_t bytes = 12 * b->off_a[b->n] + 2 * (b->off_x[b->n] + b->off_y[b->n]);
         const int K = (int) std::min<int64_t>(c->pipeline_k, b->n / 2);
         if (K > 1 && bytes >= c->pipeline_min_bytes) return posteriors_pipelined(c, b, want_indels, out, K);
     }
     if (margin_b200_upload_batch(c, b)) return 1;
-    if (margin_b200_posteriors_resident(c, want_indels, out)) return 1;
+    {
+        std::lock_guard<std::mutex> token(g_compute_token[dev_slot]);
+        if (margin_b200_posteriors_resident(c, want_indels, out)) return 1;
+    }
     return margin_b200_download_result(c, out);
 }
 

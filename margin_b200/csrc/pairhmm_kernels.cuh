@@ -179,6 +179,48 @@ band_kernel(const Job *__restrict__ jobs, int n_jobs, const int32_t *__restrict_
 // strictly increasing in x and y, inside the sequences, even expansion) and whether getSplitPoints (:913-965) would
 // cut the alignment (some anchor-free sub-matrix larger than `limit` cells).  status[2*i] = index of the first bad
 // anchor or INT_MAX, status[2*i+1] = 1 when the alignment needs the host's split path.
+// Compact anchors (include/margin_b200.h: one word per anchor, dx | dy << 12 | (expansion / 2) << 24) back to
+// (x, y, expansion) triples: one CTA per alignment, block-wide inclusive scans of dx and dy.
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS)
+expand_anchors_kernel(const uint32_t *__restrict__ packed, const int64_t *__restrict__ off_a, int32_t *__restrict__ anchors) {
+    const int64_t a0 = off_a[blockIdx.x], na = off_a[blockIdx.x + 1] - a0;
+    __shared__ int2 warp_sums[THREADS / 32];
+    __shared__ int2 carry_s;
+    if (threadIdx.x == 0) carry_s = make_int2(-1, -1);
+    __syncthreads();
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    for (int64_t base = 0; base < na; base += THREADS) {
+        const int64_t k = base + threadIdx.x;
+        const uint32_t v = k < na ? packed[a0 + k] : 0u;
+        int sx = (int) (v & 0xfffu), sy = (int) ((v >> 12) & 0xfffu);
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int nx = __shfl_up_sync(0xffffffffu, sx, o), ny = __shfl_up_sync(0xffffffffu, sy, o);
+            if (lane >= o) {
+                sx += nx;
+                sy += ny;
+            }
+        }
+        if (lane == 31) warp_sums[wid] = make_int2(sx, sy);
+        __syncthreads();
+        int2 pre = carry_s;
+        for (int w = 0; w < wid; w++) {
+            pre.x += warp_sums[w].x;
+            pre.y += warp_sums[w].y;
+        }
+        if (k < na) {
+            int32_t *q = anchors + 3 * (a0 + k);
+            q[0] = pre.x + sx;
+            q[1] = pre.y + sy;
+            q[2] = (int32_t) (v >> 24) * 2;
+        }
+        __syncthreads();
+        if (threadIdx.x == THREADS - 1) carry_s = make_int2(pre.x + sx, pre.y + sy);
+        __syncthreads();
+    }
+}
+
 __global__ void check_anchors_kernel(const int32_t *__restrict__ anchors, const int64_t *__restrict__ off_a,
                                      const int64_t *__restrict__ off_x, const int64_t *__restrict__ off_y, int64_t limit,
                                      int32_t *__restrict__ status) {
@@ -629,6 +671,16 @@ struct Pair {
     int32_t w, x, y;
 };
 
+// Final tuple store: (w, x, y) int32 triples, or MARGIN_B200_PAIRS_PACKED64 words w | (x+1) << 24 | (y+1) << 44.
+__device__ __forceinline__ void store_pair(void *out, int64_t i, int packed, const Pair &q) {
+    if (packed)
+        reinterpret_cast<unsigned long long *>(out)[i] = (unsigned long long) (uint32_t) q.w |
+                                                         ((unsigned long long) (uint32_t) (q.x + 1) << 24) |
+                                                         ((unsigned long long) (uint32_t) (q.y + 1) << 44);
+    else
+        reinterpret_cast<Pair *>(out)[i] = q;
+}
+
 // Gather form of diagonalCalculationBackward (pairwiseAligner.c:572-576 with doTransitionBackward :322-325).
 // The reference scatters from a cell into its three neighbours; a cell (x,y) of diagonal d therefore receives,
 // in this order: its match term from (x+1,y+1) while d+2 is processed, then while d+1 is processed (cells in
@@ -885,7 +937,7 @@ backward_kernel(const Job *__restrict__ jobs, const Tile *__restrict__ segs, con
 __global__ void gather_kernel(const Job *__restrict__ jobs, const Tile *__restrict__ segs, int total_slots,
                               const uint32_t *__restrict__ cell_off, const int64_t *__restrict__ seg_counts,
                               const int64_t *__restrict__ seg_off, const Pair *__restrict__ stage, int64_t stage_stride,
-                              Pair *__restrict__ out, int n_lists, int64_t out_capacity) {
+                              void *__restrict__ out, int packed, int n_lists, int64_t out_capacity) {
     const int slot = blockIdx.x;
     if (seg_off[(int64_t) 3 * total_slots] > out_capacity) return;  // the host re-runs with a larger buffer
     const Tile seg = segs[slot];
@@ -896,7 +948,7 @@ __global__ void gather_kernel(const Job *__restrict__ jobs, const Tile *__restri
         const int64_t c = seg_counts[(int64_t) l * total_slots + slot];
         const int64_t o = seg_off[(int64_t) l * total_slots + slot];
         const Pair *src = stage + (int64_t) l * stage_stride + region;
-        for (int64_t i = threadIdx.x; i < c; i += blockDim.x) out[o + i] = src[c - 1 - i];
+        for (int64_t i = threadIdx.x; i < c; i += blockDim.x) store_pair(out, o + i, packed, src[c - 1 - i]);
     }
 }
 

@@ -535,7 +535,8 @@ backward_tile_kernel(const Job *__restrict__ jobs, const Tile *__restrict__ tile
 __global__ void gather_staged_kernel(const Job *__restrict__ jobs, const Tile *__restrict__ tiles, int total_slots,
                                      const int2 *__restrict__ geo, const int64_t *__restrict__ seg_counts,
                                      const int64_t *__restrict__ seg_off, const StagedPair *__restrict__ stage,
-                                     int64_t stage_stride, Pair *__restrict__ out, int n_lists, int64_t out_capacity) {
+                                     int64_t stage_stride, void *__restrict__ out, int packed, int n_lists,
+                                     int64_t out_capacity) {
     const int slot = blockIdx.x;
     if (seg_off[(int64_t) 3 * total_slots] > out_capacity) return;  // the host re-runs with a larger buffer
     const Tile t = tiles[slot];
@@ -554,7 +555,7 @@ __global__ void gather_staged_kernel(const Job *__restrict__ jobs, const Tile *_
             q.w = (int32_t) floor(dmul(pr, 10000000.0));
             q.x = sp.x;
             q.y = sp.y;
-            out[o + i] = q;
+            store_pair(out, o + i, packed, q);
         }
     }
 }

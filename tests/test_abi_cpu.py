@@ -13,6 +13,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 def _declared():
     src = open(os.path.join(ROOT, "include", "margin_b200.h")).read()
+    src = "\n".join(l for l in src.splitlines() if not l.startswith("static inline"))  # header-only helpers
     return sorted(set(re.findall(r"\b(margin_b200_[a-z_]+)\s*\(", src)))
 
 
@@ -31,7 +32,8 @@ def test_library_exports_every_declared_symbol():
 def test_struct_layouts_match_header():
     assert C.sizeof(abi.Model) == 8 * (9 + 16 + 4 + 4) + 8 + 8 * 4 * 51 * 51
     assert C.sizeof(abi.Params) == 48
-    assert C.sizeof(abi.BatchStruct) == 80
+    assert C.sizeof(abi.BatchStruct) == 88
+    assert C.sizeof(abi.ResultStruct) == 8 + 24 + 24 + 32 + 8 + 8 + 8
     assert abi.PAIR_DTYPE.itemsize == 12
 
 

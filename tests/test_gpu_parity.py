@@ -196,6 +196,7 @@ def test_pipelined_batch_matches_the_plain_call(oracle, golden_model, monkeypatc
     plain.close()
     monkeypatch.setenv("MARGIN_B200_PIPELINE", str(k))
     monkeypatch.setenv("MARGIN_B200_PIPELINE_MIN_BYTES", "0")
+    monkeypatch.setenv("MARGIN_B200_PIPELINE_FORCE", "1")  # other tests' contexts may be alive on the device
     al = PairHmmAligner(pm.models, p, device=0)
     for _ in range(2):  # the second call reuses the pinned lists sized by the first
         got = al.posteriors_batch(items, True)
@@ -208,3 +209,42 @@ def test_pipelined_batch_matches_the_plain_call(oracle, golden_model, monkeypatc
         ref = oracle.posteriors(pm.models[it[3]], p, it[0], it[1], it[2], it[4], it[5], 1)
         compare_lists(got[i], ref, tol_w=1)
     al.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("pipeline", ["1", "3"])
+def test_compact_anchor_words_and_packed_tuples(golden_model, monkeypatch, pipeline):
+    """The compact boundary formats (4-byte anchor steps in, 8-byte tuple words out; include/margin_b200.h) give
+    exactly the lists of the plain formats, through the plain and the pipelined call."""
+    pm = golden_model("r94g360")
+    p = pm.p.copy(min_diags_between_traceback=300, dynamic_anchor_expansion=1)
+    rng = np.random.default_rng(5)
+    items = [gen.random_case(rng, int(rng.integers(1, 1200))) for _ in range(17)]
+    monkeypatch.setenv("MARGIN_B200_PIPELINE", pipeline)
+    monkeypatch.setenv("MARGIN_B200_PIPELINE_MIN_BYTES", "0")
+    monkeypatch.setenv("MARGIN_B200_PIPELINE_FORCE", "1")
+    al = PairHmmAligner(pm.models, p, device=0)
+    want = al.posteriors_batch(abi.Batch(items), True)
+    compact = abi.Batch(items, compact=True)
+    assert compact.compact and compact.h2d_bytes < abi.Batch(items).h2d_bytes
+    al.set_pair_format(abi.PAIRS_PACKED64)
+    got = al.posteriors_batch(compact, True)
+    for i in range(len(items)):
+        compare_lists(got[i], want[i], tol_w=0)
+    # an anchor step that does not fit a word: the host keeps the triples
+    far = (items[0][0], items[0][1], np.array([[0, 0, 4]], np.int32), 0, 0, 0)
+    big = np.zeros(6000, np.uint16)
+    wide = abi.Batch([(big, big, np.array([[10, 10, 2], [5000, 5000, 2]], np.int32), 0, 0, 0), far], compact=True)
+    assert not wide.compact
+    # gap lists carry -1 coordinates through the packed words
+    assert min(int(g[l]["x"].min(initial=0)) for g in got.lists for l in (1, 2)) >= -1
+    al.close()
+
+
+def test_pack_helpers_roundtrip():
+    words = np.array([0, (1 << 24) | 5, 10000000 | (123457 << 24) | (7 << 44)], np.uint64)
+    r = abi.unpack_pairs(words)
+    assert r["w"].tolist() == [0, 5, 10000000] and r["x"].tolist() == [-1, 0, 123456] and r["y"].tolist() == [-1, -1, 6]
+    a = np.array([[0, 0, 4], [3, 1, 0], [7, 9, 510]], np.int32)
+    d = abi.pack_anchors_delta(a, np.array([0, 1, 3]))
+    assert d.tolist() == [1 | (1 << 12) | (2 << 24), 4 | (2 << 12), 4 | (8 << 12) | (255 << 24)]
