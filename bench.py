@@ -327,6 +327,7 @@ def main_ours(args):
     batch = abi.Batch(items, compact=not args.plain_formats)
     pin_batch(batch)
     al = PairHmmAligner(pm.models, pm.p, device=local)
+    al.bench_workload = args.workload
     if not args.plain_formats:
         al.set_pair_format(abi.PAIRS_PACKED64)
     flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
@@ -335,7 +336,8 @@ def main_ours(args):
         flush.zero_()
         torch.cuda.synchronize(dev)
 
-    # ---- kernel-only leg: inputs resident in HBM
+    # ---- kernel-only leg: inputs resident in HBM (per-launch CUDA events on for this leg only)
+    al.set_kernel_timing(not args.no_kernel_events)
     al.upload(batch)
     for _ in range(args.warmup):
         l2_flush()
@@ -367,6 +369,7 @@ def main_ours(args):
     cell_passes = reduce_scalar(dist, 2.0 * cells, "SUM", dev)
     value = cell_passes / (ms_step * 1e-3) * 1e-9
 
+    al.set_kernel_timing(False)
     # ---- end-to-end leg: host buffers in, host tuple lists out, through the public C-ABI call
     for _ in range(max(1, min(args.warmup, 2))):
         res = al.posteriors_host(batch, True)
@@ -432,6 +435,19 @@ def main_ours(args):
     return 0
 
 
+# dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` capture of this workload
+NCU_TRAFFIC_SOURCE = "profiles/r01_v7_tiles_ncu_raw_selected.txt (ncu --set full, one launch, default workload)"
+NCU_DRAM_BYTES_PER_LAUNCH = {
+    (DEFAULT_WORKLOAD, "forward"): 0.100834e9 + 1.132209e9,
+    (DEFAULT_WORKLOAD, "backward"): 1.299964e9 + 0.137514e9,
+    (DEFAULT_WORKLOAD, "band"): 0.052305e9 + 0.023034e9,
+}
+
+
+def al_workload(al):
+    return getattr(al, "bench_workload", None)
+
+
 def roofline(dom, dom_ms, ktimes, cells, st, peaks, al):
     """Roofline of the dominant kernel.  The path is a log-space recurrence, so the pipe that bounds it is the
     non-tensor FP pipe of the arithmetic type the kernels compute in; the HBM view of the
@@ -460,7 +476,8 @@ def roofline(dom, dom_ms, ktimes, cells, st, peaks, al):
     return {
         "kernel": dom, "bound": "fp64-pipe" if dtype == "f64" else "fp32-pipe", "achieved": ach_tflops,
         "peak": peak_tflops, "unit": "TFLOP/s", "frac": ach_tflops / peak_tflops if peak_tflops else None,
-        "traffic": None, "peak_source": "%d SMs x %d lanes x 2 x %.0f MHz (%s sm_max_mhz)" % (
+        "traffic": NCU_DRAM_BYTES_PER_LAUNCH.get((al_workload(al), dom)), "traffic_source": NCU_TRAFFIC_SOURCE,
+        "peak_source": "%d SMs x %d lanes x 2 x %.0f MHz (%s sm_max_mhz)" % (
             sms, lanes, peaks["sm_max_mhz"], peaks["source"]),
         "avg_launch_ms": dom_ms, "class_ms_per_step": class_ms_step,
         "hbm": {"achieved": ach_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
@@ -477,6 +494,7 @@ def main():
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD)
     ap.add_argument("--seed", type=int, default=42)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-kernel-events", action="store_true", help="no per-launch CUDA events in the resident leg")
     ap.add_argument("--plain-formats", action="store_true",
                     help="12-byte anchor triples in, 12-byte tuple records out instead of the compact boundary formats")
     ap.add_argument("--no-sustained", action="store_true", help="skip the two-context sustained end-to-end leg")

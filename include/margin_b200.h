@@ -165,6 +165,9 @@ int margin_b200_version(void);
 
 int margin_b200_set_model(margin_b200_ctx *ctx, int slot, const margin_b200_model *model);
 int margin_b200_set_params(margin_b200_ctx *ctx, const margin_b200_params *params);
+/* CUDA events around every kernel launch, read back with margin_b200_last_kernel_ms (default off: measurement
+ * only, two driver calls per launch). */
+int margin_b200_set_kernel_timing(margin_b200_ctx *ctx, int on);
 /* Tuple format of the results of this context (default MARGIN_B200_PAIRS_TRIPLES). */
 int margin_b200_set_pair_format(margin_b200_ctx *ctx, int format);
 

@@ -207,6 +207,8 @@ def load_library():
     lib.margin_b200_set_model.restype = i32
     lib.margin_b200_set_params.argtypes = [vp, C.POINTER(Params)]
     lib.margin_b200_set_params.restype = i32
+    lib.margin_b200_set_kernel_timing.argtypes = [vp, i32]
+    lib.margin_b200_set_kernel_timing.restype = i32
     lib.margin_b200_set_pair_format.argtypes = [vp, i32]
     lib.margin_b200_set_pair_format.restype = i32
     lib.margin_b200_posteriors_batch.argtypes = [vp, C.POINTER(BatchStruct), i32, C.POINTER(ResultStruct)]
@@ -231,7 +233,7 @@ def load_library():
 
 EXPORTED_SYMBOLS = [
     "margin_b200_create", "margin_b200_destroy", "margin_b200_last_error", "margin_b200_version",
-    "margin_b200_set_model", "margin_b200_set_params", "margin_b200_set_pair_format", "margin_b200_posteriors_batch",
+    "margin_b200_set_model", "margin_b200_set_params", "margin_b200_set_pair_format", "margin_b200_set_kernel_timing", "margin_b200_posteriors_batch",
     "margin_b200_upload_batch", "margin_b200_posteriors_resident", "margin_b200_download_result",
     "margin_b200_forward_batch", "margin_b200_forward_resident", "margin_b200_bands",
     "margin_b200_last_kernel_ms", "margin_b200_device_count",

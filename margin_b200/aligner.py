@@ -76,6 +76,10 @@ class PairHmmAligner:
         self.params = params.copy()
         self._check(self.lib.margin_b200_set_params(self._h, C.byref(self.params)))
 
+    def set_kernel_timing(self, on):
+        """CUDA events around every launch (kernel_times()); off by default."""
+        self._check(self.lib.margin_b200_set_kernel_timing(self._h, int(bool(on))))
+
     def set_pair_format(self, fmt):
         """abi.PAIRS_TRIPLES (12-byte records) or abi.PAIRS_PACKED64 (8-byte words, include/margin_b200.h)."""
         self._check(self.lib.margin_b200_set_pair_format(self._h, int(fmt)))

@@ -141,6 +141,7 @@ struct margin_b200_ctx {
     int pipe_fill = 2;                                  // MARGIN_B200_PIPE_FILL: SM share a run's tiles are cut for, in 1/K
     int64_t pipeline_min_bytes = 8 << 20;               // MARGIN_B200_PIPELINE_MIN_BYTES of host input
     bool is_sub = false, last_pipelined = false, counted = false;
+    bool kernel_timing = false;                         // margin_b200_set_kernel_timing / MARGIN_B200_KERNEL_TIMING
     int pair_format = MARGIN_B200_PAIRS_TRIPLES;        // what the caller asked for
     bool packed_now = false;                            // ... and what this batch gets (sequence lengths permitting)
     DevBuf d_anchors_delta;
@@ -180,7 +181,8 @@ enum { K_BAND = 0, K_SCHEDULE, K_FORWARD, K_BACKWARD, K_SCAN, K_GATHER, K_OFFSET
 struct KTimer {
     margin_b200_ctx *c;
     int idx;
-    KTimer(margin_b200_ctx *ctx, int cls) : c(ctx) {
+    KTimer(margin_b200_ctx *ctx, int cls) : c(ctx), idx(-1) {
+        if (!c->kernel_timing) return;  // two event records per launch are driver calls the product path can do without
         if ((size_t) (2 * c->ev_used + 2) > c->ev_pool.size()) {
             cudaEvent_t a, b;
             cudaEventCreate(&a);
@@ -193,7 +195,9 @@ struct KTimer {
         c->ev_class[idx] = cls;
         cudaEventRecord(c->ev_pool[2 * idx], c->stream);
     }
-    ~KTimer() { cudaEventRecord(c->ev_pool[2 * idx + 1], c->stream); }
+    ~KTimer() {
+        if (idx >= 0) cudaEventRecord(c->ev_pool[2 * idx + 1], c->stream);
+    }
 };
 
 // Host-side phase trace (MARGIN_B200_TRACE=1): wall-clock microseconds between marks, printed to stderr.
@@ -311,6 +315,7 @@ int margin_b200_create(margin_b200_ctx **out, int device) {
         c->tile_len_fixed = true;
     }
     if (const char *e = getenv("MARGIN_B200_PIPELINE")) c->pipeline_k = std::max(1, std::min(16, atoi(e)));
+    if (const char *e = getenv("MARGIN_B200_KERNEL_TIMING")) c->kernel_timing = atoi(e) != 0;
     if (const char *e = getenv("MARGIN_B200_PIPELINE_FORCE")) c->pipeline_force = atoi(e) != 0;
     if (const char *e = getenv("MARGIN_B200_PIPE_FILL")) c->pipe_fill = std::max(1, std::min(16, atoi(e)));
     if (const char *e = getenv("MARGIN_B200_PIPELINE_MIN_BYTES")) c->pipeline_min_bytes = std::max(0ll, atoll(e));
@@ -459,6 +464,13 @@ int margin_b200_set_params(margin_b200_ctx *c, const margin_b200_params *p) {
         CU(cudaStreamSynchronize(c->stream));
         CU(cudaGetLastError());
     }
+    return 0;
+}
+
+int margin_b200_set_kernel_timing(margin_b200_ctx *c, int on) {
+    if (!c) return fail("margin_b200_set_kernel_timing: null context");
+    c->kernel_timing = on != 0;
+    for (margin_b200_ctx *sub : c->subs) sub->kernel_timing = c->kernel_timing;
     return 0;
 }
 
@@ -1351,6 +1363,7 @@ int ensure_subs(margin_b200_ctx *c, int K) {
         sub->tile_len = c->tile_len;
         sub->tile_len_fixed = c->tile_len_fixed;
         sub->warmup = c->warmup;
+        sub->kernel_timing = c->kernel_timing;
         // Tile length of a run: with bwd_slots / K every run is cut as if it owned 1/K of the SMs (same tiles as the
         // unpipelined call); a larger share means shorter tiles, i.e. a run finishes sooner (its lists reach the host
         // while later runs still compute) at the price of more warm-up diagonals.
