@@ -328,21 +328,39 @@ band_chunk_kernel(const Job *__restrict__ jobs, const BandChunk *__restrict__ ch
         for (int k = threadIdx.x; k < a_cnt; k += THREADS)
             s_diag[k] = __ldg(anc + 3 * (a_lo + k)) + __ldg(anc + 3 * (a_lo + k) + 1) + 2;
     __syncthreads();
+    // Each thread owns DPT consecutive diagonals: one binary search for the first, then the governing anchor only
+    // moves forward; one block-wide scan of the per-thread width sums covers the whole chunk.
+    constexpr int DPT = BAND_CHUNK / THREADS;
+    static_assert(DPT * THREADS == BAND_CHUNK, "a chunk is THREADS x DPT diagonals");
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    for (int base = ch.d0; base < d_end; base += THREADS) {
-        const int d = base + threadIdx.x;
+    const int dfirst = ch.d0 + threadIdx.x * DPT;
+    int wv[DPT], xv[DPT], krv[DPT];
+    int lo_a = 0;
+    if (dfirst <= N) {
+        if (staged) {
+            int lo = 0, hi = a_cnt;
+            while (lo < hi) {
+                const int mid = (lo + hi) >> 1;
+                if (s_diag[mid] >= dfirst) hi = mid; else lo = mid + 1;
+            }
+            lo_a = a_lo + lo;
+        } else {
+            lo_a = anchor_lower_bound(anc, 0, na, dfirst);
+        }
+    }
+    uint32_t tsum = 0;
+    int mw = 0;
+#pragma unroll
+    for (int k = 0; k < DPT; k++) {
+        const int d = dfirst + k;
         int w = 0, kl = 0, kr = 0;
         if (d <= N) {
-            int lo_a;
-            if (staged) {
-                int lo = 0, hi = a_cnt;
-                while (lo < hi) {
-                    const int mid = (lo + hi) >> 1;
-                    if (s_diag[mid] >= d) hi = mid; else lo = mid + 1;
+            if (k > 0) {  // smallest anchor index with (ax+1)+(ay+1) >= d: advances monotonically with d
+                if (staged) {
+                    while (lo_a - a_lo < a_cnt && s_diag[lo_a - a_lo] < d) lo_a++;
+                } else {
+                    while (lo_a < na && __ldg(anc + 3 * lo_a) + __ldg(anc + 3 * lo_a + 1) + 2 < d) lo_a++;
                 }
-                lo_a = a_lo + lo;
-            } else {
-                lo_a = anchor_lower_bound(anc, 0, na, d);
             }
             band_diagonal(anc, na, lx, ly, d, lo_a, p, kl, kr);
             w = (kr - kl) / 2 + 1;
@@ -351,28 +369,37 @@ band_chunk_kernel(const Job *__restrict__ jobs, const BandChunk *__restrict__ ch
                 w = 1;
             }
         }
-        uint32_t v = (uint32_t) w;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const uint32_t n = __shfl_up_sync(0xffffffffu, v, o);
-            if (lane >= o) v += n;
-        }
-        if (lane == 31) warp_sums[wid] = v;
-        int mw = w;
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) mw = max(mw, __shfl_xor_sync(0xffffffffu, mw, o));
-        if (lane == 0) atomicMax(&maxw_s, mw);
-        __syncthreads();
-        uint32_t pre = carry_s;
-        for (int k = 0; k < wid; k++) pre += warp_sums[k];
-        if (d < d_end) {
-            geo[job.diag_off + d] = make_int2((d + kl) >> 1, (int) (pre + v - (uint32_t) w));
-            if (kr_out) kr_out[job.diag_off + d] = kr;
-        }
-        __syncthreads();
-        if (threadIdx.x == THREADS - 1) carry_s = pre + v;
-        __syncthreads();
+        wv[k] = w;
+        xv[k] = d <= N ? (d + kl) >> 1 : lx;  // the sentinel entry N+1 keeps a valid column for prefetches
+        krv[k] = kr;
+        tsum += (uint32_t) w;
+        mw = max(mw, w);
     }
+    uint32_t v = tsum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t n = __shfl_up_sync(0xffffffffu, v, o);
+        if (lane >= o) v += n;
+    }
+    if (lane == 31) warp_sums[wid] = v;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mw = max(mw, __shfl_xor_sync(0xffffffffu, mw, o));
+    if (lane == 0) atomicMax(&maxw_s, mw);
+    __syncthreads();
+    uint32_t pre = 0;
+    for (int k = 0; k < wid; k++) pre += warp_sums[k];
+    uint32_t run = pre + v - tsum;  // exclusive prefix of this thread's first diagonal inside the chunk
+#pragma unroll
+    for (int k = 0; k < DPT; k++) {
+        const int d = dfirst + k;
+        if (d < d_end) {
+            geo[job.diag_off + d] = make_int2(xv[k], (int) run);
+            if (kr_out) kr_out[job.diag_off + d] = krv[k];
+        }
+        run += (uint32_t) wv[k];
+    }
+    if (threadIdx.x == THREADS - 1) carry_s = pre + v;
+    __syncthreads();
     if (threadIdx.x == 0) {
         chunk_sum[ci] = carry_s;
         chunk_maxw[ci] = maxw_s;

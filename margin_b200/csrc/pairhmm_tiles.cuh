@@ -257,11 +257,13 @@ forward_tile_kernel(const Job *__restrict__ jobs, const Tile *__restrict__ tiles
             c.x = ok_lower ? c.x : MB_NEG_INF;
             c.m = ok_middle ? c.m : MB_NEG_INF;
             c.y = ok_upper ? c.y : MB_NEG_INF;
-            if (live && active && d >= tb_to) {
+            {
+                // predicated stores (no divergent branch in the loop body)
                 double *q = (d == tb_to) ? bnd + 3 * r : Fj + 3 * ((int64_t) co + r);
-                q[0] = c.m;
-                q[1] = c.x;
-                q[2] = c.y;
+                asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %0, 0;\n\t@p st.global.f64 [%1], %2;\n\t"
+                             "@p st.global.f64 [%1+8], %3;\n\t@p st.global.f64 [%1+16], %4;\n\t}"
+                             :: "r"((unsigned) (live && active && d >= tb_to)), "l"(q), "d"(c.m), "d"(c.x), "d"(c.y)
+                             : "memory");
             }
             // ---- carry
             midm = lm;
@@ -319,7 +321,7 @@ struct StageLane {
             bits = (bits >> shift) & ((1u << G) - 1u);
             rot = (bits >> rot_r) | (bits << (G - rot_r));  // bits above G are masked by `below`
         }
-        if (ok) {
+        if (ok) {  // a branch, not a predicated store: most warps stage nothing on most diagonals and skip the address math
             StagedPair sp;
             sp.v = v;
             sp.x = x;
