@@ -269,6 +269,29 @@ __device__ __forceinline__ int anchor_lower_bound(const int32_t *__restrict__ an
     return lo;
 }
 
+// The four corner points of the band between the anchor pair governing diagonal(s) with lower bound `lo`
+// (band_constructDynamic, pairwiseAligner.c:161-226): the same arithmetic as band_diagonal below.
+__device__ __forceinline__ void band_corners(const int32_t *__restrict__ anc, int na, int lx, int ly, int lo,
+                                             const Params &p, int &xL, int &yL, int &xU, int &yU) {
+    int nx = lx, ny = ly, px = 0, py = 0, e;
+    if (lo < na) {
+        nx = __ldg(anc + 3 * lo) + 1;
+        ny = __ldg(anc + 3 * lo + 1) + 1;
+        e = p.dynamic ? __ldg(anc + 3 * lo + 2) : p.expansion;
+    } else {
+        e = p.dynamic ? (na > 0 ? __ldg(anc + 3 * (na - 1) + 2) : 0) : p.expansion;
+    }
+    if (lo > 0) {
+        px = __ldg(anc + 3 * (lo - 1)) + 1;
+        py = __ldg(anc + 3 * (lo - 1) + 1) + 1;
+    }
+    const int pxay = px + py, pxmy = px - py, nxay = nx + ny, nxmy = nx - ny;
+    xL = bound_coord((pxay + pxmy - e) / 2, lx);
+    yL = bound_coord((nxay - (nxmy - e)) / 2, ly);
+    xU = bound_coord((nxay + nxmy + e) / 2, lx);
+    yU = bound_coord((pxay - (pxmy + e)) / 2, ly);
+}
+
 // `lo` = anchor_lower_bound over all anchors of the job for diagonal d
 __device__ __forceinline__ void band_diagonal(const int32_t *__restrict__ anc, int na, int lx, int ly, int d, int lo,
                                               const Params &p, int &kl, int &kr) {
@@ -350,6 +373,7 @@ band_chunk_kernel(const Job *__restrict__ jobs, const BandChunk *__restrict__ ch
     }
     uint32_t tsum = 0;
     int mw = 0;
+    int cached_lo = -1, cxL = 0, cyL = 0, cxU = 0, cyU = 0;
 #pragma unroll
     for (int k = 0; k < DPT; k++) {
         const int d = dfirst + k;
@@ -362,7 +386,15 @@ band_chunk_kernel(const Job *__restrict__ jobs, const BandChunk *__restrict__ ch
                     while (lo_a < na && __ldg(anc + 3 * lo_a) + __ldg(anc + 3 * lo_a + 1) + 2 < d) lo_a++;
                 }
             }
-            band_diagonal(anc, na, lx, ly, d, lo_a, p, kl, kr);
+            if (d == 0) {
+                kl = kr = 0;
+            } else {
+                if (lo_a != cached_lo) {  // the corner points only depend on the governing anchor pair
+                    cached_lo = lo_a;
+                    band_corners(anc, na, lx, ly, lo_a, p, cxL, cyL, cxU, cyU);
+                }
+                clip_diagonal(d, cxL, cyL, cxU, cyU, kl, kr);
+            }
             w = (kr - kl) / 2 + 1;
             if (kr < kl) {  // diagonal_construct would throw (pairwiseAligner.c:22-27)
                 atomicExch(err, 1);
