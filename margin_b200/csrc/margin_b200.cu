@@ -17,6 +17,7 @@
 #include <mutex>
 #include <string>
 #include <thread>
+#include <type_traits>
 #include <vector>
 
 #include <cub/device/device_scan.cuh>
@@ -133,6 +134,11 @@ struct margin_b200_ctx {
     int32_t *p_aln_first_slot = nullptr, *p_ids = nullptr;
     std::vector<uint64_t> keys[4], key_tmp;
     std::vector<int32_t> span_tmp;
+    std::vector<uint8_t> tiny_mask;  // forward-only: jobs swept by tiny_forward_kernel (skipped by build_bins)
+    PinBuf h_tiny_ids;
+    DevBuf d_tiny_ids, d_chunks_fwd, d_job_first_chunk_fwd;
+    std::vector<mb::BandChunk> chunks_fwd;
+    std::vector<int32_t> job_first_chunk_fwd;
     // ---- pipelined batches (posteriors_pipelined): sub-contexts with their own stream and arenas
     std::vector<margin_b200_ctx *> subs;
     std::unique_ptr<margin_b200_model> user_models[2];  // as given to set_model, replayed into new sub-contexts
@@ -348,7 +354,7 @@ void margin_b200_destroy(margin_b200_ctx *c) {
                       &c->d_ids, &c->d_aln_first_slot, &c->d_F, &c->d_stage, &c->d_out, &c->d_off_out, &c->d_fwd_out,
                       &c->d_geo, &c->d_tiles, &c->d_bnd, &c->d_slot_bnd_off, &c->d_emit5[0], &c->d_emit5[1],
                       &c->d_px, &c->d_py, &c->d_stage2, &c->d_chunks, &c->d_job_first_chunk, &c->d_chunk_sum, &c->d_chunk_maxw,
-                      &c->d_totals, &c->d_band_out, &c->d_anchors_delta, &c->d_arena, &c->d_offs, &c->d_status};
+                      &c->d_totals, &c->d_band_out, &c->d_anchors_delta, &c->d_tiny_ids, &c->d_chunks_fwd, &c->d_job_first_chunk_fwd, &c->d_arena, &c->d_offs, &c->d_status};
     for (DevBuf *b : bufs) b->release();
     c->h_stage_in.release();
     c->h_small.release();
@@ -356,6 +362,7 @@ void margin_b200_destroy(margin_b200_ctx *c) {
     c->h_out.release();
     c->h_off.release();
     for (PinBuf &b : c->h_pipe_out) b.release();
+    c->h_tiny_ids.release();
     c->h_pipe_off.release();
     for (cudaEvent_t e : c->ev_pool) cudaEventDestroy(e);
     cudaEventDestroy(c->ev0);
@@ -991,7 +998,8 @@ int build_bins(margin_b200_ctx *c, bool with_slots, Bins &bins, int force_group)
     k2.clear();
     k3.clear();
     for (int j = 0; j < nj; j++)
-        if (!with_slots || !job_is_tiled(c, j)) k0.push_back(key(gbin(j), c->jobs[j].lx + c->jobs[j].ly, j));
+        if ((!with_slots || !job_is_tiled(c, j)) && !(!with_slots && j < (int) c->tiny_mask.size() && c->tiny_mask[j]))
+            k0.push_back(key(gbin(j), c->jobs[j].lx + c->jobs[j].ly, j));
     int64_t ring_cells = 0, bnd_cells = 0;
     // arena layout (16-byte aligned sections): tiles | ring_off | bnd_off | aln_first_slot | ids
     const size_t o_tiles = 0, o_ring = o_tiles + (((size_t) S + 1) * sizeof(mb::Tile) + 15) / 16 * 16,
@@ -1611,28 +1619,119 @@ extern "C" int margin_b200_forward_resident(margin_b200_ctx *c, margin_b200_resu
         return fail("margin_b200_forward: an alignment was split by splitMatrixBiggerThanThis; the forward-only "
                     "path takes whole matrices");
     CU(cudaEventRecord(c->ev0, c->stream));
-    if (run_band(c, false, false, false)) return 1;
-    Bins bins;
     c->force_group = force_group_env();
-    if (build_bins(c, false, bins, c->force_group)) return 1;
-    if (c->d_F.ensure((size_t) (c->total_cells + 1) * 3 * sizeof(double)) ||
-        c->d_fwd_out.ensure((size_t) (c->n_aln + 1) * sizeof(double)))
-        return 1;
-    launch_forward<8>(c, bins.seq_fwd[0], bins.seq_fwd[1] - bins.seq_fwd[0]);
-    launch_forward<16>(c, bins.seq_fwd[1], bins.seq_fwd[2] - bins.seq_fwd[1]);
-    launch_forward<32>(c, bins.seq_fwd[2], bins.seq_fwd[3] - bins.seq_fwd[2]);
-    if (nj > 0) {
-        { KTimer kt_(c, K_FINAL); mb::final_dot_kernel<<<(nj + 127) / 128, 128, 0, c->stream>>>(c->d_jobs.as<mb::Job>(), nj,
-                                                                      c->d_models.as<mb::DevModel>(),
-                                                                      c->d_cell_off.as<uint32_t>(), c->d_F.as<double>(),
-                                                                      c->d_fwd_out.as<double>()); }
-        c->launches++;
+    // The bubble-graph case: a matrix that is small and has no anchors is swept in registers (no band
+    // tables, no F in HBM); anything else takes the general path (band kernels, sequential forward sweep, final dot).
+    c->tiny_mask.assign(nj, 0);
+    int n_tiny = 0;
+    int64_t tiny_cells = 0;
+    if (!c->mode_sequential && !c->force_group) {
+        for (int j = 0; j < nj; j++) {
+            const mb::Job &job = c->jobs[j];
+            if (job.n_anc == 0 && std::min(job.lx, job.ly) + 1 <= 32) {
+                c->tiny_mask[j] = 1;
+                n_tiny++;
+                tiny_cells += (int64_t) (job.lx + 1) * (job.ly + 1);
+            }
+        }
+    }
+    if (c->d_fwd_out.ensure((size_t) (c->n_aln + 1) * sizeof(double))) return 1;
+    int64_t general_cells = 0;
+    if (n_tiny < nj) {
+        // band tables only for the general jobs: a chunk list without the tiny ones stands in for the batch's own
+        // during run_band (a tiny job then has no chunks and no cells)
+        const bool filtered = n_tiny > 0;
+        if (filtered) {
+            c->chunks_fwd.clear();
+            c->job_first_chunk_fwd.assign(nj + 1, 0);
+            for (int j = 0; j < nj; j++) {
+                c->job_first_chunk_fwd[j] = (int32_t) c->chunks_fwd.size();
+                if (c->tiny_mask[j]) continue;
+                const int entries = c->jobs[j].lx + c->jobs[j].ly + 2;
+                for (int d0 = 0; d0 < entries; d0 += mb::BAND_CHUNK) c->chunks_fwd.push_back(mb::BandChunk{(int32_t) j, d0});
+            }
+            c->job_first_chunk_fwd[nj] = (int32_t) c->chunks_fwd.size();
+            const size_t b_chunks = c->chunks_fwd.size() * sizeof(mb::BandChunk), b_first = ((size_t) nj + 1) * sizeof(int32_t);
+            const size_t o_first = (b_chunks + 15) / 16 * 16;
+            // staged behind the tiny id list in this call's own pinned buffer (h_stage_in may still be feeding the
+            // upload's copy kernels)
+            const size_t o_stage = ((size_t) n_tiny * 4 + 31) / 16 * 16;
+            if (c->h_tiny_ids.ensure(o_stage + o_first + b_first) || c->d_chunks_fwd.ensure(b_chunks + 16) ||
+                c->d_job_first_chunk_fwd.ensure(b_first))
+                return 1;
+            char *h = c->h_tiny_ids.as<char>() + o_stage;
+            memcpy(h, c->chunks_fwd.data(), b_chunks);
+            memcpy(h + o_first, c->job_first_chunk_fwd.data(), b_first);
+            if (ctl_copy(c->stream, c->d_chunks_fwd.p, h, b_chunks) ||
+                ctl_copy(c->stream, c->d_job_first_chunk_fwd.p, h + o_first, b_first))
+                return 1;
+            std::swap(c->d_chunks, c->d_chunks_fwd);
+            std::swap(c->d_job_first_chunk, c->d_job_first_chunk_fwd);
+            c->chunks.swap(c->chunks_fwd);
+        }
+        const int band_rc = run_band(c, false, false, false);
+        if (filtered) {
+            std::swap(c->d_chunks, c->d_chunks_fwd);
+            std::swap(c->d_job_first_chunk, c->d_job_first_chunk_fwd);
+            c->chunks.swap(c->chunks_fwd);
+        }
+        if (band_rc) return 1;
+        Bins bins;
+        if (build_bins(c, false, bins, c->force_group)) return 1;
+        if (c->d_F.ensure((size_t) (c->total_cells + 1) * 3 * sizeof(double))) return 1;
+        launch_forward<8>(c, bins.seq_fwd[0], bins.seq_fwd[1] - bins.seq_fwd[0]);
+        launch_forward<16>(c, bins.seq_fwd[1], bins.seq_fwd[2] - bins.seq_fwd[1]);
+        launch_forward<32>(c, bins.seq_fwd[2], bins.seq_fwd[3] - bins.seq_fwd[2]);
+        const int n_gen = bins.seq_fwd[3] - bins.seq_fwd[0];
+        if (n_gen > 0) {
+            { KTimer kt_(c, K_FINAL); mb::final_dot_kernel<<<(n_gen + 127) / 128, 128, 0, c->stream>>>(
+                  c->d_jobs.as<mb::Job>(), c->p_ids + bins.seq_fwd[0], n_gen, c->d_models.as<mb::DevModel>(),
+                  c->d_cell_off.as<uint32_t>(), c->d_F.as<double>(), c->d_fwd_out.as<double>()); }
+            c->launches++;
+        }
+        for (int j = 0; j < nj; j++)
+            if (!c->tiny_mask[j]) general_cells += c->job_cells[j];
+    }
+    if (n_tiny > 0) {
+        if (c->h_tiny_ids.ensure((size_t) n_tiny * 4 + 16) || c->d_tiny_ids.ensure((size_t) n_tiny * 4 + 16)) return 1;
+        int32_t *ids = c->h_tiny_ids.as<int32_t>();
+        int n16 = 0;
+        for (int j = 0; j < nj; j++)
+            if (c->tiny_mask[j] && std::min(c->jobs[j].lx, c->jobs[j].ly) + 1 <= 16) ids[n16++] = j;
+        int n_all = n16;
+        for (int j = 0; j < nj; j++)
+            if (c->tiny_mask[j] && std::min(c->jobs[j].lx, c->jobs[j].ly) + 1 > 16) ids[n_all++] = j;
+        if (ctl_copy(c->stream, c->d_tiny_ids.p, ids, (size_t) n_tiny * 4)) return 1;
+        const int32_t *d_ids = c->d_tiny_ids.as<int32_t>();
+        const int e = (int) c->params.diagonal_expansion;
+        auto launch = [&](auto g_tag, int off, int count) {
+            constexpr int G = decltype(g_tag)::value;
+            if (count <= 0) return;
+            const int per_block = kTileThreads / G;
+            const unsigned grid = (unsigned) ((count + per_block - 1) / per_block);
+            KTimer kt_(c, K_FORWARD);
+            if (c->have_switch)
+                mb::tiny_forward_kernel<G, kTileThreads, true><<<grid, kTileThreads, 0, c->stream>>>(
+                    c->d_jobs.as<mb::Job>(), d_ids + off, count, c->d_models.as<mb::DevModel>(),
+                    c->d_px.as<uint8_t>() + mb::PACK_SLACK, c->d_py.as<uint8_t>() + mb::PACK_SLACK, e,
+                    c->d_fwd_out.as<double>());
+            else
+                mb::tiny_forward_kernel<G, kTileThreads, false><<<grid, kTileThreads, 0, c->stream>>>(
+                    c->d_jobs.as<mb::Job>(), d_ids + off, count, c->d_models.as<mb::DevModel>(),
+                    c->d_px.as<uint8_t>() + mb::PACK_SLACK, c->d_py.as<uint8_t>() + mb::PACK_SLACK, e,
+                    c->d_fwd_out.as<double>());
+            c->launches++;
+        };
+        launch(std::integral_constant<int, 16>{}, 0, n16);
+        launch(std::integral_constant<int, 32>{}, n16, n_tiny - n16);
     }
     CU(cudaEventRecord(c->ev1, c->stream));
     CU(cudaStreamSynchronize(c->stream));
     CU(cudaGetLastError());
     float ms = 0;
     CU(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+    c->total_cells = general_cells + tiny_cells;  // tiny matrices are counted whole (their band leaves out far corners at most)
+    c->tiny_mask.clear();
     if (stats) {
         memset(stats, 0, sizeof(*stats));
         fill_stats(c, stats, 0, ms);

@@ -1026,12 +1026,12 @@ __global__ void list_offsets_kernel(const int32_t *__restrict__ aln_first_slot, 
 
 // computeForwardProbability's last step (pairwiseAligner.c:881-891): the only cell of the last diagonal is
 // (lX, lY); total = cell_dotProduct(F, end state probs).  An empty problem returns LOG_ONE (:860-862).
-__global__ void final_dot_kernel(const Job *__restrict__ jobs, int n_jobs, const DevModel *__restrict__ models,
-                                 const uint32_t *__restrict__ cell_off, const double *__restrict__ F,
-                                 double *__restrict__ out) {
-    const int j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= n_jobs) return;
-    const Job job = jobs[j];
+__global__ void final_dot_kernel(const Job *__restrict__ jobs, const int32_t *__restrict__ ids, int n_ids,
+                                 const DevModel *__restrict__ models, const uint32_t *__restrict__ cell_off,
+                                 const double *__restrict__ F, double *__restrict__ out) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n_ids) return;
+    const Job job = jobs[ids[k]];
     const int N = job.lx + job.ly;
     if (N == 0) {
         out[job.aln] = 0.0;

@@ -304,6 +304,128 @@ __device__ __forceinline__ double cell_dot_t(const Cell &a, const Cell &b, uint3
     return tp;
 }
 
+// ----------------------------------------------------------------------------------------- forward only, tiny
+//
+// computeForwardProbability (pairwiseAligner.c:849-903) for the matrices poa_polish scores alleles with (SURVEY A9:
+// lX, lY median 11, max 43, no anchors, ~0.4 M calls per chunk): one group of G lanes per matrix, the whole sweep in
+// registers, band geometry computed inline from the four corner points of band_construct without anchors
+// (pairwiseAligner.c:161-226 with one "anchor pair" (0,0) -> (lX,lY)), nothing written but the final log-probability
+// cell_dotProduct(F(lX,lY), end state) (:881-891).  Same lane mapping, validity rule and logAdd as the tile kernels.
+template <int G, int THREADS, bool SWITCH>
+__global__ void __launch_bounds__(THREADS)
+tiny_forward_kernel(const Job *__restrict__ jobs, const int32_t *__restrict__ ids, int n_ids,
+                    const DevModel *__restrict__ models, const uint8_t *__restrict__ px, const uint8_t *__restrict__ py,
+                    int expansion, double *__restrict__ out) {
+    __shared__ __align__(16) TileShared sh;
+    tile_shared_init<THREADS>(sh, models);
+    const int tid = tid_x_once();
+    const int g = (blockIdx.x * THREADS + tid) / G;
+    const bool real = g < n_ids;
+    const int lane = tid & (G - 1);
+    const int prev_lane = mod_g(lane - 1, G);
+    const Job job = jobs[ids[min(g, n_ids - 1)]];
+    const DevModel &m = sh.model[job.slot];
+    const uint32_t lac_s = smem_u32(sh.lac);
+    const uint32_t gx_s = smem_u32(&sh.gx[job.slot][0][0]), gy_s = smem_u32(&sh.gy[job.slot][0][0]);
+    const int lx = job.lx, ly = job.ly, N = lx + ly;
+    const uint8_t *sx = px + job.symx_off - 1, *sy = py + job.symy_off - 1;  // sx[x] = symbol of column x (1-based)
+    const double *emP = m.emit_packed;
+    const double tMM = m.t[T_MM], tXM = m.t[T_XM], tYM = m.t[T_YM];
+    // corner points of the band (band_diagonal with no anchors: previous point (0,0), next point (lX,lY))
+    const int nxay = lx + ly, nxmy = lx - ly, e = expansion;
+    const int xL = bound_coord((0 + 0 - e) / 2, lx), yL = bound_coord((nxay - (nxmy - e)) / 2, ly);
+    const int xU = bound_coord((nxay + nxmy + e) / 2, lx), yU = bound_coord((0 - (0 + e)) / 2, ly);
+    auto geo_of = [&](int d, int &xlo, int &w) {  // diagonal d >= 1 (clamped to N)
+        int kl, kr;
+        clip_diagonal(min(d, N), xL, yL, xU, yU, kl, kr);
+        xlo = (min(d, N) + kl) >> 1;
+        w = (kr - kl) / 2 + 1;
+    };
+    auto lane_x = [&](int xlo) { return xlo + mod_g(lane - xlo, G); };
+    // diagonal 0: the start state (stateMachine.c:521-530)
+    Cell f1 = cell_neg_inf(), res = cell_neg_inf();
+    double midm = MB_NEG_INF, midx = MB_NEG_INF, midy = MB_NEG_INF;
+    if (lane == 0) {
+        f1.m = job.ragged_l ? MB_NEG_INF : 0.0;
+        f1.x = job.ragged_l ? 0.0 : MB_NEG_INF;
+        f1.y = f1.x;
+    }
+    int xlo1 = 0, xlo2 = -2 * G;
+    // pipeline: geometry two diagonals ahead, symbols one ahead, emission for the current one fetched a step early
+    int xloA, wA, xloB, wB;
+    geo_of(1, xloA, wA);
+    geo_of(2, xloB, wB);
+    unsigned cxA, cyA, cxB, cyB;
+    {
+        const int xa = lane_x(xloA);
+        cxA = __ldg(sx + xa);
+        cyA = __ldg(sy + (min(1, N) - xa));
+        const int xb = lane_x(xloB);
+        cxB = __ldg(sx + xb);
+        cyB = __ldg(sy + (min(2, N) - xb));
+    }
+    double eA = __ldg(emP + cxA * PACK_STRIDE + cyA);
+    const int n_max = __reduce_max_sync(0xffffffffu, N);
+    for (int d = 1; d <= n_max; d++) {
+        // ---- loads for the diagonals ahead
+        int xloC, wC;
+        geo_of(d + 2, xloC, wC);
+        const int xc = lane_x(xloC);
+        const unsigned cxC = __ldg(sx + xc), cyC = __ldg(sy + (min(d + 2, N) - xc));
+        const double eB = __ldg(emP + cxB * PACK_STRIDE + cyB);
+        // ---- diagonal d
+        const int r = mod_g(lane - xloA, G);
+        const int x = xloA + r;
+        const bool active = r < wA && d <= N;
+        const double lm = shfl_g<G>(f1.m, prev_lane);
+        const double lx_ = shfl_g<G>(f1.x, prev_lane);
+        const double ly_ = shfl_g<G>(f1.y, prev_lane);
+        const int xe = active ? x : FAR_X;
+        const bool ok_lower = (unsigned) (xe - 1 - xlo1) < (unsigned) G;
+        const bool ok_upper = (unsigned) (xe - xlo1) < (unsigned) G;
+        const bool ok_middle = (unsigned) (xe - 1 - xlo2) < (unsigned) G;
+        const uint32_t exa = gx_s + 32u * (unsigned) packed_base(cxA), eya = gy_s + 32u * (unsigned) packed_base(cyA);
+        const double2 ex = lds_f64x2(exa), ey = lds_f64x2(eya);
+        Cell c;
+        c.x = logadd_t(dadd(lm, ex.x), dadd(lx_, ex.y), lac_s);
+        if (SWITCH) c.x = logadd_t(c.x, dadd(ly_, lds_f64(exa + 16)), lac_s);
+        c.m = logadd_t(dadd(midm, dadd(eA, tMM)), dadd(midx, dadd(eA, tXM)), lac_s);
+        c.m = logadd_t(c.m, dadd(midy, dadd(eA, tYM)), lac_s);
+        c.y = logadd_t(dadd(f1.m, ey.x), dadd(f1.y, ey.y), lac_s);
+        if (SWITCH) c.y = logadd_t(c.y, dadd(f1.x, lds_f64(eya + 16)), lac_s);
+        c.x = ok_lower ? c.x : MB_NEG_INF;
+        c.m = ok_middle ? c.m : MB_NEG_INF;
+        c.y = ok_upper ? c.y : MB_NEG_INF;
+        if (d == N && active && x == lx) res = c;
+        // ---- carry
+        midm = lm;
+        midx = lx_;
+        midy = ly_;
+        f1 = c;
+        xlo2 = xlo1;
+        xlo1 = xloA;
+        xloA = xloB;
+        wA = wB;
+        xloB = xloC;
+        wB = wC;
+        cxA = cxB;
+        cyA = cyB;
+        cxB = cxC;
+        cyB = cyC;
+        eA = eB;
+    }
+    if (N == 0) res = f1;  // (0,0) is the last cell; the caller special-cases the empty problem below
+    const int owner = N == 0 ? 0 : mod_g(lx, G);
+    if (real && lane == owner) {
+        const double *endp = m.end_p[job.ragged_r ? 1 : 0];
+        Cell ec;
+        ec.m = endp[0];
+        ec.x = endp[1];
+        ec.y = endp[2];
+        out[job.aln] = N == 0 ? 0.0 : cell_dot_t(res, ec, lac_s);  // an empty problem returns LOG_ONE (:860-862)
+    }
+}
+
 // Per-diagonal lane bookkeeping shared by the three staged lists: `bits` of a ballot are cut down to the group,
 // rotated so that bit i is the cell x = xlo + i, and a passing cell is appended behind the passing cells below it.
 template <int G>
