@@ -462,8 +462,11 @@ struct StageLane {
 // Same register pipeline as the forward kernel, walking down, with the geometry of d+1 .. d-2 in a move chain.
 // Lanes outside their diagonal keep -inf, so the three sources of a cell are valid exactly when their x lies in the
 // G-wide window of the lane mapping of their diagonal.
+#ifndef MB_BWD_MIN_BLOCKS
+#define MB_BWD_MIN_BLOCKS 4
+#endif
 template <int G, int THREADS, bool INDELS, bool SWITCH>
-__global__ void __launch_bounds__(THREADS)
+__global__ void __launch_bounds__(THREADS, MB_BWD_MIN_BLOCKS)
 backward_tile_kernel(const Job *__restrict__ jobs, const Tile *__restrict__ tiles, const int32_t *__restrict__ ids,
                      int n_ids, const DevModel *__restrict__ models, const uint8_t *__restrict__ px,
                      const uint8_t *__restrict__ py, const int2 *__restrict__ geo, const double *__restrict__ F,
