@@ -41,6 +41,7 @@ int fail(const char *fmt, ...) {
 
 constexpr int kMaxDevices = 64;
 std::atomic<int> g_live_contexts[kMaxDevices];  // top-level contexts per device (sub-contexts of a pipeline excluded)
+std::mutex g_compute_token[kMaxDevices];        // see margin_b200_posteriors_batch
 
 #define CU(call)                                                                                        \
     do {                                                                                                \
@@ -147,6 +148,7 @@ struct margin_b200_ctx {
     int pipe_fill = 2;                                  // MARGIN_B200_PIPE_FILL: SM share a run's tiles are cut for, in 1/K
     int64_t pipeline_min_bytes = 8 << 20;               // MARGIN_B200_PIPELINE_MIN_BYTES of host input
     bool is_sub = false, last_pipelined = false, counted = false;
+    bool take_token = false;                            // posteriors_resident: hold the device's compute token while the DP kernels run
     bool kernel_timing = false;                         // margin_b200_set_kernel_timing / MARGIN_B200_KERNEL_TIMING
     int pair_format = MARGIN_B200_PAIRS_TRIPLES;        // what the caller asked for
     bool packed_now = false;                            // ... and what this batch gets (sequence lengths permitting)
@@ -1199,6 +1201,10 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
         c->d_off_out.ensure((size_t) 3 * (c->n_aln + 1) * sizeof(int64_t)))
         return 1;
     CU(cudaMemsetAsync(c->d_seg_counts.p, 0, ((size_t) 3 * S + 1) * sizeof(int64_t), c->stream));
+    // Several contexts on one device take turns from here to the final synchronisation (margin_b200_posteriors_batch);
+    // the band phase above, with its host round trip, runs beside the other context's kernels.
+    std::unique_lock<std::mutex> token;
+    if (c->take_token) token = std::unique_lock<std::mutex>(g_compute_token[c->device & (kMaxDevices - 1)]);
     launch_forward<8>(c, bins.seq_fwd[0], bins.seq_fwd[1] - bins.seq_fwd[0]);
     launch_forward<16>(c, bins.seq_fwd[1], bins.seq_fwd[2] - bins.seq_fwd[1]);
     launch_forward<32>(c, bins.seq_fwd[2], bins.seq_fwd[3] - bins.seq_fwd[2]);
@@ -1544,10 +1550,6 @@ int posteriors_pipelined(margin_b200_ctx *c, const margin_b200_batch *b, int wan
 // them take turns on the SMs, so one context's copies run beside another's kernels.  A context that is the only one on
 // its device pipelines inside the call instead (posteriors_pipelined).  The choice depends on the number of live
 // contexts, not on timing, so a context always takes the same path (and its arenas are sized once).
-namespace {
-std::mutex g_compute_token[kMaxDevices];
-}  // namespace
-
 extern "C" int margin_b200_posteriors_batch(margin_b200_ctx *c, const margin_b200_batch *b, int want_indels,
                                             margin_b200_result *out) {
     if (!c || !b || !out) return fail("margin_b200_posteriors_batch: null argument");
@@ -1564,10 +1566,10 @@ extern "C" int margin_b200_posteriors_batch(margin_b200_ctx *c, const margin_b20
         if (K > 1 && bytes >= c->pipeline_min_bytes) return posteriors_pipelined(c, b, want_indels, out, K);
     }
     if (margin_b200_upload_batch(c, b)) return 1;
-    {
-        std::lock_guard<std::mutex> token(g_compute_token[dev_slot]);
-        if (margin_b200_posteriors_resident(c, want_indels, out)) return 1;
-    }
+    c->take_token = true;
+    const int rc = margin_b200_posteriors_resident(c, want_indels, out);
+    c->take_token = false;
+    if (rc) return 1;
     return margin_b200_download_result(c, out);
 }
 

@@ -12,7 +12,7 @@ def main():
     contexts = int(sys.argv[1]) if len(sys.argv) > 1 else 2
     rounds = int(sys.argv[2]) if len(sys.argv) > 2 else 4
     pm, items = bench.build_items(bench.DEFAULT_WORKLOAD, 42)
-    batch = abi.Batch(items)
+    batch = abi.Batch(items, compact=True)
     bench.pin_batch(batch)
     from margin_b200.aligner import PairHmmAligner
     al = PairHmmAligner(pm.models, pm.p, device=0)
