@@ -104,6 +104,8 @@ struct PinBuf {
 struct margin_b200_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t stream_sym = nullptr;  // symbols travel and are packed beside the anchor checks and the band phase
+    cudaEvent_t ev_sym = nullptr;       // ... and the DP kernels wait for this
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     bool have_model[2] = {false, false};
     bool have_params = false;
@@ -137,7 +139,7 @@ struct margin_b200_ctx {
     std::vector<int32_t> span_tmp;
     std::vector<uint8_t> tiny_mask;  // forward-only: jobs swept by tiny_forward_kernel (skipped by build_bins)
     PinBuf h_tiny_ids;
-    DevBuf d_tiny_ids, d_chunks_fwd, d_job_first_chunk_fwd;
+    DevBuf d_sym_err, d_tiny_ids, d_chunks_fwd, d_job_first_chunk_fwd;
     std::vector<mb::BandChunk> chunks_fwd;
     std::vector<int32_t> job_first_chunk_fwd;
     // ---- pipelined batches (posteriors_pipelined): sub-contexts with their own stream and arenas
@@ -315,6 +317,8 @@ int margin_b200_create(margin_b200_ctx **out, int device) {
     margin_b200_ctx *c = new margin_b200_ctx();
     c->device = device;
     CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&c->stream_sym, cudaStreamNonBlocking));
+    CU(cudaEventCreateWithFlags(&c->ev_sym, cudaEventDisableTiming));
     CU(cudaEventCreate(&c->ev0));
     CU(cudaEventCreate(&c->ev1));
     if (const char *e = getenv("MARGIN_B200_MODE")) c->mode_sequential = strcmp(e, "sequential") == 0;
@@ -356,7 +360,7 @@ void margin_b200_destroy(margin_b200_ctx *c) {
                       &c->d_ids, &c->d_aln_first_slot, &c->d_F, &c->d_stage, &c->d_out, &c->d_off_out, &c->d_fwd_out,
                       &c->d_geo, &c->d_tiles, &c->d_bnd, &c->d_slot_bnd_off, &c->d_emit5[0], &c->d_emit5[1],
                       &c->d_px, &c->d_py, &c->d_stage2, &c->d_chunks, &c->d_job_first_chunk, &c->d_chunk_sum, &c->d_chunk_maxw,
-                      &c->d_totals, &c->d_band_out, &c->d_anchors_delta, &c->d_tiny_ids, &c->d_chunks_fwd, &c->d_job_first_chunk_fwd, &c->d_arena, &c->d_offs, &c->d_status};
+                      &c->d_totals, &c->d_band_out, &c->d_anchors_delta, &c->d_sym_err, &c->d_tiny_ids, &c->d_chunks_fwd, &c->d_job_first_chunk_fwd, &c->d_arena, &c->d_offs, &c->d_status};
     for (DevBuf *b : bufs) b->release();
     c->h_stage_in.release();
     c->h_small.release();
@@ -369,6 +373,9 @@ void margin_b200_destroy(margin_b200_ctx *c) {
     for (cudaEvent_t e : c->ev_pool) cudaEventDestroy(e);
     cudaEventDestroy(c->ev0);
     cudaEventDestroy(c->ev1);
+    cudaStreamSynchronize(c->stream_sym);
+    cudaEventDestroy(c->ev_sym);
+    cudaStreamDestroy(c->stream_sym);
     cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -591,8 +598,7 @@ extern "C" int margin_b200_upload_batch(margin_b200_ctx *c, const margin_b200_ba
         c->d_err.ensure(sizeof(double)) ||
         c->h_small.ensure(((size_t) 2 * n + 4) * sizeof(int32_t) + (size_t) 3 * (n + 1) * sizeof(int64_t)))
         return 1;
-    if (nx) CU(cudaMemcpyAsync(c->d_symx.p, b->sym_x, nx * sizeof(uint16_t), cudaMemcpyHostToDevice, c->stream));
-    if (ny) CU(cudaMemcpyAsync(c->d_symy.p, b->sym_y, ny * sizeof(uint16_t), cudaMemcpyHostToDevice, c->stream));
+    CU(cudaStreamSynchronize(c->stream_sym));  // idle unless an upload was never followed by a sweep
     if (total_anchor_triples) {
         if (b->anchors_delta) {
             if (c->d_anchors_delta.ensure((size_t) total_anchor_triples * sizeof(uint32_t))) return 1;
@@ -621,24 +627,28 @@ extern "C" int margin_b200_upload_batch(margin_b200_ctx *c, const margin_b200_ba
                                                                      d_offs + 2 * (n + 1), p.split_matrix_bigger_than_this,
                                                                      c->d_status.as<int32_t>());
     }
-    // packed one-byte symbols for the tile kernels (slack on both sides, see pairhmm_tiles.cuh)
-    CU(cudaMemsetAsync(c->d_px.p, 0, (size_t) nx + 2 * mb::PACK_SLACK, c->stream));
-    CU(cudaMemsetAsync(c->d_py.p, 0, (size_t) ny + 2 * mb::PACK_SLACK, c->stream));
-    CU(cudaMemsetAsync(c->d_err.p, 0, sizeof(double), c->stream));
-    if (nx) mb::pack_symbols_kernel<<<(unsigned) ((nx + 255) / 256), 256, 0, c->stream>>>(
-            c->d_symx.as<uint16_t>(), c->d_px.as<uint8_t>() + mb::PACK_SLACK, nx, rle, c->d_err.as<int>());
-    if (ny) mb::pack_symbols_kernel<<<(unsigned) ((ny + 255) / 256), 256, 0, c->stream>>>(
-            c->d_symy.as<uint16_t>(), c->d_py.as<uint8_t>() + mb::PACK_SLACK, ny, rle, c->d_err.as<int>());
+    // Symbols are queued behind the anchors on their own stream: the host only waits for the anchor checks below, the
+    // band phase of the sweep runs while the symbols still travel, and the DP kernels wait for ev_sym.  Packed
+    // one-byte copies for the tile kernels (slack on both sides, see pairhmm_tiles.cuh); a run length the model cannot
+    // hold is reported by the sweep (d_sym_err).
+    if (c->d_sym_err.ensure(16)) return 1;
+    if (nx) CU(cudaMemcpyAsync(c->d_symx.p, b->sym_x, nx * sizeof(uint16_t), cudaMemcpyHostToDevice, c->stream_sym));
+    if (ny) CU(cudaMemcpyAsync(c->d_symy.p, b->sym_y, ny * sizeof(uint16_t), cudaMemcpyHostToDevice, c->stream_sym));
+    CU(cudaMemsetAsync(c->d_px.p, 0, (size_t) nx + 2 * mb::PACK_SLACK, c->stream_sym));
+    CU(cudaMemsetAsync(c->d_py.p, 0, (size_t) ny + 2 * mb::PACK_SLACK, c->stream_sym));
+    CU(cudaMemsetAsync(c->d_sym_err.p, 0, 16, c->stream_sym));
+    if (nx) mb::pack_symbols_kernel<<<(unsigned) ((nx + 255) / 256), 256, 0, c->stream_sym>>>(
+            c->d_symx.as<uint16_t>(), c->d_px.as<uint8_t>() + mb::PACK_SLACK, nx, rle, c->d_sym_err.as<int>());
+    if (ny) mb::pack_symbols_kernel<<<(unsigned) ((ny + 255) / 256), 256, 0, c->stream_sym>>>(
+            c->d_symy.as<uint16_t>(), c->d_py.as<uint8_t>() + mb::PACK_SLACK, ny, rle, c->d_sym_err.as<int>());
+    CU(cudaEventRecord(c->ev_sym, c->stream_sym));
     if (n && ctl_copy(c->stream, h_status, c->d_status.p, (size_t) 2 * n * sizeof(int32_t))) return 1;
-    if (ctl_copy(c->stream, h_status + 2 * n, c->d_err.p, sizeof(int))) return 1;
     tr.mark("enqueue");
     if (c->after_h2d_enqueue) c->after_h2d_enqueue();
     CU(cudaStreamSynchronize(c->stream));
     CU(cudaGetLastError());
     tr.mark("h2d+check sync");
-    if (h_status[2 * n])
-        return fail("a symbol carries a run length >= %d; the repeat-count model holds 0..%d", MARGIN_B200_MAX_RL,
-                    MARGIN_B200_MAX_RL - 1);
+
     // ---- job table: one job per alignment, or one per block where getSplitPoints cuts (rare: host path)
     std::vector<int32_t> extra_anchors;
     std::vector<Block> blocks;
@@ -1205,6 +1215,7 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
     // the band phase above, with its host round trip, runs beside the other context's kernels.
     std::unique_lock<std::mutex> token;
     if (c->take_token) token = std::unique_lock<std::mutex>(g_compute_token[c->device & (kMaxDevices - 1)]);
+    CU(cudaStreamWaitEvent(c->stream, c->ev_sym, 0));  // the symbols (upload's second stream) are needed from here on
     launch_forward<8>(c, bins.seq_fwd[0], bins.seq_fwd[1] - bins.seq_fwd[0]);
     launch_forward<16>(c, bins.seq_fwd[1], bins.seq_fwd[2] - bins.seq_fwd[1]);
     launch_forward<32>(c, bins.seq_fwd[2], bins.seq_fwd[3] - bins.seq_fwd[2]);
@@ -1245,6 +1256,8 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
     // back with the final synchronisation, and an overflow re-runs the gather into an exactly sized buffer.
     int64_t *bounds = reinterpret_cast<int64_t *>(c->h_small.as<char>());  // pinned; run_band's landing zone is consumed
     ctl_bounds_kernel<<<1, 32, 0, c->stream>>>(c->d_seg_off.as<int64_t>(), S, bounds);
+    bounds[4] = 0;
+    if (c->d_sym_err.p && ctl_copy(c->stream, bounds + 4, c->d_sym_err.p, 8)) return 1;  // pack_symbols_kernel's verdict
     const size_t want_cap = (size_t) cells / (want_indels ? 3 : 6) + 4096;
     if (c->d_out.cap / sizeof(mb::Pair) < want_cap && c->d_out.ensure(want_cap * sizeof(mb::Pair))) return 1;
     auto run_gather = [&]() {
@@ -1280,6 +1293,9 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
     CU(cudaStreamSynchronize(c->stream));
     CU(cudaGetLastError());
     tr.mark("final sync");
+    if (*reinterpret_cast<int *>(bounds + 4))
+        return fail("a symbol carries a run length >= %d; the repeat-count model holds 0..%d", MARGIN_B200_MAX_RL,
+                    MARGIN_B200_MAX_RL - 1);
     c->total_tuples = bounds[3];
     for (int l = 0; l < 3; l++) c->list_tuples[l] = bounds[l + 1] - bounds[l];
     if ((size_t) c->total_tuples > c->d_out.cap / sizeof(mb::Pair)) {  // estimate too small: exact size, gather again
@@ -1621,6 +1637,7 @@ extern "C" int margin_b200_forward_resident(margin_b200_ctx *c, margin_b200_resu
         return fail("margin_b200_forward: an alignment was split by splitMatrixBiggerThanThis; the forward-only "
                     "path takes whole matrices");
     CU(cudaEventRecord(c->ev0, c->stream));
+    CU(cudaStreamWaitEvent(c->stream, c->ev_sym, 0));
     c->force_group = force_group_env();
     // The bubble-graph case: a matrix that is small and has no anchors is swept in registers (no band
     // tables, no F in HBM); anything else takes the general path (band kernels, sequential forward sweep, final dot).
@@ -1728,8 +1745,15 @@ extern "C" int margin_b200_forward_resident(margin_b200_ctx *c, margin_b200_resu
         launch(std::integral_constant<int, 32>{}, n16, n_tiny - n16);
     }
     CU(cudaEventRecord(c->ev1, c->stream));
+    if (c->h_small.ensure(64)) return 1;
+    int *h_sym_err = reinterpret_cast<int *>(c->h_small.as<char>() + 32);
+    *h_sym_err = 0;
+    if (c->d_sym_err.p && ctl_copy(c->stream, h_sym_err, c->d_sym_err.p, 8)) return 1;
     CU(cudaStreamSynchronize(c->stream));
     CU(cudaGetLastError());
+    if (*h_sym_err)
+        return fail("a symbol carries a run length >= %d; the repeat-count model holds 0..%d", MARGIN_B200_MAX_RL,
+                    MARGIN_B200_MAX_RL - 1);
     float ms = 0;
     CU(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
     c->total_cells = general_cells + tiny_cells;  // tiny matrices are counted whole (their band leaves out far corners at most)

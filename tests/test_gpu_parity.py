@@ -176,6 +176,13 @@ def test_errors_are_loud(golden_model):
     with pytest.raises(AlignerError):  # traceBackDiagonals + 1 < minDiagsBetweenTraceBack (:718)
         al.set_params(pm.p.copy(min_diags_between_traceback=30))
     assert len(al.posteriors_batch([])) == 0
+    bad = sx.copy()
+    bad[3] = (51 << 8) | 1  # a run length the repeat-count model cannot hold (reported by the sweep)
+    with pytest.raises(AlignerError, match="run length"):
+        al.posteriors_batch([(bad, sx, [(5, 5, 4)], 0, 0, 0)])
+    with pytest.raises(AlignerError, match="run length"):
+        al.forward_batch([(sx, bad, np.zeros((0, 3), np.int32), 0, 0, 0)])
+    assert len(al.posteriors_batch([(sx, sx, [(5, 5, 4)], 0, 0, 0)])) == 1  # the context is usable afterwards
     al.close()
 
 
