@@ -2,13 +2,16 @@
  * pairwiseAligner_b200.c — the reference-side binding of libmargin_b200.so.
  *
  * This file is compiled AGAINST margin's own headers (inc/margin.h, sonLib) and linked INTO margin in place of the
- * bodies of five functions; everything else of impl/pairwiseAligner.c and impl/poa.c stays the reference's code:
+ * bodies of seven functions; everything else of impl/pairwiseAligner.c and impl/poa.c stays the reference's code:
  *
  *   getAlignedPairsWithIndelsUsingAnchors   inc/pairwiseAligner.h:81-84   (impl/pairwiseAligner.c:1144-1171)
  *   getAlignedPairsUsingAnchors             inc/pairwiseAligner.h:77-79   (impl/pairwiseAligner.c:1125-1142)
  *   getAlignedPairsWithIndels               inc/pairwiseAligner.h:68-72   (impl/pairwiseAligner.c:1183-1191)
  *   getAlignedPairs                         inc/pairwiseAligner.h:62-66   (impl/pairwiseAligner.c:1173-1181)
  *   poa_realign                             inc/margin.h:684              (impl/poa.c:668-716), one batched call per chunk
+ *   computeForwardProbability               inc/pairwiseAligner.h:54-57   (impl/pairwiseAligner.c:849-905)
+ *   poa_polish                              inc/margin.h:820              (impl/poa.c:1852-1873), one batched forward call
+ *                                                                          per bubble graph (impl/bubbleGraph.c:1067 unchanged)
  *
  * Same signatures, same ownership (callee-allocated stLists of individually allocated stIntTuples with
  * stIntTuple_destruct as destructor), same list order, same error behaviour (invalid band ->
@@ -45,12 +48,18 @@ typedef struct {
     bool strand;
 } B200RleNucleotideEmissions;
 
+struct B200Deferred;
+
 typedef struct {
     margin_b200_ctx *ctx;
     StateMachine *sm[2];                 /* machines currently loaded in slots 0 / 1 */
     PairwiseAlignmentParameters params;  /* parameters currently loaded */
     int haveParams;
     margin_b200_model scratch;
+    margin_b200_model loaded[2];   /* copies of what slots 0 / 1 hold (only read by the MARGIN_B200_DUMP hook) */
+    margin_b200_params loadedParams;
+    int dynamicAnchors;            /* whether b200_batch_add reads the anchors' third field (p->dynamicAnchorExpansion) */
+    struct B200Deferred *deferred; /* non-NULL while poa_polish collects forward jobs (see the last section) */
 } B200Thread;
 
 static __thread B200Thread tls;
@@ -113,9 +122,11 @@ static void b200_load_machine(int slot, StateMachine *sM) {
     }
     if (margin_b200_set_model(b200_ctx(), slot, m) != 0) b200_fail();
     tls.sm[slot] = sM;
+    tls.loaded[slot] = *m;
 }
 
 static void b200_load_params(PairwiseAlignmentParameters *p) {
+    tls.dynamicAnchors = p->dynamicAnchorExpansion;
     if (tls.haveParams && tls.params.threshold == p->threshold &&
         tls.params.minDiagsBetweenTraceBack == p->minDiagsBetweenTraceBack &&
         tls.params.traceBackDiagonals == p->traceBackDiagonals && tls.params.diagonalExpansion == p->diagonalExpansion &&
@@ -131,6 +142,7 @@ static void b200_load_params(PairwiseAlignmentParameters *p) {
     q.split_matrix_bigger_than_this = p->splitMatrixBiggerThanThis;
     q.dynamic_anchor_expansion = p->dynamicAnchorExpansion;
     if (margin_b200_set_params(b200_ctx(), &q) != 0) b200_fail();
+    tls.loadedParams = q;
     tls.params = *p;
     tls.haveParams = 1;
 }
@@ -138,7 +150,7 @@ static void b200_load_params(PairwiseAlignmentParameters *p) {
 /* ------------------------------------------------------------------------------------------------ batches */
 
 typedef struct {
-    int64_t n, capX, capY, capA;
+    int64_t n, capN, capX, capY, capA;
     uint16_t *symX, *symY;
     int32_t *anchors;
     uint32_t *anchorsDelta; /* the compact words of margin_b200_batch.anchors_delta, kept beside the triples */
@@ -150,13 +162,26 @@ typedef struct {
 static B200Batch *b200_batch_construct(int64_t n) {
     B200Batch *b = st_calloc(1, sizeof(B200Batch));
     b->compactOk = 1;
-    b->offX = st_calloc(n + 1, sizeof(int64_t));
-    b->offY = st_calloc(n + 1, sizeof(int64_t));
-    b->offA = st_calloc(n + 1, sizeof(int64_t));
-    b->slot = st_calloc(n + 1, 1);
-    b->raggedL = st_calloc(n + 1, 1);
-    b->raggedR = st_calloc(n + 1, 1);
+    b->capN = n < 1 ? 1 : n;
+    b->offX = st_calloc(b->capN + 1, sizeof(int64_t));
+    b->offY = st_calloc(b->capN + 1, sizeof(int64_t));
+    b->offA = st_calloc(b->capN + 1, sizeof(int64_t));
+    b->slot = st_calloc(b->capN + 1, 1);
+    b->raggedL = st_calloc(b->capN + 1, 1);
+    b->raggedR = st_calloc(b->capN + 1, 1);
     return b;
+}
+
+/* Room for one more alignment (the deferred forward queue does not know its size in advance). */
+static void b200_batch_grow(B200Batch *b) {
+    if (b->n < b->capN) return;
+    b->capN = b->capN * 2 + 1024;
+    b->offX = st_realloc(b->offX, (b->capN + 1) * sizeof(int64_t));
+    b->offY = st_realloc(b->offY, (b->capN + 1) * sizeof(int64_t));
+    b->offA = st_realloc(b->offA, (b->capN + 1) * sizeof(int64_t));
+    b->slot = st_realloc(b->slot, b->capN + 1);
+    b->raggedL = st_realloc(b->raggedL, b->capN + 1);
+    b->raggedR = st_realloc(b->raggedR, b->capN + 1);
 }
 
 static void b200_batch_destruct(B200Batch *b) {
@@ -176,6 +201,7 @@ static void b200_batch_destruct(B200Batch *b) {
 /* Appends one alignment; anchor x coordinates are shifted by -shiftX (the crop of impl/poa.c:637-639). */
 static void b200_batch_add(B200Batch *b, SymbolString sX, SymbolString sY, stList *anchorPairs, int64_t shiftX, int slot,
                            bool raggedL, bool raggedR) {
+    b200_batch_grow(b);
     int64_t i = b->n++;
     int64_t nA = anchorPairs == NULL ? 0 : stList_length(anchorPairs);
     int64_t oX = b->offX[i], oY = b->offY[i], oA = b->offA[i];
@@ -200,7 +226,7 @@ static void b200_batch_add(B200Batch *b, SymbolString sX, SymbolString sY, stLis
         b->anchors[3 * (oA + k) + 1] = (int32_t) stIntTuple_get(a, 1);
         /* anchors may come as pairs (x, y): band_construct then uses p->diagonalExpansion and never reads a third field */
         b->anchors[3 * (oA + k) + 2] =
-                (tls.params.dynamicAnchorExpansion && stIntTuple_length(a) > 2) ? (int32_t) stIntTuple_get(a, 2) : 0;
+                (tls.dynamicAnchors && stIntTuple_length(a) > 2) ? (int32_t) stIntTuple_get(a, 2) : 0;
         /* the same anchor as a 4-byte step from its predecessor: a third of the bytes over PCIe */
         int64_t px = k > 0 ? b->anchors[3 * (oA + k - 1)] : -1, py = k > 0 ? b->anchors[3 * (oA + k - 1) + 1] : -1;
         uint32_t w = margin_b200_pack_anchor(b->anchors[3 * (oA + k)] - px, b->anchors[3 * (oA + k) + 1] - py,
@@ -216,22 +242,55 @@ static void b200_batch_add(B200Batch *b, SymbolString sX, SymbolString sY, stLis
     b->raggedR[i] = raggedR;
 }
 
+static const uint16_t b200_noSymbols[1] = {0};
+static const int32_t b200_noAnchors[3] = {0, 0, 0};
+
+static void b200_batch_describe(const B200Batch *b, margin_b200_batch *mb) {
+    memset(mb, 0, sizeof(*mb));
+    mb->n = b->n;
+    mb->sym_x = b->symX ? b->symX : b200_noSymbols;
+    mb->off_x = b->offX;
+    mb->sym_y = b->symY ? b->symY : b200_noSymbols;
+    mb->off_y = b->offY;
+    mb->anchors = b->anchors ? b->anchors : b200_noAnchors;
+    if (b->compactOk && b->anchorsDelta) mb->anchors_delta = b->anchorsDelta; /* takes precedence over the triples */
+    mb->off_a = b->offA;
+    mb->model_slot = b->slot;
+    mb->ragged_left = b->raggedL;
+    mb->ragged_right = b->raggedR;
+}
+
+/* Debug hook: MARGIN_B200_DUMP=<prefix> writes every posterior batch (inputs, models, parameters) to
+ * <prefix>.<thread>.<n>.bin so that scripts/replay_dump.py can replay it against the oracle outside margin. */
+static void b200_batch_dump(const B200Batch *b, int wantIndels) {
+    static __thread int counter = 0;
+    const char *prefix = getenv("MARGIN_B200_DUMP");
+    if (prefix == NULL || prefix[0] == 0) return;
+    char *name = stString_print("%s.%d.%d.bin", prefix, omp_get_thread_num(), counter++);
+    FILE *fh = fopen(name, "wb");
+    if (fh == NULL) st_errAbort("margin_b200: cannot write %s\n", name);
+    int64_t tX = b->offX[b->n], tY = b->offY[b->n], tA = b->offA[b->n];
+    int64_t head[8] = {0x42323030, b->n, wantIndels, tX, tY, tA, sizeof(margin_b200_model), sizeof(margin_b200_params)};
+    fwrite(head, sizeof(head), 1, fh);
+    fwrite(&tls.loadedParams, sizeof(margin_b200_params), 1, fh);
+    fwrite(tls.loaded, sizeof(margin_b200_model), 2, fh);
+    fwrite(b->offX, sizeof(int64_t), b->n + 1, fh);
+    fwrite(b->offY, sizeof(int64_t), b->n + 1, fh);
+    fwrite(b->offA, sizeof(int64_t), b->n + 1, fh);
+    fwrite(b->slot, 1, b->n, fh);
+    fwrite(b->raggedL, 1, b->n, fh);
+    fwrite(b->raggedR, 1, b->n, fh);
+    if (tX) fwrite(b->symX, sizeof(uint16_t), tX, fh);
+    if (tY) fwrite(b->symY, sizeof(uint16_t), tY, fh);
+    if (tA) fwrite(b->anchors, 3 * sizeof(int32_t), tA, fh);
+    fclose(fh);
+    free(name);
+}
+
 static void b200_batch_run(B200Batch *b, int wantIndels, margin_b200_result *res) {
     margin_b200_batch mb;
-    uint16_t dummyS = 0;
-    int32_t dummyA[3] = {0, 0, 0};
-    memset(&mb, 0, sizeof(mb));
-    mb.n = b->n;
-    mb.sym_x = b->symX ? b->symX : &dummyS;
-    mb.off_x = b->offX;
-    mb.sym_y = b->symY ? b->symY : &dummyS;
-    mb.off_y = b->offY;
-    mb.anchors = b->anchors ? b->anchors : dummyA;
-    if (b->compactOk && b->anchorsDelta) mb.anchors_delta = b->anchorsDelta; /* takes precedence over the triples */
-    mb.off_a = b->offA;
-    mb.model_slot = b->slot;
-    mb.ragged_left = b->raggedL;
-    mb.ragged_right = b->raggedR;
+    b200_batch_describe(b, &mb);
+    b200_batch_dump(b, wantIndels);
     if (margin_b200_posteriors_batch(b200_ctx(), &mb, wantIndels, res) != 0) b200_fail();
 }
 
@@ -366,4 +425,143 @@ Poa *poa_realign(stList *bamChunkReads, stList *anchorAlignments, RleString *ref
     free(firstRefPositions);
     b200_batch_destruct(b);
     return poa;
+}
+
+/* ------------------------------------------------- impl/pairwiseAligner.c:849-905 and impl/poa.c:1852-1873, batched */
+
+/*
+ * Forward-only likelihoods.  bubbleGraph_constructFromPoaAndVCF asks for one small unbanded
+ * forward matrix per (allele, read substring) pair — 444 k calls on the bundled region, median 11 x 11 — and only
+ * stores each result as a float in Bubble.alleleReadSupports (impl/bubbleGraph.c:1067), copying it for repeated
+ * read substrings (:1058-1061); nothing reads the values before the graph is returned.  poa_polish below uses that:
+ * while it builds the graph, computeForwardProbability queues the job and returns a quiet NaN whose payload is the
+ * job number (the double -> float conversion and the copies keep the payload bits); after the graph is built all
+ * jobs run as ONE margin_b200_forward_batch and every tagged float is replaced by its job's result.
+ * bubbleGraph.c is linked unchanged.  Outside poa_polish computeForwardProbability is a batch of one.
+ */
+#define B200_TAG_LOW_MAX 0x3fffffU                    /* 22 payload bits below the quiet bit of a float NaN */
+#define B200_MAX_DEFERRED (2 * (int64_t) B200_TAG_LOW_MAX) /* the sign bit doubles the range; low bits 0 = a real NaN */
+#define B200_FLUSH_SYMBOLS (64 << 20)                 /* run the queue early beyond this many queued symbols */
+
+typedef struct B200Deferred {
+    B200Batch *queue;          /* jobs not yet run */
+    int64_t done;              /* jobs already run; results[0 .. done) are final */
+    double *results;
+    int64_t capResults;
+    StateMachine *machines[2]; /* the machines of the queued jobs (slot = index) */
+    PairwiseAlignmentParameters params;
+    int haveParams;
+    int warned;
+} B200Deferred;
+
+static double b200_tagged_nan(int64_t job) {
+    uint64_t low = (uint64_t) (job % B200_TAG_LOW_MAX) + 1, sign = (uint64_t) (job / B200_TAG_LOW_MAX);
+    uint64_t bits = (sign << 63) | 0x7ff8000000000000ULL | (low << 29); /* float: sign | 0x7fc00000 | low */
+    double d;
+    memcpy(&d, &bits, sizeof(d));
+    return d;
+}
+
+/* Job number of a tagged float, or -1 when f is an ordinary value (including an untagged NaN). */
+static int64_t b200_tag_of(float f) {
+    uint32_t u;
+    memcpy(&u, &f, sizeof(u));
+    if ((u & 0x7fc00000U) != 0x7fc00000U || (u & B200_TAG_LOW_MAX) == 0) return -1;
+    return (int64_t) (u >> 31) * B200_TAG_LOW_MAX + (int64_t) (u & B200_TAG_LOW_MAX) - 1;
+}
+
+static void b200_forward_run(B200Batch *b, double *out) {
+    margin_b200_batch mb;
+    b200_batch_describe(b, &mb);
+    if (margin_b200_forward_batch(b200_ctx(), &mb, out, NULL) != 0) b200_fail();
+}
+
+/* Runs the queued jobs; their results land behind the ones already known. */
+static void b200_deferred_flush(B200Deferred *d) {
+    int64_t n = d->queue->n;
+    if (n > 0) {
+        if (d->done + n > d->capResults) {
+            d->capResults = (d->done + n) * 2;
+            d->results = st_realloc(d->results, d->capResults * sizeof(double));
+        }
+        for (int s = 0; s < 2; s++) {
+            if (d->machines[s] != NULL) b200_load_machine(s, d->machines[s]);
+        }
+        b200_load_params(&d->params);
+        b200_forward_run(d->queue, d->results + d->done);
+        d->done += n;
+    }
+    b200_batch_destruct(d->queue);
+    d->queue = b200_batch_construct(1024);
+    d->machines[0] = d->machines[1] = NULL;
+}
+
+static int b200_same_params(const PairwiseAlignmentParameters *a, const PairwiseAlignmentParameters *b) {
+    return a->threshold == b->threshold && a->minDiagsBetweenTraceBack == b->minDiagsBetweenTraceBack &&
+           a->traceBackDiagonals == b->traceBackDiagonals && a->diagonalExpansion == b->diagonalExpansion &&
+           a->splitMatrixBiggerThanThis == b->splitMatrixBiggerThanThis &&
+           a->dynamicAnchorExpansion == b->dynamicAnchorExpansion;
+}
+
+double computeForwardProbability(SymbolString sX, SymbolString sY, stList *anchorPairs, PairwiseAlignmentParameters *p,
+                                 StateMachine *sM, bool alignmentHasRaggedLeftEnd, bool alignmentHasRaggedRightEnd) {
+    if (sX.length + sY.length == 0) return LOG_ONE; /* impl/pairwiseAligner.c:859-862 */
+    B200Deferred *d = tls.deferred;
+    if (d != NULL && d->done + d->queue->n >= B200_MAX_DEFERRED) {
+        if (!d->warned) st_logInfo("margin_b200: more than %" PRIi64 " forward jobs in one bubble graph; the rest run one by one\n",
+                                   (int64_t) B200_MAX_DEFERRED);
+        d->warned = 1;
+        d = NULL;
+    }
+    if (d == NULL) { /* a batch of one */
+        b200_load_machine(0, sM);
+        b200_load_params(p);
+        B200Batch *b = b200_batch_construct(1);
+        b200_batch_add(b, sX, sY, anchorPairs, 0, 0, alignmentHasRaggedLeftEnd, alignmentHasRaggedRightEnd);
+        double out = LOG_ZERO;
+        b200_forward_run(b, &out);
+        b200_batch_destruct(b);
+        return out;
+    }
+    if (d->haveParams && !b200_same_params(&d->params, p)) b200_deferred_flush(d);
+    d->params = *p;
+    d->haveParams = 1;
+    int slot = d->machines[0] == sM ? 0 : (d->machines[1] == sM ? 1 : -1);
+    if (slot < 0) {
+        if (d->machines[0] != NULL && d->machines[1] != NULL) b200_deferred_flush(d); /* a third machine */
+        slot = d->machines[0] == NULL ? 0 : 1;
+        d->machines[slot] = sM;
+    }
+    tls.dynamicAnchors = p->dynamicAnchorExpansion;
+    int64_t job = d->done + d->queue->n;
+    b200_batch_add(d->queue, sX, sY, anchorPairs, 0, slot, alignmentHasRaggedLeftEnd, alignmentHasRaggedRightEnd);
+    if (d->queue->offX[d->queue->n] + d->queue->offY[d->queue->n] > B200_FLUSH_SYMBOLS) b200_deferred_flush(d);
+    return b200_tagged_nan(job);
+}
+
+RleString *poa_polish(Poa *poa, stList *bamChunkReads, PolishParams *params, int64_t **poaToConsensusMap) {
+    B200Deferred d;
+    memset(&d, 0, sizeof(d));
+    d.queue = b200_batch_construct(1024);
+    tls.deferred = &d;
+    BubbleGraph *bg = bubbleGraph_constructFromPoa(poa, bamChunkReads, params);
+    tls.deferred = NULL;
+    b200_deferred_flush(&d);
+    for (uint64_t i = 0; i < bg->bubbleNo; i++) {
+        Bubble *b = &bg->bubbles[i];
+        for (uint64_t k = 0; k < b->alleleNo * b->readNo; k++) {
+            int64_t job = b200_tag_of(b->alleleReadSupports[k]);
+            if (job < 0) continue;
+            if (job >= d.done) st_errAbort("margin_b200: forward job %" PRIi64 " of %" PRIi64 " was never queued\n", job, d.done);
+            b->alleleReadSupports[k] = (float) d.results[job]; /* the conversion of impl/bubbleGraph.c:1067 */
+        }
+    }
+    b200_batch_destruct(d.queue);
+    free(d.results);
+
+    uint64_t *consensusPath = bubbleGraph_getConsensusPath(bg, params);
+    RleString *newConsensusString = bubbleGraph_getConsensusString(bg, consensusPath, poaToConsensusMap, params);
+    free(consensusPath);
+    bubbleGraph_destruct(bg);
+    return newConsensusString;
 }

@@ -169,7 +169,12 @@ struct margin_b200_ctx {
     DevBuf d_symx, d_symy, d_anchors, d_jobs, d_kl, d_kr, d_cell_off, d_job_cells, d_job_maxw, d_job_nseg, d_err;
     DevBuf d_segs, d_seg_counts, d_seg_off, d_scan_tmp, d_slot_ring_off, d_ring, d_ids, d_aln_first_slot;
     DevBuf d_F, d_stage, d_out, d_off_out, d_fwd_out;
-    PinBuf h_stage_in, h_small, h_out, h_off;
+    PinBuf h_stage_in, h_small, h_out, h_off, h_gaps;
+    // anchor-free stretches reported by the band kernel (sorted by job, start); see build_tiles
+    std::vector<mb::AnchorGap> gaps;
+    int gap_min = 32;
+    bool gaps_overflow = false;
+    int64_t n_anchors_total = 0;
     // after band_kernel
     std::vector<int64_t> job_cells;
     std::vector<int32_t> job_maxw;
@@ -341,6 +346,7 @@ int margin_b200_create(margin_b200_ctx **out, int device) {
         c->bwd_slots = sms * per_sm * (kTileThreads / 8);
     }
     if (const char *e = getenv("MARGIN_B200_WARMUP")) c->warmup = std::max(1, atoi(e));
+    if (const char *e = getenv("MARGIN_B200_GAP_MIN")) c->gap_min = std::max(1, atoi(e));
     c->counted = true;
     g_live_contexts[device & (kMaxDevices - 1)].fetch_add(1);
     *out = c;
@@ -364,6 +370,7 @@ void margin_b200_destroy(margin_b200_ctx *c) {
     for (DevBuf *b : bufs) b->release();
     c->h_stage_in.release();
     c->h_small.release();
+    c->h_gaps.release();
     c->h_arena.release();
     c->h_out.release();
     c->h_off.release();
@@ -569,6 +576,7 @@ extern "C" int margin_b200_upload_batch(margin_b200_ctx *c, const margin_b200_ba
     c->aln_first_slot.assign(n + 1, 0);
     c->aln_first_job.assign(n + 1, 0);
     const int64_t total_anchor_triples = n ? b->off_a[n] : 0;
+    c->n_anchors_total = total_anchor_triples;
     const int64_t nx = n ? b->off_x[n] : 0, ny = n ? b->off_y[n] : 0;
     // ---- cheap per-alignment checks, then everything that is O(symbols) or O(anchors) happens on the device
     bool used[2] = {false, false};
@@ -794,9 +802,16 @@ int run_band(margin_b200_ctx *c, bool dynamic, bool with_schedule, bool want_kr)
     // one device block mirrored by one pinned landing zone, so that everything the host needs comes back in one copy:
     // [totals 2 x int64][job_cells][job_maxw][job_nseg][segs][err]
     const size_t o_cells = 16, o_maxw = o_cells + (size_t) nj * 8, o_nseg = o_maxw + (size_t) nj * 4,
-                 o_segs = o_nseg + (size_t) nj * 4, o_err = o_segs + S * sizeof(mb::Seg), o_end = o_err + 8;
+                 o_segs = o_nseg + (size_t) nj * 4, o_err = o_segs + S * sizeof(mb::Seg), o_gaps = o_err + 8;
+    // [err int32][gap count int32][gap records]: the first kGapInline records come back with the control block, the
+    // rest (rare) in a second copy; more than gap_cap of them sends the batch down the sequential path
+    constexpr int kGapInline = 1024;
+    const bool want_gaps = with_schedule && !c->mode_sequential;
+    const int gap_cap = want_gaps ? (int) std::min<int64_t>(std::max<int64_t>(c->n_anchors_total + nj, kGapInline), 1 << 20) : 0;
+    const size_t o_end = o_gaps + (want_gaps ? kGapInline * sizeof(mb::AnchorGap) : 0);
+    const size_t o_dev_end = o_gaps + (size_t) gap_cap * sizeof(mb::AnchorGap);
     if (c->d_kl.ensure((c->total_diag + 1) * sizeof(int32_t)) || c->d_cell_off.ensure((c->total_diag + 1) * sizeof(uint32_t)) ||
-        c->d_geo.ensure((c->total_diag + 1) * sizeof(int2)) || c->d_band_out.ensure(o_end) ||
+        c->d_geo.ensure((c->total_diag + 1) * sizeof(int2)) || c->d_band_out.ensure(o_dev_end) ||
         c->d_chunk_sum.ensure((nc + 1) * sizeof(uint32_t)) || c->d_chunk_maxw.ensure((nc + 1) * sizeof(int32_t)))
         return 1;
     if (want_kr && c->d_kr.ensure((c->total_diag + 1) * sizeof(int32_t))) return 1;
@@ -807,14 +822,15 @@ int run_band(margin_b200_ctx *c, bool dynamic, bool with_schedule, bool want_kr)
     int32_t *d_job_maxw = reinterpret_cast<int32_t *>(dv + o_maxw), *d_job_nseg = reinterpret_cast<int32_t *>(dv + o_nseg);
     mb::Seg *d_segs = reinterpret_cast<mb::Seg *>(dv + o_segs);
     int *d_err = reinterpret_cast<int *>(dv + o_err);
-    CU(cudaMemsetAsync(dv, 0, o_end, c->stream));
+    mb::AnchorGap *d_gaps = reinterpret_cast<mb::AnchorGap *>(dv + o_gaps);
+    CU(cudaMemsetAsync(dv, 0, o_gaps, c->stream));
     if (nj > 0) {
         {
             KTimer kt_(c, K_BAND);
             mb::band_chunk_kernel<256><<<nc, 256, 0, c->stream>>>(
                 c->d_jobs.as<mb::Job>(), c->d_chunks.as<mb::BandChunk>(), nc, c->d_anchors.as<int32_t>(), q,
                 c->d_geo.as<int2>(), want_kr ? c->d_kr.as<int32_t>() : nullptr, c->d_chunk_sum.as<uint32_t>(),
-                c->d_chunk_maxw.as<int32_t>(), d_err);
+                c->d_chunk_maxw.as<int32_t>(), d_err, c->gap_min, gap_cap, d_err + 1, want_gaps ? d_gaps : nullptr);
             mb::band_jobs_kernel<<<(nj + 3) / 4, 128, 0, c->stream>>>(nj, c->d_job_first_chunk.as<int32_t>(),
                                                                      c->d_chunk_sum.as<uint32_t>(),
                                                                      c->d_chunk_maxw.as<int32_t>(), d_job_cells, d_job_maxw);
@@ -840,6 +856,28 @@ int run_band(margin_b200_ctx *c, bool dynamic, bool with_schedule, bool want_kr)
     if (*reinterpret_cast<int *>(h + o_err))
         return fail("PAIRWISE_ALIGNMENT_EXCEPTION: Attempt to create diagonal with invalid coordinates "
                     "(anchors inconsistent with the sequence lengths)");
+    c->gaps.clear();
+    c->gaps_overflow = false;
+    if (want_gaps) {
+        const int n_gaps = reinterpret_cast<int *>(h + o_err)[1];
+        if (n_gaps > gap_cap) {
+            c->gaps_overflow = true;
+        } else if (n_gaps > 0) {
+            const mb::AnchorGap *hg = reinterpret_cast<const mb::AnchorGap *>(h + o_gaps);
+            c->gaps.assign(hg, hg + std::min(n_gaps, kGapInline));
+            if (n_gaps > kGapInline) {
+                const size_t rest = (size_t) (n_gaps - kGapInline) * sizeof(mb::AnchorGap);
+                if (c->h_gaps.ensure(rest)) return 1;
+                if (ctl_copy(c->stream, c->h_gaps.as<char>(), dv + o_end, (rest + 3) / 4 * 4)) return 1;
+                CU(cudaStreamSynchronize(c->stream));
+                const mb::AnchorGap *more = c->h_gaps.as<mb::AnchorGap>();
+                c->gaps.insert(c->gaps.end(), more, more + (n_gaps - kGapInline));
+            }
+            std::sort(c->gaps.begin(), c->gaps.end(), [](const mb::AnchorGap &a, const mb::AnchorGap &b) {
+                return a.job != b.job ? a.job < b.job : a.lo < b.lo;
+            });
+        }
+    }
     c->job_cells.assign(reinterpret_cast<int64_t *>(h + o_cells), reinterpret_cast<int64_t *>(h + o_cells) + nj);
     c->job_maxw.assign(reinterpret_cast<int32_t *>(h + o_maxw), reinterpret_cast<int32_t *>(h + o_maxw) + nj);
     c->job_nseg.assign(nj, 0);
@@ -864,7 +902,7 @@ int run_band(margin_b200_ctx *c, bool dynamic, bool with_schedule, bool want_kr)
 // anything else (very wide bands, e.g. alignments without anchors; degenerate one-row matrices) takes the
 // sequential per-alignment sweep.
 bool job_is_tiled(const margin_b200_ctx *c, int j) {
-    if (c->mode_sequential) return false;
+    if (c->mode_sequential || c->gaps_overflow) return false;
     const mb::Job &job = c->jobs[j];
     return c->job_maxw[j] <= (c->force_group ? c->force_group : 32) && job.lx >= 1 && job.ly >= 1;
 }
@@ -921,9 +959,39 @@ int pick_tile_len(margin_b200_ctx *c) {
     return best_L;
 }
 
+// Warm-up ends for a tile edge at diagonal `at` of a job: the sweep starts W diagonals away, not counting diagonals
+// inside anchor-free stretches (g[0 .. ng), sorted, disjoint) — there the band is a corridor along one sequence, the
+// state distribution carries over unchanged for its whole length, and a flat start inside it would never converge to
+// the true one (a 611-base deletion of the bundled ONT region did exactly that with a fixed 128).
+inline int warmup_start_below(const mb::AnchorGap *g, int ng, int at, int W) {
+    int k = ng - 1;
+    while (k >= 0 && g[k].lo >= at) k--;  // stretches entirely above the edge do not matter
+    int need = W, pos = at;
+    for (; k >= 0 && need > 0; k--) {
+        const int clear = pos - std::min(pos, g[k].hi);  // anchored diagonals between the stretch and pos
+        if (clear >= need) return pos - need;
+        need -= clear;
+        pos = std::min(pos, g[k].lo);
+    }
+    return std::max(0, pos - need);
+}
+inline int warmup_end_above(const mb::AnchorGap *g, int ng, int at, int W, int limit) {
+    int k = 0;
+    while (k < ng && g[k].hi <= at) k++;
+    int need = W, pos = at;
+    for (; k < ng && need > 0; k++) {
+        const int clear = std::max(pos, g[k].lo) - pos;
+        if (clear >= need) return std::min(limit, pos + need);
+        need -= clear;
+        pos = std::max(pos, g[k].hi);
+    }
+    return std::min(limit, pos + need);
+}
+
 void build_tiles(margin_b200_ctx *c) {
     const int nj = (int) c->jobs.size();
     const int L = pick_tile_len(c), W = c->warmup;
+    size_t gap_at = 0;  // c->gaps is sorted by job and jobs are visited in ascending order
     c->tile_len_used = L;
     c->tiles.clear();
     c->job_first_tile.assign(nj + 1, 0);
@@ -934,6 +1002,11 @@ void build_tiles(margin_b200_ctx *c) {
             const mb::Job &job = c->jobs[j];
             const bool tiled = job_is_tiled(c, j);
             c->job_first_tile[j] = (int32_t) c->tiles.size();
+            while (gap_at < c->gaps.size() && c->gaps[gap_at].job < j) gap_at++;
+            size_t gap_end = gap_at;
+            while (gap_end < c->gaps.size() && c->gaps[gap_end].job == j) gap_end++;
+            const mb::AnchorGap *g = c->gaps.data() + gap_at;
+            const int ng = (int) (gap_end - gap_at);
             for (int s = c->job_nseg[j] - 1; s >= 0; s--) {
                 const mb::Seg &sg = c->segs[job.seg_base + s];
                 const int span = sg.tb_from - sg.tb_to;
@@ -943,8 +1016,8 @@ void build_tiles(margin_b200_ctx *c) {
                     t.job = j;
                     t.tb_from = sg.tb_from - k * L;
                     t.tb_to = (k == nt - 1) ? sg.tb_to : t.tb_from - L;
-                    t.D = (k == 0) ? sg.D : std::min(sg.D, t.tb_from + W);
-                    t.f0 = tiled ? std::max(0, t.tb_to - W) : 0;
+                    t.D = (k == 0) ? sg.D : warmup_end_above(g, ng, t.tb_from, W, sg.D);
+                    t.f0 = tiled ? warmup_start_below(g, ng, t.tb_to, W) : 0;
                     t.flags = ((t.D == sg.D && sg.at_end) ? mb::TILE_AT_END : 0) | (tiled ? mb::TILE_BND : 0);
                     c->tiles.push_back(t);
                 }

@@ -41,6 +41,11 @@ struct Seg {
     int32_t at_end;
 };
 
+// A run of anti-diagonals (lo, hi) of a job without an anchor (band_chunk_kernel).
+struct AnchorGap {
+    int32_t job, lo, hi;
+};
+
 // A unit of backward (and, in tiled mode, forward) work: a traceback segment or a piece of one (pairhmm_tiles.cuh).
 struct Tile {
     int32_t job;
@@ -322,7 +327,8 @@ template <int THREADS>
 __global__ void __launch_bounds__(THREADS)
 band_chunk_kernel(const Job *__restrict__ jobs, const BandChunk *__restrict__ chunks, int n_chunks,
                   const int32_t *__restrict__ anchors, Params p, int2 *__restrict__ geo, int32_t *__restrict__ kr_out,
-                  uint32_t *__restrict__ chunk_sum, int32_t *__restrict__ chunk_maxw, int *__restrict__ err) {
+                  uint32_t *__restrict__ chunk_sum, int32_t *__restrict__ chunk_maxw, int *__restrict__ err,
+                  int gap_min, int gap_cap, int *__restrict__ gap_count, AnchorGap *__restrict__ gaps) {
     const int ci = blockIdx.x;
     if (ci >= n_chunks) return;
     const BandChunk ch = chunks[ci];
@@ -351,6 +357,30 @@ band_chunk_kernel(const Job *__restrict__ jobs, const BandChunk *__restrict__ ch
         for (int k = threadIdx.x; k < a_cnt; k += THREADS)
             s_diag[k] = __ldg(anc + 3 * (a_lo + k)) + __ldg(anc + 3 * (a_lo + k) + 1) + 2;
     __syncthreads();
+    // Stretches of more than gap_min anti-diagonals without an anchor (long indels: the band is a narrow corridor in
+    // which the forward/backward state forgets nothing) are reported to the host, which keeps the warm-up of the
+    // tiles out of them (build_tiles).  Every anchor is owned by the chunk its diagonal falls into; the stretch after
+    // the last anchor by the job's last chunk.
+    if (gaps != nullptr) {
+        for (int k = threadIdx.x; k < a_cnt; k += THREADS) {
+            const int a = a_lo + k;
+            const int dk = staged ? s_diag[k] : __ldg(anc + 3 * a) + __ldg(anc + 3 * a + 1) + 2;
+            int dp = 0;
+            if (k > 0 && staged) dp = s_diag[k - 1];
+            else if (a > 0) dp = __ldg(anc + 3 * (a - 1)) + __ldg(anc + 3 * (a - 1) + 1) + 2;
+            if (dk - dp > gap_min) {
+                const int at = atomicAdd(gap_count, 1);
+                if (at < gap_cap) gaps[at] = AnchorGap{ch.job, dp, dk};
+            }
+        }
+        if (threadIdx.x == 0 && ch.d0 + BAND_CHUNK >= N + 2) {
+            const int dp = na > 0 ? __ldg(anc + 3 * (na - 1)) + __ldg(anc + 3 * (na - 1) + 1) + 2 : 0;
+            if (N - dp > gap_min) {
+                const int at = atomicAdd(gap_count, 1);
+                if (at < gap_cap) gaps[at] = AnchorGap{ch.job, dp, N};
+            }
+        }
+    }
     // Each thread owns DPT consecutive diagonals: one binary search for the first, then the governing anchor only
     // moves forward; one block-wide scan of the per-thread width sums covers the whole chunk.
     constexpr int DPT = BAND_CHUNK / THREADS;

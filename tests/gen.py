@@ -45,3 +45,23 @@ def random_case(rng, lx, rle=True, anchor_keep=0.7, expansions=(0, 2, 4, 10), ra
     rr = int(ragged and rng.random() < 0.3)
     slot = int(rng.random() < 0.5)
     return sx, sy, np.array(anchors, dtype=np.int32).reshape(-1, 3), slot, rl, rr
+
+
+def long_indel_case(rng, lx, at, length, deletion=True, expansion=4, rle=True):
+    """Dense anchors (one per match column, as the BAM walk of htsIntegration.c:722-729 emits them) around one long
+    deletion (reference bases missing from the read) or insertion: between the two anchors flanking it the band is a
+    corridor of constant width along one sequence, `length` anti-diagonals long."""
+    sx = random_symbols(rng, lx, rle, 0.0)
+    if deletion:
+        left, right = sx[:at], sx[at + length:]
+        sy0 = np.concatenate([left, right])
+        xs = np.concatenate([np.arange(at), np.arange(at + length, lx)])
+    else:
+        sy0 = np.concatenate([sx[:at], random_symbols(rng, length, rle, 0.0), sx[at:]])
+        xs = np.arange(lx)
+    ys = np.arange(len(sy0)) if deletion else np.concatenate([np.arange(at), np.arange(at + length, at + length + lx - at)])
+    sy = sy0.copy()
+    flip = rng.random(len(sy)) < 0.05  # substitutions keep their anchors (CIGAR M covers mismatches)
+    sy[flip] = random_symbols(rng, int(flip.sum()), rle, 0.0)
+    anchors = np.stack([xs, ys, np.full(len(xs), expansion)], axis=1).astype(np.int32)
+    return sx, sy.astype(np.uint16), anchors, 0, 0, 0

@@ -255,3 +255,32 @@ def test_pack_helpers_roundtrip():
     a = np.array([[0, 0, 4], [3, 1, 0], [7, 9, 510]], np.int32)
     d = abi.pack_anchors_delta(a, np.array([0, 1, 3]))
     assert d.tolist() == [1 | (1 << 12) | (2 << 24), 4 | (2 << 12), 4 | (8 << 12) | (255 << 24)]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("tile_len", ["0", "200"])
+def test_long_indel_corridors_keep_tile_parity(oracle, golden_model, monkeypatch, tile_len):
+    """A long deletion or insertion between dense anchors makes the band a corridor in which the DP forgets nothing:
+    a tile edge inside or just after it must take its warm-up from before the corridor (band_chunk_kernel reports
+    the anchor-free stretches, build_tiles keeps the warm-up out of them).  Found on the bundled ONT region (a
+    611-base deletion); a fixed warm-up of 128 diagonals emitted ~500 wrong tuples there."""
+    from margin_b200.aligner import PairHmmAligner
+    pm = golden_model("r94g360")
+    rng = np.random.default_rng(611)
+    items = []
+    for length, deletion in ((611, True), (611, False), (150, True), (40, False), (1500, True)):
+        items.append(gen.long_indel_case(rng, 5000, int(rng.integers(1500, 3000)), length, deletion))
+    two = gen.long_indel_case(rng, 6000, 2000, 300, True)  # two corridors close to each other
+    sx, sy, a = two[0], two[1], two[2]
+    keep = ~((a[:, 0] >= 2400) & (a[:, 0] < 2650))  # drop the anchors of 250 columns: a second anchor-free stretch
+    items.append((sx, sy, a[keep], 0, 0, 0))
+    if tile_len != "0":
+        monkeypatch.setenv("MARGIN_B200_TILE_LEN", tile_len)  # many tile edges inside every corridor
+    monkeypatch.setenv("MARGIN_B200_PIPELINE", "1")
+    al = PairHmmAligner(pm.models, pm.p, device=0)
+    got = al.posteriors_batch(items, True)
+    assert got.stats["tiles"] > len(items)
+    for i, it in enumerate(items):
+        ref = oracle.posteriors(pm.models[it[3]], pm.p, it[0], it[1], it[2], it[4], it[5], 1)
+        compare_lists(got[i], ref, tol_w=1000)  # 1e-4 in posterior probability (BASELINE.json north_star)
+    al.close()

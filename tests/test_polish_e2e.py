@@ -49,3 +49,48 @@ def test_reference_cli_reproduces_expected_digest(tmp_path):
         pytest.skip("44 s of CPU; set MARGIN_B200_SLOW_TESTS=1")
     md5, dt, _ = _polish("margin_ref", str(tmp_path / "ref"), 8)
     assert md5 == EXPECTED_FASTA_MD5
+
+
+@pytest.mark.gpu
+def test_every_batch_of_the_polish_run_matches_the_oracle(tmp_path, monkeypatch):
+    """Real-data parity below the FASTA (SURVEY.md §8 C-4 iii on config C1): every posterior batch `margin polish`
+    sends to the library on the bundled region (2 x 314 alignments, reads up to 69 k symbols, long indels, plus the
+    stitcher's overlap alignment) is dumped by the binding and replayed here; all tuple lists must have the oracle's
+    coordinates and weights within 1e-4, on the plain and on the pipelined path."""
+    import glob
+    import sys
+    import numpy as np
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from common import compare_lists, load_dump
+    from margin_b200 import abi
+    from margin_b200.aligner import PairHmmAligner
+    from oracle.oracle_py import Oracle
+    if not os.path.exists(os.path.join(REF, "margin_b200cli")):
+        pytest.skip("oracle/_ref/margin_b200cli not built (needs /root/reference at build time)")
+    env = dict(os.environ, MARGIN_B200_DUMP=str(tmp_path / "d"))
+    md5, _, _ = _polish("margin_b200cli", str(tmp_path / "b200"), 2, env)
+    assert md5 == EXPECTED_FASTA_MD5
+    dumps = sorted(glob.glob(str(tmp_path / "d.*.bin")))
+    assert len(dumps) >= 2
+    orc = Oracle()
+    n_aln = 0
+    for path in dumps:
+        items, models, params, want = load_dump(path)
+        ref, _ = orc.posteriors_batch(models, params, abi.Batch(items), want, threads=os.cpu_count() or 1)
+        for env_set in (dict(MARGIN_B200_PIPELINE="0"), dict(MARGIN_B200_PIPELINE_FORCE="1", MARGIN_B200_PIPELINE_MIN_BYTES="0")):
+            for k in ("MARGIN_B200_PIPELINE", "MARGIN_B200_PIPELINE_FORCE", "MARGIN_B200_PIPELINE_MIN_BYTES"):
+                monkeypatch.delenv(k, raising=False)
+            for k, v in env_set.items():
+                monkeypatch.setenv(k, v)
+            al = PairHmmAligner(models, params, device=0)
+            al.set_pair_format(abi.PAIRS_PACKED64)
+            got = al.posteriors_batch(abi.Batch(items, compact=True), bool(want))
+            al.close()
+            for i in range(len(items)):
+                try:
+                    compare_lists(got[i], ref[i], tol_w=1000)
+                except AssertionError as e:
+                    raise AssertionError("%s alignment %d (%s): %s" % (os.path.basename(path), i, env_set, e))
+        n_aln += len(items)
+    print("%d batches, %d alignments replayed against the oracle" % (len(dumps), n_aln))
