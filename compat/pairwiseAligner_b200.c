@@ -356,15 +356,235 @@ void getAlignedPairsWithIndels(StateMachine *sM, SymbolString sX, SymbolString s
                                           alignmentHasRaggedLeftEnd, alignmentHasRaggedRightEnd);
 }
 
+/* ------------------------------------------------------- impl/poa.c:317-543 on the library's flat tuple arrays */
+
+/*
+ * poa_augment for one read, reading the (weight, x, y) records of a margin_b200_result directly (SURVEY.md §8 f N1).
+ * The reference's version wants three stLists of individually allocated stIntTuples, builds an AVL set of the match
+ * tuples and sorts the gap lists through their pointers; with the aligner on the GPU that was half of the wall time
+ * of `margin polish`.  Same graph updates in the same order (base and repeat-count weights, observations, complete
+ * inserts and deletes with their left shift), hence the same floating-point sums:
+ *   - the match set is an open-addressing table of packed coordinates (isMatch, impl/poa.c:168-174);
+ *   - gap records are sorted in place by (x, y) / (y, x) (cmpAlignedPairsByCoordinates / ...Inverted, :137-166);
+ *   - a maximal run of gap records is scanned once per start k with a running minimum for the weight (:389-446).
+ * poaBaseObservation_construct, poaInsert_construct, poaDelete_construct and getMaxCommonSuffixLength are exported by
+ * impl/poa.c but not declared in inc/margin.h.
+ */
+PoaBaseObservation *poaBaseObservation_construct(int64_t readNo, int64_t offset, double weight);
+PoaInsert *poaInsert_construct(RleString *insert, double weight, bool strand);
+PoaDelete *poaDelete_construct(int64_t length, double weight, bool strand);
+int64_t getMaxCommonSuffixLength(RleString *str1, int64_t length1, RleString *str2, bool compareRepeatCounts);
+
+typedef struct {
+    int64_t x, y, w;
+} B200Pair;
+
+typedef struct {
+    B200Pair *pairs[3];
+    int64_t cap[3];
+    uint64_t *table; /* 0 = empty slot, else packed coordinates + 1 */
+    uint64_t tableSize;
+} B200AugmentScratch;
+
+static __thread B200AugmentScratch augmentScratch;
+
+/* List l of alignment i as flat records, x shifted back by the crop. */
+static int64_t b200_pairs(const margin_b200_result *res, int l, int64_t i, int64_t shiftX) {
+    B200AugmentScratch *sc = &augmentScratch;
+    int64_t first = res->off[l][i], n = res->off[l][i + 1] - first;
+    if (n > sc->cap[l]) {
+        sc->cap[l] = n * 2 + 1024;
+        sc->pairs[l] = st_realloc(sc->pairs[l], sc->cap[l] * sizeof(B200Pair));
+    }
+    B200Pair *out = sc->pairs[l];
+    if (res->pair_format == MARGIN_B200_PAIRS_PACKED64) {
+        const uint64_t *v = (const uint64_t *) res->pairs[l] + first;
+        for (int64_t k = 0; k < n; k++) {
+            margin_b200_pair q = margin_b200_unpack_pair(v[k]);
+            out[k].x = (int64_t) q.x + shiftX;
+            out[k].y = q.y;
+            out[k].w = q.w;
+        }
+    } else {
+        const margin_b200_pair *q = res->pairs[l] + first;
+        for (int64_t k = 0; k < n; k++) {
+            out[k].x = (int64_t) q[k].x + shiftX;
+            out[k].y = q[k].y;
+            out[k].w = q[k].w;
+        }
+    }
+    return n;
+}
+
+static inline uint64_t b200_coordinate_key(int64_t x, int64_t y) {
+    return (((uint64_t) x << 32) | (uint64_t) y) + 1;
+}
+
+static inline uint64_t b200_table_slot(uint64_t key, uint64_t mask) {
+    return ((key * 0x9E3779B97F4A7C15ULL) >> 20) & mask;
+}
+
+static void b200_match_set_fill(const B200Pair *matches, int64_t n) {
+    B200AugmentScratch *sc = &augmentScratch;
+    uint64_t size = 1024;
+    while (size < (uint64_t) n * 2 + 2) size *= 2;
+    if (size > sc->tableSize) {
+        free(sc->table);
+        sc->table = st_malloc(size * sizeof(uint64_t));
+    }
+    sc->tableSize = size;
+    memset(sc->table, 0, size * sizeof(uint64_t));
+    for (int64_t k = 0; k < n; k++) {
+        uint64_t key = b200_coordinate_key(matches[k].x, matches[k].y), at = b200_table_slot(key, size - 1);
+        while (sc->table[at] != 0) at = (at + 1) & (size - 1);
+        sc->table[at] = key;
+    }
+}
+
+static inline bool b200_is_match(int64_t x, int64_t y) {
+    const B200AugmentScratch *sc = &augmentScratch;
+    if (x < 0 || y < 0) return 0;
+    uint64_t key = b200_coordinate_key(x, y), mask = sc->tableSize - 1, at = b200_table_slot(key, mask);
+    while (sc->table[at] != 0) {
+        if (sc->table[at] == key) return 1;
+        at = (at + 1) & mask;
+    }
+    return 0;
+}
+
+static int b200_cmp_xy(const void *a, const void *b) {
+    const B200Pair *p = a, *q = b;
+    if (p->x != q->x) return p->x < q->x ? -1 : 1;
+    return p->y < q->y ? -1 : (p->y > q->y ? 1 : 0);
+}
+
+static int b200_cmp_yx(const void *a, const void *b) {
+    const B200Pair *p = a, *q = b;
+    if (p->y != q->y) return p->y < q->y ? -1 : 1;
+    return p->x < q->x ? -1 : (p->x > q->x ? 1 : 0);
+}
+
+static void b200_node_add_insert(PoaNode *node, RleString *insert, double weight, bool strand, PoaBaseObservation *obs) {
+    PoaInsert *hit = NULL;
+    for (int64_t m = 0; m < stList_length(node->inserts) && hit == NULL; m++) {
+        PoaInsert *candidate = stList_get(node->inserts, m);
+        if (rleString_eq(candidate->insert, insert)) hit = candidate;
+    }
+    if (hit == NULL) {
+        hit = poaInsert_construct(rleString_copy(insert), 0, FALSE);
+        stList_append(node->inserts, hit);
+    }
+    if (strand) hit->weightForwardStrand += weight;
+    else hit->weightReverseStrand += weight;
+    stList_append(hit->observations, obs);
+}
+
+static void b200_node_add_delete(PoaNode *node, int64_t length, double weight, bool strand, PoaBaseObservation *obs) {
+    PoaDelete *hit = NULL;
+    for (int64_t m = 0; m < stList_length(node->deletes) && hit == NULL; m++) {
+        PoaDelete *candidate = stList_get(node->deletes, m);
+        if (candidate->length == length) hit = candidate;
+    }
+    if (hit == NULL) {
+        hit = poaDelete_construct(length, 0, FALSE);
+        stList_append(node->deletes, hit);
+    }
+    if (strand) hit->weightForwardStrand += weight;
+    else hit->weightReverseStrand += weight;
+    stList_append(hit->observations, obs);
+}
+
+static void b200_poa_augment(Poa *poa, RleString *read, bool readStrand, int64_t readNo, const margin_b200_result *res,
+                             int64_t aln, int64_t shiftX, PolishParams *polishParams) {
+    B200AugmentScratch *sc = &augmentScratch;
+    bool compareRL = polishParams->poaConstructCompareRepeatCounts;
+    int64_t nMatch = b200_pairs(res, 0, aln, shiftX);
+    int64_t nDelete = b200_pairs(res, 1, aln, shiftX); /* gapX: reference base without read base */
+    int64_t nInsert = b200_pairs(res, 2, aln, shiftX); /* gapY */
+    B200Pair *matches = sc->pairs[0], *deletes = sc->pairs[1], *inserts = sc->pairs[2];
+
+    /* match weights and observations, in list order (impl/poa.c:324-341) */
+    for (int64_t k = 0; k < nMatch; k++) {
+        PoaNode *node = stList_get(poa->nodes, matches[k].x + 1);
+        int64_t y = matches[k].y;
+        node->baseWeights[poa->alphabet->convertCharToSymbol(read->rleString[y])] += matches[k].w;
+        int64_t rc = read->repeatCounts[y] < poa->maxRepeatCount ? read->repeatCounts[y] : poa->maxRepeatCount - 1;
+        node->repeatCountWeights[rc] += matches[k].w;
+        stList_append(node->observations, poaBaseObservation_construct(readNo, y, matches[k].w));
+    }
+    b200_match_set_fill(matches, nMatch);
+
+    /* complete inserts: same reference coordinate, consecutive read coordinates, flanked by matches or the ends */
+    qsort(inserts, nInsert, sizeof(B200Pair), b200_cmp_xy);
+    for (int64_t i = 0, j; i < nInsert; i = j) {
+        int64_t x = inserts[i].x, y0 = inserts[i].y;
+        for (j = i + 1; j < nInsert && inserts[j].x == x && inserts[j].y == y0 + (j - i); j++);
+        for (int64_t k = i; k < j; k++) {
+            int64_t yk = y0 + (k - i);
+            if (yk - 1 > -1 && !b200_is_match(x, yk - 1)) continue;
+            double weight = UINT_MAX;
+            for (int64_t l = k; l < j; l++) {
+                weight = weight < inserts[l].w ? weight : inserts[l].w;
+                int64_t yl = y0 + (l - i);
+                if (yl + 1 < read->length && !b200_is_match(x + 1, yl + 1)) continue;
+                RleString *insert = rleString_copySubstring(read, yk, l + 1 - k);
+                int64_t position = getShift(poa->refString, x + 1, insert, compareRL);
+                int64_t suffix = getMaxCommonSuffixLength(poa->refString, position, insert, compareRL);
+                if (suffix > 0) {
+                    rleString_rotateString(insert, suffix, polishParams->useRunLengthEncoding);
+                    position -= suffix;
+                }
+                b200_node_add_insert(stList_get(poa->nodes, position), insert, weight, readStrand,
+                                     poaBaseObservation_construct(readNo, yk, weight));
+                rleString_destruct(insert);
+            }
+        }
+    }
+
+    /* complete deletes: same read coordinate, consecutive reference coordinates */
+    qsort(deletes, nDelete, sizeof(B200Pair), b200_cmp_yx);
+    int64_t refLength = poa->refString->length;
+    for (int64_t i = 0, j; i < nDelete; i = j) {
+        int64_t x0 = deletes[i].x, y = deletes[i].y;
+        for (j = i + 1; j < nDelete && deletes[j].y == y && deletes[j].x == x0 + (j - i); j++);
+        for (int64_t k = i; k < j; k++) {
+            int64_t xk = x0 + (k - i);
+            if (xk - 1 > -1 && !b200_is_match(xk - 1, y)) continue;
+            double weight = UINT_MAX;
+            for (int64_t l = k; l < j; l++) {
+                weight = weight < deletes[l].w ? weight : deletes[l].w;
+                int64_t xl = x0 + (l - i);
+                if (xl + 1 < refLength && !b200_is_match(xl + 1, y + 1)) continue;
+                int64_t length = l - k + 1;
+                RleString *deleted = rleString_copySubstring(poa->refString, xk, length);
+                int64_t position = getShift(poa->refString, xk, deleted, compareRL);
+                position -= getMaxCommonSuffixLength(poa->refString, position, deleted, compareRL);
+                rleString_destruct(deleted);
+                b200_node_add_delete(stList_get(poa->nodes, position), length, weight, readStrand,
+                                     poaBaseObservation_construct(readNo, y, weight));
+            }
+        }
+    }
+}
+
 /* ----------------------------------------------------------------------------- impl/poa.c:668-716, batched */
 
 /*
  * poa_realign with ONE aligner call per chunk instead of one per read: pass 1 prepares every read exactly as
  * getAlignedPairsWithIndelsCroppingReference does (impl/poa.c:612-666: crop the reference to the anchored span,
  * shift the anchors, build both SymbolStrings, pick the strand's state machine), the batch runs on the GPU, pass 2
- * hands each read's three lists to poa_augment in read order (matches, inserts <- gapY, deletes <- gapX, x shifted
- * back by the crop).
+ * applies each read's three lists to the graph in read order (b200_poa_augment above: matches, inserts <- gapY,
+ * deletes <- gapX, x shifted back by the crop).
  */
+static int b200_reference_augment(void) {
+    static int cached = -1;
+    if (cached < 0) {
+        const char *e = getenv("MARGIN_B200_REFERENCE_AUGMENT");
+        cached = e != NULL && e[0] == '1';
+    }
+    return cached;
+}
+
 Poa *poa_realign(stList *bamChunkReads, stList *anchorAlignments, RleString *reference, PolishParams *polishParams) {
     uint64_t maximumRepeatLength = 2; /* MRL is exclusive */
     if (polishParams->useRunLengthEncoding) {
@@ -379,6 +599,7 @@ Poa *poa_realign(stList *bamChunkReads, stList *anchorAlignments, RleString *ref
     b200_load_machine(1, polishParams->stateMachineForReverseStrandRead);
     b200_load_params(polishParams->p);
 
+    double tStart = omp_get_wtime(), tLists = 0.0, tAugment = 0.0, tFree = 0.0;
     B200Batch *b = b200_batch_construct(n);
     int64_t *firstRefPositions = st_calloc(n, sizeof(int64_t));
     for (int64_t i = 0; i < n; i++) {
@@ -409,21 +630,37 @@ Poa *poa_realign(stList *bamChunkReads, stList *anchorAlignments, RleString *ref
         firstRefPositions[i] = firstRefPosition;
     }
 
+    double tPrepared = omp_get_wtime();
     margin_b200_result res;
     b200_batch_run(b, 1, &res);
+    double tAligned = omp_get_wtime();
 
     for (int64_t i = 0; i < n; i++) {
         BamChunkRead *chunkRead = stList_get(bamChunkReads, i);
-        stList *matches = b200_list(&res, 0, i, firstRefPositions[i]);
-        stList *deletes = b200_list(&res, 1, i, firstRefPositions[i]); /* gapX: reference base without read base */
-        stList *inserts = b200_list(&res, 2, i, firstRefPositions[i]); /* gapY */
-        poa_augment(poa, chunkRead->rleRead, chunkRead->forwardStrand, i, matches, inserts, deletes, polishParams);
-        stList_destruct(matches);
-        stList_destruct(inserts);
-        stList_destruct(deletes);
+        double t0 = omp_get_wtime();
+        if (b200_reference_augment()) { /* MARGIN_B200_REFERENCE_AUGMENT=1: the reference's poa_augment on stLists (A/B check) */
+            stList *matches = b200_list(&res, 0, i, firstRefPositions[i]);
+            stList *deletes = b200_list(&res, 1, i, firstRefPositions[i]); /* gapX: reference base without read base */
+            stList *inserts = b200_list(&res, 2, i, firstRefPositions[i]); /* gapY */
+            double t1 = omp_get_wtime();
+            poa_augment(poa, chunkRead->rleRead, chunkRead->forwardStrand, i, matches, inserts, deletes, polishParams);
+            double t2 = omp_get_wtime();
+            stList_destruct(matches);
+            stList_destruct(inserts);
+            stList_destruct(deletes);
+            tLists += t1 - t0;
+            tAugment += t2 - t1;
+            tFree += omp_get_wtime() - t2;
+        } else {
+            b200_poa_augment(poa, chunkRead->rleRead, chunkRead->forwardStrand, i, &res, i, firstRefPositions[i], polishParams);
+            tAugment += omp_get_wtime() - t0;
+        }
     }
     free(firstRefPositions);
     b200_batch_destruct(b);
+    st_logInfo(" margin_b200 poa_realign: %" PRIi64 " reads, prepare %.3f s, aligner (GPU, whole batch) %.3f s, "
+               "tuple lists %.3f s, poa_augment %.3f s, free %.3f s\n", n, tPrepared - tStart, tAligned - tPrepared,
+               tLists, tAugment, tFree);
     return poa;
 }
 
@@ -544,9 +781,12 @@ RleString *poa_polish(Poa *poa, stList *bamChunkReads, PolishParams *params, int
     memset(&d, 0, sizeof(d));
     d.queue = b200_batch_construct(1024);
     tls.deferred = &d;
+    double tStart = omp_get_wtime();
     BubbleGraph *bg = bubbleGraph_constructFromPoa(poa, bamChunkReads, params);
     tls.deferred = NULL;
+    double tBuilt = omp_get_wtime();
     b200_deferred_flush(&d);
+    double tScored = omp_get_wtime();
     for (uint64_t i = 0; i < bg->bubbleNo; i++) {
         Bubble *b = &bg->bubbles[i];
         for (uint64_t k = 0; k < b->alleleNo * b->readNo; k++) {
@@ -556,6 +796,8 @@ RleString *poa_polish(Poa *poa, stList *bamChunkReads, PolishParams *params, int
             b->alleleReadSupports[k] = (float) d.results[job]; /* the conversion of impl/bubbleGraph.c:1067 */
         }
     }
+    st_logInfo(" margin_b200 poa_polish: %" PRIi64 " forward matrices, bubble graph %.3f s, forward batch (GPU) %.3f s\n",
+               d.done, tBuilt - tStart, tScored - tBuilt);
     b200_batch_destruct(d.queue);
     free(d.results);
 
