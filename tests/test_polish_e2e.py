@@ -1,4 +1,4 @@
-"""End-to-end drop-in check (SURVEY.md §8 C-4 iv): the reference's own `margin polish` CLI, with the five functions of
+"""End-to-end drop-in check (SURVEY.md §8 C-4 iv): the reference's own `margin polish` CLI, with the seven functions of
 compat/pairwiseAligner_b200.c linked in place of the reference's (oracle/Makefile target `polish`), must write a
 polished FASTA that is byte-identical to the unmodified reference's on the bundled ONT region
 (tests/data/realData/HG002.r94g360.chr20_59M_100k.bam, r94-g360 params).  The expected digest was produced here by
