@@ -10,7 +10,9 @@ cells is credited 2*C cell-passes (forward + backward) howeve
 
 * ``value``  inputs already resident in HBM, timed with CUDA events on the library's stream, L2 flushed between steps.
 * ``e2e``    the same sweep through the C-ABI call a host program makes (``margin_b200_posteriors_batch``) with HOST
-             buffers: H2D of symbols/anchors and D2H of the tuple lists inside the timed region.
+             buffers: H2D of symbols/anchors and D2H of the tuple lists inside the timed region.  ``e2e.value`` is the
+             throughput with three host threads per GPU pushing chunk after chunk (how margin's OpenMP chunk loop
+             drives the aligner); ``e2e.single_call`` is one thread issuing one call at a time.
 * N > 1      one process per GPU (torchrun), every rank sweeps its own chunk (chunks share no state, so there is no
              data-path collective; weak scaling), time = max over ranks, value = sum of the ranks' cell-passes / time.
 * ``--impl reference``  the UNMODIFIED reference aligner (oracle/_ref, built from /root/reference by oracle/Makefile)
@@ -257,6 +259,47 @@ def time_polish(threads):
     return out
 
 
+def time_polish_synth(contig_kb, threads, seed=42, skip_reference=False):
+    """End-to-end `margin polish` on a SYNTHETIC contig of BASELINE configs[1]/[2]'s shape (60x ONT-like 20 kb reads at
+    ~10 % error, r94-g360 params, 100 kb chunks; margin_b200/synth.py: write_polish_dataset + oracle/_ref/sam2bam):
+    the unmodified reference CLI and the CLI linked against this library, -t `threads` each (the reference
+    parallelises over chunks only, polish.c:476; the binding maps thread t to GPU t % device count).  Mb/hour counts
+    the whole CLI run: BAM parsing, POA, bubble graph, stitching and FASTA output included."""
+    import hashlib
+    import subprocess
+    import tempfile
+    from margin_b200 import synth
+    ref = os.path.join(ROOT, "oracle", "_ref")
+    if not (os.path.exists(os.path.join(ref, "margin_b200cli")) and os.path.exists(os.path.join(ref, "sam2bam"))):
+        return None
+    params = os.path.join(ref, "data", "params", "polish", "ont", "r9.4", "allParams.np.human.r94-g360.json")
+    with tempfile.TemporaryDirectory() as tmp:
+        t0 = time.perf_counter()
+        fa, sam, n_reads, draft_len = synth.write_polish_dataset(tmp, seed, contig_kb * 1000, 60, 20000, synth.ONT, 0.01)
+        bam = os.path.join(tmp, "reads.bam")
+        subprocess.run([os.path.join(ref, "sam2bam"), sam, bam], check=True, stderr=subprocess.DEVNULL)
+        os.remove(sam)
+        out = {"workload": "synthetic %d kb contig, 60x 20 kb ONT-like reads (~10 %% error), ont r9.4 g360 params" % contig_kb,
+               "contig_mb": draft_len / 1e6, "reads": n_reads, "threads": threads, "seed": seed,
+               "dataset_s": time.perf_counter() - t0}
+        arms = (("b200", "margin_b200cli"),) if skip_reference else (("reference", "margin_ref"), ("b200", "margin_b200cli"))
+        for key, binary in arms:
+            prefix = os.path.join(tmp, key)
+            cmd = [os.path.join(ref, binary), "polish", bam, fa, params, "-t", str(threads), "-o", prefix]
+            t0 = time.perf_counter()
+            r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=3000)
+            dt = time.perf_counter() - t0
+            if r.returncode != 0:
+                out[key] = {"error": r.stdout[-300:]}
+                continue
+            with open(prefix + ".fa", "rb") as fh:
+                md5 = hashlib.md5(fh.read()).hexdigest()
+            out[key] = {"wall_s": dt, "mb_per_hour": draft_len / 1e6 / dt * 3600.0, "fasta_md5": md5}
+    if "fasta_md5" in out.get("reference", {}) and "fasta_md5" in out.get("b200", {}):
+        out["byte_identical"] = out["reference"]["fasta_md5"] == out["b200"]["fasta_md5"]
+    return out
+
+
 def abi_mod():
     from margin_b200 import abi
     return abi
@@ -307,7 +350,17 @@ def time_sustained(pm, batch, device, cell_passes_rank, contexts=3, rounds=4):
         raise errs[0]
     n = contexts * rounds
     return {"value": n * cell_passes_rank / dt * 1e-9, "unit": UNIT, "contexts": contexts, "chunks": n,
-            "ms_per_chunk": dt / n * 1e3}
+            "ms_per_chunk": dt / n * 1e3, "wall_s": dt, "cell_passes": n * cell_passes_rank}
+
+
+def e2e_object(single_value, single_s, h2d, d2h, sustained):
+    single = {"value": single_value, "unit": UNIT, "ms_per_step": single_s * 1e3, "host_threads": 1}
+    if sustained is None:
+        return dict(single, h2d_bytes_per_step=h2d, d2h_bytes_per_step=d2h, mode="single call")
+    return {"value": sustained["value"], "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+            "ms_per_step": sustained["ms_per_chunk"], "mode": "%d host threads per GPU, %d chunks each, back to back"
+            % (sustained["contexts"], sustained["chunks"] // sustained["contexts"]),
+            "host_threads": sustained["contexts"], "single_call": single}
 
 
 def main_ours(args):
@@ -396,8 +449,10 @@ def main_ours(args):
     sustained = None
     if not args.no_sustained:
         sustained = time_sustained(pm, batch, local, cell_passes_rank=2.0 * cells, contexts=3, rounds=4)
-        if dist is not None:
-            sustained["value"] = reduce_scalar(dist, sustained["value"], "SUM", dev)
+        # whole job: every rank's chunks over the slowest rank's wall time
+        wall = reduce_scalar(dist, sustained.pop("wall_s"), "MAX", dev)
+        sustained["value"] = reduce_scalar(dist, sustained.pop("cell_passes"), "SUM", dev) / wall * 1e-9
+        sustained["ms_per_chunk"] = wall / sustained["chunks"] * 1e3
 
     # ---- roofline of the dominant kernel (CUDA events around each launch, same timed region)
     dom = max(ktimes.items(), key=lambda kv: kv[1][0])[0] if ktimes else "none"
@@ -414,8 +469,10 @@ def main_ours(args):
                    "l2": "flushed between steps (512 MiB write)",
                    "boundary_formats": "plain" if args.plain_formats else "anchor steps 4 B, tuples 8 B", "wall_ms_per_step_incl_flush": t_wall / args.steps * 1e3},
         "clocks": clocks,
-        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": batch.h2d_bytes, "d2h_bytes_per_step": d2h,
-                "ms_per_step": e2e_s * 1e3, "sustained_three_contexts": sustained},
+        # e2e.value is THROUGHPUT through margin_b200_posteriors_batch the way margin drives it (polish.c:476: several
+        # host threads, one chunk each): 3 host threads per GPU, every chunk copied in from pinned host memory and its
+        # lists copied back.  `single_call` is one thread issuing one call at a time (latency of a lone chunk).
+        "e2e": e2e_object(e2e_value, e2e_s, batch.h2d_bytes, d2h, sustained),
         "gpu_launches": launches,
         "kernel_ms_per_step": {k: v[0] / args.steps for k, v in ktimes.items() if v[1]},
         "roofline": roof,
@@ -426,6 +483,9 @@ def main_ours(args):
                                 "sample": r["sample"]}
     if rank == 0 and world == 1 and args.polish:
         line["polish"] = time_polish(min(host_cores(), 8))
+    if rank == 0 and world == 1 and args.polish_synth > 0:
+        line["polish_synth"] = time_polish_synth(args.polish_synth, min(host_cores(), args.polish_threads), args.seed,
+                                                 args.polish_skip_reference)
     if rank == 0:
         print(json.dumps(line), flush=True)
     al.close()
@@ -498,6 +558,11 @@ def main():
     ap.add_argument("--plain-formats", action="store_true",
                     help="12-byte anchor triples in, 12-byte tuple records out instead of the compact boundary formats")
     ap.add_argument("--no-sustained", action="store_true", help="skip the two-context sustained end-to-end leg")
+    ap.add_argument("--polish-synth", type=int, default=0, metavar="KB",
+                    help="also time `margin polish` on a synthetic contig of KB kilobases (60x 20 kb ONT-like reads, one "
+                         "100 kb chunk per host thread): reference CLI vs the CLI linked against this library")
+    ap.add_argument("--polish-threads", type=int, default=16)
+    ap.add_argument("--polish-skip-reference", action="store_true")
     ap.add_argument("--polish", action="store_true",
                     help="also time `margin polish` on the bundled region: reference CLI vs the CLI linked against "
                          "this library (oracle/_ref, built where /root/reference exists)")

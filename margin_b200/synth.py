@@ -164,3 +164,77 @@ def bubble_workload(seed, n, rle=True, max_len=43):
             sy |= (np.minimum(rng.geometric(0.7, ly), 50).astype(np.uint16) << 8)
         items.append((sx, sy, np.zeros((0, 3), np.int32), int(rng.random() < 0.5), 0, 0))
     return items
+
+
+# ------------------------------------------------------------------------------------- `margin polish` datasets
+#
+# SURVEY.md §8 D-2 "BAM mode": the same contig / read / error model as make_chunk, written as the files the
+# reference CLI reads (polish.c:87: <BAM> <FASTA> <PARAMS>): a draft FASTA and a coordinate-sorted SAM whose CIGARs
+# are the true edit paths, so that convertToReadsAndAlignmentsWithFiltered (impl/htsIntegration.c:557-891) derives
+# the per-match anchors itself.  oracle/_ref/sam2bam turns the SAM into an indexed BAM (no samtools on the box).
+
+_BASES = np.frombuffer(b"ACGT", dtype=np.uint8)
+
+
+def _cigar(ax, ay, read_len):
+    """CIGAR of a read from its match columns (ax: draft positions, ay: read positions, both strictly increasing):
+    leading / trailing unaligned read bases are soft-clipped, gaps between match columns are D then I."""
+    dx = np.diff(ax) - 1
+    dy = np.diff(ay) - 1
+    brk = np.flatnonzero((dx > 0) | (dy > 0))  # a gap sits between match column i and i+1
+    parts = []
+    if ay[0] > 0:
+        parts.append("%dS" % ay[0])
+    prev = 0
+    for i, gx, gy in zip(brk.tolist(), dx[brk].tolist(), dy[brk].tolist()):
+        parts.append("%dM" % (i + 1 - prev))
+        if gx > 0:
+            parts.append("%dD" % gx)
+        if gy > 0:
+            parts.append("%dI" % gy)
+        prev = i + 1
+    parts.append("%dM" % (len(ax) - prev))
+    tail = read_len - 1 - int(ay[-1])
+    if tail > 0:
+        parts.append("%dS" % tail)
+    return "".join(parts)
+
+
+def write_polish_dataset(out_dir, seed=42, contig_len=100000, depth=60, read_len=20000, err=ONT, draft_err=0.01,
+                         contig_name="contig_1"):
+    """Writes <out_dir>/draft.fa and <out_dir>/reads.sam; returns (fasta_path, sam_path, n_reads, draft_len)."""
+    import os
+    rng = np.random.default_rng(seed)
+    truth = rng.integers(0, 4, contig_len).astype(np.uint16)
+    d3 = draft_err / 3.0
+    draft, dpos = mutate(rng, truth, d3, d3, d3, 0.6)
+    n_reads = max(1, int(round(depth * contig_len / float(read_len))))
+    recs = []
+    for k in range(n_reads):
+        rl = min(read_len, contig_len)
+        s = int(rng.integers(0, contig_len - rl + 1))
+        read, rpos = mutate(rng, truth[s:s + rl], **err)
+        fwd = bool(rng.random() < 0.5)
+        both = (rpos >= 0) & (dpos[s:s + rl] >= 0)
+        ax = dpos[s:s + rl][both]
+        ay = rpos[both]
+        if len(ax) < 2 or len(read) == 0:
+            continue
+        seq = _BASES[read].tobytes().decode()
+        # a reverse-strand read is stored reverse-complemented in a BAM, i.e. in reference orientation: the same
+        # text, flag 16 (margin picks the reverse-strand state machine from the flag, htsIntegration.c:845-848)
+        recs.append((int(ax[0]), "read_%06d" % k, 0 if fwd else 16, _cigar(ax, ay, len(read)), seq))
+    recs.sort(key=lambda r: (r[0], r[1]))
+    os.makedirs(out_dir, exist_ok=True)
+    fa = os.path.join(out_dir, "draft.fa")
+    with open(fa, "w") as fh:
+        text = _BASES[draft].tobytes().decode()
+        fh.write(">%s\n" % contig_name)
+        for i in range(0, len(text), 80):
+            fh.write(text[i:i + 80] + "\n")
+    sam = os.path.join(out_dir, "reads.sam")
+    with open(sam, "w") as fh:
+        fh.write("@HD\tVN:1.6\tSO:coordinate\n@SQ\tSN:%s\tLN:%d\n" % (contig_name, len(draft)))
+        for pos, name, flag, cigar, seq in recs:
+            fh.write("%s\t%d\t%s\t%d\t60\t%s\t*\t0\t0\t%s\t*\n" % (name, flag, contig_name, pos + 1, cigar, seq))
+    return fa, sam, len(recs), len(draft)
