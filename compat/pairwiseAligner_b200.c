@@ -384,9 +384,14 @@ typedef struct {
     int64_t cap[3];
     uint64_t *table; /* 0 = empty slot, else packed coordinates + 1 */
     uint64_t tableSize;
+    uint64_t *keys[2]; /* radix sort buffers of b200_sort_pairs */
+    int64_t capKeys;
+    RleString sub; /* the candidate insert / deleted substring (b200_substring), buffers reused across candidates */
+    uint64_t capSub;
 } B200AugmentScratch;
 
 static __thread B200AugmentScratch augmentScratch;
+static __thread double augmentPhase[4]; /* match loop, match set, inserts (sort + enumeration), deletes */
 
 /* List l of alignment i as flat records, x shifted back by the crop. */
 static int64_t b200_pairs(const margin_b200_result *res, int l, int64_t i, int64_t shiftX) {
@@ -464,6 +469,79 @@ static int b200_cmp_yx(const void *a, const void *b) {
     return p->x < q->x ? -1 : (p->x > q->x ? 1 : 0);
 }
 
+/*
+ * Sorts gap records by (x, y) (byYX = 0: cmpAlignedPairsByCoordinates, impl/poa.c:137-151) or by (y, x) (byYX = 1:
+ * ...Inverted, :153-166).  Coordinates are >= -1 and weights < 2^24, so a record packs into one 64-bit key
+ * (major + 1) << 44 | (minor + 1) << 24 | weight, which an LSD radix sort of four 10-bit digits orders in O(n); records
+ * are unique per cell, so the order equals the comparison sort's.  Falls back to qsort for short lists and for
+ * coordinates beyond 2^20.
+ */
+#define B200_RADIX_BITS 10
+static void b200_sort_pairs(B200Pair *p, int64_t n, int byYX) {
+    B200AugmentScratch *sc = &augmentScratch;
+    int ok = n >= 256;
+    for (int64_t i = 0; ok && i < n; i++) {
+        ok = p[i].x >= -1 && p[i].y >= -1 && p[i].x < (1 << 20) - 1 && p[i].y < (1 << 20) - 1 && p[i].w >= 0 &&
+             p[i].w < (1 << 24);
+    }
+    if (!ok) {
+        qsort(p, n, sizeof(B200Pair), byYX ? b200_cmp_yx : b200_cmp_xy);
+        return;
+    }
+    if (n > sc->capKeys) {
+        sc->capKeys = n * 2;
+        sc->keys[0] = st_realloc(sc->keys[0], sc->capKeys * sizeof(uint64_t));
+        sc->keys[1] = st_realloc(sc->keys[1], sc->capKeys * sizeof(uint64_t));
+    }
+    uint64_t *a = sc->keys[0], *b = sc->keys[1];
+    for (int64_t i = 0; i < n; i++) {
+        uint64_t major = (uint64_t) ((byYX ? p[i].y : p[i].x) + 1), minor = (uint64_t) ((byYX ? p[i].x : p[i].y) + 1);
+        a[i] = (major << 44) | (minor << 24) | (uint64_t) p[i].w;
+    }
+    for (int shift = 24; shift < 64; shift += B200_RADIX_BITS) {
+        int64_t count[1 << B200_RADIX_BITS];
+        memset(count, 0, sizeof(count));
+        for (int64_t i = 0; i < n; i++) count[(a[i] >> shift) & ((1 << B200_RADIX_BITS) - 1)]++;
+        if (count[(a[0] >> shift) & ((1 << B200_RADIX_BITS) - 1)] == n) continue; /* all keys agree on this digit */
+        int64_t at = 0;
+        for (int d = 0; d < (1 << B200_RADIX_BITS); d++) {
+            int64_t c = count[d];
+            count[d] = at;
+            at += c;
+        }
+        for (int64_t i = 0; i < n; i++) b[count[(a[i] >> shift) & ((1 << B200_RADIX_BITS) - 1)]++] = a[i];
+        uint64_t *t = a;
+        a = b;
+        b = t;
+    }
+    for (int64_t i = 0; i < n; i++) {
+        int64_t major = (int64_t) (a[i] >> 44) - 1, minor = (int64_t) ((a[i] >> 24) & 0xfffff) - 1;
+        p[i].x = byYX ? minor : major;
+        p[i].y = byYX ? major : minor;
+        p[i].w = (int64_t) (a[i] & 0xffffff);
+    }
+}
+
+/* rleString_copySubstring (impl/rle.c:82-102) into the thread's scratch RleString: no allocation per candidate. */
+static RleString *b200_substring(const RleString *from, int64_t start, int64_t length) {
+    B200AugmentScratch *sc = &augmentScratch;
+    if ((uint64_t) length + 1 > sc->capSub) {
+        sc->capSub = (uint64_t) length * 2 + 64;
+        sc->sub.rleString = st_realloc(sc->sub.rleString, sc->capSub);
+        sc->sub.repeatCounts = st_realloc(sc->sub.repeatCounts, sc->capSub * sizeof(uint64_t));
+    }
+    RleString *sub = &sc->sub;
+    sub->length = (uint64_t) length;
+    sub->nonRleLength = 0;
+    memcpy(sub->rleString, from->rleString + start, (size_t) length);
+    sub->rleString[length] = '\0';
+    for (int64_t i = 0; i < length; i++) {
+        sub->repeatCounts[i] = from->repeatCounts[start + i];
+        sub->nonRleLength += sub->repeatCounts[i];
+    }
+    return sub;
+}
+
 static void b200_node_add_insert(PoaNode *node, RleString *insert, double weight, bool strand, PoaBaseObservation *obs) {
     PoaInsert *hit = NULL;
     for (int64_t m = 0; m < stList_length(node->inserts) && hit == NULL; m++) {
@@ -504,6 +582,7 @@ static void b200_poa_augment(Poa *poa, RleString *read, bool readStrand, int64_t
     B200Pair *matches = sc->pairs[0], *deletes = sc->pairs[1], *inserts = sc->pairs[2];
 
     /* match weights and observations, in list order (impl/poa.c:324-341) */
+    double tPhase0 = omp_get_wtime();
     for (int64_t k = 0; k < nMatch; k++) {
         PoaNode *node = stList_get(poa->nodes, matches[k].x + 1);
         int64_t y = matches[k].y;
@@ -512,10 +591,12 @@ static void b200_poa_augment(Poa *poa, RleString *read, bool readStrand, int64_t
         node->repeatCountWeights[rc] += matches[k].w;
         stList_append(node->observations, poaBaseObservation_construct(readNo, y, matches[k].w));
     }
+    double tPhase1 = omp_get_wtime();
     b200_match_set_fill(matches, nMatch);
+    double tPhase2 = omp_get_wtime();
 
     /* complete inserts: same reference coordinate, consecutive read coordinates, flanked by matches or the ends */
-    qsort(inserts, nInsert, sizeof(B200Pair), b200_cmp_xy);
+    b200_sort_pairs(inserts, nInsert, 0);
     for (int64_t i = 0, j; i < nInsert; i = j) {
         int64_t x = inserts[i].x, y0 = inserts[i].y;
         for (j = i + 1; j < nInsert && inserts[j].x == x && inserts[j].y == y0 + (j - i); j++);
@@ -527,7 +608,7 @@ static void b200_poa_augment(Poa *poa, RleString *read, bool readStrand, int64_t
                 weight = weight < inserts[l].w ? weight : inserts[l].w;
                 int64_t yl = y0 + (l - i);
                 if (yl + 1 < read->length && !b200_is_match(x + 1, yl + 1)) continue;
-                RleString *insert = rleString_copySubstring(read, yk, l + 1 - k);
+                RleString *insert = b200_substring(read, yk, l + 1 - k);
                 int64_t position = getShift(poa->refString, x + 1, insert, compareRL);
                 int64_t suffix = getMaxCommonSuffixLength(poa->refString, position, insert, compareRL);
                 if (suffix > 0) {
@@ -536,13 +617,13 @@ static void b200_poa_augment(Poa *poa, RleString *read, bool readStrand, int64_t
                 }
                 b200_node_add_insert(stList_get(poa->nodes, position), insert, weight, readStrand,
                                      poaBaseObservation_construct(readNo, yk, weight));
-                rleString_destruct(insert);
             }
         }
     }
 
     /* complete deletes: same read coordinate, consecutive reference coordinates */
-    qsort(deletes, nDelete, sizeof(B200Pair), b200_cmp_yx);
+    double tPhase3 = omp_get_wtime();
+    b200_sort_pairs(deletes, nDelete, 1);
     int64_t refLength = poa->refString->length;
     for (int64_t i = 0, j; i < nDelete; i = j) {
         int64_t x0 = deletes[i].x, y = deletes[i].y;
@@ -556,15 +637,19 @@ static void b200_poa_augment(Poa *poa, RleString *read, bool readStrand, int64_t
                 int64_t xl = x0 + (l - i);
                 if (xl + 1 < refLength && !b200_is_match(xl + 1, y + 1)) continue;
                 int64_t length = l - k + 1;
-                RleString *deleted = rleString_copySubstring(poa->refString, xk, length);
+                RleString *deleted = b200_substring(poa->refString, xk, length);
                 int64_t position = getShift(poa->refString, xk, deleted, compareRL);
                 position -= getMaxCommonSuffixLength(poa->refString, position, deleted, compareRL);
-                rleString_destruct(deleted);
                 b200_node_add_delete(stList_get(poa->nodes, position), length, weight, readStrand,
                                      poaBaseObservation_construct(readNo, y, weight));
             }
         }
     }
+    double tPhase4 = omp_get_wtime();
+    augmentPhase[0] += tPhase1 - tPhase0;
+    augmentPhase[1] += tPhase2 - tPhase1;
+    augmentPhase[2] += tPhase3 - tPhase2;
+    augmentPhase[3] += tPhase4 - tPhase3;
 }
 
 /* ----------------------------------------------------------------------------- impl/poa.c:668-716, batched */
@@ -600,6 +685,7 @@ Poa *poa_realign(stList *bamChunkReads, stList *anchorAlignments, RleString *ref
     b200_load_params(polishParams->p);
 
     double tStart = omp_get_wtime(), tLists = 0.0, tAugment = 0.0, tFree = 0.0;
+    memset(augmentPhase, 0, sizeof(augmentPhase));
     B200Batch *b = b200_batch_construct(n);
     int64_t *firstRefPositions = st_calloc(n, sizeof(int64_t));
     for (int64_t i = 0; i < n; i++) {
@@ -659,8 +745,9 @@ Poa *poa_realign(stList *bamChunkReads, stList *anchorAlignments, RleString *ref
     free(firstRefPositions);
     b200_batch_destruct(b);
     st_logInfo(" margin_b200 poa_realign: %" PRIi64 " reads, prepare %.3f s, aligner (GPU, whole batch) %.3f s, "
-               "tuple lists %.3f s, poa_augment %.3f s, free %.3f s\n", n, tPrepared - tStart, tAligned - tPrepared,
-               tLists, tAugment, tFree);
+               "tuple lists %.3f s, poa_augment %.3f s (matches %.3f, match set %.3f, inserts %.3f, deletes %.3f), "
+               "free %.3f s\n", n, tPrepared - tStart, tAligned - tPrepared, tLists, tAugment, augmentPhase[0],
+               augmentPhase[1], augmentPhase[2], augmentPhase[3], tFree);
     return poa;
 }
 
@@ -707,10 +794,14 @@ static int64_t b200_tag_of(float f) {
     return (int64_t) (u >> 31) * B200_TAG_LOW_MAX + (int64_t) (u & B200_TAG_LOW_MAX) - 1;
 }
 
+static __thread double forwardDeviceMs; /* device time of the forward batches of this thread (CUDA events) */
+
 static void b200_forward_run(B200Batch *b, double *out) {
     margin_b200_batch mb;
+    margin_b200_result stats;
     b200_batch_describe(b, &mb);
-    if (margin_b200_forward_batch(b200_ctx(), &mb, out, NULL) != 0) b200_fail();
+    if (margin_b200_forward_batch(b200_ctx(), &mb, out, &stats) != 0) b200_fail();
+    forwardDeviceMs += stats.gpu_ms;
 }
 
 /* Runs the queued jobs; their results land behind the ones already known. */
@@ -781,6 +872,7 @@ RleString *poa_polish(Poa *poa, stList *bamChunkReads, PolishParams *params, int
     memset(&d, 0, sizeof(d));
     d.queue = b200_batch_construct(1024);
     tls.deferred = &d;
+    forwardDeviceMs = 0.0;
     double tStart = omp_get_wtime();
     BubbleGraph *bg = bubbleGraph_constructFromPoa(poa, bamChunkReads, params);
     tls.deferred = NULL;
@@ -796,8 +888,8 @@ RleString *poa_polish(Poa *poa, stList *bamChunkReads, PolishParams *params, int
             b->alleleReadSupports[k] = (float) d.results[job]; /* the conversion of impl/bubbleGraph.c:1067 */
         }
     }
-    st_logInfo(" margin_b200 poa_polish: %" PRIi64 " forward matrices, bubble graph %.3f s, forward batch (GPU) %.3f s\n",
-               d.done, tBuilt - tStart, tScored - tBuilt);
+    st_logInfo(" margin_b200 poa_polish: %" PRIi64 " forward matrices, bubble graph %.3f s, forward batch %.3f s "
+               "(%.1f ms on the device)\n", d.done, tBuilt - tStart, tScored - tBuilt, forwardDeviceMs);
     b200_batch_destruct(d.queue);
     free(d.results);
 

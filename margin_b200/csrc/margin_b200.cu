@@ -1829,6 +1829,10 @@ extern "C" int margin_b200_forward_resident(margin_b200_ctx *c, margin_b200_resu
                     MARGIN_B200_MAX_RL - 1);
     float ms = 0;
     CU(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+    if (getenv("MARGIN_B200_FWD_STATS"))
+        fprintf(stderr, "margin_b200 forward: %d matrices (%d register-resident, %lld cells; general path %lld cells), "
+                "%d launches, %.2f ms on the device\n", nj, n_tiny, (long long) tiny_cells, (long long) general_cells,
+                c->launches, ms);
     c->total_cells = general_cells + tiny_cells;  // tiny matrices are counted whole (their band leaves out far corners at most)
     c->tiny_mask.clear();
     if (stats) {

@@ -232,6 +232,8 @@ def write_polish_dataset(out_dir, seed=42, contig_len=100000, depth=60, read_len
         fh.write(">%s\n" % contig_name)
         for i in range(0, len(text), 80):
             fh.write(text[i:i + 80] + "\n")
+    with open(fa + ".fai", "w") as fh:  # written here: margin's chunk threads would otherwise race to build it
+        fh.write("%s\t%d\t%d\t80\t81\n" % (contig_name, len(draft), len(contig_name) + 2))
     sam = os.path.join(out_dir, "reads.sam")
     with open(sam, "w") as fh:
         fh.write("@HD\tVN:1.6\tSO:coordinate\n@SQ\tSN:%s\tLN:%d\n" % (contig_name, len(draft)))
