@@ -159,6 +159,11 @@ typedef struct margin_b200_ctx margin_b200_ctx;
  * without a usable CUDA device fails. */
 int margin_b200_device_count(void); /* usable CUDA devices (0 when there is none) */
 int margin_b200_create(margin_b200_ctx **ctx, int device);
+/* Optional: initialises the CUDA runtime, the primary context of every device and this library's kernel images ahead
+ * of the first margin_b200_create (safe from any thread, e.g. a helper thread started while the host program still
+ * parses its inputs: `margin polish` reads parameters and BAM records for a second or more before poa_realign
+ * (impl/polish.c:476 -> impl/poa.c:1955) needs the aligner).  Returns the device count. */
+int margin_b200_prewarm(void);
 void margin_b200_destroy(margin_b200_ctx *ctx);
 const char *margin_b200_last_error(void);
 int margin_b200_version(void);

@@ -314,6 +314,21 @@ int margin_b200_device_count(void) {
     return count;
 }
 
+int margin_b200_prewarm(void) {
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess) return 0;
+    for (int d = 0; d < count; d++) {
+        if (cudaSetDevice(d) != cudaSuccess || cudaFree(nullptr) != cudaSuccess) continue;
+        // forces the kernel images in (lazy module loading would otherwise do it inside the first batch)
+        cudaFuncAttributes fa;
+        cudaFuncGetAttributes(&fa, mb::backward_tile_kernel<8, kTileThreads, true, false>);
+        cudaFuncGetAttributes(&fa, mb::forward_tile_kernel<8, kTileThreads, false>);
+        cudaFuncGetAttributes(&fa, mb::tiny_forward_kernel<16, kTileThreads, false>);
+    }
+    cudaGetLastError();
+    return count;
+}
+
 int margin_b200_create(margin_b200_ctx **out, int device) {
     if (!out) return fail("margin_b200_create: null output pointer");
     *out = nullptr;
@@ -1703,6 +1718,7 @@ extern "C" int margin_b200_forward_resident(margin_b200_ctx *c, margin_b200_resu
     if (!c) return fail("margin_b200_forward_resident: null argument");
     if (check_device(c->device)) return 1;
     CU(cudaSetDevice(c->device));
+    Trace tr(c);
     c->launches = 0;
     c->ev_used = 0;
     const int nj = (int) c->jobs.size();
@@ -1728,6 +1744,7 @@ extern "C" int margin_b200_forward_resident(margin_b200_ctx *c, margin_b200_resu
         }
     }
     if (c->d_fwd_out.ensure((size_t) (c->n_aln + 1) * sizeof(double))) return 1;
+    tr.mark("fwd classify");
     int64_t general_cells = 0;
     if (n_tiny < nj) {
         // band tables only for the general jobs: a chunk list without the tiny ones stands in for the batch's own
@@ -1784,6 +1801,7 @@ extern "C" int margin_b200_forward_resident(margin_b200_ctx *c, margin_b200_resu
         for (int j = 0; j < nj; j++)
             if (!c->tiny_mask[j]) general_cells += c->job_cells[j];
     }
+    tr.mark("fwd general");
     if (n_tiny > 0) {
         if (c->h_tiny_ids.ensure((size_t) n_tiny * 4 + 16) || c->d_tiny_ids.ensure((size_t) n_tiny * 4 + 16)) return 1;
         int32_t *ids = c->h_tiny_ids.as<int32_t>();
@@ -1818,11 +1836,13 @@ extern "C" int margin_b200_forward_resident(margin_b200_ctx *c, margin_b200_resu
         launch(std::integral_constant<int, 32>{}, n16, n_tiny - n16);
     }
     CU(cudaEventRecord(c->ev1, c->stream));
+    tr.mark("fwd tiny enqueue");
     if (c->h_small.ensure(64)) return 1;
     int *h_sym_err = reinterpret_cast<int *>(c->h_small.as<char>() + 32);
     *h_sym_err = 0;
     if (c->d_sym_err.p && ctl_copy(c->stream, h_sym_err, c->d_sym_err.p, 8)) return 1;
     CU(cudaStreamSynchronize(c->stream));
+    tr.mark("fwd sync");
     CU(cudaGetLastError());
     if (*h_sym_err)
         return fail("a symbol carries a run length >= %d; the repeat-count model holds 0..%d", MARGIN_B200_MAX_RL,
