@@ -201,6 +201,8 @@ def load_library():
     lib.margin_b200_last_error.restype = C.c_char_p
     lib.margin_b200_device_count.argtypes = []
     lib.margin_b200_device_count.restype = i32
+    lib.margin_b200_prewarm.argtypes = []
+    lib.margin_b200_prewarm.restype = i32
     lib.margin_b200_version.argtypes = []
     lib.margin_b200_version.restype = i32
     lib.margin_b200_set_model.argtypes = [vp, i32, C.POINTER(Model)]
@@ -236,7 +238,7 @@ EXPORTED_SYMBOLS = [
     "margin_b200_set_model", "margin_b200_set_params", "margin_b200_set_pair_format", "margin_b200_set_kernel_timing", "margin_b200_posteriors_batch",
     "margin_b200_upload_batch", "margin_b200_posteriors_resident", "margin_b200_download_result",
     "margin_b200_forward_batch", "margin_b200_forward_resident", "margin_b200_bands",
-    "margin_b200_last_kernel_ms", "margin_b200_device_count",
+    "margin_b200_last_kernel_ms", "margin_b200_device_count", "margin_b200_prewarm",
 ]
 
 KERNEL_CLASSES = ["band", "schedule", "forward", "backward", "scan", "gather", "offsets", "final"]
