@@ -895,14 +895,33 @@ double computeForwardProbability(SymbolString sX, SymbolString sY, stList *ancho
     return b200_tagged_nan(job);
 }
 
-RleString *poa_polish(Poa *poa, stList *bamChunkReads, PolishParams *params, int64_t **poaToConsensusMap) {
+/*
+ * bubbleGraph_constructFromPoaAndVCF (impl/bubbleGraph.c:918-1124) with its forward matrices run as one batch.  Both
+ * callers come through here: poa_polish below (haploid consensus, via the reference's bubbleGraph_constructFromPoa
+ * arguments: no VCF, phasing = FALSE) and the diploid path of polish.c:676 (phasing = TRUE, once per bubble-finding
+ * iteration) — without this a diploid run would issue every matrix as a GPU batch of one.  The reference's body is
+ * linked under the name bubbleGraph_constructFromPoaAndVCF_reference (oracle/Makefile renames the symbol in
+ * bubbleGraph.o; INTEGRATION.md shows the one-line source patch) and is called unchanged.
+ */
+BubbleGraph *bubbleGraph_constructFromPoaAndVCF_reference(Poa *poa, stList *bamChunkReads, stList *vcfEntries,
+                                                          PolishParams *params, bool phasing);
+
+BubbleGraph *bubbleGraph_constructFromPoaAndVCF(Poa *poa, stList *bamChunkReads, stList *vcfEntries, PolishParams *params,
+                                                bool phasing) {
+    static int batching = -1; /* MARGIN_B200_BUBBLE_BATCH=0: every matrix as a batch of one (A/B measurement only) */
+    if (batching < 0) {
+        const char *e = getenv("MARGIN_B200_BUBBLE_BATCH");
+        batching = !(e != NULL && e[0] == '0');
+    }
+    if (tls.deferred != NULL || !batching) /* nested calls do not occur in the reference; the outer one would patch */
+        return bubbleGraph_constructFromPoaAndVCF_reference(poa, bamChunkReads, vcfEntries, params, phasing);
     B200Deferred d;
     memset(&d, 0, sizeof(d));
     d.queue = b200_batch_construct(1024);
     tls.deferred = &d;
     forwardDeviceMs = 0.0;
     double tStart = omp_get_wtime();
-    BubbleGraph *bg = bubbleGraph_constructFromPoa(poa, bamChunkReads, params);
+    BubbleGraph *bg = bubbleGraph_constructFromPoaAndVCF_reference(poa, bamChunkReads, vcfEntries, params, phasing);
     tls.deferred = NULL;
     double tBuilt = omp_get_wtime();
     b200_deferred_flush(&d);
@@ -916,10 +935,17 @@ RleString *poa_polish(Poa *poa, stList *bamChunkReads, PolishParams *params, int
             b->alleleReadSupports[k] = (float) d.results[job]; /* the conversion of impl/bubbleGraph.c:1067 */
         }
     }
-    st_logInfo(" margin_b200 poa_polish: %" PRIi64 " forward matrices, bubble graph %.3f s, forward batch %.3f s "
-               "(%.1f ms on the device)\n", d.done, tBuilt - tStart, tScored - tBuilt, forwardDeviceMs);
+    st_logInfo(" margin_b200 bubble graph%s: %" PRIi64 " forward matrices, graph %.3f s, forward batch %.3f s "
+               "(%.1f ms on the device)\n", phasing ? " (phasing)" : "", d.done, tBuilt - tStart, tScored - tBuilt,
+               forwardDeviceMs);
     b200_batch_destruct(d.queue);
     free(d.results);
+    return bg;
+}
+
+/* poa_polish (impl/poa.c:1852-1873): the reference's body, its bubble graph built through the batching wrapper above. */
+RleString *poa_polish(Poa *poa, stList *bamChunkReads, PolishParams *params, int64_t **poaToConsensusMap) {
+    BubbleGraph *bg = bubbleGraph_constructFromPoaAndVCF(poa, bamChunkReads, NULL, params, FALSE);
 
     uint64_t *consensusPath = bubbleGraph_getConsensusPath(bg, params);
     RleString *newConsensusString = bubbleGraph_getConsensusString(bg, consensusPath, poaToConsensusMap, params);

@@ -41,6 +41,34 @@ def test_margin_polish_with_b200_aligner_is_byte_identical(tmp_path, mode):
     assert md5 == EXPECTED_FASTA_MD5
 
 
+# `margin polish --diploid` (polish.c:676: phasing bubble graphs, then one polish per haplotype) on the same region; the
+# digests are the unmodified reference's (oracle/_ref/margin_ref -2, 43 s on 8 cores of the GPU box,
+# profiles/r01_v13_diploid.log).
+EXPECTED_DIPLOID_MD5 = {"hap1": "5d467b84be719d49a0bf18a8caaca4ae", "hap2": "8b8440e24cf2ad7aa411afe6e4fc86bb"}
+
+
+@pytest.mark.gpu
+def test_diploid_polish_with_b200_aligner_is_byte_identical(tmp_path):
+    """The diploid path builds its bubble graphs from polish.c, not from poa_polish: the binding's wrapper of
+    bubbleGraph_constructFromPoaAndVCF must batch those forward matrices too and leave both haplotype FASTAs as the
+    reference writes them."""
+    if not os.path.exists(os.path.join(REF, "margin_b200cli")):
+        pytest.skip("oracle/_ref/margin_b200cli not built (needs /root/reference at build time)")
+    data = os.path.join(REF, "data")
+    prefix = str(tmp_path / "dip")
+    cmd = [os.path.join(REF, "margin_b200cli"), "polish", os.path.join(data, "HG002.r94g360.chr20_59M_100k.bam"),
+           os.path.join(data, "hg38.chr20_59M_100k.fa"),
+           os.path.join(data, "params", "polish", "ont", "r9.4", "allParams.np.human.r94-g360.json"),
+           "-t", "4", "-o", prefix, "-2", "-a", "info"]
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:]
+    batched = [l for l in r.stdout.splitlines() if "margin_b200 bubble graph (phasing)" in l]
+    assert batched, "the phasing bubble graphs did not go through the batching wrapper"
+    for hap, want in EXPECTED_DIPLOID_MD5.items():
+        with open("%s.fa.%s" % (prefix, hap), "rb") as fh:
+            assert hashlib.md5(fh.read()).hexdigest() == want, hap
+
+
 def test_reference_cli_reproduces_expected_digest(tmp_path):
     """CPU: the unmodified reference built by oracle/Makefile writes the expected FASTA (pins the digest itself)."""
     if not os.path.exists(os.path.join(REF, "margin_ref")):
