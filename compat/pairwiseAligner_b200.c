@@ -785,11 +785,14 @@ Poa *poa_realign(stList *bamChunkReads, stList *anchorAlignments, RleString *ref
  * Forward-only likelihoods.  bubbleGraph_constructFromPoaAndVCF asks for one small unbanded
  * forward matrix per (allele, read substring) pair — 444 k calls on the bundled region, median 11 x 11 — and only
  * stores each result as a float in Bubble.alleleReadSupports (impl/bubbleGraph.c:1067), copying it for repeated
- * read substrings (:1058-1061); nothing reads the values before the graph is returned.  poa_polish below uses that:
- * while it builds the graph, computeForwardProbability queues the job and returns a quiet NaN whose payload is the
- * job number (the double -> float conversion and the copies keep the payload bits); after the graph is built all
- * jobs run as ONE margin_b200_forward_batch and every tagged float is replaced by its job's result.
- * bubbleGraph.c is linked unchanged.  Outside poa_polish computeForwardProbability is a batch of one.
+ * read substrings (:1058-1061); nothing reads the values before the graph is returned.  The wrapper of
+ * bubbleGraph_constructFromPoaAndVCF below uses that: while the reference's body builds the graph,
+ * computeForwardProbability queues the job and returns a quiet NaN whose payload is the job number (the double ->
+ * float conversion and the copies keep the payload bits); after the graph is built all jobs run as ONE
+ * margin_b200_forward_batch and every tagged float is replaced by its job's result.  bubbleGraph.c is compiled
+ * unchanged.  Everywhere else computeForwardProbability is a batch of one: the VCF-driven constructors of `margin
+ * phase` (impl/bubbleGraph.c:1126, :1338) could be wrapped the same way, bubbleGraph_partitionFilteredReads (:1500)
+ * reads each value at once (:1663) and cannot.
  */
 #define B200_TAG_LOW_MAX 0x3fffffU                    /* 22 payload bits below the quiet bit of a float NaN */
 #define B200_MAX_DEFERRED (2 * (int64_t) B200_TAG_LOW_MAX) /* the sign bit doubles the range; low bits 0 = a real NaN */
