@@ -251,15 +251,18 @@ def time_polish(threads):
             if r.returncode != 0:
                 out[key] = {"error": r.stdout[-300:]}
                 continue
-            with open(prefix + ".fa", "rb") as fh:
-                md5 = hashlib.md5(fh.read()).hexdigest()
+            h = hashlib.md5()
+            for name in ([prefix + ".fa.hap1", prefix + ".fa.hap2"] if diploid else [prefix + ".fa"]):
+                with open(name, "rb") as fh:
+                    h.update(fh.read())
+            md5 = h.hexdigest()
             out[key] = {"wall_s": dt, "mb_per_hour": 0.1 / dt * 3600.0, "fasta_md5": md5}
     if "reference" in out and "b200" in out and "fasta_md5" in out["reference"] and "fasta_md5" in out["b200"]:
         out["byte_identical"] = out["reference"]["fasta_md5"] == out["b200"]["fasta_md5"]
     return out
 
 
-def time_polish_synth(contig_kb, threads, seed=42, skip_reference=False):
+def time_polish_synth(contig_kb, threads, seed=42, skip_reference=False, diploid=False, depth=60):
     """End-to-end `margin polish` on a SYNTHETIC contig of BASELINE configs[1]/[2]'s shape (60x ONT-like 20 kb reads at
     ~10 % error, r94-g360 params, 100 kb chunks; margin_b200/synth.py: write_polish_dataset + oracle/_ref/sam2bam):
     the unmodified reference CLI and the CLI linked against this library, -t `threads` each (the reference
@@ -275,25 +278,32 @@ def time_polish_synth(contig_kb, threads, seed=42, skip_reference=False):
     params = os.path.join(ref, "data", "params", "polish", "ont", "r9.4", "allParams.np.human.r94-g360.json")
     with tempfile.TemporaryDirectory() as tmp:
         t0 = time.perf_counter()
-        fa, sam, n_reads, draft_len = synth.write_polish_dataset(tmp, seed, contig_kb * 1000, 60, 20000, synth.ONT, 0.01)
+        fa, sam, n_reads, draft_len = synth.write_polish_dataset(tmp, seed, contig_kb * 1000, depth, 20000, synth.ONT, 0.01,
+                                                                 het=synth.HET if diploid else None)
         bam = os.path.join(tmp, "reads.bam")
         subprocess.run([os.path.join(ref, "sam2bam"), sam, bam], check=True, stderr=subprocess.DEVNULL)
         os.remove(sam)
-        out = {"workload": "synthetic %d kb contig, 60x 20 kb ONT-like reads (~10 %% error), ont r9.4 g360 params" % contig_kb,
+        out = {"workload": "synthetic %d kb %scontig, %dx 20 kb ONT-like reads (~10 %% error), ont r9.4 g360 params%s"
+                           % (contig_kb, "diploid " if diploid else "", depth, ", margin polish --diploid" if diploid else ""),
                "contig_mb": draft_len / 1e6, "reads": n_reads, "threads": threads, "seed": seed,
                "dataset_s": time.perf_counter() - t0}
         arms = (("b200", "margin_b200cli"),) if skip_reference else (("reference", "margin_ref"), ("b200", "margin_b200cli"))
         for key, binary in arms:
             prefix = os.path.join(tmp, key)
             cmd = [os.path.join(ref, binary), "polish", bam, fa, params, "-t", str(threads), "-o", prefix]
+            if diploid:
+                cmd.append("-2")  # phasing bubble graphs, then one polished FASTA per haplotype (<prefix>.fa.hap1/.hap2)
             t0 = time.perf_counter()
             r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=3000)
             dt = time.perf_counter() - t0
             if r.returncode != 0:
                 out[key] = {"error": r.stdout[-300:]}
                 continue
-            with open(prefix + ".fa", "rb") as fh:
-                md5 = hashlib.md5(fh.read()).hexdigest()
+            h = hashlib.md5()  # diploid: both haplotype FASTAs in one digest
+            for name in ([prefix + ".fa.hap1", prefix + ".fa.hap2"] if diploid else [prefix + ".fa"]):
+                with open(name, "rb") as fh:
+                    h.update(fh.read())
+            md5 = h.hexdigest()
             out[key] = {"wall_s": dt, "mb_per_hour": draft_len / 1e6 / dt * 3600.0, "fasta_md5": md5}
     if "fasta_md5" in out.get("reference", {}) and "fasta_md5" in out.get("b200", {}):
         out["byte_identical"] = out["reference"]["fasta_md5"] == out["b200"]["fasta_md5"]

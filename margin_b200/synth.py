@@ -122,7 +122,18 @@ def make_chunk(seed, contig_len=100000, depth=60, read_len=20000, err=ONT, draft
     for _ in range(n_reads):
         rl = min(read_len, contig_len)
         s = int(rng.integers(0, contig_len - rl + 1))
-        read, rpos = mutate(rng, truth[s:s + rl], **err)
+        if het and rng.random() < 0.5:
+            # a read of the second haplotype: mutate its stretch of hap_b, then carry read positions back to the
+            # truth coordinates of the window through bpos
+            valid = bpos[s:s + rl] >= 0
+            hb = bpos[s:s + rl][valid]
+            if len(hb) < 2:
+                continue
+            read, rpos_b = mutate(rng, hap_b[hb[0]:hb[-1] + 1], **err)
+            rpos = np.full(rl, -1, np.int64)
+            rpos[valid] = rpos_b[hb - hb[0]]
+        else:
+            read, rpos = mutate(rng, truth[s:s + rl], **err)
         fwd = bool(rng.random() < 0.5)
         both = (rpos >= 0) & (dpos[s:s + rl] >= 0)
         ax = dpos[s:s + rl][both]
@@ -200,14 +211,20 @@ def _cigar(ax, ay, read_len):
     return "".join(parts)
 
 
+HET = dict(sub=0.001, ins=0.0001, dele=0.0001, hp_frac=0.6)  # second haplotype of BASELINE configs[4] (SURVEY D-2)
+
+
 def write_polish_dataset(out_dir, seed=42, contig_len=100000, depth=60, read_len=20000, err=ONT, draft_err=0.01,
-                         contig_name="contig_1"):
-    """Writes <out_dir>/draft.fa and <out_dir>/reads.sam; returns (fasta_path, sam_path, n_reads, draft_len)."""
+                         contig_name="contig_1", het=None):
+    """Writes <out_dir>/draft.fa and <out_dir>/reads.sam; returns (fasta_path, sam_path, n_reads, draft_len).
+    ``het`` (e.g. HET): a second haplotype = the truth mutated at these rates; every read is drawn from one of the
+    two haplotypes with probability 1/2 (the diploid workload of `margin polish --diploid`)."""
     import os
     rng = np.random.default_rng(seed)
     truth = rng.integers(0, 4, contig_len).astype(np.uint16)
     d3 = draft_err / 3.0
     draft, dpos = mutate(rng, truth, d3, d3, d3, 0.6)
+    hap_b, bpos = mutate(rng, truth, **het) if het else (None, None)
     n_reads = max(1, int(round(depth * contig_len / float(read_len))))
     recs = []
     for k in range(n_reads):

@@ -1,7 +1,7 @@
 """`margin polish` on a synthetic multi-chunk contig: reference CLI vs the CLI linked against libmargin_b200.so
 (bench.py: time_polish_synth).  Prints one JSON object.
 
-  python scripts/polish_synth.py --kb 500 --threads 16 [--skip-reference] [--seed 42]
+  python scripts/polish_synth.py --kb 500 --threads 16 [--skip-reference] [--seed 42] [--diploid --depth 40]
 """
 import argparse
 import json
@@ -18,5 +18,7 @@ if __name__ == "__main__":
     ap.add_argument("--threads", type=int, default=16)
     ap.add_argument("--seed", type=int, default=42)
     ap.add_argument("--skip-reference", action="store_true")
+    ap.add_argument("--diploid", action="store_true", help="two haplotypes, margin polish --diploid (BASELINE configs[4] shape)")
+    ap.add_argument("--depth", type=int, default=60)
     a = ap.parse_args()
-    print(json.dumps(bench.time_polish_synth(a.kb, min(bench.host_cores(), a.threads), a.seed, a.skip_reference)))
+    print(json.dumps(bench.time_polish_synth(a.kb, min(bench.host_cores(), a.threads), a.seed, a.skip_reference, a.diploid, a.depth)))
