@@ -262,7 +262,7 @@ def time_polish(threads):
     return out
 
 
-def time_polish_synth(contig_kb, threads, seed=42, skip_reference=False, diploid=False, depth=60):
+def time_polish_synth(contig_kb, threads, seed=42, skip_reference=False, diploid=False, depth=60, platform="ont"):
     """End-to-end `margin polish` on a SYNTHETIC contig of BASELINE configs[1]/[2]'s shape (60x ONT-like 20 kb reads at
     ~10 % error, r94-g360 params, 100 kb chunks; margin_b200/synth.py: write_polish_dataset + oracle/_ref/sam2bam):
     the unmodified reference CLI and the CLI linked against this library, -t `threads` each (the reference
@@ -276,15 +276,19 @@ def time_polish_synth(contig_kb, threads, seed=42, skip_reference=False, diploid
     if not (os.path.exists(os.path.join(ref, "margin_b200cli")) and os.path.exists(os.path.join(ref, "sam2bam"))):
         return None
     params = os.path.join(ref, "data", "params", "polish", "ont", "r9.4", "allParams.np.human.r94-g360.json")
+    read_len, err, draft_err, what = 20000, synth.ONT, 0.01, "20 kb ONT-like reads (~10 % error), ont r9.4 g360 params"
+    if platform == "hifi":  # BASELINE configs[3]: 15 kb reads at ~1 % error, pb-hifi params (50 kb chunks, narrow bands)
+        params = os.path.join(ref, "data", "params", "polish", "pacbio", "hifi", "allParams.hifi.json")
+        read_len, err, draft_err, what = 15000, synth.HIFI, 0.001, "15 kb HiFi-like reads (~1 % error), pacbio hifi params"
     with tempfile.TemporaryDirectory() as tmp:
         t0 = time.perf_counter()
-        fa, sam, n_reads, draft_len = synth.write_polish_dataset(tmp, seed, contig_kb * 1000, depth, 20000, synth.ONT, 0.01,
+        fa, sam, n_reads, draft_len = synth.write_polish_dataset(tmp, seed, contig_kb * 1000, depth, read_len, err, draft_err,
                                                                  het=synth.HET if diploid else None)
         bam = os.path.join(tmp, "reads.bam")
         subprocess.run([os.path.join(ref, "sam2bam"), sam, bam], check=True, stderr=subprocess.DEVNULL)
         os.remove(sam)
-        out = {"workload": "synthetic %d kb %scontig, %dx 20 kb ONT-like reads (~10 %% error), ont r9.4 g360 params%s"
-                           % (contig_kb, "diploid " if diploid else "", depth, ", margin polish --diploid" if diploid else ""),
+        out = {"workload": "synthetic %d kb %scontig, %dx %s%s"
+                           % (contig_kb, "diploid " if diploid else "", depth, what, ", margin polish --diploid" if diploid else ""),
                "contig_mb": draft_len / 1e6, "reads": n_reads, "threads": threads, "seed": seed,
                "dataset_s": time.perf_counter() - t0}
         arms = (("b200", "margin_b200cli"),) if skip_reference else (("reference", "margin_ref"), ("b200", "margin_b200cli"))

@@ -20,5 +20,6 @@ if __name__ == "__main__":
     ap.add_argument("--skip-reference", action="store_true")
     ap.add_argument("--diploid", action="store_true", help="two haplotypes, margin polish --diploid (BASELINE configs[4] shape)")
     ap.add_argument("--depth", type=int, default=60)
+    ap.add_argument("--platform", choices=["ont", "hifi"], default="ont", help="hifi: BASELINE configs[3] (use --depth 30)")
     a = ap.parse_args()
-    print(json.dumps(bench.time_polish_synth(a.kb, min(bench.host_cores(), a.threads), a.seed, a.skip_reference, a.diploid, a.depth)))
+    print(json.dumps(bench.time_polish_synth(a.kb, min(bench.host_cores(), a.threads), a.seed, a.skip_reference, a.diploid, a.depth, a.platform)))
