@@ -59,7 +59,7 @@ def test_diploid_polish_with_b200_aligner_is_byte_identical(tmp_path):
     cmd = [os.path.join(REF, "margin_b200cli"), "polish", os.path.join(data, "HG002.r94g360.chr20_59M_100k.bam"),
            os.path.join(data, "hg38.chr20_59M_100k.fa"),
            os.path.join(data, "params", "polish", "ont", "r9.4", "allParams.np.human.r94-g360.json"),
-           "-t", "4", "-o", prefix, "-2", "-a", "info"]
+           "-t", "8", "-o", prefix, "-2", "-a", "info"]
     r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=900)
     assert r.returncode == 0, r.stdout[-3000:]
     batched = [l for l in r.stdout.splitlines() if "margin_b200 bubble graph (phasing)" in l]
