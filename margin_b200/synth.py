@@ -122,18 +122,7 @@ def make_chunk(seed, contig_len=100000, depth=60, read_len=20000, err=ONT, draft
     for _ in range(n_reads):
         rl = min(read_len, contig_len)
         s = int(rng.integers(0, contig_len - rl + 1))
-        if het and rng.random() < 0.5:
-            # a read of the second haplotype: mutate its stretch of hap_b, then carry read positions back to the
-            # truth coordinates of the window through bpos
-            valid = bpos[s:s + rl] >= 0
-            hb = bpos[s:s + rl][valid]
-            if len(hb) < 2:
-                continue
-            read, rpos_b = mutate(rng, hap_b[hb[0]:hb[-1] + 1], **err)
-            rpos = np.full(rl, -1, np.int64)
-            rpos[valid] = rpos_b[hb - hb[0]]
-        else:
-            read, rpos = mutate(rng, truth[s:s + rl], **err)
+        read, rpos = mutate(rng, truth[s:s + rl], **err)
         fwd = bool(rng.random() < 0.5)
         both = (rpos >= 0) & (dpos[s:s + rl] >= 0)
         ax = dpos[s:s + rl][both]
@@ -230,7 +219,18 @@ def write_polish_dataset(out_dir, seed=42, contig_len=100000, depth=60, read_len
     for k in range(n_reads):
         rl = min(read_len, contig_len)
         s = int(rng.integers(0, contig_len - rl + 1))
-        read, rpos = mutate(rng, truth[s:s + rl], **err)
+        if het and rng.random() < 0.5:
+            # a read of the second haplotype: mutate its stretch of hap_b, then carry read positions back to the
+            # truth coordinates of the window through bpos
+            valid = bpos[s:s + rl] >= 0
+            hb = bpos[s:s + rl][valid]
+            if len(hb) < 2:
+                continue
+            read, rpos_b = mutate(rng, hap_b[hb[0]:hb[-1] + 1], **err)
+            rpos = np.full(rl, -1, np.int64)
+            rpos[valid] = rpos_b[hb - hb[0]]
+        else:
+            read, rpos = mutate(rng, truth[s:s + rl], **err)
         fwd = bool(rng.random() < 0.5)
         both = (rpos >= 0) & (dpos[s:s + rl] >= 0)
         ax = dpos[s:s + rl][both]
