@@ -252,9 +252,8 @@ def time_polish(threads):
                 out[key] = {"error": r.stdout[-300:]}
                 continue
             h = hashlib.md5()
-            for name in ([prefix + ".fa.hap1", prefix + ".fa.hap2"] if diploid else [prefix + ".fa"]):
-                with open(name, "rb") as fh:
-                    h.update(fh.read())
+            with open(prefix + ".fa", "rb") as fh:
+                h.update(fh.read())
             md5 = h.hexdigest()
             out[key] = {"wall_s": dt, "mb_per_hour": 0.1 / dt * 3600.0, "fasta_md5": md5}
     if "reference" in out and "b200" in out and "fasta_md5" in out["reference"] and "fasta_md5" in out["b200"]:

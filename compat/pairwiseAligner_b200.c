@@ -117,8 +117,82 @@ static int b200_is_rle(StateMachine *sM) {
            e->emission(e, (Symbol) ((2 << 8) | 0), (Symbol) ((1 << 8) | 0));
 }
 
+/*
+ * Layout self-check.  The two structs above are private to impl/stateMachine.c; if the reference
+ * ever changes them the flattened model would silently be wrong.  So every freshly flattened model is compared with
+ * what the reference's own function pointers say: stateMachine3_cellCalculate (impl/stateMachine.c:562-586) is run
+ * with a recording doTransition callback, which yields the nine transitions and the three emissions it pairs them
+ * with, and emissions->emission / gapEmissionX / gapEmissionY are sampled over all base pairs and a spread of run
+ * lengths.  Values must agree bit for bit (the device forms match + 2.3025 * rsm with the same two operations).
+ */
+typedef struct {
+    double eP[3][3], tP[3][3];
+    int seen[3][3];
+} B200Probe;
+
+static void b200_probe_transition(double *fromCells, double *toCells, int64_t from, int64_t to, double eP, double tP,
+                                  void *extraArgs) {
+    (void) fromCells;
+    (void) toCells;
+    B200Probe *pr = extraArgs;
+    if (from < 0 || from > 2 || to < 0 || to > 2) st_errAbort("margin_b200: state machine with unexpected state numbers\n");
+    pr->eP[from][to] = eP;
+    pr->tP[from][to] = tP;
+    pr->seen[from][to] = 1;
+}
+
+static double b200_flat_emission(const margin_b200_model *m, Symbol cX, Symbol cY) {
+    unsigned xb = m->rle ? (cX & 255u) : cX, yb = m->rle ? (cY & 255u) : cY;
+    double sub = (xb >= 4 || yb >= 4) ? -2.772588722 : m->match[xb * 4 + yb]; /* impl/stateMachine.c:378-383 */
+    if (!m->rle) return sub;
+    unsigned tb = xb >= 4 ? 0 : xb;
+    return sub + 2.3025 * m->rsm[((size_t) tb * MARGIN_B200_MAX_RL + (cX >> 8)) * MARGIN_B200_MAX_RL + (cY >> 8)];
+}
+
+static int b200_same_bits(double a, double b) { return memcmp(&a, &b, sizeof(double)) == 0; }
+
+static void b200_check_flattening(StateMachine *sM, const margin_b200_model *m) {
+    if (sM->matchState != 0 || sM->gapXState != 1 || sM->gapYState != 2 || sM->stateNumber != 3)
+        st_errAbort("margin_b200: state machine is not the 3-state (match, gapX, gapY) machine\n");
+    B200Probe pr;
+    memset(&pr, 0, sizeof(pr));
+    double cells[4][3];
+    memset(cells, 0, sizeof(cells));
+    Symbol cX = (Symbol) ((m->rle ? 3 << 8 : 0) | 1), cY = (Symbol) ((m->rle ? 2 << 8 : 0) | 2);
+    sM->cellCalculate(sM, cells[0], cells[1], cells[2], cells[3], cX, cY, b200_probe_transition, &pr);
+    /* [from][to] in (match, gapX, gapY) order against the MB_T_* slots */
+    static const int slotOf[3][3] = {{MB_T_MATCH_CONTINUE, MB_T_GAP_OPEN_X, MB_T_GAP_OPEN_Y},
+                                     {MB_T_MATCH_FROM_GAP_X, MB_T_GAP_EXTEND_X, MB_T_GAP_SWITCH_TO_Y},
+                                     {MB_T_MATCH_FROM_GAP_Y, MB_T_GAP_SWITCH_TO_X, MB_T_GAP_EXTEND_Y}};
+    Emissions *e = sM->emissions;
+    double want[3] = {e->emission(e, cX, cY), e->gapEmissionX(e, cX), e->gapEmissionY(e, cY)};
+    for (int from = 0; from < 3; from++) {
+        for (int to = 0; to < 3; to++) {
+            if (!pr.seen[from][to] || !b200_same_bits(pr.tP[from][to], m->t[slotOf[from][to]]) ||
+                !b200_same_bits(pr.eP[from][to], want[to]))
+                st_errAbort("margin_b200: StateMachine3 layout check failed for transition %d -> %d "
+                            "(private structs of impl/stateMachine.c changed?)\n", from, to);
+        }
+    }
+    static const int runLengths[6] = {0, 1, 2, 7, 23, 50};
+    for (int xb = 0; xb < 5; xb++) {
+        if (xb < 4 && (!b200_same_bits(e->gapEmissionX(e, (Symbol) xb), m->gap_x[xb]) ||
+                       !b200_same_bits(e->gapEmissionY(e, (Symbol) xb), m->gap_y[xb])))
+            st_errAbort("margin_b200: emission layout check failed for the gap emissions of base %d\n", xb);
+        for (int yb = 0; yb < 5; yb++) {
+            for (int i = 0; i < (m->rle ? 6 : 1); i++) {
+                for (int j = 0; j < (m->rle ? 6 : 1); j++) {
+                    Symbol sx = (Symbol) ((m->rle ? runLengths[i] << 8 : 0) | xb), sy = (Symbol) ((m->rle ? runLengths[j] << 8 : 0) | yb);
+                    if (!b200_same_bits(e->emission(e, sx, sy), b200_flat_emission(m, sx, sy)))
+                        st_errAbort("margin_b200: emission layout check failed for symbols %d / %d "
+                                    "(private structs of impl/stateMachine.c changed?)\n", (int) sx, (int) sy);
+                }
+            }
+        }
+    }
+}
+
 static void b200_load_machine(int slot, StateMachine *sM) {
-    if (tls.sm[slot] == sM) return;
     if (sM->type != threeState && sM->type != threeStateAsymmetric) st_errAbort("margin_b200: unsupported state machine\n");
     B200StateMachine3 *s = (B200StateMachine3 *) sM;
     margin_b200_model *m = &tls.scratch;
@@ -147,6 +221,13 @@ static void b200_load_machine(int slot, StateMachine *sM) {
             memcpy(m->rsm + b * sq, r->logProbabilities + (re->strand ? b : 3 - b) * sq, sizeof(double) * sq);
         }
     }
+    /* The slot is keyed by CONTENT, not by the StateMachine pointer: a machine freed and rebuilt at the same address
+     * (the reference's test suites do that in loops) or modified in place must not keep a stale model on the device. */
+    if (tls.sm[slot] != NULL && memcmp(m, &tls.loaded[slot], sizeof(*m)) == 0) {
+        tls.sm[slot] = sM;
+        return;
+    }
+    b200_check_flattening(sM, m);
     if (margin_b200_set_model(b200_ctx(), slot, m) != 0) b200_fail();
     tls.sm[slot] = sM;
     tls.loaded[slot] = *m;
@@ -679,6 +760,38 @@ static void b200_poa_augment(Poa *poa, RleString *read, bool readStrand, int64_t
     augmentPhase[3] += tPhase4 - tPhase3;
 }
 
+/*
+ * Test hook (oracle/b200_tests.c): b200_poa_augment on the reference's own list representation, so that
+ * tests/polisherTest.c:163-244 (hand-made tuples, golden POA) can be replayed against it.  Lists are
+ * (weight, x, y) stIntTuples: matches, inserts (gapY), deletes (gapX), as poa_augment takes them (impl/poa.c:317).
+ */
+void margin_b200_binding_augment_lists(Poa *poa, RleString *read, bool readStrand, int64_t readNo, stList *matches,
+                                       stList *inserts, stList *deletes, PolishParams *polishParams) {
+    stList *lists[3] = {matches, deletes, inserts}; /* result order: match, gapX = delete, gapY = insert */
+    margin_b200_result res;
+    memset(&res, 0, sizeof(res));
+    margin_b200_pair *pairs[3];
+    int64_t off[3][2];
+    for (int l = 0; l < 3; l++) {
+        int64_t n = stList_length(lists[l]);
+        pairs[l] = st_calloc(n + 1, sizeof(margin_b200_pair));
+        for (int64_t k = 0; k < n; k++) {
+            stIntTuple *t = stList_get(lists[l], k);
+            pairs[l][k].w = (int32_t) stIntTuple_get(t, 0);
+            pairs[l][k].x = (int32_t) stIntTuple_get(t, 1);
+            pairs[l][k].y = (int32_t) stIntTuple_get(t, 2);
+        }
+        off[l][0] = 0;
+        off[l][1] = n;
+        res.pairs[l] = pairs[l];
+        res.off[l] = off[l];
+    }
+    res.n = 1;
+    res.pair_format = MARGIN_B200_PAIRS_TRIPLES;
+    b200_poa_augment(poa, read, readStrand, readNo, &res, 0, 0, polishParams);
+    for (int l = 0; l < 3; l++) free(pairs[l]);
+}
+
 /* ----------------------------------------------------------------------------- impl/poa.c:668-716, batched */
 
 /*
@@ -688,14 +801,19 @@ static void b200_poa_augment(Poa *poa, RleString *read, bool readStrand, int64_t
  * applies each read's three lists to the graph in read order (b200_poa_augment above: matches, inserts <- gapY,
  * deletes <- gapX, x shifted back by the crop).
  */
+static int b200_referenceAugment = -1; /* -1 = not decided yet: MARGIN_B200_REFERENCE_AUGMENT=1 turns it on */
+
 static int b200_reference_augment(void) {
-    static int cached = -1;
-    if (cached < 0) {
+    if (b200_referenceAugment < 0) {
         const char *e = getenv("MARGIN_B200_REFERENCE_AUGMENT");
-        cached = e != NULL && e[0] == '1';
+        b200_referenceAugment = e != NULL && e[0] == '1';
     }
-    return cached;
+    return b200_referenceAugment;
 }
+
+/* A/B hook of the test suite (oracle/b200_tests.c): 1 = apply the lists with the reference's own poa_augment
+ * (impl/poa.c:317-543) on stLists, 0 = with b200_poa_augment on the flat arrays. */
+void margin_b200_binding_set_reference_augment(int on) { b200_referenceAugment = on != 0; }
 
 Poa *poa_realign(stList *bamChunkReads, stList *anchorAlignments, RleString *reference, PolishParams *polishParams) {
     uint64_t maximumRepeatLength = 2; /* MRL is exclusive */
@@ -909,14 +1027,18 @@ double computeForwardProbability(SymbolString sX, SymbolString sY, stList *ancho
 BubbleGraph *bubbleGraph_constructFromPoaAndVCF_reference(Poa *poa, stList *bamChunkReads, stList *vcfEntries,
                                                           PolishParams *params, bool phasing);
 
+static int b200_bubbleBatching = -1;
+
+/* A/B hook of the test suite (oracle/b200_tests.c): 0 = every forward matrix as a GPU batch of one. */
+void margin_b200_binding_set_bubble_batching(int on) { b200_bubbleBatching = on != 0; }
+
 BubbleGraph *bubbleGraph_constructFromPoaAndVCF(Poa *poa, stList *bamChunkReads, stList *vcfEntries, PolishParams *params,
                                                 bool phasing) {
-    static int batching = -1; /* MARGIN_B200_BUBBLE_BATCH=0: every matrix as a batch of one (A/B measurement only) */
-    if (batching < 0) {
+    if (b200_bubbleBatching < 0) { /* MARGIN_B200_BUBBLE_BATCH=0: every matrix as a batch of one (A/B check only) */
         const char *e = getenv("MARGIN_B200_BUBBLE_BATCH");
-        batching = !(e != NULL && e[0] == '0');
+        b200_bubbleBatching = !(e != NULL && e[0] == '0');
     }
-    if (tls.deferred != NULL || !batching) /* nested calls do not occur in the reference; the outer one would patch */
+    if (tls.deferred != NULL || !b200_bubbleBatching) /* nested calls do not occur in the reference; the outer one would patch */
         return bubbleGraph_constructFromPoaAndVCF_reference(poa, bamChunkReads, vcfEntries, params, phasing);
     B200Deferred d;
     memset(&d, 0, sizeof(d));

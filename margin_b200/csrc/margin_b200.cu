@@ -567,7 +567,7 @@ int validate_anchors(const int32_t *anc, int64_t na, int64_t lx, int64_t ly, int
     for (int64_t i = 0; i < na; i++) {
         const int64_t x = anc[3 * i], y = anc[3 * i + 1], e = anc[3 * i + 2];
         if (x <= px || y <= py || x < 0 || y < 0 || x >= lx || y >= ly || e < 0 || (e & 1))
-            return fail("alignment %lld: anchor %lld (%lld,%lld,%lld) is not strictly increasing / in range / even",
+            return fail("PAIRWISE_ALIGNMENT_EXCEPTION: alignment %lld: anchor %lld (%lld,%lld,%lld) is not strictly increasing / in range / even",
                         (long long) aln, (long long) i, (long long) x, (long long) y, (long long) e);
         px = x;
         py = y;
@@ -682,7 +682,7 @@ extern "C" int margin_b200_upload_batch(margin_b200_ctx *c, const margin_b200_ba
         const int64_t lx = b->off_x[i + 1] - b->off_x[i], ly = b->off_y[i + 1] - b->off_y[i];
         const int64_t na = b->off_a[i + 1] - b->off_a[i];
         const int32_t *anc = b->anchors + 3 * b->off_a[i];
-        if (h_status[2 * i] != 0x7fffffff) return validate_anchors(anc, na, lx, ly, i) ? 1 : fail("alignment %lld: bad anchors", (long long) i);
+        if (h_status[2 * i] != 0x7fffffff) return (b->anchors && validate_anchors(anc, na, lx, ly, i)) ? 1 : fail("PAIRWISE_ALIGNMENT_EXCEPTION: alignment %lld: bad anchors", (long long) i);
         const bool rl = b->ragged_left && b->ragged_left[i], rr = b->ragged_right && b->ragged_right[i];
         const uint8_t slot = b->model_slot ? b->model_slot[i] : 0;
         if (h_status[2 * i + 1]) {
