@@ -533,16 +533,22 @@ def roofline(dom, dom_ms, ktimes, cells, st, peaks, al):
     peak_tflops = sms * lanes * 2 * peaks["sm_max_mhz"] * 1e6 * 1e-12
     n_launch = max(ktimes[dom][1], 1) if ktimes else 1
     steps = max(1, n_launch // max(1, al.launches_per_step(dom)))
-    # algorithmic work of one step attributed to the dominant kernel class
+    # algorithmic work of one step attributed to the dominant kernel class.  HBM bytes per SURVEY.md §8 D-4: symbols
+    # ~0.9 B, band descriptor ~2.7 B, output tuples ~2.6 B per band cell (forward state on chip: 0 B).  This design spills
+    # the forward state once in each direction; those bytes are reported as `moved_bytes`, not as algorithmic bytes.
+    f_spill = cells * al.f_bytes_per_cell()
     if dom == "forward":
         flop = cells * FLOP_PER_CELL_PASS
-        bytes_alg = cells * (0.9 + 2.7 + al.f_bytes_per_cell())
+        bytes_alg = cells * (0.9 + 2.7)
+        bytes_moved = bytes_alg + f_spill
     elif dom in ("backward", "fused"):
         flop = cells * ((2.0 if dom == "fused" else 1.0) * FLOP_PER_CELL_PASS + FLOP_PER_POSTERIOR_CELL)
-        bytes_alg = cells * (0.9 + 2.7 + 2.6 + (al.f_bytes_per_cell() if dom == "backward" else 0.0))
+        bytes_alg = cells * (0.9 + 2.7 + 2.6)
+        bytes_moved = bytes_alg + (f_spill if dom == "backward" else 0.0)
     else:
         flop = 0.0
         bytes_alg = cells * 2.6
+        bytes_moved = bytes_alg
     class_ms_step = ktimes[dom][0] / steps if ktimes else 0.0
     ach_tflops = flop / (class_ms_step * 1e-3) * 1e-12 if class_ms_step > 0 else 0.0
     ach_gbs = bytes_alg / (class_ms_step * 1e-3) * 1e-9 if class_ms_step > 0 else 0.0
@@ -554,8 +560,81 @@ def roofline(dom, dom_ms, ktimes, cells, st, peaks, al):
             sms, lanes, peaks["sm_max_mhz"], peaks["source"]),
         "avg_launch_ms": dom_ms, "class_ms_per_step": class_ms_step,
         "hbm": {"achieved": ach_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                "frac": ach_gbs / peaks["hbm_gbs"], "algorithmic_bytes": bytes_alg, "peak_source": peaks["source"]},
+                "frac": ach_gbs / peaks["hbm_gbs"], "algorithmic_bytes": bytes_alg, "moved_bytes": bytes_moved,
+                "moved_gbs": bytes_moved / (class_ms_step * 1e-3) * 1e-9 if class_ms_step > 0 else 0.0,
+                "f_spill_bytes_per_cell": al.f_bytes_per_cell(), "peak_source": peaks["source"]},
     }
+
+
+def main_replay(args):
+    """`--workload c1_replay`: every posterior batch `margin polish` sends to the library on the bundled ONT region
+    (BASELINE configs[0]: round 1 with BAM-CIGAR anchors, round 2 with posterior anchors and per-anchor expansions, the
+    stitcher's overlap alignment), dumped by the binding and replayed with inputs resident and through the host call.
+    Reports GCUPS per batch, the share of band cells on the wide-tile and sequential paths, and the seam guard counts:
+    what real data, unlike the synthetic chunk, does to the tiling."""
+    import tempfile
+    import torch
+    from margin_b200 import abi, replay
+    from margin_b200.aligner import PairHmmAligner
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+    ref = os.path.join(ROOT, "oracle", "_ref")
+    if not os.path.exists(os.path.join(ref, "margin_b200cli")):
+        print(json.dumps({"workload": "c1_replay", "unavailable": "oracle/_ref/margin_b200cli not built"}))
+        return 0
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(0)
+    flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
+    rows, tot_cells, tot_ms, tot_e2e = [], 0, 0.0, 0.0
+    launches = 0
+    with tempfile.TemporaryDirectory() as tmp:
+        t0 = time.perf_counter()
+        dumps = replay.dump_bundled_region(os.path.join(tmp, "d"), ref)
+        cli_s = time.perf_counter() - t0
+        for path in dumps:
+            items, models, params, want = replay.load_dump(path)
+            batch = abi.Batch(items, compact=True)
+            al = PairHmmAligner(models, params, device=0)
+            al.set_pair_format(abi.PAIRS_PACKED64)
+            al.upload(batch)
+            for _ in range(args.warmup):
+                st = al.posteriors_resident(bool(want))
+            ms = 0.0
+            for _ in range(args.steps):
+                flush.zero_()
+                torch.cuda.synchronize(dev)
+                st = al.posteriors_resident(bool(want))
+                ms += st["gpu_ms"]
+                launches += st["kernel_launches"]
+            ms /= args.steps
+            al.posteriors_host(batch, bool(want))
+            t0 = time.perf_counter()
+            for _ in range(args.steps):
+                al.posteriors_host(batch, bool(want))
+            e2e_ms = (time.perf_counter() - t0) / args.steps * 1e3
+            al.close()
+            cells = int(st["band_cells"])
+            lens = [len(it[1]) for it in items]
+            rows.append({"batch": os.path.basename(path), "alignments": len(items), "want_indels": int(want),
+                         "read_len_max": int(max(lens)) if lens else 0, "band_cells": cells, "tiles": int(st["tiles"]),
+                         "wide_cell_share": st["wide_cells"] / max(cells, 1),
+                         "sequential_cell_share": st["sequential_cells"] / max(cells, 1),
+                         "guard_seams": int(st["guard_seams"]), "guard_failures": int(st["guard_failures"]),
+                         "ms_resident": ms, "gcups_resident": 2.0 * cells / (ms * 1e-3) * 1e-9 if ms > 0 else 0.0,
+                         "ms_host_call": e2e_ms, "gcups_host_call": 2.0 * cells / (e2e_ms * 1e-3) * 1e-9})
+            tot_cells += cells
+            tot_ms += ms
+            tot_e2e += e2e_ms
+    line = {"metric": METRIC, "value": 2.0 * tot_cells / (tot_ms * 1e-3) * 1e-9 if tot_ms else 0.0, "unit": UNIT, "n_gpus": 1,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": tot_ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "real (bundled HG002 chr20 100 kb region, batches dumped from margin polish)",
+            "config": {"workload": "c1_replay", "batches": len(rows), "band_cells": tot_cells, "l2": "flushed between steps",
+                       "margin_polish_wall_s": cli_s},
+            "e2e": {"value": 2.0 * tot_cells / (tot_e2e * 1e-3) * 1e-9 if tot_e2e else 0.0, "unit": UNIT,
+                    "mode": "one host thread, one call per batch, pageable numpy buffers"},
+            "gpu_launches": launches, "replay": rows}
+    print(json.dumps(line), flush=True)
+    return 0
 
 
 def main():
@@ -582,6 +661,8 @@ def main():
     args = ap.parse_args()
     if args.impl == "reference":
         return main_reference(args)
+    if args.workload == "c1_replay":
+        return main_replay(args)
     return main_ours(args)
 
 

@@ -150,6 +150,15 @@ typedef struct margin_b200_result {
     int64_t tiles;           /* independent forward/backward work units the segments were cut into */
     int32_t pair_format;     /* MARGIN_B200_PAIRS_*: with PACKED64, pairs[l] points at uint64_t words */
     int32_t reserved;
+    /* where the band cells went: lane-group tile kernels (the rest), the general tile path for tiles with a diagonal
+     * wider than 32 cells, or a sequential sweep of the whole job (degenerate matrices, MARGIN_B200_MODE=sequential,
+     * jobs re-run after a failed seam) */
+    int64_t wide_cells;
+    int64_t sequential_cells;
+    /* seam guard: tile edges whose independently computed copies of F / B were compared, and how many of them differed
+     * by more than the tolerance (their jobs were re-run sequentially inside the call, so results are unaffected) */
+    int32_t guard_seams;
+    int32_t guard_failures;
 } margin_b200_result;
 
 typedef struct margin_b200_ctx margin_b200_ctx;
@@ -200,8 +209,8 @@ int margin_b200_forward_resident(margin_b200_ctx *ctx, margin_b200_result *stats
 
 /* Device time of the last *_resident / *_batch call split by kernel class (CUDA events recorded on the
  * context's stream around every launch): ms[k] = summed duration, launches[k] = number of launches.
- * Classes, in order: band, schedule, forward, backward, scan, gather, offsets, final. */
-#define MARGIN_B200_KERNEL_CLASSES 8
+ * Classes, in order: band, schedule, forward, backward, scan, gather, offsets, final, guard. */
+#define MARGIN_B200_KERNEL_CLASSES 9
 int margin_b200_last_kernel_ms(margin_b200_ctx *ctx, float *ms, int32_t *launches, int n_class);
 
 /* Band geometry only (band_constructDynamic / band_construct): for alignment i

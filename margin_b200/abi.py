@@ -121,6 +121,10 @@ class ResultStruct(C.Structure):
         ("tiles", C.c_int64),
         ("pair_format", C.c_int32),
         ("reserved", C.c_int32),
+        ("wide_cells", C.c_int64),
+        ("sequential_cells", C.c_int64),
+        ("guard_seams", C.c_int32),
+        ("guard_failures", C.c_int32),
     ]
 
 
@@ -241,4 +245,4 @@ EXPORTED_SYMBOLS = [
     "margin_b200_last_kernel_ms", "margin_b200_device_count", "margin_b200_prewarm",
 ]
 
-KERNEL_CLASSES = ["band", "schedule", "forward", "backward", "scan", "gather", "offsets", "final"]
+KERNEL_CLASSES = ["band", "schedule", "forward", "backward", "scan", "gather", "offsets", "final", "guard"]

@@ -37,7 +37,8 @@ class BatchResult:
 
 def _stats(res):
     return dict(band_cells=res.band_cells, diagonals=res.diagonals, jobs=res.jobs, segments=res.segments,
-                gpu_ms=res.gpu_ms, kernel_launches=res.kernel_launches, tiles=res.tiles)
+                gpu_ms=res.gpu_ms, kernel_launches=res.kernel_launches, tiles=res.tiles, wide_cells=res.wide_cells,
+                sequential_cells=res.sequential_cells, guard_seams=res.guard_seams, guard_failures=res.guard_failures)
 
 
 class PairHmmAligner:

@@ -168,7 +168,19 @@ struct margin_b200_ctx {
     bool have_switch = false;
     DevBuf d_symx, d_symy, d_anchors, d_jobs, d_kl, d_kr, d_cell_off, d_job_cells, d_job_maxw, d_job_nseg, d_err;
     DevBuf d_segs, d_seg_counts, d_seg_off, d_scan_tmp, d_slot_ring_off, d_ring, d_ids, d_aln_first_slot;
-    DevBuf d_F, d_stage, d_out, d_off_out, d_fwd_out;
+    DevBuf d_F, d_Fpriv, d_stage, d_out, d_off_out, d_fwd_out;
+    // per-tile classification and the seam guard (build_tiles, guard_check_kernel)
+    std::vector<uint32_t> chunk_base;    // first cell of every band chunk inside its job
+    std::vector<int32_t> chunk_maxw;     // widest diagonal of every band chunk
+    std::vector<int32_t> tile_maxw;      // widest diagonal of [f0, D] per tile (to chunk granularity)
+    std::vector<uint8_t> job_force_seq;  // jobs a failed seam sent to the sequential sweep
+    std::vector<mb::Seam> seams;
+    mb::Seam *p_seams = nullptr;
+    int32_t *p_guard_flags = nullptr;
+    bool guard_on = true;                // MARGIN_B200_GUARD=0 turns the seam guard off
+    double guard_tol = 1e-9, guard_floor = 100.0;
+    int64_t wide_cells = 0, seq_cells = 0, priv_cells = 0, stage_cells = 0;
+    int guard_failures = 0, guard_reruns = 0;
     PinBuf h_stage_in, h_small, h_out, h_off, h_gaps;
     // anchor-free stretches reported by the band kernel (sorted by job, start); see build_tiles
     std::vector<mb::AnchorGap> gaps;
@@ -190,7 +202,7 @@ struct margin_b200_ctx {
 
 namespace {
 
-enum { K_BAND = 0, K_SCHEDULE, K_FORWARD, K_BACKWARD, K_SCAN, K_GATHER, K_OFFSETS, K_FINAL, K_NCLASS };
+enum { K_BAND = 0, K_SCHEDULE, K_FORWARD, K_BACKWARD, K_SCAN, K_GATHER, K_OFFSETS, K_FINAL, K_GUARD, K_NCLASS };
 
 // Records an event pair around one launch; the pairs are resolved by margin_b200_last_kernel_ms.
 struct KTimer {
@@ -321,7 +333,7 @@ int margin_b200_prewarm(void) {
         if (cudaSetDevice(d) != cudaSuccess || cudaFree(nullptr) != cudaSuccess) continue;
         // forces the kernel images in (lazy module loading would otherwise do it inside the first batch)
         cudaFuncAttributes fa;
-        cudaFuncGetAttributes(&fa, mb::backward_tile_kernel<8, kTileThreads, true, false>);
+        cudaFuncGetAttributes(&fa, mb::backward_tile_kernel<8, kTileThreads, true, false, true>);
         cudaFuncGetAttributes(&fa, mb::forward_tile_kernel<8, kTileThreads, false>);
         cudaFuncGetAttributes(&fa, mb::tiny_forward_kernel<16, kTileThreads, false>);
     }
@@ -356,12 +368,14 @@ int margin_b200_create(margin_b200_ctx **out, int device) {
         // lane groups of 8 the backward tile kernel keeps resident: occupancy x SMs x groups per CTA
         int sms = 0, per_sm = 0;
         CU(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
-        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, mb::backward_tile_kernel<8, kTileThreads, true, false>,
+        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, mb::backward_tile_kernel<8, kTileThreads, true, false, true>,
                                                          kTileThreads, 0));
         c->bwd_slots = sms * per_sm * (kTileThreads / 8);
     }
     if (const char *e = getenv("MARGIN_B200_WARMUP")) c->warmup = std::max(1, atoi(e));
     if (const char *e = getenv("MARGIN_B200_GAP_MIN")) c->gap_min = std::max(1, atoi(e));
+    if (const char *e = getenv("MARGIN_B200_GUARD")) c->guard_on = atoi(e) != 0;
+    if (const char *e = getenv("MARGIN_B200_GUARD_TOL")) c->guard_tol = atof(e);
     c->counted = true;
     g_live_contexts[device & (kMaxDevices - 1)].fetch_add(1);
     *out = c;
@@ -378,7 +392,7 @@ void margin_b200_destroy(margin_b200_ctx *c) {
     DevBuf *bufs[] = {&c->d_models, &c->d_rsm[0], &c->d_rsm[1], &c->d_symx, &c->d_symy, &c->d_anchors, &c->d_jobs,
                       &c->d_kl, &c->d_kr, &c->d_cell_off, &c->d_job_cells, &c->d_job_maxw, &c->d_job_nseg, &c->d_err,
                       &c->d_segs, &c->d_seg_counts, &c->d_seg_off, &c->d_scan_tmp, &c->d_slot_ring_off, &c->d_ring,
-                      &c->d_ids, &c->d_aln_first_slot, &c->d_F, &c->d_stage, &c->d_out, &c->d_off_out, &c->d_fwd_out,
+                      &c->d_ids, &c->d_aln_first_slot, &c->d_F, &c->d_Fpriv, &c->d_stage, &c->d_out, &c->d_off_out, &c->d_fwd_out,
                       &c->d_geo, &c->d_tiles, &c->d_bnd, &c->d_slot_bnd_off, &c->d_emit5[0], &c->d_emit5[1],
                       &c->d_px, &c->d_py, &c->d_stage2, &c->d_chunks, &c->d_job_first_chunk, &c->d_chunk_sum, &c->d_chunk_maxw,
                       &c->d_totals, &c->d_band_out, &c->d_anchors_delta, &c->d_sym_err, &c->d_tiny_ids, &c->d_chunks_fwd, &c->d_job_first_chunk_fwd, &c->d_arena, &c->d_offs, &c->d_status};
@@ -830,7 +844,10 @@ int run_band(margin_b200_ctx *c, bool dynamic, bool with_schedule, bool want_kr)
         c->d_chunk_sum.ensure((nc + 1) * sizeof(uint32_t)) || c->d_chunk_maxw.ensure((nc + 1) * sizeof(int32_t)))
         return 1;
     if (want_kr && c->d_kr.ensure((c->total_diag + 1) * sizeof(int32_t))) return 1;
-    if (c->h_small.ensure(o_end)) return 1;
+    // per-chunk cell bases and widest diagonals come back too: build_tiles classifies every tile by its own widest diagonal
+    const size_t o_cbase = (o_end + 15) / 16 * 16, o_cmaxw = o_cbase + ((size_t) nc * 4 + 15) / 16 * 16,
+                 o_all = o_cmaxw + (size_t) nc * 4;
+    if (c->h_small.ensure(with_schedule ? o_all : o_end)) return 1;
     char *h = c->h_small.as<char>();
     char *dv = c->d_band_out.as<char>();
     int64_t *d_totals = reinterpret_cast<int64_t *>(dv), *d_job_cells = reinterpret_cast<int64_t *>(dv + o_cells);
@@ -866,8 +883,17 @@ int run_band(margin_b200_ctx *c, bool dynamic, bool with_schedule, bool want_kr)
         }
     }
     if (ctl_copy(c->stream, h, dv, (o_end + 3) / 4 * 4)) return 1;
+    if (with_schedule && nc > 0 && nj > 0) {
+        if (ctl_copy(c->stream, h + o_cbase, c->d_chunk_sum.p, (size_t) nc * 4) ||
+            ctl_copy(c->stream, h + o_cmaxw, c->d_chunk_maxw.p, (size_t) nc * 4))
+            return 1;
+    }
     CU(cudaStreamSynchronize(c->stream));
     CU(cudaGetLastError());
+    if (with_schedule) {
+        c->chunk_base.assign(reinterpret_cast<uint32_t *>(h + o_cbase), reinterpret_cast<uint32_t *>(h + o_cbase) + (nj > 0 ? nc : 0));
+        c->chunk_maxw.assign(reinterpret_cast<int32_t *>(h + o_cmaxw), reinterpret_cast<int32_t *>(h + o_cmaxw) + (nj > 0 ? nc : 0));
+    }
     if (*reinterpret_cast<int *>(h + o_err))
         return fail("PAIRWISE_ALIGNMENT_EXCEPTION: Attempt to create diagonal with invalid coordinates "
                     "(anchors inconsistent with the sequence lengths)");
@@ -913,13 +939,34 @@ int run_band(margin_b200_ctx *c, bool dynamic, bool with_schedule, bool want_kr)
     return 0;
 }
 
-// A job runs on the tiled kernels when its widest diagonal fits a lane group and both sequences are non-empty;
-// anything else (very wide bands, e.g. alignments without anchors; degenerate one-row matrices) takes the
-// sequential per-alignment sweep.
+// A job is cut into tiles when both sequences are non-empty; degenerate one-row matrices, MARGIN_B200_MODE=sequential,
+// an overflowing anchor-gap table and jobs a failed seam guard sent back (job_force_seq) take the sequential
+// per-alignment sweep.  How a tile runs (lane-group width, or the general wide path) is decided per TILE, from the widest
+// diagonal of the tile's own range: one wide spot in a 70 k-symbol read costs one tile, not the read.
 bool job_is_tiled(const margin_b200_ctx *c, int j) {
     if (c->mode_sequential || c->gaps_overflow) return false;
+    if (j < (int) c->job_force_seq.size() && c->job_force_seq[j]) return false;
     const mb::Job &job = c->jobs[j];
-    return c->job_maxw[j] <= (c->force_group ? c->force_group : 32) && job.lx >= 1 && job.ly >= 1;
+    return job.lx >= 1 && job.ly >= 1;
+}
+
+// Widest diagonal among d_lo .. d_hi of job j, to the granularity of the band chunks (an upper bound).
+int range_maxw(const margin_b200_ctx *c, int j, int d_lo, int d_hi) {
+    const int c0 = c->job_first_chunk[j], c1 = c->job_first_chunk[j + 1];
+    if (c1 <= c0 || c->chunk_maxw.empty()) return c->job_maxw[j];
+    const int k0 = std::min(c1 - 1, c0 + std::max(d_lo, 0) / mb::BAND_CHUNK), k1 = std::min(c1 - 1, c0 + std::max(d_hi, 0) / mb::BAND_CHUNK);
+    int mw = 0;
+    for (int k = k0; k <= k1; k++) mw = std::max(mw, c->chunk_maxw[k]);
+    return mw;
+}
+
+// Upper bound of the band cells on diagonals d_lo .. d_hi of job j: the cells of the band chunks they touch.
+int64_t range_cells_bound(const margin_b200_ctx *c, int j, int d_lo, int d_hi) {
+    const int c0 = c->job_first_chunk[j], c1 = c->job_first_chunk[j + 1];
+    if (c1 <= c0 || c->chunk_base.empty()) return c->job_cells[j];
+    const int k0 = std::min(c1 - 1, c0 + std::max(d_lo, 0) / mb::BAND_CHUNK), k1 = std::min(c1 - 1, c0 + std::max(d_hi, 0) / mb::BAND_CHUNK);
+    const int64_t hi = k1 + 1 < c1 ? (int64_t) c->chunk_base[k1 + 1] : c->job_cells[j];
+    return hi - (int64_t) c->chunk_base[k0];
 }
 
 // Cuts every traceback segment into tiles (see pairhmm_tiles.cuh) and lays the tiles out in the order of the
@@ -1003,14 +1050,42 @@ inline int warmup_end_above(const mb::AnchorGap *g, int ng, int at, int W, int l
     return std::min(limit, pos + need);
 }
 
-void build_tiles(margin_b200_ctx *c) {
+// Tile edges of one traceback segment, from tb_from downwards in steps of L (multiples of 10 below tb_from, so that
+// every tile's top diagonal is one of the reference's total-probability samples).  An edge never lands inside an
+// anchor-free stretch: it moves down to the stretch's start, so a long stretch (whose warm-ups would each have to
+// cross all of it) belongs to ONE tile, and an alignment without anchors is one tile per traceback.
+void cut_segment(const mb::AnchorGap *g, int ng, int tb_to, int tb_from, int L, std::vector<int32_t> &edges) {
+    edges.clear();
+    edges.push_back(tb_from);
+    int cur = tb_from;
+    while (cur - tb_to > L) {
+        int b = cur - L;
+        for (int k = 0; k < ng; k++) {
+            if (g[k].lo < b && b < g[k].hi) {
+                b = cur - (cur - g[k].lo + 9) / 10 * 10;
+                break;
+            }
+        }
+        if (b - tb_to < L / 4) break;  // a short remainder is merged into this tile
+        edges.push_back(b);
+        cur = b;
+    }
+    edges.push_back(tb_to);
+}
+
+void build_tiles(margin_b200_ctx *c, int L) {
     const int nj = (int) c->jobs.size();
-    const int L = pick_tile_len(c), W = c->warmup;
+    const int W = c->warmup;
+    const int gmax = c->force_group ? c->force_group : 32;  // widest diagonal the lane-group tile kernels take
     size_t gap_at = 0;  // c->gaps is sorted by job and jobs are visited in ascending order
     c->tile_len_used = L;
     c->tiles.clear();
+    c->tile_maxw.clear();
+    c->seams.clear();
     c->job_first_tile.assign(nj + 1, 0);
-    int64_t a = 0;
+    c->wide_cells = c->seq_cells = c->priv_cells = c->stage_cells = 0;
+    std::vector<int32_t> edges;
+    std::vector<std::pair<int32_t, int32_t>> blocks;  // [first, last) tile of every segment of the current job
     for (int64_t i = 0; i < c->n_aln; i++) {
         c->aln_first_slot[i] = (int32_t) c->tiles.size();
         for (int j = c->aln_first_job[i]; j < c->aln_first_job[i + 1]; j++) {
@@ -1022,25 +1097,73 @@ void build_tiles(margin_b200_ctx *c) {
             while (gap_end < c->gaps.size() && c->gaps[gap_end].job == j) gap_end++;
             const mb::AnchorGap *g = c->gaps.data() + gap_at;
             const int ng = (int) (gap_end - gap_at);
+            if (!tiled) c->seq_cells += c->job_cells[j];
+            blocks.clear();
             for (int s = c->job_nseg[j] - 1; s >= 0; s--) {
                 const mb::Seg &sg = c->segs[job.seg_base + s];
-                const int span = sg.tb_from - sg.tb_to;
-                const int nt = tiled ? tiles_of_span(span, L) : 1;
-                for (int k = nt - 1; k >= 0; k--) {  // lowest diagonals first
+                const int32_t first = (int32_t) c->tiles.size();
+                if (!tiled) {
                     mb::Tile t;
                     t.job = j;
-                    t.tb_from = sg.tb_from - k * L;
-                    t.tb_to = (k == nt - 1) ? sg.tb_to : t.tb_from - L;
-                    t.D = (k == 0) ? sg.D : warmup_end_above(g, ng, t.tb_from, W, sg.D);
-                    t.f0 = tiled ? warmup_start_below(g, ng, t.tb_to, W) : 0;
-                    t.flags = ((t.D == sg.D && sg.at_end) ? mb::TILE_AT_END : 0) | (tiled ? mb::TILE_BND : 0);
+                    t.tb_from = sg.tb_from;
+                    t.tb_to = sg.tb_to;
+                    t.D = sg.D;
+                    t.f0 = 0;
+                    t.flags = sg.at_end ? mb::TILE_AT_END : 0;
+                    t.priv_off = -1;
+                    t.stage_off = c->stage_cells;
+                    c->stage_cells += range_cells_bound(c, j, t.tb_to + 1, t.tb_from);
                     c->tiles.push_back(t);
+                    c->tile_maxw.push_back(c->job_maxw[j]);
+                    continue;
+                }
+                cut_segment(g, ng, sg.tb_to, sg.tb_from, L, edges);
+                for (int k = (int) edges.size() - 2; k >= 0; k--) {  // lowest diagonals first
+                    mb::Tile t;
+                    t.job = j;
+                    t.tb_from = edges[k];
+                    t.tb_to = edges[k + 1];
+                    t.D = (k == 0) ? sg.D : warmup_end_above(g, ng, t.tb_from, W, sg.D);
+                    t.f0 = warmup_start_below(g, ng, t.tb_to, W);
+                    const int mw = range_maxw(c, j, t.f0, t.D + 1);
+                    const bool wide = mw > gmax;
+                    t.flags = ((t.D == sg.D && sg.at_end) ? mb::TILE_AT_END : 0) | (wide ? mb::TILE_WIDE : mb::TILE_BND);
+                    t.priv_off = -1;
+                    t.stage_off = 0;
+                    if (wide) {
+                        t.priv_off = c->priv_cells;
+                        c->priv_cells += range_cells_bound(c, j, t.f0, t.tb_from);
+                        t.stage_off = c->stage_cells;
+                        const int64_t own = range_cells_bound(c, j, t.tb_to + 1, t.tb_from);
+                        c->stage_cells += own;
+                        c->wide_cells += own;
+                    }
+                    c->tiles.push_back(t);
+                    c->tile_maxw.push_back(mw);
+                }
+                blocks.emplace_back(first, (int32_t) c->tiles.size());
+            }
+            // seams of the job, walking its tiles from the lowest diagonals up: blocks hold later tracebacks first
+            if (tiled && c->guard_on) {
+                int32_t prev = -1;
+                bool prev_same_segment = false;
+                for (int bi = (int) blocks.size() - 1; bi >= 0; bi--) {
+                    for (int32_t u = blocks[bi].first; u < blocks[bi].second; u++) {
+                        if (prev >= 0) {
+                            const mb::Tile &lo = c->tiles[prev], &up = c->tiles[u];
+                            if (up.f0 > 0) c->seams.push_back(mb::Seam{prev, u, up.tb_to, 0});
+                            // inside a traceback the lower tile's backward sweep is warmed up through the upper tile's range
+                            if (prev_same_segment && lo.D > lo.tb_from + 1 && lo.D < c->segs[job.seg_base + ((int) blocks.size() - 1 - bi)].D)
+                                c->seams.push_back(mb::Seam{prev, u, lo.tb_from + 1, 1});
+                        }
+                        prev = u;
+                        prev_same_segment = true;
+                    }
+                    prev_same_segment = false;
                 }
             }
         }
-        a++;
     }
-    (void) a;
     c->aln_first_slot[c->n_aln] = (int32_t) c->tiles.size();
     c->job_first_tile[nj] = (int32_t) c->tiles.size();
     c->total_slots = (int) c->tiles.size();
@@ -1084,8 +1207,8 @@ void sort_keys(std::vector<uint64_t> &k, std::vector<uint64_t> &tmp, std::vector
 int build_bins(margin_b200_ctx *c, bool with_slots, Bins &bins, int force_group) {
     const int nj = (int) c->jobs.size();
     const int S = with_slots ? c->total_slots : 0;
-    auto gbin = [&](int j) {
-        const int g = force_group ? force_group : group_of(c->job_maxw[j]);
+    auto bin_of = [&](int maxw) {
+        const int g = force_group ? force_group : group_of(maxw);
         return g == 8 ? 0 : (g == 16 ? 1 : 2);
     };
     // sort keys: (lane-group bin ascending, work descending, id ascending) packed into one integer
@@ -1097,38 +1220,47 @@ int build_bins(margin_b200_ctx *c, bool with_slots, Bins &bins, int force_group)
     k1.clear();
     k2.clear();
     k3.clear();
+    // general forward sweeps: whole jobs (id = job) ...
     for (int j = 0; j < nj; j++)
         if ((!with_slots || !job_is_tiled(c, j)) && !(!with_slots && j < (int) c->tiny_mask.size() && c->tiny_mask[j]))
-            k0.push_back(key(gbin(j), c->jobs[j].lx + c->jobs[j].ly, j));
+            k0.push_back(key(bin_of(c->job_maxw[j]), c->jobs[j].lx + c->jobs[j].ly, j));
     int64_t ring_cells = 0, bnd_cells = 0;
-    // arena layout (16-byte aligned sections): tiles | ring_off | bnd_off | aln_first_slot | ids
+    const int n_seams = with_slots ? (int) c->seams.size() : 0;
+    // arena layout (16-byte aligned sections): tiles | ring_off | bnd_off | aln_first_slot | seams | guard flags | ids
     const size_t o_tiles = 0, o_ring = o_tiles + (((size_t) S + 1) * sizeof(mb::Tile) + 15) / 16 * 16,
-                 o_bnd = o_ring + ((size_t) S + 1) * 8, o_first = o_bnd + ((size_t) S + 1) * 8,
-                 o_ids = o_first + (((size_t) c->n_aln + 1) * 4 + 15) / 16 * 16,
-                 o_end = o_ids + ((size_t) nj + 2 * (size_t) S + 4) * 4;
+                 o_bnd = o_ring + ((size_t) S + 2) * 8, o_first = o_bnd + ((size_t) S + 2) * 8,
+                 o_seams = o_first + (((size_t) c->n_aln + 1) * 4 + 15) / 16 * 16,
+                 o_flags = o_seams + ((size_t) n_seams + 1) * sizeof(mb::Seam),
+                 o_ids = o_flags + (((size_t) n_seams + 4) * 4 + 15) / 16 * 16,
+                 o_end = o_ids + ((size_t) nj + 4 * (size_t) S + 4) * 4;
+    static_assert(sizeof(mb::Seam) == 16 && sizeof(mb::Tile) % 8 == 0, "arena sections stay aligned");
     if (c->h_arena.ensure(o_end) || c->d_arena.ensure(o_end)) return 1;
     char *h = c->h_arena.as<char>();
     int64_t *ring_off = reinterpret_cast<int64_t *>(h + o_ring), *bnd_off = reinterpret_cast<int64_t *>(h + o_bnd);
     if (with_slots) {
         for (int s = 0; s < S; s++) {
             const mb::Tile &t = c->tiles[s];
-            const int b = gbin(t.job);
+            const int mw = c->tile_maxw[s];
+            // every tile owns three boundary sections of its widest diagonal (mb::BND_*)
+            bnd_off[s] = bnd_cells;
+            bnd_cells += 3 * (int64_t) std::max(mw, 1);
+            ring_off[s] = 0;
             if (t.flags & mb::TILE_BND) {
-                k1.push_back(key(b, t.tb_from - t.f0, s));
-                k3.push_back(key(b, t.D - t.tb_to, s));
-                bnd_off[s] = bnd_cells;
-                ring_off[s] = 0;
-                bnd_cells += c->jobs[t.job].ring_w;
+                k1.push_back(key(bin_of(mw), t.tb_from - t.f0, s));
+                k3.push_back(key(bin_of(mw), t.D - t.tb_to, s));
             } else {
-                k2.push_back(key(b, t.D - t.tb_to, s));
+                if (t.flags & mb::TILE_WIDE) k0.push_back(key(bin_of(mw), t.tb_from - t.f0, ~s));  // ... and wide tiles (id = ~slot)
+                k2.push_back(key(bin_of(mw), t.D - t.tb_to, s));
                 ring_off[s] = ring_cells;
-                bnd_off[s] = 0;
                 ring_cells += 3 * (int64_t) c->jobs[t.job].ring_w;
             }
         }
-        ring_off[S] = bnd_off[S] = 0;
+        ring_off[S] = 0;
+        bnd_off[S] = bnd_cells;
         if (S) memcpy(h + o_tiles, c->tiles.data(), (size_t) S * sizeof(mb::Tile));
         memcpy(h + o_first, c->aln_first_slot.data(), ((size_t) c->n_aln + 1) * 4);
+        if (n_seams) memcpy(h + o_seams, c->seams.data(), (size_t) n_seams * sizeof(mb::Seam));
+        memset(h + o_flags, 0, ((size_t) n_seams + 4) * 4);
     }
     int32_t *ids = reinterpret_cast<int32_t *>(h + o_ids);
     int n_ids = 0;
@@ -1155,6 +1287,8 @@ int build_bins(margin_b200_ctx *c, bool with_slots, Bins &bins, int force_group)
     c->p_ring_off = reinterpret_cast<int64_t *>(dv + o_ring);
     c->p_bnd_off = reinterpret_cast<int64_t *>(dv + o_bnd);
     c->p_aln_first_slot = reinterpret_cast<int32_t *>(dv + o_first);
+    c->p_seams = reinterpret_cast<mb::Seam *>(dv + o_seams);
+    c->p_guard_flags = reinterpret_cast<int32_t *>(dv + o_flags);
     c->p_ids = reinterpret_cast<int32_t *>(dv + o_ids);
     if (with_slots) {
         if (c->d_ring.ensure((size_t) (ring_cells + 1) * 3 * sizeof(double)) ||
@@ -1190,9 +1324,9 @@ void launch_forward(margin_b200_ctx *c, int off, int count) {
     const int per_block = kFwdThreads / G;
     KTimer kt_(c, K_FORWARD);
     mb::forward_kernel<G, kFwdThreads><<<(count + per_block - 1) / per_block, kFwdThreads, 0, c->stream>>>(
-        c->d_jobs.as<mb::Job>(), c->p_ids + off, count, c->d_models.as<mb::DevModel>(),
+        c->d_jobs.as<mb::Job>(), c->p_tiles, c->p_ids + off, count, c->d_models.as<mb::DevModel>(),
         c->d_symx.as<uint16_t>(), c->d_symy.as<uint16_t>(), c->d_kl.as<int32_t>(), c->d_cell_off.as<uint32_t>(),
-        c->d_F.as<double>());
+        c->d_F.as<double>(), c->d_Fpriv.as<double>());
     c->launches++;
 }
 
@@ -1222,17 +1356,17 @@ void launch_backward(margin_b200_ctx *c, int off, int count, int64_t stage_strid
     mb::backward_kernel<G, kBwdThreads, INDELS><<<(count + per_block - 1) / per_block, kBwdThreads, 0, c->stream>>>(
         c->d_jobs.as<mb::Job>(), c->p_tiles, c->p_ids + off, count,
         c->d_models.as<mb::DevModel>(), c->d_symx.as<uint16_t>(), c->d_symy.as<uint16_t>(), c->d_kl.as<int32_t>(),
-        c->d_cell_off.as<uint32_t>(), c->d_F.as<double>(), dev_params(c->params), c->d_ring.as<double>(),
-        c->p_ring_off, c->d_stage.as<mb::Pair>(), stage_stride, c->d_seg_counts.as<int64_t>(),
-        c->total_slots);
+        c->d_cell_off.as<uint32_t>(), c->d_F.as<double>(), c->d_Fpriv.as<double>(), dev_params(c->params),
+        c->d_ring.as<double>(), c->p_ring_off, c->d_stage.as<mb::Pair>(), stage_stride, c->d_seg_counts.as<int64_t>(),
+        c->total_slots, c->d_bnd.as<double>(), c->p_bnd_off);
     c->launches++;
 }
 
-template <int G, bool INDELS, bool SW>
-void launch_backward_tiles2(margin_b200_ctx *c, int off, int count, int64_t stage_stride) {
+template <int G, bool INDELS, bool SW, bool GUARD>
+void launch_backward_tiles3(margin_b200_ctx *c, int off, int count, int64_t stage_stride) {
     const int per_block = kTileThreads / G;
     KTimer kt_(c, K_BACKWARD);
-    mb::backward_tile_kernel<G, kTileThreads, INDELS, SW><<<(count + per_block - 1) / per_block, kTileThreads, 0, c->stream>>>(
+    mb::backward_tile_kernel<G, kTileThreads, INDELS, SW, GUARD><<<(count + per_block - 1) / per_block, kTileThreads, 0, c->stream>>>(
         c->d_jobs.as<mb::Job>(), c->p_tiles, c->p_ids + off, count,
         c->d_models.as<mb::DevModel>(), c->d_px.as<uint8_t>() + mb::PACK_SLACK, c->d_py.as<uint8_t>() + mb::PACK_SLACK,
         c->d_geo.as<int2>(), c->d_F.as<double>(), c->d_bnd.as<double>(), c->p_bnd_off, c->v_thr,
@@ -1243,8 +1377,14 @@ void launch_backward_tiles2(margin_b200_ctx *c, int off, int count, int64_t stag
 template <int G, bool INDELS>
 void launch_backward_tiles(margin_b200_ctx *c, int off, int count, int64_t stage_stride) {
     if (count <= 0) return;
-    if (c->have_switch) launch_backward_tiles2<G, INDELS, true>(c, off, count, stage_stride);
-    else launch_backward_tiles2<G, INDELS, false>(c, off, count, stage_stride);
+    const bool guard = c->guard_on && !c->seams.empty();
+    if (c->have_switch) {
+        if (guard) launch_backward_tiles3<G, INDELS, true, true>(c, off, count, stage_stride);
+        else launch_backward_tiles3<G, INDELS, true, false>(c, off, count, stage_stride);
+    } else {
+        if (guard) launch_backward_tiles3<G, INDELS, false, true>(c, off, count, stage_stride);
+        else launch_backward_tiles3<G, INDELS, false, false>(c, off, count, stage_stride);
+    }
 }
 
 int force_group_env() {
@@ -1277,128 +1417,172 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
     c->total_tuples = 0;
     c->list_tuples[0] = c->list_tuples[1] = c->list_tuples[2] = 0;
     c->force_group = force_group_env();
+    c->guard_failures = c->guard_reruns = 0;
     const int nj = (int) c->jobs.size();
     const int n_lists = want_indels ? 3 : 1;
     Trace tr(c);
     CU(cudaEventRecord(c->ev0, c->stream));
     if (run_band(c, c->params.dynamic_anchor_expansion != 0, true, false)) return 1;
     tr.mark("band+sync");
-    build_tiles(c);
-    tr.mark("tiles");
-    Bins bins;
-    if (build_bins(c, true, bins, c->force_group)) return 1;
-    tr.mark("bins+h2d+sync");
+    c->job_force_seq.assign(nj, 0);
+    const int L = pick_tile_len(c);  // fixed across guard re-runs: the tiles of unaffected jobs must not move
     const int64_t cells = c->total_cells;
-    const int S = c->total_slots;
-    const bool any_generic = bins.gen_bwd[3] > bins.gen_bwd[0], any_tiled = bins.tile_fwd[3] > bins.tile_fwd[0];
-    if (c->d_F.ensure((size_t) (cells + 1) * 3 * sizeof(double)) ||
-        (any_generic && c->d_stage.ensure((size_t) (cells + 1) * n_lists * sizeof(mb::Pair))) ||
-        (any_tiled && c->d_stage2.ensure((size_t) (cells + 1) * n_lists * sizeof(mb::StagedPair))) ||
-        c->d_seg_counts.ensure(((size_t) 3 * S + 1) * sizeof(int64_t)) ||
-        c->d_seg_off.ensure(((size_t) 3 * S + 1) * sizeof(int64_t)) ||
-        c->d_off_out.ensure((size_t) 3 * (c->n_aln + 1) * sizeof(int64_t)))
-        return 1;
-    CU(cudaMemsetAsync(c->d_seg_counts.p, 0, ((size_t) 3 * S + 1) * sizeof(int64_t), c->stream));
-    // Several contexts on one device take turns from here to the final synchronisation (margin_b200_posteriors_batch);
-    // the band phase above, with its host round trip, runs beside the other context's kernels.
+    int64_t *bounds = nullptr;
+    int S = 0, n_seams = 0;
+    // Several contexts on one device take turns from the first DP launch to the final synchronisation
+    // (margin_b200_posteriors_batch); the band phase above, with its host round trip, runs beside the other context's kernels.
     std::unique_lock<std::mutex> token;
-    if (c->take_token) token = std::unique_lock<std::mutex>(g_compute_token[c->device & (kMaxDevices - 1)]);
-    CU(cudaStreamWaitEvent(c->stream, c->ev_sym, 0));  // the symbols (upload's second stream) are needed from here on
-    launch_forward<8>(c, bins.seq_fwd[0], bins.seq_fwd[1] - bins.seq_fwd[0]);
-    launch_forward<16>(c, bins.seq_fwd[1], bins.seq_fwd[2] - bins.seq_fwd[1]);
-    launch_forward<32>(c, bins.seq_fwd[2], bins.seq_fwd[3] - bins.seq_fwd[2]);
-    launch_forward_tiles<8>(c, bins.tile_fwd[0], bins.tile_fwd[1] - bins.tile_fwd[0]);
-    launch_forward_tiles<16>(c, bins.tile_fwd[1], bins.tile_fwd[2] - bins.tile_fwd[1]);
-    launch_forward_tiles<32>(c, bins.tile_fwd[2], bins.tile_fwd[3] - bins.tile_fwd[2]);
-    if (finish_bins(c, bins)) return 1;
-    const int64_t stride = cells + 1;
-    if (want_indels) {
-        launch_backward<8, true>(c, bins.gen_bwd[0], bins.gen_bwd[1] - bins.gen_bwd[0], stride);
-        launch_backward<16, true>(c, bins.gen_bwd[1], bins.gen_bwd[2] - bins.gen_bwd[1], stride);
-        launch_backward<32, true>(c, bins.gen_bwd[2], bins.gen_bwd[3] - bins.gen_bwd[2], stride);
-        launch_backward_tiles<8, true>(c, bins.tile_bwd[0], bins.tile_bwd[1] - bins.tile_bwd[0], stride);
-        launch_backward_tiles<16, true>(c, bins.tile_bwd[1], bins.tile_bwd[2] - bins.tile_bwd[1], stride);
-        launch_backward_tiles<32, true>(c, bins.tile_bwd[2], bins.tile_bwd[3] - bins.tile_bwd[2], stride);
-    } else {
-        launch_backward<8, false>(c, bins.gen_bwd[0], bins.gen_bwd[1] - bins.gen_bwd[0], stride);
-        launch_backward<16, false>(c, bins.gen_bwd[1], bins.gen_bwd[2] - bins.gen_bwd[1], stride);
-        launch_backward<32, false>(c, bins.gen_bwd[2], bins.gen_bwd[3] - bins.gen_bwd[2], stride);
-        launch_backward_tiles<8, false>(c, bins.tile_bwd[0], bins.tile_bwd[1] - bins.tile_bwd[0], stride);
-        launch_backward_tiles<16, false>(c, bins.tile_bwd[1], bins.tile_bwd[2] - bins.tile_bwd[1], stride);
-        launch_backward_tiles<32, false>(c, bins.tile_bwd[2], bins.tile_bwd[3] - bins.tile_bwd[2], stride);
-    }
-    // exclusive scan of the tuple counts over [list][slot] (+ one trailing zero so that the total comes out too)
-    size_t tmp_bytes = 0;
-    const int n_scan = 3 * S + 1;
-    CU(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, c->d_seg_counts.as<int64_t>(), c->d_seg_off.as<int64_t>(), n_scan,
-                                     c->stream));
-    if (c->d_scan_tmp.ensure(tmp_bytes + 16)) return 1;
-    {
-        KTimer kt_(c, K_SCAN);
-        CU(cub::DeviceScan::ExclusiveSum(c->d_scan_tmp.p, tmp_bytes, c->d_seg_counts.as<int64_t>(),
-                                         c->d_seg_off.as<int64_t>(), n_scan, c->stream));
-    }
-    c->launches++;
-    // The list totals are only known on the device at this point.  The output buffer is sized from an estimate
-    // (0.22 tuples per band cell were measured on real data) and the gather refuses to write past it; the totals come
-    // back with the final synchronisation, and an overflow re-runs the gather into an exactly sized buffer.
-    int64_t *bounds = reinterpret_cast<int64_t *>(c->h_small.as<char>());  // pinned; run_band's landing zone is consumed
-    ctl_bounds_kernel<<<1, 32, 0, c->stream>>>(c->d_seg_off.as<int64_t>(), S, bounds);
-    bounds[4] = 0;
-    if (c->d_sym_err.p && ctl_copy(c->stream, bounds + 4, c->d_sym_err.p, 8)) return 1;  // pack_symbols_kernel's verdict
-    const size_t want_cap = (size_t) cells / (want_indels ? 3 : 6) + 4096;
-    if (c->d_out.cap / sizeof(mb::Pair) < want_cap && c->d_out.ensure(want_cap * sizeof(mb::Pair))) return 1;
-    auto run_gather = [&]() {
-        const int64_t cap = (int64_t) (c->d_out.cap / sizeof(mb::Pair));
-        if (S > 0 && nj > 0 && any_generic) {
-            KTimer kt_(c, K_GATHER);
-            mb::gather_kernel<<<S, 128, 0, c->stream>>>(c->d_jobs.as<mb::Job>(), c->p_tiles, S, c->d_cell_off.as<uint32_t>(),
-                                                        c->d_seg_counts.as<int64_t>(), c->d_seg_off.as<int64_t>(),
-                                                        c->d_stage.as<mb::Pair>(), stride, c->d_out.p, c->packed_now ? 1 : 0,
-                                                        n_lists, cap);
+    for (int attempt = 0;; attempt++) {
+        build_tiles(c, L);
+        tr.mark("tiles");
+        Bins bins;
+        if (build_bins(c, true, bins, c->force_group)) return 1;
+        tr.mark("bins+h2d");
+        S = c->total_slots;
+        n_seams = (int) c->seams.size();
+        const bool any_generic = bins.gen_bwd[3] > bins.gen_bwd[0], any_tiled = bins.tile_fwd[3] > bins.tile_fwd[0];
+        const int64_t stage_stride = c->stage_cells + 1;  // general kernels: private regions (Tile::stage_off)
+        if (c->d_F.ensure((size_t) (cells + 1) * 3 * sizeof(double)) ||
+            c->d_Fpriv.ensure((size_t) (c->priv_cells + 1) * 3 * sizeof(double)) ||
+            (any_generic && c->d_stage.ensure((size_t) stage_stride * n_lists * sizeof(mb::Pair))) ||
+            (any_tiled && c->d_stage2.ensure((size_t) (cells + 1) * n_lists * sizeof(mb::StagedPair))) ||
+            c->d_seg_counts.ensure(((size_t) 3 * S + 1) * sizeof(int64_t)) ||
+            c->d_seg_off.ensure(((size_t) 3 * S + 1) * sizeof(int64_t)) ||
+            c->d_off_out.ensure((size_t) 3 * (c->n_aln + 1) * sizeof(int64_t)))
+            return 1;
+        CU(cudaMemsetAsync(c->d_seg_counts.p, 0, ((size_t) 3 * S + 1) * sizeof(int64_t), c->stream));
+        if (c->take_token && !token.owns_lock()) token = std::unique_lock<std::mutex>(g_compute_token[c->device & (kMaxDevices - 1)]);
+        CU(cudaStreamWaitEvent(c->stream, c->ev_sym, 0));  // the symbols (upload's second stream) are needed from here on
+        launch_forward<8>(c, bins.seq_fwd[0], bins.seq_fwd[1] - bins.seq_fwd[0]);
+        launch_forward<16>(c, bins.seq_fwd[1], bins.seq_fwd[2] - bins.seq_fwd[1]);
+        launch_forward<32>(c, bins.seq_fwd[2], bins.seq_fwd[3] - bins.seq_fwd[2]);
+        launch_forward_tiles<8>(c, bins.tile_fwd[0], bins.tile_fwd[1] - bins.tile_fwd[0]);
+        launch_forward_tiles<16>(c, bins.tile_fwd[1], bins.tile_fwd[2] - bins.tile_fwd[1]);
+        launch_forward_tiles<32>(c, bins.tile_fwd[2], bins.tile_fwd[3] - bins.tile_fwd[2]);
+        if (finish_bins(c, bins)) return 1;
+        const int64_t stride = cells + 1;  // tile kernels: staging addressed by band cell
+        if (want_indels) {
+            launch_backward<8, true>(c, bins.gen_bwd[0], bins.gen_bwd[1] - bins.gen_bwd[0], stage_stride);
+            launch_backward<16, true>(c, bins.gen_bwd[1], bins.gen_bwd[2] - bins.gen_bwd[1], stage_stride);
+            launch_backward<32, true>(c, bins.gen_bwd[2], bins.gen_bwd[3] - bins.gen_bwd[2], stage_stride);
+            launch_backward_tiles<8, true>(c, bins.tile_bwd[0], bins.tile_bwd[1] - bins.tile_bwd[0], stride);
+            launch_backward_tiles<16, true>(c, bins.tile_bwd[1], bins.tile_bwd[2] - bins.tile_bwd[1], stride);
+            launch_backward_tiles<32, true>(c, bins.tile_bwd[2], bins.tile_bwd[3] - bins.tile_bwd[2], stride);
+        } else {
+            launch_backward<8, false>(c, bins.gen_bwd[0], bins.gen_bwd[1] - bins.gen_bwd[0], stage_stride);
+            launch_backward<16, false>(c, bins.gen_bwd[1], bins.gen_bwd[2] - bins.gen_bwd[1], stage_stride);
+            launch_backward<32, false>(c, bins.gen_bwd[2], bins.gen_bwd[3] - bins.gen_bwd[2], stage_stride);
+            launch_backward_tiles<8, false>(c, bins.tile_bwd[0], bins.tile_bwd[1] - bins.tile_bwd[0], stride);
+            launch_backward_tiles<16, false>(c, bins.tile_bwd[1], bins.tile_bwd[2] - bins.tile_bwd[1], stride);
+            launch_backward_tiles<32, false>(c, bins.tile_bwd[2], bins.tile_bwd[3] - bins.tile_bwd[2], stride);
+        }
+        // seam guard: every tile edge is checked (pairhmm_tiles.cuh: guard_check_kernel); the verdict comes back with the
+        // final synchronisation (flags[n_seams] = number of failed seams)
+        if (n_seams > 0) {
+            KTimer kt_(c, K_GUARD);
+            mb::guard_check_kernel<<<(n_seams + 3) / 4, 128, 0, c->stream>>>(
+                c->d_jobs.as<mb::Job>(), c->p_tiles, c->p_seams, n_seams, c->d_geo.as<int2>(), c->d_F.as<double>(),
+                c->d_Fpriv.as<double>(), c->d_bnd.as<double>(), c->p_bnd_off, c->guard_tol, c->guard_floor, c->p_guard_flags,
+                c->p_guard_flags + n_seams);
             c->launches++;
         }
-        if (S > 0 && nj > 0 && any_tiled) {
-            KTimer kt_(c, K_GATHER);
-            mb::gather_staged_kernel<<<S, 128, 0, c->stream>>>(c->d_jobs.as<mb::Job>(), c->p_tiles, S, c->d_geo.as<int2>(),
-                                                               c->d_seg_counts.as<int64_t>(), c->d_seg_off.as<int64_t>(),
-                                                               c->d_stage2.as<mb::StagedPair>(), stride, c->d_out.p,
-                                                               c->packed_now ? 1 : 0, n_lists, cap);
-            c->launches++;
+        // exclusive scan of the tuple counts over [list][slot] (+ one trailing zero so that the total comes out too)
+        size_t tmp_bytes = 0;
+        const int n_scan = 3 * S + 1;
+        CU(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, c->d_seg_counts.as<int64_t>(), c->d_seg_off.as<int64_t>(), n_scan,
+                                         c->stream));
+        if (c->d_scan_tmp.ensure(tmp_bytes + 16)) return 1;
+        {
+            KTimer kt_(c, K_SCAN);
+            CU(cub::DeviceScan::ExclusiveSum(c->d_scan_tmp.p, tmp_bytes, c->d_seg_counts.as<int64_t>(),
+                                             c->d_seg_off.as<int64_t>(), n_scan, c->stream));
         }
-    };
-    run_gather();
-    {
-        const int threads = 128;
-        const int blocks = (int) ((c->n_aln + 1 + threads - 1) / threads);
-        KTimer kt_(c, K_OFFSETS);
-        mb::list_offsets_kernel<<<blocks, threads, 0, c->stream>>>(c->p_aln_first_slot, (int) c->n_aln, S,
-                                                                   c->d_seg_off.as<int64_t>(), c->d_off_out.as<int64_t>());
         c->launches++;
-    }
-    CU(cudaEventRecord(c->ev1, c->stream));
-    tr.mark("launches");
-    CU(cudaStreamSynchronize(c->stream));
-    CU(cudaGetLastError());
-    tr.mark("final sync");
-    if (*reinterpret_cast<int *>(bounds + 4))
-        return fail("a symbol carries a run length >= %d; the repeat-count model holds 0..%d", MARGIN_B200_MAX_RL,
-                    MARGIN_B200_MAX_RL - 1);
-    c->total_tuples = bounds[3];
-    for (int l = 0; l < 3; l++) c->list_tuples[l] = bounds[l + 1] - bounds[l];
-    if ((size_t) c->total_tuples > c->d_out.cap / sizeof(mb::Pair)) {  // estimate too small: exact size, gather again
-        if (c->d_out.ensure((size_t) (c->total_tuples + 1) * sizeof(mb::Pair))) return 1;
+        // The list totals are only known on the device at this point.  The output buffer is sized from an estimate
+        // (0.22 tuples per band cell were measured on real data) and the gather refuses to write past it; the totals come
+        // back with the final synchronisation, and an overflow re-runs the gather into an exactly sized buffer.
+        bounds = reinterpret_cast<int64_t *>(c->h_small.as<char>());  // pinned; run_band's landing zone is consumed
+        ctl_bounds_kernel<<<1, 32, 0, c->stream>>>(c->d_seg_off.as<int64_t>(), S, bounds);
+        bounds[4] = 0;
+        bounds[5] = 0;
+        if (c->d_sym_err.p && ctl_copy(c->stream, bounds + 4, c->d_sym_err.p, 8)) return 1;  // pack_symbols_kernel's verdict
+        if (n_seams > 0 && ctl_copy(c->stream, bounds + 5, c->p_guard_flags + n_seams, 4)) return 1;
+        const size_t want_cap = (size_t) cells / (want_indels ? 3 : 6) + 4096;
+        if (c->d_out.cap / sizeof(mb::Pair) < want_cap && c->d_out.ensure(want_cap * sizeof(mb::Pair))) return 1;
+        auto run_gather = [&]() {
+            const int64_t cap = (int64_t) (c->d_out.cap / sizeof(mb::Pair));
+            if (S > 0 && nj > 0 && any_generic) {
+                KTimer kt_(c, K_GATHER);
+                mb::gather_kernel<<<S, 128, 0, c->stream>>>(c->p_tiles, S, c->d_seg_counts.as<int64_t>(),
+                                                            c->d_seg_off.as<int64_t>(), c->d_stage.as<mb::Pair>(), stage_stride,
+                                                            c->d_out.p, c->packed_now ? 1 : 0, n_lists, cap);
+                c->launches++;
+            }
+            if (S > 0 && nj > 0 && any_tiled) {
+                KTimer kt_(c, K_GATHER);
+                mb::gather_staged_kernel<<<S, 128, 0, c->stream>>>(c->d_jobs.as<mb::Job>(), c->p_tiles, S, c->d_geo.as<int2>(),
+                                                                   c->d_seg_counts.as<int64_t>(), c->d_seg_off.as<int64_t>(),
+                                                                   c->d_stage2.as<mb::StagedPair>(), stride, c->d_out.p,
+                                                                   c->packed_now ? 1 : 0, n_lists, cap);
+                c->launches++;
+            }
+        };
         run_gather();
+        {
+            const int threads = 128;
+            const int blocks = (int) ((c->n_aln + 1 + threads - 1) / threads);
+            KTimer kt_(c, K_OFFSETS);
+            mb::list_offsets_kernel<<<blocks, threads, 0, c->stream>>>(c->p_aln_first_slot, (int) c->n_aln, S,
+                                                                       c->d_seg_off.as<int64_t>(), c->d_off_out.as<int64_t>());
+            c->launches++;
+        }
         CU(cudaEventRecord(c->ev1, c->stream));
+        tr.mark("launches");
         CU(cudaStreamSynchronize(c->stream));
         CU(cudaGetLastError());
+        tr.mark("final sync");
+        if (*reinterpret_cast<int *>(bounds + 4))
+            return fail("a symbol carries a run length >= %d; the repeat-count model holds 0..%d", MARGIN_B200_MAX_RL,
+                        MARGIN_B200_MAX_RL - 1);
+        const int failed = *reinterpret_cast<int32_t *>(bounds + 5);
+        if (failed > 0) {
+            // a tile edge where the warmed-up state had not converged: the jobs concerned are swept sequentially (the
+            // reference's own recurrence, no tiling) and the batch runs again; all other tiles are cut exactly as before
+            if (attempt >= 2) return fail("internal error: the seam guard keeps failing after the affected jobs went sequential");
+            std::vector<int32_t> flags((size_t) n_seams);
+            int32_t *pin = reinterpret_cast<int32_t *>(c->h_arena.as<char>());  // the arena's host copy is consumed by now
+            if (c->h_arena.cap < (size_t) n_seams * 4) return fail("internal error: arena smaller than the guard flags");
+            if (ctl_copy(c->stream, pin, c->p_guard_flags, (size_t) n_seams * 4)) return 1;
+            CU(cudaStreamSynchronize(c->stream));
+            for (int k = 0; k < n_seams; k++)
+                if (pin[k]) c->job_force_seq[c->tiles[c->seams[k].lower].job] = 1;
+            c->guard_failures += failed;
+            c->guard_reruns++;
+            tr.mark("guard re-run");
+            continue;
+        }
+        c->total_tuples = bounds[3];
+        for (int l = 0; l < 3; l++) c->list_tuples[l] = bounds[l + 1] - bounds[l];
+        if ((size_t) c->total_tuples > c->d_out.cap / sizeof(mb::Pair)) {  // estimate too small: exact size, gather again
+            if (c->d_out.ensure((size_t) (c->total_tuples + 1) * sizeof(mb::Pair))) return 1;
+            run_gather();
+            CU(cudaEventRecord(c->ev1, c->stream));
+            CU(cudaStreamSynchronize(c->stream));
+            CU(cudaGetLastError());
+        }
+        break;
     }
+    if (token.owns_lock()) token.unlock();
     float ms = 0;
     CU(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
     int64_t segments = 0;
     for (int j = 0; j < nj; j++) segments += c->job_nseg[j];
     fill_stats(c, out, segments, ms);
     out->tiles = S;
+    out->wide_cells = c->wide_cells;
+    out->sequential_cells = c->seq_cells;
+    out->guard_seams = n_seams;
+    out->guard_failures = c->guard_failures;
     return 0;
 }
 
@@ -1482,6 +1666,9 @@ int ensure_subs(margin_b200_ctx *c, int K) {
         sub->tile_len_fixed = c->tile_len_fixed;
         sub->warmup = c->warmup;
         sub->kernel_timing = c->kernel_timing;
+        sub->guard_on = c->guard_on;
+        sub->guard_tol = c->guard_tol;
+        sub->gap_min = c->gap_min;
         // Tile length of a run: with bwd_slots / K every run is cut as if it owned 1/K of the SMs (same tiles as the
         // unpipelined call); a larger share means shorter tiles, i.e. a run finishes sooner (its lists reach the host
         // while later runs still compute) at the price of more warm-up diagonals.
@@ -1637,6 +1824,10 @@ int posteriors_pipelined(margin_b200_ctx *c, const margin_b200_batch *b, int wan
         out->segments += r.res.segments;
         out->tiles += r.res.tiles;
         out->kernel_launches += r.res.kernel_launches;
+        out->wide_cells += r.res.wide_cells;
+        out->sequential_cells += r.res.sequential_cells;
+        out->guard_seams += r.res.guard_seams;
+        out->guard_failures += r.res.guard_failures;
     }
     CU(cudaEventRecord(c->ev1, c->stream));
     CU(cudaEventSynchronize(c->ev1));

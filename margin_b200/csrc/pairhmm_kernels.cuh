@@ -47,6 +47,14 @@ struct AnchorGap {
 };
 
 // A unit of backward (and, in tiled mode, forward) work: a traceback segment or a piece of one (pairhmm_tiles.cuh).
+// Three kinds:
+//   TILE_BND   narrow tile (every diagonal of [f0, D] fits a lane group): forward_tile_kernel / backward_tile_kernel,
+//              F in the batch's shared F array, its own copy of F(tb_to) in the boundary buffer;
+//   TILE_WIDE  tile with a diagonal wider than 32 cells: the general range kernels below (neighbours through memory)
+//              with a PRIVATE copy of F for [f0, tb_from] at priv_off, so that its warm-up never touches cells other
+//              tiles own;
+//   neither    a whole traceback segment of a job swept sequentially (MARGIN_B200_MODE=sequential, degenerate
+//              matrices, guard re-runs): F comes from the job's own forward sweep in the shared array.
 struct Tile {
     int32_t job;
     int32_t D;        // diagonal where the backward sweep starts
@@ -54,8 +62,22 @@ struct Tile {
     int32_t tb_from;
     int32_t f0;       // diagonal where the tile's forward sweep starts (0 = the true start state)
     int32_t flags;    // TILE_* bits
+    int64_t priv_off;   // TILE_WIDE: first cell of the tile's private F (cells of f0 .. tb_from); else -1
+    int64_t stage_off;  // general backward kernel: first staged tuple of the tile in each list's staging array
 };
-enum { TILE_AT_END = 1, TILE_BND = 2 };  // D is the job's last diagonal; F(tb_to) lives in the boundary buffer
+enum { TILE_AT_END = 1, TILE_BND = 2, TILE_WIDE = 4 };  // AT_END: D is the job's last diagonal
+
+// Each tile owns 3 * w cells in the boundary buffer (w = widest diagonal of the tile): its own F(tb_to), and for the
+// seam guard B(tb_to + 1) (the last diagonal of its backward sweep) and B(tb_from + 1) (a warm-up diagonal the tile
+// above owns); see guard_check_kernel.
+enum { BND_F = 0, BND_B_LOW = 1, BND_B_HIGH = 2 };
+
+// A seam between two tiles of a job: both computed the same cells of diagonal d (one of them during its warm-up).
+struct Seam {
+    int32_t lower, upper;  // tile slots: `lower` owns diagonals <= d (forward seam) resp. starts above d (backward seam)
+    int32_t d;             // the diagonal compared: F(d) for a forward seam, B(d) for a backward seam
+    int32_t backward;      // 0 = forward seam, 1 = backward seam
+};
 
 struct Params {
     double threshold;
@@ -671,14 +693,17 @@ __device__ __forceinline__ Cell forward_cell(const DevModel &m, bool has_lower, 
 
 __device__ __forceinline__ int mod_g(int v, int G) { return v & (G - 1); }
 
-// Forward sweep.  One group of G lanes per job; lane = x mod G.  F (3 doubles per band cell) goes to HBM for the
+// Forward sweep.  One group of G lanes per work item; lane = x mod G.  F (3 doubles per band cell) goes to HBM for the
 // backward kernel.  Neighbour diagonals no wider than G stay in registers and move by one rotate-shuffle.
+// Work items: id >= 0 is the whole job `id`, swept from the true start state on diagonal 0 to its last diagonal, F in
+// the batch's shared array; id < 0 is the TILE_WIDE tile ~id, swept from a flat state on its diagonal f0 (the true start
+// state when f0 == 0) to tb_from, F in the tile's private array (see Tile).
 template <int G, int THREADS>
 __global__ void __launch_bounds__(THREADS)
-forward_kernel(const Job *__restrict__ jobs, const int32_t *__restrict__ job_ids, int n_ids,
+forward_kernel(const Job *__restrict__ jobs, const Tile *__restrict__ tiles, const int32_t *__restrict__ ids, int n_ids,
                const DevModel *__restrict__ models, const uint16_t *__restrict__ symx,
                const uint16_t *__restrict__ symy, const int32_t *__restrict__ kl_arr,
-               const uint32_t *__restrict__ cell_off, double *__restrict__ F) {
+               const uint32_t *__restrict__ cell_off, double *__restrict__ F, double *__restrict__ Fpriv) {
     __shared__ DevModel sm[2];
     for (int i = threadIdx.x; i < (int) (2 * sizeof(DevModel) / 8); i += THREADS)
         reinterpret_cast<double *>(sm)[i] = reinterpret_cast<const double *>(models)[i];
@@ -687,26 +712,52 @@ forward_kernel(const Job *__restrict__ jobs, const int32_t *__restrict__ job_ids
     if (g >= n_ids) return;
     const unsigned gm = group_mask<G>();
     const int lane = threadIdx.x & (G - 1);
-    const Job job = jobs[job_ids[g]];
+    const int id = ids[g];
+    int d_first = 0, d_last = -1;
+    int64_t priv = -1;
+    int ji = id;
+    if (id < 0) {
+        const Tile t = tiles[~id];
+        ji = t.job;
+        d_first = t.f0;
+        d_last = t.tb_from;
+        priv = t.priv_off;
+    }
+    const Job job = jobs[ji];
     const DevModel &m = sm[job.slot];
     const int N = job.lx + job.ly;
+    if (id >= 0) d_last = N;
     const uint16_t *sx = symx + job.symx_off, *sy = symy + job.symy_off;
     const int32_t *kls = kl_arr + job.diag_off;
     const uint32_t *co = cell_off + job.diag_off;
-    double *Fj = F + 3 * job.cell_base;
+    double *Fj = id >= 0 ? F + 3 * job.cell_base : Fpriv + 3 * (priv - (int64_t) co[d_first]);
 
-    // diagonal 0: the single cell (0,0) holds the start state (stateMachine.c:521-530)
     Cell f1 = cell_neg_inf(), f2 = cell_neg_inf();
-    if (lane == 0) {
-        f1.m = job.ragged_l ? MB_NEG_INF : 0.0;
-        f1.x = job.ragged_l ? 0.0 : MB_NEG_INF;
-        f1.y = f1.x;
-        store_cell(Fj, 0, f1);
-    }
     int xlo1 = 0, w1 = 1, xlo2 = 0, w2 = 0;
     uint32_t co1 = 0, co2 = 0;
+    if (d_first == 0) {
+        // diagonal 0: the single cell (0,0) holds the start state (stateMachine.c:521-530)
+        if (lane == 0) {
+            f1.m = job.ragged_l ? MB_NEG_INF : 0.0;
+            f1.x = job.ragged_l ? 0.0 : MB_NEG_INF;
+            f1.y = f1.x;
+            store_cell(Fj, 0, f1);
+        }
+    } else {
+        // a tile's warm-up starts from a flat state on every cell of diagonal f0
+        co1 = co[d_first];
+        w1 = (int) (co[d_first + 1] - co1);
+        xlo1 = (d_first + kls[d_first]) >> 1;
+        for (int jc = 0; jc * G < w1; jc++) {
+            const int r = mod_g(lane - xlo1, G) + jc * G;
+            if (r < w1) {
+                f1.m = f1.x = f1.y = 0.0;
+                store_cell(Fj, (int64_t) co1 + r, f1);
+            }
+        }
+    }
     const int prev_lane = mod_g(lane - 1, G);
-    for (int d = 1; d <= N; d++) {
+    for (int d = d_first + 1; d <= d_last; d++) {
         const int kl = kls[d];
         const uint32_t cod = co[d];
         const int w = (int) (co[d + 1] - cod);
@@ -852,9 +903,10 @@ __global__ void __launch_bounds__(THREADS)
 backward_kernel(const Job *__restrict__ jobs, const Tile *__restrict__ segs, const int32_t *__restrict__ slot_ids,
                 int n_ids, const DevModel *__restrict__ models, const uint16_t *__restrict__ symx,
                 const uint16_t *__restrict__ symy, const int32_t *__restrict__ kl_arr,
-                const uint32_t *__restrict__ cell_off, const double *__restrict__ F, Params p,
-                double *__restrict__ ring, const int64_t *__restrict__ slot_ring_off, Pair *__restrict__ stage,
-                int64_t stage_stride, int64_t *__restrict__ seg_counts, int total_slots) {
+                const uint32_t *__restrict__ cell_off, const double *__restrict__ F, const double *__restrict__ Fpriv,
+                Params p, double *__restrict__ ring, const int64_t *__restrict__ slot_ring_off, Pair *__restrict__ stage,
+                int64_t stage_stride, int64_t *__restrict__ seg_counts, int total_slots, double *__restrict__ bnd,
+                const int64_t *__restrict__ slot_bnd_off) {
     __shared__ DevModel sm[2];
     for (int i = threadIdx.x; i < (int) (2 * sizeof(DevModel) / 8); i += THREADS)
         reinterpret_cast<double *>(sm)[i] = reinterpret_cast<const double *>(models)[i];
@@ -870,14 +922,18 @@ backward_kernel(const Job *__restrict__ jobs, const Tile *__restrict__ segs, con
     const uint16_t *sx = symx + job.symx_off, *sy = symy + job.symy_off;
     const int32_t *kls = kl_arr + job.diag_off;
     const uint32_t *co = cell_off + job.diag_off;
-    const double *Fj = F + 3 * job.cell_base;
+    const bool wide = (seg.flags & TILE_WIDE) != 0;
+    const double *Fj = wide ? Fpriv + 3 * (seg.priv_off - (int64_t) co[seg.f0]) : F + 3 * job.cell_base;
     const int ring_w = job.ring_w;
     double *rg = ring + 3 * slot_ring_off[slot];
     const int D = seg.D, tb_to = seg.tb_to, tb_from = seg.tb_from;
     const double *endp = m.end_p[((seg.flags & TILE_AT_END) && job.ragged_r) ? 1 : 0];
-    const int64_t region = job.cell_base + co[tb_to + 1];
-    Pair *stM = stage + region, *stX = stage + stage_stride + region, *stY = stage + 2 * stage_stride + region;
+    Pair *stM = stage + seg.stage_off, *stX = stage + stage_stride + seg.stage_off,
+         *stY = stage + 2 * stage_stride + seg.stage_off;
     int cntM = 0, cntX = 0, cntY = 0;
+    // seam guard (TILE_WIDE only): B(tb_to + 1) and B(tb_from + 1) go to the tile's boundary sections
+    const int64_t bnd_cells = wide ? (slot_bnd_off[slot + 1] - slot_bnd_off[slot]) / 3 : 0;
+    double *bnd_t = bnd + 3 * slot_bnd_off[slot];
 
     Cell b1 = cell_neg_inf(), b2 = cell_neg_inf();
     int xlo1 = 0, w1 = 0, xlo2 = 0, w2 = 0;
@@ -936,6 +992,8 @@ backward_kernel(const Job *__restrict__ jobs, const Tile *__restrict__ segs, con
                     q[1] = b.x;
                     q[2] = b.y;
                 }
+                if (wide && (d == tb_to + 1 || (d == tb_from + 1 && d < D)) && x - xlo < bnd_cells)
+                    store_cell(bnd_t, (int64_t) (d == tb_to + 1 ? BND_B_LOW : BND_B_HIGH) * bnd_cells + (x - xlo), b);
             }
             if (do_total) {
                 double dot = MB_NEG_INF;
@@ -1023,16 +1081,14 @@ backward_kernel(const Job *__restrict__ jobs, const Tile *__restrict__ segs, con
 // Moves the staged tuples of every segment into the final lists.  seg_off is the exclusive scan of seg_counts over
 // [list][slot]; slots are already in final order (schedule_kernel), and inside a segment the reference's pop loop
 // (pairwiseAligner.c:1104-1123) reverses the emission order.
-__global__ void gather_kernel(const Job *__restrict__ jobs, const Tile *__restrict__ segs, int total_slots,
-                              const uint32_t *__restrict__ cell_off, const int64_t *__restrict__ seg_counts,
+__global__ void gather_kernel(const Tile *__restrict__ segs, int total_slots, const int64_t *__restrict__ seg_counts,
                               const int64_t *__restrict__ seg_off, const Pair *__restrict__ stage, int64_t stage_stride,
                               void *__restrict__ out, int packed, int n_lists, int64_t out_capacity) {
     const int slot = blockIdx.x;
     if (seg_off[(int64_t) 3 * total_slots] > out_capacity) return;  // the host re-runs with a larger buffer
     const Tile seg = segs[slot];
     if (seg.flags & TILE_BND) return;  // tiled jobs are gathered by gather_staged_kernel
-    const Job job = jobs[seg.job];
-    const int64_t region = job.cell_base + cell_off[job.diag_off + seg.tb_to + 1];
+    const int64_t region = seg.stage_off;
     for (int l = 0; l < n_lists; l++) {
         const int64_t c = seg_counts[(int64_t) l * total_slots + slot];
         const int64_t o = seg_off[(int64_t) l * total_slots + slot];

@@ -465,12 +465,12 @@ struct StageLane {
 #ifndef MB_BWD_MIN_BLOCKS
 #define MB_BWD_MIN_BLOCKS 4
 #endif
-template <int G, int THREADS, bool INDELS, bool SWITCH>
+template <int G, int THREADS, bool INDELS, bool SWITCH, bool GUARD>
 __global__ void __launch_bounds__(THREADS, MB_BWD_MIN_BLOCKS)
 backward_tile_kernel(const Job *__restrict__ jobs, const Tile *__restrict__ tiles, const int32_t *__restrict__ ids,
                      int n_ids, const DevModel *__restrict__ models, const uint8_t *__restrict__ px,
                      const uint8_t *__restrict__ py, const int2 *__restrict__ geo, const double *__restrict__ F,
-                     const double *__restrict__ Fbnd, const int64_t *__restrict__ slot_bnd_off, double v_thr,
+                     double *__restrict__ Fbnd, const int64_t *__restrict__ slot_bnd_off, double v_thr,
                      StagedPair *__restrict__ stage, int64_t stage_stride, int64_t *__restrict__ seg_counts,
                      int total_slots) {
     __shared__ __align__(16) TileShared sh;
@@ -489,7 +489,8 @@ backward_tile_kernel(const Job *__restrict__ jobs, const Tile *__restrict__ tile
     const uint8_t *sx = px + job.symx_off, *sy = py + job.symy_off;
     const int2 *gj = geo + job.diag_off;
     const double *Fj = F + 3 * job.cell_base;
-    const double *bnd = Fbnd + 3 * slot_bnd_off[slot];
+    double *bnd = Fbnd + 3 * slot_bnd_off[slot];  // [F(tb_to) | B(tb_to + 1) | B(tb_from + 1)], see Tile
+    const int bnd_cells = GUARD ? (int) ((slot_bnd_off[slot + 1] - slot_bnd_off[slot]) / 3) : 0;
     const double *emP = m.emit_packed;
     const double tMM = m.t[T_MM], tXM = m.t[T_XM], tYM = m.t[T_YM];
     const int D = t.D, tb_to = t.tb_to, tb_from = t.tb_from;
@@ -593,6 +594,17 @@ backward_tile_kernel(const Job *__restrict__ jobs, const Tile *__restrict__ tile
                     b.y = active ? endp[2] : MB_NEG_INF;
                 }
             }
+            if (GUARD) {
+                // seam guard: the last diagonal of this sweep and the warm-up diagonal just above the tile's own range
+                // are kept, so that guard_check_kernel can compare them with the neighbouring tiles' values
+                const bool low = d == tb_to + 1;
+                double *q = bnd + 3 * ((low ? BND_B_LOW : BND_B_HIGH) * bnd_cells + rank);
+                asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %0, 0;\n\t@p st.global.f64 [%1], %2;\n\t"
+                             "@p st.global.f64 [%1+8], %3;\n\t@p st.global.f64 [%1+16], %4;\n\t}"
+                             :: "r"((unsigned) (live && active && (low || (d == tb_from + 1 && it > 0)))), "l"(q),
+                                "d"(b.m), "d"(b.x), "d"(b.y)
+                             : "memory");
+            }
             if (MB_TOTAL_ON && __any_sync(0xffffffffu, do_total)) {
                 // diagonalCalculationTotalProbability (pairwiseAligner.c:578-596); groups that do not sample on this
                 // iteration run along (uniform control flow) and discard the result
@@ -684,6 +696,82 @@ __global__ void gather_staged_kernel(const Job *__restrict__ jobs, const Tile *_
             q.y = sp.y;
             store_pair(out, o + i, packed, q);
         }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------- seam guard
+//
+// The tiling rests on both recurrences forgetting their start within the warm-up.  That is a property of the data
+// (anchor density, band width), so it is CHECKED for every tile edge of every call: at a seam two tiles have
+// computed the same diagonal independently — the lower tile's own F(d) against the upper tile's warmed-up F(d), and
+// the upper tile's own B(d) against the lower tile's warmed-up B(d).  Each tile carries its own constant shift, so
+// the comparison is made after aligning the two copies on the largest value of the converged one; cells that are more
+// than `floor_gap` below it in both copies cannot move a posterior and are ignored.  A seam whose copies differ by
+// more than `tol` is flagged; the host then re-runs the batch with the affected jobs swept sequentially (exactly the
+// reference's recurrence), so a slow-forgetting stretch costs time, never correctness.
+// One warp per seam.
+__global__ void guard_check_kernel(const Job *__restrict__ jobs, const Tile *__restrict__ tiles,
+                                   const Seam *__restrict__ seams, int n_seams, const int2 *__restrict__ geo,
+                                   const double *__restrict__ F, const double *__restrict__ Fpriv,
+                                   const double *__restrict__ bnd, const int64_t *__restrict__ slot_bnd_off, double tol,
+                                   double floor_gap, int32_t *__restrict__ flags, int32_t *__restrict__ n_failed) {
+    const int k = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (k >= n_seams) return;
+    const Seam sm = seams[k];
+    const Tile lo = tiles[sm.lower], up = tiles[sm.upper];
+    const Job job = jobs[lo.job];
+    const int2 *gj = geo + job.diag_off;
+    const int64_t cod = (uint32_t) gj[sm.d].y;
+    const int w = (int) ((uint32_t) gj[sm.d + 1].y - (uint32_t) gj[sm.d].y);
+    auto sect = [&](int slot, int which) {
+        const int64_t cells = (slot_bnd_off[slot + 1] - slot_bnd_off[slot]) / 3;
+        return bnd + 3 * (slot_bnd_off[slot] + which * cells);
+    };
+    auto priv_at = [&](const Tile &t) { return Fpriv + 3 * (t.priv_off - (int64_t) (uint32_t) gj[t.f0].y + cod); };
+    const double *conv, *warm;  // the copy at the end of a long sweep / the copy at the end of a warm-up
+    if (!sm.backward) {
+        conv = (lo.flags & TILE_WIDE) ? priv_at(lo) : F + 3 * (job.cell_base + cod);
+        warm = (up.flags & TILE_WIDE) ? priv_at(up) : sect(sm.upper, BND_F);
+    } else {
+        conv = sect(sm.upper, BND_B_LOW);
+        warm = sect(sm.lower, BND_B_HIGH);
+    }
+    // largest value of the converged copy and where it is
+    double best = MB_NEG_INF;
+    int at = -1;
+    for (int i = lane; i < 3 * w; i += 32) {
+        const double v = conv[i];
+        if (v > best) {
+            best = v;
+            at = i;
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        const double ob = __shfl_xor_sync(0xffffffffu, best, o);
+        const int oa = __shfl_xor_sync(0xffffffffu, at, o);
+        if (ob > best || (ob == best && oa >= 0 && (at < 0 || oa < at))) {
+            best = ob;
+            at = oa;
+        }
+    }
+    bool bad = false;
+    if (at < 0) {  // nothing finite: the other copy must be empty as well
+        for (int i = lane; i < 3 * w; i += 32) bad |= warm[i] != MB_NEG_INF;
+    } else {
+        const double shift = warm[at] - best;
+        if (!(fabs(shift) < 1e300)) bad = true;
+        for (int i = lane; i < 3 * w; i += 32) {
+            const double a = conv[i], b = warm[i] - shift;
+            if (a == MB_NEG_INF && warm[i] == MB_NEG_INF) continue;
+            if (a < best - floor_gap && b < best - floor_gap) continue;
+            if (!(fabs(a - b) <= tol)) bad = true;
+        }
+    }
+    bad = __any_sync(0xffffffffu, bad);
+    if (lane == 0) {
+        flags[k] = bad ? 1 : 0;
+        if (bad) atomicAdd(n_failed, 1);
     }
 }
 

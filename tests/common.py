@@ -34,30 +34,4 @@ def compare_lists(got, want, tol_w=1):
     return ndiff
 
 
-def load_dump(path):
-    """A posterior batch written by the margin-side binding under MARGIN_B200_DUMP (compat/pairwiseAligner_b200.c):
-    (items, models, params, want_indels)."""
-    from margin_b200 import abi
-    raw = open(path, "rb").read()
-    head = np.frombuffer(raw, np.int64, 8)
-    assert head[0] == 0x42323030, "not a margin_b200 dump"
-    n, want, tx, ty, ta, sz_model, sz_params = (int(v) for v in head[1:8])
-    assert sz_model == C.sizeof(abi.Model) and sz_params == C.sizeof(abi.Params)
-    o = 64
-    params = abi.Params.from_buffer_copy(raw[o:o + sz_params]); o += sz_params
-    models = []
-    for _ in range(2):
-        models.append(abi.Model.from_buffer_copy(raw[o:o + sz_model])); o += sz_model
-
-    def take(dt, count):
-        nonlocal o
-        a = np.frombuffer(raw, dt, count, o).copy()
-        o += a.nbytes
-        return a
-    off_x, off_y, off_a = take(np.int64, n + 1), take(np.int64, n + 1), take(np.int64, n + 1)
-    slot, rl, rr = take(np.uint8, n), take(np.uint8, n), take(np.uint8, n)
-    sx, sy = take(np.uint16, tx), take(np.uint16, ty)
-    anc = take(np.int32, 3 * ta).reshape(-1, 3)
-    items = [(sx[off_x[i]:off_x[i + 1]], sy[off_y[i]:off_y[i + 1]], anc[off_a[i]:off_a[i + 1]], int(slot[i]),
-              int(rl[i]), int(rr[i])) for i in range(n)]
-    return items, models, params, want
+from margin_b200.replay import load_dump  # noqa: E402,F401

@@ -65,3 +65,30 @@ def long_indel_case(rng, lx, at, length, deletion=True, expansion=4, rle=True):
     sy[flip] = random_symbols(rng, int(flip.sum()), rle, 0.0)
     anchors = np.stack([xs, ys, np.full(len(xs), expansion)], axis=1).astype(np.int32)
     return sx, sy.astype(np.uint16), anchors, 0, 0, 0
+
+
+def low_complexity_case(rng, lx, period=2, anchor_keep=0.15, expansion=10, rle=True):
+    """A tandem repeat (unit of `period` symbols) with a few unique islands: inside the repeat every shift by a multiple
+    of the period aligns equally well, the posterior spreads over several diagonals and the recurrences forget their
+    start slowly.  Sparse anchors with a wide expansion keep the band open (round-2 style anchors)."""
+    unit = random_symbols(rng, period, rle, 0.0)
+    sx = np.tile(unit, lx // period + 1)[:lx].copy()
+    for _ in range(max(1, lx // 700)):  # unique islands
+        at = int(rng.integers(0, max(1, lx - 40)))
+        sx[at:at + 30] = random_symbols(rng, len(sx[at:at + 30]), rle, 0.0)
+    sy, true = mutate(rng, sx, sub=0.03, ins=0.03, dele=0.03, rle=rle)
+    anchors = [(x, y, expansion) for (x, y) in true if rng.random() < anchor_keep]
+    return sx, sy, np.array(anchors, dtype=np.int32).reshape(-1, 3), 0, 0, 0
+
+
+def gapped_anchor_case(rng, lx, gap_cols, n_gaps=3, expansion=4, rle=True):
+    """Dense anchors (one per match column) with `n_gaps` stretches of `gap_cols` columns whose anchors are dropped: the
+    band opens into a diamond about gap_cols wide there (a wide tile when gap_cols > 32) and is narrow elsewhere."""
+    sx = random_symbols(rng, lx, rle, 0.0)
+    sy, true = mutate(rng, sx, sub=0.04, ins=0.03, dele=0.03, rle=rle)
+    a = np.array([(x, y, expansion) for (x, y) in true], dtype=np.int32).reshape(-1, 3)
+    keep = np.ones(len(a), bool)
+    for _ in range(n_gaps):
+        at = int(rng.integers(lx // 10, max(lx // 10 + 1, lx - gap_cols - lx // 10)))
+        keep &= ~((a[:, 0] >= at) & (a[:, 0] < at + gap_cols))
+    return sx, sy, a[keep], int(rng.random() < 0.5), 0, 0

@@ -282,5 +282,88 @@ def test_long_indel_corridors_keep_tile_parity(oracle, golden_model, monkeypatch
     assert got.stats["tiles"] > len(items)
     for i, it in enumerate(items):
         ref = oracle.posteriors(pm.models[it[3]], pm.p, it[0], it[1], it[2], it[4], it[5], 1)
-        compare_lists(got[i], ref, tol_w=1000)  # 1e-4 in posterior probability (BASELINE.json north_star)
+        compare_lists(got[i], ref, tol_w=1)  # every seam is guarded: one unit of 1e-7, as everywhere else
+    al.close()
+
+
+@pytest.mark.gpu
+def test_wide_spots_cost_a_tile_not_the_read(oracle, golden_model, monkeypatch):
+    """Per-tile classification: a long read whose band opens wider than 32 cells in a few places (anchors missing over
+    60-200 columns) keeps its narrow stretches on the lane-group tile kernels; only the tiles that contain a wide
+    diagonal take the general path (private F), and no job falls back to the sequential sweep.  Strict parity."""
+    pm = golden_model("r94g360")
+    rng = np.random.default_rng(108)
+    items = [gen.gapped_anchor_case(rng, 6000, gap) for gap in (60, 110, 200)]
+    items.append(gen.random_case(rng, 5000, anchor_keep=0.9, expansions=(4,), ragged=False))  # all narrow
+    items.append(gen.random_case(rng, 300, anchor_keep=0.0))  # no anchors at all: one wide tile per traceback
+    monkeypatch.setenv("MARGIN_B200_PIPELINE", "1")
+    al = PairHmmAligner(pm.models, pm.p, device=0)
+    got = al.posteriors_batch(items, True)
+    st = got.stats
+    assert st["wide_cells"] > 0 and st["sequential_cells"] == 0 and st["tiles"] > 20, st
+    assert st["wide_cells"] < st["band_cells"] // 2, st
+    assert st["guard_seams"] > 0 and st["guard_failures"] == 0, st
+    for i, it in enumerate(items):
+        ref = oracle.posteriors(pm.models[it[3]], pm.p, it[0], it[1], it[2], it[4], it[5], 1)
+        compare_lists(got[i], ref, tol_w=1)
+    al.close()
+
+
+@pytest.mark.gpu
+def test_seam_guard_catches_an_unconverged_warmup(oracle, golden_model, monkeypatch):
+    """With a warm-up far too short for the recurrences to forget their flat start (8 diagonals) the tile edges disagree:
+    the guard must flag them, the affected jobs are re-run sequentially inside the call, and the lists are the oracle's.
+    With the guard off the same setting produces wrong weights (which is what the guard is for)."""
+    pm = golden_model("r94g360")
+    rng = np.random.default_rng(4242)
+    items = [gen.random_case(rng, 2500, anchor_keep=0.9, expansions=(4,), ragged=False) for _ in range(4)]
+    refs = [oracle.posteriors(pm.models[it[3]], pm.p, it[0], it[1], it[2], it[4], it[5], 1) for it in items]
+    monkeypatch.setenv("MARGIN_B200_PIPELINE", "1")
+    monkeypatch.setenv("MARGIN_B200_TILE_LEN", "200")
+    monkeypatch.setenv("MARGIN_B200_WARMUP", "8")
+    al = PairHmmAligner(pm.models, pm.p, device=0)
+    got = al.posteriors_batch(items, True)
+    assert got.stats["guard_failures"] > 0 and got.stats["sequential_cells"] > 0, got.stats
+    for i in range(len(items)):
+        compare_lists(got[i], refs[i], tol_w=1)
+    al.close()
+    monkeypatch.setenv("MARGIN_B200_GUARD", "0")
+    al = PairHmmAligner(pm.models, pm.p, device=0)
+    bad = al.posteriors_batch(items, True)
+    assert bad.stats["guard_seams"] == 0
+    worst = 0
+    for i in range(len(items)):
+        for l in range(3):
+            if len(bad[i][l]) != len(refs[i][l]) or not np.array_equal(bad[i][l]["x"], refs[i][l]["x"]):
+                worst = 10 ** 9
+            else:
+                worst = max(worst, int(np.abs(bad[i][l]["w"].astype(np.int64) - refs[i][l]["w"]).max(initial=0)))
+    assert worst > 100, "an 8-diagonal warm-up should not have converged (worst weight error %d)" % worst
+    al.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("tile_len", ["0", "200"])
+def test_adversarial_seams_stay_exact(oracle, golden_model, monkeypatch, tile_len):
+    """Inputs chosen against the forgetting assumption: anchor-free corridors of 16-40 diagonals (below the
+    32-diagonal threshold of the corridor logic), tandem repeats with sparse wide anchors, bands just under 32 cells.
+    Whatever the tiler does, the lists must be the oracle's to one unit of 1e-7: either the seams converge or the guard
+    sends the job to the sequential sweep."""
+    pm = golden_model("r94g360")
+    rng = np.random.default_rng(1632)
+    items = []
+    for length in (16, 20, 24, 28, 31, 33, 36, 40):
+        items.append(gen.long_indel_case(rng, 3000, int(rng.integers(800, 2200)), length, bool(length % 8 == 0)))
+    for period in (1, 2, 3, 5):
+        items.append(gen.low_complexity_case(rng, 3000, period))
+    items.append(gen.random_case(rng, 3000, anchor_keep=0.5, expansions=(28, 30), ragged=False))  # bands just under 32
+    if tile_len != "0":
+        monkeypatch.setenv("MARGIN_B200_TILE_LEN", tile_len)
+    monkeypatch.setenv("MARGIN_B200_PIPELINE", "1")
+    al = PairHmmAligner(pm.models, pm.p, device=0)
+    got = al.posteriors_batch(items, True)
+    print("adversarial seams (tile_len %s): %s" % (tile_len, got.stats))
+    for i, it in enumerate(items):
+        ref = oracle.posteriors(pm.models[it[3]], pm.p, it[0], it[1], it[2], it[4], it[5], 1)
+        compare_lists(got[i], ref, tol_w=1)
     al.close()
