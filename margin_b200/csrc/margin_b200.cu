@@ -123,7 +123,7 @@ struct margin_b200_ctx {
     int total_slots = 0;     // tiles of the current batch
     // tiling (pairhmm_tiles.cuh): tile length in diagonals (multiple of 10), warm-up diagonals on either side
     bool mode_sequential = false;
-    int tile_len = 1000, warmup = 128, force_group = 0, tile_len_used = 0, bwd_slots = 0;
+    int tile_len = 1000, warmup = 192, force_group = 0, tile_len_used = 0, bwd_slots = 0;
     bool tile_len_fixed = false;  // tile_len % 10 == 0: tiles start on total-probability samples
     std::vector<mb::Seg> segs;
     std::vector<mb::Tile> tiles;
@@ -172,7 +172,12 @@ struct margin_b200_ctx {
     // per-tile classification and the seam guard (build_tiles, guard_check_kernel)
     std::vector<uint32_t> chunk_base;    // first cell of every band chunk inside its job
     std::vector<int32_t> chunk_maxw;     // widest diagonal of every band chunk
-    std::vector<int32_t> tile_maxw;      // widest diagonal of [f0, D] per tile (to chunk granularity)
+    std::vector<int32_t> tile_maxw;      // widest diagonal of [f0, D] per tile as first cut (sizes its boundary sections)
+    std::vector<int32_t> tile_binw;      // ... of its current [f0, D] (picks the kernel; grows when a repair extends the warm-up)
+    std::vector<int32_t> tile_seg;       // index into segs of the traceback segment the tile belongs to
+    std::vector<uint8_t> tile_rerun;     // repair pass: the tiles that run again (empty = all)
+    std::vector<int32_t> job_gap_first;  // first entry of c->gaps per job (job_gap_first[nj] = gaps.size())
+    int repair_factor = 8;               // a failed seam re-runs its tile with this many times the warm-up
     std::vector<uint8_t> job_force_seq;  // jobs a failed seam sent to the sequential sweep
     std::vector<mb::Seam> seams;
     mb::Seam *p_seams = nullptr;
@@ -181,6 +186,8 @@ struct margin_b200_ctx {
     double guard_tol = 1e-9, guard_floor = 100.0;
     int64_t wide_cells = 0, seq_cells = 0, priv_cells = 0, stage_cells = 0;
     int guard_failures = 0, guard_reruns = 0;
+    bool guard_stats = false;            // MARGIN_B200_GUARD_STATS=1: histogram of the seam differences on stderr
+    DevBuf d_guard_worst, d_class_cells;
     PinBuf h_stage_in, h_small, h_out, h_off, h_gaps;
     // anchor-free stretches reported by the band kernel (sorted by job, start); see build_tiles
     std::vector<mb::AnchorGap> gaps;
@@ -376,6 +383,8 @@ int margin_b200_create(margin_b200_ctx **out, int device) {
     if (const char *e = getenv("MARGIN_B200_GAP_MIN")) c->gap_min = std::max(1, atoi(e));
     if (const char *e = getenv("MARGIN_B200_GUARD")) c->guard_on = atoi(e) != 0;
     if (const char *e = getenv("MARGIN_B200_GUARD_TOL")) c->guard_tol = atof(e);
+    if (const char *e = getenv("MARGIN_B200_GUARD_STATS")) c->guard_stats = atoi(e) != 0;
+    if (const char *e = getenv("MARGIN_B200_REPAIR_FACTOR")) c->repair_factor = std::max(2, atoi(e));
     c->counted = true;
     g_live_contexts[device & (kMaxDevices - 1)].fetch_add(1);
     *out = c;
@@ -392,7 +401,7 @@ void margin_b200_destroy(margin_b200_ctx *c) {
     DevBuf *bufs[] = {&c->d_models, &c->d_rsm[0], &c->d_rsm[1], &c->d_symx, &c->d_symy, &c->d_anchors, &c->d_jobs,
                       &c->d_kl, &c->d_kr, &c->d_cell_off, &c->d_job_cells, &c->d_job_maxw, &c->d_job_nseg, &c->d_err,
                       &c->d_segs, &c->d_seg_counts, &c->d_seg_off, &c->d_scan_tmp, &c->d_slot_ring_off, &c->d_ring,
-                      &c->d_ids, &c->d_aln_first_slot, &c->d_F, &c->d_Fpriv, &c->d_stage, &c->d_out, &c->d_off_out, &c->d_fwd_out,
+                      &c->d_ids, &c->d_aln_first_slot, &c->d_F, &c->d_Fpriv, &c->d_guard_worst, &c->d_class_cells, &c->d_stage, &c->d_out, &c->d_off_out, &c->d_fwd_out,
                       &c->d_geo, &c->d_tiles, &c->d_bnd, &c->d_slot_bnd_off, &c->d_emit5[0], &c->d_emit5[1],
                       &c->d_px, &c->d_py, &c->d_stage2, &c->d_chunks, &c->d_job_first_chunk, &c->d_chunk_sum, &c->d_chunk_maxw,
                       &c->d_totals, &c->d_band_out, &c->d_anchors_delta, &c->d_sym_err, &c->d_tiny_ids, &c->d_chunks_fwd, &c->d_job_first_chunk_fwd, &c->d_arena, &c->d_offs, &c->d_status};
@@ -1081,6 +1090,9 @@ void build_tiles(margin_b200_ctx *c, int L) {
     c->tile_len_used = L;
     c->tiles.clear();
     c->tile_maxw.clear();
+    c->tile_seg.clear();
+    c->tile_rerun.clear();
+    c->job_gap_first.assign(nj + 1, (int32_t) c->gaps.size());
     c->seams.clear();
     c->job_first_tile.assign(nj + 1, 0);
     c->wide_cells = c->seq_cells = c->priv_cells = c->stage_cells = 0;
@@ -1097,6 +1109,7 @@ void build_tiles(margin_b200_ctx *c, int L) {
             while (gap_end < c->gaps.size() && c->gaps[gap_end].job == j) gap_end++;
             const mb::AnchorGap *g = c->gaps.data() + gap_at;
             const int ng = (int) (gap_end - gap_at);
+            c->job_gap_first[j] = (int32_t) gap_at;
             if (!tiled) c->seq_cells += c->job_cells[j];
             blocks.clear();
             for (int s = c->job_nseg[j] - 1; s >= 0; s--) {
@@ -1115,6 +1128,7 @@ void build_tiles(margin_b200_ctx *c, int L) {
                     c->stage_cells += range_cells_bound(c, j, t.tb_to + 1, t.tb_from);
                     c->tiles.push_back(t);
                     c->tile_maxw.push_back(c->job_maxw[j]);
+                    c->tile_seg.push_back(job.seg_base + s);
                     continue;
                 }
                 cut_segment(g, ng, sg.tb_to, sg.tb_from, L, edges);
@@ -1140,6 +1154,7 @@ void build_tiles(margin_b200_ctx *c, int L) {
                     }
                     c->tiles.push_back(t);
                     c->tile_maxw.push_back(mw);
+                    c->tile_seg.push_back(job.seg_base + s);
                 }
                 blocks.emplace_back(first, (int32_t) c->tiles.size());
             }
@@ -1164,9 +1179,51 @@ void build_tiles(margin_b200_ctx *c, int L) {
             }
         }
     }
+    for (int j = nj - 1; j >= 0; j--)  // jobs without gaps point at their successor's first entry
+        if (c->job_gap_first[j] > c->job_gap_first[j + 1]) c->job_gap_first[j] = c->job_gap_first[j + 1];
+    c->tile_binw = c->tile_maxw;
     c->aln_first_slot[c->n_aln] = (int32_t) c->tiles.size();
     c->job_first_tile[nj] = (int32_t) c->tiles.size();
     c->total_slots = (int) c->tiles.size();
+}
+
+// Repair of failed seams: the tile whose warm-up had not converged (the upper tile of a forward seam, the lower tile of a
+// backward seam) gets `factor` times the warm-up on that side and is marked to run again; every other tile, its slot,
+// its staging and its boundary sections stay exactly as they are.  Returns false when a repair cannot be made in
+// place (the longer range contains a diagonal that changes the tile's kernel class, or nothing is left to extend):
+// the caller then sends the jobs concerned to the sequential sweep and runs the whole batch again.
+bool repair_tiles(margin_b200_ctx *c, const int32_t *flags, int factor) {
+    const int S = c->total_slots, gmax = c->force_group ? c->force_group : 32;
+    c->tile_rerun.assign(S, 0);
+    bool in_place = true;
+    for (size_t k = 0; k < c->seams.size(); k++) {
+        if (!flags[k]) continue;
+        const mb::Seam &sm = c->seams[k];
+        const int s = sm.backward ? sm.lower : sm.upper;
+        mb::Tile &t = c->tiles[s];
+        const int j = t.job;
+        const mb::AnchorGap *g = c->gaps.data() + c->job_gap_first[j];
+        const int ng = c->job_gap_first[j + 1] - c->job_gap_first[j];
+        const mb::Seg &sg = c->segs[c->tile_seg[s]];
+        const int W = c->warmup * factor;
+        if (!sm.backward) {
+            const int f0 = warmup_start_below(g, ng, t.tb_to, W);
+            if (f0 >= t.f0) in_place = false;  // already at the job's first diagonal
+            t.f0 = f0;
+        } else {
+            const int D = warmup_end_above(g, ng, t.tb_from, W, sg.D);
+            if (D <= t.D) in_place = false;
+            t.D = D;
+            if (D == sg.D && sg.at_end) t.flags |= mb::TILE_AT_END;
+        }
+        const int mw = range_maxw(c, j, t.f0, t.D + 1);
+        if ((mw > gmax) != ((t.flags & mb::TILE_WIDE) != 0)) in_place = false;
+        if ((t.flags & mb::TILE_WIDE)) in_place = false;  // a wide tile's private F was sized for its old range
+        c->tile_binw[s] = mw;
+        c->tile_rerun[s] = 1;
+        if (!in_place) c->job_force_seq[j] = 1;
+    }
+    return in_place;
 }
 
 // Id lists for the launches, each sorted by work (longest first) so that the groups sharing a warp finish together.
@@ -1220,8 +1277,9 @@ int build_bins(margin_b200_ctx *c, bool with_slots, Bins &bins, int force_group)
     k1.clear();
     k2.clear();
     k3.clear();
+    const bool partial = with_slots && !c->tile_rerun.empty();  // repair pass: only the marked tiles run again
     // general forward sweeps: whole jobs (id = job) ...
-    for (int j = 0; j < nj; j++)
+    for (int j = 0; j < nj && !partial; j++)
         if ((!with_slots || !job_is_tiled(c, j)) && !(!with_slots && j < (int) c->tiny_mask.size() && c->tiny_mask[j]))
             k0.push_back(key(bin_of(c->job_maxw[j]), c->jobs[j].lx + c->jobs[j].ly, j));
     int64_t ring_cells = 0, bnd_cells = 0;
@@ -1240,19 +1298,22 @@ int build_bins(margin_b200_ctx *c, bool with_slots, Bins &bins, int force_group)
     if (with_slots) {
         for (int s = 0; s < S; s++) {
             const mb::Tile &t = c->tiles[s];
-            const int mw = c->tile_maxw[s];
             // every tile owns three boundary sections of its widest diagonal (mb::BND_*)
             bnd_off[s] = bnd_cells;
-            bnd_cells += 3 * (int64_t) std::max(mw, 1);
+            bnd_cells += 3 * (int64_t) std::max(c->tile_maxw[s], 1);
             ring_off[s] = 0;
+            if (!(t.flags & mb::TILE_BND)) {
+                ring_off[s] = ring_cells;
+                ring_cells += 3 * (int64_t) c->jobs[t.job].ring_w;
+            }
+            if (partial && !c->tile_rerun[s]) continue;
+            const int mw = c->tile_binw[s];
             if (t.flags & mb::TILE_BND) {
                 k1.push_back(key(bin_of(mw), t.tb_from - t.f0, s));
                 k3.push_back(key(bin_of(mw), t.D - t.tb_to, s));
             } else {
                 if (t.flags & mb::TILE_WIDE) k0.push_back(key(bin_of(mw), t.tb_from - t.f0, ~s));  // ... and wide tiles (id = ~slot)
                 k2.push_back(key(bin_of(mw), t.D - t.tb_to, s));
-                ring_off[s] = ring_cells;
-                ring_cells += 3 * (int64_t) c->jobs[t.job].ring_w;
             }
         }
         ring_off[S] = 0;
@@ -1387,6 +1448,38 @@ void launch_backward_tiles(margin_b200_ctx *c, int off, int count, int64_t stage
     }
 }
 
+// MARGIN_B200_GUARD_STATS=1: what the seams of this batch looked like (log10 histogram of the largest difference per
+// seam, forward and backward seams apart) and how wide its tiles are.  Diagnostic only.
+void guard_report(margin_b200_ctx *c, int n_seams, int attempt) {
+    std::vector<float> worst((size_t) n_seams);
+    if (n_seams) cudaMemcpy(worst.data(), c->d_guard_worst.p, (size_t) n_seams * sizeof(float), cudaMemcpyDeviceToHost);
+    int hist[2][20] = {};
+    float mx[2] = {0, 0};
+    for (int k = 0; k < n_seams; k++) {
+        const int b = c->seams[k].backward ? 1 : 0;
+        const float v = worst[k];
+        mx[b] = std::max(mx[b], v);
+        int bin = v <= 0 ? 0 : (int) std::floor(std::log10((double) v)) + 18;  // 1e-18 .. 1e1
+        hist[b][std::max(0, std::min(19, bin))]++;
+    }
+    for (int b = 0; b < 2; b++) {
+        fprintf(stderr, "[margin_b200 guard] attempt %d %s seams: max %.3g;", attempt, b ? "backward" : "forward", mx[b]);
+        for (int i = 0; i < 20; i++)
+            if (hist[b][i]) fprintf(stderr, " 1e%d:%d", i - 18, hist[b][i]);
+        fprintf(stderr, "\n");
+    }
+    int wh[12] = {};
+    for (int32_t w : c->tile_maxw) {
+        int bin = 0;
+        while (bin < 11 && (8 << bin) < w) bin++;
+        wh[bin]++;
+    }
+    fprintf(stderr, "[margin_b200 guard] tiles by widest diagonal:");
+    for (int i = 0; i < 12; i++)
+        if (wh[i]) fprintf(stderr, " <=%d:%d", 8 << i, wh[i]);
+    fprintf(stderr, "; L=%d W=%d\n", c->tile_len_used, c->warmup);
+}
+
 int force_group_env() {
     const char *e = getenv("MARGIN_B200_FORCE_GROUP");  // test hook: 8, 16 or 32 exercises the wide-diagonal fallback
     if (!e) return 0;
@@ -1427,30 +1520,20 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
     c->job_force_seq.assign(nj, 0);
     const int L = pick_tile_len(c);  // fixed across guard re-runs: the tiles of unaffected jobs must not move
     const int64_t cells = c->total_cells;
+    const int64_t stride = cells + 1;  // tile kernels: staging addressed by band cell
     int64_t *bounds = nullptr;
     int S = 0, n_seams = 0;
+    int64_t stage_stride = 1;
+    bool any_generic = false, any_tiled = false;
     // Several contexts on one device take turns from the first DP launch to the final synchronisation
     // (margin_b200_posteriors_batch); the band phase above, with its host round trip, runs beside the other context's kernels.
     std::unique_lock<std::mutex> token;
-    for (int attempt = 0;; attempt++) {
-        build_tiles(c, L);
-        tr.mark("tiles");
+
+    // forward + backward launches of one pass (all tiles, or the tiles of a repair pass), then the seam guard
+    auto run_dp = [&]() -> int {
         Bins bins;
         if (build_bins(c, true, bins, c->force_group)) return 1;
         tr.mark("bins+h2d");
-        S = c->total_slots;
-        n_seams = (int) c->seams.size();
-        const bool any_generic = bins.gen_bwd[3] > bins.gen_bwd[0], any_tiled = bins.tile_fwd[3] > bins.tile_fwd[0];
-        const int64_t stage_stride = c->stage_cells + 1;  // general kernels: private regions (Tile::stage_off)
-        if (c->d_F.ensure((size_t) (cells + 1) * 3 * sizeof(double)) ||
-            c->d_Fpriv.ensure((size_t) (c->priv_cells + 1) * 3 * sizeof(double)) ||
-            (any_generic && c->d_stage.ensure((size_t) stage_stride * n_lists * sizeof(mb::Pair))) ||
-            (any_tiled && c->d_stage2.ensure((size_t) (cells + 1) * n_lists * sizeof(mb::StagedPair))) ||
-            c->d_seg_counts.ensure(((size_t) 3 * S + 1) * sizeof(int64_t)) ||
-            c->d_seg_off.ensure(((size_t) 3 * S + 1) * sizeof(int64_t)) ||
-            c->d_off_out.ensure((size_t) 3 * (c->n_aln + 1) * sizeof(int64_t)))
-            return 1;
-        CU(cudaMemsetAsync(c->d_seg_counts.p, 0, ((size_t) 3 * S + 1) * sizeof(int64_t), c->stream));
         if (c->take_token && !token.owns_lock()) token = std::unique_lock<std::mutex>(g_compute_token[c->device & (kMaxDevices - 1)]);
         CU(cudaStreamWaitEvent(c->stream, c->ev_sym, 0));  // the symbols (upload's second stream) are needed from here on
         launch_forward<8>(c, bins.seq_fwd[0], bins.seq_fwd[1] - bins.seq_fwd[0]);
@@ -1460,7 +1543,6 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
         launch_forward_tiles<16>(c, bins.tile_fwd[1], bins.tile_fwd[2] - bins.tile_fwd[1]);
         launch_forward_tiles<32>(c, bins.tile_fwd[2], bins.tile_fwd[3] - bins.tile_fwd[2]);
         if (finish_bins(c, bins)) return 1;
-        const int64_t stride = cells + 1;  // tile kernels: staging addressed by band cell
         if (want_indels) {
             launch_backward<8, true>(c, bins.gen_bwd[0], bins.gen_bwd[1] - bins.gen_bwd[0], stage_stride);
             launch_backward<16, true>(c, bins.gen_bwd[1], bins.gen_bwd[2] - bins.gen_bwd[1], stage_stride);
@@ -1479,13 +1561,36 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
         // seam guard: every tile edge is checked (pairhmm_tiles.cuh: guard_check_kernel); the verdict comes back with the
         // final synchronisation (flags[n_seams] = number of failed seams)
         if (n_seams > 0) {
+            if (c->guard_stats && c->d_guard_worst.ensure((size_t) n_seams * sizeof(float))) return 1;
             KTimer kt_(c, K_GUARD);
             mb::guard_check_kernel<<<(n_seams + 3) / 4, 128, 0, c->stream>>>(
                 c->d_jobs.as<mb::Job>(), c->p_tiles, c->p_seams, n_seams, c->d_geo.as<int2>(), c->d_F.as<double>(),
                 c->d_Fpriv.as<double>(), c->d_bnd.as<double>(), c->p_bnd_off, c->guard_tol, c->guard_floor, c->p_guard_flags,
-                c->p_guard_flags + n_seams);
+                c->p_guard_flags + n_seams, c->guard_stats ? c->d_guard_worst.as<float>() : nullptr);
             c->launches++;
         }
+        return 0;
+    };
+    auto run_gather = [&]() {
+        const int64_t cap = (int64_t) (c->d_out.cap / sizeof(mb::Pair));
+        if (S > 0 && nj > 0 && any_generic) {
+            KTimer kt_(c, K_GATHER);
+            mb::gather_kernel<<<S, 128, 0, c->stream>>>(c->p_tiles, S, c->d_seg_counts.as<int64_t>(),
+                                                        c->d_seg_off.as<int64_t>(), c->d_stage.as<mb::Pair>(), stage_stride,
+                                                        c->d_out.p, c->packed_now ? 1 : 0, n_lists, cap);
+            c->launches++;
+        }
+        if (S > 0 && nj > 0 && any_tiled) {
+            KTimer kt_(c, K_GATHER);
+            mb::gather_staged_kernel<<<S, 128, 0, c->stream>>>(c->d_jobs.as<mb::Job>(), c->p_tiles, S, c->d_geo.as<int2>(),
+                                                               c->d_seg_counts.as<int64_t>(), c->d_seg_off.as<int64_t>(),
+                                                               c->d_stage2.as<mb::StagedPair>(), stride, c->d_out.p,
+                                                               c->packed_now ? 1 : 0, n_lists, cap);
+            c->launches++;
+        }
+    };
+    // scan of the tuple counts, gather into the final lists, per-alignment offsets, then the call's one synchronisation
+    auto finish_pass = [&]() -> int {
         // exclusive scan of the tuple counts over [list][slot] (+ one trailing zero so that the total comes out too)
         size_t tmp_bytes = 0;
         const int n_scan = 3 * S + 1;
@@ -1507,26 +1612,17 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
         bounds[5] = 0;
         if (c->d_sym_err.p && ctl_copy(c->stream, bounds + 4, c->d_sym_err.p, 8)) return 1;  // pack_symbols_kernel's verdict
         if (n_seams > 0 && ctl_copy(c->stream, bounds + 5, c->p_guard_flags + n_seams, 4)) return 1;
+        bounds[6] = bounds[7] = 0;
+        if (any_generic && S > 0) {  // exact cell counts of the wide-tile and sequential paths (result counters)
+            if (c->d_class_cells.ensure(16)) return 1;
+            CU(cudaMemsetAsync(c->d_class_cells.p, 0, 16, c->stream));
+            mb::class_cells_kernel<<<(S + 127) / 128, 128, 0, c->stream>>>(c->d_jobs.as<mb::Job>(), c->p_tiles, S, c->d_geo.as<int2>(),
+                                                                        c->d_class_cells.as<unsigned long long>());
+            if (ctl_copy(c->stream, bounds + 6, c->d_class_cells.p, 16)) return 1;
+            c->launches++;
+        }
         const size_t want_cap = (size_t) cells / (want_indels ? 3 : 6) + 4096;
         if (c->d_out.cap / sizeof(mb::Pair) < want_cap && c->d_out.ensure(want_cap * sizeof(mb::Pair))) return 1;
-        auto run_gather = [&]() {
-            const int64_t cap = (int64_t) (c->d_out.cap / sizeof(mb::Pair));
-            if (S > 0 && nj > 0 && any_generic) {
-                KTimer kt_(c, K_GATHER);
-                mb::gather_kernel<<<S, 128, 0, c->stream>>>(c->p_tiles, S, c->d_seg_counts.as<int64_t>(),
-                                                            c->d_seg_off.as<int64_t>(), c->d_stage.as<mb::Pair>(), stage_stride,
-                                                            c->d_out.p, c->packed_now ? 1 : 0, n_lists, cap);
-                c->launches++;
-            }
-            if (S > 0 && nj > 0 && any_tiled) {
-                KTimer kt_(c, K_GATHER);
-                mb::gather_staged_kernel<<<S, 128, 0, c->stream>>>(c->d_jobs.as<mb::Job>(), c->p_tiles, S, c->d_geo.as<int2>(),
-                                                                   c->d_seg_counts.as<int64_t>(), c->d_seg_off.as<int64_t>(),
-                                                                   c->d_stage2.as<mb::StagedPair>(), stride, c->d_out.p,
-                                                                   c->packed_now ? 1 : 0, n_lists, cap);
-                c->launches++;
-            }
-        };
         run_gather();
         {
             const int threads = 128;
@@ -1544,33 +1640,72 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
         if (*reinterpret_cast<int *>(bounds + 4))
             return fail("a symbol carries a run length >= %d; the repeat-count model holds 0..%d", MARGIN_B200_MAX_RL,
                         MARGIN_B200_MAX_RL - 1);
-        const int failed = *reinterpret_cast<int32_t *>(bounds + 5);
-        if (failed > 0) {
-            // a tile edge where the warmed-up state had not converged: the jobs concerned are swept sequentially (the
-            // reference's own recurrence, no tiling) and the batch runs again; all other tiles are cut exactly as before
-            if (attempt >= 2) return fail("internal error: the seam guard keeps failing after the affected jobs went sequential");
-            std::vector<int32_t> flags((size_t) n_seams);
-            int32_t *pin = reinterpret_cast<int32_t *>(c->h_arena.as<char>());  // the arena's host copy is consumed by now
-            if (c->h_arena.cap < (size_t) n_seams * 4) return fail("internal error: arena smaller than the guard flags");
+        return 0;
+    };
+
+    for (int attempt = 0;; attempt++) {
+        // ---- a full pass: cut the tiles (jobs sent back by a failed repair are swept sequentially), run everything
+        build_tiles(c, L);
+        tr.mark("tiles");
+        S = c->total_slots;
+        n_seams = (int) c->seams.size();
+        any_generic = any_tiled = false;
+        for (const mb::Tile &t : c->tiles) {
+            if (t.flags & mb::TILE_BND) any_tiled = true;
+            else any_generic = true;
+        }
+        stage_stride = c->stage_cells + 1;  // general kernels: private regions (Tile::stage_off)
+        if (c->d_F.ensure((size_t) (cells + 1) * 3 * sizeof(double)) ||
+            c->d_Fpriv.ensure((size_t) (c->priv_cells + 1) * 3 * sizeof(double)) ||
+            (any_generic && c->d_stage.ensure((size_t) stage_stride * n_lists * sizeof(mb::Pair))) ||
+            (any_tiled && c->d_stage2.ensure((size_t) (cells + 1) * n_lists * sizeof(mb::StagedPair))) ||
+            c->d_seg_counts.ensure(((size_t) 3 * S + 1) * sizeof(int64_t)) ||
+            c->d_seg_off.ensure(((size_t) 3 * S + 1) * sizeof(int64_t)) ||
+            c->d_off_out.ensure((size_t) 3 * (c->n_aln + 1) * sizeof(int64_t)))
+            return 1;
+        CU(cudaMemsetAsync(c->d_seg_counts.p, 0, ((size_t) 3 * S + 1) * sizeof(int64_t), c->stream));
+        if (run_dp() || finish_pass()) return 1;
+        int failed = *reinterpret_cast<int32_t *>(bounds + 5);
+        if (c->guard_stats) guard_report(c, n_seams, attempt);
+        if (failed == 0) break;
+        // ---- a tile edge where the warmed-up state had not converged.  First the tiles concerned run again with a much
+        // longer warm-up, everything else staying in place (repair pass); what still fails, or cannot be repaired in
+        // place, sends its job to the sequential sweep (the reference's own recurrence) and the batch runs again.
+        if (attempt >= 2) return fail("internal error: the seam guard keeps failing after the affected jobs went sequential");
+        c->guard_failures += failed;
+        c->guard_reruns++;
+        int32_t *pin = reinterpret_cast<int32_t *>(c->h_arena.as<char>());  // the arena's host copy is consumed by now
+        if (c->h_arena.cap < (size_t) n_seams * 4) return fail("internal error: arena smaller than the guard flags");
+        auto fetch_flags = [&]() -> int {
             if (ctl_copy(c->stream, pin, c->p_guard_flags, (size_t) n_seams * 4)) return 1;
             CU(cudaStreamSynchronize(c->stream));
-            for (int k = 0; k < n_seams; k++)
-                if (pin[k]) c->job_force_seq[c->tiles[c->seams[k].lower].job] = 1;
+            return 0;
+        };
+        if (fetch_flags()) return 1;
+        std::vector<int32_t> flags(pin, pin + n_seams);
+        if (repair_tiles(c, flags.data(), c->repair_factor)) {
+            tr.mark("repair");
+            if (run_dp() || finish_pass()) return 1;
+            failed = *reinterpret_cast<int32_t *>(bounds + 5);
+            if (c->guard_stats) guard_report(c, n_seams, 100 + attempt);
+            c->tile_rerun.clear();
+            if (failed == 0) break;
             c->guard_failures += failed;
-            c->guard_reruns++;
-            tr.mark("guard re-run");
-            continue;
+            if (fetch_flags()) return 1;
+            flags.assign(pin, pin + n_seams);
         }
-        c->total_tuples = bounds[3];
-        for (int l = 0; l < 3; l++) c->list_tuples[l] = bounds[l + 1] - bounds[l];
-        if ((size_t) c->total_tuples > c->d_out.cap / sizeof(mb::Pair)) {  // estimate too small: exact size, gather again
-            if (c->d_out.ensure((size_t) (c->total_tuples + 1) * sizeof(mb::Pair))) return 1;
-            run_gather();
-            CU(cudaEventRecord(c->ev1, c->stream));
-            CU(cudaStreamSynchronize(c->stream));
-            CU(cudaGetLastError());
-        }
-        break;
+        for (int k = 0; k < n_seams; k++)
+            if (flags[k]) c->job_force_seq[c->tiles[c->seams[k].lower].job] = 1;
+        tr.mark("guard re-run");
+    }
+    c->total_tuples = bounds[3];
+    for (int l = 0; l < 3; l++) c->list_tuples[l] = bounds[l + 1] - bounds[l];
+    if ((size_t) c->total_tuples > c->d_out.cap / sizeof(mb::Pair)) {  // estimate too small: exact size, gather again
+        if (c->d_out.ensure((size_t) (c->total_tuples + 1) * sizeof(mb::Pair))) return 1;
+        run_gather();
+        CU(cudaEventRecord(c->ev1, c->stream));
+        CU(cudaStreamSynchronize(c->stream));
+        CU(cudaGetLastError());
     }
     if (token.owns_lock()) token.unlock();
     float ms = 0;
@@ -1579,8 +1714,8 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
     for (int j = 0; j < nj; j++) segments += c->job_nseg[j];
     fill_stats(c, out, segments, ms);
     out->tiles = S;
-    out->wide_cells = c->wide_cells;
-    out->sequential_cells = c->seq_cells;
+    out->wide_cells = bounds[6];
+    out->sequential_cells = bounds[7];
     out->guard_seams = n_seams;
     out->guard_failures = c->guard_failures;
     return 0;

@@ -714,7 +714,8 @@ __global__ void guard_check_kernel(const Job *__restrict__ jobs, const Tile *__r
                                    const Seam *__restrict__ seams, int n_seams, const int2 *__restrict__ geo,
                                    const double *__restrict__ F, const double *__restrict__ Fpriv,
                                    const double *__restrict__ bnd, const int64_t *__restrict__ slot_bnd_off, double tol,
-                                   double floor_gap, int32_t *__restrict__ flags, int32_t *__restrict__ n_failed) {
+                                   double floor_gap, int32_t *__restrict__ flags, int32_t *__restrict__ n_failed,
+                                   float *__restrict__ worst_out /* may be null: largest difference per seam */) {
     const int k = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
     if (k >= n_seams) return;
@@ -756,6 +757,7 @@ __global__ void guard_check_kernel(const Job *__restrict__ jobs, const Tile *__r
         }
     }
     bool bad = false;
+    double worst = 0.0;
     if (at < 0) {  // nothing finite: the other copy must be empty as well
         for (int i = lane; i < 3 * w; i += 32) bad |= warm[i] != MB_NEG_INF;
     } else {
@@ -765,14 +767,31 @@ __global__ void guard_check_kernel(const Job *__restrict__ jobs, const Tile *__r
             const double a = conv[i], b = warm[i] - shift;
             if (a == MB_NEG_INF && warm[i] == MB_NEG_INF) continue;
             if (a < best - floor_gap && b < best - floor_gap) continue;
-            if (!(fabs(a - b) <= tol)) bad = true;
+            const double diff = fabs(a - b);
+            if (!(diff <= tol)) bad = true;
+            worst = (diff == diff) ? fmax(worst, diff) : 1e300;
         }
     }
     bad = __any_sync(0xffffffffu, bad);
+    for (int o = 16; o > 0; o >>= 1) worst = fmax(worst, __shfl_xor_sync(0xffffffffu, worst, o));
     if (lane == 0) {
         flags[k] = bad ? 1 : 0;
         if (bad) atomicAdd(n_failed, 1);
+        if (worst_out) worst_out[k] = bad && worst <= tol ? 3e38f : (float) fmin(worst, 3e38);
     }
+}
+
+// Band cells per execution path (result counters): out[0] = cells owned by TILE_WIDE tiles, out[1] = cells of tiles
+// swept sequentially (neither TILE_BND nor TILE_WIDE).
+__global__ void class_cells_kernel(const Job *__restrict__ jobs, const Tile *__restrict__ tiles, int n_tiles,
+                                   const int2 *__restrict__ geo, unsigned long long *__restrict__ out) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n_tiles) return;
+    const Tile t = tiles[s];
+    if (t.flags & TILE_BND) return;
+    const int2 *gj = geo + jobs[t.job].diag_off;
+    const unsigned long long own = (uint32_t) gj[t.tb_from + 1].y - (uint32_t) gj[t.tb_to + 1].y;
+    atomicAdd(out + ((t.flags & TILE_WIDE) ? 0 : 1), own);
 }
 
 // exp(v) >= threshold  <=>  v >= v_thr for the device's exp(): scans the doubles around log(threshold) and returns

@@ -294,14 +294,16 @@ def test_wide_spots_cost_a_tile_not_the_read(oracle, golden_model, monkeypatch):
     pm = golden_model("r94g360")
     rng = np.random.default_rng(108)
     items = [gen.gapped_anchor_case(rng, 6000, gap) for gap in (60, 110, 200)]
-    items.append(gen.random_case(rng, 5000, anchor_keep=0.9, expansions=(4,), ragged=False))  # all narrow
-    items.append(gen.random_case(rng, 300, anchor_keep=0.0))  # no anchors at all: one wide tile per traceback
+    items.append(gen.gapped_anchor_case(rng, 5000, 0, n_gaps=0))  # all narrow
+    sx = gen.random_symbols(rng, 300)
+    sy, _ = gen.mutate(rng, sx)
+    items.append((sx, sy, np.zeros((0, 3), np.int32), 0, 0, 0))  # no anchors at all: one wide tile per traceback
     monkeypatch.setenv("MARGIN_B200_PIPELINE", "1")
     al = PairHmmAligner(pm.models, pm.p, device=0)
     got = al.posteriors_batch(items, True)
     st = got.stats
     assert st["wide_cells"] > 0 and st["sequential_cells"] == 0 and st["tiles"] > 20, st
-    assert st["wide_cells"] < st["band_cells"] // 2, st
+    assert st["wide_cells"] < 0.6 * st["band_cells"], st
     assert st["guard_seams"] > 0 and st["guard_failures"] == 0, st
     for i, it in enumerate(items):
         ref = oracle.posteriors(pm.models[it[3]], pm.p, it[0], it[1], it[2], it[4], it[5], 1)
@@ -312,7 +314,8 @@ def test_wide_spots_cost_a_tile_not_the_read(oracle, golden_model, monkeypatch):
 @pytest.mark.gpu
 def test_seam_guard_catches_an_unconverged_warmup(oracle, golden_model, monkeypatch):
     """With a warm-up far too short for the recurrences to forget their flat start (8 diagonals) the tile edges disagree:
-    the guard must flag them, the affected jobs are re-run sequentially inside the call, and the lists are the oracle's.
+    the guard must flag them, the tiles concerned run again with a longer warm-up (or their jobs sequentially) inside the
+    call, and the lists are the oracle's.
     With the guard off the same setting produces wrong weights (which is what the guard is for)."""
     pm = golden_model("r94g360")
     rng = np.random.default_rng(4242)
@@ -323,7 +326,7 @@ def test_seam_guard_catches_an_unconverged_warmup(oracle, golden_model, monkeypa
     monkeypatch.setenv("MARGIN_B200_WARMUP", "8")
     al = PairHmmAligner(pm.models, pm.p, device=0)
     got = al.posteriors_batch(items, True)
-    assert got.stats["guard_failures"] > 0 and got.stats["sequential_cells"] > 0, got.stats
+    assert got.stats["guard_failures"] > 0, got.stats  # repaired in place (longer warm-up) or swept sequentially
     for i in range(len(items)):
         compare_lists(got[i], refs[i], tol_w=1)
     al.close()
