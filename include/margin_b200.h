@@ -182,6 +182,15 @@ int margin_b200_set_params(margin_b200_ctx *ctx, const margin_b200_params *param
 /* CUDA events around every kernel launch, read back with margin_b200_last_kernel_ms (default off: measurement
  * only, two driver calls per launch). */
 int margin_b200_set_kernel_timing(margin_b200_ctx *ctx, int on);
+/* Arithmetic of the lane-group tile kernels (default MARGIN_B200_F64, or the environment's MARGIN_B200_PRECISION).
+ *   F64  the reference's own arithmetic (impl/pairwiseAligner.c is double throughout): every add and multiply in the
+ *        reference's order; tuple weights equal the reference's up to one unit of 1e-7.
+ *   F32  cell values in FP32, renormalised every 32 diagonals, same piece-wise cubic logAdd: posteriors within 1e-4 of
+ *        the reference's (BASELINE.json north_star), about twice the throughput.  Tiles wider than 32 cells, sequential
+ *        sweeps and margin_b200_forward_batch stay FP64 in both modes. */
+enum { MARGIN_B200_F64 = 0, MARGIN_B200_F32 = 1 };
+int margin_b200_set_precision(margin_b200_ctx *ctx, int precision);
+int margin_b200_get_precision(margin_b200_ctx *ctx);
 /* Tuple format of the results of this context (default MARGIN_B200_PAIRS_TRIPLES). */
 int margin_b200_set_pair_format(margin_b200_ctx *ctx, int format);
 

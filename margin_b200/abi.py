@@ -77,6 +77,7 @@ class BatchStruct(C.Structure):
 
 PAIR_DTYPE = np.dtype([("w", "<i4"), ("x", "<i4"), ("y", "<i4")])
 PAIRS_TRIPLES, PAIRS_PACKED64 = 0, 1  # MARGIN_B200_PAIRS_*
+F64, F32 = 0, 1  # MARGIN_B200_F64 / MARGIN_B200_F32 (margin_b200_set_precision)
 
 
 def unpack_pairs(words):
@@ -217,6 +218,10 @@ def load_library():
     lib.margin_b200_set_kernel_timing.restype = i32
     lib.margin_b200_set_pair_format.argtypes = [vp, i32]
     lib.margin_b200_set_pair_format.restype = i32
+    lib.margin_b200_set_precision.argtypes = [vp, i32]
+    lib.margin_b200_set_precision.restype = i32
+    lib.margin_b200_get_precision.argtypes = [vp]
+    lib.margin_b200_get_precision.restype = i32
     lib.margin_b200_posteriors_batch.argtypes = [vp, C.POINTER(BatchStruct), i32, C.POINTER(ResultStruct)]
     lib.margin_b200_posteriors_batch.restype = i32
     lib.margin_b200_upload_batch.argtypes = [vp, C.POINTER(BatchStruct)]
@@ -239,7 +244,8 @@ def load_library():
 
 EXPORTED_SYMBOLS = [
     "margin_b200_create", "margin_b200_destroy", "margin_b200_last_error", "margin_b200_version",
-    "margin_b200_set_model", "margin_b200_set_params", "margin_b200_set_pair_format", "margin_b200_set_kernel_timing", "margin_b200_posteriors_batch",
+    "margin_b200_set_model", "margin_b200_set_params", "margin_b200_set_pair_format", "margin_b200_set_precision",
+    "margin_b200_get_precision", "margin_b200_set_kernel_timing", "margin_b200_posteriors_batch",
     "margin_b200_upload_batch", "margin_b200_posteriors_resident", "margin_b200_download_result",
     "margin_b200_forward_batch", "margin_b200_forward_resident", "margin_b200_bands",
     "margin_b200_last_kernel_ms", "margin_b200_device_count", "margin_b200_prewarm",

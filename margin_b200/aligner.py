@@ -124,13 +124,17 @@ class PairHmmAligner:
         out["tuple_bytes"] = 8 if res.pair_format == abi.PAIRS_PACKED64 else 12
         return out
 
+    def set_precision(self, precision):
+        """abi.F64 (the reference's arithmetic) or abi.F32 (renormalised FP32 tile kernels, |dp| <= 1e-4)."""
+        self._check(self.lib.margin_b200_set_precision(self._h, int(precision)))
+
     def arithmetic(self):
-        """Arithmetic type of the DP kernels."""
-        return "f64"
+        """Arithmetic type of the lane-group tile kernels."""
+        return "f32" if self.lib.margin_b200_get_precision(self._h) == abi.F32 else "f64"
 
     def f_bytes_per_cell(self):
-        """Bytes of forward state per band cell that cross HBM in each direction (3 doubles)."""
-        return 24.0
+        """Bytes of forward state per band cell that cross HBM in each direction (3 doubles, or one float4)."""
+        return 16.0 if self.arithmetic() == "f32" else 24.0
 
     def launches_per_step(self, kernel_class):
         """Launches of a kernel class per call: one per lane-group width (8/16/32) that has jobs."""

@@ -23,7 +23,7 @@
 #include <cub/device/device_scan.cuh>
 
 #include "../../include/margin_b200.h"
-#include "pairhmm_tiles.cuh"
+#include "pairhmm_tiles_f32.cuh"
 
 namespace {
 
@@ -188,6 +188,12 @@ struct margin_b200_ctx {
     int guard_failures = 0, guard_reruns = 0;
     bool guard_stats = false;            // MARGIN_B200_GUARD_STATS=1: histogram of the seam differences on stderr
     DevBuf d_guard_worst, d_class_cells;
+    // FP32 fast mode (pairhmm_tiles_f32.cuh): lane-group tiles in FP32 with renormalisation, F as float4
+    bool f32 = false;                    // margin_b200_set_precision / MARGIN_B200_PRECISION=f32
+    bool warmup_env = false;             // MARGIN_B200_WARMUP pins the warm-up for both precisions
+    double guard_tol32 = 1e-3;
+    float v_thr_f = 0.f;
+    DevBuf d_F32, d_shiftF, d_emit_f[2], d_emit_f_ptrs;
     PinBuf h_stage_in, h_small, h_out, h_off, h_gaps;
     // anchor-free stretches reported by the band kernel (sorted by job, start); see build_tiles
     std::vector<mb::AnchorGap> gaps;
@@ -379,7 +385,12 @@ int margin_b200_create(margin_b200_ctx **out, int device) {
                                                          kTileThreads, 0));
         c->bwd_slots = sms * per_sm * (kTileThreads / 8);
     }
-    if (const char *e = getenv("MARGIN_B200_WARMUP")) c->warmup = std::max(1, atoi(e));
+    if (const char *e = getenv("MARGIN_B200_WARMUP")) {
+        c->warmup = std::max(1, atoi(e));
+        c->warmup_env = true;
+    }
+    if (const char *e = getenv("MARGIN_B200_PRECISION")) margin_b200_set_precision(c, strcmp(e, "f32") == 0 ? MARGIN_B200_F32 : MARGIN_B200_F64);
+    if (const char *e = getenv("MARGIN_B200_GUARD_TOL32")) c->guard_tol32 = atof(e);
     if (const char *e = getenv("MARGIN_B200_GAP_MIN")) c->gap_min = std::max(1, atoi(e));
     if (const char *e = getenv("MARGIN_B200_GUARD")) c->guard_on = atoi(e) != 0;
     if (const char *e = getenv("MARGIN_B200_GUARD_TOL")) c->guard_tol = atof(e);
@@ -401,7 +412,8 @@ void margin_b200_destroy(margin_b200_ctx *c) {
     DevBuf *bufs[] = {&c->d_models, &c->d_rsm[0], &c->d_rsm[1], &c->d_symx, &c->d_symy, &c->d_anchors, &c->d_jobs,
                       &c->d_kl, &c->d_kr, &c->d_cell_off, &c->d_job_cells, &c->d_job_maxw, &c->d_job_nseg, &c->d_err,
                       &c->d_segs, &c->d_seg_counts, &c->d_seg_off, &c->d_scan_tmp, &c->d_slot_ring_off, &c->d_ring,
-                      &c->d_ids, &c->d_aln_first_slot, &c->d_F, &c->d_Fpriv, &c->d_guard_worst, &c->d_class_cells, &c->d_stage, &c->d_out, &c->d_off_out, &c->d_fwd_out,
+                      &c->d_ids, &c->d_aln_first_slot, &c->d_F, &c->d_Fpriv, &c->d_guard_worst, &c->d_class_cells, &c->d_F32, &c->d_shiftF, &c->d_emit_f[0], &c->d_emit_f[1],
+                      &c->d_emit_f_ptrs, &c->d_stage, &c->d_out, &c->d_off_out, &c->d_fwd_out,
                       &c->d_geo, &c->d_tiles, &c->d_bnd, &c->d_slot_bnd_off, &c->d_emit5[0], &c->d_emit5[1],
                       &c->d_px, &c->d_py, &c->d_stage2, &c->d_chunks, &c->d_job_first_chunk, &c->d_chunk_sum, &c->d_chunk_maxw,
                       &c->d_totals, &c->d_band_out, &c->d_anchors_delta, &c->d_sym_err, &c->d_tiny_ids, &c->d_chunks_fwd, &c->d_job_first_chunk_fwd, &c->d_arena, &c->d_offs, &c->d_status};
@@ -488,6 +500,12 @@ int margin_b200_set_model(margin_b200_ctx *c, int slot, const margin_b200_model 
             }
         if (c->d_emit5[slot].ensure(ep.size() * sizeof(double))) return 1;
         CU(cudaMemcpyAsync(c->d_emit5[slot].p, ep.data(), ep.size() * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+        // the same table in FP32 for the fast tile kernels, and the two tables' addresses
+        std::vector<float> epf(ep.begin(), ep.end());
+        if (c->d_emit_f[slot].ensure(epf.size() * sizeof(float)) || c->d_emit_f_ptrs.ensure(2 * sizeof(float *))) return 1;
+        CU(cudaMemcpyAsync(c->d_emit_f[slot].p, epf.data(), epf.size() * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+        const float *ptrs[2] = {c->d_emit_f[0].as<float>(), c->d_emit_f[1].as<float>()};
+        CU(cudaMemcpyAsync(c->d_emit_f_ptrs.p, ptrs, sizeof(ptrs), cudaMemcpyHostToDevice, c->stream));
         CU(cudaStreamSynchronize(c->stream));
         d.emit_packed = c->d_emit5[slot].as<double>();
     }
@@ -525,8 +543,28 @@ int margin_b200_set_params(margin_b200_ctx *c, const margin_b200_params *p) {
         CU(cudaStreamSynchronize(c->stream));
         CU(cudaGetLastError());
     }
+    // the same threshold for FP32 log posteriors: the smallest float that is not below it
+    c->v_thr_f = (float) c->v_thr;
+    if ((double) c->v_thr_f < c->v_thr) c->v_thr_f = std::nextafterf(c->v_thr_f, INFINITY);
     return 0;
 }
+
+int margin_b200_set_precision(margin_b200_ctx *c, int precision) {
+    if (!c) return fail("margin_b200_set_precision: null context");
+    if (precision != MARGIN_B200_F64 && precision != MARGIN_B200_F32) return fail("margin_b200_set_precision: unknown precision %d", precision);
+    c->f32 = precision == MARGIN_B200_F32;
+    if (!c->warmup_env) c->warmup = c->f32 ? 128 : 192;
+    int sms = 0, per_sm = 0;
+    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device) == cudaSuccess) {
+        if (c->f32) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, mb::backward_tile_kernel_f<8, kTileThreads, true, false, true>, kTileThreads, 0);
+        else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, mb::backward_tile_kernel<8, kTileThreads, true, false, true>, kTileThreads, 0);
+        if (per_sm > 0) c->bwd_slots = sms * per_sm * (kTileThreads / 8);
+    }
+    for (margin_b200_ctx *sub : c->subs) margin_b200_set_precision(sub, precision);
+    return 0;
+}
+
+int margin_b200_get_precision(margin_b200_ctx *c) { return c && c->f32 ? MARGIN_B200_F32 : MARGIN_B200_F64; }
 
 int margin_b200_set_kernel_timing(margin_b200_ctx *c, int on) {
     if (!c) return fail("margin_b200_set_kernel_timing: null context");
@@ -1013,18 +1051,29 @@ int pick_tile_len(margin_b200_ctx *c) {
     const int64_t n_min = std::max<int64_t>(1, (T + slots * Lmax - 1) / (slots * Lmax));
     int best_L = Lmax;
     double best_cost = 1e300;
-    for (int64_t n = n_min; n <= n_min + 1; n++) {
-        // the length at which ~n waves are full; its neighbours absorb the per-segment remainders
-        const int64_t L0 = (T / (n * slots) + 9) / 10 * 10;
-        for (int dl = 0; dl <= 40; dl += 20) {
-            const int L = (int) std::min<int64_t>(Lmax, std::max<int64_t>(Lmin, L0 + dl));
-            int64_t cnt = 0;
-            for (int32_t sp : spans) cnt += tiles_of_span(sp, L);
-            const double cost = (double) ((cnt + slots - 1) / slots) * (L + W);
-            if (cost < best_cost) {
-                best_cost = cost;
-                best_L = L;
+    auto count = [&](int L) {
+        int64_t cnt = 0;
+        for (int32_t sp : spans) cnt += tiles_of_span(sp, L);
+        return cnt;
+    };
+    for (int64_t n = n_min; n <= n_min + 2; n++) {
+        // the shortest length whose tiles fit n waves: start where n waves would be exactly full and grow until the
+        // per-segment remainders fit too (a launch takes about waves x (L + W) steps)
+        int L = (int) std::min<int64_t>(Lmax, std::max<int64_t>(Lmin, (T / (n * slots) + 9) / 10 * 10));
+        int64_t cnt = count(L);
+        if (cnt > n * slots && L < Lmax) {  // bisect [L, min(Lmax, L + 640)] in steps of 10 (the count falls as L grows)
+            int lo = L / 10, hi = std::min(Lmax, L + 640) / 10;
+            while (lo < hi) {
+                const int mid = (lo + hi) / 2;
+                if (count(mid * 10) > n * slots) lo = mid + 1; else hi = mid;
             }
+            L = lo * 10;
+            cnt = count(L);
+        }
+        const double cost = (double) ((cnt + slots - 1) / slots) * (L + W);
+        if (cost < best_cost) {
+            best_cost = cost;
+            best_L = L;
         }
     }
     return best_L;
@@ -1088,6 +1137,13 @@ void build_tiles(margin_b200_ctx *c, int L) {
     const int gmax = c->force_group ? c->force_group : 32;  // widest diagonal the lane-group tile kernels take
     size_t gap_at = 0;  // c->gaps is sorted by job and jobs are visited in ascending order
     c->tile_len_used = L;
+    {
+        const size_t guess = (size_t) (c->total_diag / std::max(L, 1)) + 2 * c->segs.size() + 16;
+        c->tiles.reserve(guess);
+        c->tile_maxw.reserve(guess);
+        c->tile_seg.reserve(guess);
+        c->seams.reserve(2 * guess);
+    }
     c->tiles.clear();
     c->tile_maxw.clear();
     c->tile_seg.clear();
@@ -1395,10 +1451,16 @@ template <int G, bool SW>
 void launch_forward_tiles2(margin_b200_ctx *c, int off, int count) {
     const int per_block = kTileThreads / G;
     KTimer kt_(c, K_FORWARD);
-    mb::forward_tile_kernel<G, kTileThreads, SW><<<(count + per_block - 1) / per_block, kTileThreads, 0, c->stream>>>(
-        c->d_jobs.as<mb::Job>(), c->p_tiles, c->p_ids + off, count,
-        c->d_models.as<mb::DevModel>(), c->d_px.as<uint8_t>() + mb::PACK_SLACK, c->d_py.as<uint8_t>() + mb::PACK_SLACK,
-        c->d_geo.as<int2>(), c->d_F.as<double>(), c->d_bnd.as<double>(), c->p_bnd_off);
+    if (c->f32)
+        mb::forward_tile_kernel_f<G, kTileThreads, SW><<<(count + per_block - 1) / per_block, kTileThreads, 0, c->stream>>>(
+            c->d_jobs.as<mb::Job>(), c->p_tiles, c->p_ids + off, count, c->d_models.as<mb::DevModel>(),
+            c->d_emit_f_ptrs.as<const float *>(), c->d_px.as<uint8_t>() + mb::PACK_SLACK, c->d_py.as<uint8_t>() + mb::PACK_SLACK,
+            c->d_geo.as<int2>(), c->d_F32.as<float>(), c->d_bnd.as<float>(), c->p_bnd_off, c->d_shiftF.as<float>());
+    else
+        mb::forward_tile_kernel<G, kTileThreads, SW><<<(count + per_block - 1) / per_block, kTileThreads, 0, c->stream>>>(
+            c->d_jobs.as<mb::Job>(), c->p_tiles, c->p_ids + off, count,
+            c->d_models.as<mb::DevModel>(), c->d_px.as<uint8_t>() + mb::PACK_SLACK, c->d_py.as<uint8_t>() + mb::PACK_SLACK,
+            c->d_geo.as<int2>(), c->d_F.as<double>(), c->d_bnd.as<double>(), c->p_bnd_off);
     c->launches++;
 }
 
@@ -1427,11 +1489,18 @@ template <int G, bool INDELS, bool SW, bool GUARD>
 void launch_backward_tiles3(margin_b200_ctx *c, int off, int count, int64_t stage_stride) {
     const int per_block = kTileThreads / G;
     KTimer kt_(c, K_BACKWARD);
-    mb::backward_tile_kernel<G, kTileThreads, INDELS, SW, GUARD><<<(count + per_block - 1) / per_block, kTileThreads, 0, c->stream>>>(
-        c->d_jobs.as<mb::Job>(), c->p_tiles, c->p_ids + off, count,
-        c->d_models.as<mb::DevModel>(), c->d_px.as<uint8_t>() + mb::PACK_SLACK, c->d_py.as<uint8_t>() + mb::PACK_SLACK,
-        c->d_geo.as<int2>(), c->d_F.as<double>(), c->d_bnd.as<double>(), c->p_bnd_off, c->v_thr,
-        c->d_stage2.as<mb::StagedPair>(), stage_stride, c->d_seg_counts.as<int64_t>(), c->total_slots);
+    if (c->f32)
+        mb::backward_tile_kernel_f<G, kTileThreads, INDELS, SW, GUARD><<<(count + per_block - 1) / per_block, kTileThreads, 0, c->stream>>>(
+            c->d_jobs.as<mb::Job>(), c->p_tiles, c->p_ids + off, count, c->d_models.as<mb::DevModel>(),
+            c->d_emit_f_ptrs.as<const float *>(), c->d_px.as<uint8_t>() + mb::PACK_SLACK, c->d_py.as<uint8_t>() + mb::PACK_SLACK,
+            c->d_geo.as<int2>(), c->d_F32.as<float>(), c->d_bnd.as<float>(), c->p_bnd_off, c->d_shiftF.as<float>(), c->v_thr_f,
+            c->d_stage2.as<mb::StagedPair>(), stage_stride, c->d_seg_counts.as<int64_t>(), c->total_slots);
+    else
+        mb::backward_tile_kernel<G, kTileThreads, INDELS, SW, GUARD><<<(count + per_block - 1) / per_block, kTileThreads, 0, c->stream>>>(
+            c->d_jobs.as<mb::Job>(), c->p_tiles, c->p_ids + off, count,
+            c->d_models.as<mb::DevModel>(), c->d_px.as<uint8_t>() + mb::PACK_SLACK, c->d_py.as<uint8_t>() + mb::PACK_SLACK,
+            c->d_geo.as<int2>(), c->d_F.as<double>(), c->d_bnd.as<double>(), c->p_bnd_off, c->v_thr,
+            c->d_stage2.as<mb::StagedPair>(), stage_stride, c->d_seg_counts.as<int64_t>(), c->total_slots);
     c->launches++;
 }
 
@@ -1565,8 +1634,9 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
             KTimer kt_(c, K_GUARD);
             mb::guard_check_kernel<<<(n_seams + 3) / 4, 128, 0, c->stream>>>(
                 c->d_jobs.as<mb::Job>(), c->p_tiles, c->p_seams, n_seams, c->d_geo.as<int2>(), c->d_F.as<double>(),
-                c->d_Fpriv.as<double>(), c->d_bnd.as<double>(), c->p_bnd_off, c->guard_tol, c->guard_floor, c->p_guard_flags,
-                c->p_guard_flags + n_seams, c->guard_stats ? c->d_guard_worst.as<float>() : nullptr);
+                c->d_F32.as<float>(), c->d_Fpriv.as<double>(), c->d_bnd.as<double>(), c->p_bnd_off, c->f32 ? 1 : 0, c->guard_tol,
+                c->guard_tol32, c->guard_floor, c->p_guard_flags, c->p_guard_flags + n_seams,
+                c->guard_stats ? c->d_guard_worst.as<float>() : nullptr);
             c->launches++;
         }
         return 0;
@@ -1655,7 +1725,11 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
             else any_generic = true;
         }
         stage_stride = c->stage_cells + 1;  // general kernels: private regions (Tile::stage_off)
-        if (c->d_F.ensure((size_t) (cells + 1) * 3 * sizeof(double)) ||
+        bool any_sequential = false;  // whole jobs swept by the general kernels keep their F in the FP64 array
+        for (const mb::Tile &t : c->tiles) any_sequential |= !(t.flags & (mb::TILE_BND | mb::TILE_WIDE));
+        if (((!c->f32 || any_sequential) && c->d_F.ensure((size_t) (cells + 1) * 3 * sizeof(double))) ||
+            (c->f32 && (c->d_F32.ensure((size_t) (cells + 1) * 4 * sizeof(float)) ||
+                        c->d_shiftF.ensure((size_t) (c->total_diag + 1) * sizeof(float)))) ||
             c->d_Fpriv.ensure((size_t) (c->priv_cells + 1) * 3 * sizeof(double)) ||
             (any_generic && c->d_stage.ensure((size_t) stage_stride * n_lists * sizeof(mb::Pair))) ||
             (any_tiled && c->d_stage2.ensure((size_t) (cells + 1) * n_lists * sizeof(mb::StagedPair))) ||
@@ -1803,6 +1877,9 @@ int ensure_subs(margin_b200_ctx *c, int K) {
         sub->kernel_timing = c->kernel_timing;
         sub->guard_on = c->guard_on;
         sub->guard_tol = c->guard_tol;
+        sub->guard_tol32 = c->guard_tol32;
+        sub->f32 = c->f32;
+        sub->repair_factor = c->repair_factor;
         sub->gap_min = c->gap_min;
         // Tile length of a run: with bwd_slots / K every run is cut as if it owned 1/K of the SMs (same tiles as the
         // unpipelined call); a larger share means shorter tiles, i.e. a run finishes sooner (its lists reach the host

@@ -712,8 +712,9 @@ __global__ void gather_staged_kernel(const Job *__restrict__ jobs, const Tile *_
 // One warp per seam.
 __global__ void guard_check_kernel(const Job *__restrict__ jobs, const Tile *__restrict__ tiles,
                                    const Seam *__restrict__ seams, int n_seams, const int2 *__restrict__ geo,
-                                   const double *__restrict__ F, const double *__restrict__ Fpriv,
-                                   const double *__restrict__ bnd, const int64_t *__restrict__ slot_bnd_off, double tol,
+                                   const double *__restrict__ F, const float *__restrict__ F32,
+                                   const double *__restrict__ Fpriv, const double *__restrict__ bnd,
+                                   const int64_t *__restrict__ slot_bnd_off, int f32, double tol, double tol32,
                                    double floor_gap, int32_t *__restrict__ flags, int32_t *__restrict__ n_failed,
                                    float *__restrict__ worst_out /* may be null: largest difference per seam */) {
     const int k = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -725,24 +726,41 @@ __global__ void guard_check_kernel(const Job *__restrict__ jobs, const Tile *__r
     const int2 *gj = geo + job.diag_off;
     const int64_t cod = (uint32_t) gj[sm.d].y;
     const int w = (int) ((uint32_t) gj[sm.d + 1].y - (uint32_t) gj[sm.d].y);
+    // A copy of a diagonal: FP64 cells of three doubles (general kernels, FP64 tile kernels) or, with the FP32 tile
+    // kernels (f32), float4 cells for everything a lane-group tile stores.
+    struct Side {
+        const void *p;
+        bool is_float;
+        __device__ double at(int i) const {
+            return is_float ? (double) reinterpret_cast<const float *>(p)[4 * (i / 3) + i % 3] : reinterpret_cast<const double *>(p)[i];
+        }
+    };
     auto sect = [&](int slot, int which) {
         const int64_t cells = (slot_bnd_off[slot + 1] - slot_bnd_off[slot]) / 3;
-        return bnd + 3 * (slot_bnd_off[slot] + which * cells);
+        const int64_t cell = slot_bnd_off[slot] + which * cells;
+        const bool fl = f32 && (tiles[slot].flags & TILE_BND);
+        return Side{fl ? (const void *) (reinterpret_cast<const float *>(bnd) + 4 * cell) : (const void *) (bnd + 3 * cell), fl};
     };
-    auto priv_at = [&](const Tile &t) { return Fpriv + 3 * (t.priv_off - (int64_t) (uint32_t) gj[t.f0].y + cod); };
-    const double *conv, *warm;  // the copy at the end of a long sweep / the copy at the end of a warm-up
+    auto priv_at = [&](const Tile &t) {
+        return Side{Fpriv + 3 * (t.priv_off - (int64_t) (uint32_t) gj[t.f0].y + cod), false};
+    };
+    auto shared_at = [&]() {
+        return f32 ? Side{F32 + 4 * (job.cell_base + cod), true} : Side{F + 3 * (job.cell_base + cod), false};
+    };
+    Side conv, warm;  // the copy at the end of a long sweep / the copy at the end of a warm-up
     if (!sm.backward) {
-        conv = (lo.flags & TILE_WIDE) ? priv_at(lo) : F + 3 * (job.cell_base + cod);
+        conv = (lo.flags & TILE_WIDE) ? priv_at(lo) : shared_at();
         warm = (up.flags & TILE_WIDE) ? priv_at(up) : sect(sm.upper, BND_F);
     } else {
         conv = sect(sm.upper, BND_B_LOW);
         warm = sect(sm.lower, BND_B_HIGH);
     }
+    if (conv.is_float || warm.is_float) tol = tol32;
     // largest value of the converged copy and where it is
     double best = MB_NEG_INF;
     int at = -1;
     for (int i = lane; i < 3 * w; i += 32) {
-        const double v = conv[i];
+        const double v = conv.at(i);
         if (v > best) {
             best = v;
             at = i;
@@ -759,13 +777,13 @@ __global__ void guard_check_kernel(const Job *__restrict__ jobs, const Tile *__r
     bool bad = false;
     double worst = 0.0;
     if (at < 0) {  // nothing finite: the other copy must be empty as well
-        for (int i = lane; i < 3 * w; i += 32) bad |= warm[i] != MB_NEG_INF;
+        for (int i = lane; i < 3 * w; i += 32) bad |= warm.at(i) != MB_NEG_INF;
     } else {
-        const double shift = warm[at] - best;
+        const double shift = warm.at(at) - best;
         if (!(fabs(shift) < 1e300)) bad = true;
         for (int i = lane; i < 3 * w; i += 32) {
-            const double a = conv[i], b = warm[i] - shift;
-            if (a == MB_NEG_INF && warm[i] == MB_NEG_INF) continue;
+            const double a = conv.at(i), wv = warm.at(i), b = wv - shift;
+            if (a == MB_NEG_INF && wv == MB_NEG_INF) continue;
             if (a < best - floor_gap && b < best - floor_gap) continue;
             const double diff = fabs(a - b);
             if (!(diff <= tol)) bad = true;
