@@ -267,9 +267,28 @@ typedef struct {
     uint8_t *slot, *raggedL, *raggedR;
 } B200Batch;
 
+/* One retired set of bulk arrays per thread, so that a batch (of one, often) does not page-lock memory on every call. */
+static __thread struct {
+    uint16_t *symX, *symY;
+    int32_t *anchors;
+    uint32_t *anchorsDelta;
+    int64_t capX, capY, capA;
+    int full;
+} b200_spare;
+
 static B200Batch *b200_batch_construct(int64_t n) {
     B200Batch *b = st_calloc(1, sizeof(B200Batch));
     b->compactOk = 1;
+    if (b200_spare.full) {
+        b->symX = b200_spare.symX;
+        b->symY = b200_spare.symY;
+        b->anchors = b200_spare.anchors;
+        b->anchorsDelta = b200_spare.anchorsDelta;
+        b->capX = b200_spare.capX;
+        b->capY = b200_spare.capY;
+        b->capA = b200_spare.capA;
+        b200_spare.full = 0;
+    }
     b->capN = n < 1 ? 1 : n;
     b->offX = st_calloc(b->capN + 1, sizeof(int64_t));
     b->offY = st_calloc(b->capN + 1, sizeof(int64_t));
@@ -292,11 +311,34 @@ static void b200_batch_grow(B200Batch *b) {
     b->raggedR = st_realloc(b->raggedR, b->capN + 1);
 }
 
+/* The arrays that cross PCIe (symbols, compact anchor words) live in page-locked memory (margin_b200_pinned_alloc):
+ * the copies to the device are then asynchronous DMA instead of the driver's staged pageable path. */
+static void *b200_pinned_grow(void *old, int64_t oldBytes, int64_t newBytes) {
+    void *p = margin_b200_pinned_alloc((size_t) newBytes);
+    if (p == NULL) b200_fail();
+    if (old != NULL) {
+        memcpy(p, old, (size_t) oldBytes);
+        margin_b200_pinned_free(old);
+    }
+    return p;
+}
+
 static void b200_batch_destruct(B200Batch *b) {
-    free(b->symX);
-    free(b->symY);
-    free(b->anchors);
-    free(b->anchorsDelta);
+    if (!b200_spare.full) {
+        b200_spare.symX = b->symX;
+        b200_spare.symY = b->symY;
+        b200_spare.anchors = b->anchors;
+        b200_spare.anchorsDelta = b->anchorsDelta;
+        b200_spare.capX = b->capX;
+        b200_spare.capY = b->capY;
+        b200_spare.capA = b->capA;
+        b200_spare.full = 1;
+    } else {
+        margin_b200_pinned_free(b->symX);
+        margin_b200_pinned_free(b->symY);
+        free(b->anchors);
+        margin_b200_pinned_free(b->anchorsDelta);
+    }
     free(b->offX);
     free(b->offY);
     free(b->offA);
@@ -314,17 +356,20 @@ static void b200_batch_add(B200Batch *b, SymbolString sX, SymbolString sY, stLis
     int64_t nA = anchorPairs == NULL ? 0 : stList_length(anchorPairs);
     int64_t oX = b->offX[i], oY = b->offY[i], oA = b->offA[i];
     if (oX + sX.length > b->capX) {
-        b->capX = (oX + sX.length) * 2 + 1024;
-        b->symX = st_realloc(b->symX, b->capX * sizeof(uint16_t));
+        int64_t cap = (oX + sX.length) * 2 + 1024;
+        b->symX = b200_pinned_grow(b->symX, oX * sizeof(uint16_t), cap * sizeof(uint16_t));
+        b->capX = cap;
     }
     if (oY + sY.length > b->capY) {
-        b->capY = (oY + sY.length) * 2 + 1024;
-        b->symY = st_realloc(b->symY, b->capY * sizeof(uint16_t));
+        int64_t cap = (oY + sY.length) * 2 + 1024;
+        b->symY = b200_pinned_grow(b->symY, oY * sizeof(uint16_t), cap * sizeof(uint16_t));
+        b->capY = cap;
     }
     if (oA + nA > b->capA) {
-        b->capA = (oA + nA) * 2 + 1024;
-        b->anchors = st_realloc(b->anchors, b->capA * 3 * sizeof(int32_t));
-        b->anchorsDelta = st_realloc(b->anchorsDelta, b->capA * sizeof(uint32_t));
+        int64_t cap = (oA + nA) * 2 + 1024;
+        b->anchors = st_realloc(b->anchors, cap * 3 * sizeof(int32_t));
+        b->anchorsDelta = b200_pinned_grow(b->anchorsDelta, oA * sizeof(uint32_t), cap * sizeof(uint32_t));
+        b->capA = cap;
     }
     memcpy(b->symX + oX, sX.sequence, sX.length * sizeof(uint16_t)); /* Symbol is uint16_t, inc/stateMachine.h:15 */
     memcpy(b->symY + oY, sY.sequence, sY.length * sizeof(uint16_t));

@@ -218,6 +218,10 @@ def load_library():
     lib.margin_b200_set_kernel_timing.restype = i32
     lib.margin_b200_set_pair_format.argtypes = [vp, i32]
     lib.margin_b200_set_pair_format.restype = i32
+    lib.margin_b200_pinned_alloc.argtypes = [C.c_size_t]
+    lib.margin_b200_pinned_alloc.restype = vp
+    lib.margin_b200_pinned_free.argtypes = [vp]
+    lib.margin_b200_pinned_free.restype = None
     lib.margin_b200_set_precision.argtypes = [vp, i32]
     lib.margin_b200_set_precision.restype = i32
     lib.margin_b200_get_precision.argtypes = [vp]
@@ -245,7 +249,7 @@ def load_library():
 EXPORTED_SYMBOLS = [
     "margin_b200_create", "margin_b200_destroy", "margin_b200_last_error", "margin_b200_version",
     "margin_b200_set_model", "margin_b200_set_params", "margin_b200_set_pair_format", "margin_b200_set_precision",
-    "margin_b200_get_precision", "margin_b200_set_kernel_timing", "margin_b200_posteriors_batch",
+    "margin_b200_get_precision", "margin_b200_pinned_alloc", "margin_b200_pinned_free", "margin_b200_set_kernel_timing", "margin_b200_posteriors_batch",
     "margin_b200_upload_batch", "margin_b200_posteriors_resident", "margin_b200_download_result",
     "margin_b200_forward_batch", "margin_b200_forward_resident", "margin_b200_bands",
     "margin_b200_last_kernel_ms", "margin_b200_device_count", "margin_b200_prewarm",

@@ -62,7 +62,7 @@ struct DevBuf {
         if (p) cudaFree(p);
         p = nullptr;
         cap = 0;
-        size_t want = bytes + bytes / 8 + 256;
+        size_t want = bytes + bytes / 4 + 256;  // geometric growth: a slightly larger chunk must not re-allocate GBs
         cudaError_t e = cudaMalloc(&p, want);
         if (e != cudaSuccess) return fail("cudaMalloc(%zu bytes) failed: %s", want, cudaGetErrorString(e));
         cap = want;
@@ -98,6 +98,15 @@ struct PinBuf {
     }
     template <typename T> T *as() { return reinterpret_cast<T *>(p); }
 };
+
+// The large scratch arrays of a posterior sweep — the forward values, the staged tuples — are only live while a context
+// holds its device's compute token (first DP launch to final synchronisation), so the contexts of one device share
+// ONE set: `margin polish -t 48` on one GPU needs the memory of one sweep, not of 48.  A context that runs without the
+// token (sub-contexts of a pipelined call, the *_resident entry points) uses buffers of its own.
+struct ScratchPool {
+    DevBuf F, F32, shiftF, Fpriv, stage, stage2;
+};
+ScratchPool g_scratch[kMaxDevices];
 
 }  // namespace
 
@@ -145,7 +154,7 @@ struct margin_b200_ctx {
     // ---- pipelined batches (posteriors_pipelined): sub-contexts with their own stream and arenas
     std::vector<margin_b200_ctx *> subs;
     std::unique_ptr<margin_b200_model> user_models[2];  // as given to set_model, replayed into new sub-contexts
-    int pipeline_k = 3;                                 // MARGIN_B200_PIPELINE (1 = off)
+    int pipeline_k = 1;                                 // MARGIN_B200_PIPELINE: in-call pipeline of K runs (opt-in; 1 = off)
     bool pipeline_force = false;                        // MARGIN_B200_PIPELINE_FORCE: pipeline even beside other contexts
     int pipe_fill = 2;                                  // MARGIN_B200_PIPE_FILL: SM share a run's tiles are cut for, in 1/K
     int64_t pipeline_min_bytes = 8 << 20;               // MARGIN_B200_PIPELINE_MIN_BYTES of host input
@@ -339,6 +348,23 @@ int margin_b200_device_count(void) {
     return count;
 }
 
+// Page-locked host memory for the caller's batch arrays: cudaMemcpyAsync from pageable memory is staged by the driver
+// (synchronous, a few GB/s); a host program that assembles its batch in memory from here gets true asynchronous copies.
+void *margin_b200_pinned_alloc(size_t bytes) {
+    void *p = nullptr;
+    if (bytes == 0) bytes = 1;
+    if (cudaMallocHost(&p, bytes) != cudaSuccess) {
+        cudaGetLastError();
+        fail("margin_b200_pinned_alloc: cudaMallocHost(%zu bytes) failed", bytes);
+        return nullptr;
+    }
+    return p;
+}
+
+void margin_b200_pinned_free(void *p) {
+    if (p) cudaFreeHost(p);
+}
+
 int margin_b200_prewarm(void) {
     int count = 0;
     if (cudaGetDeviceCount(&count) != cudaSuccess) return 0;
@@ -349,6 +375,8 @@ int margin_b200_prewarm(void) {
         cudaFuncGetAttributes(&fa, mb::backward_tile_kernel<8, kTileThreads, true, false, true>);
         cudaFuncGetAttributes(&fa, mb::forward_tile_kernel<8, kTileThreads, false>);
         cudaFuncGetAttributes(&fa, mb::tiny_forward_kernel<16, kTileThreads, false>);
+        cudaFuncGetAttributes(&fa, mb::backward_tile_kernel_f<8, kTileThreads, true, false, true>);
+        cudaFuncGetAttributes(&fa, mb::forward_tile_kernel_f<8, kTileThreads, false>);
     }
     cudaGetLastError();
     return count;
@@ -1568,6 +1596,30 @@ void fill_stats(margin_b200_ctx *c, margin_b200_result *out, int64_t segments, f
 
 }  // namespace
 
+namespace {
+// Swaps the device's shared scratch arrays into the context for the duration of a sweep (token held) and back.
+struct ScratchLease {
+    margin_b200_ctx *c = nullptr;
+    void take(margin_b200_ctx *ctx) {
+        if (c) return;
+        c = ctx;
+        swap();
+    }
+    void swap() {
+        ScratchPool &p = g_scratch[c->device & (kMaxDevices - 1)];
+        std::swap(c->d_F, p.F);
+        std::swap(c->d_F32, p.F32);
+        std::swap(c->d_shiftF, p.shiftF);
+        std::swap(c->d_Fpriv, p.Fpriv);
+        std::swap(c->d_stage, p.stage);
+        std::swap(c->d_stage2, p.stage2);
+    }
+    ~ScratchLease() {
+        if (c) swap();
+    }
+};
+}  // namespace
+
 extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_indels, margin_b200_result *out) {
     if (!c || !out) return fail("margin_b200_posteriors_resident: null argument");
     if (check_device(c->device)) return 1;
@@ -1597,13 +1649,13 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
     // Several contexts on one device take turns from the first DP launch to the final synchronisation
     // (margin_b200_posteriors_batch); the band phase above, with its host round trip, runs beside the other context's kernels.
     std::unique_lock<std::mutex> token;
+    ScratchLease lease;  // destroyed before the token is released
 
     // forward + backward launches of one pass (all tiles, or the tiles of a repair pass), then the seam guard
     auto run_dp = [&]() -> int {
         Bins bins;
         if (build_bins(c, true, bins, c->force_group)) return 1;
         tr.mark("bins+h2d");
-        if (c->take_token && !token.owns_lock()) token = std::unique_lock<std::mutex>(g_compute_token[c->device & (kMaxDevices - 1)]);
         CU(cudaStreamWaitEvent(c->stream, c->ev_sym, 0));  // the symbols (upload's second stream) are needed from here on
         launch_forward<8>(c, bins.seq_fwd[0], bins.seq_fwd[1] - bins.seq_fwd[0]);
         launch_forward<16>(c, bins.seq_fwd[1], bins.seq_fwd[2] - bins.seq_fwd[1]);
@@ -1725,6 +1777,10 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
             else any_generic = true;
         }
         stage_stride = c->stage_cells + 1;  // general kernels: private regions (Tile::stage_off)
+        if (c->take_token && !token.owns_lock()) {
+            token = std::unique_lock<std::mutex>(g_compute_token[c->device & (kMaxDevices - 1)]);
+            lease.take(c);
+        }
         bool any_sequential = false;  // whole jobs swept by the general kernels keep their F in the FP64 array
         for (const mb::Tile &t : c->tiles) any_sequential |= !(t.flags & (mb::TILE_BND | mb::TILE_WIDE));
         if (((!c->f32 || any_sequential) && c->d_F.ensure((size_t) (cells + 1) * 3 * sizeof(double))) ||
@@ -1781,7 +1837,6 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
         CU(cudaStreamSynchronize(c->stream));
         CU(cudaGetLastError());
     }
-    if (token.owns_lock()) token.unlock();
     float ms = 0;
     CU(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
     int64_t segments = 0;

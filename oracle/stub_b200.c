@@ -54,6 +54,14 @@ int margin_b200_version(void) { return 100; }
 int margin_b200_device_count(void) { return 1; }
 int margin_b200_prewarm(void) { return 1; }
 
+void *margin_b200_pinned_alloc(size_t bytes) { return malloc(bytes ? bytes : 1); }
+void margin_b200_pinned_free(void *p) { free(p); }
+int margin_b200_set_precision(margin_b200_ctx *c, int precision) {
+    (void) c;
+    (void) precision;
+    return 0;
+}
+
 int margin_b200_create(margin_b200_ctx **out, int device) {
     (void) device;
     *out = calloc(1, sizeof(margin_b200_ctx));
