@@ -174,7 +174,7 @@ int margin_b200_create(margin_b200_ctx **ctx, int device);
  * (impl/polish.c:476 -> impl/poa.c:1955) needs the aligner).  Returns the device count. */
 int margin_b200_prewarm(void);
 void margin_b200_destroy(margin_b200_ctx *ctx);
-/* Page-locked host memory for the arrays of a margin_b200_batch (optional: any host memory works, page-locked memory
+/* Page-locked host memory for the arrays a batch points at; optional: any host memory works, page-locked memory
  * makes the host->device copies asynchronous and several times faster).  NULL on failure (margin_b200_last_error). */
 void *margin_b200_pinned_alloc(size_t bytes);
 void margin_b200_pinned_free(void *p);
