@@ -188,7 +188,9 @@ def main_reference(args):
             dist.barrier()
             dist.destroy_process_group()
         return 0
-    pm, items = build_items(args.workload, args.seed)
+    from margin_b200 import model
+    pm = model.load_flat_model(MODEL_FILE)
+    items = build_chunk(pm, args.seed, 0)  # chunk 0 of the bench contig = BASELINE configs[1]
     threads = host_cores()
     r = time_reference(pm, items, args.steps, args.warmup, threads)
     line = {
@@ -202,6 +204,8 @@ def main_reference(args):
         "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
+    if args.polish_synth > 0:  # the reference's own CLI on the same synthetic contig as our arm's `polish` object
+        line["polish"] = time_polish_synth(args.polish_synth, min(threads, args.polish_threads), args.seed, only_reference=True)
     print(json.dumps(line), flush=True)
     if dist is not None:
         dist.barrier()
@@ -211,16 +215,22 @@ def main_reference(args):
 
 # ---------------------------------------------------------------------------------------------------- our arm
 
-def pin_batch(batch):
-    """Page-locks the batch's host arrays (cudaHostRegister) so that the e2e leg copies from pinned memory."""
-    import torch
-    rt = torch.cuda.cudart()
-    arrays = [batch.sym_x, batch.sym_y, batch.anchors, batch.off_x, batch.off_y, batch.off_a]
-    if batch.compact:
-        arrays.append(batch.anchors_delta)
-    for a in arrays:
-        if a.nbytes:
-            rt.cudaHostRegister(a.ctypes.data, a.nbytes, 0)
+# Chunk lengths of the bench contig, cycled: chunks differ in size (and seed), so arenas, tile cuts and transfer sizes
+# change from step to step the way they do in a real run (polish.c:476 hands every thread chunk after chunk).
+CHUNK_LENGTH_FACTORS = (1.0, 0.8, 1.3, 0.9)
+CHUNK_LEN = 100000
+
+
+def chunk_length(k):
+    return int(CHUNK_LEN * CHUNK_LENGTH_FACTORS[k % len(CHUNK_LENGTH_FACTORS)])
+
+
+def build_chunk(pm, seed, k):
+    """Chunk k of the synthetic contig (BASELINE configs[1] shape: 60x 20 kb ONT-like reads at ~10 % error; chunk 0 is
+    exactly the 100 kb chunk of configs[1] with the bench seed)."""
+    from margin_b200 import synth
+    ch = synth.make_chunk(seed + 1000 * k, chunk_length(k), 60, 20000, synth.ONT, 0.01, int(pm.p.diagonal_expansion))
+    return ch.items(pm)
 
 
 def time_polish(threads):
@@ -261,7 +271,8 @@ def time_polish(threads):
     return out
 
 
-def time_polish_synth(contig_kb, threads, seed=42, skip_reference=False, diploid=False, depth=60, platform="ont"):
+def time_polish_synth(contig_kb, threads, seed=42, skip_reference=False, diploid=False, depth=60, platform="ont", gpus=None,
+                      precision=None, only_reference=False):
     """End-to-end `margin polish` on a SYNTHETIC contig of BASELINE configs[1]/[2]'s shape (60x ONT-like 20 kb reads at
     ~10 % error, r94-g360 params, 100 kb chunks; margin_b200/synth.py: write_polish_dataset + oracle/_ref/sam2bam):
     the unmodified reference CLI and the CLI linked against this library, -t `threads` each (the reference
@@ -291,13 +302,22 @@ def time_polish_synth(contig_kb, threads, seed=42, skip_reference=False, diploid
                "contig_mb": draft_len / 1e6, "reads": n_reads, "threads": threads, "seed": seed,
                "dataset_s": time.perf_counter() - t0}
         arms = (("b200", "margin_b200cli"),) if skip_reference else (("reference", "margin_ref"), ("b200", "margin_b200cli"))
+        if only_reference:
+            arms = (("reference", "margin_ref"),)
+        env = dict(os.environ)
+        if gpus:  # the binding maps OpenMP thread t to device t % (visible devices)
+            env["CUDA_VISIBLE_DEVICES"] = ",".join(str(i) for i in range(gpus))
+            out["gpus"] = gpus
+        if precision:
+            env["MARGIN_B200_PRECISION"] = precision
+            out["precision"] = precision
         for key, binary in arms:
             prefix = os.path.join(tmp, key)
             cmd = [os.path.join(ref, binary), "polish", bam, fa, params, "-t", str(threads), "-o", prefix]
             if diploid:
                 cmd.append("-2")  # phasing bubble graphs, then one polished FASTA per haplotype (<prefix>.fa.hap1/.hap2)
             t0 = time.perf_counter()
-            r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=3000)
+            r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=3000, env=env)
             dt = time.perf_counter() - t0
             if r.returncode != 0:
                 out[key] = {"error": r.stdout[-300:]}
@@ -318,20 +338,22 @@ def abi_mod():
     return abi
 
 
-def time_sustained(pm, batch, device, cell_passes_rank, contexts=3, rounds=4):
-    """`contexts` aligner contexts on one GPU, one host thread each, every thread pushes `rounds` chunks (the bench
-    chunk, host buffers in, host lists out) through margin_b200_posteriors_batch back to back."""
+def time_sustained(pm, batches, cells, device, precision, contexts=3, min_seconds=2.0):
+    """`contexts` aligner contexts on one GPU, one host thread each; every thread pushes this rank's chunks, one after the
+    other and round after round, through margin_b200_posteriors_batch (host buffers in, host lists out) until
+    `min_seconds` have passed: how margin's OpenMP chunk loop drives the aligner (polish.c:476)."""
+    from margin_b200 import abi
     from margin_b200.aligner import PairHmmAligner
     als = [PairHmmAligner(pm.models, pm.p, device=device) for _ in range(contexts)]
     for al in als:
-        if batch.compact:
-            al.set_pair_format(abi_mod().PAIRS_PACKED64)
+        al.set_precision(precision)
+        al.set_pair_format(abi.PAIRS_PACKED64)
     warm = threading.Barrier(contexts)
 
-    def warm_up(al):  # sizes the arenas of both call paths (alone on the device / beside another context)
-        al.posteriors_host(batch, True)
+    def warm_up(al):  # every context sees every chunk once (arenas reach their steady size)
+        for b in batches:
+            al.posteriors_host(b, True)
         warm.wait()
-        al.posteriors_host(batch, True)
 
     ws = [threading.Thread(target=warm_up, args=(al,)) for al in als]
     for t in ws:
@@ -339,21 +361,29 @@ def time_sustained(pm, batch, device, cell_passes_rank, contexts=3, rounds=4):
     for t in ws:
         t.join()
     start = threading.Barrier(contexts + 1)
-    errs = []
+    errs, done = [], [0.0] * contexts
+    calls = [0] * contexts
+    stop = [False]
 
-    def worker(al):
+    def worker(i, al):
         try:
             start.wait()
-            for _ in range(rounds):
-                al.posteriors_host(batch, True)
+            k = i
+            while not stop[0]:
+                al.posteriors_host(batches[k % len(batches)], True)
+                done[i] += 2.0 * cells[k % len(batches)]
+                calls[i] += 1
+                k += 1
         except Exception as e:  # noqa: BLE001
             errs.append(e)
 
-    ths = [threading.Thread(target=worker, args=(al,)) for al in als]
+    ths = [threading.Thread(target=worker, args=(i, al)) for i, al in enumerate(als)]
     for t in ths:
         t.start()
     start.wait()
     t0 = time.perf_counter()
+    time.sleep(min_seconds)
+    stop[0] = True
     for t in ths:
         t.join()
     dt = time.perf_counter() - t0
@@ -361,24 +391,26 @@ def time_sustained(pm, batch, device, cell_passes_rank, contexts=3, rounds=4):
         al.close()
     if errs:
         raise errs[0]
-    n = contexts * rounds
-    return {"value": n * cell_passes_rank / dt * 1e-9, "unit": UNIT, "contexts": contexts, "chunks": n,
-            "ms_per_chunk": dt / n * 1e3, "wall_s": dt, "cell_passes": n * cell_passes_rank}
+    n = sum(calls)
+    return {"value": sum(done) / dt * 1e-9, "unit": UNIT, "contexts": contexts, "chunks": n,
+            "ms_per_chunk": dt / max(n, 1) * 1e3, "wall_s": dt, "cell_passes": sum(done)}
 
 
 def e2e_object(single_value, single_s, h2d, d2h, sustained):
     single = {"value": single_value, "unit": UNIT, "ms_per_step": single_s * 1e3, "host_threads": 1}
+    buffers = "batch arrays in page-locked memory from margin_b200_pinned_alloc (as compat/pairwiseAligner_b200.c builds them)"
     if sustained is None:
-        return dict(single, h2d_bytes_per_step=h2d, d2h_bytes_per_step=d2h, mode="single call")
+        return dict(single, h2d_bytes_per_step=h2d, d2h_bytes_per_step=d2h, mode="single call", host_buffers=buffers)
     return {"value": sustained["value"], "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-            "ms_per_step": sustained["ms_per_chunk"], "mode": "%d host threads per GPU, %d chunks each, back to back"
-            % (sustained["contexts"], sustained["chunks"] // sustained["contexts"]),
-            "host_threads": sustained["contexts"], "single_call": single}
+            "ms_per_step": sustained["ms_per_chunk"],
+            "mode": "%d host threads per GPU, every thread sweeps this rank's chunks in turn for %.1f s (%d calls)"
+                    % (sustained["contexts"], sustained["wall_s"], sustained["chunks"]),
+            "host_threads": sustained["contexts"], "host_buffers": buffers, "single_call": single}
 
 
 def main_ours(args):
     import torch
-    from margin_b200 import abi
+    from margin_b200 import abi, model, scheduler
     from margin_b200.aligner import PairHmmAligner
 
     rank, local, world, dist = dist_setup(args.gpus)
@@ -387,12 +419,20 @@ def main_ours(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     peaks = load_peaks()
+    precision = abi.F32 if args.precision == "f32" else abi.F64
 
-    pm, items = build_items(args.workload, args.seed + rank)  # every rank polishes its own chunk
-    # the boundary formats a host program uses (include/margin_b200.h): 4-byte anchor steps in, 8-byte tuples out
-    batch = abi.Batch(items, compact=not args.plain_formats)
-    pin_batch(batch)
+    # ---- the chunks: one synthetic contig of chunks_per_gpu x N chunks, sharded over the ranks the way the reference's
+    # size-ordered dynamic schedule would (scheduler.shard_chunks: sizes are known from the chunk lengths alone, so every
+    # rank derives the same assignment and generates only its own chunks; no data-path collective)
+    pm = model.load_flat_model(MODEL_FILE)
+    n_chunks = args.chunks_per_gpu * world
+    mine = scheduler.shard_chunks([chunk_length(k) for k in range(n_chunks)], world)[rank]
+    t_gen = time.perf_counter()
+    chunk_items = {k: build_chunk(pm, args.seed, k) for k in mine}
+    t_gen = time.perf_counter() - t_gen
+    batches = [abi.Batch(chunk_items[k], compact=not args.plain_formats).to_pinned() for k in mine]
     al = PairHmmAligner(pm.models, pm.p, device=local)
+    al.set_precision(precision)
     al.bench_workload = args.workload
     if not args.plain_formats:
         al.set_pair_format(abi.PAIRS_PACKED64)
@@ -402,10 +442,10 @@ def main_ours(args):
         flush.zero_()
         torch.cuda.synchronize(dev)
 
-    # ---- kernel-only leg: inputs resident in HBM (per-launch CUDA events on for this leg only)
+    # ---- kernel-only leg: a chunk's inputs resident in HBM (upload outside the timed region), per-launch CUDA events
     al.set_kernel_timing(not args.no_kernel_events)
-    al.upload(batch)
-    for _ in range(args.warmup):
+    for i in range(max(args.warmup, len(batches))):
+        al.upload(batches[i % len(batches)])
         l2_flush()
         st = al.posteriors_resident(True)
     if dist is not None:
@@ -413,14 +453,20 @@ def main_ours(args):
     torch.cuda.synchronize(dev)
     sampler = ClockSampler(local)
     sampler.start()
-    dev_ms, launches = 0.0, 0
-    ktimes = {}
+    dev_ms, launches, cells_done = 0.0, 0, 0
+    ktimes, chunk_cells, stats_sum = {}, [0] * len(batches), {}
     t_wall0 = time.perf_counter()
-    for _ in range(args.steps):
+    for i in range(args.steps):
+        b = i % len(batches)
+        al.upload(batches[b])
         l2_flush()
         st = al.posteriors_resident(True)
         dev_ms += st["gpu_ms"]
         launches += st["kernel_launches"]
+        cells_done += st["band_cells"]
+        chunk_cells[b] = st["band_cells"]
+        for key in ("tiles", "wide_cells", "sequential_cells", "guard_seams", "guard_failures", "diagonals", "segments"):
+            stats_sum[key] = stats_sum.get(key, 0) + int(st[key])
         for k, (ms, ln) in al.kernel_times().items():
             a = ktimes.setdefault(k, [0.0, 0])
             a[0] += ms
@@ -430,78 +476,88 @@ def main_ours(args):
     clocks = sampler.finish()
     if dist is not None:
         dist.barrier()
-    cells = st["band_cells"]
+    for b in range(len(batches)):  # chunks the timed steps did not reach (steps < chunks)
+        if not chunk_cells[b]:
+            al.upload(batches[b])
+            chunk_cells[b] = al.posteriors_resident(True)["band_cells"]
     ms_step = reduce_scalar(dist, dev_ms / args.steps, "MAX", dev)
-    cell_passes = reduce_scalar(dist, 2.0 * cells, "SUM", dev)
-    value = cell_passes / (ms_step * 1e-3) * 1e-9
+    cell_passes_step = reduce_scalar(dist, 2.0 * cells_done / args.steps, "SUM", dev)
+    value = cell_passes_step / (ms_step * 1e-3) * 1e-9
 
     al.set_kernel_timing(False)
     # ---- end-to-end leg: host buffers in, host tuple lists out, through the public C-ABI call
-    for _ in range(max(1, min(args.warmup, 2))):
-        res = al.posteriors_host(batch, True)
+    for b in batches[:2]:
+        res = al.posteriors_host(b, True)
     if dist is not None:
         dist.barrier()
     torch.cuda.synchronize(dev)
+    e2e_steps = max(len(batches), min(args.steps, 8))
     t0 = time.perf_counter()
-    e2e_steps = max(1, min(args.steps, 5))
-    for _ in range(e2e_steps):
-        l2_flush()
-        res = al.posteriors_host(batch, True)
+    e2e_cells, d2h, h2d = 0, 0, 0
+    for i in range(e2e_steps):
+        b = i % len(batches)
+        res = al.posteriors_host(batches[b], True)
+        e2e_cells += chunk_cells[b]
+        d2h += int(res["tuples"]) * int(res["tuple_bytes"]) + 3 * (batches[b].n + 1) * 8
+        h2d += batches[b].h2d_bytes
     e2e_s = (time.perf_counter() - t0) / e2e_steps
-    # the flush is not part of the path: time it and take it out
-    t0 = time.perf_counter()
-    for _ in range(e2e_steps):
-        l2_flush()
-    e2e_s -= (time.perf_counter() - t0) / e2e_steps
     e2e_s = reduce_scalar(dist, e2e_s, "MAX", dev)
-    e2e_value = cell_passes / e2e_s * 1e-9
-    d2h = int(res["tuples"]) * int(res["tuple_bytes"]) + 3 * (batch.n + 1) * 8
+    e2e_value = reduce_scalar(dist, 2.0 * e2e_cells / e2e_steps, "SUM", dev) / e2e_s * 1e-9
 
-    # ---- sustained end-to-end: two contexts on this GPU, each sweeping chunk after chunk from host buffers, so that one
-    # chunk's copies overlap the other's kernels (what the chunk scheduler does with contexts_per_gpu = 2)
+    # ---- sustained end-to-end: three contexts on this GPU, each sweeping the rank's chunks from host buffers, so that
+    # one chunk's copies overlap another's kernels (what `margin polish -t` does with several threads per GPU)
     sustained = None
     if not args.no_sustained:
-        sustained = time_sustained(pm, batch, local, cell_passes_rank=2.0 * cells, contexts=3, rounds=4)
-        # whole job: every rank's chunks over the slowest rank's wall time
-        wall = reduce_scalar(dist, sustained.pop("wall_s"), "MAX", dev)
+        sustained = time_sustained(pm, batches, chunk_cells, local, precision, contexts=3, min_seconds=args.e2e_seconds)
+        wall = reduce_scalar(dist, sustained["wall_s"], "MAX", dev)  # whole job: all ranks' chunks over the slowest rank
         sustained["value"] = reduce_scalar(dist, sustained.pop("cell_passes"), "SUM", dev) / wall * 1e-9
-        sustained["ms_per_chunk"] = wall / sustained["chunks"] * 1e3
 
     # ---- roofline of the dominant kernel (CUDA events around each launch, same timed region)
     dom = max(ktimes.items(), key=lambda kv: kv[1][0])[0] if ktimes else "none"
     dom_ms = ktimes[dom][0] / max(ktimes[dom][1], 1) if ktimes else 0.0
-    roof = roofline(dom, dom_ms, ktimes, cells, st, peaks, al)
+    roof = roofline(dom, dom_ms, ktimes, cells_done / args.steps, args.steps, peaks, al)
 
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": al.arithmetic(), "data": "synthetic",
-        "config": {"workload": args.workload, "seed": args.seed, "reads_per_chunk": batch.n, "chunks_per_gpu": 1,
-                   "band_cells_per_chunk": int(cells), "diagonals": int(st["diagonals"]),
-                   "segments": int(st["segments"]), "params": "ont/r9.4 r94-g360 (RLE, repeat counts)",
-                   "l2": "flushed between steps (512 MiB write)",
-                   "boundary_formats": "plain" if args.plain_formats else "anchor steps 4 B, tuples 8 B", "wall_ms_per_step_incl_flush": t_wall / args.steps * 1e3},
+        "config": {"workload": args.workload, "seed": args.seed, "chunks_per_gpu": args.chunks_per_gpu,
+                   "chunk_lengths_kb": [chunk_length(k) // 1000 for k in mine],
+                   "reads_per_chunk": [b.n for b in batches], "band_cells_per_chunk": [int(c) for c in chunk_cells],
+                   "sharding": "one contig of %d chunks, scheduler.shard_chunks (size-descending LPT), no collective" % n_chunks,
+                   "params": "ont/r9.4 r94-g360 (RLE, repeat counts)", "l2": "flushed between steps (512 MiB write)",
+                   "boundary_formats": "plain" if args.plain_formats else "anchor steps 4 B, tuples 8 B",
+                   "tiles_per_step": stats_sum.get("tiles", 0) / args.steps,
+                   "wide_cell_share": stats_sum.get("wide_cells", 0) / max(cells_done, 1),
+                   "sequential_cell_share": stats_sum.get("sequential_cells", 0) / max(cells_done, 1),
+                   "guard_seams_per_step": stats_sum.get("guard_seams", 0) / args.steps,
+                   "guard_failures": stats_sum.get("guard_failures", 0),
+                   "wall_ms_per_step_incl_upload_and_flush": t_wall / args.steps * 1e3, "chunk_generation_s": t_gen},
         "clocks": clocks,
         # e2e.value is THROUGHPUT through margin_b200_posteriors_batch the way margin drives it (polish.c:476: several
-        # host threads, one chunk each): 3 host threads per GPU, every chunk copied in from pinned host memory and its
-        # lists copied back.  `single_call` is one thread issuing one call at a time (latency of a lone chunk).
-        "e2e": e2e_object(e2e_value, e2e_s, batch.h2d_bytes, d2h, sustained),
+        # host threads, one chunk each): 3 host threads per GPU sweeping distinct chunks for e2e_seconds, every chunk copied
+        # in from page-locked host memory and its lists copied back.  `single_call` is one thread, one call at a time.
+        "e2e": e2e_object(e2e_value, e2e_s, h2d // e2e_steps, d2h // e2e_steps, sustained),
         "gpu_launches": launches,
         "kernel_ms_per_step": {k: v[0] / args.steps for k, v in ktimes.items() if v[1]},
         "roofline": roof,
     }
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        r = time_reference(pm, items, 1, 1, host_cores())
+        r = time_reference(pm, chunk_items[mine[0]], 1, 1, host_cores())
         line["cpu_baseline"] = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": r["kind"],
                                 "sample": r["sample"]}
+    al.close()
+    for b in batches:
+        b.release_pinned()
+    # ---- the product-level number: polished Mb/hour of `margin polish` (reference CLI linked against this library) on a
+    # synthetic contig, all N GPUs of the box visible to it; rank 0 runs it while the other ranks wait at the barrier
+    if rank == 0 and args.polish_synth > 0:
+        line["polish"] = time_polish_synth(args.polish_synth, min(host_cores(), args.polish_threads), args.seed,
+                                           skip_reference=True, gpus=world, precision=args.precision)
     if rank == 0 and world == 1 and args.polish:
-        line["polish"] = time_polish(min(host_cores(), 8))
-    if rank == 0 and world == 1 and args.polish_synth > 0:
-        line["polish_synth"] = time_polish_synth(args.polish_synth, min(host_cores(), args.polish_threads), args.seed,
-                                                 args.polish_skip_reference)
+        line["polish_bundled_region"] = time_polish(min(host_cores(), 8))
     if rank == 0:
         print(json.dumps(line), flush=True)
-    al.close()
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
@@ -521,7 +577,7 @@ def al_workload(al):
     return getattr(al, "bench_workload", None)
 
 
-def roofline(dom, dom_ms, ktimes, cells, st, peaks, al):
+def roofline(dom, dom_ms, ktimes, cells, steps, peaks, al):
     """Roofline of the dominant kernel.  The path is a log-space recurrence, so the pipe that bounds it is the
     non-tensor FP pipe of the arithmetic type the kernels compute in; the HBM view of the
     same launch is reported beside it."""
@@ -531,8 +587,7 @@ def roofline(dom, dom_ms, ktimes, cells, st, peaks, al):
     dtype = al.arithmetic()
     lanes = 64 if dtype == "f64" else 128  # FP64 units per SM are half the FP32 lanes on sm_100
     peak_tflops = sms * lanes * 2 * peaks["sm_max_mhz"] * 1e6 * 1e-12
-    n_launch = max(ktimes[dom][1], 1) if ktimes else 1
-    steps = max(1, n_launch // max(1, al.launches_per_step(dom)))
+    steps = max(1, steps)
     # algorithmic work of one step attributed to the dominant kernel class.  HBM bytes per SURVEY.md §8 D-4: symbols
     # ~0.9 B, band descriptor ~2.7 B, output tuples ~2.6 B per band cell (forward state on chip: 0 B).  This design spills
     # the forward state once in each direction; those bytes are reported as `moved_bytes`, not as algorithmic bytes.
@@ -555,7 +610,8 @@ def roofline(dom, dom_ms, ktimes, cells, st, peaks, al):
     return {
         "kernel": dom, "bound": "fp64-pipe" if dtype == "f64" else "fp32-pipe", "achieved": ach_tflops,
         "peak": peak_tflops, "unit": "TFLOP/s", "frac": ach_tflops / peak_tflops if peak_tflops else None,
-        "traffic": NCU_DRAM_BYTES_PER_LAUNCH.get((al_workload(al), dom)), "traffic_source": NCU_TRAFFIC_SOURCE,
+        "traffic": NCU_DRAM_BYTES_PER_LAUNCH.get((dtype, dom)), "traffic_source": NCU_TRAFFIC_SOURCE,
+        "flop_per_cell": flop / max(cells, 1), "cells_per_launch": cells,
         "peak_source": "%d SMs x %d lanes x 2 x %.0f MHz (%s sm_max_mhz)" % (
             sms, lanes, peaks["sm_max_mhz"], peaks["source"]),
         "avg_launch_ms": dom_ms, "class_ms_per_step": class_ms_step,
@@ -650,9 +706,14 @@ def main():
     ap.add_argument("--plain-formats", action="store_true",
                     help="12-byte anchor triples in, 12-byte tuple records out instead of the compact boundary formats")
     ap.add_argument("--no-sustained", action="store_true", help="skip the two-context sustained end-to-end leg")
-    ap.add_argument("--polish-synth", type=int, default=0, metavar="KB",
-                    help="also time `margin polish` on a synthetic contig of KB kilobases (60x 20 kb ONT-like reads, one "
-                         "100 kb chunk per host thread): reference CLI vs the CLI linked against this library")
+    ap.add_argument("--polish-synth", type=int, default=1000, metavar="KB",
+                    help="polished Mb/hour of `margin polish` on a synthetic contig of KB kilobases (60x 20 kb ONT-like reads, "
+                         "100 kb chunks; BASELINE configs[2] is 5000): the CLI linked against this library, or the unmodified "
+                         "reference CLI with --impl reference; 0 = skip")
+    ap.add_argument("--chunks-per-gpu", type=int, default=4, help="distinct chunks every rank sweeps (weak scaling)")
+    ap.add_argument("--precision", default="f64", choices=["f64", "f32"],
+                    help="arithmetic of the lane-group tile kernels (include/margin_b200.h: margin_b200_set_precision)")
+    ap.add_argument("--e2e-seconds", type=float, default=2.0, help="timed window of the sustained end-to-end leg")
     ap.add_argument("--polish-threads", type=int, default=16)
     ap.add_argument("--polish-skip-reference", action="store_true")
     ap.add_argument("--polish", action="store_true",

@@ -171,6 +171,36 @@ class Batch:
         self.compact = True
         return True
 
+    def to_pinned(self):
+        """Moves the arrays that cross PCIe into page-locked memory from margin_b200_pinned_alloc — where the margin-side
+        binding assembles its batches (compat/pairwiseAligner_b200.c: b200_pinned_grow) — and re-points the struct."""
+        lib = load_library()
+        self._pinned = []
+
+        def move(a):
+            p = lib.margin_b200_pinned_alloc(max(a.nbytes, 1))
+            if not p:
+                raise RuntimeError(lib.margin_b200_last_error().decode())
+            self._pinned.append(p)
+            out = np.frombuffer((C.c_char * max(a.nbytes, 1)).from_address(p), dtype=a.dtype, count=a.size).reshape(a.shape)
+            out[...] = a
+            return out
+        self.sym_x, self.sym_y = move(self.sym_x), move(self.sym_y)
+        self.struct.sym_x, self.struct.sym_y = self.sym_x.ctypes.data, self.sym_y.ctypes.data
+        if self.compact:
+            self.anchors_delta = move(self.anchors_delta)
+            self.struct.anchors_delta = self.anchors_delta.ctypes.data
+        else:
+            self.anchors = move(self.anchors)
+            self.struct.anchors = self.anchors.ctypes.data
+        return self
+
+    def release_pinned(self):
+        lib = load_library()
+        for p in getattr(self, "_pinned", []):
+            lib.margin_b200_pinned_free(p)
+        self._pinned = []
+
     def item(self, i):
         return (self.sym_x[self.off_x[i]:self.off_x[i + 1]], self.sym_y[self.off_y[i]:self.off_y[i + 1]],
                 self.anchors[self.off_a[i]:self.off_a[i + 1]], int(self.model_slot[i]), int(self.ragged_left[i]),

@@ -132,7 +132,7 @@ struct margin_b200_ctx {
     int total_slots = 0;     // tiles of the current batch
     // tiling (pairhmm_tiles.cuh): tile length in diagonals (multiple of 10), warm-up diagonals on either side
     bool mode_sequential = false;
-    int tile_len = 1000, warmup = 192, force_group = 0, tile_len_used = 0, bwd_slots = 0;
+    int tile_len = 1600, warmup = 192, force_group = 0, tile_len_used = 0, bwd_slots = 0;
     bool tile_len_fixed = false;  // tile_len % 10 == 0: tiles start on total-probability samples
     std::vector<mb::Seg> segs;
     std::vector<mb::Tile> tiles;
@@ -202,7 +202,7 @@ struct margin_b200_ctx {
     bool warmup_env = false;             // MARGIN_B200_WARMUP pins the warm-up for both precisions
     double guard_tol32 = 1e-3;
     float v_thr_f = 0.f;
-    DevBuf d_F32, d_shiftF, d_emit_f[2], d_emit_f_ptrs;
+    DevBuf d_F32, d_shiftF, d_bnd32, d_emit_f[2], d_emit_f_ptrs;  // d_bnd32: boundary sections of FP32 tiles (float4 cells)
     PinBuf h_stage_in, h_small, h_out, h_off, h_gaps;
     // anchor-free stretches reported by the band kernel (sorted by job, start); see build_tiles
     std::vector<mb::AnchorGap> gaps;
@@ -440,7 +440,7 @@ void margin_b200_destroy(margin_b200_ctx *c) {
     DevBuf *bufs[] = {&c->d_models, &c->d_rsm[0], &c->d_rsm[1], &c->d_symx, &c->d_symy, &c->d_anchors, &c->d_jobs,
                       &c->d_kl, &c->d_kr, &c->d_cell_off, &c->d_job_cells, &c->d_job_maxw, &c->d_job_nseg, &c->d_err,
                       &c->d_segs, &c->d_seg_counts, &c->d_seg_off, &c->d_scan_tmp, &c->d_slot_ring_off, &c->d_ring,
-                      &c->d_ids, &c->d_aln_first_slot, &c->d_F, &c->d_Fpriv, &c->d_guard_worst, &c->d_class_cells, &c->d_F32, &c->d_shiftF, &c->d_emit_f[0], &c->d_emit_f[1],
+                      &c->d_ids, &c->d_aln_first_slot, &c->d_F, &c->d_Fpriv, &c->d_guard_worst, &c->d_class_cells, &c->d_F32, &c->d_shiftF, &c->d_bnd32, &c->d_emit_f[0], &c->d_emit_f[1],
                       &c->d_emit_f_ptrs, &c->d_stage, &c->d_out, &c->d_off_out, &c->d_fwd_out,
                       &c->d_geo, &c->d_tiles, &c->d_bnd, &c->d_slot_bnd_off, &c->d_emit5[0], &c->d_emit5[1],
                       &c->d_px, &c->d_py, &c->d_stage2, &c->d_chunks, &c->d_job_first_chunk, &c->d_chunk_sum, &c->d_chunk_maxw,
@@ -1437,7 +1437,8 @@ int build_bins(margin_b200_ctx *c, bool with_slots, Bins &bins, int force_group)
     c->p_ids = reinterpret_cast<int32_t *>(dv + o_ids);
     if (with_slots) {
         if (c->d_ring.ensure((size_t) (ring_cells + 1) * 3 * sizeof(double)) ||
-            c->d_bnd.ensure((size_t) (bnd_cells + 1) * 3 * sizeof(double)))
+            c->d_bnd.ensure((size_t) (bnd_cells + 1) * 3 * sizeof(double)) ||
+            (c->f32 && c->d_bnd32.ensure((size_t) (bnd_cells + 1) * 4 * sizeof(float))))
             return 1;
     }
     return 0;
@@ -1483,7 +1484,7 @@ void launch_forward_tiles2(margin_b200_ctx *c, int off, int count) {
         mb::forward_tile_kernel_f<G, kTileThreads, SW><<<(count + per_block - 1) / per_block, kTileThreads, 0, c->stream>>>(
             c->d_jobs.as<mb::Job>(), c->p_tiles, c->p_ids + off, count, c->d_models.as<mb::DevModel>(),
             c->d_emit_f_ptrs.as<const float *>(), c->d_px.as<uint8_t>() + mb::PACK_SLACK, c->d_py.as<uint8_t>() + mb::PACK_SLACK,
-            c->d_geo.as<int2>(), c->d_F32.as<float>(), c->d_bnd.as<float>(), c->p_bnd_off, c->d_shiftF.as<float>());
+            c->d_geo.as<int2>(), c->d_F32.as<float>(), c->d_bnd32.as<float>(), c->p_bnd_off, c->d_shiftF.as<float>());
     else
         mb::forward_tile_kernel<G, kTileThreads, SW><<<(count + per_block - 1) / per_block, kTileThreads, 0, c->stream>>>(
             c->d_jobs.as<mb::Job>(), c->p_tiles, c->p_ids + off, count,
@@ -1521,7 +1522,7 @@ void launch_backward_tiles3(margin_b200_ctx *c, int off, int count, int64_t stag
         mb::backward_tile_kernel_f<G, kTileThreads, INDELS, SW, GUARD><<<(count + per_block - 1) / per_block, kTileThreads, 0, c->stream>>>(
             c->d_jobs.as<mb::Job>(), c->p_tiles, c->p_ids + off, count, c->d_models.as<mb::DevModel>(),
             c->d_emit_f_ptrs.as<const float *>(), c->d_px.as<uint8_t>() + mb::PACK_SLACK, c->d_py.as<uint8_t>() + mb::PACK_SLACK,
-            c->d_geo.as<int2>(), c->d_F32.as<float>(), c->d_bnd.as<float>(), c->p_bnd_off, c->d_shiftF.as<float>(), c->v_thr_f,
+            c->d_geo.as<int2>(), c->d_F32.as<float>(), c->d_bnd32.as<float>(), c->p_bnd_off, c->d_shiftF.as<float>(), c->v_thr_f,
             c->d_stage2.as<mb::StagedPair>(), stage_stride, c->d_seg_counts.as<int64_t>(), c->total_slots);
     else
         mb::backward_tile_kernel<G, kTileThreads, INDELS, SW, GUARD><<<(count + per_block - 1) / per_block, kTileThreads, 0, c->stream>>>(
@@ -1686,7 +1687,8 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
             KTimer kt_(c, K_GUARD);
             mb::guard_check_kernel<<<(n_seams + 3) / 4, 128, 0, c->stream>>>(
                 c->d_jobs.as<mb::Job>(), c->p_tiles, c->p_seams, n_seams, c->d_geo.as<int2>(), c->d_F.as<double>(),
-                c->d_F32.as<float>(), c->d_Fpriv.as<double>(), c->d_bnd.as<double>(), c->p_bnd_off, c->f32 ? 1 : 0, c->guard_tol,
+                c->d_F32.as<float>(), c->d_Fpriv.as<double>(), c->d_bnd.as<double>(), c->d_bnd32.as<float>(), c->p_bnd_off,
+                c->f32 ? 1 : 0, c->guard_tol,
                 c->guard_tol32, c->guard_floor, c->p_guard_flags, c->p_guard_flags + n_seams,
                 c->guard_stats ? c->d_guard_worst.as<float>() : nullptr);
             c->launches++;

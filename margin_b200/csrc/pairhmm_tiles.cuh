@@ -258,12 +258,16 @@ forward_tile_kernel(const Job *__restrict__ jobs, const Tile *__restrict__ tiles
             c.m = ok_middle ? c.m : MB_NEG_INF;
             c.y = ok_upper ? c.y : MB_NEG_INF;
             {
-                // predicated stores (no divergent branch in the loop body)
-                double *q = (d == tb_to) ? bnd + 3 * r : Fj + 3 * ((int64_t) co + r);
+                // predicated stores (no divergent branch in the loop body); the one diagonal that goes to the boundary
+                // buffer instead of F takes a warp-uniform branch
+                double *q = Fj + 3 * ((int64_t) co + r);
                 asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %0, 0;\n\t@p st.global.f64 [%1], %2;\n\t"
                              "@p st.global.f64 [%1+8], %3;\n\t@p st.global.f64 [%1+16], %4;\n\t}"
-                             :: "r"((unsigned) (live && active && d >= tb_to)), "l"(q), "d"(c.m), "d"(c.x), "d"(c.y)
+                             :: "r"((unsigned) (live && active && d > tb_to)), "l"(q), "d"(c.m), "d"(c.x), "d"(c.y)
                              : "memory");
+                if (__any_sync(0xffffffffu, live && d == tb_to)) {
+                    if (live && active && d == tb_to) store_cell(bnd, r, c);
+                }
             }
             // ---- carry
             midm = lm;
@@ -596,14 +600,13 @@ backward_tile_kernel(const Job *__restrict__ jobs, const Tile *__restrict__ tile
             }
             if (GUARD) {
                 // seam guard: the last diagonal of this sweep and the warm-up diagonal just above the tile's own range
-                // are kept, so that guard_check_kernel can compare them with the neighbouring tiles' values
+                // are kept, so that guard_check_kernel can compare them with the neighbouring tiles' values.  Two
+                // diagonals per tile: a warp-uniform branch keeps the stores out of the other iterations.
                 const bool low = d == tb_to + 1;
-                double *q = bnd + 3 * ((low ? BND_B_LOW : BND_B_HIGH) * bnd_cells + rank);
-                asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %0, 0;\n\t@p st.global.f64 [%1], %2;\n\t"
-                             "@p st.global.f64 [%1+8], %3;\n\t@p st.global.f64 [%1+16], %4;\n\t}"
-                             :: "r"((unsigned) (live && active && (low || (d == tb_from + 1 && it > 0)))), "l"(q),
-                                "d"(b.m), "d"(b.x), "d"(b.y)
-                             : "memory");
+                const bool keep = live && (low || (d == tb_from + 1 && it > 0));
+                if (__any_sync(0xffffffffu, keep)) {
+                    if (keep && active) store_cell(bnd, (int64_t) (low ? BND_B_LOW : BND_B_HIGH) * bnd_cells + rank, b);
+                }
             }
             if (MB_TOTAL_ON && __any_sync(0xffffffffu, do_total)) {
                 // diagonalCalculationTotalProbability (pairwiseAligner.c:578-596); groups that do not sample on this
@@ -714,7 +717,8 @@ __global__ void guard_check_kernel(const Job *__restrict__ jobs, const Tile *__r
                                    const Seam *__restrict__ seams, int n_seams, const int2 *__restrict__ geo,
                                    const double *__restrict__ F, const float *__restrict__ F32,
                                    const double *__restrict__ Fpriv, const double *__restrict__ bnd,
-                                   const int64_t *__restrict__ slot_bnd_off, int f32, double tol, double tol32,
+                                   const float *__restrict__ bnd32, const int64_t *__restrict__ slot_bnd_off, int f32,
+                                   double tol, double tol32,
                                    double floor_gap, int32_t *__restrict__ flags, int32_t *__restrict__ n_failed,
                                    float *__restrict__ worst_out /* may be null: largest difference per seam */) {
     const int k = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -739,7 +743,7 @@ __global__ void guard_check_kernel(const Job *__restrict__ jobs, const Tile *__r
         const int64_t cells = (slot_bnd_off[slot + 1] - slot_bnd_off[slot]) / 3;
         const int64_t cell = slot_bnd_off[slot] + which * cells;
         const bool fl = f32 && (tiles[slot].flags & TILE_BND);
-        return Side{fl ? (const void *) (reinterpret_cast<const float *>(bnd) + 4 * cell) : (const void *) (bnd + 3 * cell), fl};
+        return Side{fl ? (const void *) (bnd32 + 4 * cell) : (const void *) (bnd + 3 * cell), fl};
     };
     auto priv_at = [&](const Tile &t) {
         return Side{Fpriv + 3 * (t.priv_off - (int64_t) (uint32_t) gj[t.f0].y + cod), false};

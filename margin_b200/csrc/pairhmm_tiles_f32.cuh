@@ -255,8 +255,10 @@ forward_tile_kernel_f(const Job *__restrict__ jobs, const Tile *__restrict__ til
             c.m = ok_middle ? c.m : MB_NEG_INF_F;
             c.y = ok_upper ? c.y : MB_NEG_INF_F;
             {
-                float *q = (d == tb_to) ? bnd + 4 * r : Fj + 4 * ((int64_t) co + r);
-                stg_cell_f(q, live && active && d >= tb_to, c);
+                stg_cell_f(Fj + 4 * ((int64_t) co + r), live && active && d > tb_to, c);
+                if (__any_sync(0xffffffffu, live && d == tb_to)) {  // the boundary diagonal: once per tile
+                    stg_cell_f(bnd + 4 * r, live && active && d == tb_to, c);
+                }
                 if (live && lane == 0 && d > tb_to) sFj[d] = pend;  // frame change in front of this diagonal
                 pend = 0.f;
             }
@@ -470,9 +472,10 @@ backward_tile_kernel_f(const Job *__restrict__ jobs, const Tile *__restrict__ ti
             }
             if (GUARD) {
                 const bool low = d == tb_to + 1;
-                CellF bs = b;
-                stg_cell_f(bnd + 4 * ((low ? BND_B_LOW : BND_B_HIGH) * bnd_cells + rank),
-                           live && active && (low || (d == tb_from + 1 && it > 0)), bs);
+                const bool keep = live && (low || (d == tb_from + 1 && it > 0));
+                if (__any_sync(0xffffffffu, keep)) {  // two diagonals per tile
+                    stg_cell_f(bnd + 4 * ((low ? BND_B_LOW : BND_B_HIGH) * bnd_cells + rank), keep && active, b);
+                }
             }
             if (__any_sync(0xffffffffu, do_total)) {
                 // diagonalCalculationTotalProbability (pairwiseAligner.c:578-596) in the frame of diagonal d
