@@ -148,7 +148,8 @@ struct margin_b200_ctx {
     std::vector<int32_t> span_tmp;
     std::vector<uint8_t> tiny_mask;  // forward-only: jobs swept by tiny_forward_kernel (skipped by build_bins)
     PinBuf h_tiny_ids;
-    DevBuf d_sym_err, d_tiny_ids, d_chunks_fwd, d_job_first_chunk_fwd;
+    DevBuf d_sym_err, d_tiny_ids, d_chunks_fwd, d_job_first_chunk_fwd, d_fwd_flags, d_fwd_counts;
+    margin_b200_ctx *fwd_sub = nullptr;  // the few matrices too large for the register-resident kernel (fast forward path)
     std::vector<mb::BandChunk> chunks_fwd;
     std::vector<int32_t> job_first_chunk_fwd;
     // ---- pipelined batches (posteriors_pipelined): sub-contexts with their own stream and arenas
@@ -434,6 +435,8 @@ void margin_b200_destroy(margin_b200_ctx *c) {
     if (!c) return;
     for (margin_b200_ctx *sub : c->subs) margin_b200_destroy(sub);
     c->subs.clear();
+    if (c->fwd_sub) margin_b200_destroy(c->fwd_sub);
+    c->fwd_sub = nullptr;
     if (c->counted) g_live_contexts[c->device & (kMaxDevices - 1)].fetch_sub(1);
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
@@ -444,7 +447,7 @@ void margin_b200_destroy(margin_b200_ctx *c) {
                       &c->d_emit_f_ptrs, &c->d_stage, &c->d_out, &c->d_off_out, &c->d_fwd_out,
                       &c->d_geo, &c->d_tiles, &c->d_bnd, &c->d_slot_bnd_off, &c->d_emit5[0], &c->d_emit5[1],
                       &c->d_px, &c->d_py, &c->d_stage2, &c->d_chunks, &c->d_job_first_chunk, &c->d_chunk_sum, &c->d_chunk_maxw,
-                      &c->d_totals, &c->d_band_out, &c->d_anchors_delta, &c->d_sym_err, &c->d_tiny_ids, &c->d_chunks_fwd, &c->d_job_first_chunk_fwd, &c->d_arena, &c->d_offs, &c->d_status};
+                      &c->d_totals, &c->d_band_out, &c->d_anchors_delta, &c->d_sym_err, &c->d_tiny_ids, &c->d_fwd_flags, &c->d_fwd_counts, &c->d_chunks_fwd, &c->d_job_first_chunk_fwd, &c->d_arena, &c->d_offs, &c->d_status};
     for (DevBuf *b : bufs) b->release();
     c->h_stage_in.release();
     c->h_small.release();
@@ -2322,9 +2325,188 @@ extern "C" int margin_b200_forward_resident(margin_b200_ctx *c, margin_b200_resu
     return 0;
 }
 
+namespace {
+
+// Forward-only batch WITHOUT anchors (the bubble-graph case): nothing per alignment happens on the host.  The
+// job table and the work lists are built by forward_jobs_kernel from the offsets; matrices whose shorter side fits a lane
+// group are swept in registers; the few larger ones go through the general path as a small batch of their own.
+int forward_batch_fast(margin_b200_ctx *c, const margin_b200_batch *b, double *out_log_prob, margin_b200_result *stats) {
+    if (!c->have_params) return fail("margin_b200_forward_batch: margin_b200_set_params has not been called");
+    if (check_device(c->device)) return 1;
+    CU(cudaSetDevice(c->device));
+    Trace tr(c);
+    const int64_t n = b->n;
+    const int64_t nx = b->off_x[n], ny = b->off_y[n];
+    if (n >= ((int64_t) 1 << 31) - 1) return fail("margin_b200_forward_batch: too many alignments");
+    const bool both = c->have_model[0] && c->have_model[1];
+    if (both && c->host_models[0].rle != c->host_models[1].rle)
+        return fail("the two state machines of a batch must both use (or both not use) repeat counts");
+    const int rle = c->host_models[c->have_model[0] ? 0 : 1].rle;
+    c->have_switch = false;
+    for (int k = 0; k < 2; k++)
+        if (c->have_model[k] && (c->host_models[k].t[mb::T_YX] != -INFINITY || c->host_models[k].t[mb::T_XY] != -INFINITY))
+            c->have_switch = true;
+    c->launches = 0;
+    c->ev_used = 0;
+    if (c->d_symx.ensure((nx + 1) * sizeof(uint16_t)) || c->d_symy.ensure((ny + 1) * sizeof(uint16_t)) ||
+        c->d_px.ensure((size_t) nx + 2 * mb::PACK_SLACK) || c->d_py.ensure((size_t) ny + 2 * mb::PACK_SLACK) ||
+        c->d_offs.ensure((size_t) 2 * (n + 1) * sizeof(int64_t)) || c->d_fwd_flags.ensure((size_t) 3 * n + 16) ||
+        c->d_jobs.ensure(((size_t) n + 1) * sizeof(mb::Job)) || c->d_tiny_ids.ensure((size_t) 3 * n * sizeof(int32_t) + 16) ||
+        c->d_fwd_counts.ensure(64) || c->d_fwd_out.ensure((size_t) (n + 1) * sizeof(double)) || c->d_sym_err.ensure(16) ||
+        c->h_small.ensure(128))
+        return 1;
+    CU(cudaStreamSynchronize(c->stream_sym));
+    CU(cudaEventRecord(c->ev0, c->stream));
+    // symbols on their own stream, packed to bytes there (as in margin_b200_upload_batch)
+    if (nx) CU(cudaMemcpyAsync(c->d_symx.p, b->sym_x, nx * sizeof(uint16_t), cudaMemcpyHostToDevice, c->stream_sym));
+    if (ny) CU(cudaMemcpyAsync(c->d_symy.p, b->sym_y, ny * sizeof(uint16_t), cudaMemcpyHostToDevice, c->stream_sym));
+    CU(cudaMemsetAsync(c->d_px.p, 0, (size_t) nx + 2 * mb::PACK_SLACK, c->stream_sym));
+    CU(cudaMemsetAsync(c->d_py.p, 0, (size_t) ny + 2 * mb::PACK_SLACK, c->stream_sym));
+    CU(cudaMemsetAsync(c->d_sym_err.p, 0, 16, c->stream_sym));
+    if (nx) mb::pack_symbols_kernel<<<(unsigned) ((nx + 255) / 256), 256, 0, c->stream_sym>>>(
+            c->d_symx.as<uint16_t>(), c->d_px.as<uint8_t>() + mb::PACK_SLACK, nx, rle, c->d_sym_err.as<int>());
+    if (ny) mb::pack_symbols_kernel<<<(unsigned) ((ny + 255) / 256), 256, 0, c->stream_sym>>>(
+            c->d_symy.as<uint16_t>(), c->d_py.as<uint8_t>() + mb::PACK_SLACK, ny, rle, c->d_sym_err.as<int>());
+    CU(cudaEventRecord(c->ev_sym, c->stream_sym));
+    // offsets and per-alignment flags, then the job table and the work lists on the device
+    int64_t *d_offx = c->d_offs.as<int64_t>(), *d_offy = d_offx + (n + 1);
+    uint8_t *d_flags = c->d_fwd_flags.as<uint8_t>();
+    CU(cudaMemcpyAsync(d_offx, b->off_x, (n + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(d_offy, b->off_y, (n + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, c->stream));
+    if (b->model_slot) CU(cudaMemcpyAsync(d_flags, b->model_slot, n, cudaMemcpyHostToDevice, c->stream));
+    if (b->ragged_left) CU(cudaMemcpyAsync(d_flags + n, b->ragged_left, n, cudaMemcpyHostToDevice, c->stream));
+    if (b->ragged_right) CU(cudaMemcpyAsync(d_flags + 2 * n, b->ragged_right, n, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemsetAsync(c->d_fwd_counts.p, 0, 64, c->stream));
+    int32_t *ids16 = c->d_tiny_ids.as<int32_t>(), *ids32 = ids16 + n, *ids_gen = ids32 + n;
+    int32_t *d_counts = c->d_fwd_counts.as<int32_t>();
+    unsigned long long *d_cells = reinterpret_cast<unsigned long long *>(c->d_fwd_counts.as<char>() + 32);
+    mb::forward_jobs_kernel<<<(unsigned) ((n + 255) / 256), 256, 0, c->stream>>>(
+        n, d_offx, d_offy, b->model_slot ? d_flags : nullptr, b->ragged_left ? d_flags + n : nullptr,
+        b->ragged_right ? d_flags + 2 * n : nullptr, c->have_model[0] ? 1 : 0, c->have_model[1] ? 1 : 0,
+        c->d_jobs.as<mb::Job>(), ids16, ids32, ids_gen, d_counts, d_cells);
+    c->launches++;
+    int32_t *h_counts = reinterpret_cast<int32_t *>(c->h_small.as<char>());
+    if (ctl_copy(c->stream, h_counts, c->d_fwd_counts.p, 64)) return 1;
+    CU(cudaStreamSynchronize(c->stream));
+    CU(cudaGetLastError());
+    tr.mark("fwd jobs on device");
+    if (h_counts[3]) return fail("margin_b200_forward_batch: an alignment uses a model slot that has not been set");
+    const int n16 = h_counts[0], n32 = h_counts[1], n_gen = h_counts[2];
+    const int64_t tiny_cells = (int64_t) *reinterpret_cast<unsigned long long *>(reinterpret_cast<char *>(h_counts) + 32);
+    CU(cudaStreamWaitEvent(c->stream, c->ev_sym, 0));
+    const int e = (int) c->params.diagonal_expansion;
+    auto launch = [&](auto g_tag, const int32_t *ids, int count) {
+        constexpr int G = decltype(g_tag)::value;
+        if (count <= 0) return;
+        const int per_block = kTileThreads / G;
+        const unsigned grid = (unsigned) ((count + per_block - 1) / per_block);
+        KTimer kt_(c, K_FORWARD);
+        if (c->have_switch)
+            mb::tiny_forward_kernel<G, kTileThreads, true><<<grid, kTileThreads, 0, c->stream>>>(
+                c->d_jobs.as<mb::Job>(), ids, count, c->d_models.as<mb::DevModel>(), c->d_px.as<uint8_t>() + mb::PACK_SLACK,
+                c->d_py.as<uint8_t>() + mb::PACK_SLACK, e, c->d_fwd_out.as<double>());
+        else
+            mb::tiny_forward_kernel<G, kTileThreads, false><<<grid, kTileThreads, 0, c->stream>>>(
+                c->d_jobs.as<mb::Job>(), ids, count, c->d_models.as<mb::DevModel>(), c->d_px.as<uint8_t>() + mb::PACK_SLACK,
+                c->d_py.as<uint8_t>() + mb::PACK_SLACK, e, c->d_fwd_out.as<double>());
+        c->launches++;
+    };
+    launch(std::integral_constant<int, 16>{}, ids16, n16);
+    launch(std::integral_constant<int, 32>{}, ids32, n32);
+    CU(cudaEventRecord(c->ev1, c->stream));
+    int *h_sym_err = reinterpret_cast<int *>(c->h_small.as<char>() + 64);
+    *h_sym_err = 0;
+    if (ctl_copy(c->stream, h_sym_err, c->d_sym_err.p, 8)) return 1;
+    if (n) CU(cudaMemcpyAsync(out_log_prob, c->d_fwd_out.p, (size_t) n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    // ---- the matrices that do not fit a lane group: a small batch of their own on the general path
+    int64_t general_cells = 0;
+    std::vector<int32_t> gen_ids;
+    if (n_gen > 0) {
+        gen_ids.resize(n_gen);
+        CU(cudaMemcpyAsync(gen_ids.data(), ids_gen, (size_t) n_gen * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+    }
+    CU(cudaStreamSynchronize(c->stream));
+    CU(cudaGetLastError());
+    tr.mark("fwd tiny");
+    if (*h_sym_err)
+        return fail("a symbol carries a run length >= %d; the repeat-count model holds 0..%d", MARGIN_B200_MAX_RL,
+                    MARGIN_B200_MAX_RL - 1);
+    int sub_launches = 0;
+    if (n_gen > 0) {
+        std::sort(gen_ids.begin(), gen_ids.end());
+        if (!c->fwd_sub) {
+            if (margin_b200_create(&c->fwd_sub, c->device)) return 1;
+            c->fwd_sub->is_sub = true;
+            c->fwd_sub->counted = false;
+            g_live_contexts[c->device & (kMaxDevices - 1)].fetch_sub(1);
+        }
+        margin_b200_ctx *sub = c->fwd_sub;
+        sub->mode_sequential = true;  // whole matrices, no tiling: the general forward path
+        for (int slot = 0; slot < 2; slot++)
+            if (c->have_model[slot] && margin_b200_set_model(sub, slot, c->user_models[slot].get())) return 1;
+        if (margin_b200_set_params(sub, &c->params)) return 1;
+        std::vector<uint16_t> sx, sy;
+        std::vector<int64_t> ox(n_gen + 1, 0), oy(n_gen + 1, 0), oa(n_gen + 1, 0);
+        std::vector<uint8_t> sl(n_gen, 0), rl(n_gen, 0), rr(n_gen, 0);
+        for (int k = 0; k < n_gen; k++) {
+            const int64_t i = gen_ids[k];
+            sx.insert(sx.end(), b->sym_x + b->off_x[i], b->sym_x + b->off_x[i + 1]);
+            sy.insert(sy.end(), b->sym_y + b->off_y[i], b->sym_y + b->off_y[i + 1]);
+            ox[k + 1] = (int64_t) sx.size();
+            oy[k + 1] = (int64_t) sy.size();
+            sl[k] = b->model_slot ? b->model_slot[i] : 0;
+            rl[k] = b->ragged_left ? b->ragged_left[i] : 0;
+            rr[k] = b->ragged_right ? b->ragged_right[i] : 0;
+        }
+        static const uint16_t no_sym[1] = {0};
+        static const int32_t no_anc[3] = {0, 0, 0};
+        margin_b200_batch gb{};
+        gb.n = n_gen;
+        gb.sym_x = sx.empty() ? no_sym : sx.data();
+        gb.sym_y = sy.empty() ? no_sym : sy.data();
+        gb.off_x = ox.data();
+        gb.off_y = oy.data();
+        gb.off_a = oa.data();
+        gb.anchors = no_anc;
+        gb.model_slot = sl.data();
+        gb.ragged_left = rl.data();
+        gb.ragged_right = rr.data();
+        std::vector<double> go(n_gen, 0.0);
+        margin_b200_result gs;
+        if (margin_b200_forward_batch(sub, &gb, go.data(), &gs)) return 1;
+        for (int k = 0; k < n_gen; k++) out_log_prob[gen_ids[k]] = go[k];
+        general_cells = gs.band_cells;
+        sub_launches = gs.kernel_launches;
+        tr.mark("fwd general");
+    }
+    float ms = 0;
+    CU(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+    if (getenv("MARGIN_B200_FWD_STATS"))
+        fprintf(stderr, "margin_b200 forward: %lld matrices (%d register-resident, %lld cells; general path %d matrices, %lld "
+                "cells), %d launches, %.2f ms on the device\n", (long long) n, n16 + n32, (long long) tiny_cells, n_gen,
+                (long long) general_cells, c->launches + sub_launches, ms);
+    c->n_aln = n;
+    c->jobs.clear();
+    c->total_cells = tiny_cells + general_cells;
+    if (stats) {
+        memset(stats, 0, sizeof(*stats));
+        stats->n = n;
+        stats->band_cells = c->total_cells;
+        stats->jobs = n;
+        stats->gpu_ms = ms;
+        stats->kernel_launches = c->launches + sub_launches;
+    }
+    return 0;
+}
+
+}  // namespace
+
 extern "C" int margin_b200_forward_batch(margin_b200_ctx *c, const margin_b200_batch *b, double *out_log_prob,
                                          margin_b200_result *stats) {
     if (!c || !b || !out_log_prob) return fail("margin_b200_forward_batch: null argument");
+    // no anchors anywhere (every caller of computeForwardProbability in margin): nothing per alignment on the host
+    if (b->n > 0 && b->off_a[b->n] == 0 && !c->mode_sequential && !c->is_sub && !force_group_env() && !getenv("MARGIN_B200_FWD_SLOW"))
+        return forward_batch_fast(c, b, out_log_prob, stats);
     // the forward-only path never splits: lift the limit for the upload, then restore it
     const int64_t saved = c->params.split_matrix_bigger_than_this;
     c->params.split_matrix_bigger_than_this = INT64_MAX;

@@ -430,6 +430,60 @@ tiny_forward_kernel(const Job *__restrict__ jobs, const int32_t *__restrict__ id
     }
 }
 
+// Job table and work lists of an anchor-free forward-only batch, built on the device (margin_b200_forward_batch's fast
+// path: poa_polish sends ~0.4-2 M tiny matrices per chunk, and a host loop over them — 80-byte jobs, a band chunk each —
+// cost more than the DP).  One thread per alignment: writes its Job, and appends its index to the list of the kernel that
+// takes it: lane groups of 16 (min(lX, lY) + 1 <= 16), of 32 (<= 32), or the general path (counts[2], ids_gen).
+// counts: [0..2] list lengths, [3] bad model slot seen; cells[0] = cells of the register-resident matrices.
+__global__ void forward_jobs_kernel(int64_t n, const int64_t *__restrict__ off_x, const int64_t *__restrict__ off_y,
+                                    const uint8_t *__restrict__ slot, const uint8_t *__restrict__ ragged_l,
+                                    const uint8_t *__restrict__ ragged_r, int have_slot0, int have_slot1,
+                                    Job *__restrict__ jobs, int32_t *__restrict__ ids16, int32_t *__restrict__ ids32,
+                                    int32_t *__restrict__ ids_gen, int32_t *__restrict__ counts,
+                                    unsigned long long *__restrict__ cells) {
+    const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    int cls = 3;  // no list
+    unsigned long long mine = 0;
+    if (i < n) {
+        Job job;
+        job.symx_off = off_x[i];
+        job.symy_off = off_y[i];
+        job.anc_off = 0;
+        job.diag_off = 0;
+        job.cell_base = 0;
+        job.ring_off = 0;
+        job.lx = (int32_t) (off_x[i + 1] - off_x[i]);
+        job.ly = (int32_t) (off_y[i + 1] - off_y[i]);
+        job.n_anc = 0;
+        job.x1 = job.y1 = 0;
+        job.aln = (int32_t) i;
+        job.seg_base = job.max_seg = 0;
+        job.ring_w = 0;
+        job.slot = slot ? slot[i] : 0;
+        job.ragged_l = ragged_l ? ragged_l[i] : 0;
+        job.ragged_r = ragged_r ? ragged_r[i] : 0;
+        job.pad = 0;
+        if (job.slot > 1 || !(job.slot ? have_slot1 : have_slot0) || job.lx < 0 || job.ly < 0) atomicExch(counts + 3, 1);
+        jobs[i] = job;
+        const int m = min(job.lx, job.ly) + 1;
+        cls = m <= 16 ? 0 : (m <= 32 ? 1 : 2);
+        if (cls < 2) mine = (unsigned long long) (job.lx + 1) * (unsigned long long) (job.ly + 1);
+    }
+    const int lane = threadIdx.x & 31;
+    int32_t *lists[3] = {ids16, ids32, ids_gen};
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        const unsigned m = __ballot_sync(0xffffffffu, cls == k);
+        if (m == 0) continue;
+        int base = 0;
+        if (lane == __ffs(m) - 1) base = atomicAdd(counts + k, __popc(m));
+        base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
+        if (cls == k) lists[k][base + __popc(m & ((1u << lane) - 1u))] = (int32_t) i;
+    }
+    for (int o = 16; o > 0; o >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, o);
+    if (lane == 0 && mine) atomicAdd(cells, mine);
+}
+
 // Per-diagonal lane bookkeeping shared by the three staged lists: `bits` of a ballot are cut down to the group,
 // rotated so that bit i is the cell x = xlo + i, and a passing cell is appended behind the passing cells below it.
 template <int G>
