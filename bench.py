@@ -136,6 +136,39 @@ def dist_setup(n_gpus):
     return rank, local, world, dist
 
 
+ALL_CORES = None
+
+
+def unbind_cores():
+    """Back to every core of the box (the `margin polish` run of rank 0 uses all of them, like the reference's)."""
+    if ALL_CORES:
+        try:
+            os.sched_setaffinity(0, ALL_CORES)
+        except OSError:
+            pass
+
+
+def bind_rank_to_cores(local, world):
+    """One process per GPU: every rank keeps its host threads (and therefore the page-locked buffers they allocate) on a
+    disjoint slice of the box's cores, so that eight ranks do not all queue on one NUMA node's memory (SCALE r01: end-to-end
+    efficiency 0.58 at N=8 with unbound ranks).  Returns the cores this rank runs on."""
+    global ALL_CORES
+    try:
+        avail = sorted(os.sched_getaffinity(0))
+    except AttributeError:
+        return None
+    ALL_CORES = avail
+    if world <= 1 or len(avail) < 2 * world:
+        return avail
+    per = len(avail) // world
+    mine = avail[local * per:(local + 1) * per]
+    try:
+        os.sched_setaffinity(0, mine)
+    except OSError:
+        return avail
+    return mine
+
+
 def reduce_scalar(dist, value, op, device):
     if dist is None:
         return value
@@ -416,6 +449,7 @@ def main_ours(args):
     rank, local, world, dist = dist_setup(args.gpus)
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+    cores = bind_rank_to_cores(local, world)
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     peaks = load_peaks()
@@ -532,7 +566,8 @@ def main_ours(args):
                    "sequential_cell_share": stats_sum.get("sequential_cells", 0) / max(cells_done, 1),
                    "guard_seams_per_step": stats_sum.get("guard_seams", 0) / args.steps,
                    "guard_failures": stats_sum.get("guard_failures", 0),
-                   "wall_ms_per_step_incl_upload_and_flush": t_wall / args.steps * 1e3, "chunk_generation_s": t_gen},
+                   "wall_ms_per_step_incl_upload_and_flush": t_wall / args.steps * 1e3, "chunk_generation_s": t_gen,
+                   "host_cores_of_rank0": len(cores) if cores else None},
         "clocks": clocks,
         # e2e.value is THROUGHPUT through margin_b200_posteriors_batch the way margin drives it (polish.c:476: several
         # host threads, one chunk each): 3 host threads per GPU sweeping distinct chunks for e2e_seconds, every chunk copied
@@ -552,6 +587,7 @@ def main_ours(args):
     # ---- the product-level number: polished Mb/hour of `margin polish` (reference CLI linked against this library) on a
     # synthetic contig, all N GPUs of the box visible to it; rank 0 runs it while the other ranks wait at the barrier
     if rank == 0 and args.polish_synth > 0:
+        unbind_cores()
         line["polish"] = time_polish_synth(args.polish_synth, min(host_cores(), args.polish_threads), args.seed,
                                            skip_reference=True, gpus=world, precision=args.precision)
     if rank == 0 and world == 1 and args.polish:

@@ -67,8 +67,17 @@ __device__ __forceinline__ Cell cell_sel(bool p, const Cell &c) {
 template <int G>
 __device__ __forceinline__ double shfl_g(double v, int src) { return __shfl_sync(0xffffffffu, v, src, G); }
 
+// lookup() (pairwiseAligner.c:282-293) picks its cubic by d <= 1, <= 2.5, <= 4.5 (< 7.5): all multiples of 1/2, so
+// ceil(2 d) in 0..16 names the piece exactly, and fma.rp(d, 2, 1.5 * 2^52) leaves that integer in the low word of the
+// sum — one FP64 instruction instead of three compares and three selects.  The coefficient table therefore has one row
+// per value of ceil(2 d) (row 16: d > 7.5, never used for a result), and eight copies of every row, [row][copy]: lane j
+// of a quarter-warp reads copy j, which lies in its own four banks, so the LDS.128 never conflicts.
+constexpr int LA_ROWS = 17;
+__device__ __forceinline__ int la_piece_of_row(int r) { return r <= 2 ? 0 : (r <= 5 ? 1 : (r <= 9 ? 2 : (r <= 15 ? 3 : 4))); }
+
 struct TileShared {
-    double lac[16];       // lookup() pieces, one 32-byte row {c3, c2, c1, c0} per piece (pairwiseAligner.c:282-293)
+    double2 lac32[LA_ROWS][8];  // {c3, c2} of the piece of row ceil(2 d)
+    double2 lac10[LA_ROWS][8];  // {c1, c0}
     double gx[2][5][4];   // [model][base] {M->X, X->X, Y->X, 0}: the reference's (eP + tP) of the gap-X transitions
     double gy[2][5][4];   // [model][base] {M->Y, Y->Y, X->Y, 0}
     DevModel model[2];
@@ -78,7 +87,11 @@ template <int THREADS>
 __device__ __forceinline__ void tile_shared_init(TileShared &s, const DevModel *__restrict__ models) {
     for (int i = threadIdx.x; i < (int) (2 * sizeof(DevModel) / 8); i += THREADS)
         reinterpret_cast<double *>(s.model)[i] = reinterpret_cast<const double *>(models)[i];
-    if (threadIdx.x < 16) s.lac[threadIdx.x] = LA_COEF[threadIdx.x];
+    for (int i = threadIdx.x; i < LA_ROWS * 8; i += THREADS) {
+        const int p = la_piece_of_row(i >> 3);
+        s.lac32[i >> 3][i & 7] = p < 4 ? make_double2(LA_COEF[4 * p], LA_COEF[4 * p + 1]) : make_double2(0.0, 0.0);
+        s.lac10[i >> 3][i & 7] = p < 4 ? make_double2(LA_COEF[4 * p + 2], LA_COEF[4 * p + 3]) : make_double2(0.0, 0.0);
+    }
     if (threadIdx.x < 40) {
         const int k = threadIdx.x & 3, b = (threadIdx.x >> 2) % 5, md = threadIdx.x / 20;
         s.gx[md][b][k] = k < 3 ? models[md].ex_t[b][k] : 0.0;
@@ -103,26 +116,21 @@ __device__ __forceinline__ double lds_f64(uint32_t a) {
 
 // logAdd (pairwiseAligner.c:279-299) for the tile kernels, operation-for-operation the arithmetic of logadd():
 //   |x - y| is the reference's (max - min) bit for bit, so the difference is formed first and the hi/lo selects run
-//   beside the polynomial instead of in front of it; the piece is chosen by a three-deep select of the row offset
-//   (d > 1, d > 2.5, d > 4.5); lo == -inf gives d = +inf (or NaN when both are -inf), "d < 7.5" fails and hi comes out.
-// lac_s = shared-space address of TileShared::lac.
+//   beside the polynomial instead of in front of it; the piece comes from the row ceil(2 d) (see TileShared);
+//   lo == -inf gives d = +inf (or NaN when both are -inf), "d < 7.5" fails and hi comes out.
+// lac_s = shared-space address of this lane's copy of TileShared::lac32 (copy = lane & 7).
 __device__ __forceinline__ double logadd_t(double x, double y, uint32_t lac_s) {
     const double ds = dadd(x, -y);
     const bool lt = __double2hiint(ds) < 0;
     const double hi = lt ? y : x;
     const double lo = lt ? x : y;
     const double d = fabs(ds);
-    uint32_t row;
-    asm("{\n\t.reg .pred p1, p2, p3;\n\t"
-        "setp.gt.f64 p1, %1, 0d3FF0000000000000;\n\t"
-        "setp.gt.f64 p2, %1, 0d4004000000000000;\n\t"
-        "setp.gt.f64 p3, %1, 0d4012000000000000;\n\t"
-        "selp.u32 %0, 32, 0, p1;\n\t"
-        "selp.u32 %0, 64, %0, p2;\n\t"
-        "selp.u32 %0, 96, %0, p3;\n\t}"
-        : "=r"(row) : "d"(d));
-    const double2 c32 = lds_f64x2(lac_s + row);
-    const double2 c10 = lds_f64x2(lac_s + row + 16);
+    double t;
+    asm("fma.rp.f64 %0, %1, 0d4000000000000000, 0d4338000000000000;" : "=d"(t) : "d"(d));
+    const uint32_t row = min((uint32_t) __double2loint(t), (uint32_t) (LA_ROWS - 1));  // inf, NaN, huge d: any row will do
+    const uint32_t a = lac_s + row * 128u;
+    const double2 c32 = lds_f64x2(a);
+    const double2 c10 = lds_f64x2(a + LA_ROWS * 128u);
     double v = dadd(dmul(c32.x, d), c32.y);
     v = dadd(dmul(v, d), c10.x);
     v = dadd(dmul(v, d), c10.y);
@@ -162,7 +170,7 @@ forward_tile_kernel(const Job *__restrict__ jobs, const Tile *__restrict__ tiles
     const Tile t = tiles[slot];
     const Job job = jobs[t.job];
     const DevModel &m = sh.model[job.slot];
-    const uint32_t lac_s = smem_u32(sh.lac);
+    const uint32_t lac_s = smem_u32(&sh.lac32[0][tid & 7]);
     const uint32_t gx_s = smem_u32(&sh.gx[job.slot][0][0]), gy_s = smem_u32(&sh.gy[job.slot][0][0]);
     const int N = job.lx + job.ly;
     const uint8_t *sx = px + job.symx_off - 1, *sy = py + job.symy_off - 1;  // sx[x] = symbol of column x (1-based)
@@ -329,7 +337,7 @@ tiny_forward_kernel(const Job *__restrict__ jobs, const int32_t *__restrict__ id
     const int prev_lane = mod_g(lane - 1, G);
     const Job job = jobs[ids[min(g, n_ids - 1)]];
     const DevModel &m = sh.model[job.slot];
-    const uint32_t lac_s = smem_u32(sh.lac);
+    const uint32_t lac_s = smem_u32(&sh.lac32[0][tid & 7]);
     const uint32_t gx_s = smem_u32(&sh.gx[job.slot][0][0]), gy_s = smem_u32(&sh.gy[job.slot][0][0]);
     const int lx = job.lx, ly = job.ly, N = lx + ly;
     const uint8_t *sx = px + job.symx_off - 1, *sy = py + job.symy_off - 1;  // sx[x] = symbol of column x (1-based)
@@ -542,7 +550,7 @@ backward_tile_kernel(const Job *__restrict__ jobs, const Tile *__restrict__ tile
     const Tile t = tiles[slot];
     const Job job = jobs[t.job];
     const DevModel &m = sh.model[job.slot];
-    const uint32_t lac_s = smem_u32(sh.lac);
+    const uint32_t lac_s = smem_u32(&sh.lac32[0][tid & 7]);
     const uint32_t gx_s = smem_u32(&sh.gx[job.slot][0][0]), gy_s = smem_u32(&sh.gy[job.slot][0][0]);
     const uint8_t *sx = px + job.symx_off, *sy = py + job.symy_off;
     const int2 *gj = geo + job.diag_off;

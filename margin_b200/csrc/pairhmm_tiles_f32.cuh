@@ -51,8 +51,6 @@ struct TileSharedF {
     const float *emit[2];
 };
 
-// Row r of the table serves d in ((r-1)/2, r/2]: pieces d <= 1 | <= 2.5 | <= 4.5 | < 7.5 (pairwiseAligner.c:282-293).
-__device__ __forceinline__ int la_piece_of_row(int r) { return r <= 2 ? 0 : (r <= 5 ? 1 : (r <= 9 ? 2 : (r <= 15 ? 3 : 4))); }
 
 template <int THREADS>
 __device__ __forceinline__ void tile_shared_init_f(TileSharedF &s, const DevModel *__restrict__ models,

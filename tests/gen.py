@@ -92,3 +92,61 @@ def gapped_anchor_case(rng, lx, gap_cols, n_gaps=3, expansion=4, rle=True):
         at = int(rng.integers(lx // 10, max(lx // 10 + 1, lx - gap_cols - lx // 10)))
         keep &= ~((a[:, 0] >= at) & (a[:, 0] < at + gap_cols))
     return sx, sy, a[keep], int(rng.random() < 0.5), 0, 0
+
+
+# ------------------------------------------------------------------------------------------ the parity corpus
+#
+# >= 10 k fixed-seed alignments.  Case i is a pure function of i (its own Generator), so the
+# corpus needs no input files: tests/golden/make_corpus.py runs the UNMODIFIED reference on every case here and commits
+# only digests (tests/golden/corpus_digests.npz); the GPU test regenerates the inputs on the box.
+
+CORPUS_SIZE = 10240
+CORPUS_PARAM_SETS = ((5000, 1), (100, 1), (150, 1), (5000, 0), (130, 0))  # (minDiagsBetweenTraceBack, dynamicAnchorExpansion)
+
+
+def corpus_case(i):
+    """-> (item, param_set index).  Mix: short random problems with every edge the generator knows (empty sequences, no
+    anchors, ragged ends, N, clipped run lengths), wide spots, long indels, tandem repeats, and alignments of more
+    than 5000 diagonals at the shipped parameters (several tracebacks)."""
+    rng = np.random.default_rng([20260105, i])
+    kind = i % 20
+    if kind < 13:
+        item = random_case(rng, int(rng.integers(0, 700)))
+        ps = int(rng.integers(0, len(CORPUS_PARAM_SETS)))
+    elif kind < 15:
+        item = gapped_anchor_case(rng, int(rng.integers(1200, 2600)), int(rng.integers(36, 120)), n_gaps=int(rng.integers(1, 4)))
+        ps = int(rng.choice([0, 1]))
+    elif kind == 15:
+        item = long_indel_case(rng, int(rng.integers(1500, 3000)), int(rng.integers(300, 1000)), int(rng.integers(12, 700)),
+                               bool(rng.random() < 0.5))
+        ps = 0
+    elif kind == 16:
+        item = low_complexity_case(rng, int(rng.integers(800, 2400)), int(rng.integers(1, 6)))
+        ps = int(rng.choice([0, 2]))
+    elif kind == 17:
+        item = gapped_anchor_case(rng, int(rng.integers(4500, 7000)), 0, n_gaps=0)  # > 5000 diagonals: several tracebacks
+        ps = 0
+    elif kind == 18:
+        lx, ly = int(rng.integers(0, 4)), int(rng.integers(0, 4))
+        item = (random_symbols(rng, lx), random_symbols(rng, ly), np.zeros((0, 3), np.int32), int(rng.random() < 0.5),
+                int(rng.random() < 0.5), int(rng.random() < 0.5))
+        ps = int(rng.integers(0, len(CORPUS_PARAM_SETS)))
+    else:
+        sx = random_symbols(rng, int(rng.integers(20, 260)))
+        sy, _ = mutate(rng, sx)
+        item = (sx, sy, np.zeros((0, 3), np.int32), int(rng.random() < 0.5), int(rng.random() < 0.3), int(rng.random() < 0.3))
+        ps = int(rng.integers(0, len(CORPUS_PARAM_SETS)))
+    return item, ps
+
+
+def list_digest(lst):
+    """(count, order-sensitive hash of the (x, y) sequence, sum of weights) of one tuple list."""
+    n = len(lst)
+    if n == 0:
+        return 0, 0, 0
+    x = lst["x"].astype(np.int64).astype(np.uint64)
+    y = lst["y"].astype(np.int64).astype(np.uint64)
+    k = np.arange(1, n + 1, dtype=np.uint64)
+    with np.errstate(over="ignore"):
+        h = ((x * np.uint64(1000003) + y + np.uint64(7)) * (k * np.uint64(0x9E3779B97F4A7C15) + np.uint64(1))).sum(dtype=np.uint64)
+    return n, int(h), int(lst["w"].astype(np.int64).sum())
