@@ -61,6 +61,7 @@ typedef struct {
     margin_b200_params loadedParams;
     int dynamicAnchors;            /* whether b200_batch_add reads the anchors' third field (p->dynamicAnchorExpansion) */
     struct B200Deferred *deferred; /* non-NULL while poa_polish collects forward jobs (see the last section) */
+    struct B200Deferred *replay;   /* non-NULL while a record / replay wrapper hands the results back in order */
 } B200Thread;
 
 static __thread B200Thread tls;
@@ -970,6 +971,11 @@ typedef struct B200Deferred {
     PairwiseAlignmentParameters params;
     int haveParams;
     int warned;
+    /* record / replay (b200_partition wrapper below): lengths of every recorded job, to check that the replay asks the
+     * same questions in the same order */
+    int64_t *lengths;
+    int64_t capLengths;
+    int64_t cursor;
 } B200Deferred;
 
 static double b200_tagged_nan(int64_t job) {
@@ -1028,8 +1034,14 @@ static int b200_same_params(const PairwiseAlignmentParameters *a, const Pairwise
 double computeForwardProbability(SymbolString sX, SymbolString sY, stList *anchorPairs, PairwiseAlignmentParameters *p,
                                  StateMachine *sM, bool alignmentHasRaggedLeftEnd, bool alignmentHasRaggedRightEnd) {
     if (sX.length + sY.length == 0) return LOG_ONE; /* impl/pairwiseAligner.c:859-862 */
+    if (tls.replay != NULL) { /* second pass of a record / replay wrapper: the answers are already known */
+        B200Deferred *r = tls.replay;
+        if (r->cursor >= r->done || r->lengths[2 * r->cursor] != sX.length || r->lengths[2 * r->cursor + 1] != sY.length)
+            st_errAbort("margin_b200: replayed forward job %" PRIi64 " does not match the recorded one\n", r->cursor);
+        return r->results[r->cursor++];
+    }
     B200Deferred *d = tls.deferred;
-    if (d != NULL && d->done + d->queue->n >= B200_MAX_DEFERRED) {
+    if (d != NULL && d->capLengths == 0 && d->done + d->queue->n >= B200_MAX_DEFERRED) { /* tags run out (not when recording) */
         if (!d->warned) st_logInfo("margin_b200: more than %" PRIi64 " forward jobs in one bubble graph; the rest run one by one\n",
                                    (int64_t) B200_MAX_DEFERRED);
         d->warned = 1;
@@ -1056,6 +1068,14 @@ double computeForwardProbability(SymbolString sX, SymbolString sY, stList *ancho
     }
     tls.dynamicAnchors = p->dynamicAnchorExpansion;
     int64_t job = d->done + d->queue->n;
+    if (d->lengths != NULL || d->capLengths < 0) { /* recording for a replay */
+        if (2 * (job + 1) > d->capLengths) {
+            d->capLengths = d->capLengths < 0 ? 4096 : d->capLengths * 2;
+            d->lengths = st_realloc(d->lengths, d->capLengths * sizeof(int64_t));
+        }
+        d->lengths[2 * job] = sX.length;
+        d->lengths[2 * job + 1] = sY.length;
+    }
     b200_batch_add(d->queue, sX, sY, anchorPairs, 0, slot, alignmentHasRaggedLeftEnd, alignmentHasRaggedRightEnd);
     if (d->queue->offX[d->queue->n] + d->queue->offY[d->queue->n] > B200_FLUSH_SYMBOLS) b200_deferred_flush(d);
     return b200_tagged_nan(job);
@@ -1077,40 +1097,143 @@ static int b200_bubbleBatching = -1;
 /* A/B hook of the test suite (oracle/b200_tests.c): 0 = every forward matrix as a GPU batch of one. */
 void margin_b200_binding_set_bubble_batching(int on) { b200_bubbleBatching = on != 0; }
 
-BubbleGraph *bubbleGraph_constructFromPoaAndVCF(Poa *poa, stList *bamChunkReads, stList *vcfEntries, PolishParams *params,
-                                                bool phasing) {
+static int b200_batching_on(void) {
     if (b200_bubbleBatching < 0) { /* MARGIN_B200_BUBBLE_BATCH=0: every matrix as a batch of one (A/B check only) */
         const char *e = getenv("MARGIN_B200_BUBBLE_BATCH");
         b200_bubbleBatching = !(e != NULL && e[0] == '0');
     }
-    if (tls.deferred != NULL || !b200_bubbleBatching) /* nested calls do not occur in the reference; the outer one would patch */
-        return bubbleGraph_constructFromPoaAndVCF_reference(poa, bamChunkReads, vcfEntries, params, phasing);
-    B200Deferred d;
-    memset(&d, 0, sizeof(d));
-    d.queue = b200_batch_construct(1024);
-    tls.deferred = &d;
+    return b200_bubbleBatching && tls.deferred == NULL && tls.replay == NULL; /* nested calls do not occur in the reference */
+}
+
+static void b200_deferred_begin(B200Deferred *d) {
+    memset(d, 0, sizeof(*d));
+    d->queue = b200_batch_construct(1024);
+    tls.deferred = d;
     forwardDeviceMs = 0.0;
-    double tStart = omp_get_wtime();
-    BubbleGraph *bg = bubbleGraph_constructFromPoaAndVCF_reference(poa, bamChunkReads, vcfEntries, params, phasing);
+}
+
+/* Runs what is queued and replaces every tagged float of the graph by its job's result. */
+static void b200_deferred_patch(B200Deferred *d, BubbleGraph *bg) {
     tls.deferred = NULL;
-    double tBuilt = omp_get_wtime();
-    b200_deferred_flush(&d);
-    double tScored = omp_get_wtime();
-    for (uint64_t i = 0; i < bg->bubbleNo; i++) {
+    b200_deferred_flush(d);
+    for (uint64_t i = 0; bg != NULL && i < bg->bubbleNo; i++) {
         Bubble *b = &bg->bubbles[i];
         for (uint64_t k = 0; k < b->alleleNo * b->readNo; k++) {
             int64_t job = b200_tag_of(b->alleleReadSupports[k]);
             if (job < 0) continue;
-            if (job >= d.done) st_errAbort("margin_b200: forward job %" PRIi64 " of %" PRIi64 " was never queued\n", job, d.done);
-            b->alleleReadSupports[k] = (float) d.results[job]; /* the conversion of impl/bubbleGraph.c:1067 */
+            if (job >= d->done) st_errAbort("margin_b200: forward job %" PRIi64 " of %" PRIi64 " was never queued\n", job, d->done);
+            b->alleleReadSupports[k] = (float) d->results[job]; /* the conversion of impl/bubbleGraph.c:1067 */
         }
     }
+}
+
+static void b200_deferred_end(B200Deferred *d) {
+    b200_batch_destruct(d->queue);
+    free(d->results);
+    free(d->lengths);
+}
+
+BubbleGraph *bubbleGraph_constructFromPoaAndVCF(Poa *poa, stList *bamChunkReads, stList *vcfEntries, PolishParams *params,
+                                                bool phasing) {
+    if (!b200_batching_on())
+        return bubbleGraph_constructFromPoaAndVCF_reference(poa, bamChunkReads, vcfEntries, params, phasing);
+    B200Deferred d;
+    b200_deferred_begin(&d);
+    double tStart = omp_get_wtime();
+    BubbleGraph *bg = bubbleGraph_constructFromPoaAndVCF_reference(poa, bamChunkReads, vcfEntries, params, phasing);
+    double tBuilt = omp_get_wtime();
+    b200_deferred_patch(&d, bg);
+    double tScored = omp_get_wtime();
     st_logInfo(" margin_b200 bubble graph%s: %" PRIi64 " forward matrices, graph %.3f s, forward batch %.3f s "
                "(%.1f ms on the device)\n", phasing ? " (phasing)" : "", d.done, tBuilt - tStart, tScored - tBuilt,
                forwardDeviceMs);
-    b200_batch_destruct(d.queue);
-    free(d.results);
+    b200_deferred_end(&d);
     return bg;
+}
+
+/*
+ * The VCF-driven constructors of `margin phase` / `margin polish --vcf` (impl/bubbleGraph.c:1126, :1338) store their
+ * forward likelihoods in Bubble.alleleReadSupports exactly like the constructor above (:1232, :1453) and return the
+ * graph: same deferral.  Linked under *_reference names like it (oracle/Makefile).
+ */
+BubbleGraph *bubbleGraph_constructFromPoaAndVCFOnlyVCFAllele_reference(Poa *poa, stList *bamChunkReads,
+                                                                       RleString *referenceSeqRLE, stList *vcfEntries,
+                                                                       Params *params);
+BubbleGraph *bubbleGraph_constructFromVCFAndBamChunkReadVcfEntrySubstrings_reference(stList *bamChunkReads,
+                                                                                     stList *vcfEntries, Params *params,
+                                                                                     stList **vcfEntriesToBubbleIdx);
+
+BubbleGraph *bubbleGraph_constructFromPoaAndVCFOnlyVCFAllele(Poa *poa, stList *bamChunkReads, RleString *referenceSeqRLE,
+                                                             stList *vcfEntries, Params *params) {
+    if (!b200_batching_on())
+        return bubbleGraph_constructFromPoaAndVCFOnlyVCFAllele_reference(poa, bamChunkReads, referenceSeqRLE, vcfEntries, params);
+    B200Deferred d;
+    b200_deferred_begin(&d);
+    BubbleGraph *bg = bubbleGraph_constructFromPoaAndVCFOnlyVCFAllele_reference(poa, bamChunkReads, referenceSeqRLE, vcfEntries, params);
+    b200_deferred_patch(&d, bg);
+    st_logInfo(" margin_b200 bubble graph (VCF alleles): %" PRIi64 " forward matrices in one batch\n", d.done);
+    b200_deferred_end(&d);
+    return bg;
+}
+
+BubbleGraph *bubbleGraph_constructFromVCFAndBamChunkReadVcfEntrySubstrings(stList *bamChunkReads, stList *vcfEntries,
+                                                                           Params *params, stList **vcfEntriesToBubbleIdx) {
+    if (!b200_batching_on())
+        return bubbleGraph_constructFromVCFAndBamChunkReadVcfEntrySubstrings_reference(bamChunkReads, vcfEntries, params,
+                                                                                       vcfEntriesToBubbleIdx);
+    B200Deferred d;
+    b200_deferred_begin(&d);
+    BubbleGraph *bg = bubbleGraph_constructFromVCFAndBamChunkReadVcfEntrySubstrings_reference(bamChunkReads, vcfEntries, params,
+                                                                                              vcfEntriesToBubbleIdx);
+    b200_deferred_patch(&d, bg);
+    st_logInfo(" margin_b200 bubble graph (VCF read substrings): %" PRIi64 " forward matrices in one batch\n", d.done);
+    b200_deferred_end(&d);
+    return bg;
+}
+
+/*
+ * bubbleGraph_partitionFilteredReads (impl/bubbleGraph.c:1500-1745; the diploid path, polish.c:821) consumes every
+ * likelihood in the iteration that asks for it (:1657-1670), so tagging does not work.  But which matrices it asks for
+ * does not depend on the answers: the wrapper runs the reference's body TWICE.  The first pass records (every
+ * computeForwardProbability queues its job; outputs go to throw-away sets, no file), the queue runs as one batch, and
+ * the second pass is the real one, with computeForwardProbability handing the recorded answers back in order (each
+ * checked against the recorded matrix size).  The price is the function's host-side bookkeeping twice; what it buys is
+ * one GPU batch instead of one launch + synchronisation per 11 x 11 matrix.
+ */
+BubbleGraph *bubbleGraph_partitionFilteredReads_reference(Poa *poa, stList *bamChunkReads, stGenomeFragment *gF,
+                                                          BubbleGraph *bg, BamChunk *bamChunk,
+                                                          uint64_t *reference_rleToNonRleCoordMap, stSet *hap1Reads,
+                                                          stSet *hap2Reads, PolishParams *params, FILE *out,
+                                                          char *logIdentifier);
+
+BubbleGraph *bubbleGraph_partitionFilteredReads(Poa *poa, stList *bamChunkReads, stGenomeFragment *gF, BubbleGraph *bg,
+                                                BamChunk *bamChunk, uint64_t *reference_rleToNonRleCoordMap,
+                                                stSet *hap1Reads, stSet *hap2Reads, PolishParams *params, FILE *out,
+                                                char *logIdentifier) {
+    if (!b200_batching_on())
+        return bubbleGraph_partitionFilteredReads_reference(poa, bamChunkReads, gF, bg, bamChunk, reference_rleToNonRleCoordMap,
+                                                            hap1Reads, hap2Reads, params, out, logIdentifier);
+    B200Deferred d;
+    b200_deferred_begin(&d);
+    d.capLengths = -1; /* record the matrix sizes too */
+    stSet *scratch1 = stSet_construct(), *scratch2 = stSet_construct();
+    char *dryRunId = stString_print("%s (margin_b200 dry run: queueing forward matrices)", logIdentifier);
+    bubbleGraph_partitionFilteredReads_reference(poa, bamChunkReads, gF, bg, bamChunk, reference_rleToNonRleCoordMap, scratch1,
+                                                 scratch2, params, NULL, dryRunId);
+    free(dryRunId);
+    stSet_destruct(scratch1);
+    stSet_destruct(scratch2);
+    b200_deferred_patch(&d, NULL);
+    tls.replay = &d;
+    d.cursor = 0;
+    BubbleGraph *r = bubbleGraph_partitionFilteredReads_reference(poa, bamChunkReads, gF, bg, bamChunk,
+                                                                  reference_rleToNonRleCoordMap, hap1Reads, hap2Reads, params,
+                                                                  out, logIdentifier);
+    tls.replay = NULL;
+    if (d.cursor != d.done) st_errAbort("margin_b200: replay used %" PRIi64 " of %" PRIi64 " recorded forward jobs\n", d.cursor, d.done);
+    st_logInfo(" margin_b200 partition of filtered reads: %" PRIi64 " forward matrices in one batch\n", d.done);
+    b200_deferred_end(&d);
+    return r;
 }
 
 /* poa_polish (impl/poa.c:1852-1873): the reference's body, its bubble graph built through the batching wrapper above. */

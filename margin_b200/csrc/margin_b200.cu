@@ -1050,12 +1050,13 @@ int64_t range_cells_bound(const margin_b200_ctx *c, int j, int d_lo, int d_hi) {
 // Cuts every traceback segment into tiles (see pairhmm_tiles.cuh) and lays the tiles out in the order of the
 // reference's final lists: alignments in batch order, blocks of an alignment in order, later tracebacks first, and
 // inside a traceback the lowest diagonals first (each tile's tuples are reversed by the gather).
-// Number of tiles a traceback segment of `span` diagonals is cut into at tile length L (a remainder shorter than
-// L/4 is merged into the lowest tile).
-inline int tiles_of_span(int span, int L) {
-    if (span <= L) return 1;
-    const int nt = span / L;
-    return nt + ((span - nt * L >= L / 4) ? 1 : 0);
+// Number of tiles a traceback segment of `span` diagonals is cut into at tile length L: the fewest tiles no longer than
+// L, all of (nearly) the same length, so that the groups of a warp finish together and the tile count falls smoothly
+// as L grows (a fixed step with a merged remainder left a fifth of the slots empty on some chunk sizes).
+inline int tiles_of_span(int span, int L) { return span <= L ? 1 : (span + L - 1) / L; }
+inline int tile_step(int span, int L) {
+    const int nt = tiles_of_span(span, L);
+    return std::max(10, ((span + nt - 1) / nt + 9) / 10 * 10);
 }
 
 // Tile length for this batch.  The backward kernel is the longest launch and runs bwd_slots lane groups of 8 at a time
@@ -1146,16 +1147,17 @@ inline int warmup_end_above(const mb::AnchorGap *g, int ng, int at, int W, int l
 void cut_segment(const mb::AnchorGap *g, int ng, int tb_to, int tb_from, int L, std::vector<int32_t> &edges) {
     edges.clear();
     edges.push_back(tb_from);
+    const int step = tile_step(tb_from - tb_to, L);
     int cur = tb_from;
-    while (cur - tb_to > L) {
-        int b = cur - L;
+    while (cur - tb_to > step) {
+        int b = cur - step;
         for (int k = 0; k < ng; k++) {
             if (g[k].lo < b && b < g[k].hi) {
                 b = cur - (cur - g[k].lo + 9) / 10 * 10;
                 break;
             }
         }
-        if (b - tb_to < L / 4) break;  // a short remainder is merged into this tile
+        if (b - tb_to < 10) break;  // nothing worth a tile of its own is left
         edges.push_back(b);
         cur = b;
     }

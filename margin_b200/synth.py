@@ -204,10 +204,13 @@ HET = dict(sub=0.001, ins=0.0001, dele=0.0001, hp_frac=0.6)  # second haplotype 
 
 
 def write_polish_dataset(out_dir, seed=42, contig_len=100000, depth=60, read_len=20000, err=ONT, draft_err=0.01,
-                         contig_name="contig_1", het=None):
+                         contig_name="contig_1", het=None, low_mapq_frac=0.0):
     """Writes <out_dir>/draft.fa and <out_dir>/reads.sam; returns (fasta_path, sam_path, n_reads, draft_len).
     ``het`` (e.g. HET): a second haplotype = the truth mutated at these rates; every read is drawn from one of the
-    two haplotypes with probability 1/2 (the diploid workload of `margin polish --diploid`)."""
+    two haplotypes with probability 1/2 (the diploid workload of `margin polish --diploid`).
+    ``low_mapq_frac``: this share of the reads gets MAPQ 1, below filterAlignmentsWithMapQBelowThisThreshold (5): margin
+    sets them aside as filtered reads and, in a diploid run, assigns them to haplotypes afterwards
+    (bubbleGraph_partitionFilteredReads, polish.c:776-821)."""
     import os
     rng = np.random.default_rng(seed)
     truth = rng.integers(0, 4, contig_len).astype(np.uint16)
@@ -240,7 +243,8 @@ def write_polish_dataset(out_dir, seed=42, contig_len=100000, depth=60, read_len
         seq = _BASES[read].tobytes().decode()
         # a reverse-strand read is stored reverse-complemented in a BAM, i.e. in reference orientation: the same
         # text, flag 16 (margin picks the reverse-strand state machine from the flag, htsIntegration.c:845-848)
-        recs.append((int(ax[0]), "read_%06d" % k, 0 if fwd else 16, _cigar(ax, ay, len(read)), seq))
+        mapq = 1 if rng.random() < low_mapq_frac else 60
+        recs.append((int(ax[0]), "read_%06d" % k, 0 if fwd else 16, _cigar(ax, ay, len(read)), seq, mapq))
     recs.sort(key=lambda r: (r[0], r[1]))
     os.makedirs(out_dir, exist_ok=True)
     fa = os.path.join(out_dir, "draft.fa")
@@ -254,6 +258,6 @@ def write_polish_dataset(out_dir, seed=42, contig_len=100000, depth=60, read_len
     sam = os.path.join(out_dir, "reads.sam")
     with open(sam, "w") as fh:
         fh.write("@HD\tVN:1.6\tSO:coordinate\n@SQ\tSN:%s\tLN:%d\n" % (contig_name, len(draft)))
-        for pos, name, flag, cigar, seq in recs:
-            fh.write("%s\t%d\t%s\t%d\t60\t%s\t*\t0\t0\t%s\t*\n" % (name, flag, contig_name, pos + 1, cigar, seq))
+        for pos, name, flag, cigar, seq, mapq in recs:
+            fh.write("%s\t%d\t%s\t%d\t%d\t%s\t*\t0\t0\t%s\t*\n" % (name, flag, contig_name, pos + 1, mapq, cigar, seq))
     return fa, sam, len(recs), len(draft)

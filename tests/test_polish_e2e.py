@@ -122,3 +122,44 @@ def test_every_batch_of_the_polish_run_matches_the_oracle(tmp_path, monkeypatch)
                     raise AssertionError("%s alignment %d (%s): %s" % (os.path.basename(path), i, env_set, e))
         n_aln += len(items)
     print("%d batches, %d alignments replayed against the oracle" % (len(dumps), n_aln))
+
+
+# Synthetic diploid region with reads that margin sets aside and assigns to haplotypes afterwards (MAPQ below the filter
+# threshold): exercises bubbleGraph_partitionFilteredReads (impl/bubbleGraph.c:1500, polish.c:821), which the binding
+# wraps with its record / replay batching.  Digests of both haplotype FASTAs from the unmodified reference
+# (oracle/_ref/margin_ref -2 -t 1 in this container; 41 filtered reads: 18 to hap1, 23 to hap2).
+EXPECTED_FILTERED_DIPLOID_MD5 = ("21485d0dde6ca98ff9307926e0729b81", "840c07e181bc34c1dbe5b44835ea26a9")
+
+
+def _filtered_diploid_run(tmp_path, binary):
+    import sys
+    sys.path.insert(0, ROOT)
+    from margin_b200 import synth
+    if not (os.path.exists(os.path.join(REF, binary)) and os.path.exists(os.path.join(REF, "sam2bam"))):
+        pytest.skip("oracle/_ref/%s not built (needs /root/reference at build time)" % binary)
+    fa, sam, _, _ = synth.write_polish_dataset(str(tmp_path), 7, 30000, 40, 8000, synth.ONT, 0.01, het=synth.HET, low_mapq_frac=0.25)
+    bam = str(tmp_path / "reads.bam")
+    subprocess.run([os.path.join(REF, "sam2bam"), sam, bam], check=True, stderr=subprocess.DEVNULL)
+    prefix = str(tmp_path / "out")
+    cmd = [os.path.join(REF, binary), "polish", bam, fa,
+           os.path.join(REF, "data", "params", "polish", "ont", "r9.4", "allParams.np.human.r94-g360.json"),
+           "-t", "1", "-2", "-o", prefix, "-a", "info"]
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=1500)
+    assert r.returncode == 0, r.stdout[-3000:]
+    got = tuple(hashlib.md5(open("%s.fa.%s" % (prefix, h), "rb").read()).hexdigest() for h in ("hap1", "hap2"))
+    return got, r.stdout
+
+
+def test_filtered_reads_partition_on_the_cpu_stand_in(tmp_path):
+    """CPU: host side of the record / replay wrapper against oracle/stub_b200.c (test-only stand-in for the CUDA library)."""
+    got, log = _filtered_diploid_run(tmp_path, "margin_stubcli")
+    assert "margin_b200 partition of filtered reads: 465 forward matrices in one batch" in log
+    assert "Of 41 filtered reads: 18 (0.44) were hap1, 23 (0.56) were hap2" in log
+    assert got == EXPECTED_FILTERED_DIPLOID_MD5
+
+
+@pytest.mark.gpu
+def test_filtered_reads_partition_is_batched_and_identical(tmp_path):
+    got, log = _filtered_diploid_run(tmp_path, "margin_b200cli")
+    assert "margin_b200 partition of filtered reads: 465 forward matrices in one batch" in log
+    assert got == EXPECTED_FILTERED_DIPLOID_MD5
