@@ -30,11 +30,13 @@ def _polish(binary, out_prefix, threads, env=None):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("mode", ["tiles", "sequential"])
+@pytest.mark.parametrize("mode", ["tiles", "sequential", "tiles_f32"])
 def test_margin_polish_with_b200_aligner_is_byte_identical(tmp_path, mode):
     if not os.path.exists(os.path.join(REF, "margin_b200cli")):
         pytest.skip("oracle/_ref/margin_b200cli not built (needs /root/reference at build time)")
-    env = dict(os.environ, MARGIN_B200_MODE=mode)
+    env = dict(os.environ, MARGIN_B200_MODE=mode.split("_")[0])
+    if mode.endswith("f32"):  # the FP32 fast mode: posteriors differ by ~1e-5, the consensus must not
+        env["MARGIN_B200_PRECISION"] = "f32"
     md5, dt, log = _polish("margin_b200cli", str(tmp_path / "b200"), 2, env)
     stages = [l.strip() for l in log.splitlines() if "Took" in l]
     print("margin_b200cli (%s): %.1f s wall\n%s" % (mode, dt, "\n".join(stages[:12])))
