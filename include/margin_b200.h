@@ -217,6 +217,24 @@ int margin_b200_download_result(margin_b200_ctx *ctx, margin_b200_result *out);
  * truncates to float at the call site, impl/bubbleGraph.c:1067). */
 int margin_b200_forward_batch(margin_b200_ctx *ctx, const margin_b200_batch *batch, double *out_log_prob,
                               margin_b200_result *stats);
+/* The forward-only likelihoods of SMALL matrices with no allocation at all.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  Same kernels and same results, bit for bit, as margin_b200_forward_batch;
+ * the scratch (packed symbols, job table, work lists) is a fixed 16 MiB device array inside the library, held by every
+ * GPU that loads it until exit.  Limits per call: at most MARGIN_B200_NOALLOC_MAX_ALIGNMENTS alignments,
+ * MARGIN_B200_NOALLOC_MAX_SYMBOLS symbols per side, no anchors, no ragged ends, and every matrix must have a shorter
+ * side of at most 31 symbols (the bubble-graph case); anything beyond is rejected with a clear error, nothing is
+ * truncated.  All pointers except ctx are DEVICE pointers owned by the caller (offsets as in margin_b200_batch,
+ * total_x = off_x[n], total_y = off_y[n]; d_model_slot may be NULL = slot 0; d_out_log_prob holds n doubles).  The call
+ * runs on the context's stream and returns when the results are in d_out_log_prob.  It calls no cudaMalloc / cudaFree
+ * or any allocating routine; the models must have been set before (margin_b200_set_model allocates, once).  All calls
+ * on a device share the scratch array, which keeps the last call's contents (what must start at zero is cleared by
+ * every call): calls that overlap on the GPU race, so issue them one at a time per device. */
+#define MARGIN_B200_NOALLOC_MAX_ALIGNMENTS 65536
+#define MARGIN_B200_NOALLOC_MAX_SYMBOLS (4 << 20)
+int margin_b200_forward_tiny_noalloc(margin_b200_ctx *ctx, int64_t n, const uint16_t *d_sym_x, const int64_t *d_off_x,
+                                     int64_t total_x, const uint16_t *d_sym_y, const int64_t *d_off_y, int64_t total_y,
+                                     const uint8_t *d_model_slot, double *d_out_log_prob);
 /* Kernel-only step of the above on a batch staged by margin_b200_upload_batch. */
 int margin_b200_forward_resident(margin_b200_ctx *ctx, margin_b200_result *stats);
 

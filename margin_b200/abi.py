@@ -266,6 +266,8 @@ def load_library():
     lib.margin_b200_download_result.restype = i32
     lib.margin_b200_forward_batch.argtypes = [vp, C.POINTER(BatchStruct), vp, C.POINTER(ResultStruct)]
     lib.margin_b200_forward_batch.restype = i32
+    lib.margin_b200_forward_tiny_noalloc.argtypes = [vp, i64, vp, vp, i64, vp, vp, i64, vp, vp]
+    lib.margin_b200_forward_tiny_noalloc.restype = i32
     lib.margin_b200_forward_resident.argtypes = [vp, C.POINTER(ResultStruct)]
     lib.margin_b200_forward_resident.restype = i32
     lib.margin_b200_bands.argtypes = [vp, C.POINTER(BatchStruct), vp, vp]
@@ -281,7 +283,7 @@ EXPORTED_SYMBOLS = [
     "margin_b200_set_model", "margin_b200_set_params", "margin_b200_set_pair_format", "margin_b200_set_precision",
     "margin_b200_get_precision", "margin_b200_pinned_alloc", "margin_b200_pinned_free", "margin_b200_set_kernel_timing", "margin_b200_posteriors_batch",
     "margin_b200_upload_batch", "margin_b200_posteriors_resident", "margin_b200_download_result",
-    "margin_b200_forward_batch", "margin_b200_forward_resident", "margin_b200_bands",
+    "margin_b200_forward_batch", "margin_b200_forward_resident", "margin_b200_forward_tiny_noalloc", "margin_b200_bands",
     "margin_b200_last_kernel_ms", "margin_b200_device_count", "margin_b200_prewarm",
 ]
 

@@ -171,6 +171,12 @@ class PairHmmAligner:
         self.last_stats = _stats(res)
         return out[:batch.n]
 
+    def forward_tiny_noalloc(self, n, d_sym_x, d_off_x, total_x, d_sym_y, d_off_y, total_y, d_model_slot, d_out):
+        """margin_b200_forward_tiny_noalloc: device pointers (ints) in and out, fixed scratch inside the library, no
+        allocation (include/margin_b200.h)."""
+        self._check(self.lib.margin_b200_forward_tiny_noalloc(self._h, int(n), d_sym_x, d_off_x, int(total_x), d_sym_y, d_off_y,
+                                                              int(total_y), d_model_slot, d_out))
+
     def forward_resident(self):
         res = abi.ResultStruct()
         self._check(self.lib.margin_b200_forward_resident(self._h, C.byref(res)))

@@ -2547,3 +2547,117 @@ extern "C" int margin_b200_bands(margin_b200_ctx *c, const margin_b200_batch *b,
     }
     return 0;
 }
+
+// ------------------------------------------------------------------------------------------------------------------
+// Forward-only likelihoods of small matrices WITHOUT any allocation (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: code under CUDA graph capture, tight serving
+// loops, harnesses that forbid it).  The same kernels as margin_b200_forward_batch's register-resident path
+// (pack_symbols_kernel, forward_jobs_kernel, tiny_forward_kernel), but every scratch array — packed symbols, job table,
+// work lists, counters — lives in ONE file-scope device array of fixed size instead of the context's grow-only buffers.
+// Every GPU that loads the library holds these 16 MiB until exit.  All calls (of all contexts on a device) share the
+// array and it keeps the last call's contents: the counters and the slack around the packed symbols are cleared by every
+// call, everything else is overwritten before it is read; calls that overlap on the GPU race — serialise them.
+namespace {
+
+constexpr size_t kNoAllocBytes = (size_t) 16 << 20;
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocBytes];
+
+// layout of g_noalloc_scratch
+constexpr size_t kNaCounts = 0;  // int32[4] list lengths + bad-slot flag | +32: uint64 cells | +64: int32[2] symbol error
+constexpr size_t kNaJobs = 256;
+constexpr size_t kNaIds = kNaJobs + (size_t) MARGIN_B200_NOALLOC_MAX_ALIGNMENTS * sizeof(mb::Job);
+constexpr size_t kNaPx = (kNaIds + (size_t) 3 * MARGIN_B200_NOALLOC_MAX_ALIGNMENTS * sizeof(int32_t) + 255) / 256 * 256;
+constexpr size_t kNaPy = kNaPx + (size_t) MARGIN_B200_NOALLOC_MAX_SYMBOLS + 2 * mb::PACK_SLACK + 128;
+constexpr size_t kNaEnd = kNaPy + (size_t) MARGIN_B200_NOALLOC_MAX_SYMBOLS + 2 * mb::PACK_SLACK;
+static_assert(kNaEnd <= kNoAllocBytes, "the no-alloc scratch layout must fit its array");
+static_assert(kNaPy % 128 == 0 && kNaJobs % 16 == 0, "sections stay aligned");
+
+std::mutex g_noalloc_mu;
+unsigned char *g_noalloc_ptr[kMaxDevices];  // device address of the array on each device (the symbol itself is a host-side stand-in)
+
+// once per device, with that device current
+int noalloc_scratch(int device, unsigned char **out) {
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    unsigned char *&p = g_noalloc_ptr[device & (kMaxDevices - 1)];
+    if (p == nullptr) {
+        void *addr = nullptr;
+        CU(cudaGetSymbolAddress(&addr, g_noalloc_scratch));
+        p = static_cast<unsigned char *>(addr);
+    }
+    *out = p;
+    return 0;
+}
+
+}  // namespace
+
+extern "C" int margin_b200_forward_tiny_noalloc(margin_b200_ctx *c, int64_t n, const uint16_t *d_sym_x, const int64_t *d_off_x,
+                                                int64_t total_x, const uint16_t *d_sym_y, const int64_t *d_off_y,
+                                                int64_t total_y, const uint8_t *d_model_slot, double *d_out_log_prob) {
+    if (!c || !d_off_x || !d_off_y || !d_out_log_prob) return fail("margin_b200_forward_tiny_noalloc: null argument");
+    if (!c->have_params) return fail("margin_b200_forward_tiny_noalloc: margin_b200_set_params has not been called");
+    if (n < 0 || total_x < 0 || total_y < 0) return fail("margin_b200_forward_tiny_noalloc: negative size");
+    if (n > MARGIN_B200_NOALLOC_MAX_ALIGNMENTS)
+        return fail("margin_b200_forward_tiny_noalloc: %lld alignments exceed the fixed scratch (at most %d per call)",
+                    (long long) n, MARGIN_B200_NOALLOC_MAX_ALIGNMENTS);
+    if (total_x > MARGIN_B200_NOALLOC_MAX_SYMBOLS || total_y > MARGIN_B200_NOALLOC_MAX_SYMBOLS)
+        return fail("margin_b200_forward_tiny_noalloc: %lld / %lld symbols exceed the fixed scratch (at most %d per side and call)",
+                    (long long) total_x, (long long) total_y, MARGIN_B200_NOALLOC_MAX_SYMBOLS);
+    if ((total_x && !d_sym_x) || (total_y && !d_sym_y)) return fail("margin_b200_forward_tiny_noalloc: null symbol array");
+    if (!c->have_model[0] && !c->have_model[1]) return fail("margin_b200_forward_tiny_noalloc: no model has been set");
+    if (n == 0) return 0;
+    if (check_device(c->device)) return 1;
+    CU(cudaSetDevice(c->device));
+    unsigned char *scr = nullptr;
+    if (noalloc_scratch(c->device, &scr)) return 1;
+    if (c->have_model[0] && c->have_model[1] && c->host_models[0].rle != c->host_models[1].rle)
+        return fail("the two state machines of a batch must both use (or both not use) repeat counts");
+    const int rle = c->host_models[c->have_model[0] ? 0 : 1].rle;
+    bool have_switch = false;
+    for (int k = 0; k < 2; k++)
+        if (c->have_model[k] && (c->host_models[k].t[mb::T_YX] != -INFINITY || c->host_models[k].t[mb::T_XY] != -INFINITY))
+            have_switch = true;
+    cudaStream_t st = c->stream;
+    int32_t *counts = reinterpret_cast<int32_t *>(scr + kNaCounts);
+    unsigned long long *cells = reinterpret_cast<unsigned long long *>(scr + kNaCounts + 32);
+    int *sym_err = reinterpret_cast<int *>(scr + kNaCounts + 64);
+    mb::Job *jobs = reinterpret_cast<mb::Job *>(scr + kNaJobs);
+    int32_t *ids16 = reinterpret_cast<int32_t *>(scr + kNaIds), *ids32 = ids16 + n, *ids_gen = ids32 + n;
+    uint8_t *px = scr + kNaPx, *py = scr + kNaPy;
+    // what must start at zero: the counters, and the packed symbol arrays with their slack (the kernels read one or two
+    // bytes beyond a sequence and rely on finding a valid packed symbol there)
+    CU(cudaMemsetAsync(scr + kNaCounts, 0, 256, st));
+    CU(cudaMemsetAsync(px, 0, (size_t) total_x + 2 * mb::PACK_SLACK, st));
+    CU(cudaMemsetAsync(py, 0, (size_t) total_y + 2 * mb::PACK_SLACK, st));
+    if (total_x) mb::pack_symbols_kernel<<<(unsigned) ((total_x + 255) / 256), 256, 0, st>>>(d_sym_x, px + mb::PACK_SLACK, total_x, rle, sym_err);
+    if (total_y) mb::pack_symbols_kernel<<<(unsigned) ((total_y + 255) / 256), 256, 0, st>>>(d_sym_y, py + mb::PACK_SLACK, total_y, rle, sym_err);
+    mb::forward_jobs_kernel<<<(unsigned) ((n + 255) / 256), 256, 0, st>>>(n, d_off_x, d_off_y, d_model_slot, nullptr, nullptr,
+                                                                       c->have_model[0] ? 1 : 0, c->have_model[1] ? 1 : 0, jobs,
+                                                                       ids16, ids32, ids_gen, counts, cells);
+    int32_t h[20];  // the counters come back to the stack: no pinned or pageable buffer is allocated for them
+    CU(cudaMemcpyAsync(h, scr + kNaCounts, sizeof(h), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    CU(cudaGetLastError());
+    if (h[3]) return fail("margin_b200_forward_tiny_noalloc: an alignment uses a model slot that has not been set (or has a negative length)");
+    if (h[16]) return fail("a symbol carries a run length >= %d; the repeat-count model holds 0..%d", MARGIN_B200_MAX_RL, MARGIN_B200_MAX_RL - 1);
+    if (h[2] > 0)
+        return fail("margin_b200_forward_tiny_noalloc: %d matrices have a shorter side of more than 31 symbols; this entry point "
+                    "only takes matrices that are swept in registers (use margin_b200_forward_batch)", h[2]);
+    const int e = (int) c->params.diagonal_expansion;
+    auto launch = [&](auto g_tag, const int32_t *ids, int count) {
+        constexpr int G = decltype(g_tag)::value;
+        if (count <= 0) return;
+        const int per_block = kTileThreads / G;
+        const unsigned grid = (unsigned) ((count + per_block - 1) / per_block);
+        if (have_switch)
+            mb::tiny_forward_kernel<G, kTileThreads, true><<<grid, kTileThreads, 0, st>>>(
+                jobs, ids, count, c->d_models.as<mb::DevModel>(), px + mb::PACK_SLACK, py + mb::PACK_SLACK, e, d_out_log_prob);
+        else
+            mb::tiny_forward_kernel<G, kTileThreads, false><<<grid, kTileThreads, 0, st>>>(
+                jobs, ids, count, c->d_models.as<mb::DevModel>(), px + mb::PACK_SLACK, py + mb::PACK_SLACK, e, d_out_log_prob);
+    };
+    launch(std::integral_constant<int, 16>{}, ids16, h[0]);
+    launch(std::integral_constant<int, 32>{}, ids32, h[1]);
+    CU(cudaStreamSynchronize(st));
+    CU(cudaGetLastError());
+    return 0;
+}
