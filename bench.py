@@ -641,11 +641,13 @@ def main_ours(args):
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` capture of this workload
-NCU_TRAFFIC_SOURCE = "profiles/r01_v7_tiles_ncu_raw_selected.txt (ncu --set full, one launch, default workload)"
-NCU_DRAM_BYTES_PER_LAUNCH = {
-    (DEFAULT_WORKLOAD, "forward"): 0.100834e9 + 1.132209e9,
-    (DEFAULT_WORKLOAD, "backward"): 1.299964e9 + 0.137514e9,
-    (DEFAULT_WORKLOAD, "band"): 0.052305e9 + 0.023034e9,
+NCU_TRAFFIC_SOURCE = ("profiles/r02_tiles_ncu_raw_selected.txt (ncu --set full, one launch of the 100 kb chunk of configs[1], "
+                      "scripts/ncu_target.py)")
+NCU_DRAM_BYTES_PER_LAUNCH = {  # keyed by (arithmetic, kernel class)
+    ("f64", "forward"): 0.104837e9 + 1.132977e9,
+    ("f64", "backward"): 1.305050e9 + 0.140474e9,
+    ("f32", "forward"): 0.111883e9 + 0.779340e9,
+    ("f32", "backward"): 0.953477e9 + 0.139526e9,
 }
 
 
@@ -782,7 +784,7 @@ def main():
     ap.add_argument("--plain-formats", action="store_true",
                     help="12-byte anchor triples in, 12-byte tuple records out instead of the compact boundary formats")
     ap.add_argument("--no-sustained", action="store_true", help="skip the two-context sustained end-to-end leg")
-    ap.add_argument("--polish-synth", type=int, default=1000, metavar="KB",
+    ap.add_argument("--polish-synth", type=int, default=2000, metavar="KB",
                     help="polished Mb/hour of `margin polish` on a synthetic contig of KB kilobases (60x 20 kb ONT-like reads, "
                          "100 kb chunks; BASELINE configs[2] is 5000): the CLI linked against this library, or the unmodified "
                          "reference CLI with --impl reference; 0 = skip")
@@ -791,7 +793,7 @@ def main():
                     help="arithmetic of the lane-group tile kernels (include/margin_b200.h: margin_b200_set_precision)")
     ap.add_argument("--e2e-seconds", type=float, default=2.0, help="timed window of the sustained end-to-end leg")
     ap.add_argument("--no-fast-mode", action="store_true", help="skip the FP32 fast-mode object of the line")
-    ap.add_argument("--polish-threads", type=int, default=16)
+    ap.add_argument("--polish-threads", type=int, default=64, help="-t of the margin polish runs (capped at the host's cores)")
     ap.add_argument("--polish-skip-reference", action="store_true")
     ap.add_argument("--polish", action="store_true",
                     help="also time `margin polish` on the bundled region: reference CLI vs the CLI linked against "
