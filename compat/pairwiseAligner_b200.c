@@ -12,6 +12,7 @@
  *   computeForwardProbability               inc/pairwiseAligner.h:54-57   (impl/pairwiseAligner.c:849-905)
  *   poa_polish                              inc/margin.h:820              (impl/poa.c:1852-1873), one batched forward call
  *                                                                          per bubble graph (impl/bubbleGraph.c:1067 unchanged)
+ *   poa_estimateRepeatCountsUsingBayesianModel  inc/margin.h              (impl/poa.c:1715-1727), flat arrays, same sums
  *
  * Same signatures, same ownership (callee-allocated stLists of individually allocated stIntTuples with
  * stIntTuple_destruct as destructor), same list order, same error behaviour (invalid band ->
@@ -696,15 +697,115 @@ static RleString *b200_substring(const RleString *from, int64_t start, int64_t l
     return sub;
 }
 
+/* The backing array of an stList (its first field, externalTools/sonLib/C/impl/sonLibListPrivate.h:11-16), checked once
+ * against stList_get: the per-tuple loops below would otherwise spend a tenth of a chunk in that accessor. */
+static void **b200_list_array(stList *list) {
+    static int checked = 0;
+    if (!checked) {
+        stList *probe = stList_construct();
+        stList_append(probe, &checked);
+        stList_append(probe, &probe);
+        void **a = *(void ***) probe;
+        if (a[0] != stList_get(probe, 0) || a[1] != stList_get(probe, 1)) st_errAbort("margin_b200: stList layout check failed\n");
+        stList_destruct(probe);
+        checked = 1;
+    }
+    return *(void ***) list;
+}
+
+/*
+ * Where an insert / delete of a node already exists.  poa_augment (impl/poa.c:180-232) scans the node's list for every
+ * candidate (rleString_eq per entry): with a few hundred reads the lists grow to dozens of low-weight entries and the
+ * scans were a quarter of the augment.  During one poa_realign the graph starts without inserts and deletes, so an
+ * open-addressing table filled by this file's own appends knows every entry: key = (node position, delete length), or
+ * (node position, hash of the insert) verified with rleString_eq.  The lists themselves and their order are untouched.
+ */
+typedef struct {
+    uint64_t key; /* 0 = empty */
+    const void *owner; /* the PoaNode whose list holds the entry */
+    void *entry;
+} B200IndelSlot;
+
+typedef struct {
+    B200IndelSlot *slots;
+    uint64_t size, used;
+    int active; /* 0: the graph may hold entries this table does not know (test hook): scan the lists */
+} B200IndelTable;
+
+static __thread B200IndelTable indelTable;
+
+static void b200_indel_table_begin(int fresh) {
+    B200IndelTable *t = &indelTable;
+    if (t->slots == NULL) {
+        t->size = 1 << 16;
+        t->slots = st_calloc(t->size, sizeof(B200IndelSlot));
+    } else if (t->used > 0) {
+        memset(t->slots, 0, t->size * sizeof(B200IndelSlot));
+    }
+    t->used = 0;
+    t->active = fresh;
+}
+
+static inline uint64_t b200_mix(uint64_t h) {
+    h ^= h >> 33;
+    h *= 0xff51afd7ed558ccdULL;
+    h ^= h >> 33;
+    h *= 0xc4ceb9fe1a85ec53ULL;
+    h ^= h >> 33;
+    return h | 1; /* never 0 */
+}
+
+static void b200_indel_table_put(uint64_t key, const void *owner, void *entry) {
+    B200IndelTable *t = &indelTable;
+    if ((t->used + 1) * 2 > t->size) { /* grow and re-insert */
+        B200IndelSlot *old = t->slots;
+        uint64_t oldSize = t->size;
+        t->size *= 4;
+        t->slots = st_calloc(t->size, sizeof(B200IndelSlot));
+        for (uint64_t i = 0; i < oldSize; i++) {
+            if (old[i].key == 0) continue;
+            uint64_t at = old[i].key & (t->size - 1);
+            while (t->slots[at].key != 0) at = (at + 1) & (t->size - 1);
+            t->slots[at] = old[i];
+        }
+        free(old);
+    }
+    uint64_t at = key & (t->size - 1);
+    while (t->slots[at].key != 0) at = (at + 1) & (t->size - 1);
+    t->slots[at].key = key;
+    t->slots[at].owner = owner;
+    t->slots[at].entry = entry;
+    t->used++;
+}
+
+static inline uint64_t b200_insert_key(const PoaNode *node, const RleString *insert) {
+    uint64_t h = (uint64_t) (uintptr_t) node * 0x9E3779B97F4A7C15ULL + insert->length;
+    for (uint64_t i = 0; i < insert->length; i++)
+        h = (h ^ ((uint64_t) (unsigned char) insert->rleString[i] | (insert->repeatCounts[i] << 8))) * 0x100000001B3ULL;
+    return b200_mix(h);
+}
+
 static void b200_node_add_insert(PoaNode *node, RleString *insert, double weight, bool strand, PoaBaseObservation *obs) {
     PoaInsert *hit = NULL;
-    for (int64_t m = 0; m < stList_length(node->inserts) && hit == NULL; m++) {
-        PoaInsert *candidate = stList_get(node->inserts, m);
-        if (rleString_eq(candidate->insert, insert)) hit = candidate;
+    uint64_t key = 0;
+    if (indelTable.active) {
+        const B200IndelTable *t = &indelTable;
+        key = b200_insert_key(node, insert);
+        for (uint64_t at = key & (t->size - 1); t->slots[at].key != 0 && hit == NULL; at = (at + 1) & (t->size - 1)) {
+            if (t->slots[at].key != key || t->slots[at].owner != node) continue;
+            PoaInsert *candidate = t->slots[at].entry;
+            if (rleString_eq(candidate->insert, insert)) hit = candidate;
+        }
+    } else {
+        for (int64_t m = 0; m < stList_length(node->inserts) && hit == NULL; m++) {
+            PoaInsert *candidate = stList_get(node->inserts, m);
+            if (rleString_eq(candidate->insert, insert)) hit = candidate;
+        }
     }
     if (hit == NULL) {
         hit = poaInsert_construct(rleString_copy(insert), 0, FALSE);
         stList_append(node->inserts, hit);
+        if (indelTable.active) b200_indel_table_put(key, node, hit);
     }
     if (strand) hit->weightForwardStrand += weight;
     else hit->weightReverseStrand += weight;
@@ -713,13 +814,25 @@ static void b200_node_add_insert(PoaNode *node, RleString *insert, double weight
 
 static void b200_node_add_delete(PoaNode *node, int64_t length, double weight, bool strand, PoaBaseObservation *obs) {
     PoaDelete *hit = NULL;
-    for (int64_t m = 0; m < stList_length(node->deletes) && hit == NULL; m++) {
-        PoaDelete *candidate = stList_get(node->deletes, m);
-        if (candidate->length == length) hit = candidate;
+    uint64_t key = 0;
+    if (indelTable.active) {
+        const B200IndelTable *t = &indelTable;
+        key = b200_mix(((uint64_t) (uintptr_t) node * 0x9E3779B97F4A7C15ULL) ^ ((uint64_t) length * 0xD6E8FEB86659FD93ULL));
+        for (uint64_t at = key & (t->size - 1); t->slots[at].key != 0 && hit == NULL; at = (at + 1) & (t->size - 1)) {
+            if (t->slots[at].key != key || t->slots[at].owner != node) continue;
+            PoaDelete *candidate = t->slots[at].entry;
+            if (candidate->length == length) hit = candidate;
+        }
+    } else {
+        for (int64_t m = 0; m < stList_length(node->deletes) && hit == NULL; m++) {
+            PoaDelete *candidate = stList_get(node->deletes, m);
+            if (candidate->length == length) hit = candidate;
+        }
     }
     if (hit == NULL) {
         hit = poaDelete_construct(length, 0, FALSE);
         stList_append(node->deletes, hit);
+        if (indelTable.active) b200_indel_table_put(key, node, hit);
     }
     if (strand) hit->weightForwardStrand += weight;
     else hit->weightReverseStrand += weight;
@@ -737,8 +850,9 @@ static void b200_poa_augment(Poa *poa, RleString *read, bool readStrand, int64_t
 
     /* match weights and observations, in list order (impl/poa.c:324-341) */
     double tPhase0 = omp_get_wtime();
+    void **nodes = b200_list_array(poa->nodes);
     for (int64_t k = 0; k < nMatch; k++) {
-        PoaNode *node = stList_get(poa->nodes, matches[k].x + 1);
+        PoaNode *node = nodes[matches[k].x + 1];
         int64_t y = matches[k].y;
         node->baseWeights[poa->alphabet->convertCharToSymbol(read->rleString[y])] += matches[k].w;
         int64_t rc = read->repeatCounts[y] < poa->maxRepeatCount ? read->repeatCounts[y] : poa->maxRepeatCount - 1;
@@ -769,7 +883,7 @@ static void b200_poa_augment(Poa *poa, RleString *read, bool readStrand, int64_t
                     rleString_rotateString(insert, suffix, polishParams->useRunLengthEncoding);
                     position -= suffix;
                 }
-                b200_node_add_insert(stList_get(poa->nodes, position), insert, weight, readStrand,
+                b200_node_add_insert(nodes[position], insert, weight, readStrand,
                                      poaBaseObservation_construct(readNo, yk, weight));
             }
         }
@@ -794,7 +908,7 @@ static void b200_poa_augment(Poa *poa, RleString *read, bool readStrand, int64_t
                 RleString *deleted = b200_substring(poa->refString, xk, length);
                 int64_t position = getShift(poa->refString, xk, deleted, compareRL);
                 position -= getMaxCommonSuffixLength(poa->refString, position, deleted, compareRL);
-                b200_node_add_delete(stList_get(poa->nodes, position), length, weight, readStrand,
+                b200_node_add_delete(nodes[position], length, weight, readStrand,
                                      poaBaseObservation_construct(readNo, y, weight));
             }
         }
@@ -834,8 +948,130 @@ void margin_b200_binding_augment_lists(Poa *poa, RleString *read, bool readStran
     }
     res.n = 1;
     res.pair_format = MARGIN_B200_PAIRS_TRIPLES;
+    b200_indel_table_begin(0); /* the graph may already hold inserts and deletes: scan the lists as the reference does */
     b200_poa_augment(poa, read, readStrand, readNo, &res, 0, 0, polishParams);
     for (int l = 0; l < 3; l++) free(pairs[l]);
+}
+
+/* ---------------------------------------------------- impl/poa.c:1678-1727 + impl/repeatSubMatrix.c:65-151, flat */
+
+/*
+ * poa_estimateRepeatCountsUsingBayesianModel (SURVEY.md §8 f N4: the per-node run-length argmax, 5 % of a chunk once the
+ * aligner is on the GPU).  The reference walks every node's observation list once for the range of observed run lengths
+ * and once more per candidate length, through stList_get, the read list and repeatSubMatrix_getLogProb's index
+ * arithmetic each time.  Here: one pass that resolves every observation to (table row, weight), then one pass that
+ * updates all candidates per observation.  Every candidate's sum still receives its terms in list order, one multiply and
+ * one add each (this file is compiled with the reference's own flags), so the log-probabilities, their maximum and the
+ * consensus are bit for bit the reference's.
+ */
+typedef struct {
+    const double *row; /* logProbabilities + strand-resolved base block + observed run length */
+    double weight;
+} B200RlTerm;
+
+static __thread B200RlTerm *rlTerms;
+static __thread int64_t rlTermsCap;
+
+static int64_t b200_ml_repeat_count(Poa *poa, PoaNode *node, void **reads, RepeatSubMatrix *rsm) {
+    int64_t M = rsm->maximumRepeatLength;
+    Symbol base = poa->alphabet->convertCharToSymbol(node->base);
+    if (base >= rsm->alphabet->alphabetSize - 1) { /* repeatSubMatrix_setLogProb (impl/repeatSubMatrix.c:16-27): N counts as A */
+        if (base > rsm->alphabet->alphabetSize - 1) st_errAbort("margin_b200: base > 'Nn' (%d) not supported for repeat estimation!\n", (int) base);
+        base = 0;
+    }
+    const double *blockF = rsm->logProbabilities + (int64_t) base * M * M, *blockR = rsm->logProbabilities + (int64_t) (3 - base) * M * M;
+    int64_t n = stList_length(node->observations);
+    void **obs = b200_list_array(node->observations);
+    if (n > rlTermsCap) {
+        rlTermsCap = n * 2 + 64;
+        rlTerms = st_realloc(rlTerms, rlTermsCap * sizeof(B200RlTerm));
+    }
+    int64_t minRL = M, maxRL = 0;
+    char *maxRLReadId = NULL;
+    for (int64_t k = 0; k < n; k++) {
+        PoaBaseObservation *o = obs[k];
+        BamChunkRead *read = reads[o->readNo];
+        int64_t observed = read->rleRead->repeatCounts[o->offset];
+        if (observed < minRL) minRL = observed;
+        if (observed > maxRL) {
+            maxRL = observed;
+            maxRLReadId = read->readName;
+        }
+        if (observed >= M) observed = M - 1; /* "Be robust to over-long repeat count observations" */
+        rlTerms[k].row = (read->forwardStrand ? blockF : blockR) + observed;
+        rlTerms[k].weight = o->weight;
+    }
+    if (maxRL >= M) {
+        char *logIdentifier = getLogIdentifier();
+        st_logInfo(" %s Got overlong repeat observation(s), max: %" PRIi64 " (%s), ignoring this and cutting off overlong repeat counts to max\n",
+                   logIdentifier, maxRL, maxRLReadId);
+        maxRL = M - 1;
+        free(logIdentifier);
+    }
+    if (minRL == M) return 0; /* no valid observations: a repeat length of 0 (the caller turns it into 1) */
+    if (minRL > maxRL) st_errAbort("margin_b200: every repeat count observation of a node is over-long\n");
+    double logProb[MARGIN_B200_MAX_RL + 1];
+    if (M > MARGIN_B200_MAX_RL) st_errAbort("margin_b200: repeat matrix larger than %d\n", MARGIN_B200_MAX_RL);
+    int64_t range = maxRL - minRL + 1;
+    for (int64_t u = 0; u < range; u++) logProb[u] = LOG_ONE;
+    for (int64_t k = 0; k < n; k++) {
+        const double *row = rlTerms[k].row + minRL * M; /* [underlying][observed]: one row of M entries per candidate */
+        double w = rlTerms[k].weight;
+        for (int64_t u = 0; u < range; u++) logProb[u] += row[u * M] * w;
+    }
+    int64_t best = 0;
+    double bestValue = logProb[0] / PAIR_ALIGNMENT_PROB_1;
+    for (int64_t u = 1; u < range; u++) { /* getMax (impl/repeatSubMatrix.c:153-167): the first of equal maxima */
+        double v = logProb[u] / PAIR_ALIGNMENT_PROB_1;
+        if (v > bestValue) {
+            bestValue = v;
+            best = u;
+        }
+    }
+    return best + minRL;
+}
+
+/* getRunLengthMode (impl/poa.c:1678-1699), for parameter sets without a repeat matrix: the run length that first reaches
+ * the highest count among the observations of the node's own base. */
+static int64_t b200_run_length_mode(Poa *poa, PoaNode *node, void **reads) {
+    Symbol base = poa->alphabet->convertCharToSymbol(node->base);
+    int64_t n = stList_length(node->observations), nDistinct = 0, maxCount = 0, maxRL = 0;
+    void **obs = b200_list_array(node->observations);
+    int64_t values[64], counts[64];
+    for (int64_t k = 0; k < n; k++) {
+        PoaBaseObservation *o = obs[k];
+        RleString *rleString = ((BamChunkRead *) reads[o->readNo])->rleRead;
+        if (poa->alphabet->convertCharToSymbol(rleString->rleString[o->offset]) != base) continue;
+        int64_t rl = rleString->repeatCounts[o->offset], at = 0;
+        while (at < nDistinct && values[at] != rl) at++;
+        if (at == nDistinct) {
+            if (nDistinct == 64) st_errAbort("margin_b200: more than 64 distinct run lengths at one node\n");
+            values[nDistinct] = rl;
+            counts[nDistinct++] = 0;
+        }
+        if (++counts[at] > maxCount) {
+            maxCount = counts[at];
+            maxRL = rl;
+        }
+    }
+    return maxRL;
+}
+
+void poa_estimateRepeatCountsUsingBayesianModel(Poa *poa, stList *bamChunkReads, RepeatSubMatrix *repeatSubMatrix) {
+    double tStart = omp_get_wtime();
+    poa->refString->nonRleLength = 0;
+    int64_t nNodes = stList_length(poa->nodes);
+    void **nodes = b200_list_array(poa->nodes), **reads = b200_list_array(bamChunkReads);
+    for (int64_t i = 1; i < nNodes; i++) {
+        PoaNode *node = nodes[i];
+        int64_t rc = repeatSubMatrix == NULL ? b200_run_length_mode(poa, node, reads)
+                                             : b200_ml_repeat_count(poa, node, reads, repeatSubMatrix);
+        if (rc == 0) rc = 1; /* Prevent zero length estimates */
+        poa->refString->repeatCounts[i - 1] = rc;
+        node->repeatCount = rc;
+        poa->refString->nonRleLength += rc;
+    }
+    st_logInfo(" margin_b200 repeat counts: %" PRIi64 " nodes in %.3f s\n", nNodes - 1, omp_get_wtime() - tStart);
 }
 
 /* ----------------------------------------------------------------------------- impl/poa.c:668-716, batched */
@@ -913,6 +1149,7 @@ Poa *poa_realign(stList *bamChunkReads, stList *anchorAlignments, RleString *ref
     b200_batch_run(b, 1, &res);
     double tAligned = omp_get_wtime();
 
+    b200_indel_table_begin(1); /* the graph is fresh: every insert and delete from here on goes through the table */
     for (int64_t i = 0; i < n; i++) {
         BamChunkRead *chunkRead = stList_get(bamChunkReads, i);
         double t0 = omp_get_wtime();

@@ -169,7 +169,7 @@ struct margin_b200_ctx {
     PinBuf h_pipe_out[3], h_pipe_off;
     std::function<void()> after_h2d_enqueue;            // fired once the batch's host->device copies are queued
     int32_t *bins_ids_h = nullptr;
-    size_t bins_ids_off = 0;
+    size_t bins_ids_off = 0, arena_o_seams = 0, arena_o_flags = 0;
     int bins_n_ids = 0;
     std::vector<uint32_t> key_cnt;
     std::vector<mb::BandChunk> chunks;
@@ -1228,7 +1228,7 @@ void build_tiles(margin_b200_ctx *c, int L) {
                     t.tb_to = edges[k + 1];
                     t.D = (k == 0) ? sg.D : warmup_end_above(g, ng, t.tb_from, W, sg.D);
                     t.f0 = warmup_start_below(g, ng, t.tb_to, W);
-                    const int mw = range_maxw(c, j, t.f0, t.D + 1);
+                    const int mw = c->job_maxw[j] <= 8 ? c->job_maxw[j] : range_maxw(c, j, t.f0, t.D + 1);  // 8 = narrowest lane group
                     const bool wide = mw > gmax;
                     t.flags = ((t.D == sg.D && sg.at_end) ? mb::TILE_AT_END : 0) | (wide ? mb::TILE_WIDE : mb::TILE_BND);
                     t.priv_off = -1;
@@ -1247,25 +1247,6 @@ void build_tiles(margin_b200_ctx *c, int L) {
                 }
                 blocks.emplace_back(first, (int32_t) c->tiles.size());
             }
-            // seams of the job, walking its tiles from the lowest diagonals up: blocks hold later tracebacks first
-            if (tiled && c->guard_on) {
-                int32_t prev = -1;
-                bool prev_same_segment = false;
-                for (int bi = (int) blocks.size() - 1; bi >= 0; bi--) {
-                    for (int32_t u = blocks[bi].first; u < blocks[bi].second; u++) {
-                        if (prev >= 0) {
-                            const mb::Tile &lo = c->tiles[prev], &up = c->tiles[u];
-                            if (up.f0 > 0) c->seams.push_back(mb::Seam{prev, u, up.tb_to, 0});
-                            // inside a traceback the lower tile's backward sweep is warmed up through the upper tile's range
-                            if (prev_same_segment && lo.D > lo.tb_from + 1 && lo.D < c->segs[job.seg_base + ((int) blocks.size() - 1 - bi)].D)
-                                c->seams.push_back(mb::Seam{prev, u, lo.tb_from + 1, 1});
-                        }
-                        prev = u;
-                        prev_same_segment = true;
-                    }
-                    prev_same_segment = false;
-                }
-            }
         }
     }
     for (int j = nj - 1; j >= 0; j--)  // jobs without gaps point at their successor's first entry
@@ -1274,6 +1255,40 @@ void build_tiles(margin_b200_ctx *c, int L) {
     c->aln_first_slot[c->n_aln] = (int32_t) c->tiles.size();
     c->job_first_tile[nj] = (int32_t) c->tiles.size();
     c->total_slots = (int) c->tiles.size();
+}
+
+// Seams of the batch (guard_check_kernel): for every job, walking its tiles from the lowest diagonals up, the forward
+// seam with the tile below and, inside a traceback, the backward seam.  Built after the forward launches (finish_bins), so
+// that this piece of host work runs beside them.
+void build_seams(margin_b200_ctx *c) {
+    c->seams.clear();
+    if (!c->guard_on) return;
+    const int nj = (int) c->jobs.size();
+    std::vector<std::pair<int32_t, int32_t>> blocks;  // [first, last) tile of every segment of the job, later tracebacks first
+    for (int j = 0; j < nj; j++) {
+        const int32_t t0 = c->job_first_tile[j], t1 = c->job_first_tile[j + 1];
+        if (t1 <= t0 || !(c->tiles[t0].flags & (mb::TILE_BND | mb::TILE_WIDE))) continue;  // swept sequentially: exact
+        blocks.clear();
+        for (int32_t u = t0; u < t1; u++) {
+            if (u == t0 || c->tile_seg[u] != c->tile_seg[u - 1]) blocks.emplace_back(u, u + 1);
+            else blocks.back().second = u + 1;
+        }
+        int32_t prev = -1;
+        for (int bi = (int) blocks.size() - 1; bi >= 0; bi--) {
+            bool prev_same_segment = false;
+            for (int32_t u = blocks[bi].first; u < blocks[bi].second; u++) {
+                if (prev >= 0) {
+                    const mb::Tile &lo = c->tiles[prev], &up = c->tiles[u];
+                    if (up.f0 > 0) c->seams.push_back(mb::Seam{prev, u, up.tb_to, 0});
+                    // inside a traceback the lower tile's backward sweep is warmed up through the upper tile's range
+                    if (prev_same_segment && lo.D > lo.tb_from + 1 && lo.D < c->segs[c->tile_seg[prev]].D)
+                        c->seams.push_back(mb::Seam{prev, u, lo.tb_from + 1, 1});
+                }
+                prev = u;
+                prev_same_segment = true;
+            }
+        }
+    }
 }
 
 // Repair of failed seams: the tile whose warm-up had not converged (the upper tile of a forward seam, the lower tile of a
@@ -1372,7 +1387,7 @@ int build_bins(margin_b200_ctx *c, bool with_slots, Bins &bins, int force_group)
         if ((!with_slots || !job_is_tiled(c, j)) && !(!with_slots && j < (int) c->tiny_mask.size() && c->tiny_mask[j]))
             k0.push_back(key(bin_of(c->job_maxw[j]), c->jobs[j].lx + c->jobs[j].ly, j));
     int64_t ring_cells = 0, bnd_cells = 0;
-    const int n_seams = with_slots ? (int) c->seams.size() : 0;
+    const int n_seams = 2 * S;  // capacity: the seams themselves are built and sent by finish_bins()
     // arena layout (16-byte aligned sections): tiles | ring_off | bnd_off | aln_first_slot | seams | guard flags | ids
     const size_t o_tiles = 0, o_ring = o_tiles + (((size_t) S + 1) * sizeof(mb::Tile) + 15) / 16 * 16,
                  o_bnd = o_ring + ((size_t) S + 2) * 8, o_first = o_bnd + ((size_t) S + 2) * 8,
@@ -1409,8 +1424,6 @@ int build_bins(margin_b200_ctx *c, bool with_slots, Bins &bins, int force_group)
         bnd_off[S] = bnd_cells;
         if (S) memcpy(h + o_tiles, c->tiles.data(), (size_t) S * sizeof(mb::Tile));
         memcpy(h + o_first, c->aln_first_slot.data(), ((size_t) c->n_aln + 1) * 4);
-        if (n_seams) memcpy(h + o_seams, c->seams.data(), (size_t) n_seams * sizeof(mb::Seam));
-        memset(h + o_flags, 0, ((size_t) n_seams + 4) * 4);
     }
     int32_t *ids = reinterpret_cast<int32_t *>(h + o_ids);
     int n_ids = 0;
@@ -1431,8 +1444,10 @@ int build_bins(margin_b200_ctx *c, bool with_slots, Bins &bins, int force_group)
     c->bins_ids_h = ids;
     c->bins_ids_off = o_ids;
     c->bins_n_ids = n_ids;
-    if (ctl_copy(c->stream, c->d_arena.p, h, o_ids + (size_t) n_ids * 4)) return 1;
+    c->arena_o_seams = o_seams;
+    c->arena_o_flags = o_flags;
     char *dv = c->d_arena.as<char>();
+    if (ctl_copy(c->stream, dv, h, o_seams) || ctl_copy(c->stream, dv + o_ids, h + o_ids, (size_t) n_ids * 4)) return 1;
     c->p_tiles = reinterpret_cast<mb::Tile *>(dv + o_tiles);
     c->p_ring_off = reinterpret_cast<int64_t *>(dv + o_ring);
     c->p_bnd_off = reinterpret_cast<int64_t *>(dv + o_bnd);
@@ -1450,6 +1465,17 @@ int build_bins(margin_b200_ctx *c, bool with_slots, Bins &bins, int force_group)
 }
 
 int finish_bins(margin_b200_ctx *c, Bins &bins) {
+    // seams of this pass (a repair pass keeps the ones it is repairing) and their zeroed verdicts
+    if (c->tile_rerun.empty()) build_seams(c);
+    {
+        char *h = c->h_arena.as<char>();
+        const size_t n_seams = c->seams.size();
+        if (n_seams) memcpy(h + c->arena_o_seams, c->seams.data(), n_seams * sizeof(mb::Seam));
+        memset(h + c->arena_o_flags, 0, (n_seams + 4) * 4);
+        if (n_seams && ctl_copy(c->stream, c->d_arena.as<char>() + c->arena_o_seams, h + c->arena_o_seams, n_seams * sizeof(mb::Seam)))
+            return 1;
+        if (ctl_copy(c->stream, c->d_arena.as<char>() + c->arena_o_flags, h + c->arena_o_flags, (n_seams + 4) * 4)) return 1;
+    }
     std::vector<uint64_t> &k3 = c->keys[3];
     sort_keys(k3, c->key_tmp, c->key_cnt);
     int32_t *ids = c->bins_ids_h;
@@ -1646,6 +1672,7 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
     tr.mark("band+sync");
     c->job_force_seq.assign(nj, 0);
     const int L = pick_tile_len(c);  // fixed across guard re-runs: the tiles of unaffected jobs must not move
+    tr.mark("tile length");
     const int64_t cells = c->total_cells;
     const int64_t stride = cells + 1;  // tile kernels: staging addressed by band cell
     int64_t *bounds = nullptr;
@@ -1670,6 +1697,7 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
         launch_forward_tiles<16>(c, bins.tile_fwd[1], bins.tile_fwd[2] - bins.tile_fwd[1]);
         launch_forward_tiles<32>(c, bins.tile_fwd[2], bins.tile_fwd[3] - bins.tile_fwd[2]);
         if (finish_bins(c, bins)) return 1;
+        n_seams = (int) c->seams.size();
         if (want_indels) {
             launch_backward<8, true>(c, bins.gen_bwd[0], bins.gen_bwd[1] - bins.gen_bwd[0], stage_stride);
             launch_backward<16, true>(c, bins.gen_bwd[1], bins.gen_bwd[2] - bins.gen_bwd[1], stage_stride);
@@ -1777,7 +1805,6 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
         build_tiles(c, L);
         tr.mark("tiles");
         S = c->total_slots;
-        n_seams = (int) c->seams.size();
         any_generic = any_tiled = false;
         for (const mb::Tile &t : c->tiles) {
             if (t.flags & mb::TILE_BND) any_tiled = true;

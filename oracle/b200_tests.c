@@ -13,6 +13,8 @@
  *                                  tests/pairwiseAlignerTest.c:27-35 style) and the context stays usable.
  *   test_b200_bubble_batch_ab      poa_polish with the forward matrices deferred into one batch against the same
  *                                  matrices issued one by one (MARGIN_B200_BUBBLE_BATCH): identical consensus.
+ *   test_b200_repeat_counts_ab     the flat poa_estimateRepeatCountsUsingBayesianModel against the reference's
+ *                                  repeatSubMatrix_getMLRepeatCount, node by node.
  */
 #include "CuTest.h"
 #include "margin.h"
@@ -298,6 +300,44 @@ static void test_b200_bubble_batch_ab(CuTest *testCase) {
     params_destruct(params);
 }
 
+static void test_b200_repeat_counts_ab(CuTest *testCase) {
+    /* the binding's flat restatement of poa_estimateRepeatCountsUsingBayesianModel against the reference's own
+     * repeatSubMatrix_getMLRepeatCount (impl/repeatSubMatrix.c:124-151), node by node */
+    Params *params = params_readParams(b200ParamsFile);
+    PolishParams *polishParams = params->polishParams;
+    for (int64_t test = 0; test < 6; test++) {
+        char *truth = b200_random_sequence(400 + (int64_t) (b200_rng() % 1500));
+        char *draft = b200_mutate(truth, 1, 1);
+        RleString *reference = rleString_construct(draft);
+        int64_t readNumber = 5 + (int64_t) (b200_rng() % 20);
+        stList *reads = stList_construct3(0, (void (*)(void *)) bamChunkRead_destruct);
+        for (int64_t i = 0; i < readNumber; i++) {
+            stList_append(reads, bamChunkRead_construct2(stString_print("read_%d", (int) i), b200_mutate(truth, 4, 4), NULL,
+                                                         b200_rng() % 2, polishParams->useRunLengthEncoding));
+        }
+        Poa *poa = poa_realign(reads, NULL, reference, polishParams);
+        poa_estimateRepeatCountsUsingBayesianModel(poa, reads, polishParams->repeatSubMatrix);
+        uint64_t total = 0;
+        for (int64_t i = 1; i < stList_length(poa->nodes); i++) {
+            PoaNode *node = stList_get(poa->nodes, i);
+            double logProbability;
+            int64_t want = repeatSubMatrix_getMLRepeatCount(polishParams->repeatSubMatrix, poa->alphabet->convertCharToSymbol(node->base),
+                                                            node->observations, reads, &logProbability);
+            if (want == 0) want = 1;
+            CuAssertIntEquals(testCase, want, (int64_t) poa->refString->repeatCounts[i - 1]);
+            CuAssertIntEquals(testCase, want, (int64_t) node->repeatCount);
+            total += want;
+        }
+        CuAssertTrue(testCase, total == poa->refString->nonRleLength);
+        poa_destruct(poa);
+        stList_destruct(reads);
+        rleString_destruct(reference);
+        free(truth);
+        free(draft);
+    }
+    params_destruct(params);
+}
+
 CuSuite *b200BindingTestSuite(void) {
     CuSuite *suite = CuSuiteNew();
     SUITE_ADD_TEST(suite, test_b200_augment_example);
@@ -305,5 +345,6 @@ CuSuite *b200BindingTestSuite(void) {
     SUITE_ADD_TEST(suite, test_b200_realign_tiny_example);
     SUITE_ADD_TEST(suite, test_b200_exception_path);
     SUITE_ADD_TEST(suite, test_b200_bubble_batch_ab);
+    SUITE_ADD_TEST(suite, test_b200_repeat_counts_ab);
     return suite;
 }

@@ -42,7 +42,7 @@ def test_binding_suite_on_the_cpu_stand_in():
     deferred bubble-graph queue, stThrowNew) against oracle/stub_b200.c, a test-only stand-in for the CUDA library
     built on the oracle.  The same suite runs against the real library in test_binding_suite (GPU)."""
     n, _ = _run("cutest_stub", ["b200"], 900)
-    assert n == 5
+    assert n == 6
 
 
 @pytest.mark.gpu
@@ -60,4 +60,4 @@ def test_reference_polisher_and_stitching_suites_on_the_binding():
 @pytest.mark.gpu
 def test_binding_suite():
     n, _ = _run("cutest_b200", ["b200"], 900)
-    assert n == 5
+    assert n == 6
