@@ -158,7 +158,7 @@ def bind_rank_to_cores(local, world):
     except AttributeError:
         return None
     ALL_CORES = avail
-    if world <= 1 or len(avail) < 2 * world:
+    if world <= 1 or len(avail) < 2 * world or os.environ.get("MARGIN_B200_BENCH_NO_BIND"):
         return avail
     per = len(avail) // world
     mine = avail[local * per:(local + 1) * per]
@@ -380,7 +380,7 @@ def time_sustained(pm, batches, cells, device, precision, contexts=3, min_second
     als = [PairHmmAligner(pm.models, pm.p, device=device) for _ in range(contexts)]
     for al in als:
         al.set_precision(precision)
-        al.set_pair_format(abi.PAIRS_PACKED64)
+        al.set_pair_format(abi.PAIRS_DELTA32)
     warm = threading.Barrier(contexts)
 
     def warm_up(al):  # every context sees every chunk once (arenas reach their steady size)
@@ -469,7 +469,7 @@ def main_ours(args):
     al.set_precision(precision)
     al.bench_workload = args.workload
     if not args.plain_formats:
-        al.set_pair_format(abi.PAIRS_PACKED64)
+        al.set_pair_format(abi.PAIRS_DELTA32)
     flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
 
     def l2_flush():
@@ -532,7 +532,7 @@ def main_ours(args):
         b = i % len(batches)
         res = al.posteriors_host(batches[b], True)
         e2e_cells += chunk_cells[b]
-        d2h += int(res["tuples"]) * int(res["tuple_bytes"]) + 3 * (batches[b].n + 1) * 8
+        d2h += int(res["tuples"]) * int(res["tuple_bytes"]) + int(res["escapes"]) * 8 + 6 * (batches[b].n + 1) * 8
         h2d += batches[b].h2d_bytes
     e2e_s = (time.perf_counter() - t0) / e2e_steps
     e2e_s = reduce_scalar(dist, e2e_s, "MAX", dev)
@@ -560,7 +560,7 @@ def main_ours(args):
                    "reads_per_chunk": [b.n for b in batches], "band_cells_per_chunk": [int(c) for c in chunk_cells],
                    "sharding": "one contig of %d chunks, scheduler.shard_chunks (size-descending LPT), no collective" % n_chunks,
                    "params": "ont/r9.4 r94-g360 (RLE, repeat counts)", "l2": "flushed between steps (512 MiB write)",
-                   "boundary_formats": "plain" if args.plain_formats else "anchor steps 4 B, tuples 8 B",
+                   "boundary_formats": "plain" if args.plain_formats else "anchor steps 4 B, tuples 4 B step records + escapes",
                    "tiles_per_step": stats_sum.get("tiles", 0) / args.steps,
                    "wide_cell_share": stats_sum.get("wide_cells", 0) / max(cells_done, 1),
                    "sequential_cell_share": stats_sum.get("sequential_cells", 0) / max(cells_done, 1),
@@ -583,7 +583,7 @@ def main_ours(args):
     if precision == abi.F64 and not args.no_fast_mode:
         fast = PairHmmAligner(pm.models, pm.p, device=local)
         fast.set_precision(abi.F32)
-        fast.set_pair_format(abi.PAIRS_PACKED64)
+        fast.set_pair_format(abi.PAIRS_DELTA32)
         fast.set_kernel_timing(True)
         for i in range(len(batches)):
             fast.upload(batches[i])
@@ -729,7 +729,7 @@ def main_replay(args):
             items, models, params, want = replay.load_dump(path)
             batch = abi.Batch(items, compact=True)
             al = PairHmmAligner(models, params, device=0)
-            al.set_pair_format(abi.PAIRS_PACKED64)
+            al.set_pair_format(abi.PAIRS_DELTA32)
             al.upload(batch)
             for _ in range(args.warmup):
                 st = al.posteriors_resident(bool(want))

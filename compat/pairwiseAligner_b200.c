@@ -106,8 +106,9 @@ static margin_b200_ctx *b200_ctx(void) {
         int n = margin_b200_device_count();
         if (n <= 0) st_errAbort("margin_b200: no CUDA device; this build of margin has no CPU aligner\n");
         if (margin_b200_create(&tls.ctx, omp_get_thread_num() % n) != 0) b200_fail();
-        /* 8-byte tuples over PCIe; b200_list() unpacks them while it builds the stIntTuples */
-        if (margin_b200_set_pair_format(tls.ctx, MARGIN_B200_PAIRS_PACKED64) != 0) b200_fail();
+        /* 4-byte step records over PCIe (half of the 8-byte words, a third of the triples: the device->host link is what
+         * bounds a box of eight GPUs); b200_list() / b200_pairs() decode them while they walk the lists anyway */
+        if (margin_b200_set_pair_format(tls.ctx, MARGIN_B200_PAIRS_DELTA32) != 0) b200_fail();
     }
     return tls.ctx;
 }
@@ -452,6 +453,14 @@ static void b200_batch_run(B200Batch *b, int wantIndels, margin_b200_result *res
 /* List l of alignment i as an stList of stIntTuple(weight, x + shiftX, y), the reference's own representation. */
 static stList *b200_list(const margin_b200_result *res, int l, int64_t i, int64_t shiftX) {
     stList *out = stList_construct3(0, (void (*)(void *)) stIntTuple_destruct);
+    if (res->pair_format == MARGIN_B200_PAIRS_DELTA32) {
+        margin_b200_delta_cursor cur = {(const uint32_t *) res->pairs[l] + res->off[l][i], res->escapes[l] + res->escape_off[l][i], 0, 0};
+        for (int64_t k = res->off[l][i]; k < res->off[l][i + 1]; k++) {
+            margin_b200_pair q = margin_b200_delta_next(&cur);
+            stList_append(out, stIntTuple_construct3(q.w, (int64_t) q.x + shiftX, q.y));
+        }
+        return out;
+    }
     if (res->pair_format == MARGIN_B200_PAIRS_PACKED64) {
         const uint64_t *v = (const uint64_t *) res->pairs[l];
         for (int64_t k = res->off[l][i]; k < res->off[l][i + 1]; k++) {
@@ -557,7 +566,15 @@ static int64_t b200_pairs(const margin_b200_result *res, int l, int64_t i, int64
         sc->pairs[l] = st_realloc(sc->pairs[l], sc->cap[l] * sizeof(B200Pair));
     }
     B200Pair *out = sc->pairs[l];
-    if (res->pair_format == MARGIN_B200_PAIRS_PACKED64) {
+    if (res->pair_format == MARGIN_B200_PAIRS_DELTA32) {
+        margin_b200_delta_cursor cur = {(const uint32_t *) res->pairs[l] + first, res->escapes[l] + res->escape_off[l][i], 0, 0};
+        for (int64_t k = 0; k < n; k++) {
+            margin_b200_pair q = margin_b200_delta_next(&cur);
+            out[k].x = (int64_t) q.x + shiftX;
+            out[k].y = q.y;
+            out[k].w = q.w;
+        }
+    } else if (res->pair_format == MARGIN_B200_PAIRS_PACKED64) {
         const uint64_t *v = (const uint64_t *) res->pairs[l] + first;
         for (int64_t k = 0; k < n; k++) {
             margin_b200_pair q = margin_b200_unpack_pair(v[k]);

@@ -121,7 +121,41 @@ typedef struct margin_b200_pair {
  *   bits 0-23 weight, bits 24-43 x + 1, bits 44-63 y + 1,
  * which moves 8 instead of 12 bytes per tuple to the host; it needs every sequence of the batch to be shorter than
  * 2^20 - 1 symbols, otherwise the call falls back to TRIPLES and says so in margin_b200_result.pair_format. */
-enum { MARGIN_B200_PAIRS_TRIPLES = 0, MARGIN_B200_PAIRS_PACKED64 = 1 };
+enum { MARGIN_B200_PAIRS_TRIPLES = 0, MARGIN_B200_PAIRS_PACKED64 = 1, MARGIN_B200_PAIRS_DELTA32 = 2 };
+
+/* DELTA32: one 32-bit record per tuple — bits 0-23 weight, bits 24-31 the step from the previous tuple of the same list
+ * of the same alignment: (anti-diagonal step 0..15) << 4 | (x step + 8), i.e. x += (code & 15) - 8 and
+ * y += (code >> 4) - ((code & 15) - 8); code 0xFF takes (x, y) from the list's escape array (margin_b200_result.escapes,
+ * consumed in order) instead.  The first tuple of a list is always an escape.  Half the bytes of PACKED64 over the host
+ * link; no limit on sequence lengths.  The inline decoder below walks a list with a cursor. */
+typedef struct margin_b200_xy {
+    int32_t x, y;
+} margin_b200_xy;
+
+typedef struct margin_b200_delta_cursor {
+    const uint32_t *rec;       /* next record */
+    const margin_b200_xy *esc; /* next escape */
+    int32_t x, y;              /* coordinates of the previous tuple */
+} margin_b200_delta_cursor;
+
+static inline margin_b200_pair margin_b200_delta_next(margin_b200_delta_cursor *c) {
+    const uint32_t r = *c->rec++;
+    const uint32_t code = r >> 24;
+    margin_b200_pair p;
+    if (code == 0xFFu) {
+        c->x = c->esc->x;
+        c->y = c->esc->y;
+        c->esc++;
+    } else {
+        const int32_t dx = (int32_t) (code & 15u) - 8;
+        c->x += dx;
+        c->y += (int32_t) (code >> 4) - dx;
+    }
+    p.w = (int32_t) (r & 0xffffffu);
+    p.x = c->x;
+    p.y = c->y;
+    return p;
+}
 
 static inline margin_b200_pair margin_b200_unpack_pair(uint64_t v) {
     margin_b200_pair p;
@@ -159,6 +193,10 @@ typedef struct margin_b200_result {
      * by more than the tolerance (their jobs were re-run sequentially inside the call, so results are unaffected) */
     int32_t guard_seams;
     int32_t guard_failures;
+    /* MARGIN_B200_PAIRS_DELTA32 only (NULL otherwise): list l of alignment i consumes escapes[l] from
+     * escape_off[l][i] on; pairs[l] then points at uint32_t records */
+    const margin_b200_xy *escapes[3];
+    const int64_t *escape_off[3];
 } margin_b200_result;
 
 typedef struct margin_b200_ctx margin_b200_ctx;

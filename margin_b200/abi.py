@@ -76,7 +76,7 @@ class BatchStruct(C.Structure):
 
 
 PAIR_DTYPE = np.dtype([("w", "<i4"), ("x", "<i4"), ("y", "<i4")])
-PAIRS_TRIPLES, PAIRS_PACKED64 = 0, 1  # MARGIN_B200_PAIRS_*
+PAIRS_TRIPLES, PAIRS_PACKED64, PAIRS_DELTA32 = 0, 1, 2  # MARGIN_B200_PAIRS_*
 F64, F32 = 0, 1  # MARGIN_B200_F64 / MARGIN_B200_F32 (margin_b200_set_precision)
 
 
@@ -87,6 +87,32 @@ def unpack_pairs(words):
     out["w"] = (words & np.uint64(0xffffff)).astype(np.int32)
     out["x"] = ((words >> np.uint64(24)) & np.uint64(0xfffff)).astype(np.int32) - 1
     out["y"] = (words >> np.uint64(44)).astype(np.int32) - 1
+    return out
+
+
+def unpack_delta32(records, escapes, off, esc_off):
+    """MARGIN_B200_PAIRS_DELTA32 records of ONE list of a whole batch -> (w, x, y) records (margin_b200_delta_next,
+    vectorised): `off` / `esc_off` are the per-alignment offsets into `records` / `escapes`.  Every alignment's first
+    tuple is an escape, so one running sum over the batch decodes all alignments at once."""
+    rec = np.asarray(records, dtype=np.uint32)
+    out = np.empty(len(rec), dtype=PAIR_DTYPE)
+    out["w"] = (rec & np.uint32(0xffffff)).astype(np.int32)
+    if len(rec) == 0:
+        return out
+    code = (rec >> np.uint32(24)).astype(np.int64)
+    is_esc = code == 0xFF
+    dx = np.where(is_esc, 0, (code & 15) - 8)
+    dy = np.where(is_esc, 0, (code >> 4) - ((code & 15) - 8))
+    esc = np.asarray(escapes, dtype=np.int32).reshape(-1, 2).astype(np.int64)
+    k = np.cumsum(is_esc) - 1  # index of the governing escape
+    assert is_esc[0] and int(is_esc.sum()) == len(esc), "escape stream does not match the records"
+    # offsets of the escapes are consistent with the alignments' first tuples
+    first = np.asarray(off[:-1])[np.diff(np.asarray(off)) > 0]
+    assert is_esc[first].all() and np.array_equal(k[first], np.asarray(esc_off[:-1])[np.diff(np.asarray(off)) > 0])
+    cx, cy = np.cumsum(dx), np.cumsum(dy)
+    at = np.flatnonzero(is_esc)
+    out["x"] = (esc[k, 0] + cx - cx[at][k]).astype(np.int32)
+    out["y"] = (esc[k, 1] + cy - cy[at][k]).astype(np.int32)
     return out
 
 
@@ -126,6 +152,8 @@ class ResultStruct(C.Structure):
         ("sequential_cells", C.c_int64),
         ("guard_seams", C.c_int32),
         ("guard_failures", C.c_int32),
+        ("escapes", C.c_void_p * 3),
+        ("escape_off", C.c_void_p * 3),
     ]
 
 

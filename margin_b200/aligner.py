@@ -82,7 +82,8 @@ class PairHmmAligner:
         self._check(self.lib.margin_b200_set_kernel_timing(self._h, int(bool(on))))
 
     def set_pair_format(self, fmt):
-        """abi.PAIRS_TRIPLES (12-byte records) or abi.PAIRS_PACKED64 (8-byte words, include/margin_b200.h)."""
+        """abi.PAIRS_TRIPLES (12-byte records), abi.PAIRS_PACKED64 (8-byte words) or abi.PAIRS_DELTA32 (4-byte step
+        records + escapes; include/margin_b200.h)."""
         self._check(self.lib.margin_b200_set_pair_format(self._h, int(fmt)))
 
     # ------------------------------------------------------------- batched calls
@@ -93,7 +94,14 @@ class PairHmmAligner:
             for l in range(3):
                 off = np.ctypeslib.as_array(C.cast(res.off[l], C.POINTER(C.c_int64)), shape=(n + 1,)).copy()
                 tot = int(off[n])
-                if tot and res.pair_format == abi.PAIRS_PACKED64:
+                if tot and res.pair_format == abi.PAIRS_DELTA32:
+                    rec = np.frombuffer((C.c_char * (tot * 4)).from_address(res.pairs[l]), dtype=np.uint32)
+                    eoff = np.ctypeslib.as_array(C.cast(res.escape_off[l], C.POINTER(C.c_int64)), shape=(n + 1,)).copy()
+                    ne = int(eoff[n])
+                    esc = (np.frombuffer((C.c_char * (ne * 8)).from_address(res.escapes[l]), dtype=np.int32) if ne
+                           else np.zeros(0, np.int32))
+                    arrs.append(abi.unpack_delta32(rec, esc, off, eoff))
+                elif tot and res.pair_format == abi.PAIRS_PACKED64:
                     buf = (C.c_char * (tot * 8)).from_address(res.pairs[l])
                     arrs.append(abi.unpack_pairs(np.frombuffer(buf, dtype=np.uint64)))
                 elif tot:
@@ -121,7 +129,9 @@ class PairHmmAligner:
         out = _stats(res)
         n = batch.n
         out["tuples"] = sum(int(C.cast(res.off[l], C.POINTER(C.c_int64))[n]) for l in range(3)) if n else 0
-        out["tuple_bytes"] = 8 if res.pair_format == abi.PAIRS_PACKED64 else 12
+        out["tuple_bytes"] = {abi.PAIRS_PACKED64: 8, abi.PAIRS_DELTA32: 4}.get(res.pair_format, 12)
+        out["escapes"] = (sum(int(C.cast(res.escape_off[l], C.POINTER(C.c_int64))[n]) for l in range(3))
+                          if n and res.pair_format == abi.PAIRS_DELTA32 else 0)
         return out
 
     def set_precision(self, precision):

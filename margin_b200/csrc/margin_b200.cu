@@ -164,6 +164,10 @@ struct margin_b200_ctx {
     bool kernel_timing = false;                         // margin_b200_set_kernel_timing / MARGIN_B200_KERNEL_TIMING
     int pair_format = MARGIN_B200_PAIRS_TRIPLES;        // what the caller asked for
     bool packed_now = false;                            // ... and what this batch gets (sequence lengths permitting)
+    int fmt_now = MARGIN_B200_PAIRS_TRIPLES;            // MARGIN_B200_PAIRS_* of this batch
+    DevBuf d_esc_counts, d_esc_off, d_esc, d_esc_off_out;  // DELTA32: escapes per [list][slot], their scan, the escapes, per-alignment offsets
+    PinBuf h_esc, h_esc_off;
+    int64_t esc_total = 0, esc_list[3] = {0, 0, 0};
     DevBuf d_anchors_delta;
     int last_k = 0;
     PinBuf h_pipe_out[3], h_pipe_off;
@@ -443,7 +447,7 @@ void margin_b200_destroy(margin_b200_ctx *c) {
     DevBuf *bufs[] = {&c->d_models, &c->d_rsm[0], &c->d_rsm[1], &c->d_symx, &c->d_symy, &c->d_anchors, &c->d_jobs,
                       &c->d_kl, &c->d_kr, &c->d_cell_off, &c->d_job_cells, &c->d_job_maxw, &c->d_job_nseg, &c->d_err,
                       &c->d_segs, &c->d_seg_counts, &c->d_seg_off, &c->d_scan_tmp, &c->d_slot_ring_off, &c->d_ring,
-                      &c->d_ids, &c->d_aln_first_slot, &c->d_F, &c->d_Fpriv, &c->d_guard_worst, &c->d_class_cells, &c->d_F32, &c->d_shiftF, &c->d_bnd32, &c->d_emit_f[0], &c->d_emit_f[1],
+                      &c->d_ids, &c->d_aln_first_slot, &c->d_F, &c->d_Fpriv, &c->d_guard_worst, &c->d_class_cells, &c->d_esc_counts, &c->d_esc_off, &c->d_esc, &c->d_esc_off_out, &c->d_F32, &c->d_shiftF, &c->d_bnd32, &c->d_emit_f[0], &c->d_emit_f[1],
                       &c->d_emit_f_ptrs, &c->d_stage, &c->d_out, &c->d_off_out, &c->d_fwd_out,
                       &c->d_geo, &c->d_tiles, &c->d_bnd, &c->d_slot_bnd_off, &c->d_emit5[0], &c->d_emit5[1],
                       &c->d_px, &c->d_py, &c->d_stage2, &c->d_chunks, &c->d_job_first_chunk, &c->d_chunk_sum, &c->d_chunk_maxw,
@@ -457,6 +461,8 @@ void margin_b200_destroy(margin_b200_ctx *c) {
     c->h_off.release();
     for (PinBuf &b : c->h_pipe_out) b.release();
     c->h_tiny_ids.release();
+    c->h_esc.release();
+    c->h_esc_off.release();
     c->h_pipe_off.release();
     for (cudaEvent_t e : c->ev_pool) cudaEventDestroy(e);
     cudaEventDestroy(c->ev0);
@@ -606,7 +612,7 @@ int margin_b200_set_kernel_timing(margin_b200_ctx *c, int on) {
 
 int margin_b200_set_pair_format(margin_b200_ctx *c, int format) {
     if (!c) return fail("margin_b200_set_pair_format: null context");
-    if (format != MARGIN_B200_PAIRS_TRIPLES && format != MARGIN_B200_PAIRS_PACKED64)
+    if (format != MARGIN_B200_PAIRS_TRIPLES && format != MARGIN_B200_PAIRS_PACKED64 && format != MARGIN_B200_PAIRS_DELTA32)
         return fail("margin_b200_set_pair_format: unknown format %d", format);
     c->pair_format = format;
     for (margin_b200_ctx *sub : c->subs) sub->pair_format = format;
@@ -702,6 +708,8 @@ extern "C" int margin_b200_upload_batch(margin_b200_ctx *c, const margin_b200_ba
         return fail("the two state machines of a batch must both use (or both not use) repeat counts");
     const int rle = c->host_models[used[0] ? 0 : 1].rle;
     c->packed_now = c->pair_format == MARGIN_B200_PAIRS_PACKED64 && fits_packed;
+    c->fmt_now = c->pair_format == MARGIN_B200_PAIRS_DELTA32 ? MARGIN_B200_PAIRS_DELTA32
+                                                             : (c->packed_now ? MARGIN_B200_PAIRS_PACKED64 : MARGIN_B200_PAIRS_TRIPLES);
     c->have_switch = false;
     for (int k = 0; k < 2; k++)
         if (used[k] && (c->host_models[k].t[mb::T_YX] != -INFINITY || c->host_models[k].t[mb::T_XY] != -INFINITY))
@@ -1728,7 +1736,20 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
         }
         return 0;
     };
+    const bool delta = c->fmt_now == MARGIN_B200_PAIRS_DELTA32;
     auto run_gather = [&]() {
+        if (delta) {
+            if (S > 0 && nj > 0) {
+                KTimer kt_(c, K_GATHER);
+                mb::delta32_gather_kernel<<<S, 128, 0, c->stream>>>(
+                    c->d_jobs.as<mb::Job>(), c->p_tiles, S, c->d_geo.as<int2>(), c->d_seg_counts.as<int64_t>(),
+                    c->d_seg_off.as<int64_t>(), c->d_esc_off.as<int64_t>(), c->d_stage2.as<mb::StagedPair>(), stride,
+                    c->d_stage.as<mb::Pair>(), stage_stride, c->d_out.as<uint32_t>(), c->d_esc.as<mb::TupleXY>(), n_lists,
+                    (int64_t) (c->d_out.cap / sizeof(uint32_t)), (int64_t) (c->d_esc.cap / sizeof(mb::TupleXY)));
+                c->launches++;
+            }
+            return;
+        }
         const int64_t cap = (int64_t) (c->d_out.cap / sizeof(mb::Pair));
         if (S > 0 && nj > 0 && any_generic) {
             KTimer kt_(c, K_GATHER);
@@ -1780,7 +1801,31 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
         }
         const size_t want_cap = (size_t) cells / (want_indels ? 3 : 6) + 4096;
         if (c->d_out.cap / sizeof(mb::Pair) < want_cap && c->d_out.ensure(want_cap * sizeof(mb::Pair))) return 1;
+        bounds[8] = bounds[9] = bounds[10] = bounds[11] = 0;
+        if (delta && S > 0) {
+            // escapes per [list][slot], their scan (same length as the tuple scan: its temporary storage fits), totals
+            if (c->d_esc_counts.ensure(((size_t) 3 * S + 1) * sizeof(int64_t)) || c->d_esc_off.ensure(((size_t) 3 * S + 1) * sizeof(int64_t)) ||
+                c->d_esc_off_out.ensure((size_t) 3 * (c->n_aln + 1) * sizeof(int64_t)) ||
+                c->d_esc.ensure(((size_t) cells / 32 + (size_t) 3 * S + 4096) * sizeof(mb::TupleXY)))
+                return 1;
+            CU(cudaMemsetAsync(c->d_esc_counts.p, 0, ((size_t) 3 * S + 1) * sizeof(int64_t), c->stream));
+            KTimer kt_(c, K_GATHER);
+            mb::delta32_count_kernel<<<S, 128, 0, c->stream>>>(c->d_jobs.as<mb::Job>(), c->p_tiles, S, c->d_geo.as<int2>(),
+                                                               c->d_seg_counts.as<int64_t>(), c->d_stage2.as<mb::StagedPair>(), stride,
+                                                               c->d_stage.as<mb::Pair>(), stage_stride, n_lists,
+                                                               c->d_esc_counts.as<int64_t>());
+            CU(cub::DeviceScan::ExclusiveSum(c->d_scan_tmp.p, tmp_bytes, c->d_esc_counts.as<int64_t>(), c->d_esc_off.as<int64_t>(),
+                                             n_scan, c->stream));
+            ctl_bounds_kernel<<<1, 32, 0, c->stream>>>(c->d_esc_off.as<int64_t>(), S, bounds + 8);
+            c->launches += 3;
+        }
         run_gather();
+        if (delta && S > 0) {
+            const int threads = 128;
+            mb::list_offsets_kernel<<<(int) ((c->n_aln + 1 + threads - 1) / threads), threads, 0, c->stream>>>(
+                c->p_aln_first_slot, (int) c->n_aln, S, c->d_esc_off.as<int64_t>(), c->d_esc_off_out.as<int64_t>());
+            c->launches++;
+        }
         {
             const int threads = 128;
             const int blocks = (int) ((c->n_aln + 1 + threads - 1) / threads);
@@ -1864,7 +1909,11 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
     }
     c->total_tuples = bounds[3];
     for (int l = 0; l < 3; l++) c->list_tuples[l] = bounds[l + 1] - bounds[l];
-    if ((size_t) c->total_tuples > c->d_out.cap / sizeof(mb::Pair)) {  // estimate too small: exact size, gather again
+    c->esc_total = delta ? bounds[11] : 0;
+    for (int l = 0; l < 3; l++) c->esc_list[l] = delta ? bounds[9 + l] - bounds[8 + l] : 0;
+    if ((size_t) c->total_tuples > c->d_out.cap / sizeof(mb::Pair) ||
+        (delta && (size_t) c->esc_total > c->d_esc.cap / sizeof(mb::TupleXY))) {  // estimate too small: exact size, gather again
+        if (delta && c->d_esc.ensure((size_t) (c->esc_total + 1) * sizeof(mb::TupleXY))) return 1;
         if (c->d_out.ensure((size_t) (c->total_tuples + 1) * sizeof(mb::Pair))) return 1;
         run_gather();
         CU(cudaEventRecord(c->ev1, c->stream));
@@ -1891,7 +1940,15 @@ extern "C" int margin_b200_download_result(margin_b200_ctx *c, margin_b200_resul
     if (c->h_out.ensure((size_t) (c->total_tuples + 1) * sizeof(mb::Pair)) ||
         c->h_off.ensure((size_t) 3 * (n + 1) * sizeof(int64_t)))
         return 1;
-    const size_t tuple_bytes = c->packed_now ? sizeof(uint64_t) : sizeof(mb::Pair);
+    const bool delta = c->fmt_now == MARGIN_B200_PAIRS_DELTA32;
+    const size_t tuple_bytes = delta ? sizeof(uint32_t) : (c->packed_now ? sizeof(uint64_t) : sizeof(mb::Pair));
+    if (delta) {
+        if (c->h_esc.ensure((size_t) (c->esc_total + 1) * sizeof(mb::TupleXY)) || c->h_esc_off.ensure((size_t) 3 * (n + 1) * sizeof(int64_t)))
+            return 1;
+        if (c->esc_total)
+            CU(cudaMemcpyAsync(c->h_esc.p, c->d_esc.p, (size_t) c->esc_total * sizeof(mb::TupleXY), cudaMemcpyDeviceToHost, c->stream));
+        if (ctl_copy(c->stream, c->h_esc_off.p, c->d_esc_off_out.p, (size_t) 3 * (n + 1) * sizeof(int64_t))) return 1;
+    }
     if (c->total_tuples)
         CU(cudaMemcpyAsync(c->h_out.p, c->d_out.p, (size_t) c->total_tuples * tuple_bytes, cudaMemcpyDeviceToHost, c->stream));
     if (ctl_copy(c->stream, c->h_off.p, c->d_off_out.p, (size_t) 3 * (n + 1) * sizeof(int64_t))) return 1;
@@ -1903,7 +1960,13 @@ extern "C" int margin_b200_download_result(margin_b200_ctx *c, margin_b200_resul
         out->off[l] = c->h_off.as<int64_t>() + (size_t) l * (n + 1);
         acc += c->list_tuples[l];
     }
-    out->pair_format = c->packed_now ? MARGIN_B200_PAIRS_PACKED64 : MARGIN_B200_PAIRS_TRIPLES;
+    int64_t esc_acc = 0;
+    for (int l = 0; l < 3; l++) {
+        out->escapes[l] = delta ? c->h_esc.as<margin_b200_xy>() + esc_acc : nullptr;
+        out->escape_off[l] = delta ? c->h_esc_off.as<int64_t>() + (size_t) l * (n + 1) : nullptr;
+        esc_acc += c->esc_list[l];
+    }
+    out->pair_format = c->fmt_now;
     return 0;
 }
 
@@ -2156,7 +2219,8 @@ extern "C" int margin_b200_posteriors_batch(margin_b200_ctx *c, const margin_b20
         return margin_b200_download_result(c, out);
     }
     const int dev_slot = c->device & (kMaxDevices - 1);
-    if ((g_live_contexts[dev_slot].load() == 1 || c->pipeline_force) && c->pipeline_k > 1 && b->n >= 2 && c->have_params) {
+    if ((g_live_contexts[dev_slot].load() == 1 || c->pipeline_force) && c->pipeline_k > 1 && b->n >= 2 && c->have_params &&
+        c->pair_format != MARGIN_B200_PAIRS_DELTA32) {  // the in-call pipeline assembles TRIPLES / PACKED64 lists only
         const int64_t bytes = 12 * b->off_a[b->n] + 2 * (b->off_x[b->n] + b->off_y[b->n]);
         const int K = (int) std::min<int64_t>(c->pipeline_k, b->n / 2);
         if (K > 1 && bytes >= c->pipeline_min_bytes) return posteriors_pipelined(c, b, want_indels, out, K);

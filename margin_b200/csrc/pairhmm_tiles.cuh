@@ -764,6 +764,145 @@ __global__ void gather_staged_kernel(const Job *__restrict__ jobs, const Tile *_
     }
 }
 
+// --------------------------------------------------------------------------------- compact tuples (DELTA32)
+//
+// MARGIN_B200_PAIRS_DELTA32 (include/margin_b200.h): one 32-bit record per tuple, weight in the low 24 bits and in the high
+// 8 bits the step from the previous tuple of the same list — (anti-diagonal step 0..15) << 4 | (x step + 8) — or 0xFF,
+// which takes the tuple's coordinates from the list's escape array instead.  In list order consecutive tuples sit on the
+// same or the next few anti-diagonals, so almost every match tuple and most gap tuples fit a step; the first tuple of
+// every tile (lists are assembled tile by tile) is always an escape.  Half the bytes of PACKED64 over the host link,
+// which is what bounds the end-to-end rate when eight GPUs share one host (measured 15 GB/s per GPU device->host).
+struct TupleXY {
+    int32_t x, y;
+};
+
+__device__ __forceinline__ bool delta32_code(int px, int py, int x, int y, unsigned &code) {
+    const int dd = (x + y) - (px + py), dx = x - px;
+    code = ((unsigned) dd << 4) | (unsigned) (dx + 8);
+    return (unsigned) dd <= 15u && (unsigned) (dx + 8) <= 15u && code != 0xFFu;
+}
+
+// Coordinates of entry i (final order) of a tile's list: tiles of the lane-group kernels stage StagedPair records, the
+// general kernels Pair records; both in emission order, i.e. reversed.
+struct DeltaSrc {
+    const StagedPair *sp;
+    const Pair *pr;
+    int64_t c;
+    __device__ __forceinline__ void xy(int64_t i, int &x, int &y) const {
+        if (sp) {
+            x = sp[c - 1 - i].x;
+            y = sp[c - 1 - i].y;
+        } else {
+            x = pr[c - 1 - i].x;
+            y = pr[c - 1 - i].y;
+        }
+    }
+    __device__ __forceinline__ int32_t weight(int64_t i) const {
+        if (!sp) return pr[c - 1 - i].w;
+        double p = exp(sp[c - 1 - i].v);
+        if (p > 1.0) p = 1.0;
+        return (int32_t) floor(dmul(p, 10000000.0));
+    }
+};
+
+__device__ __forceinline__ DeltaSrc delta_src(const Job *jobs, const Tile &t, int slot, int l, int total_slots,
+                                              const int2 *geo, const int64_t *seg_counts, const StagedPair *stage2,
+                                              int64_t stride2, const Pair *stage1, int64_t stride1) {
+    DeltaSrc s;
+    s.c = seg_counts[(int64_t) l * total_slots + slot];
+    if (t.flags & TILE_BND) {
+        const Job job = jobs[t.job];
+        s.sp = stage2 + (int64_t) l * stride2 + job.cell_base + (uint32_t) geo[job.diag_off + t.tb_to + 1].y;
+        s.pr = nullptr;
+    } else {
+        s.sp = nullptr;
+        s.pr = stage1 + (int64_t) l * stride1 + t.stage_off;
+    }
+    return s;
+}
+
+// escapes per [list][slot]: one CTA per tile
+__global__ void delta32_count_kernel(const Job *__restrict__ jobs, const Tile *__restrict__ tiles, int total_slots,
+                                     const int2 *__restrict__ geo, const int64_t *__restrict__ seg_counts,
+                                     const StagedPair *__restrict__ stage2, int64_t stride2, const Pair *__restrict__ stage1,
+                                     int64_t stride1, int n_lists, int64_t *__restrict__ esc_counts) {
+    const int slot = blockIdx.x;
+    const Tile t = tiles[slot];
+    __shared__ int total;
+    for (int l = 0; l < n_lists; l++) {
+        const DeltaSrc src = delta_src(jobs, t, slot, l, total_slots, geo, seg_counts, stage2, stride2, stage1, stride1);
+        if (threadIdx.x == 0) total = 0;
+        __syncthreads();
+        int mine = 0;
+        for (int64_t i = threadIdx.x; i < src.c; i += blockDim.x) {
+            bool esc = i == 0;
+            if (!esc) {
+                int px, py, x, y;
+                unsigned code;
+                src.xy(i - 1, px, py);
+                src.xy(i, x, y);
+                esc = !delta32_code(px, py, x, y, code);
+            }
+            mine += esc ? 1 : 0;
+        }
+        for (int o = 16; o > 0; o >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, o);
+        if ((threadIdx.x & 31) == 0 && mine) atomicAdd(&total, mine);
+        __syncthreads();
+        if (threadIdx.x == 0) esc_counts[(int64_t) l * total_slots + slot] = total;
+        __syncthreads();
+    }
+}
+
+// records and escapes of every tile at their final places; blockDim.x must be 128
+__global__ void delta32_gather_kernel(const Job *__restrict__ jobs, const Tile *__restrict__ tiles, int total_slots,
+                                      const int2 *__restrict__ geo, const int64_t *__restrict__ seg_counts,
+                                      const int64_t *__restrict__ seg_off, const int64_t *__restrict__ esc_off,
+                                      const StagedPair *__restrict__ stage2, int64_t stride2,
+                                      const Pair *__restrict__ stage1, int64_t stride1, uint32_t *__restrict__ out,
+                                      TupleXY *__restrict__ esc_out, int n_lists, int64_t out_capacity,
+                                      int64_t esc_capacity) {
+    const int slot = blockIdx.x;
+    if (seg_off[(int64_t) 3 * total_slots] > out_capacity || esc_off[(int64_t) 3 * total_slots] > esc_capacity) return;
+    const Tile t = tiles[slot];
+    __shared__ int warp_tot[4];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    for (int l = 0; l < n_lists; l++) {
+        const DeltaSrc src = delta_src(jobs, t, slot, l, total_slots, geo, seg_counts, stage2, stride2, stage1, stride1);
+        const int64_t o = seg_off[(int64_t) l * total_slots + slot];
+        int64_t eo = esc_off[(int64_t) l * total_slots + slot];
+        for (int64_t base = 0; base < src.c; base += blockDim.x) {
+            const int64_t i = base + threadIdx.x;
+            bool esc = false;
+            unsigned code = 0xFFu;
+            int x = 0, y = 0;
+            if (i < src.c) {
+                src.xy(i, x, y);
+                esc = i == 0;
+                if (!esc) {
+                    int px, py;
+                    src.xy(i - 1, px, py);
+                    esc = !delta32_code(px, py, x, y, code);
+                }
+                if (esc) code = 0xFFu;
+                out[o + i] = ((uint32_t) src.weight(i) & 0xffffffu) | (code << 24);
+            }
+            const unsigned bal = __ballot_sync(0xffffffffu, esc);
+            if (lane == 0) warp_tot[wid] = __popc(bal);
+            __syncthreads();
+            int before = __popc(bal & ((1u << lane) - 1u));
+            for (int w = 0; w < wid; w++) before += warp_tot[w];
+            if (esc) {
+                TupleXY e;
+                e.x = x;
+                e.y = y;
+                esc_out[eo + before] = e;
+            }
+            eo += warp_tot[0] + warp_tot[1] + warp_tot[2] + warp_tot[3];
+            __syncthreads();
+        }
+    }
+}
+
 // ------------------------------------------------------------------------------------------------- seam guard
 //
 // The tiling rests on both recurrences forgetting their start within the warm-up.  That is a property of the data

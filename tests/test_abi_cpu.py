@@ -33,7 +33,7 @@ def test_struct_layouts_match_header():
     assert C.sizeof(abi.Model) == 8 * (9 + 16 + 4 + 4) + 8 + 8 * 4 * 51 * 51
     assert C.sizeof(abi.Params) == 48
     assert C.sizeof(abi.BatchStruct) == 88
-    assert C.sizeof(abi.ResultStruct) == 8 + 24 + 24 + 32 + 8 + 8 + 8 + 16 + 8
+    assert C.sizeof(abi.ResultStruct) == 8 + 24 + 24 + 32 + 8 + 8 + 8 + 16 + 8 + 24 + 24
     assert abi.PAIR_DTYPE.itemsize == 12
 
 

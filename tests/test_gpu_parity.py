@@ -370,3 +370,25 @@ def test_adversarial_seams_stay_exact(oracle, golden_model, monkeypatch, tile_le
         ref = oracle.posteriors(pm.models[it[3]], pm.p, it[0], it[1], it[2], it[4], it[5], 1)
         compare_lists(got[i], ref, tol_w=1)
     al.close()
+
+
+@pytest.mark.gpu
+def test_delta32_tuples_decode_to_the_plain_lists(golden_model, monkeypatch):
+    """MARGIN_B200_PAIRS_DELTA32 (4-byte step records + escapes, include/margin_b200.h) decodes to exactly the lists of
+    the plain format: narrow tiles, wide tiles, sequential jobs, split alignments, empty lists, -1 coordinates of the gap
+    lists, match-only calls."""
+    pm = golden_model("r94g360")
+    rng = np.random.default_rng(32)
+    items = [gen.random_case(rng, int(rng.integers(0, 1500))) for _ in range(40)]
+    items += [gen.gapped_anchor_case(rng, 4000, 90), gen.long_indel_case(rng, 3000, 1200, 400, True)]
+    items.insert(3, (np.zeros(0, np.uint16), np.zeros(0, np.uint16), np.zeros((0, 3), np.int32), 0, 0, 0))
+    for md, split, wi in ((300, 3000 * 3000, 1), (5000, 80 * 80, 1), (150, 3000 * 3000, 0)):
+        p = pm.p.copy(min_diags_between_traceback=md, split_matrix_bigger_than_this=split)
+        al = PairHmmAligner(pm.models, p, device=0)
+        want = al.posteriors_batch(items, bool(wi))
+        al.set_pair_format(abi.PAIRS_DELTA32)
+        got = al.posteriors_batch(items, bool(wi))
+        assert sum(len(x) for g in got.lists for x in g) == sum(len(x) for g in want.lists for x in g) > 0
+        for i in range(len(items)):
+            compare_lists(got[i], want[i], tol_w=0)
+        al.close()
