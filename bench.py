@@ -560,7 +560,7 @@ def main_ours(args):
                    "reads_per_chunk": [b.n for b in batches], "band_cells_per_chunk": [int(c) for c in chunk_cells],
                    "sharding": "one contig of %d chunks, scheduler.shard_chunks (size-descending LPT), no collective" % n_chunks,
                    "params": "ont/r9.4 r94-g360 (RLE, repeat counts)", "l2": "flushed between steps (512 MiB write)",
-                   "boundary_formats": "plain" if args.plain_formats else "anchor steps 4 B, tuples 4 B step records + escapes",
+                   "boundary_formats": "plain" if args.plain_formats else "symbols 1 B, anchors as 4 B runs, tuples 4 B step records + escapes",
                    "tiles_per_step": stats_sum.get("tiles", 0) / args.steps,
                    "wide_cell_share": stats_sum.get("wide_cells", 0) / max(cells_done, 1),
                    "sequential_cell_share": stats_sum.get("sequential_cells", 0) / max(cells_done, 1),

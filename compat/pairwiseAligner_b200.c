@@ -266,7 +266,12 @@ typedef struct {
     int32_t *anchors;
     uint32_t *anchorsDelta; /* the compact words of margin_b200_batch.anchors_delta, kept beside the triples */
     int compactOk;          /* every anchor so far fits a compact word */
-    int64_t *offX, *offY, *offA;
+    uint8_t *packedX, *packedY; /* one byte per symbol (margin_b200_pack_symbol): what travels when packedOk */
+    int packedOk;
+    uint32_t *runs;         /* the anchors as runs (margin_b200_batch.anchors_runs): what travels when runsOk */
+    int64_t nRuns;
+    int runsOk;
+    int64_t *offX, *offY, *offA, *offR;
     uint8_t *slot, *raggedL, *raggedR;
 } B200Batch;
 
@@ -274,15 +279,19 @@ typedef struct {
 static __thread struct {
     uint16_t *symX, *symY;
     int32_t *anchors;
-    uint32_t *anchorsDelta;
+    uint32_t *anchorsDelta, *runs;
+    uint8_t *packedX, *packedY;
     int64_t capX, capY, capA;
     int full;
 } b200_spare;
 
 static B200Batch *b200_batch_construct(int64_t n) {
     B200Batch *b = st_calloc(1, sizeof(B200Batch));
-    b->compactOk = 1;
+    b->compactOk = b->packedOk = b->runsOk = 1;
     if (b200_spare.full) {
+        b->packedX = b200_spare.packedX;
+        b->packedY = b200_spare.packedY;
+        b->runs = b200_spare.runs;
         b->symX = b200_spare.symX;
         b->symY = b200_spare.symY;
         b->anchors = b200_spare.anchors;
@@ -296,6 +305,7 @@ static B200Batch *b200_batch_construct(int64_t n) {
     b->offX = st_calloc(b->capN + 1, sizeof(int64_t));
     b->offY = st_calloc(b->capN + 1, sizeof(int64_t));
     b->offA = st_calloc(b->capN + 1, sizeof(int64_t));
+    b->offR = st_calloc(b->capN + 1, sizeof(int64_t));
     b->slot = st_calloc(b->capN + 1, 1);
     b->raggedL = st_calloc(b->capN + 1, 1);
     b->raggedR = st_calloc(b->capN + 1, 1);
@@ -309,6 +319,7 @@ static void b200_batch_grow(B200Batch *b) {
     b->offX = st_realloc(b->offX, (b->capN + 1) * sizeof(int64_t));
     b->offY = st_realloc(b->offY, (b->capN + 1) * sizeof(int64_t));
     b->offA = st_realloc(b->offA, (b->capN + 1) * sizeof(int64_t));
+    b->offR = st_realloc(b->offR, (b->capN + 1) * sizeof(int64_t));
     b->slot = st_realloc(b->slot, b->capN + 1);
     b->raggedL = st_realloc(b->raggedL, b->capN + 1);
     b->raggedR = st_realloc(b->raggedR, b->capN + 1);
@@ -332,6 +343,9 @@ static void b200_batch_destruct(B200Batch *b) {
         b200_spare.symY = b->symY;
         b200_spare.anchors = b->anchors;
         b200_spare.anchorsDelta = b->anchorsDelta;
+        b200_spare.runs = b->runs;
+        b200_spare.packedX = b->packedX;
+        b200_spare.packedY = b->packedY;
         b200_spare.capX = b->capX;
         b200_spare.capY = b->capY;
         b200_spare.capA = b->capA;
@@ -341,10 +355,14 @@ static void b200_batch_destruct(B200Batch *b) {
         margin_b200_pinned_free(b->symY);
         free(b->anchors);
         margin_b200_pinned_free(b->anchorsDelta);
+        margin_b200_pinned_free(b->runs);
+        margin_b200_pinned_free(b->packedX);
+        margin_b200_pinned_free(b->packedY);
     }
     free(b->offX);
     free(b->offY);
     free(b->offA);
+    free(b->offR);
     free(b->slot);
     free(b->raggedL);
     free(b->raggedR);
@@ -353,7 +371,7 @@ static void b200_batch_destruct(B200Batch *b) {
 
 /* Appends one alignment; anchor x coordinates are shifted by -shiftX (the crop of impl/poa.c:637-639). */
 static void b200_batch_add(B200Batch *b, SymbolString sX, SymbolString sY, stList *anchorPairs, int64_t shiftX, int slot,
-                           bool raggedL, bool raggedR) {
+                           bool raggedL, bool raggedR, int rle) {
     b200_batch_grow(b);
     int64_t i = b->n++;
     int64_t nA = anchorPairs == NULL ? 0 : stList_length(anchorPairs);
@@ -361,21 +379,30 @@ static void b200_batch_add(B200Batch *b, SymbolString sX, SymbolString sY, stLis
     if (oX + sX.length > b->capX) {
         int64_t cap = (oX + sX.length) * 2 + 1024;
         b->symX = b200_pinned_grow(b->symX, oX * sizeof(uint16_t), cap * sizeof(uint16_t));
+        b->packedX = b200_pinned_grow(b->packedX, oX, cap);
         b->capX = cap;
     }
     if (oY + sY.length > b->capY) {
         int64_t cap = (oY + sY.length) * 2 + 1024;
         b->symY = b200_pinned_grow(b->symY, oY * sizeof(uint16_t), cap * sizeof(uint16_t));
+        b->packedY = b200_pinned_grow(b->packedY, oY, cap);
         b->capY = cap;
     }
     if (oA + nA > b->capA) {
         int64_t cap = (oA + nA) * 2 + 1024;
         b->anchors = st_realloc(b->anchors, cap * 3 * sizeof(int32_t));
         b->anchorsDelta = b200_pinned_grow(b->anchorsDelta, oA * sizeof(uint32_t), cap * sizeof(uint32_t));
+        b->runs = b200_pinned_grow(b->runs, b->nRuns * sizeof(uint32_t), cap * sizeof(uint32_t));
         b->capA = cap;
     }
     memcpy(b->symX + oX, sX.sequence, sX.length * sizeof(uint16_t)); /* Symbol is uint16_t, inc/stateMachine.h:15 */
     memcpy(b->symY + oY, sY.sequence, sY.length * sizeof(uint16_t));
+    /* one byte per symbol for the host link (a symbol that does not fit keeps the whole batch on the uint16 arrays, where
+     * the library reports it) */
+    for (int64_t k = 0; k < sX.length && b->packedOk; k++)
+        if ((b->packedX[oX + k] = margin_b200_pack_symbol(sX.sequence[k], rle)) == 255) b->packedOk = 0;
+    for (int64_t k = 0; k < sY.length && b->packedOk; k++)
+        if ((b->packedY[oY + k] = margin_b200_pack_symbol(sY.sequence[k], rle)) == 255) b->packedOk = 0;
     for (int64_t k = 0; k < nA; k++) {
         stIntTuple *a = stList_get(anchorPairs, k);
         b->anchors[3 * (oA + k)] = (int32_t) (stIntTuple_get(a, 0) - shiftX);
@@ -389,7 +416,18 @@ static void b200_batch_add(B200Batch *b, SymbolString sX, SymbolString sY, stLis
                                              b->anchors[3 * (oA + k) + 2]);
         if (w == 0) b->compactOk = 0;
         b->anchorsDelta[oA + k] = w;
+        /* and as runs: BAM-derived anchors are one per match column, so most steps are (+1, +1) with the same expansion */
+        int64_t dx = b->anchors[3 * (oA + k)] - px, dy = b->anchors[3 * (oA + k) + 1] - py, e = b->anchors[3 * (oA + k) + 2];
+        if (k > 0 && dx == 1 && dy == 1 && e == b->anchors[3 * (oA + k - 1) + 2] && (b->runs[b->nRuns - 1] & 255u) < 255u &&
+            b->runs[b->nRuns - 1] != 0) {
+            b->runs[b->nRuns - 1]++;
+        } else {
+            uint32_t r = margin_b200_pack_anchor_run(dx, dy, e);
+            if (r == 0) b->runsOk = 0;
+            b->runs[b->nRuns++] = r;
+        }
     }
+    b->offR[i + 1] = b->nRuns;
     b->offX[i + 1] = oX + sX.length;
     b->offY[i + 1] = oY + sY.length;
     b->offA[i + 1] = oA + nA;
@@ -410,6 +448,14 @@ static void b200_batch_describe(const B200Batch *b, margin_b200_batch *mb) {
     mb->off_y = b->offY;
     mb->anchors = b->anchors ? b->anchors : b200_noAnchors;
     if (b->compactOk && b->anchorsDelta) mb->anchors_delta = b->anchorsDelta; /* takes precedence over the triples */
+    if (b->runsOk && b->nRuns > 0) { /* ... and the runs over both */
+        mb->anchors_runs = b->runs;
+        mb->off_r = b->offR;
+    }
+    if (b->packedOk && b->packedX && b->packedY) {
+        mb->packed_x = b->packedX;
+        mb->packed_y = b->packedY;
+    }
     mb->off_a = b->offA;
     mb->model_slot = b->slot;
     mb->ragged_left = b->raggedL;
@@ -485,7 +531,7 @@ void getAlignedPairsWithIndelsUsingAnchors(StateMachine *sM, SymbolString sX, Sy
     b200_load_machine(0, sM);
     b200_load_params(p);
     B200Batch *b = b200_batch_construct(1);
-    b200_batch_add(b, sX, sY, anchorPairs, 0, 0, alignmentHasRaggedLeftEnd, alignmentHasRaggedRightEnd);
+    b200_batch_add(b, sX, sY, anchorPairs, 0, 0, alignmentHasRaggedLeftEnd, alignmentHasRaggedRightEnd, tls.loaded[0].rle);
     margin_b200_result res;
     b200_batch_run(b, 1, &res);
     *alignedPairs = b200_list(&res, 0, 0, 0);
@@ -500,7 +546,7 @@ stList *getAlignedPairsUsingAnchors(StateMachine *sM, SymbolString sX, SymbolStr
     b200_load_machine(0, sM);
     b200_load_params(p);
     B200Batch *b = b200_batch_construct(1);
-    b200_batch_add(b, sX, sY, anchorPairs, 0, 0, alignmentHasRaggedLeftEnd, alignmentHasRaggedRightEnd);
+    b200_batch_add(b, sX, sY, anchorPairs, 0, 0, alignmentHasRaggedLeftEnd, alignmentHasRaggedRightEnd, tls.loaded[0].rle);
     margin_b200_result res;
     b200_batch_run(b, 0, &res);
     stList *alignedPairs = b200_list(&res, 0, 0, 0);
@@ -1155,7 +1201,7 @@ Poa *poa_realign(stList *bamChunkReads, stList *anchorAlignments, RleString *ref
                                                           polishParams->useRepeatCountsInAlignment, maxRL);
         SymbolString sY = rleString_constructSymbolString(read, 0, read->length, polishParams->alphabet,
                                                           polishParams->useRepeatCountsInAlignment, maxRL);
-        b200_batch_add(b, sX, sY, anchorPairs, firstRefPosition, chunkRead->forwardStrand ? 0 : 1, 0, 0);
+        b200_batch_add(b, sX, sY, anchorPairs, firstRefPosition, chunkRead->forwardStrand ? 0 : 1, 0, 0, tls.loaded[0].rle);
         symbolString_destruct(sX);
         symbolString_destruct(sY);
         firstRefPositions[i] = firstRefPosition;
@@ -1222,6 +1268,7 @@ typedef struct B200Deferred {
     double *results;
     int64_t capResults;
     StateMachine *machines[2]; /* the machines of the queued jobs (slot = index) */
+    int rle[2];                /* ... and whether their symbols carry run lengths */
     PairwiseAlignmentParameters params;
     int haveParams;
     int warned;
@@ -1305,7 +1352,7 @@ double computeForwardProbability(SymbolString sX, SymbolString sY, stList *ancho
         b200_load_machine(0, sM);
         b200_load_params(p);
         B200Batch *b = b200_batch_construct(1);
-        b200_batch_add(b, sX, sY, anchorPairs, 0, 0, alignmentHasRaggedLeftEnd, alignmentHasRaggedRightEnd);
+        b200_batch_add(b, sX, sY, anchorPairs, 0, 0, alignmentHasRaggedLeftEnd, alignmentHasRaggedRightEnd, tls.loaded[0].rle);
         double out = LOG_ZERO;
         b200_forward_run(b, &out);
         b200_batch_destruct(b);
@@ -1319,6 +1366,7 @@ double computeForwardProbability(SymbolString sX, SymbolString sY, stList *ancho
         if (d->machines[0] != NULL && d->machines[1] != NULL) b200_deferred_flush(d); /* a third machine */
         slot = d->machines[0] == NULL ? 0 : 1;
         d->machines[slot] = sM;
+        d->rle[slot] = b200_is_rle(sM);
     }
     tls.dynamicAnchors = p->dynamicAnchorExpansion;
     int64_t job = d->done + d->queue->n;
@@ -1330,7 +1378,7 @@ double computeForwardProbability(SymbolString sX, SymbolString sY, stList *ancho
         d->lengths[2 * job] = sX.length;
         d->lengths[2 * job + 1] = sY.length;
     }
-    b200_batch_add(d->queue, sX, sY, anchorPairs, 0, slot, alignmentHasRaggedLeftEnd, alignmentHasRaggedRightEnd);
+    b200_batch_add(d->queue, sX, sY, anchorPairs, 0, slot, alignmentHasRaggedLeftEnd, alignmentHasRaggedRightEnd, d->rle[slot]);
     if (d->queue->offX[d->queue->n] + d->queue->offY[d->queue->n] > B200_FLUSH_SYMBOLS) b200_deferred_flush(d);
     return b200_tagged_nan(job);
 }

@@ -102,7 +102,38 @@ typedef struct margin_b200_batch {
      * device expands it back to triples.  A batch with a step >= 4096 or an expansion >= 512 must use `anchors`
      * (the margin_b200_pack_anchor helper below returns 0 for such an anchor). */
     const uint32_t *anchors_delta;
+    /* Optional still more compact forms (NULL = not used); both exist because the host link, not the GPU, bounds a box
+     * of eight GPUs.
+     * packed_x / packed_y: the symbols as one byte each, min(base, 4) * 51 + run length (run length 0 without repeat
+     * counts), same offsets as sym_x / sym_y, which may then be NULL.  The host checks run lengths < 51 while packing
+     * (margin_b200_pack_symbol returns 255 for a symbol that does not fit; such a batch must send sym_x / sym_y).
+     * anchors_runs / off_r: the anchors as runs, one 32-bit word per run (alignment i owns words off_r[i] .. off_r[i+1]):
+     *   bits 0-7   run: this many FURTHER anchors follow at step (+1, +1) with the same expansion
+     *   bits 8-17  x - x_prev of the run's first anchor (x_prev = -1 before an alignment's first anchor), 1..1023
+     *   bits 18-27 y - y_prev, likewise
+     *   bits 28-31 expansion / 2 (expansion even, 0..30)
+     * off_a still counts anchors.  Takes precedence over anchors_delta and anchors; `anchors` should still be given
+     * (the rare host-side paths — large-gap splitting, the message for a bad anchor — read the triples). */
+    const uint8_t *packed_x;
+    const uint8_t *packed_y;
+    const uint32_t *anchors_runs;
+    const int64_t *off_r;
 } margin_b200_batch;
+
+/* The packed byte of a Symbol (inc/stateMachine.h:15: base | run length << 8 with repeat counts, else the base), or 255
+ * when it does not fit (run length >= 51). */
+static inline uint8_t margin_b200_pack_symbol(uint16_t symbol, int rle) {
+    const unsigned b = rle ? (symbol & 255u) : symbol, r = rle ? (unsigned) (symbol >> 8) : 0u;
+    if (r >= (unsigned) MARGIN_B200_MAX_RL) return 255;
+    return (uint8_t) ((b > 4u ? 4u : b) * MARGIN_B200_MAX_RL + r);
+}
+
+/* The first word of a run (run = 0), or 0 when the anchor does not fit (dx, dy in 1..1023, expansion even in 0..30);
+ * a following anchor at step (+1, +1) with the same expansion extends the run by adding 1 to the word, up to 255 times. */
+static inline uint32_t margin_b200_pack_anchor_run(int64_t dx, int64_t dy, int64_t expansion) {
+    if (dx < 1 || dx > 1023 || dy < 1 || dy > 1023 || expansion < 0 || expansion > 30 || (expansion & 1)) return 0;
+    return ((uint32_t) dx << 8) | ((uint32_t) dy << 18) | ((uint32_t) (expansion / 2) << 28);
+}
 
 /* The compact anchor word, or 0 when the anchor does not fit (dx, dy in 1..4095, expansion even in 0..510). */
 static inline uint32_t margin_b200_pack_anchor(int64_t dx, int64_t dy, int64_t expansion) {

@@ -72,6 +72,10 @@ class BatchStruct(C.Structure):
         ("ragged_left", C.c_void_p),
         ("ragged_right", C.c_void_p),
         ("anchors_delta", C.c_void_p),
+        ("packed_x", C.c_void_p),
+        ("packed_y", C.c_void_p),
+        ("anchors_runs", C.c_void_p),
+        ("off_r", C.c_void_p),
     ]
 
 
@@ -184,9 +188,13 @@ class Batch:
         self.struct = BatchStruct(
             n, self.sym_x.ctypes.data, self.off_x.ctypes.data, self.sym_y.ctypes.data, self.off_y.ctypes.data,
             self.anchors.ctypes.data, self.off_a.ctypes.data, self.model_slot.ctypes.data,
-            self.ragged_left.ctypes.data, self.ragged_right.ctypes.data, None)
+            self.ragged_left.ctypes.data, self.ragged_right.ctypes.data, None, None, None, None, None)
+        self.runs = False
+        self.packed = False
         if compact:
             self.use_compact_anchors()
+            self.use_packed_symbols()
+            self.use_anchor_runs()
 
     def use_compact_anchors(self):
         """Switches the batch to the 4-byte anchor words (what a C host emits while walking its anchor lists); keeps
@@ -197,6 +205,52 @@ class Batch:
         self.anchors_delta = np.ascontiguousarray(d)
         self.struct.anchors_delta = self.anchors_delta.ctypes.data  # takes precedence; the triples stay for the oracle
         self.compact = True
+        return True
+
+    def use_packed_symbols(self):
+        """One byte per symbol (margin_b200_pack_symbol); keeps the uint16 arrays when a run length does not fit."""
+        def pack(a):
+            b = np.minimum(a & 255, 4).astype(np.uint16)
+            r = a >> 8
+            return None if (r >= MAX_RL).any() else (b * MAX_RL + r).astype(np.uint8)
+        px, py = pack(self.sym_x), pack(self.sym_y)
+        if px is None or py is None:
+            return False
+        self.packed_x, self.packed_y = np.ascontiguousarray(px), np.ascontiguousarray(py)
+        self.struct.packed_x, self.struct.packed_y = self.packed_x.ctypes.data, self.packed_y.ctypes.data
+        self.packed = True
+        return True
+
+    def use_anchor_runs(self):
+        """The anchors as runs (margin_b200_pack_anchor_run): an anchor at step (+1, +1) from its predecessor with the same
+        expansion extends the predecessor's run (up to 255 followers).  Keeps the other forms when an anchor does not fit."""
+        a = np.asarray(self.anchors, dtype=np.int64).reshape(-1, 3)
+        na = int(self.off_a[-1])
+        if na == 0 or self.n == 0:
+            return False
+        a = a[:na]
+        prev = np.empty((na, 3), np.int64)
+        prev[1:] = a[:-1]
+        first = np.asarray(self.off_a[:-1], dtype=np.int64)
+        first = first[np.diff(self.off_a) > 0]
+        prev[first, :2] = -1
+        prev[first, 2] = -2  # never equal to an expansion: the first anchor of an alignment starts a run
+        d = a[:, :2] - prev[:, :2]
+        e = a[:, 2]
+        if (d < 1).any() or (d > 1023).any() or (e < 0).any() or (e > 30).any() or (e & 1).any():
+            return False
+        follow = (d[:, 0] == 1) & (d[:, 1] == 1) & (e == prev[:, 2])
+        # position inside a maximal stretch of followers; every 256th follower starts a new run
+        idx = np.arange(na)
+        start = np.maximum.accumulate(np.where(~follow, idx, 0))
+        follow &= ((idx - start) % 256) != 0
+        heads = np.flatnonzero(~follow)
+        run = np.diff(np.append(heads, na)) - 1
+        words = (run | (d[heads, 0] << 8) | (d[heads, 1] << 18) | ((e[heads] // 2) << 28)).astype(np.uint32)
+        self.anchors_runs = np.ascontiguousarray(words)
+        self.off_r = np.searchsorted(heads, np.asarray(self.off_a, dtype=np.int64)).astype(np.int64)
+        self.struct.anchors_runs, self.struct.off_r = self.anchors_runs.ctypes.data, self.off_r.ctypes.data
+        self.runs = True
         return True
 
     def to_pinned(self):
@@ -213,9 +267,16 @@ class Batch:
             out = np.frombuffer((C.c_char * max(a.nbytes, 1)).from_address(p), dtype=a.dtype, count=a.size).reshape(a.shape)
             out[...] = a
             return out
-        self.sym_x, self.sym_y = move(self.sym_x), move(self.sym_y)
-        self.struct.sym_x, self.struct.sym_y = self.sym_x.ctypes.data, self.sym_y.ctypes.data
-        if self.compact:
+        if self.packed:
+            self.packed_x, self.packed_y = move(self.packed_x), move(self.packed_y)
+            self.struct.packed_x, self.struct.packed_y = self.packed_x.ctypes.data, self.packed_y.ctypes.data
+        else:
+            self.sym_x, self.sym_y = move(self.sym_x), move(self.sym_y)
+            self.struct.sym_x, self.struct.sym_y = self.sym_x.ctypes.data, self.sym_y.ctypes.data
+        if self.runs:
+            self.anchors_runs = move(self.anchors_runs)
+            self.struct.anchors_runs = self.anchors_runs.ctypes.data
+        elif self.compact:
             self.anchors_delta = move(self.anchors_delta)
             self.struct.anchors_delta = self.anchors_delta.ctypes.data
         else:
@@ -236,8 +297,10 @@ class Batch:
 
     @property
     def h2d_bytes(self):
-        anchors = self.anchors_delta.nbytes if self.compact else self.anchors.nbytes
-        return int(self.sym_x.nbytes + self.sym_y.nbytes + anchors + 3 * self.off_x.nbytes + 3 * self.n)
+        anchors = (self.anchors_runs.nbytes + self.off_r.nbytes if self.runs
+                   else (self.anchors_delta.nbytes if self.compact else self.anchors.nbytes))
+        syms = self.packed_x.nbytes + self.packed_y.nbytes if self.packed else self.sym_x.nbytes + self.sym_y.nbytes
+        return int(syms + anchors + 3 * self.off_x.nbytes + 3 * self.n)
 
 
 _LIB = None

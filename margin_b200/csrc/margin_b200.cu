@@ -714,16 +714,24 @@ extern "C" int margin_b200_upload_batch(margin_b200_ctx *c, const margin_b200_ba
     for (int k = 0; k < 2; k++)
         if (used[k] && (c->host_models[k].t[mb::T_YX] != -INFINITY || c->host_models[k].t[mb::T_XY] != -INFINITY))
             c->have_switch = true;
+    const bool packed_in = b->packed_x != nullptr && b->packed_y != nullptr;
+    const bool runs_in = b->anchors_runs != nullptr && b->off_r != nullptr;
+    if (!packed_in && ((nx && !b->sym_x) || (ny && !b->sym_y))) return fail("margin_b200_upload_batch: no symbols given");
     if (c->d_symx.ensure((nx + 1) * sizeof(uint16_t)) || c->d_symy.ensure((ny + 1) * sizeof(uint16_t)) ||
         c->d_anchors.ensure(((size_t) 3 * total_anchor_triples + 3) * sizeof(int32_t)) ||
-        c->d_offs.ensure((size_t) 3 * (n + 1) * sizeof(int64_t)) || c->d_status.ensure(((size_t) 2 * n + 2) * sizeof(int32_t)) ||
+        c->d_offs.ensure((size_t) 4 * (n + 1) * sizeof(int64_t)) || c->d_status.ensure(((size_t) 2 * n + 2) * sizeof(int32_t)) ||
         c->d_px.ensure((size_t) nx + 2 * mb::PACK_SLACK) || c->d_py.ensure((size_t) ny + 2 * mb::PACK_SLACK) ||
         c->d_err.ensure(sizeof(double)) ||
-        c->h_small.ensure(((size_t) 2 * n + 4) * sizeof(int32_t) + (size_t) 3 * (n + 1) * sizeof(int64_t)))
+        c->h_small.ensure(((size_t) 2 * n + 4) * sizeof(int32_t) + (size_t) 4 * (n + 1) * sizeof(int64_t)))
         return 1;
     CU(cudaStreamSynchronize(c->stream_sym));  // idle unless an upload was never followed by a sweep
     if (total_anchor_triples) {
-        if (b->anchors_delta) {
+        if (runs_in) {
+            const int64_t n_words = b->off_r[n];
+            if (c->d_anchors_delta.ensure((size_t) (n_words + 1) * sizeof(uint32_t))) return 1;
+            CU(cudaMemcpyAsync(c->d_anchors_delta.p, b->anchors_runs, (size_t) n_words * sizeof(uint32_t), cudaMemcpyHostToDevice,
+                               c->stream));
+        } else if (b->anchors_delta) {
             if (c->d_anchors_delta.ensure((size_t) total_anchor_triples * sizeof(uint32_t))) return 1;
             CU(cudaMemcpyAsync(c->d_anchors_delta.p, b->anchors_delta, (size_t) total_anchor_triples * sizeof(uint32_t),
                                cudaMemcpyHostToDevice, c->stream));
@@ -741,9 +749,16 @@ extern "C" int margin_b200_upload_batch(margin_b200_ctx *c, const margin_b200_ba
         memcpy(h_offs, b->off_a, (n + 1) * sizeof(int64_t));
         memcpy(h_offs + (n + 1), b->off_x, (n + 1) * sizeof(int64_t));
         memcpy(h_offs + 2 * (n + 1), b->off_y, (n + 1) * sizeof(int64_t));
-        if (ctl_copy(c->stream, d_offs, h_offs, (size_t) 3 * (n + 1) * sizeof(int64_t))) return 1;
+        if (runs_in) memcpy(h_offs + 3 * (n + 1), b->off_r, (n + 1) * sizeof(int64_t));
+        if (ctl_copy(c->stream, d_offs, h_offs, (size_t) (runs_in ? 4 : 3) * (n + 1) * sizeof(int64_t))) return 1;
         ctl_fill_status_kernel<<<(unsigned) ((n + 255) / 256), 256, 0, c->stream>>>(c->d_status.as<int32_t>(), n);
-        if (total_anchor_triples && b->anchors_delta)
+        if (total_anchor_triples && runs_in) {
+            if (c->d_sym_err.ensure(16)) return 1;
+            CU(cudaMemsetAsync(c->d_sym_err.as<char>() + 8, 0, 8, c->stream));
+            mb::expand_anchor_runs_kernel<256><<<(unsigned) n, 256, 0, c->stream>>>(c->d_anchors_delta.as<uint32_t>(), d_offs + 3 * (n + 1),
+                                                                                    d_offs, c->d_anchors.as<int32_t>(),
+                                                                                    c->d_sym_err.as<int>() + 2);
+        } else if (total_anchor_triples && b->anchors_delta)
             mb::expand_anchors_kernel<256><<<(unsigned) n, 256, 0, c->stream>>>(c->d_anchors_delta.as<uint32_t>(), d_offs,
                                                                                 c->d_anchors.as<int32_t>());
         mb::check_anchors_kernel<<<(unsigned) n, 256, 0, c->stream>>>(c->d_anchors.as<int32_t>(), d_offs, d_offs + (n + 1),
@@ -755,22 +770,35 @@ extern "C" int margin_b200_upload_batch(margin_b200_ctx *c, const margin_b200_ba
     // one-byte copies for the tile kernels (slack on both sides, see pairhmm_tiles.cuh); a run length the model cannot
     // hold is reported by the sweep (d_sym_err).
     if (c->d_sym_err.ensure(16)) return 1;
-    if (nx) CU(cudaMemcpyAsync(c->d_symx.p, b->sym_x, nx * sizeof(uint16_t), cudaMemcpyHostToDevice, c->stream_sym));
-    if (ny) CU(cudaMemcpyAsync(c->d_symy.p, b->sym_y, ny * sizeof(uint16_t), cudaMemcpyHostToDevice, c->stream_sym));
     CU(cudaMemsetAsync(c->d_px.p, 0, (size_t) nx + 2 * mb::PACK_SLACK, c->stream_sym));
     CU(cudaMemsetAsync(c->d_py.p, 0, (size_t) ny + 2 * mb::PACK_SLACK, c->stream_sym));
-    CU(cudaMemsetAsync(c->d_sym_err.p, 0, 16, c->stream_sym));
-    if (nx) mb::pack_symbols_kernel<<<(unsigned) ((nx + 255) / 256), 256, 0, c->stream_sym>>>(
-            c->d_symx.as<uint16_t>(), c->d_px.as<uint8_t>() + mb::PACK_SLACK, nx, rle, c->d_sym_err.as<int>());
-    if (ny) mb::pack_symbols_kernel<<<(unsigned) ((ny + 255) / 256), 256, 0, c->stream_sym>>>(
-            c->d_symy.as<uint16_t>(), c->d_py.as<uint8_t>() + mb::PACK_SLACK, ny, rle, c->d_sym_err.as<int>());
+    CU(cudaMemsetAsync(c->d_sym_err.p, 0, 8, c->stream_sym));  // [0]: symbols (this stream); [2]: anchor runs (main stream)
+    if (packed_in) {
+        // one byte per symbol over the link; the uint16 Symbols the general kernels read are rebuilt on the device
+        if (nx) CU(cudaMemcpyAsync(c->d_px.as<uint8_t>() + mb::PACK_SLACK, b->packed_x, nx, cudaMemcpyHostToDevice, c->stream_sym));
+        if (ny) CU(cudaMemcpyAsync(c->d_py.as<uint8_t>() + mb::PACK_SLACK, b->packed_y, ny, cudaMemcpyHostToDevice, c->stream_sym));
+        if (nx) mb::unpack_symbols_kernel<<<(unsigned) ((nx + 255) / 256), 256, 0, c->stream_sym>>>(
+                c->d_px.as<uint8_t>() + mb::PACK_SLACK, c->d_symx.as<uint16_t>(), nx, rle, c->d_sym_err.as<int>());
+        if (ny) mb::unpack_symbols_kernel<<<(unsigned) ((ny + 255) / 256), 256, 0, c->stream_sym>>>(
+                c->d_py.as<uint8_t>() + mb::PACK_SLACK, c->d_symy.as<uint16_t>(), ny, rle, c->d_sym_err.as<int>());
+    } else {
+        if (nx) CU(cudaMemcpyAsync(c->d_symx.p, b->sym_x, nx * sizeof(uint16_t), cudaMemcpyHostToDevice, c->stream_sym));
+        if (ny) CU(cudaMemcpyAsync(c->d_symy.p, b->sym_y, ny * sizeof(uint16_t), cudaMemcpyHostToDevice, c->stream_sym));
+        if (nx) mb::pack_symbols_kernel<<<(unsigned) ((nx + 255) / 256), 256, 0, c->stream_sym>>>(
+                c->d_symx.as<uint16_t>(), c->d_px.as<uint8_t>() + mb::PACK_SLACK, nx, rle, c->d_sym_err.as<int>());
+        if (ny) mb::pack_symbols_kernel<<<(unsigned) ((ny + 255) / 256), 256, 0, c->stream_sym>>>(
+                c->d_symy.as<uint16_t>(), c->d_py.as<uint8_t>() + mb::PACK_SLACK, ny, rle, c->d_sym_err.as<int>());
+    }
     CU(cudaEventRecord(c->ev_sym, c->stream_sym));
     if (n && ctl_copy(c->stream, h_status, c->d_status.p, (size_t) 2 * n * sizeof(int32_t))) return 1;
+    h_status[2 * n] = 0;
+    if (n && runs_in && total_anchor_triples && ctl_copy(c->stream, h_status + 2 * n, c->d_sym_err.as<char>() + 8, 8)) return 1;
     tr.mark("enqueue");
     if (c->after_h2d_enqueue) c->after_h2d_enqueue();
     CU(cudaStreamSynchronize(c->stream));
     CU(cudaGetLastError());
     tr.mark("h2d+check sync");
+    if (h_status[2 * n]) return fail("margin_b200_upload_batch: anchors_runs does not expand to the anchor counts of off_a");
 
     // ---- job table: one job per alignment, or one per block where getSplitPoints cuts (rare: host path)
     std::vector<int32_t> extra_anchors;
@@ -781,11 +809,12 @@ extern "C" int margin_b200_upload_batch(margin_b200_ctx *c, const margin_b200_ba
     for (int64_t i = 0; i < n; i++) {
         const int64_t lx = b->off_x[i + 1] - b->off_x[i], ly = b->off_y[i + 1] - b->off_y[i];
         const int64_t na = b->off_a[i + 1] - b->off_a[i];
-        const int32_t *anc = b->anchors + 3 * b->off_a[i];
+        const int32_t *anc = b->anchors ? b->anchors + 3 * b->off_a[i] : nullptr;
         if (h_status[2 * i] != 0x7fffffff) return (b->anchors && validate_anchors(anc, na, lx, ly, i)) ? 1 : fail("PAIRWISE_ALIGNMENT_EXCEPTION: alignment %lld: bad anchors", (long long) i);
         const bool rl = b->ragged_left && b->ragged_left[i], rr = b->ragged_right && b->ragged_right[i];
         const uint8_t slot = b->model_slot ? b->model_slot[i] : 0;
         if (h_status[2 * i + 1]) {
+            if (!anc && na) return fail("alignment %lld needs large-gap splitting: the batch must also carry its anchors as triples", (long long) i);
             split_points(anc, na, lx, ly, p.split_matrix_bigger_than_this, rl, rr, blocks);
         } else {
             blocks.assign(1, Block{0, 0, lx, ly});
@@ -2220,7 +2249,7 @@ extern "C" int margin_b200_posteriors_batch(margin_b200_ctx *c, const margin_b20
     }
     const int dev_slot = c->device & (kMaxDevices - 1);
     if ((g_live_contexts[dev_slot].load() == 1 || c->pipeline_force) && c->pipeline_k > 1 && b->n >= 2 && c->have_params &&
-        c->pair_format != MARGIN_B200_PAIRS_DELTA32) {  // the in-call pipeline assembles TRIPLES / PACKED64 lists only
+        c->pair_format != MARGIN_B200_PAIRS_DELTA32 && !b->packed_x && !b->anchors_runs) {  // the in-call pipeline predates the compact formats
         const int64_t bytes = 12 * b->off_a[b->n] + 2 * (b->off_x[b->n] + b->off_y[b->n]);
         const int K = (int) std::min<int64_t>(c->pipeline_k, b->n / 2);
         if (K > 1 && bytes >= c->pipeline_min_bytes) return posteriors_pipelined(c, b, want_indels, out, K);
@@ -2451,15 +2480,25 @@ int forward_batch_fast(margin_b200_ctx *c, const margin_b200_batch *b, double *o
     CU(cudaStreamSynchronize(c->stream_sym));
     CU(cudaEventRecord(c->ev0, c->stream));
     // symbols on their own stream, packed to bytes there (as in margin_b200_upload_batch)
-    if (nx) CU(cudaMemcpyAsync(c->d_symx.p, b->sym_x, nx * sizeof(uint16_t), cudaMemcpyHostToDevice, c->stream_sym));
-    if (ny) CU(cudaMemcpyAsync(c->d_symy.p, b->sym_y, ny * sizeof(uint16_t), cudaMemcpyHostToDevice, c->stream_sym));
+    const bool packed_in = b->packed_x != nullptr && b->packed_y != nullptr;
     CU(cudaMemsetAsync(c->d_px.p, 0, (size_t) nx + 2 * mb::PACK_SLACK, c->stream_sym));
     CU(cudaMemsetAsync(c->d_py.p, 0, (size_t) ny + 2 * mb::PACK_SLACK, c->stream_sym));
     CU(cudaMemsetAsync(c->d_sym_err.p, 0, 16, c->stream_sym));
-    if (nx) mb::pack_symbols_kernel<<<(unsigned) ((nx + 255) / 256), 256, 0, c->stream_sym>>>(
-            c->d_symx.as<uint16_t>(), c->d_px.as<uint8_t>() + mb::PACK_SLACK, nx, rle, c->d_sym_err.as<int>());
-    if (ny) mb::pack_symbols_kernel<<<(unsigned) ((ny + 255) / 256), 256, 0, c->stream_sym>>>(
-            c->d_symy.as<uint16_t>(), c->d_py.as<uint8_t>() + mb::PACK_SLACK, ny, rle, c->d_sym_err.as<int>());
+    if (packed_in) {  // the register-resident kernel reads packed bytes only; the unpack kernel is run for its range check
+        if (nx) CU(cudaMemcpyAsync(c->d_px.as<uint8_t>() + mb::PACK_SLACK, b->packed_x, nx, cudaMemcpyHostToDevice, c->stream_sym));
+        if (ny) CU(cudaMemcpyAsync(c->d_py.as<uint8_t>() + mb::PACK_SLACK, b->packed_y, ny, cudaMemcpyHostToDevice, c->stream_sym));
+        if (nx) mb::unpack_symbols_kernel<<<(unsigned) ((nx + 255) / 256), 256, 0, c->stream_sym>>>(
+                c->d_px.as<uint8_t>() + mb::PACK_SLACK, c->d_symx.as<uint16_t>(), nx, rle, c->d_sym_err.as<int>());
+        if (ny) mb::unpack_symbols_kernel<<<(unsigned) ((ny + 255) / 256), 256, 0, c->stream_sym>>>(
+                c->d_py.as<uint8_t>() + mb::PACK_SLACK, c->d_symy.as<uint16_t>(), ny, rle, c->d_sym_err.as<int>());
+    } else {
+        if (nx) CU(cudaMemcpyAsync(c->d_symx.p, b->sym_x, nx * sizeof(uint16_t), cudaMemcpyHostToDevice, c->stream_sym));
+        if (ny) CU(cudaMemcpyAsync(c->d_symy.p, b->sym_y, ny * sizeof(uint16_t), cudaMemcpyHostToDevice, c->stream_sym));
+        if (nx) mb::pack_symbols_kernel<<<(unsigned) ((nx + 255) / 256), 256, 0, c->stream_sym>>>(
+                c->d_symx.as<uint16_t>(), c->d_px.as<uint8_t>() + mb::PACK_SLACK, nx, rle, c->d_sym_err.as<int>());
+        if (ny) mb::pack_symbols_kernel<<<(unsigned) ((ny + 255) / 256), 256, 0, c->stream_sym>>>(
+                c->d_symy.as<uint16_t>(), c->d_py.as<uint8_t>() + mb::PACK_SLACK, ny, rle, c->d_sym_err.as<int>());
+    }
     CU(cudaEventRecord(c->ev_sym, c->stream_sym));
     // offsets and per-alignment flags, then the job table and the work lists on the device
     int64_t *d_offx = c->d_offs.as<int64_t>(), *d_offy = d_offx + (n + 1);
@@ -2543,8 +2582,14 @@ int forward_batch_fast(margin_b200_ctx *c, const margin_b200_batch *b, double *o
         std::vector<uint8_t> sl(n_gen, 0), rl(n_gen, 0), rr(n_gen, 0);
         for (int k = 0; k < n_gen; k++) {
             const int64_t i = gen_ids[k];
-            sx.insert(sx.end(), b->sym_x + b->off_x[i], b->sym_x + b->off_x[i + 1]);
-            sy.insert(sy.end(), b->sym_y + b->off_y[i], b->sym_y + b->off_y[i + 1]);
+            if (packed_in) {  // back to Symbols for the general path's small batch
+                auto sym = [&](uint8_t p) { return (uint16_t) (rle ? ((unsigned) (p % MARGIN_B200_MAX_RL) << 8) | (p / MARGIN_B200_MAX_RL) : p / MARGIN_B200_MAX_RL); };
+                for (int64_t q = b->off_x[i]; q < b->off_x[i + 1]; q++) sx.push_back(sym(b->packed_x[q]));
+                for (int64_t q = b->off_y[i]; q < b->off_y[i + 1]; q++) sy.push_back(sym(b->packed_y[q]));
+            } else {
+                sx.insert(sx.end(), b->sym_x + b->off_x[i], b->sym_x + b->off_x[i + 1]);
+                sy.insert(sy.end(), b->sym_y + b->off_y[i], b->sym_y + b->off_y[i + 1]);
+            }
             ox[k + 1] = (int64_t) sx.size();
             oy[k + 1] = (int64_t) sy.size();
             sl[k] = b->model_slot ? b->model_slot[i] : 0;

@@ -248,6 +248,66 @@ expand_anchors_kernel(const uint32_t *__restrict__ packed, const int64_t *__rest
     }
 }
 
+// Run-length form of the anchors (include/margin_b200.h: anchors_runs): one word per run,
+//   bits 0-7 run = following anchors at step (+1, +1) with the same expansion, bits 8-17 dx, bits 18-27 dy (steps of the
+//   run's first anchor from its predecessor, (-1, -1) before an alignment's first anchor), bits 28-31 expansion / 2.
+// BAM-derived anchors are one per match column (htsIntegration.c:722-729), so a run covers a whole gap-free stretch and
+// the anchors of a chunk travel in ~2 MB instead of 52 MB of triples.  One CTA per alignment, block-wide scans.
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS)
+expand_anchor_runs_kernel(const uint32_t *__restrict__ words, const int64_t *__restrict__ off_r,
+                          const int64_t *__restrict__ off_a, int32_t *__restrict__ anchors, int *__restrict__ err) {
+    const int64_t w0 = off_r[blockIdx.x], nw = off_r[blockIdx.x + 1] - w0;
+    const int64_t a0 = off_a[blockIdx.x], na = off_a[blockIdx.x + 1] - a0;
+    __shared__ int3 warp_sums[THREADS / 32];
+    __shared__ int3 carry_s;  // anchors so far, x and y of the last anchor
+    if (threadIdx.x == 0) carry_s = make_int3(0, -1, -1);
+    __syncthreads();
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    for (int64_t base = 0; base < nw; base += THREADS) {
+        const int64_t k = base + threadIdx.x;
+        const uint32_t v = k < nw ? words[w0 + k] : 0u;
+        const int run = (int) (v & 0xffu), dx = (int) ((v >> 8) & 0x3ffu), dy = (int) ((v >> 18) & 0x3ffu);
+        int sc = k < nw ? 1 + run : 0, sx = k < nw ? dx + run : 0, sy = k < nw ? dy + run : 0;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int nc = __shfl_up_sync(0xffffffffu, sc, o), nx = __shfl_up_sync(0xffffffffu, sx, o),
+                      ny = __shfl_up_sync(0xffffffffu, sy, o);
+            if (lane >= o) {
+                sc += nc;
+                sx += nx;
+                sy += ny;
+            }
+        }
+        if (lane == 31) warp_sums[wid] = make_int3(sc, sx, sy);
+        __syncthreads();
+        int3 pre = carry_s;
+        for (int w = 0; w < wid; w++) {
+            pre.x += warp_sums[w].x;
+            pre.y += warp_sums[w].y;
+            pre.z += warp_sums[w].z;
+        }
+        if (k < nw) {
+            // inclusive sums end at the run's last anchor; its first anchor is `run` steps before
+            const int first = pre.x + sc - (1 + run), x0 = pre.y + sx - run, y0 = pre.z + sy - run, e = (int) (v >> 28) * 2;
+            if (first + run >= na) {
+                atomicExch(err, 1);  // more anchors than off_a announces
+            } else {
+                int32_t *q = anchors + 3 * (a0 + first);
+                for (int j = 0; j <= run; j++) {
+                    q[3 * j] = x0 + j;
+                    q[3 * j + 1] = y0 + j;
+                    q[3 * j + 2] = e;
+                }
+            }
+        }
+        __syncthreads();
+        if (threadIdx.x == THREADS - 1) carry_s = make_int3(pre.x + sc, pre.y + sx, pre.z + sy);
+        __syncthreads();
+    }
+    if (threadIdx.x == 0 && carry_s.x != (int) na) atomicExch(err, 1);
+}
+
 __global__ void check_anchors_kernel(const int32_t *__restrict__ anchors, const int64_t *__restrict__ off_a,
                                      const int64_t *__restrict__ off_x, const int64_t *__restrict__ off_y, int64_t limit,
                                      int32_t *__restrict__ status) {

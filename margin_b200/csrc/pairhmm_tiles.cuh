@@ -56,6 +56,17 @@ __global__ void pack_symbols_kernel(const uint16_t *__restrict__ in, uint8_t *__
 
 __device__ __forceinline__ int packed_base(unsigned p) { return (int) ((p * 1286u) >> 16); }  // p / 51 for p < 255
 
+// packed byte -> uint16 Symbol, for the general kernels (wide tiles, sequential sweeps) when the host sent packed symbols
+__global__ void unpack_symbols_kernel(const uint8_t *__restrict__ in, uint16_t *__restrict__ out, int64_t n, int rle,
+                                      int *__restrict__ err) {
+    const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const unsigned p = in[i];
+    if (p >= (unsigned) PACK_STRIDE) atomicExch(err, 2);
+    const unsigned b = (p * 1286u) >> 16, r = p - b * MARGIN_B200_MAX_RL;
+    out[i] = (uint16_t) (rle ? ((r << 8) | b) : b);
+}
+
 __device__ __forceinline__ Cell cell_sel(bool p, const Cell &c) {
     Cell r;
     r.m = p ? c.m : MB_NEG_INF;

@@ -128,6 +128,32 @@ static int check_batch(margin_b200_ctx *c, const margin_b200_batch *b) {
             px = x;
             py = y;
         }
+        /* the compact forms the binding sends beside the plain arrays must expand to exactly those arrays */
+        if (b->anchors_runs != NULL) {
+            int64_t k = b->off_a[i];
+            px = py = -1;
+            for (int64_t r = b->off_r[i]; r < b->off_r[i + 1]; r++) {
+                uint32_t w = b->anchors_runs[r];
+                int64_t run = w & 255u, dx = (w >> 8) & 1023u, dy = (w >> 18) & 1023u, e = 2 * (int64_t) (w >> 28);
+                for (int64_t t = 0; t <= run; t++, k++) {
+                    px += t == 0 ? dx : 1;
+                    py += t == 0 ? dy : 1;
+                    if (k >= b->off_a[i + 1] || b->anchors[3 * k] != px || b->anchors[3 * k + 1] != py || b->anchors[3 * k + 2] != e)
+                        return fail("alignment %lld: anchors_runs does not expand to the anchor triples at anchor %lld",
+                                    (long long) i, (long long) (k - b->off_a[i]));
+                }
+            }
+            if (k != b->off_a[i + 1]) return fail("alignment %lld: anchors_runs ends early", (long long) i);
+        }
+        if (b->packed_x != NULL && b->packed_y != NULL && b->sym_x != NULL && b->sym_y != NULL) {
+            const int rle = c->models[slot].rle;
+            for (int64_t k = b->off_x[i]; k < b->off_x[i + 1]; k++)
+                if (b->packed_x[k] != margin_b200_pack_symbol(b->sym_x[k], rle))
+                    return fail("alignment %lld: packed_x differs from sym_x at %lld", (long long) i, (long long) (k - b->off_x[i]));
+            for (int64_t k = b->off_y[i]; k < b->off_y[i + 1]; k++)
+                if (b->packed_y[k] != margin_b200_pack_symbol(b->sym_y[k], rle))
+                    return fail("alignment %lld: packed_y differs from sym_y at %lld", (long long) i, (long long) (k - b->off_y[i]));
+        }
     }
     return 0;
 }

@@ -4,6 +4,7 @@ import ctypes as C
 import os
 import re
 
+import numpy as np
 import pytest
 
 from margin_b200 import abi
@@ -32,7 +33,7 @@ def test_library_exports_every_declared_symbol():
 def test_struct_layouts_match_header():
     assert C.sizeof(abi.Model) == 8 * (9 + 16 + 4 + 4) + 8 + 8 * 4 * 51 * 51
     assert C.sizeof(abi.Params) == 48
-    assert C.sizeof(abi.BatchStruct) == 88
+    assert C.sizeof(abi.BatchStruct) == 88 + 32
     assert C.sizeof(abi.ResultStruct) == 8 + 24 + 24 + 32 + 8 + 8 + 8 + 16 + 8 + 24 + 24
     assert abi.PAIR_DTYPE.itemsize == 12
 
@@ -45,3 +46,15 @@ def test_no_cpu_fallback_without_device():
     h = C.c_void_p()
     assert lib.margin_b200_create(C.byref(h), 0) != 0
     assert b"no usable CUDA device" in lib.margin_b200_last_error()
+
+
+def test_symbol_and_run_packing_on_the_host():
+    sx = np.array([0, 1 | (3 << 8), 4 | (50 << 8), 7 | (2 << 8)], np.uint16)
+    b = abi.Batch([(sx, sx[:2], np.array([[0, 0, 2], [1, 1, 2], [2, 3, 2], [3, 4, 2], [4, 5, 4]], np.int32), 0, 0, 0)], compact=True)
+    assert b.packed_x.tolist() == [0, 51 + 3, 4 * 51 + 50, 4 * 51 + 2]
+    assert b.anchors_runs.tolist() == [(1 << 8) | (1 << 18) | (1 << 28) | 1, (1 << 8) | (2 << 18) | (1 << 28) | 1,
+                                       (1 << 8) | (1 << 18) | (2 << 28)]
+    assert b.off_r.tolist() == [0, 3]
+    over = sx.copy()
+    over[0] = 51 << 8
+    assert not abi.Batch([(over, sx, np.zeros((0, 3), np.int32), 0, 0, 0)], compact=True).packed

@@ -392,3 +392,48 @@ def test_delta32_tuples_decode_to_the_plain_lists(golden_model, monkeypatch):
         for i in range(len(items)):
             compare_lists(got[i], want[i], tol_w=0)
         al.close()
+
+
+@pytest.mark.gpu
+def test_packed_symbols_and_anchor_runs_give_the_plain_results(golden_model):
+    """The one-byte symbols and the run-length anchors (margin_b200_batch.packed_x/packed_y/anchors_runs,
+    include/margin_b200.h) are expanded on the device to exactly the arrays of the plain call: identical lists,
+    identical forward totals, in both tuple formats; out-of-range anchors inside a run are still reported."""
+    pm = golden_model("r94g360")
+    rng = np.random.default_rng(77)
+    items = [gen.random_case(rng, int(rng.integers(1, 1500))) for _ in range(25)]
+    items += [gen.gapped_anchor_case(rng, 4000, 90), gen.long_indel_case(rng, 3000, 1200, 400, True)]
+    # one anchor per column over a long identical stretch: runs longer than a word's 255 followers, expansion changes
+    sx = gen.random_symbols(rng, 1400, True, 0.0)
+    dense = np.array([[i, i, 2 if i < 900 else 4] for i in range(3, 1390)], np.int32)
+    items.append((sx, sx.copy(), dense, 1, 0, 0))
+    items.insert(2, (np.zeros(0, np.uint16), np.zeros(0, np.uint16), np.zeros((0, 3), np.int32), 0, 0, 0))
+    p = pm.p.copy(min_diags_between_traceback=300)
+    al = PairHmmAligner(pm.models, p, device=0)
+    plain, compact = abi.Batch(items), abi.Batch(items, compact=True)
+    assert compact.packed and compact.runs and compact.h2d_bytes < 0.5 * plain.h2d_bytes
+    assert len(compact.anchors_runs) < 0.5 * len(compact.anchors)
+    for fmt in (abi.PAIRS_TRIPLES, abi.PAIRS_DELTA32):
+        al.set_pair_format(fmt)
+        want = al.posteriors_batch(plain, True)
+        got = al.posteriors_batch(compact, True)
+        assert sum(len(x) for g in want.lists for x in g) > 0
+        for i in range(len(items)):
+            compare_lists(got[i], want[i], tol_w=0)
+    small = [(it[0][:40], it[1][:40], np.zeros((0, 3), np.int32), it[3], it[4], it[5]) for it in items]
+    big = [(it[0], it[1], np.zeros((0, 3), np.int32), it[3], 0, 0) for it in items[:6]]
+    for fw in (small, small + big):
+        a, b = al.forward_batch(abi.Batch(fw)), al.forward_batch(abi.Batch(fw, compact=True))
+        assert np.array_equal(np.asarray(a), np.asarray(b))
+    # what does not fit stays on the wider forms
+    far = abi.Batch([(np.zeros(3000, np.uint16), np.zeros(3000, np.uint16), np.array([[10, 10, 2], [2000, 2100, 2]], np.int32),
+                      0, 0, 0)], compact=True)
+    assert far.compact and not far.runs and far.packed
+    assert len(al.posteriors_batch(far, False)) == 1
+    # a run that walks off the end of a sequence
+    off = abi.Batch([(sx[:100], sx[:100], np.array([[i, i, 2] for i in range(90, 104)], np.int32), 0, 0, 0)], compact=True)
+    assert off.runs
+    with pytest.raises(AlignerError):
+        al.posteriors_batch(off, False)
+    assert len(al.posteriors_batch(plain, False)) == len(items)  # the context is usable afterwards
+    al.close()
