@@ -777,6 +777,103 @@ static void **b200_list_array(stList *list) {
 }
 
 /*
+ * Observation slabs.  poa_augment allocates one 24-byte PoaBaseObservation per tuple (impl/poa.c:21-29,
+ * :338, :203, :232): nine million callocs per sweep of a 100 kb chunk and as many frees when the graph dies, more time
+ * than everything else the host does for the chunk.  A graph built by this file's poa_realign takes its observations from
+ * slabs instead: the match observations of all reads from ONE block laid out node by node (counted first, so every
+ * node's list is created at its final size and filled in place), insert / delete observations from a bump allocator.  The
+ * lists that hold slab observations get a NULL element destructor; the slabs hang off a registry keyed by the Poa and are
+ * released by poa_destruct below, which replaces the reference's (weakened, oracle/Makefile) and otherwise does what
+ * impl/poa.c:128-132 does.  Order and content of every list are those of the reference's read-by-read appends.
+ */
+typedef struct B200Slab {
+    struct B200Slab *next;
+    int64_t bytes;
+} B200Slab;
+
+typedef struct {
+    Poa *poa;
+    B200Slab *slabs;
+} B200SlabOwner;
+
+static pthread_mutex_t b200_slabLock = PTHREAD_MUTEX_INITIALIZER;
+static B200SlabOwner **b200_slabOwners; /* live graphs that own slabs (at most a few per thread) */
+static int64_t b200_slabOwnersN, b200_slabOwnersCap;
+
+static __thread struct {
+    B200SlabOwner *owner;         /* NULL: observations come from poaBaseObservation_construct */
+    char *at, *end;               /* the bump allocator's current slab */
+    PoaBaseObservation **nextObs; /* per node: where its next match observation goes ... */
+    void ***nextSlot;             /* ... and the slot of its list that will point at it */
+    int64_t capNodes;
+} slabState;
+
+#define B200_SLAB_BYTES (4 << 20)
+
+static void *b200_slab_new(B200SlabOwner *owner, int64_t bytes) {
+    B200Slab *slab = st_malloc(sizeof(B200Slab) + (size_t) bytes);
+    slab->bytes = bytes;
+    slab->next = owner->slabs; /* only the thread that builds the graph touches the chain until poa_destruct */
+    owner->slabs = slab;
+    return slab + 1;
+}
+
+static B200SlabOwner *b200_slab_owner(Poa *poa) {
+    B200SlabOwner *owner = st_calloc(1, sizeof(B200SlabOwner));
+    owner->poa = poa;
+    pthread_mutex_lock(&b200_slabLock);
+    if (b200_slabOwnersN == b200_slabOwnersCap) {
+        b200_slabOwnersCap = b200_slabOwnersCap * 2 + 64;
+        b200_slabOwners = st_realloc(b200_slabOwners, b200_slabOwnersCap * sizeof(B200SlabOwner *));
+    }
+    b200_slabOwners[b200_slabOwnersN++] = owner;
+    pthread_mutex_unlock(&b200_slabLock);
+    return owner;
+}
+
+static inline void *b200_slab_alloc(int64_t bytes) { /* 8-byte aligned, not zeroed */
+    bytes = (bytes + 7) & ~(int64_t) 7;
+    if (slabState.at + bytes > slabState.end) {
+        int64_t size = bytes > B200_SLAB_BYTES ? bytes : B200_SLAB_BYTES;
+        slabState.at = b200_slab_new(slabState.owner, size);
+        slabState.end = slabState.at + size;
+    }
+    void *out = slabState.at;
+    slabState.at += bytes;
+    return out;
+}
+
+static inline PoaBaseObservation *b200_observation(int64_t readNo, int64_t offset, double weight) {
+    if (slabState.owner == NULL) return poaBaseObservation_construct(readNo, offset, weight);
+    PoaBaseObservation *obs = b200_slab_alloc(sizeof(PoaBaseObservation));
+    obs->readNo = readNo;
+    obs->offset = offset;
+    obs->weight = weight;
+    return obs;
+}
+
+void poa_destruct(Poa *poa) {
+    B200Slab *slabs = NULL;
+    pthread_mutex_lock(&b200_slabLock);
+    for (int64_t i = 0; i < b200_slabOwnersN; i++) {
+        if (b200_slabOwners[i]->poa != poa) continue;
+        slabs = b200_slabOwners[i]->slabs;
+        free(b200_slabOwners[i]);
+        b200_slabOwners[i] = b200_slabOwners[--b200_slabOwnersN];
+        break;
+    }
+    pthread_mutex_unlock(&b200_slabLock);
+    stList_destruct(poa->nodes); /* lists of slab observations carry no element destructor */
+    rleString_destruct(poa->refString);
+    free(poa);
+    while (slabs != NULL) {
+        B200Slab *next = slabs->next;
+        free(slabs);
+        slabs = next;
+    }
+}
+
+/*
  * Where an insert / delete of a node already exists.  poa_augment (impl/poa.c:180-232) scans the node's list for every
  * candidate (rleString_eq per entry): with a few hundred reads the lists grow to dozens of low-weight entries and the
  * scans were a quarter of the augment.  During one poa_realign the graph starts without inserts and deletes, so an
@@ -867,6 +964,7 @@ static void b200_node_add_insert(PoaNode *node, RleString *insert, double weight
     }
     if (hit == NULL) {
         hit = poaInsert_construct(rleString_copy(insert), 0, FALSE);
+        if (slabState.owner != NULL) stList_setDestructor(hit->observations, NULL);
         stList_append(node->inserts, hit);
         if (indelTable.active) b200_indel_table_put(key, node, hit);
     }
@@ -894,12 +992,248 @@ static void b200_node_add_delete(PoaNode *node, int64_t length, double weight, b
     }
     if (hit == NULL) {
         hit = poaDelete_construct(length, 0, FALSE);
+        if (slabState.owner != NULL) stList_setDestructor(hit->observations, NULL);
         stList_append(node->deletes, hit);
         if (indelTable.active) b200_indel_table_put(key, node, hit);
     }
     if (strand) hit->weightForwardStrand += weight;
     else hit->weightReverseStrand += weight;
     stList_append(hit->observations, obs);
+}
+
+/*
+ * Inserts and deletes, node by node.  poa_augment looks every candidate up in its node's list the
+ * moment it is found (impl/poa.c:180-232); read after read that touches a different node, entry, observation list and
+ * string each time, a handful of cache misses per candidate and most of what is left of the augment.  With slabs on, the
+ * read loop only RECORDS candidates (node, read, offset, weight, strand, the shifted and rotated string); after the last
+ * read b200_candidates_commit orders them by node with a stable counting sort and walks each node once: its few distinct
+ * strings / lengths are matched in a small local table, every entry's observation list is created at its final size and
+ * the observations come from the slab.  The sort is stable and the recording order is the reference's processing order,
+ * so every list (inserts of a node, deletes of a node, observations of an entry) has the reference's order; weights are
+ * sums of integers below 2^24 and exact in any order.
+ */
+typedef struct {
+    int32_t node, readNo, offset, weight;
+    int64_t at;      /* inserts: where the string starts in B200Candidates.bases / counts; deletes: the length */
+    uint64_t hash;   /* inserts: of the string; deletes: unused */
+    int32_t length;  /* inserts: symbols of the string */
+    int32_t strand;
+} B200Candidate;
+
+typedef struct {
+    B200Candidate *items, *sorted;
+    int64_t n, cap, capSorted;
+    char *bases;
+    uint64_t *counts;
+    int64_t nSymbols, capSymbols;
+} B200Candidates;
+
+static __thread B200Candidates candidates[2]; /* 0 = inserts, 1 = deletes */
+static __thread int64_t candidateStats[4];    /* candidates and distinct entries of the last commit, per kind */
+
+static inline B200Candidate *b200_candidate_push(B200Candidates *c, int64_t node, int64_t readNo, int64_t offset, double weight,
+                                                 bool strand) {
+    if (c->n == c->cap) {
+        c->cap = c->cap * 2 + (1 << 16);
+        c->items = st_realloc(c->items, c->cap * sizeof(B200Candidate));
+    }
+    B200Candidate *it = &c->items[c->n++];
+    it->node = (int32_t) node;
+    it->readNo = (int32_t) readNo;
+    it->offset = (int32_t) offset;
+    it->weight = (int32_t) weight;
+    it->strand = strand;
+    return it;
+}
+
+static inline void b200_candidate_insert(int64_t node, const RleString *insert, double weight, bool strand, int64_t readNo,
+                                         int64_t offset) {
+    B200Candidates *c = &candidates[0];
+    B200Candidate *it = b200_candidate_push(c, node, readNo, offset, weight, strand);
+    if (c->nSymbols + (int64_t) insert->length > c->capSymbols) {
+        c->capSymbols = (c->capSymbols + (int64_t) insert->length) * 2 + (1 << 16);
+        c->bases = st_realloc(c->bases, c->capSymbols);
+        c->counts = st_realloc(c->counts, c->capSymbols * sizeof(uint64_t));
+    }
+    it->at = c->nSymbols;
+    it->length = (int32_t) insert->length;
+    uint64_t h = insert->length;
+    for (uint64_t i = 0; i < insert->length; i++) {
+        c->bases[c->nSymbols + i] = insert->rleString[i];
+        c->counts[c->nSymbols + i] = insert->repeatCounts[i];
+        h = (h ^ ((uint64_t) (unsigned char) insert->rleString[i] | (insert->repeatCounts[i] << 8))) * 0x100000001B3ULL;
+    }
+    it->hash = h;
+    c->nSymbols += insert->length;
+}
+
+static inline void b200_candidate_delete(int64_t node, int64_t length, double weight, bool strand, int64_t readNo, int64_t offset) {
+    B200Candidate *it = b200_candidate_push(&candidates[1], node, readNo, offset, weight, strand);
+    it->at = length;
+    it->hash = 0;
+    it->length = 0;
+}
+
+static void b200_candidates_sort(B200Candidates *c, int64_t nNodes) {
+    if (c->n > c->capSorted) {
+        c->capSorted = c->cap;
+        free(c->sorted);
+        c->sorted = st_malloc(c->capSorted * sizeof(B200Candidate));
+    }
+    int64_t *first = st_calloc(nNodes + 1, sizeof(int64_t));
+    for (int64_t k = 0; k < c->n; k++) first[c->items[k].node + 1]++;
+    for (int64_t j = 0; j < nNodes; j++) first[j + 1] += first[j];
+    for (int64_t k = 0; k < c->n; k++) c->sorted[first[c->items[k].node]++] = c->items[k];
+    free(first);
+}
+
+/* Inserts and deletes of a slab graph live in the slab themselves (struct, RleString, its two arrays): only their
+ * observation lists are separate allocations (so that a list can still be appended to), and releasing those is all
+ * the element destructor of node->inserts / node->deletes has left to do (cf. poaInsert_destruct, impl/poa.c:49-53). */
+static void b200_slab_insert_destruct(void *insert) { stList_destruct(((PoaInsert *) insert)->observations); }
+static void b200_slab_delete_destruct(void *delete) { stList_destruct(((PoaDelete *) delete)->observations); }
+
+static PoaInsert *b200_slab_insert(const char *bases, const uint64_t *counts, int64_t length) {
+    PoaInsert *insert = b200_slab_alloc(sizeof(PoaInsert));
+    RleString *string = b200_slab_alloc(sizeof(RleString));
+    string->rleString = b200_slab_alloc(length + 1);
+    string->repeatCounts = b200_slab_alloc(length * (int64_t) sizeof(uint64_t));
+    memcpy(string->rleString, bases, length);
+    string->rleString[length] = '\0';
+    string->length = (uint64_t) length;
+    string->nonRleLength = 0;
+    for (int64_t i = 0; i < length; i++) string->nonRleLength += (string->repeatCounts[i] = counts[i]);
+    insert->insert = string;
+    insert->weightForwardStrand = insert->weightReverseStrand = 0.0;
+    insert->observations = NULL;
+    return insert;
+}
+
+static PoaDelete *b200_slab_delete(int64_t length) {
+    PoaDelete *delete = b200_slab_alloc(sizeof(PoaDelete));
+    delete->length = length;
+    delete->weightForwardStrand = delete->weightReverseStrand = 0.0;
+    delete->observations = NULL;
+    return delete;
+}
+
+static void b200_candidates_commit(Poa *poa) {
+    int64_t nNodes = stList_length(poa->nodes);
+    void **nodes = b200_list_array(poa->nodes);
+    int64_t capLocal = 64, *entryOf = NULL, capEntryOf = 0;
+    struct {
+        uint64_t key;
+        void *entry;
+        int64_t count, filled;
+        void **slots;
+    } *local = st_malloc(capLocal * sizeof(*local));
+    for (int kind = 0; kind < 2; kind++) {
+        B200Candidates *c = &candidates[kind];
+        b200_candidates_sort(c, nNodes);
+        candidateStats[2 * kind] = c->n;
+        candidateStats[2 * kind + 1] = 0;
+        for (int64_t i = 0, j; i < c->n; i = j) {
+            PoaNode *node = nodes[c->sorted[i].node];
+            for (j = i + 1; j < c->n && c->sorted[j].node == c->sorted[i].node; j++);
+            if (j - i > capEntryOf) {
+                capEntryOf = (j - i) * 2 + 64;
+                entryOf = st_realloc(entryOf, capEntryOf * sizeof(int64_t));
+            }
+            int64_t nLocal = 0;
+            for (int64_t k = i; k < j; k++) { /* which entry of the node each candidate belongs to, new entries in order */
+                const B200Candidate *it = &c->sorted[k];
+                uint64_t key = kind == 0 ? it->hash : (uint64_t) it->at;
+                int64_t e = 0;
+                for (; e < nLocal; e++) {
+                    if (local[e].key != key) continue;
+                    if (kind == 1) break;
+                    const RleString *have = ((PoaInsert *) local[e].entry)->insert;
+                    if ((int64_t) have->length == it->length && memcmp(have->rleString, c->bases + it->at, it->length) == 0 &&
+                        memcmp(have->repeatCounts, c->counts + it->at, it->length * sizeof(uint64_t)) == 0) break;
+                }
+                if (e == nLocal) {
+                    if (nLocal == capLocal) {
+                        capLocal *= 2;
+                        local = st_realloc(local, capLocal * sizeof(*local));
+                    }
+                    local[e].key = key;
+                    local[e].count = 0;
+                    local[e].filled = 0;
+                    local[e].entry = kind == 0 ? (void *) b200_slab_insert(c->bases + it->at, c->counts + it->at, it->length)
+                                               : (void *) b200_slab_delete(it->at);
+                    nLocal++;
+                }
+                local[e].count++;
+                entryOf[k - i] = e;
+            }
+            candidateStats[2 * kind + 1] += nLocal;
+            /* the node's list and every entry's observation list at their final sizes */
+            stList **entries = kind == 0 ? &node->inserts : &node->deletes;
+            if (stList_length(*entries) != 0) st_errAbort("margin_b200: the graph is not fresh\n");
+            stList_destruct(*entries);
+            *entries = stList_construct3(nLocal, kind == 0 ? b200_slab_insert_destruct : b200_slab_delete_destruct);
+            void **entrySlots = b200_list_array(*entries);
+            for (int64_t e = 0; e < nLocal; e++) {
+                stList *observations = stList_construct3(local[e].count, NULL);
+                if (kind == 0) ((PoaInsert *) local[e].entry)->observations = observations;
+                else ((PoaDelete *) local[e].entry)->observations = observations;
+                local[e].slots = b200_list_array(observations);
+                entrySlots[e] = local[e].entry;
+            }
+            for (int64_t k = i; k < j; k++) {
+                const B200Candidate *it = &c->sorted[k];
+                int64_t e = entryOf[k - i];
+                double *forward = kind == 0 ? &((PoaInsert *) local[e].entry)->weightForwardStrand
+                                            : &((PoaDelete *) local[e].entry)->weightForwardStrand;
+                double *reverse = kind == 0 ? &((PoaInsert *) local[e].entry)->weightReverseStrand
+                                            : &((PoaDelete *) local[e].entry)->weightReverseStrand;
+                *(it->strand ? forward : reverse) += it->weight;
+                local[e].slots[local[e].filled++] = b200_observation(it->readNo, it->offset, it->weight);
+            }
+        }
+        c->n = 0;
+        c->nSymbols = 0;
+    }
+    free(local);
+    free(entryOf);
+}
+
+/*
+ * Counts the match tuples of ALL reads per node, takes one block for their observations and gives every node of the
+ * (fresh) graph an observation list of its final length; b200_poa_augment then writes observation k of a node straight
+ * into its place.  Reads are still walked in order, so each list holds what the reference's appends would (impl/poa.c:338).
+ */
+static void b200_match_lists_presize(Poa *poa, const margin_b200_result *res, int64_t n, const int64_t *shiftX) {
+    int64_t nNodes = stList_length(poa->nodes), total = 0;
+    if (nNodes + 1 > slabState.capNodes) {
+        slabState.capNodes = nNodes + 1;
+        slabState.nextObs = st_realloc(slabState.nextObs, slabState.capNodes * sizeof(PoaBaseObservation *));
+        slabState.nextSlot = st_realloc(slabState.nextSlot, slabState.capNodes * sizeof(void **));
+    }
+    int64_t *counts = st_calloc(nNodes + 1, sizeof(int64_t));
+    for (int64_t i = 0; i < n; i++) {
+        int64_t m = b200_pairs(res, 0, i, shiftX[i]);
+        const B200Pair *matches = augmentScratch.pairs[0];
+        for (int64_t k = 0; k < m; k++) {
+            if (matches[k].x + 1 < 1 || matches[k].x + 1 >= nNodes) st_errAbort("margin_b200: a match beyond the graph\n");
+            counts[matches[k].x + 1]++;
+        }
+        total += m;
+    }
+    slabState.owner = b200_slab_owner(poa);
+    slabState.at = slabState.end = NULL;
+    PoaBaseObservation *block = b200_slab_new(slabState.owner, (total + 1) * (int64_t) sizeof(PoaBaseObservation));
+    void **nodes = b200_list_array(poa->nodes);
+    for (int64_t j = 0; j < nNodes; j++) {
+        PoaNode *node = nodes[j];
+        if (stList_length(node->observations) != 0) st_errAbort("margin_b200: the graph is not fresh\n");
+        stList_destruct(node->observations);
+        node->observations = stList_construct3(counts[j], NULL);
+        slabState.nextObs[j] = block;
+        slabState.nextSlot[j] = b200_list_array(node->observations);
+        block += counts[j];
+    }
+    free(counts);
 }
 
 static void b200_poa_augment(Poa *poa, RleString *read, bool readStrand, int64_t readNo, const margin_b200_result *res,
@@ -920,7 +1254,15 @@ static void b200_poa_augment(Poa *poa, RleString *read, bool readStrand, int64_t
         node->baseWeights[poa->alphabet->convertCharToSymbol(read->rleString[y])] += matches[k].w;
         int64_t rc = read->repeatCounts[y] < poa->maxRepeatCount ? read->repeatCounts[y] : poa->maxRepeatCount - 1;
         node->repeatCountWeights[rc] += matches[k].w;
-        stList_append(node->observations, poaBaseObservation_construct(readNo, y, matches[k].w));
+        if (slabState.owner != NULL) { /* the node's list has its final size already (b200_match_lists_presize) */
+            PoaBaseObservation *obs = slabState.nextObs[matches[k].x + 1]++;
+            obs->readNo = readNo;
+            obs->offset = y;
+            obs->weight = matches[k].w;
+            *slabState.nextSlot[matches[k].x + 1]++ = obs;
+        } else {
+            stList_append(node->observations, poaBaseObservation_construct(readNo, y, matches[k].w));
+        }
     }
     double tPhase1 = omp_get_wtime();
     b200_match_set_fill(matches, nMatch);
@@ -946,8 +1288,8 @@ static void b200_poa_augment(Poa *poa, RleString *read, bool readStrand, int64_t
                     rleString_rotateString(insert, suffix, polishParams->useRunLengthEncoding);
                     position -= suffix;
                 }
-                b200_node_add_insert(nodes[position], insert, weight, readStrand,
-                                     poaBaseObservation_construct(readNo, yk, weight));
+                if (slabState.owner != NULL) b200_candidate_insert(position, insert, weight, readStrand, readNo, yk);
+                else b200_node_add_insert(nodes[position], insert, weight, readStrand, b200_observation(readNo, yk, weight));
             }
         }
     }
@@ -971,8 +1313,8 @@ static void b200_poa_augment(Poa *poa, RleString *read, bool readStrand, int64_t
                 RleString *deleted = b200_substring(poa->refString, xk, length);
                 int64_t position = getShift(poa->refString, xk, deleted, compareRL);
                 position -= getMaxCommonSuffixLength(poa->refString, position, deleted, compareRL);
-                b200_node_add_delete(nodes[position], length, weight, readStrand,
-                                     poaBaseObservation_construct(readNo, y, weight));
+                if (slabState.owner != NULL) b200_candidate_delete(position, length, weight, readStrand, readNo, y);
+                else b200_node_add_delete(nodes[position], length, weight, readStrand, b200_observation(readNo, y, weight));
             }
         }
     }
@@ -1160,6 +1502,18 @@ static int b200_reference_augment(void) {
  * (impl/poa.c:317-543) on stLists, 0 = with b200_poa_augment on the flat arrays. */
 void margin_b200_binding_set_reference_augment(int on) { b200_referenceAugment = on != 0; }
 
+static int b200_observationSlabs = -1; /* MARGIN_B200_OBSERVATION_SLABS=0: one calloc per observation, as the reference */
+
+static int b200_observation_slabs(void) {
+    if (b200_observationSlabs < 0) {
+        const char *e = getenv("MARGIN_B200_OBSERVATION_SLABS");
+        b200_observationSlabs = e == NULL || atoi(e) != 0;
+    }
+    return b200_observationSlabs;
+}
+
+void margin_b200_binding_set_observation_slabs(int on) { b200_observationSlabs = on != 0; }
+
 Poa *poa_realign(stList *bamChunkReads, stList *anchorAlignments, RleString *reference, PolishParams *polishParams) {
     uint64_t maximumRepeatLength = 2; /* MRL is exclusive */
     if (polishParams->useRunLengthEncoding) {
@@ -1213,6 +1567,12 @@ Poa *poa_realign(stList *bamChunkReads, stList *anchorAlignments, RleString *ref
     double tAligned = omp_get_wtime();
 
     b200_indel_table_begin(1); /* the graph is fresh: every insert and delete from here on goes through the table */
+    slabState.owner = NULL;
+    if (!b200_reference_augment() && b200_observation_slabs()) {
+        double t0 = omp_get_wtime();
+        b200_match_lists_presize(poa, &res, n, firstRefPositions);
+        tLists += omp_get_wtime() - t0;
+    }
     for (int64_t i = 0; i < n; i++) {
         BamChunkRead *chunkRead = stList_get(bamChunkReads, i);
         double t0 = omp_get_wtime();
@@ -1234,12 +1594,22 @@ Poa *poa_realign(stList *bamChunkReads, stList *anchorAlignments, RleString *ref
             tAugment += omp_get_wtime() - t0;
         }
     }
+    double tCommit = 0.0;
+    if (slabState.owner != NULL) { /* the recorded inserts and deletes, node by node */
+        double t0 = omp_get_wtime();
+        b200_candidates_commit(poa);
+        tCommit = omp_get_wtime() - t0;
+        tAugment += tCommit;
+    }
+    slabState.owner = NULL;
     free(firstRefPositions);
     b200_batch_destruct(b);
     st_logInfo(" margin_b200 poa_realign: %" PRIi64 " reads, setup (graph, context, model) %.3f s, prepare %.3f s, aligner (GPU, whole batch) %.3f s, "
-               "tuple lists %.3f s, poa_augment %.3f s (matches %.3f, match set %.3f, inserts %.3f, deletes %.3f), "
-               "free %.3f s\n", n, tStart - tSetup, tPrepared - tStart, tAligned - tPrepared, tLists, tAugment, augmentPhase[0],
-               augmentPhase[1], augmentPhase[2], augmentPhase[3], tFree);
+               "tuple lists / list sizing %.3f s, poa_augment %.3f s (matches %.3f, match set %.3f, inserts %.3f, deletes %.3f, "
+               "node-ordered commit %.3f: %" PRIi64 " insert candidates -> %" PRIi64 " inserts, %" PRIi64 " -> %" PRIi64 " deletes), free %.3f s\n",
+               n, tStart - tSetup, tPrepared - tStart, tAligned - tPrepared, tLists, tAugment, augmentPhase[0], augmentPhase[1],
+               augmentPhase[2], augmentPhase[3], tCommit, candidateStats[0], candidateStats[1], candidateStats[2], candidateStats[3],
+               tFree);
     return poa;
 }
 

@@ -21,6 +21,7 @@
 
 void margin_b200_binding_set_reference_augment(int on);
 void margin_b200_binding_set_bubble_batching(int on);
+void margin_b200_binding_set_observation_slabs(int on);
 void margin_b200_binding_augment_lists(Poa *poa, RleString *read, bool readStrand, int64_t readNo, stList *matches,
                                        stList *inserts, stList *deletes, PolishParams *polishParams);
 
@@ -170,6 +171,13 @@ static void test_b200_augment_ab(CuTest *testCase) {
         margin_b200_binding_set_reference_augment(1);
         Poa *theirs = poa_realign(reads, NULL, reference, polishParams);
         assert_poas_equal(testCase, ours, theirs);
+        /* observations from slabs (the default, `ours`) and one calloc each give the same graph */
+        margin_b200_binding_set_reference_augment(0);
+        margin_b200_binding_set_observation_slabs(0);
+        Poa *plain = poa_realign(reads, NULL, reference, polishParams);
+        margin_b200_binding_set_observation_slabs(1);
+        assert_poas_equal(testCase, plain, theirs);
+        poa_destruct(plain);
         /* round 2: anchors from the posteriors, as poa_realignIterative does (impl/poa.c:1910-1916) */
         stList *anchors = poa_getAnchorAlignments(ours, NULL, stList_length(reads), polishParams);
         margin_b200_binding_set_reference_augment(0);
