@@ -1289,6 +1289,21 @@ void build_tiles(margin_b200_ctx *c, int L) {
     for (int j = nj - 1; j >= 0; j--)  // jobs without gaps point at their successor's first entry
         if (c->job_gap_first[j] > c->job_gap_first[j + 1]) c->job_gap_first[j] = c->job_gap_first[j + 1];
     c->tile_binw = c->tile_maxw;
+    if (getenv("MARGIN_B200_TILE_STATS")) {  // widest diagonal per tile, weighted by the diagonals the tile walks
+        int64_t hist[34] = {0}, steps = 0;
+        for (size_t t = 0; t < c->tiles.size(); t++) {
+            const int64_t len = 2 * (int64_t) (c->tiles[t].D - c->tiles[t].f0);  // forward + backward
+            hist[std::min(c->tile_maxw[t], 33)] += len;
+            steps += len;
+        }
+        int longest = 0;
+        for (size_t t = 0; t < c->tiles.size(); t++) longest = std::max(longest, c->tiles[t].D - c->tiles[t].f0);
+        fprintf(stderr, "margin_b200 tile stats: %zu tiles for %d slots, tile length %d, longest sweep %d, %lld diagonal steps; "
+                "share of steps by widest diagonal:", c->tiles.size(), c->bwd_slots, L, longest, (long long) steps);
+        for (int w = 0; w < 34; w++)
+            if (hist[w]) fprintf(stderr, " %d:%.3f", w, (double) hist[w] / (double) std::max<int64_t>(steps, 1));
+        fprintf(stderr, "\n");
+    }
     c->aln_first_slot[c->n_aln] = (int32_t) c->tiles.size();
     c->job_first_tile[nj] = (int32_t) c->tiles.size();
     c->total_slots = (int) c->tiles.size();
