@@ -133,9 +133,10 @@ __device__ __forceinline__ double lds_f64(uint32_t a) {
 __device__ __forceinline__ double logadd_t(double x, double y, uint32_t lac_s) {
     const double ds = dadd(x, -y);
     const bool lt = __double2hiint(ds) < 0;
-    const double hi = lt ? y : x;
-    const double lo = lt ? x : y;
     const double d = fabs(ds);
+    const bool small = d < 7.5;
+    // lo when the polynomial counts, hi when it does not: one select instead of hi, lo and the final choice
+    const double base = (lt == small) ? x : y;
     double t;
     asm("fma.rp.f64 %0, %1, 0d4000000000000000, 0d4338000000000000;" : "=d"(t) : "d"(d));
     const uint32_t row = min((uint32_t) __double2loint(t), (uint32_t) (LA_ROWS - 1));  // inf, NaN, huge d: any row will do
@@ -145,8 +146,7 @@ __device__ __forceinline__ double logadd_t(double x, double y, uint32_t lac_s) {
     double v = dadd(dmul(c32.x, d), c32.y);
     v = dadd(dmul(v, d), c10.x);
     v = dadd(dmul(v, d), c10.y);
-    v = dadd(v, lo);
-    return (d < 7.5) ? v : hi;
+    return dadd(small ? v : 0.0, base);  // v + lo, or hi + 0 = hi
 }
 
 // A staged posterior: the log posterior v = F + B - total of a cell state that passes the threshold; the gather
