@@ -370,31 +370,40 @@ static void b200_batch_destruct(B200Batch *b) {
 }
 
 /* Appends one alignment; anchor x coordinates are shifted by -shiftX (the crop of impl/poa.c:637-639). */
+/* Room for nX / nY symbols and nA anchors in all (the filled parts are kept).  poa_realign knows the totals of a chunk
+ * before it adds the first read, so that the page-locked arrays are taken once instead of doubling their way up. */
+static void b200_batch_reserve(B200Batch *b, int64_t nX, int64_t nY, int64_t nA) {
+    int64_t oX = b->offX[b->n], oY = b->offY[b->n], oA = b->offA[b->n];
+    if (nX > b->capX) {
+        b->symX = b200_pinned_grow(b->symX, oX * sizeof(uint16_t), nX * sizeof(uint16_t));
+        b->packedX = b200_pinned_grow(b->packedX, oX, nX);
+        b->capX = nX;
+    }
+    if (nY > b->capY) {
+        b->symY = b200_pinned_grow(b->symY, oY * sizeof(uint16_t), nY * sizeof(uint16_t));
+        b->packedY = b200_pinned_grow(b->packedY, oY, nY);
+        b->capY = nY;
+    }
+    if (nA > b->capA) {
+        b->anchors = st_realloc(b->anchors, nA * 3 * sizeof(int32_t));
+        b->anchorsDelta = b200_pinned_grow(b->anchorsDelta, oA * sizeof(uint32_t), nA * sizeof(uint32_t));
+        b->runs = b200_pinned_grow(b->runs, b->nRuns * sizeof(uint32_t), nA * sizeof(uint32_t));
+        b->capA = nA;
+    }
+}
+
 static void b200_batch_add(B200Batch *b, SymbolString sX, SymbolString sY, stList *anchorPairs, int64_t shiftX, int slot,
                            bool raggedL, bool raggedR, int rle) {
     b200_batch_grow(b);
     int64_t i = b->n++;
     int64_t nA = anchorPairs == NULL ? 0 : stList_length(anchorPairs);
     int64_t oX = b->offX[i], oY = b->offY[i], oA = b->offA[i];
-    if (oX + sX.length > b->capX) {
-        int64_t cap = (oX + sX.length) * 2 + 1024;
-        b->symX = b200_pinned_grow(b->symX, oX * sizeof(uint16_t), cap * sizeof(uint16_t));
-        b->packedX = b200_pinned_grow(b->packedX, oX, cap);
-        b->capX = cap;
-    }
-    if (oY + sY.length > b->capY) {
-        int64_t cap = (oY + sY.length) * 2 + 1024;
-        b->symY = b200_pinned_grow(b->symY, oY * sizeof(uint16_t), cap * sizeof(uint16_t));
-        b->packedY = b200_pinned_grow(b->packedY, oY, cap);
-        b->capY = cap;
-    }
-    if (oA + nA > b->capA) {
-        int64_t cap = (oA + nA) * 2 + 1024;
-        b->anchors = st_realloc(b->anchors, cap * 3 * sizeof(int32_t));
-        b->anchorsDelta = b200_pinned_grow(b->anchorsDelta, oA * sizeof(uint32_t), cap * sizeof(uint32_t));
-        b->runs = b200_pinned_grow(b->runs, b->nRuns * sizeof(uint32_t), cap * sizeof(uint32_t));
-        b->capA = cap;
-    }
+    b->n--; /* b200_batch_reserve looks at the filled part */
+    if (oX + (int64_t) sX.length > b->capX || oY + (int64_t) sY.length > b->capY || oA + nA > b->capA)
+        b200_batch_reserve(b, oX + (int64_t) sX.length > b->capX ? (oX + sX.length) * 2 + 1024 : b->capX,
+                           oY + (int64_t) sY.length > b->capY ? (oY + sY.length) * 2 + 1024 : b->capY,
+                           oA + nA > b->capA ? (oA + nA) * 2 + 1024 : b->capA);
+    b->n++;
     memcpy(b->symX + oX, sX.sequence, sX.length * sizeof(uint16_t)); /* Symbol is uint16_t, inc/stateMachine.h:15 */
     memcpy(b->symY + oY, sY.sequence, sY.length * sizeof(uint16_t));
     /* one byte per symbol for the host link (a symbol that does not fit keeps the whole batch on the uint16 arrays, where
@@ -1532,6 +1541,26 @@ Poa *poa_realign(stList *bamChunkReads, stList *anchorAlignments, RleString *ref
     double tStart = omp_get_wtime(), tLists = 0.0, tAugment = 0.0, tFree = 0.0;
     memset(augmentPhase, 0, sizeof(augmentPhase));
     B200Batch *b = b200_batch_construct(n);
+    {
+        /* totals of the chunk: read symbols exactly, reference symbols from the reads' spans (bounded by the anchors'
+         * ends plus the read's overhang, or the whole reference without anchors), anchors exactly */
+        int64_t totalX = 0, totalY = 0, totalA = 0;
+        for (int64_t i = 0; i < n; i++) {
+            BamChunkRead *chunkRead = stList_get(bamChunkReads, i);
+            stList *anchorPairs = anchorAlignments == NULL ? NULL : stList_get(anchorAlignments, i);
+            int64_t nA = anchorPairs == NULL ? 0 : stList_length(anchorPairs), span = reference->length;
+            if (nA > 0) {
+                stIntTuple *fPair = stList_get(anchorPairs, 0), *lPair = stList_peek(anchorPairs);
+                span = stIntTuple_get(lPair, 0) - stIntTuple_get(fPair, 0) + 1 + chunkRead->rleRead->length -
+                       (stIntTuple_get(lPair, 1) - stIntTuple_get(fPair, 1));
+                if (span > (int64_t) reference->length) span = reference->length;
+            }
+            totalX += span;
+            totalY += chunkRead->rleRead->length;
+            totalA += nA;
+        }
+        b200_batch_reserve(b, totalX + 1024, totalY + 1024, totalA + 1024);
+    }
     int64_t *firstRefPositions = st_calloc(n, sizeof(int64_t));
     for (int64_t i = 0; i < n; i++) {
         BamChunkRead *chunkRead = stList_get(bamChunkReads, i);

@@ -13,6 +13,8 @@
 #include <cstring>
 #include <condition_variable>
 #include <functional>
+#include <iterator>
+#include <map>
 #include <memory>
 #include <mutex>
 #include <string>
@@ -53,28 +55,127 @@ constexpr int kFwdThreads = 128;
 constexpr int kBwdThreads = 128;
 constexpr int kTileThreads = 128;
 
+// ---- block caches
+// cudaFree and cudaFreeHost synchronise the whole device, and cudaMallocHost pins pages under a process-wide lock: with
+// `margin polish -t 16` every thread owns a context whose buffers are still growing during its first chunks, and each
+// growth stalled all the other threads' kernels and copies (measured on the 2 Mb contig: `aligner` 0.06 s alone, 1.4-5.7 s
+// with 16 threads; batch assembly in pinned memory 0.3 -> 3 s).  Device and pinned blocks therefore come in size classes
+// (2^k x {1, 1.25, 1.5, 1.75}) and go back to a process-wide cache instead of to the driver; a block is handed to the
+// cache only after the streams of the releasing thread's context are idle, so its next owner may use it at once.  The
+// caches are trimmed (largest blocks first) only beyond a byte limit or when an allocation fails.
+struct BlockCache {
+    std::mutex mu;
+    std::multimap<size_t, void *> blocks;
+    size_t bytes = 0;
+};
+BlockCache g_dev_cache[kMaxDevices], g_pin_cache;
+constexpr size_t kDevCacheLimit = (size_t) 24 << 30, kPinCacheLimit = (size_t) 8 << 30;
+thread_local cudaStream_t tls_streams[2] = {nullptr, nullptr};  // streams of the context this thread is working for
+
+inline size_t block_class(size_t bytes) {
+    size_t c = 4096;
+    while (c < bytes) c <<= 1;
+    if (c <= 65536) return c;
+    const size_t h = c >> 1;  // h < bytes <= c
+    for (int j = 1; j <= 3; j++)
+        if (h + (h >> 2) * j >= bytes) return h + (h >> 2) * j;
+    return c;
+}
+
+inline void *cache_take(BlockCache &cache, size_t cls) {
+    std::lock_guard<std::mutex> lock(cache.mu);
+    auto it = cache.blocks.find(cls);
+    if (it == cache.blocks.end()) return nullptr;
+    void *p = it->second;
+    cache.blocks.erase(it);
+    cache.bytes -= cls;
+    return p;
+}
+
+template <typename FreeFn>
+inline void cache_trim(BlockCache &cache, size_t keep, FreeFn free_fn) {  // caller holds no lock
+    std::vector<void *> victims;
+    {
+        std::lock_guard<std::mutex> lock(cache.mu);
+        while (cache.bytes > keep && !cache.blocks.empty()) {
+            auto it = std::prev(cache.blocks.end());
+            victims.push_back(it->second);
+            cache.bytes -= it->first;
+            cache.blocks.erase(it);
+        }
+    }
+    for (void *p : victims) free_fn(p);
+}
+
+inline void quiesce_own_streams() {
+    for (cudaStream_t st : tls_streams)
+        if (st) cudaStreamSynchronize(st);
+}
+
+template <typename FreeFn>
+inline void cache_put(BlockCache &cache, void *p, size_t cls, size_t limit, FreeFn free_fn) {
+    quiesce_own_streams();
+    bool over;
+    {
+        std::lock_guard<std::mutex> lock(cache.mu);
+        cache.blocks.emplace(cls, p);
+        cache.bytes += cls;
+        over = cache.bytes > limit;
+    }
+    if (over) cache_trim(cache, limit / 2, free_fn);
+}
+
 // Grow-only device buffer.
 struct DevBuf {
     void *p = nullptr;
     size_t cap = 0;
+    int dev = 0;
     int ensure(size_t bytes) {
         if (bytes <= cap) return 0;
-        if (p) cudaFree(p);
-        p = nullptr;
-        cap = 0;
-        size_t want = bytes + bytes / 4 + 256;  // geometric growth: a slightly larger chunk must not re-allocate GBs
-        cudaError_t e = cudaMalloc(&p, want);
-        if (e != cudaSuccess) return fail("cudaMalloc(%zu bytes) failed: %s", want, cudaGetErrorString(e));
+        release();
+        if (cudaGetDevice(&dev) != cudaSuccess) return fail("cudaGetDevice failed");
+        dev &= kMaxDevices - 1;
+        // geometric growth: a slightly larger chunk must not re-allocate GBs
+        const size_t want = block_class(bytes + bytes / 8 + 256);
+        p = cache_take(g_dev_cache[dev], want);
+        if (!p) {
+            cudaError_t e = cudaMalloc(&p, want);
+            if (e != cudaSuccess) {  // give the cached blocks back to the driver and try once more
+                cudaGetLastError();
+                cache_trim(g_dev_cache[dev], 0, [](void *q) { cudaFree(q); });
+                e = cudaMalloc(&p, want);
+            }
+            if (e != cudaSuccess) {
+                p = nullptr;
+                return fail("cudaMalloc(%zu bytes) failed: %s", want, cudaGetErrorString(e));
+            }
+        }
         cap = want;
         return 0;
     }
     void release() {
-        if (p) cudaFree(p);
+        if (p) cache_put(g_dev_cache[dev], p, cap, kDevCacheLimit, [](void *q) { cudaFree(q); });
         p = nullptr;
         cap = 0;
     }
     template <typename T> T *as() { return reinterpret_cast<T *>(p); }
 };
+
+inline void *pinned_take(size_t want) {
+    void *p = cache_take(g_pin_cache, want);
+    if (p) return p;
+    cudaError_t e = cudaMallocHost(&p, want);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        cache_trim(g_pin_cache, 0, [](void *q) { cudaFreeHost(q); });
+        e = cudaMallocHost(&p, want);
+    }
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return nullptr;
+    }
+    return p;
+}
 
 // Grow-only pinned host buffer.
 struct PinBuf {
@@ -82,17 +183,15 @@ struct PinBuf {
     size_t cap = 0;
     int ensure(size_t bytes) {
         if (bytes <= cap) return 0;
-        if (p) cudaFreeHost(p);
-        p = nullptr;
-        cap = 0;
-        size_t want = bytes + bytes / 8 + 256;
-        cudaError_t e = cudaMallocHost(&p, want);
-        if (e != cudaSuccess) return fail("cudaMallocHost(%zu bytes) failed: %s", want, cudaGetErrorString(e));
+        release();
+        const size_t want = block_class(bytes + bytes / 8 + 256);
+        p = pinned_take(want);
+        if (!p) return fail("cudaMallocHost(%zu bytes) failed", want);
         cap = want;
         return 0;
     }
     void release() {
-        if (p) cudaFreeHost(p);
+        if (p) cache_put(g_pin_cache, p, cap, kPinCacheLimit, [](void *q) { cudaFreeHost(q); });
         p = nullptr;
         cap = 0;
     }
@@ -228,6 +327,15 @@ struct margin_b200_ctx {
 };
 
 namespace {
+// Makes the context's device current and tells the block caches which streams this thread's work runs on.
+inline cudaError_t enter_ctx(margin_b200_ctx *c) {
+    tls_streams[0] = c->stream;
+    tls_streams[1] = c->stream_sym;
+    return cudaSetDevice(c->device);
+}
+}  // namespace
+
+namespace {
 
 enum { K_BAND = 0, K_SCHEDULE, K_FORWARD, K_BACKWARD, K_SCAN, K_GATHER, K_OFFSETS, K_FINAL, K_GUARD, K_NCLASS };
 
@@ -356,18 +464,22 @@ int margin_b200_device_count(void) {
 // Page-locked host memory for the caller's batch arrays: cudaMemcpyAsync from pageable memory is staged by the driver
 // (synchronous, a few GB/s); a host program that assembles its batch in memory from here gets true asynchronous copies.
 void *margin_b200_pinned_alloc(size_t bytes) {
-    void *p = nullptr;
-    if (bytes == 0) bytes = 1;
-    if (cudaMallocHost(&p, bytes) != cudaSuccess) {
-        cudaGetLastError();
-        fail("margin_b200_pinned_alloc: cudaMallocHost(%zu bytes) failed", bytes);
+    // one 64-byte header in front of the caller's memory remembers the block's size class for margin_b200_pinned_free
+    const size_t want = block_class(bytes + 64);
+    unsigned char *p = static_cast<unsigned char *>(pinned_take(want));
+    if (!p) {
+        fail("margin_b200_pinned_alloc: cudaMallocHost(%zu bytes) failed", want);
         return nullptr;
     }
-    return p;
+    *reinterpret_cast<size_t *>(p) = want;
+    return p + 64;
 }
 
 void margin_b200_pinned_free(void *p) {
-    if (p) cudaFreeHost(p);
+    if (!p) return;
+    unsigned char *base = static_cast<unsigned char *>(p) - 64;
+    // the caller is done with the memory, and every library call that read or wrote it has synchronised its stream
+    cache_put(g_pin_cache, base, *reinterpret_cast<size_t *>(base), kPinCacheLimit, [](void *q) { cudaFreeHost(q); });
 }
 
 int margin_b200_prewarm(void) {
@@ -442,8 +554,9 @@ void margin_b200_destroy(margin_b200_ctx *c) {
     if (c->fwd_sub) margin_b200_destroy(c->fwd_sub);
     c->fwd_sub = nullptr;
     if (c->counted) g_live_contexts[c->device & (kMaxDevices - 1)].fetch_sub(1);
-    cudaSetDevice(c->device);
+    enter_ctx(c);
     cudaStreamSynchronize(c->stream);
+    if (c->stream_sym) cudaStreamSynchronize(c->stream_sym);
     DevBuf *bufs[] = {&c->d_models, &c->d_rsm[0], &c->d_rsm[1], &c->d_symx, &c->d_symy, &c->d_anchors, &c->d_jobs,
                       &c->d_kl, &c->d_kr, &c->d_cell_off, &c->d_job_cells, &c->d_job_maxw, &c->d_job_nseg, &c->d_err,
                       &c->d_segs, &c->d_seg_counts, &c->d_seg_off, &c->d_scan_tmp, &c->d_slot_ring_off, &c->d_ring,
@@ -478,7 +591,7 @@ int margin_b200_set_model(margin_b200_ctx *c, int slot, const margin_b200_model 
     if (!c || !m) return fail("margin_b200_set_model: null argument");
     if (slot < 0 || slot > 1) return fail("margin_b200_set_model: slot must be 0 or 1");
     if (m->rle && m->max_rl != MARGIN_B200_MAX_RL) return fail("margin_b200_set_model: max_rl must be %d", MARGIN_B200_MAX_RL);
-    CU(cudaSetDevice(c->device));
+    CU(enter_ctx(c));
     if (!c->is_sub) {
         if (c->user_models[slot].get() != m) c->user_models[slot].reset(new margin_b200_model(*m));
         for (margin_b200_ctx *sub : c->subs)
@@ -573,7 +686,7 @@ int margin_b200_set_params(margin_b200_ctx *c, const margin_b200_params *p) {
         c->v_thr = std::log(p->threshold);
     } else {
         if (check_device(c->device)) return 1;
-        CU(cudaSetDevice(c->device));
+        CU(enter_ctx(c));
         if (c->d_err.ensure(sizeof(double))) return 1;
         mb::find_log_threshold_kernel<<<1, 1, 0, c->stream>>>(p->threshold, std::log(p->threshold), c->d_err.as<double>());
         CU(cudaMemcpyAsync(&c->v_thr, c->d_err.p, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
@@ -680,7 +793,7 @@ extern "C" int margin_b200_upload_batch(margin_b200_ctx *c, const margin_b200_ba
     if (!c->have_params) return fail("margin_b200_upload_batch: margin_b200_set_params has not been called");
     if (b->n < 0) return fail("margin_b200_upload_batch: negative batch size");
     if (check_device(c->device)) return 1;
-    CU(cudaSetDevice(c->device));
+    CU(enter_ctx(c));
     Trace tr(c);
     const margin_b200_params &p = c->params;
     const int64_t n = b->n;
@@ -1707,7 +1820,7 @@ struct ScratchLease {
 extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_indels, margin_b200_result *out) {
     if (!c || !out) return fail("margin_b200_posteriors_resident: null argument");
     if (check_device(c->device)) return 1;
-    CU(cudaSetDevice(c->device));
+    CU(enter_ctx(c));
     memset(out, 0, sizeof(*out));
     c->last_pipelined = false;
     c->launches = 0;
@@ -1737,10 +1850,7 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
     ScratchLease lease;  // destroyed before the token is released
 
     // forward + backward launches of one pass (all tiles, or the tiles of a repair pass), then the seam guard
-    auto run_dp = [&]() -> int {
-        Bins bins;
-        if (build_bins(c, true, bins, c->force_group)) return 1;
-        tr.mark("bins+h2d");
+    auto run_dp = [&](Bins &bins) -> int {
         CU(cudaStreamWaitEvent(c->stream, c->ev_sym, 0));  // the symbols (upload's second stream) are needed from here on
         launch_forward<8>(c, bins.seq_fwd[0], bins.seq_fwd[1] - bins.seq_fwd[0]);
         launch_forward<16>(c, bins.seq_fwd[1], bins.seq_fwd[2] - bins.seq_fwd[1]);
@@ -1900,9 +2010,33 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
             else any_generic = true;
         }
         stage_stride = c->stage_cells + 1;  // general kernels: private regions (Tile::stage_off)
+        // Everything this context owns is sized and the work lists are built and on their way BEFORE the token is taken:
+        // a context's first batches grow a few dozen buffers, and allocations made while holding the token were paid by
+        // every thread queueing behind it (16 threads' first chunks: waits of up to 8 s for 0.1 s of kernels).
+        {
+            size_t tmp_bytes = 0;
+            CU(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, c->d_seg_counts.as<int64_t>(), c->d_seg_off.as<int64_t>(), 3 * S + 1,
+                                             c->stream));
+            const size_t want_cap = (size_t) cells / (want_indels ? 3 : 6) + 4096;
+            if (c->d_seg_counts.ensure(((size_t) 3 * S + 1) * sizeof(int64_t)) ||
+                c->d_seg_off.ensure(((size_t) 3 * S + 1) * sizeof(int64_t)) ||
+                c->d_off_out.ensure((size_t) 3 * (c->n_aln + 1) * sizeof(int64_t)) || c->d_scan_tmp.ensure(tmp_bytes + 16) ||
+                c->d_class_cells.ensure(16) ||
+                (c->d_out.cap / sizeof(mb::Pair) < want_cap && c->d_out.ensure(want_cap * sizeof(mb::Pair))))
+                return 1;
+            if (delta && S > 0 &&
+                (c->d_esc_counts.ensure(((size_t) 3 * S + 1) * sizeof(int64_t)) || c->d_esc_off.ensure(((size_t) 3 * S + 1) * sizeof(int64_t)) ||
+                 c->d_esc_off_out.ensure((size_t) 3 * (c->n_aln + 1) * sizeof(int64_t)) ||
+                 c->d_esc.ensure(((size_t) cells / 32 + (size_t) 3 * S + 4096) * sizeof(mb::TupleXY))))
+                return 1;
+        }
+        Bins bins;
+        if (build_bins(c, true, bins, c->force_group)) return 1;
+        tr.mark("bins+h2d");
         if (c->take_token && !token.owns_lock()) {
             token = std::unique_lock<std::mutex>(g_compute_token[c->device & (kMaxDevices - 1)]);
             lease.take(c);
+            tr.mark("token");
         }
         bool any_sequential = false;  // whole jobs swept by the general kernels keep their F in the FP64 array
         for (const mb::Tile &t : c->tiles) any_sequential |= !(t.flags & (mb::TILE_BND | mb::TILE_WIDE));
@@ -1917,7 +2051,7 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
             c->d_off_out.ensure((size_t) 3 * (c->n_aln + 1) * sizeof(int64_t)))
             return 1;
         CU(cudaMemsetAsync(c->d_seg_counts.p, 0, ((size_t) 3 * S + 1) * sizeof(int64_t), c->stream));
-        if (run_dp() || finish_pass()) return 1;
+        if (run_dp(bins) || finish_pass()) return 1;
         int failed = *reinterpret_cast<int32_t *>(bounds + 5);
         if (c->guard_stats) guard_report(c, n_seams, attempt);
         if (failed == 0) break;
@@ -1938,7 +2072,9 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
         std::vector<int32_t> flags(pin, pin + n_seams);
         if (repair_tiles(c, flags.data(), c->repair_factor)) {
             tr.mark("repair");
-            if (run_dp() || finish_pass()) return 1;
+            Bins repair_bins;
+            if (build_bins(c, true, repair_bins, c->force_group)) return 1;
+            if (run_dp(repair_bins) || finish_pass()) return 1;
             failed = *reinterpret_cast<int32_t *>(bounds + 5);
             if (c->guard_stats) guard_report(c, n_seams, 100 + attempt);
             c->tile_rerun.clear();
@@ -1979,7 +2115,7 @@ extern "C" int margin_b200_posteriors_resident(margin_b200_ctx *c, int want_inde
 
 extern "C" int margin_b200_download_result(margin_b200_ctx *c, margin_b200_result *out) {
     if (!c || !out) return fail("margin_b200_download_result: null argument");
-    CU(cudaSetDevice(c->device));
+    CU(enter_ctx(c));
     const int64_t n = c->n_aln;
     if (c->h_out.ensure((size_t) (c->total_tuples + 1) * sizeof(mb::Pair)) ||
         c->h_off.ensure((size_t) 3 * (n + 1) * sizeof(int64_t)))
@@ -2155,12 +2291,12 @@ int posteriors_pipelined(margin_b200_ctx *c, const margin_b200_batch *b, int wan
     for (int k = 0; k < K; k++) c->subs[k]->pair_format = fmt;
     PipeShared sh;
     sh.base.assign(K + 1, {0, 0, 0});
-    CU(cudaSetDevice(c->device));
+    CU(enter_ctx(c));
     CU(cudaEventRecord(c->ev0, c->stream));
     auto work = [&](int k) {
         PipeRun &r = runs[k];
         margin_b200_ctx *sub = c->subs[k];
-        cudaSetDevice(c->device);
+        enter_ctx(sub);
         bool released = false;
         auto release = [&]() {
             if (released) return;
@@ -2281,7 +2417,7 @@ static_assert(sizeof(mb::Pair) == sizeof(margin_b200_pair), "tuple layouts must 
 
 extern "C" int margin_b200_last_kernel_ms(margin_b200_ctx *c, float *ms, int32_t *launches, int n_class) {
     if (!c || !ms || !launches) return fail("margin_b200_last_kernel_ms: null argument");
-    CU(cudaSetDevice(c->device));
+    CU(enter_ctx(c));
     CU(cudaStreamSynchronize(c->stream));
     for (int k = 0; k < n_class; k++) {
         ms[k] = 0.f;
@@ -2317,7 +2453,7 @@ extern "C" int margin_b200_last_kernel_ms(margin_b200_ctx *c, float *ms, int32_t
 extern "C" int margin_b200_forward_resident(margin_b200_ctx *c, margin_b200_result *stats) {
     if (!c) return fail("margin_b200_forward_resident: null argument");
     if (check_device(c->device)) return 1;
-    CU(cudaSetDevice(c->device));
+    CU(enter_ctx(c));
     Trace tr(c);
     c->launches = 0;
     c->ev_used = 0;
@@ -2470,7 +2606,7 @@ namespace {
 int forward_batch_fast(margin_b200_ctx *c, const margin_b200_batch *b, double *out_log_prob, margin_b200_result *stats) {
     if (!c->have_params) return fail("margin_b200_forward_batch: margin_b200_set_params has not been called");
     if (check_device(c->device)) return 1;
-    CU(cudaSetDevice(c->device));
+    CU(enter_ctx(c));
     Trace tr(c);
     const int64_t n = b->n;
     const int64_t nx = b->off_x[n], ny = b->off_y[n];
@@ -2757,7 +2893,7 @@ extern "C" int margin_b200_forward_tiny_noalloc(margin_b200_ctx *c, int64_t n, c
     if (!c->have_model[0] && !c->have_model[1]) return fail("margin_b200_forward_tiny_noalloc: no model has been set");
     if (n == 0) return 0;
     if (check_device(c->device)) return 1;
-    CU(cudaSetDevice(c->device));
+    CU(enter_ctx(c));
     unsigned char *scr = nullptr;
     if (noalloc_scratch(c->device, &scr)) return 1;
     if (c->have_model[0] && c->have_model[1] && c->host_models[0].rle != c->host_models[1].rle)

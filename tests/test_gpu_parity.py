@@ -437,3 +437,25 @@ def test_packed_symbols_and_anchor_runs_give_the_plain_results(golden_model):
         al.posteriors_batch(off, False)
     assert len(al.posteriors_batch(plain, False)) == len(items)  # the context is usable afterwards
     al.close()
+
+
+@pytest.mark.gpu
+def test_pinned_blocks_are_recycled_not_returned_to_the_driver():
+    """margin_b200_pinned_free hands a block to the process-wide cache (cudaFreeHost would synchronise the device under
+    every other host thread's feet): the next request of the same size class gets the same memory."""
+    lib = abi.load_library()
+    a = lib.margin_b200_pinned_alloc(3 << 20)  # classes are 2^k x {1, 1.25, 1.5, 1.75}; 64 bytes of header
+    assert a and a % 64 == 0
+    np.ctypeslib.as_array((abi.C.c_uint8 * (3 << 20)).from_address(a))[:] = 7  # writable over its whole length
+    lib.margin_b200_pinned_free(a)
+    again = []  # earlier tests may have left blocks of this class in the cache: a comes back once those are handed out
+    for _ in range(64):
+        again.append(lib.margin_b200_pinned_alloc((3 << 20) + 4096))  # same size class (3 MB + header -> 3.5 MB)
+        if again[-1] == a:
+            break
+    assert a in again and len(set(again)) == len(again)
+    for p in again:
+        lib.margin_b200_pinned_free(p)
+    z = lib.margin_b200_pinned_alloc(0)  # a zero-byte request still returns memory
+    assert z
+    lib.margin_b200_pinned_free(z)
