@@ -309,7 +309,8 @@ def time_polish_synth(contig_kb, threads, seed=42, skip_reference=False, diploid
     """End-to-end `margin polish` on a SYNTHETIC contig of BASELINE configs[1]/[2]'s shape (60x ONT-like 20 kb reads at
     ~10 % error, r94-g360 params, 100 kb chunks; margin_b200/synth.py: write_polish_dataset + oracle/_ref/sam2bam):
     the unmodified reference CLI and the CLI linked against this library, -t `threads` each (the reference
-    parallelises over chunks only, polish.c:476; the binding maps thread t to GPU t % device count).  Mb/hour counts
+    parallelises over chunks only, polish.c:476; the binding adds one of the visible GPUs per 16 threads of the team,
+    compat/pairwiseAligner_b200.c: b200_device_of_thread).  Mb/hour counts
     the whole CLI run: BAM parsing, POA, bubble graph, stitching and FASTA output included."""
     import hashlib
     import subprocess
@@ -341,6 +342,7 @@ def time_polish_synth(contig_kb, threads, seed=42, skip_reference=False, diploid
         if gpus:  # the binding maps OpenMP thread t to device t % (visible devices)
             env["CUDA_VISIBLE_DEVICES"] = ",".join(str(i) for i in range(gpus))
             out["gpus"] = gpus
+            out["devices_used"] = min(gpus, max(1, -(-threads // int(os.environ.get("MARGIN_B200_THREADS_PER_GPU", "16")))))
         if precision:
             env["MARGIN_B200_PRECISION"] = precision
             out["precision"] = precision

@@ -86,11 +86,77 @@ static int b200_prewarmStarted = 0;
 
 static void *b200_prewarm_main(void *arg) {
     (void) arg;
-    margin_b200_prewarm();
+    /* device 0 only: how many devices the run will drive is known when the OpenMP team exists (b200_device_of_thread);
+     * the first thread mapped to another device creates that context itself, beside the others' work */
+    margin_b200_prewarm_devices(1);
     return NULL;
 }
 
+/*
+ * OpenMP thread t -> device.  The aligner is a few per cent of a chunk's wall, so one B200 keeps
+ * well over 16 host threads fed, while every further device costs its primary context (0.5-0.7 s, created one after the
+ * other by the driver), its own scratch pool and its own cold block caches: `margin polish -t 32` on the 2 Mb contig
+ * took 14 s with one device, 14.7 s with four and 26 s with eight when every visible device was used.  So a device is
+ * added per MARGIN_B200_THREADS_PER_GPU threads of the team (default 16), up to the visible devices.
+ */
+static int b200_device_of_thread(int devices) {
+    static int perGpu = 0;
+    if (perGpu == 0) {
+        const char *e = getenv("MARGIN_B200_THREADS_PER_GPU");
+        perGpu = e != NULL && atoi(e) > 0 ? atoi(e) : 16;
+    }
+    int team = omp_get_num_threads(), used = (team + perGpu - 1) / perGpu;
+    if (used > devices) used = devices;
+    if (used < 1) used = 1;
+    return omp_get_thread_num() % used;
+}
+
+/*
+ * A CUDA process pays for every device it can SEE when the driver initialises (measured: context set-up of the first
+ * chunks 0.5 s with one visible B200, 2.4 s with four, about 5 s with eight), whether or not it ever uses them.  The
+ * thread count of a margin run is on its command line (-t / --threads, polish.c:150, phase.c), so before CUDA starts the
+ * visible devices are cut down to the ones b200_device_of_thread will use: the first ceil(threads / 16) of
+ * CUDA_VISIBLE_DEVICES (or of 0, 1, 2, ... when it is unset).  MARGIN_B200_KEEP_VISIBLE_DEVICES=1 leaves the list alone.
+ */
+static void b200_limit_visible_devices(void) {
+    const char *keep = getenv("MARGIN_B200_KEEP_VISIBLE_DEVICES");
+    if (keep != NULL && keep[0] != '0') return;
+    FILE *fh = fopen("/proc/self/cmdline", "rb");
+    if (fh == NULL) return;
+    static char buf[1 << 16];
+    size_t len = fread(buf, 1, sizeof(buf) - 2, fh);
+    fclose(fh);
+    buf[len] = buf[len + 1] = '\0';
+    long threads = 1; /* margin's default */
+    for (char *a = buf; a < buf + len; a += strlen(a) + 1) {
+        const char *value = NULL;
+        if (strcmp(a, "-t") == 0 || strcmp(a, "--threads") == 0) value = a + strlen(a) + 1;
+        else if (strncmp(a, "--threads=", 10) == 0) value = a + 10;
+        else if (a[0] == '-' && a[1] == 't' && a[2] >= '0' && a[2] <= '9') value = a + 2;
+        if (value != NULL && value < buf + len && atol(value) > 0) threads = atol(value);
+    }
+    const char *per = getenv("MARGIN_B200_THREADS_PER_GPU");
+    long perGpu = per != NULL && atol(per) > 0 ? atol(per) : 16, wanted = (threads + perGpu - 1) / perGpu;
+    if (wanted < 1) wanted = 1;
+    if (wanted > 64) return;
+    const char *visible = getenv("CUDA_VISIBLE_DEVICES");
+    char list[1024];
+    size_t at = 0;
+    if (visible == NULL) {
+        for (long d = 0; d < wanted && at + 8 < sizeof(list); d++) at += (size_t) snprintf(list + at, sizeof(list) - at, d ? ",%ld" : "%ld", d);
+    } else {
+        long seen = 0;
+        for (const char *c = visible; *c != '\0' && at + 1 < sizeof(list); c++) {
+            if (*c == ',' && ++seen >= wanted) break;
+            list[at++] = *c;
+        }
+    }
+    list[at] = '\0';
+    setenv("CUDA_VISIBLE_DEVICES", list, 1);
+}
+
 __attribute__((constructor)) static void b200_prewarm_start(void) {
+    b200_limit_visible_devices();
     const char *e = getenv("MARGIN_B200_PREWARM");
     if (e != NULL && e[0] == '0') return;
     if (pthread_create(&b200_prewarmThread, NULL, b200_prewarm_main, NULL) == 0) b200_prewarmStarted = 1;
@@ -105,7 +171,7 @@ static margin_b200_ctx *b200_ctx(void) {
     if (tls.ctx == NULL) {
         int n = margin_b200_device_count();
         if (n <= 0) st_errAbort("margin_b200: no CUDA device; this build of margin has no CPU aligner\n");
-        if (margin_b200_create(&tls.ctx, omp_get_thread_num() % n) != 0) b200_fail();
+        if (margin_b200_create(&tls.ctx, b200_device_of_thread(n)) != 0) b200_fail();
         /* 4-byte step records over PCIe (half of the 8-byte words, a third of the triples: the device->host link is what
          * bounds a box of eight GPUs); b200_list() / b200_pairs() decode them while they walk the lists anyway */
         if (margin_b200_set_pair_format(tls.ctx, MARGIN_B200_PAIRS_DELTA32) != 0) b200_fail();

@@ -242,6 +242,9 @@ int margin_b200_create(margin_b200_ctx **ctx, int device);
  * parses its inputs: `margin polish` reads parameters and BAM records for a second or more before poa_realign
  * (impl/polish.c:476 -> impl/poa.c:1955) needs the aligner).  Returns the device count. */
 int margin_b200_prewarm(void);
+/* The same for devices 0 .. n-1 only (a primary context costs 0.5-0.7 s per B200 and the driver creates them one after
+ * the other: a host program that will drive two of eight GPUs should not wait for eight). */
+int margin_b200_prewarm_devices(int n);
 void margin_b200_destroy(margin_b200_ctx *ctx);
 /* Page-locked host memory for the arrays a batch points at; optional: any host memory works, page-locked memory
  * makes the host->device copies asynchronous and several times faster).  NULL on failure (margin_b200_last_error). */

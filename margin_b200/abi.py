@@ -329,6 +329,8 @@ def load_library():
     lib.margin_b200_device_count.restype = i32
     lib.margin_b200_prewarm.argtypes = []
     lib.margin_b200_prewarm.restype = i32
+    lib.margin_b200_prewarm_devices.argtypes = [i32]
+    lib.margin_b200_prewarm_devices.restype = i32
     lib.margin_b200_version.argtypes = []
     lib.margin_b200_version.restype = i32
     lib.margin_b200_set_model.argtypes = [vp, i32, C.POINTER(Model)]
@@ -375,7 +377,7 @@ EXPORTED_SYMBOLS = [
     "margin_b200_get_precision", "margin_b200_pinned_alloc", "margin_b200_pinned_free", "margin_b200_set_kernel_timing", "margin_b200_posteriors_batch",
     "margin_b200_upload_batch", "margin_b200_posteriors_resident", "margin_b200_download_result",
     "margin_b200_forward_batch", "margin_b200_forward_resident", "margin_b200_forward_tiny_noalloc", "margin_b200_bands",
-    "margin_b200_last_kernel_ms", "margin_b200_device_count", "margin_b200_prewarm",
+    "margin_b200_last_kernel_ms", "margin_b200_device_count", "margin_b200_prewarm", "margin_b200_prewarm_devices",
 ]
 
 KERNEL_CLASSES = ["band", "schedule", "forward", "backward", "scan", "gather", "offsets", "final", "guard"]

@@ -482,10 +482,12 @@ void margin_b200_pinned_free(void *p) {
     cache_put(g_pin_cache, base, *reinterpret_cast<size_t *>(base), kPinCacheLimit, [](void *q) { cudaFreeHost(q); });
 }
 
-int margin_b200_prewarm(void) {
+int margin_b200_prewarm(void) { return margin_b200_prewarm_devices(kMaxDevices); }
+
+int margin_b200_prewarm_devices(int n) {
     int count = 0;
     if (cudaGetDeviceCount(&count) != cudaSuccess) return 0;
-    for (int d = 0; d < count; d++) {
+    for (int d = 0; d < count && d < n; d++) {
         if (cudaSetDevice(d) != cudaSuccess || cudaFree(nullptr) != cudaSuccess) continue;
         // forces the kernel images in (lazy module loading would otherwise do it inside the first batch)
         cudaFuncAttributes fa;

@@ -53,6 +53,10 @@ const char *margin_b200_last_error(void) { return g_err; }
 int margin_b200_version(void) { return 100; }
 int margin_b200_device_count(void) { return 1; }
 int margin_b200_prewarm(void) { return 1; }
+int margin_b200_prewarm_devices(int n) {
+    (void) n;
+    return 1;
+}
 
 void *margin_b200_pinned_alloc(size_t bytes) { return malloc(bytes ? bytes : 1); }
 void margin_b200_pinned_free(void *p) { free(p); }
