@@ -17,6 +17,8 @@
 #include <map>
 #include <memory>
 #include <mutex>
+#include <shared_mutex>
+#include <unordered_set>
 #include <string>
 #include <thread>
 #include <type_traits>
@@ -68,9 +70,11 @@ struct BlockCache {
     std::multimap<size_t, void *> blocks;
     size_t bytes = 0;
 };
-BlockCache g_dev_cache[kMaxDevices], g_pin_cache;
+// Never destroyed: a host program may still hand blocks back while the process is exiting (after static destructors ran).
+BlockCache *const g_dev_cache = new BlockCache[kMaxDevices];
+BlockCache &g_pin_cache = *new BlockCache;
 constexpr size_t kDevCacheLimit = (size_t) 24 << 30, kPinCacheLimit = (size_t) 8 << 30;
-thread_local cudaStream_t tls_streams[2] = {nullptr, nullptr};  // streams of the context this thread is working for
+void quiesce_own_streams();  // waits for the streams of the context this thread last worked for (defined below the context)
 
 inline size_t block_class(size_t bytes) {
     size_t c = 4096;
@@ -105,11 +109,6 @@ inline void cache_trim(BlockCache &cache, size_t keep, FreeFn free_fn) {  // cal
         }
     }
     for (void *p : victims) free_fn(p);
-}
-
-inline void quiesce_own_streams() {
-    for (cudaStream_t st : tls_streams)
-        if (st) cudaStreamSynchronize(st);
 }
 
 template <typename FreeFn>
@@ -327,11 +326,27 @@ struct margin_b200_ctx {
 };
 
 namespace {
+// Contexts whose streams exist.  A thread remembers the context it last worked for; the block caches wait for that
+// context's streams before a block changes hands, unless the context has been destroyed in the meantime.
+std::shared_mutex &g_live_mu = *new std::shared_mutex;  // leaked on purpose, like the caches
+std::unordered_set<const margin_b200_ctx *> &g_live = *new std::unordered_set<const margin_b200_ctx *>;
+thread_local margin_b200_ctx *tls_ctx = nullptr;
+
 // Makes the context's device current and tells the block caches which streams this thread's work runs on.
 inline cudaError_t enter_ctx(margin_b200_ctx *c) {
-    tls_streams[0] = c->stream;
-    tls_streams[1] = c->stream_sym;
+    tls_ctx = c;
     return cudaSetDevice(c->device);
+}
+
+void quiesce_own_streams() {
+    if (!tls_ctx) return;
+    std::shared_lock<std::shared_mutex> lock(g_live_mu);
+    if (!g_live.count(tls_ctx)) {
+        tls_ctx = nullptr;
+        return;
+    }
+    if (tls_ctx->stream) cudaStreamSynchronize(tls_ctx->stream);
+    if (tls_ctx->stream_sym) cudaStreamSynchronize(tls_ctx->stream_sym);
 }
 }  // namespace
 
@@ -510,6 +525,10 @@ int margin_b200_create(margin_b200_ctx **out, int device) {
     c->device = device;
     CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&c->stream_sym, cudaStreamNonBlocking));
+    {
+        std::unique_lock<std::shared_mutex> lock(g_live_mu);
+        g_live.insert(c);
+    }
     CU(cudaEventCreateWithFlags(&c->ev_sym, cudaEventDisableTiming));
     CU(cudaEventCreate(&c->ev0));
     CU(cudaEventCreate(&c->ev1));
@@ -584,6 +603,11 @@ void margin_b200_destroy(margin_b200_ctx *c) {
     cudaEventDestroy(c->ev1);
     cudaStreamSynchronize(c->stream_sym);
     cudaEventDestroy(c->ev_sym);
+    {
+        std::unique_lock<std::shared_mutex> lock(g_live_mu);  // no thread is waiting on these streams from here on
+        g_live.erase(c);
+    }
+    if (tls_ctx == c) tls_ctx = nullptr;
     cudaStreamDestroy(c->stream_sym);
     cudaStreamDestroy(c->stream);
     delete c;
@@ -2194,7 +2218,9 @@ int ensure_subs(margin_b200_ctx *c, int K) {
             int least = 0, greatest = 0;
             CU(cudaDeviceGetStreamPriorityRange(&least, &greatest));
             const int prio = std::min(least, greatest + (int) c->subs.size());
+            std::unique_lock<std::shared_mutex> lock(g_live_mu);
             cudaStreamDestroy(sub->stream);
+            sub->stream = nullptr;
             CU(cudaStreamCreateWithPriority(&sub->stream, cudaStreamNonBlocking, prio));
         }
         c->subs.push_back(sub);
