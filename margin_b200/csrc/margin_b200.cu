@@ -65,9 +65,13 @@ constexpr int kTileThreads = 128;
 // (2^k x {1, 1.25, 1.5, 1.75}) and go back to a process-wide cache instead of to the driver; a block is handed to the
 // cache only after the streams of the releasing thread's context are idle, so its next owner may use it at once.  The
 // caches are trimmed (largest blocks first) only beyond a byte limit or when an allocation fails.
+struct CachedBlock {
+    void *p;
+    bool part;  // a piece of a larger driver allocation (small size classes are allocated 4-16 at a time): never freed
+};
 struct BlockCache {
     std::mutex mu;
-    std::multimap<size_t, void *> blocks;
+    std::multimap<size_t, CachedBlock> blocks;
     size_t bytes = 0;
 };
 // Never destroyed: a host program may still hand blocks back while the process is exiting (after static destructors ran).
@@ -86,14 +90,21 @@ inline size_t block_class(size_t bytes) {
     return c;
 }
 
-inline void *cache_take(BlockCache &cache, size_t cls) {
+// Blocks of a small class come 4-16 to a driver call: sixteen threads' contexts, each with some seventy mostly small
+// buffers, otherwise queue up in the driver's allocator during their first batches.
+inline int blocks_per_allocation(size_t cls) {
+    if (cls > ((size_t) 1 << 20)) return 1;
+    return (int) std::max<size_t>(4, std::min<size_t>(16, ((size_t) 4 << 20) / cls));
+}
+
+inline bool cache_take(BlockCache &cache, size_t cls, CachedBlock &out) {
     std::lock_guard<std::mutex> lock(cache.mu);
     auto it = cache.blocks.find(cls);
-    if (it == cache.blocks.end()) return nullptr;
-    void *p = it->second;
+    if (it == cache.blocks.end()) return false;
+    out = it->second;
     cache.blocks.erase(it);
     cache.bytes -= cls;
-    return p;
+    return true;
 }
 
 template <typename FreeFn>
@@ -101,27 +112,56 @@ inline void cache_trim(BlockCache &cache, size_t keep, FreeFn free_fn) {  // cal
     std::vector<void *> victims;
     {
         std::lock_guard<std::mutex> lock(cache.mu);
-        while (cache.bytes > keep && !cache.blocks.empty()) {
-            auto it = std::prev(cache.blocks.end());
-            victims.push_back(it->second);
+        for (auto it = cache.blocks.end(); cache.bytes > keep && it != cache.blocks.begin();) {
+            --it;
+            if (it->second.part) continue;
+            victims.push_back(it->second.p);
             cache.bytes -= it->first;
-            cache.blocks.erase(it);
+            it = cache.blocks.erase(it);
         }
     }
     for (void *p : victims) free_fn(p);
 }
 
 template <typename FreeFn>
-inline void cache_put(BlockCache &cache, void *p, size_t cls, size_t limit, FreeFn free_fn) {
+inline void cache_put(BlockCache &cache, void *p, bool part, size_t cls, size_t limit, FreeFn free_fn) {
     quiesce_own_streams();
     bool over;
     {
         std::lock_guard<std::mutex> lock(cache.mu);
-        cache.blocks.emplace(cls, p);
+        cache.blocks.emplace(cls, CachedBlock{p, part});
         cache.bytes += cls;
         over = cache.bytes > limit;
     }
     if (over) cache_trim(cache, limit / 2, free_fn);
+}
+
+// A block of class `cls` from the cache, or from the driver (alloc_fn(&ptr, bytes) -> cudaError_t); the surplus blocks of
+// a multi-block allocation go straight into the cache.
+template <typename AllocFn, typename FreeFn>
+inline bool block_take(BlockCache &cache, size_t cls, CachedBlock &out, AllocFn alloc_fn, FreeFn free_fn) {
+    if (cache_take(cache, cls, out)) return true;
+    const int n = blocks_per_allocation(cls);
+    void *base = nullptr;
+    cudaError_t e = alloc_fn(&base, cls * (size_t) n);
+    if (e != cudaSuccess) {  // give the cached blocks back to the driver and try once more, for one block
+        cudaGetLastError();
+        cache_trim(cache, 0, free_fn);
+        e = alloc_fn(&base, cls);
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            return false;
+        }
+        out = CachedBlock{base, false};
+        return true;
+    }
+    out = CachedBlock{base, n > 1};
+    if (n > 1) {
+        std::lock_guard<std::mutex> lock(cache.mu);
+        for (int k = 1; k < n; k++) cache.blocks.emplace(cls, CachedBlock{static_cast<char *>(base) + (size_t) k * cls, true});
+        cache.bytes += cls * (size_t) (n - 1);
+    }
+    return true;
 }
 
 // Grow-only device buffer.
@@ -129,6 +169,7 @@ struct DevBuf {
     void *p = nullptr;
     size_t cap = 0;
     int dev = 0;
+    bool part = false;
     int ensure(size_t bytes) {
         if (bytes <= cap) return 0;
         release();
@@ -136,61 +177,44 @@ struct DevBuf {
         dev &= kMaxDevices - 1;
         // geometric growth: a slightly larger chunk must not re-allocate GBs
         const size_t want = block_class(bytes + bytes / 8 + 256);
-        p = cache_take(g_dev_cache[dev], want);
-        if (!p) {
-            cudaError_t e = cudaMalloc(&p, want);
-            if (e != cudaSuccess) {  // give the cached blocks back to the driver and try once more
-                cudaGetLastError();
-                cache_trim(g_dev_cache[dev], 0, [](void *q) { cudaFree(q); });
-                e = cudaMalloc(&p, want);
-            }
-            if (e != cudaSuccess) {
-                p = nullptr;
-                return fail("cudaMalloc(%zu bytes) failed: %s", want, cudaGetErrorString(e));
-            }
-        }
+        CachedBlock b;
+        if (!block_take(g_dev_cache[dev], want, b, [](void **q, size_t n) { return cudaMalloc(q, n); }, [](void *q) { cudaFree(q); }))
+            return fail("cudaMalloc(%zu bytes) failed", want);
+        p = b.p;
+        part = b.part;
         cap = want;
         return 0;
     }
     void release() {
-        if (p) cache_put(g_dev_cache[dev], p, cap, kDevCacheLimit, [](void *q) { cudaFree(q); });
+        if (p) cache_put(g_dev_cache[dev], p, part, cap, kDevCacheLimit, [](void *q) { cudaFree(q); });
         p = nullptr;
         cap = 0;
     }
     template <typename T> T *as() { return reinterpret_cast<T *>(p); }
 };
 
-inline void *pinned_take(size_t want) {
-    void *p = cache_take(g_pin_cache, want);
-    if (p) return p;
-    cudaError_t e = cudaMallocHost(&p, want);
-    if (e != cudaSuccess) {
-        cudaGetLastError();
-        cache_trim(g_pin_cache, 0, [](void *q) { cudaFreeHost(q); });
-        e = cudaMallocHost(&p, want);
-    }
-    if (e != cudaSuccess) {
-        cudaGetLastError();
-        return nullptr;
-    }
-    return p;
+inline bool pinned_take(size_t want, CachedBlock &out) {
+    return block_take(g_pin_cache, want, out, [](void **q, size_t n) { return cudaMallocHost(q, n); }, [](void *q) { cudaFreeHost(q); });
 }
 
 // Grow-only pinned host buffer.
 struct PinBuf {
     void *p = nullptr;
     size_t cap = 0;
+    bool part = false;
     int ensure(size_t bytes) {
         if (bytes <= cap) return 0;
         release();
         const size_t want = block_class(bytes + bytes / 8 + 256);
-        p = pinned_take(want);
-        if (!p) return fail("cudaMallocHost(%zu bytes) failed", want);
+        CachedBlock b;
+        if (!pinned_take(want, b)) return fail("cudaMallocHost(%zu bytes) failed", want);
+        p = b.p;
+        part = b.part;
         cap = want;
         return 0;
     }
     void release() {
-        if (p) cache_put(g_pin_cache, p, cap, kPinCacheLimit, [](void *q) { cudaFreeHost(q); });
+        if (p) cache_put(g_pin_cache, p, part, cap, kPinCacheLimit, [](void *q) { cudaFreeHost(q); });
         p = nullptr;
         cap = 0;
     }
@@ -479,14 +503,16 @@ int margin_b200_device_count(void) {
 // Page-locked host memory for the caller's batch arrays: cudaMemcpyAsync from pageable memory is staged by the driver
 // (synchronous, a few GB/s); a host program that assembles its batch in memory from here gets true asynchronous copies.
 void *margin_b200_pinned_alloc(size_t bytes) {
-    // one 64-byte header in front of the caller's memory remembers the block's size class for margin_b200_pinned_free
+    // a 64-byte header in front of the caller's memory remembers the block's size class for margin_b200_pinned_free
     const size_t want = block_class(bytes + 64);
-    unsigned char *p = static_cast<unsigned char *>(pinned_take(want));
-    if (!p) {
+    CachedBlock b;
+    if (!pinned_take(want, b)) {
         fail("margin_b200_pinned_alloc: cudaMallocHost(%zu bytes) failed", want);
         return nullptr;
     }
-    *reinterpret_cast<size_t *>(p) = want;
+    unsigned char *p = static_cast<unsigned char *>(b.p);
+    reinterpret_cast<size_t *>(p)[0] = want;
+    reinterpret_cast<size_t *>(p)[1] = b.part ? 1 : 0;
     return p + 64;
 }
 
@@ -494,7 +520,8 @@ void margin_b200_pinned_free(void *p) {
     if (!p) return;
     unsigned char *base = static_cast<unsigned char *>(p) - 64;
     // the caller is done with the memory, and every library call that read or wrote it has synchronised its stream
-    cache_put(g_pin_cache, base, *reinterpret_cast<size_t *>(base), kPinCacheLimit, [](void *q) { cudaFreeHost(q); });
+    cache_put(g_pin_cache, base, reinterpret_cast<size_t *>(base)[1] != 0, reinterpret_cast<size_t *>(base)[0], kPinCacheLimit,
+              [](void *q) { cudaFreeHost(q); });
 }
 
 int margin_b200_prewarm(void) { return margin_b200_prewarm_devices(kMaxDevices); }
