@@ -417,10 +417,10 @@ static void b200_batch_destruct(B200Batch *b) {
         b200_spare.capA = b->capA;
         b200_spare.full = 1;
     } else {
-        margin_b200_pinned_free(b->symX);
-        margin_b200_pinned_free(b->symY);
+        free(b->symX);
+        free(b->symY);
         free(b->anchors);
-        margin_b200_pinned_free(b->anchorsDelta);
+        free(b->anchorsDelta);
         margin_b200_pinned_free(b->runs);
         margin_b200_pinned_free(b->packedX);
         margin_b200_pinned_free(b->packedY);
@@ -441,18 +441,18 @@ static void b200_batch_destruct(B200Batch *b) {
 static void b200_batch_reserve(B200Batch *b, int64_t nX, int64_t nY, int64_t nA) {
     int64_t oX = b->offX[b->n], oY = b->offY[b->n], oA = b->offA[b->n];
     if (nX > b->capX) {
-        b->symX = b200_pinned_grow(b->symX, oX * sizeof(uint16_t), nX * sizeof(uint16_t));
+        b->symX = st_realloc(b->symX, nX * sizeof(uint16_t)); /* fallback forms stay pageable: they travel only when packing fails */
         b->packedX = b200_pinned_grow(b->packedX, oX, nX);
         b->capX = nX;
     }
     if (nY > b->capY) {
-        b->symY = b200_pinned_grow(b->symY, oY * sizeof(uint16_t), nY * sizeof(uint16_t));
+        b->symY = st_realloc(b->symY, nY * sizeof(uint16_t));
         b->packedY = b200_pinned_grow(b->packedY, oY, nY);
         b->capY = nY;
     }
     if (nA > b->capA) {
         b->anchors = st_realloc(b->anchors, nA * 3 * sizeof(int32_t));
-        b->anchorsDelta = b200_pinned_grow(b->anchorsDelta, oA * sizeof(uint32_t), nA * sizeof(uint32_t));
+        b->anchorsDelta = st_realloc(b->anchorsDelta, nA * sizeof(uint32_t));
         b->runs = b200_pinned_grow(b->runs, b->nRuns * sizeof(uint32_t), nA * sizeof(uint32_t));
         b->capA = nA;
     }

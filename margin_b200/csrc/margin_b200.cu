@@ -2170,11 +2170,11 @@ extern "C" int margin_b200_download_result(margin_b200_ctx *c, margin_b200_resul
     if (!c || !out) return fail("margin_b200_download_result: null argument");
     CU(enter_ctx(c));
     const int64_t n = c->n_aln;
-    if (c->h_out.ensure((size_t) (c->total_tuples + 1) * sizeof(mb::Pair)) ||
-        c->h_off.ensure((size_t) 3 * (n + 1) * sizeof(int64_t)))
-        return 1;
     const bool delta = c->fmt_now == MARGIN_B200_PAIRS_DELTA32;
     const size_t tuple_bytes = delta ? sizeof(uint32_t) : (c->packed_now ? sizeof(uint64_t) : sizeof(mb::Pair));
+    // pinned memory is the slowest thing to allocate: exactly what the format needs, not the widest record
+    if (c->h_out.ensure((size_t) (c->total_tuples + 1) * tuple_bytes) || c->h_off.ensure((size_t) 3 * (n + 1) * sizeof(int64_t)))
+        return 1;
     if (delta) {
         if (c->h_esc.ensure((size_t) (c->esc_total + 1) * sizeof(mb::TupleXY)) || c->h_esc_off.ensure((size_t) 3 * (n + 1) * sizeof(int64_t)))
             return 1;
