@@ -165,3 +165,42 @@ def test_filtered_reads_partition_is_batched_and_identical(tmp_path):
     got, log = _filtered_diploid_run(tmp_path, "margin_b200cli")
     assert "margin_b200 partition of filtered reads: 465 forward matrices in one batch" in log
     assert got == EXPECTED_FILTERED_DIPLOID_MD5
+
+
+# Two overlapping chunks polished by two threads at once: batch assembly, the graph built from slabs (observations, node-ordered
+# inserts / deletes), deferred bubble-graph likelihoods, repeat counts and the stitcher, host side only.  Digest of the polished
+# FASTA from the unmodified reference (oracle/_ref/margin_ref -t 2 in this container).
+EXPECTED_TWO_CHUNK_MD5 = "abb95603c7cfc7b48999defb7b3f1464"
+
+
+def _two_chunk_run(tmp_path, binary):
+    import sys
+    sys.path.insert(0, ROOT)
+    from margin_b200 import synth
+    if not (os.path.exists(os.path.join(REF, binary)) and os.path.exists(os.path.join(REF, "sam2bam"))):
+        pytest.skip("oracle/_ref/%s not built (needs /root/reference at build time)" % binary)
+    fa, sam, _, _ = synth.write_polish_dataset(str(tmp_path), 11, 130000, 12, 12000, synth.ONT, 0.01)
+    bam = str(tmp_path / "reads.bam")
+    subprocess.run([os.path.join(REF, "sam2bam"), sam, bam], check=True, stderr=subprocess.DEVNULL)
+    prefix = str(tmp_path / "out")
+    cmd = [os.path.join(REF, binary), "polish", bam, fa,
+           os.path.join(REF, "data", "params", "polish", "ont", "r9.4", "allParams.np.human.r94-g360.json"),
+           "-t", "2", "-o", prefix, "-a", "info"]
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=1500)
+    assert r.returncode == 0, r.stdout[-3000:]
+    return hashlib.md5(open(prefix + ".fa", "rb").read()).hexdigest(), r.stdout
+
+
+def test_two_chunks_two_threads_on_the_cpu_stand_in(tmp_path):
+    """CPU: the binding's host side on a multi-chunk, multi-thread run against oracle/stub_b200.c, FASTA byte-identical to
+    the unmodified reference's."""
+    got, log = _two_chunk_run(tmp_path, "margin_stubcli")
+    assert "Merging results from 2 chunks" in log and "node-ordered commit" in log
+    assert got == EXPECTED_TWO_CHUNK_MD5
+
+
+@pytest.mark.gpu
+def test_two_chunks_two_threads_are_byte_identical(tmp_path):
+    got, log = _two_chunk_run(tmp_path, "margin_b200cli")
+    assert "Merging results from 2 chunks" in log
+    assert got == EXPECTED_TWO_CHUNK_MD5
