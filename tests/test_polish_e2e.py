@@ -204,3 +204,37 @@ def test_two_chunks_two_threads_are_byte_identical(tmp_path):
     got, log = _two_chunk_run(tmp_path, "margin_b200cli")
     assert "Merging results from 2 chunks" in log
     assert got == EXPECTED_TWO_CHUNK_MD5
+
+
+# `margin phase` on the bundled region and its VCF (tests/data/realData in the reference, copied by oracle/Makefile): the
+# bubble graph comes from bubbleGraph_constructFromVCFAndBamChunkReadVcfEntrySubstrings (impl/bubbleGraph.c:1338), which the
+# binding wraps so that its 6 334 forward likelihoods run as one batch.  -p 10000: no down-sampling (lp_solve is stubbed out
+# of the oracle build).  Digests of the phased VCF and the haplotagged BAM from the unmodified reference in this container.
+EXPECTED_PHASE_MD5 = ("4be6af00df7d7c95408bf98f1762c29d", "7c843561f21834b233db361e59e9e1eb")
+
+
+def _phase_run(tmp_path, binary):
+    data = os.path.join(REF, "data")
+    vcf = os.path.join(data, "HG002.r94g360.chr20_59M_100k.vcf")
+    if not (os.path.exists(os.path.join(REF, binary)) and os.path.exists(vcf)):
+        pytest.skip("oracle/_ref/%s or the bundled VCF not there (needs /root/reference at build time)" % binary)
+    prefix = str(tmp_path / "out")
+    cmd = [os.path.join(REF, binary), "phase", os.path.join(data, "HG002.r94g360.chr20_59M_100k.bam"),
+           os.path.join(data, "hg38.chr20_59M_100k.fa"), vcf,
+           os.path.join(data, "params", "phase", "allParams.phase_vcf.ont.json"), "-t", "2", "-p", "10000", "-a", "info", "-o", prefix]
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=1500)
+    assert r.returncode == 0, r.stdout[-3000:]
+    return tuple(hashlib.md5(open(prefix + ext, "rb").read()).hexdigest() for ext in (".phased.vcf", ".haplotagged.bam")), r.stdout
+
+
+def test_margin_phase_on_the_cpu_stand_in(tmp_path):
+    got, log = _phase_run(tmp_path, "margin_stubcli")
+    assert "margin_b200 bubble graph (VCF read substrings): 6334 forward matrices in one batch" in log
+    assert got == EXPECTED_PHASE_MD5
+
+
+@pytest.mark.gpu
+def test_margin_phase_is_batched_and_identical(tmp_path):
+    got, log = _phase_run(tmp_path, "margin_b200cli")
+    assert "margin_b200 bubble graph (VCF read substrings): 6334 forward matrices in one batch" in log
+    assert got == EXPECTED_PHASE_MD5
