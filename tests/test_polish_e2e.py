@@ -238,3 +238,36 @@ def test_margin_phase_is_batched_and_identical(tmp_path):
     got, log = _phase_run(tmp_path, "margin_b200cli")
     assert "margin_b200 bubble graph (VCF read substrings): 6334 forward matrices in one batch" in log
     assert got == EXPECTED_PHASE_MD5
+
+
+# `margin polish --diploid --vcf VCF --onlyVcfAlleles --skipOutputFasta` (no-RLE params): the phasing bubble graphs come from
+# bubbleGraph_constructFromPoaAndVCFOnlyVCFAllele (impl/bubbleGraph.c:1126), the third constructor the binding wraps.
+# Digest of the haplotagged BAM from the unmodified reference in this container.
+EXPECTED_VCF_ALLELES_BAM_MD5 = "7c843561f21834b233db361e59e9e1eb"
+
+
+def _vcf_alleles_run(tmp_path, binary):
+    data = os.path.join(REF, "data")
+    vcf = os.path.join(data, "HG002.r94g360.chr20_59M_100k.vcf")
+    if not (os.path.exists(os.path.join(REF, binary)) and os.path.exists(vcf)):
+        pytest.skip("oracle/_ref/%s or the bundled VCF not there (needs /root/reference at build time)" % binary)
+    prefix = str(tmp_path / "out")
+    cmd = [os.path.join(REF, binary), "polish", os.path.join(data, "HG002.r94g360.chr20_59M_100k.bam"),
+           os.path.join(data, "hg38.chr20_59M_100k.fa"), os.path.join(data, "params", "polish", "misc", "allParams.no_rle.json"),
+           "-t", "2", "-p", "10000", "-2", "-v", vcf, "-A", "-T", "-a", "info", "-o", prefix]
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=1500)
+    assert r.returncode == 0, r.stdout[-3000:]
+    return hashlib.md5(open(prefix + ".haplotagged.bam", "rb").read()).hexdigest(), r.stdout
+
+
+def test_vcf_allele_graphs_on_the_cpu_stand_in(tmp_path):
+    got, log = _vcf_alleles_run(tmp_path, "margin_stubcli")
+    assert "margin_b200 bubble graph (VCF alleles): 4190 forward matrices in one batch" in log
+    assert got == EXPECTED_VCF_ALLELES_BAM_MD5
+
+
+@pytest.mark.gpu
+def test_vcf_allele_graphs_are_batched_and_identical(tmp_path):
+    got, log = _vcf_alleles_run(tmp_path, "margin_b200cli")
+    assert "margin_b200 bubble graph (VCF alleles): 4190 forward matrices in one batch" in log
+    assert got == EXPECTED_VCF_ALLELES_BAM_MD5
