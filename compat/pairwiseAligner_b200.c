@@ -436,6 +436,8 @@ static void b200_batch_destruct(B200Batch *b) {
 }
 
 /* Appends one alignment; anchor x coordinates are shifted by -shiftX (the crop of impl/poa.c:637-639). */
+static void **b200_list_array(stList *list); /* defined with the augment code below */
+
 /* Room for nX / nY symbols and nA anchors in all (the filled parts are kept).  poa_realign knows the totals of a chunk
  * before it adds the first read, so that the page-locked arrays are taken once instead of doubling their way up. */
 static void b200_batch_reserve(B200Batch *b, int64_t nX, int64_t nY, int64_t nA) {
@@ -478,29 +480,39 @@ static void b200_batch_add(B200Batch *b, SymbolString sX, SymbolString sY, stLis
         if ((b->packedX[oX + k] = margin_b200_pack_symbol(sX.sequence[k], rle)) == 255) b->packedOk = 0;
     for (int64_t k = 0; k < sY.length && b->packedOk; k++)
         if ((b->packedY[oY + k] = margin_b200_pack_symbol(sY.sequence[k], rle)) == 255) b->packedOk = 0;
-    for (int64_t k = 0; k < nA; k++) {
-        stIntTuple *a = stList_get(anchorPairs, k);
-        b->anchors[3 * (oA + k)] = (int32_t) (stIntTuple_get(a, 0) - shiftX);
-        b->anchors[3 * (oA + k) + 1] = (int32_t) stIntTuple_get(a, 1);
-        /* anchors may come as pairs (x, y): band_construct then uses p->diagonalExpansion and never reads a third field */
-        b->anchors[3 * (oA + k) + 2] =
-                (tls.dynamicAnchors && stIntTuple_length(a) > 2) ? (int32_t) stIntTuple_get(a, 2) : 0;
-        /* the same anchor as a 4-byte step from its predecessor: a third of the bytes over PCIe */
-        int64_t px = k > 0 ? b->anchors[3 * (oA + k - 1)] : -1, py = k > 0 ? b->anchors[3 * (oA + k - 1) + 1] : -1;
-        uint32_t w = margin_b200_pack_anchor(b->anchors[3 * (oA + k)] - px, b->anchors[3 * (oA + k) + 1] - py,
-                                             b->anchors[3 * (oA + k) + 2]);
-        if (w == 0) b->compactOk = 0;
-        b->anchorsDelta[oA + k] = w;
-        /* and as runs: BAM-derived anchors are one per match column, so most steps are (+1, +1) with the same expansion */
-        int64_t dx = b->anchors[3 * (oA + k)] - px, dy = b->anchors[3 * (oA + k) + 1] - py, e = b->anchors[3 * (oA + k) + 2];
-        if (k > 0 && dx == 1 && dy == 1 && e == b->anchors[3 * (oA + k - 1) + 2] && (b->runs[b->nRuns - 1] & 255u) < 255u &&
-            b->runs[b->nRuns - 1] != 0) {
-            b->runs[b->nRuns - 1]++;
-        } else {
-            uint32_t r = margin_b200_pack_anchor_run(dx, dy, e);
-            if (r == 0) b->runsOk = 0;
-            b->runs[b->nRuns++] = r;
+    {
+        /* an stIntTuple is an int64_t array with its length in front (sonLibTuples.c:32-39; poa.c:601-606 writes into it the
+         * same way), the list's backing array is read directly (b200_list_array): 4.7 M anchors per chunk */
+        void **tuples = nA > 0 ? b200_list_array(anchorPairs) : NULL;
+        int32_t *triples = b->anchors + 3 * oA;
+        uint32_t *steps = b->anchorsDelta + oA, *runs = b->runs;
+        int64_t px = -1, py = -1, pe = -1, nRuns = b->nRuns;
+        const int dynamic = tls.dynamicAnchors;
+        for (int64_t k = 0; k < nA; k++) {
+            const int64_t *a = tuples[k];
+            /* anchors may come as pairs (x, y): band_construct then uses p->diagonalExpansion and never reads a third field */
+            const int64_t x = (int32_t) (a[1] - shiftX), y = (int32_t) a[2], e = (dynamic && a[0] > 2) ? (int32_t) a[3] : 0;
+            triples[3 * k] = (int32_t) x;
+            triples[3 * k + 1] = (int32_t) y;
+            triples[3 * k + 2] = (int32_t) e;
+            const int64_t dx = x - px, dy = y - py;
+            /* the same anchor as a 4-byte step from its predecessor ... */
+            const uint32_t w = margin_b200_pack_anchor(dx, dy, e);
+            if (w == 0) b->compactOk = 0;
+            steps[k] = w;
+            /* ... and as runs: BAM-derived anchors are one per match column, so most steps are (+1, +1) with the same expansion */
+            if (k > 0 && dx == 1 && dy == 1 && e == pe && (runs[nRuns - 1] & 255u) < 255u && runs[nRuns - 1] != 0) {
+                runs[nRuns - 1]++;
+            } else {
+                const uint32_t r = margin_b200_pack_anchor_run(dx, dy, e);
+                if (r == 0) b->runsOk = 0;
+                runs[nRuns++] = r;
+            }
+            px = x;
+            py = y;
+            pe = e;
         }
+        b->nRuns = nRuns;
     }
     b->offR[i + 1] = b->nRuns;
     b->offX[i + 1] = oX + sX.length;
